@@ -1,0 +1,365 @@
+// Fused BatchNorm (+residual) (+ReLU) for NHWC bf16 activations, forward and backward.
+//
+// Replaces slim.batch_norm + ReLU + the residual add/ReLU of the reference's units
+// (reference: core/resnet.py:71,87,126,148,242,373-387; decay/eps from model.py:16-17).
+// Semantics follow TF's fused batch norm: biased variance for normalisation, unbiased
+// variance into the moving average, moving = decay*moving + (1-decay)*batch.
+//
+// Everything is memory bound, so the structure is: one column-reduction pass that reads the
+// tensor once (16-byte vector loads, per-CTA partials in a scratch buffer, deterministic
+// second-level reduce in fp64), and one elementwise pass.
+#include "tdl_common.cuh"
+
+namespace tdl {
+namespace bn {
+
+constexpr int kThreads = 256;
+
+struct ReduceShape {
+  int tx;       // threads across channel-vectors
+  int ty;       // threads across rows
+  int gx;       // CTAs across rows
+  int gy;       // CTAs across channel-vectors
+};
+
+static ReduceShape reduce_shape(int64_t rows, int C) {
+  ReduceShape s;
+  const int c8 = C / 8;
+  s.tx = 1;
+  while (s.tx < 32 && s.tx < c8) s.tx <<= 1;
+  s.ty = kThreads / s.tx;
+  s.gy = (int)cdiv(c8, s.tx);
+  int64_t want = cdiv(rows, (int64_t)s.ty * 4);
+  int64_t cap = (int64_t)num_sms() * 8 / s.gy;
+  if (cap < 1) cap = 1;
+  if (want > cap) want = cap;
+  if (want < 1) want = 1;
+  s.gx = (int)want;
+  return s;
+}
+
+// The one definition of the normalised+activated value, shared by forward and backward so the
+// recomputed ReLU mask in backward matches the forward bit for bit.
+__device__ __forceinline__ float bn_affine(float x, float scale, float shift) { return fmaf(x, scale, shift); }
+
+// ---- forward statistics: per-CTA partial (sum, sumsq) -> scratch[gx][2][C] ----
+__global__ void __launch_bounds__(kThreads)
+bn_partial_stats_kernel(const bf16* __restrict__ x, int64_t rows, int C, int tx, int ty, float* __restrict__ partial) {
+  extern __shared__ float sm[];  // [ty][tx][16]
+  const int cx = threadIdx.x % tx;
+  const int ry = threadIdx.x / tx;
+  const int c8 = C / 8;
+  const int cv = blockIdx.y * tx + cx;
+  float s[8], q[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s[j] = q[j] = 0.f;
+  if (cv < c8) {
+    for (int64_t r = (int64_t)blockIdx.x * ty + ry; r < rows; r += (int64_t)gridDim.x * ty) {
+      float f[8];
+      unpack8(ld8(x + r * C + cv * 8), f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        s[j] += f[j];
+        q[j] = fmaf(f[j], f[j], q[j]);
+      }
+    }
+  }
+  float* mine = sm + (size_t)(ry * tx + cx) * 16;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    mine[j] = s[j];
+    mine[8 + j] = q[j];
+  }
+  __syncthreads();
+  // tx*16 (column, value) pairs are each reduced over the ty row-threads by one thread
+  for (int idx = threadIdx.x; idx < tx * 16; idx += kThreads) {
+    const int col = idx >> 4;
+    const int val = idx & 15;
+    const int cvv = blockIdx.y * tx + col;
+    if (cvv >= c8) continue;
+    float acc = 0.f;
+    for (int t = 0; t < ty; ++t) acc += sm[(size_t)(t * tx + col) * 16 + val];
+    const int which = val >> 3;  // 0 = first statistic, 1 = second
+    const int ch = cvv * 8 + (val & 7);
+    partial[((size_t)blockIdx.x * 2 + which) * C + ch] = acc;
+  }
+}
+
+__global__ void bn_finalize_stats_kernel(const float* __restrict__ partial, int nparts, int C, double inv_n,
+                                         double unbias, const float* __restrict__ gamma,
+                                         const float* __restrict__ beta, float* __restrict__ running_mean,
+                                         float* __restrict__ running_var, float decay, float eps,
+                                         float* __restrict__ mean_out, float* __restrict__ invstd_out,
+                                         float* __restrict__ scale_out, float* __restrict__ shift_out) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  double s = 0.0, q = 0.0;
+  for (int p = 0; p < nparts; ++p) {
+    s += (double)partial[((size_t)p * 2) * C + c];
+    q += (double)partial[((size_t)p * 2 + 1) * C + c];
+  }
+  const double m = s * inv_n;
+  double var = q * inv_n - m * m;
+  if (var < 0.0) var = 0.0;
+  const float invstd = (float)(1.0 / sqrt(var + (double)eps));
+  const float g = gamma ? gamma[c] : 1.f;
+  const float b = beta ? beta[c] : 0.f;
+  const float scale = g * invstd;
+  mean_out[c] = (float)m;
+  invstd_out[c] = invstd;
+  scale_out[c] = scale;
+  shift_out[c] = b - (float)m * scale;
+  if (running_mean) running_mean[c] = decay * running_mean[c] + (1.f - decay) * (float)m;
+  if (running_var) running_var[c] = decay * running_var[c] + (1.f - decay) * (float)(var * unbias);
+}
+
+__global__ void bn_infer_scale_shift_kernel(const float* __restrict__ gamma, const float* __restrict__ beta,
+                                            const float* __restrict__ rm, const float* __restrict__ rv, float eps,
+                                            float* __restrict__ scale, float* __restrict__ shift, int C) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const float invstd = rsqrtf(rv[c] + eps);
+  const float g = gamma ? gamma[c] : 1.f;
+  const float s = g * invstd;
+  scale[c] = s;
+  shift[c] = (beta ? beta[c] : 0.f) - rm[c] * s;
+}
+
+// ---- forward apply: y = relu(x*scale + shift (+ residual)) ----
+__global__ void __launch_bounds__(kThreads)
+bn_apply_kernel(const bf16* __restrict__ x, const float* __restrict__ scale, const float* __restrict__ shift,
+                const bf16* __restrict__ residual, bf16* __restrict__ y, int64_t nvec, int c8, int relu) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
+    const int cv = (int)(i % c8);
+    float f[8];
+    unpack8(ld8(x + i * 8), f);
+    const float4 s0 = *reinterpret_cast<const float4*>(scale + cv * 8);
+    const float4 s1 = *reinterpret_cast<const float4*>(scale + cv * 8 + 4);
+    const float4 h0 = *reinterpret_cast<const float4*>(shift + cv * 8);
+    const float4 h1 = *reinterpret_cast<const float4*>(shift + cv * 8 + 4);
+    const float sc[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+    const float sh[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+#pragma unroll
+    for (int j = 0; j < 8; ++j) f[j] = bn_affine(f[j], sc[j], sh[j]);
+    if (residual) {
+      float r[8];
+      unpack8(ld8(residual + i * 8), r);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] += r[j];
+    }
+    if (relu) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
+    }
+    st8(y + i * 8, pack8(f));
+  }
+}
+
+// ---- backward reduce: dbeta = sum(dy), dgamma = sum(dy * xhat), dy = dz * relu_mask ----
+__global__ void __launch_bounds__(kThreads)
+bn_bwd_partial_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ x, const bf16* __restrict__ z,
+                      const float* __restrict__ scale, const float* __restrict__ shift,
+                      const float* __restrict__ mean, const float* __restrict__ invstd, int64_t rows, int C, int tx,
+                      int ty, int relu, float* __restrict__ partial) {
+  extern __shared__ float sm[];
+  const int cx = threadIdx.x % tx;
+  const int ry = threadIdx.x / tx;
+  const int c8 = C / 8;
+  const int cv = blockIdx.y * tx + cx;
+  float s[8], q[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s[j] = q[j] = 0.f;
+  if (cv < c8) {
+    float sc[8], sh[8], mu[8], is[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      sc[j] = scale[cv * 8 + j];
+      sh[j] = shift[cv * 8 + j];
+      mu[j] = mean[cv * 8 + j];
+      is[j] = invstd[cv * 8 + j];
+    }
+    for (int64_t r = (int64_t)blockIdx.x * ty + ry; r < rows; r += (int64_t)gridDim.x * ty) {
+      float g[8], f[8];
+      unpack8(ld8(dz + r * C + cv * 8), g);
+      unpack8(ld8(x + r * C + cv * 8), f);
+      if (relu) {
+        if (z) {
+          float zz[8];
+          unpack8(ld8(z + r * C + cv * 8), zz);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) g[j] = zz[j] > 0.f ? g[j] : 0.f;
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) g[j] = bn_affine(f[j], sc[j], sh[j]) > 0.f ? g[j] : 0.f;
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        s[j] += g[j];
+        q[j] = fmaf(g[j], (f[j] - mu[j]) * is[j], q[j]);
+      }
+    }
+  }
+  float* mine = sm + (size_t)(ry * tx + cx) * 16;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    mine[j] = s[j];
+    mine[8 + j] = q[j];
+  }
+  __syncthreads();
+  // tx*16 (column, value) pairs are each reduced over the ty row-threads by one thread
+  for (int idx = threadIdx.x; idx < tx * 16; idx += kThreads) {
+    const int col = idx >> 4;
+    const int val = idx & 15;
+    const int cvv = blockIdx.y * tx + col;
+    if (cvv >= c8) continue;
+    float acc = 0.f;
+    for (int t = 0; t < ty; ++t) acc += sm[(size_t)(t * tx + col) * 16 + val];
+    const int which = val >> 3;  // 0 = first statistic, 1 = second
+    const int ch = cvv * 8 + (val & 7);
+    partial[((size_t)blockIdx.x * 2 + which) * C + ch] = acc;
+  }
+}
+
+__global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int nparts, int C,
+                                       float* __restrict__ dbeta, float* __restrict__ dgamma,
+                                       float* __restrict__ acc_dbeta, float* __restrict__ acc_dgamma) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  double s = 0.0, q = 0.0;
+  for (int p = 0; p < nparts; ++p) {
+    s += (double)partial[((size_t)p * 2) * C + c];
+    q += (double)partial[((size_t)p * 2 + 1) * C + c];
+  }
+  dbeta[c] = (float)s;
+  dgamma[c] = (float)q;
+  if (acc_dbeta) acc_dbeta[c] += (float)s;
+  if (acc_dgamma) acc_dgamma[c] += (float)q;
+}
+
+// ---- backward apply: dx = gamma*invstd*(dy - dbeta/n - xhat*dgamma/n); dres = dy ----
+__global__ void __launch_bounds__(kThreads)
+bn_bwd_apply_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ x, const bf16* __restrict__ z,
+                    const float* __restrict__ scale, const float* __restrict__ shift, const float* __restrict__ mean,
+                    const float* __restrict__ invstd, const float* __restrict__ dbeta,
+                    const float* __restrict__ dgamma, float inv_n, bf16* __restrict__ dx, bf16* __restrict__ dres,
+                    int64_t nvec, int c8, int relu) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
+    const int cv = (int)(i % c8);
+    float g[8], f[8];
+    unpack8(ld8(dz + i * 8), g);
+    unpack8(ld8(x + i * 8), f);
+    float zz[8];
+    if (relu && z) unpack8(ld8(z + i * 8), zz);
+    float o[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int c = cv * 8 + j;
+      const float sc = scale[c], sh = shift[c], mu = mean[c], is = invstd[c];
+      if (relu) {
+        const bool on = z ? (zz[j] > 0.f) : (bn_affine(f[j], sc, sh) > 0.f);
+        g[j] = on ? g[j] : 0.f;
+      }
+      const float xhat = (f[j] - mu) * is;
+      // scale == gamma * invstd
+      o[j] = sc * (g[j] - dbeta[c] * inv_n - xhat * dgamma[c] * inv_n);
+    }
+    st8(dx + i * 8, pack8(o));
+    if (dres) st8(dres + i * 8, pack8(g));
+  }
+}
+
+static int ew_blocks(int64_t nvec) {
+  int64_t b = cdiv(nvec, kThreads);
+  const int64_t cap = (int64_t)num_sms() * 16;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return (int)b;
+}
+
+}  // namespace bn
+}  // namespace tdl
+
+using namespace tdl;
+using namespace tdl::bn;
+
+// Number of fp32 scratch elements tdl_bn_fwd_stats / tdl_bn_bwd_reduce need for this shape.
+TDL_API int64_t tdl_bn_scratch_floats(int64_t rows, int C) {
+  if (C <= 0 || C % 8) return -1;
+  ReduceShape s = reduce_shape(rows, C);
+  return (int64_t)s.gx * 2 * C;
+}
+
+// Batch statistics of x[rows, C] -> mean, invstd, and the folded scale/shift; updates the moving averages.
+TDL_API int tdl_bn_fwd_stats(const void* x, int64_t rows, int C, float* scratch, int64_t scratch_floats,
+                             const float* gamma, const float* beta, float* running_mean, float* running_var,
+                             float decay, float eps, float* mean, float* invstd, float* scale, float* shift,
+                             void* stream) {
+  TDL_REQUIRE(C > 0 && C % 8 == 0, "C must be a positive multiple of 8");
+  TDL_REQUIRE(rows > 0, "empty input");
+  ReduceShape s = reduce_shape(rows, C);
+  TDL_REQUIRE(scratch_floats >= (int64_t)s.gx * 2 * C, "scratch too small (see tdl_bn_scratch_floats)");
+  cudaStream_t st = (cudaStream_t)stream;
+  dim3 grid(s.gx, s.gy);
+  bn_partial_stats_kernel<<<grid, kThreads, kThreads * 16 * sizeof(float), st>>>((const bf16*)x, rows, C, s.tx, s.ty,
+                                                                                  scratch);
+  TDL_LAUNCH_OK("bn_partial_stats_kernel");
+  const double unbias = rows > 1 ? (double)rows / (double)(rows - 1) : 1.0;
+  bn_finalize_stats_kernel<<<(C + 127) / 128, 128, 0, st>>>(scratch, s.gx, C, 1.0 / (double)rows, unbias, gamma, beta,
+                                                            running_mean, running_var, decay, eps, mean, invstd, scale,
+                                                            shift);
+  TDL_LAUNCH_OK("bn_finalize_stats_kernel");
+  return 0;
+}
+
+TDL_API int tdl_bn_infer_scale_shift(const float* gamma, const float* beta, const float* running_mean,
+                                     const float* running_var, float eps, float* scale, float* shift, int C,
+                                     void* stream) {
+  bn_infer_scale_shift_kernel<<<(C + 127) / 128, 128, 0, (cudaStream_t)stream>>>(gamma, beta, running_mean,
+                                                                                 running_var, eps, scale, shift, C);
+  TDL_LAUNCH_OK("bn_infer_scale_shift_kernel");
+  return 0;
+}
+
+// y = relu?(x*scale + shift (+ residual))
+TDL_API int tdl_bn_apply(const void* x, const float* scale, const float* shift, const void* residual, void* y,
+                         int64_t rows, int C, int relu, void* stream) {
+  TDL_REQUIRE(C > 0 && C % 8 == 0, "C must be a positive multiple of 8");
+  const int64_t nvec = rows * (C / 8);
+  if (nvec == 0) return 0;
+  bn_apply_kernel<<<ew_blocks(nvec), kThreads, 0, (cudaStream_t)stream>>>(
+      (const bf16*)x, scale, shift, (const bf16*)residual, (bf16*)y, nvec, C / 8, relu);
+  TDL_LAUNCH_OK("bn_apply_kernel");
+  return 0;
+}
+
+// dbeta/dgamma for this layer (written), optionally also accumulated into acc_* (the flat gradient slots).
+TDL_API int tdl_bn_bwd_reduce(const void* dz, const void* x, const void* z, const float* scale, const float* shift,
+                              const float* mean, const float* invstd, int64_t rows, int C, int relu, float* scratch,
+                              int64_t scratch_floats, float* dgamma, float* dbeta, float* acc_dgamma,
+                              float* acc_dbeta, void* stream) {
+  TDL_REQUIRE(C > 0 && C % 8 == 0, "C must be a positive multiple of 8");
+  ReduceShape s = reduce_shape(rows, C);
+  TDL_REQUIRE(scratch_floats >= (int64_t)s.gx * 2 * C, "scratch too small (see tdl_bn_scratch_floats)");
+  cudaStream_t st = (cudaStream_t)stream;
+  dim3 grid(s.gx, s.gy);
+  bn_bwd_partial_kernel<<<grid, kThreads, kThreads * 16 * sizeof(float), st>>>(
+      (const bf16*)dz, (const bf16*)x, (const bf16*)z, scale, shift, mean, invstd, rows, C, s.tx, s.ty, relu, scratch);
+  TDL_LAUNCH_OK("bn_bwd_partial_kernel");
+  bn_bwd_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(scratch, s.gx, C, dbeta, dgamma, acc_dbeta, acc_dgamma);
+  TDL_LAUNCH_OK("bn_bwd_finalize_kernel");
+  return 0;
+}
+
+TDL_API int tdl_bn_bwd_apply(const void* dz, const void* x, const void* z, const float* scale, const float* shift,
+                             const float* mean, const float* invstd, const float* dgamma, const float* dbeta,
+                             void* dx, void* dres, int64_t rows, int C, int relu, void* stream) {
+  TDL_REQUIRE(C > 0 && C % 8 == 0, "C must be a positive multiple of 8");
+  const int64_t nvec = rows * (C / 8);
+  if (nvec == 0) return 0;
+  bn_bwd_apply_kernel<<<ew_blocks(nvec), kThreads, 0, (cudaStream_t)stream>>>(
+      (const bf16*)dz, (const bf16*)x, (const bf16*)z, scale, shift, mean, invstd, dbeta, dgamma,
+      1.f / (float)rows, (bf16*)dx, (bf16*)dres, nvec, C / 8, relu);
+  TDL_LAUNCH_OK("bn_bwd_apply_kernel");
+  return 0;
+}

@@ -1,0 +1,662 @@
+// Convolution as tap-shifted GEMMs on the 5th-gen tensor cores (tcgen05 + TMEM + TMA).
+//
+// Replaces the cuDNN convolutions that the reference reaches through slim.conv2d
+// (reference: core/resnet.py:79-85,130-144,164-166,449-492; core/layers.py:43-49).
+//
+// Design (B200-first, not a cuDNN clone):
+//   * Activations are NHWC bf16, weights are [Cout, R*S, Cin] bf16 ("OHWI").
+//   * A CTA tile of 128 GEMM rows is a (TN x TH x TW) patch of output pixels.  For filter tap
+//     (r, s) the A operand is the input patch shifted by (r*dil - pad, s*dil - pad); ONE 4-D
+//     TMA box fetches it, and TMA's out-of-bounds zero fill *is* the convolution padding.
+//     Stride comes from the tensor map's element strides, dilation from the coordinates.
+//     No im2col buffer, no index math in the mainloop.
+//   * K loop = taps x ceil(Cin/64); every stage is a 128x64 (A) and BLOCK_Nx64 (B) bf16 tile in
+//     128B-swizzled shared memory feeding tcgen05.mma (M=128, N=BLOCK_N, K=16), fp32
+//     accumulators in TMEM, double buffered so the epilogue of tile i overlaps tile i+1.
+//   * Warp roles: warp 0 = TMA producer, warp 1 = TMEM owner + single-thread MMA issuer,
+//     warps 2-5 = epilogue (tcgen05.ld -> bias / residual / ReLU -> bf16 -> global).
+//   * Persistent: grid = #SMs, static round-robin tile schedule with the Cout tile fastest so
+//     CTAs running together share the activation patch in L2.
+//   * wgrad is the transposed problem: both operands are "MN-major" (pixel index is the GEMM K
+//     dimension), split over pixel patches across CTAs, fp32 `red.global.add` into dW.
+#include "tdl_common.cuh"
+
+#include <cudaTypedefs.h>
+
+namespace tdl {
+namespace conv {
+
+// ------------------------------------------------------------------------------------------
+// Host: tensor-map encoding through the driver entry point (no link-time libcuda dependency,
+// so the library also loads on GPU-less build machines).
+// ------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn) return fn;
+  void* p = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+      q != cudaDriverEntryPointSuccess)
+    return nullptr;
+  fn = reinterpret_cast<EncodeTiledFn>(p);
+  return fn;
+}
+
+// dims/box/estr are innermost-first; strides are derived for a dense tensor.
+static int encode_bf16(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint32_t* box,
+                       const uint32_t* estr) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return tdl::fail(-3, "%s%s", "cuTensorMapEncodeTiled entry point unavailable", "");
+  cuuint64_t gdim[5], gstr[5];
+  cuuint32_t b[5], e[5];
+  uint64_t pitch = 2;
+  for (int i = 0; i < rank; ++i) {
+    gdim[i] = dims[i];
+    b[i] = box[i];
+    e[i] = estr[i];
+    pitch *= dims[i];
+    if (i + 1 < rank) gstr[i] = pitch;  // stride of dimension i+1, bytes
+  }
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gdim, gstr, b, e,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    snprintf(tdl::err_buf(), 512,
+             "cuTensorMapEncodeTiled failed (%d): rank %d dims [%llu,%llu,%llu,%llu] box [%u,%u,%u,%u]", (int)r, rank,
+             (unsigned long long)dims[0], (unsigned long long)(rank > 1 ? dims[1] : 0),
+             (unsigned long long)(rank > 2 ? dims[2] : 0), (unsigned long long)(rank > 3 ? dims[3] : 0), box[0],
+             rank > 1 ? box[1] : 0, rank > 2 ? box[2] : 0, rank > 3 ? box[3] : 0);
+    return -4;
+  }
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// Problem description shared by fprop and wgrad.
+// ------------------------------------------------------------------------------------------
+struct Geometry {
+  int N, H, W, C;          // input (as seen by the kernel; the flat 1x1 mode rewrites these)
+  int P, Q, K;             // output spatial size, output channels
+  int R, S;                // filter taps
+  int stride, dil, pad_h, pad_w;
+  int TN, TH, TW;          // pixel patch owned by one GEMM tile (TN*TH*TW <= rows per tile)
+  int tiles_n, tiles_h, tiles_w;
+  int num_kb;              // ceil(C / 64)
+  int n_tiles;             // Cout tiles (fprop)
+  int relu, has_bias, has_res;
+};
+
+// Pick the (TN, TH, TW) pixel patch with the best row utilisation for `rows` GEMM rows.
+static void choose_patch(int N, int P, int Q, int rows, int stride, int* tn, int* th, int* tw) {
+  double best = -1.0;
+  int bn = 1, bh = 1, bw = 1;
+  int max_w = Q < rows ? Q : rows;
+  if (max_w * stride > 256) max_w = 256 / stride;
+  for (int w = 1; w <= max_w; ++w) {
+    int max_h = rows / w;
+    if (max_h > P) max_h = P;
+    if (max_h * stride > 256) max_h = 256 / stride;
+    for (int h = 1; h <= max_h; ++h) {
+      int n = 1;
+      if (w == Q && h == P) {
+        n = rows / (w * h);
+        if (n > N) n = N;
+        if (n < 1) n = 1;
+      }
+      double tiles = (double)tdl::cdiv(N, n) * tdl::cdiv(P, h) * tdl::cdiv(Q, w);
+      double eff = ((double)N * P * Q) / (tiles * rows);
+      // prefer wider patches on ties: longer contiguous runs per TMA row
+      if (eff > best + 1e-9 || (eff > best - 1e-9 && w > bw)) {
+        best = eff;
+        bn = n;
+        bh = h;
+        bw = w;
+      }
+    }
+  }
+  *tn = bn;
+  *th = bh;
+  *tw = bw;
+}
+
+// ------------------------------------------------------------------------------------------
+// fprop kernel
+// ------------------------------------------------------------------------------------------
+constexpr int kBlockM = 128;
+constexpr int kBlockK = 64;                       // bf16 elements = 128 bytes = one swizzle row
+constexpr int kABytes = kBlockM * kBlockK * 2;    // 16 KB
+constexpr int kThreads = 192;                     // 6 warps
+constexpr int kEpiWarp0 = 2;
+
+template <int BLOCK_N>
+struct FpropCfg {
+  static constexpr int kBBytes = BLOCK_N * kBlockK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kStages = (192 * 1024) / kStageBytes;
+  static constexpr int kTmemCols = 2 * BLOCK_N;  // double-buffered accumulator
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+template <int BLOCK_N>
+__global__ void __launch_bounds__(kThreads, 1)
+conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
+                  const Geometry g, bf16* __restrict__ y, const float* __restrict__ bias,
+                  const bf16* __restrict__ residual) {
+  using Cfg = FpropCfg<BLOCK_N>;
+  constexpr int kStages = Cfg::kStages;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + kStages * kABytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes);
+  uint64_t* full_bar = bars;
+  uint64_t* empty_bar = bars + kStages;
+  uint64_t* tmem_full = bars + 2 * kStages;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  const int m_tiles = g.tiles_n * g.tiles_h * g.tiles_w;
+  const int total_tiles = m_tiles * g.n_tiles;
+  const int k_iters = g.R * g.S * g.num_kb;
+  const uint32_t a_tx = (uint32_t)(g.TN * g.TH * g.TW) * 128u;
+  const uint32_t stage_tx = a_tx + (uint32_t)Cfg::kBBytes;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tm_x);
+    ptx::prefetch_tmap(&tm_w);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int i = 0; i < kStages; ++i) {
+        ptx::mbar_init(&full_bar[i], 1);
+        ptx::mbar_init(&empty_bar[i], 1);
+      }
+      for (int i = 0; i < 2; ++i) {
+        ptx::mbar_init(&tmem_full[i], 1);
+        ptx::mbar_init(&tmem_empty[i], 4);  // one arrival per epilogue warp
+      }
+      ptx::fence_mbar_init();
+    }
+    __syncwarp();
+    ptx::tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int n_tile = tile % g.n_tiles;
+        const int m_tile = tile / g.n_tiles;
+        const int tw_i = m_tile % g.tiles_w;
+        const int th_i = (m_tile / g.tiles_w) % g.tiles_h;
+        const int tn_i = m_tile / (g.tiles_w * g.tiles_h);
+        const int w_in = tw_i * g.TW * g.stride - g.pad_w;
+        const int h_in = th_i * g.TH * g.stride - g.pad_h;
+        const int n_in = tn_i * g.TN;
+        for (int it = 0; it < k_iters; ++it) {
+          const int tap = it / g.num_kb;
+          const int kb = it - tap * g.num_kb;
+          const int r = tap / g.S;
+          const int s = tap - r * g.S;
+          ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+          ptx::mbar_expect_tx(&full_bar[stage], stage_tx);
+          ptx::tma_load_4d(smem_a + stage * kABytes, &tm_x, &full_bar[stage], kb * kBlockK, w_in + s * g.dil,
+                           h_in + r * g.dil, n_in);
+          ptx::tma_load_3d(smem_b + stage * Cfg::kBBytes, &tm_w, &full_bar[stage], kb * kBlockK, tap,
+                           n_tile * BLOCK_N);
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (one thread) =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = ptx::umma_idesc_bf16(kBlockM, BLOCK_N, 0, 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        ptx::mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+        ptx::tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BLOCK_N);
+        for (int it = 0; it < k_iters; ++it) {
+          ptx::mbar_wait(&full_bar[stage], phase);
+          ptx::tc_fence_after();
+          const uint64_t a_desc = ptx::umma_smem_desc_sw128(ptx::smem_u32(smem_a + stage * kABytes), 16, 1024);
+          const uint64_t b_desc = ptx::umma_smem_desc_sw128(ptx::smem_u32(smem_b + stage * Cfg::kBBytes), 16, 1024);
+#pragma unroll
+          for (int k = 0; k < kBlockK / 16; ++k) {
+            // advance 16 bf16 (32 bytes) along K inside the 128B swizzle row: +2 in 16-byte units
+            ptx::umma_bf16(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc,
+                           (it > 0 || k > 0) ? 1u : 0u);
+          }
+          ptx::umma_commit(&empty_bar[stage]);  // frees the smem stage when these MMAs retire
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        ptx::umma_commit(&tmem_full[acc]);  // accumulator complete -> epilogue
+        if (++acc == 2) {
+          acc = 0;
+          acc_phase ^= 1;
+        }
+      }
+    }
+  } else {
+    // ===================== epilogue warps =====================
+    const int quarter = warp & 3;  // TMEM lane quarter this warp may access
+    const int row = quarter * 32 + lane;
+    const int patch = g.TH * g.TW;
+    const int dn = row / patch;
+    const int rem = row - dn * patch;
+    const int dh = rem / g.TW;
+    const int dw = rem - dh * g.TW;
+    const bool row_in_patch = row < g.TN * patch;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const int n_tile = tile % g.n_tiles;
+      const int m_tile = tile / g.n_tiles;
+      const int tw_i = m_tile % g.tiles_w;
+      const int th_i = (m_tile / g.tiles_w) % g.tiles_h;
+      const int tn_i = m_tile / (g.tiles_w * g.tiles_h);
+      const int n = tn_i * g.TN + dn;
+      const int p = th_i * g.TH + dh;
+      const int q = tw_i * g.TW + dw;
+      const bool valid = row_in_patch && n < g.N && p < g.P && q < g.Q;
+      const size_t pix = ((size_t)n * g.P + p) * g.Q + q;
+      ptx::mbar_wait(&tmem_full[acc], acc_phase);
+      ptx::tc_fence_after();
+#pragma unroll 1
+      for (int c = 0; c < BLOCK_N / 32; ++c) {
+        uint32_t v[32];
+        ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BLOCK_N + c * 32), v);
+        ptx::tmem_ld_wait();
+        const int co0 = n_tile * BLOCK_N + c * 32;
+        if (valid && co0 < g.K) {
+          bf16* dst = y + pix * g.K + co0;
+          const bf16* res = g.has_res ? residual + pix * g.K + co0 : nullptr;
+#pragma unroll
+          for (int j8 = 0; j8 < 4; ++j8) {
+            if (co0 + j8 * 8 < g.K) {  // K is a multiple of 8
+              float f[8];
+#pragma unroll
+              for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(v[j8 * 8 + j]);
+              if (g.has_bias) {
+                const float4 b0 = *reinterpret_cast<const float4*>(bias + co0 + j8 * 8);
+                const float4 b1 = *reinterpret_cast<const float4*>(bias + co0 + j8 * 8 + 4);
+                f[0] += b0.x; f[1] += b0.y; f[2] += b0.z; f[3] += b0.w;
+                f[4] += b1.x; f[5] += b1.y; f[6] += b1.z; f[7] += b1.w;
+              }
+              if (g.has_res) {
+                float rr[8];
+                unpack8(ld8(res + j8 * 8), rr);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) f[j] += rr[j];
+              }
+              if (g.relu) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
+              }
+              st8(dst + j8 * 8, pack8(f));
+            }
+          }
+        }
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&tmem_empty[acc]);
+      if (++acc == 2) {
+        acc = 0;
+        acc_phase ^= 1;
+      }
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// wgrad kernel:  dW[co, tap, ci] += sum_pixels dY[pixel, co] * X[pixel shifted by tap, ci]
+// GEMM M = Cout (128), N = Cin (BLOCK_N), K = pixels (64 per stage).  Both operands are stored
+// with the GEMM-K (pixel) index as the *row* of a 128B-swizzled tile, i.e. MN-major.
+// ------------------------------------------------------------------------------------------
+constexpr int kWgradStages = 5;
+
+template <int BLOCK_N>
+struct WgradCfg {
+  static constexpr int kABytes = 128 * 64 * 2;        // 2 blocks of [64 px][64 co]
+  static constexpr int kBBytes = BLOCK_N * 64 * 2;    // BLOCK_N/64 blocks of [64 px][64 ci]
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kTmemCols = BLOCK_N < 32 ? 32 : BLOCK_N;
+  static constexpr int kSmemBytes = kWgradStages * kStageBytes + 1024 + 256;
+};
+
+template <int BLOCK_N>
+__global__ void __launch_bounds__(kThreads, 1)
+conv_wgrad_kernel(const __grid_constant__ CUtensorMap tm_dy, const __grid_constant__ CUtensorMap tm_x,
+                  const Geometry g, float* __restrict__ dw, int m_tiles_co, int n_tiles_ci) {
+  using Cfg = WgradCfg<BLOCK_N>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + kWgradStages * Cfg::kABytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kWgradStages * Cfg::kStageBytes);
+  uint64_t* full_bar = bars;
+  uint64_t* empty_bar = bars + kWgradStages;
+  uint64_t* tmem_full = bars + 2 * kWgradStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  // work item
+  int wi = blockIdx.y;
+  const int ci_tile = wi % n_tiles_ci;
+  wi /= n_tiles_ci;
+  const int co_tile = wi % m_tiles_co;
+  const int tap = wi / m_tiles_co;
+  const int r = tap / g.S;
+  const int s = tap - r * g.S;
+
+  const int patches = g.tiles_n * g.tiles_h * g.tiles_w;
+  const int my_iters = (patches - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+  if (my_iters <= 0) return;  // uniform across the CTA
+
+  // Pixel rows a TMA box does not cover must read as zero in BOTH operands for every stage.
+  {
+    uint4 z = make_uint4(0, 0, 0, 0);
+    uint4* p4 = reinterpret_cast<uint4*>(smem);
+    const int n16 = kWgradStages * Cfg::kStageBytes / 16;
+    for (int i = threadIdx.x; i < n16; i += kThreads) p4[i] = z;
+    ptx::fence_proxy_async_smem();
+  }
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tm_dy);
+    ptx::prefetch_tmap(&tm_x);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int i = 0; i < kWgradStages; ++i) {
+        ptx::mbar_init(&full_bar[i], 1);
+        ptx::mbar_init(&empty_bar[i], 1);
+      }
+      ptx::mbar_init(tmem_full, 1);
+      ptx::fence_mbar_init();
+    }
+    __syncwarp();
+    ptx::tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const uint32_t px_bytes = (uint32_t)(g.TN * g.TH * g.TW) * 128u;                 // one 64-channel box
+  const uint32_t stage_tx = px_bytes * (uint32_t)(2 + BLOCK_N / 64);
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int i = 0; i < my_iters; ++i) {
+        const int patch = (int)blockIdx.x + i * (int)gridDim.x;
+        const int tw_i = patch % g.tiles_w;
+        const int th_i = (patch / g.tiles_w) % g.tiles_h;
+        const int tn_i = patch / (g.tiles_w * g.tiles_h);
+        ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+        ptx::mbar_expect_tx(&full_bar[stage], stage_tx);
+        uint8_t* a = smem_a + stage * Cfg::kABytes;
+        uint8_t* b = smem_b + stage * Cfg::kBBytes;
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+          ptx::tma_load_4d(a + h * 8192, &tm_dy, &full_bar[stage], co_tile * 128 + h * 64, tw_i * g.TW, th_i * g.TH,
+                           tn_i * g.TN);
+#pragma unroll
+        for (int h = 0; h < BLOCK_N / 64; ++h)
+          ptx::tma_load_4d(b + h * 8192, &tm_x, &full_bar[stage], ci_tile * BLOCK_N + h * 64,
+                           tw_i * g.TW * g.stride + s * g.dil - g.pad_w,
+                           th_i * g.TH * g.stride + r * g.dil - g.pad_h, tn_i * g.TN);
+        if (++stage == kWgradStages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = ptx::umma_idesc_bf16(128, BLOCK_N, 1, 1);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int i = 0; i < my_iters; ++i) {
+        ptx::mbar_wait(&full_bar[stage], phase);
+        ptx::tc_fence_after();
+        // MN-major SW128: 64-element MN blocks 8192 B apart (LBO), 8-pixel-row groups 1024 B apart (SBO)
+        const uint64_t a_desc = ptx::umma_smem_desc_sw128(ptx::smem_u32(smem_a + stage * Cfg::kABytes), 8192, 1024);
+        const uint64_t b_desc = ptx::umma_smem_desc_sw128(ptx::smem_u32(smem_b + stage * Cfg::kBBytes), 8192, 1024);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          // 16 pixel rows = 2048 bytes = +128 in 16-byte units
+          ptx::umma_bf16(tmem_base, a_desc + (uint64_t)(128 * k), b_desc + (uint64_t)(128 * k), idesc,
+                         (i > 0 || k > 0) ? 1u : 0u);
+        }
+        ptx::umma_commit(&empty_bar[stage]);
+        if (++stage == kWgradStages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      ptx::umma_commit(tmem_full);
+    }
+  } else {
+    const int quarter = warp & 3;
+    const int co = co_tile * 128 + quarter * 32 + lane;
+    ptx::mbar_wait(tmem_full, 0);
+    ptx::tc_fence_after();
+    const int taps = g.R * g.S;
+#pragma unroll 1
+    for (int c = 0; c < BLOCK_N / 32; ++c) {
+      uint32_t v[32];
+      ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(c * 32), v);
+      ptx::tmem_ld_wait();
+      const int ci0 = ci_tile * BLOCK_N + c * 32;
+      if (co < g.K) {
+        float* dst = dw + ((size_t)co * taps + tap) * g.C + ci0;
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (ci0 + j < g.C) atomicAdd(dst + j, __uint_as_float(v[j]));
+      }
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// weight re-layout:  fp32 master [K, R*S, C]  ->  bf16 fprop copy [K, R*S, C]
+//                                              and bf16 dgrad copy [C, R*S (flipped), K]
+// ------------------------------------------------------------------------------------------
+__global__ void weight_prep_kernel(const float* __restrict__ w, bf16* __restrict__ w_fprop,
+                                   bf16* __restrict__ w_dgrad, int K, int taps, int C) {
+  const size_t total = (size_t)K * taps * C;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    const int t = (int)((i / C) % taps);
+    const int k = (int)(i / ((size_t)C * taps));
+    const bf16 v = __float2bfloat16(w[i]);
+    if (w_fprop) w_fprop[i] = v;
+    if (w_dgrad) w_dgrad[((size_t)c * taps + (taps - 1 - t)) * K + k] = v;
+  }
+}
+
+template <int BLOCK_N>
+static int launch_fprop(const CUtensorMap& tx, const CUtensorMap& tw, const Geometry& g, bf16* y, const float* bias,
+                        const bf16* res, cudaStream_t st) {
+  using Cfg = FpropCfg<BLOCK_N>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    TDL_CUDA_OK(cudaFuncSetAttribute(conv_fprop_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     Cfg::kSmemBytes));
+    attr_set = true;
+  }
+  const int total = g.tiles_n * g.tiles_h * g.tiles_w * g.n_tiles;
+  const int grid = total < tdl::num_sms() ? total : tdl::num_sms();
+  conv_fprop_kernel<BLOCK_N><<<grid, kThreads, Cfg::kSmemBytes, st>>>(tx, tw, g, y, bias, res);
+  TDL_LAUNCH_OK("conv_fprop_kernel");
+  return 0;
+}
+
+template <int BLOCK_N>
+static int launch_wgrad(const CUtensorMap& tdy, const CUtensorMap& tx, const Geometry& g, float* dw, cudaStream_t st) {
+  using Cfg = WgradCfg<BLOCK_N>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    TDL_CUDA_OK(cudaFuncSetAttribute(conv_wgrad_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     Cfg::kSmemBytes));
+    attr_set = true;
+  }
+  const int m_tiles = (int)tdl::cdiv(g.K, 128);
+  const int n_tiles = (int)tdl::cdiv(g.C, BLOCK_N);
+  const int items = m_tiles * n_tiles * g.R * g.S;
+  const int patches = g.tiles_n * g.tiles_h * g.tiles_w;
+  int splits = (int)tdl::cdiv(2 * tdl::num_sms(), items);
+  if (splits > patches) splits = patches;
+  if (splits < 1) splits = 1;
+  dim3 grid(splits, items);
+  conv_wgrad_kernel<BLOCK_N><<<grid, kThreads, Cfg::kSmemBytes, st>>>(tdy, tx, g, dw, m_tiles, n_tiles);
+  TDL_LAUNCH_OK("conv_wgrad_kernel");
+  return 0;
+}
+
+}  // namespace conv
+}  // namespace tdl
+
+using namespace tdl;
+using namespace tdl::conv;
+
+// y[N,P,Q,K] = conv(x[N,H,W,C], w[K,R*S,C]) (+bias) (+residual) (ReLU)      bf16 in/out, fp32 accumulate
+TDL_API int tdl_conv2d_fprop_bf16(const void* x, const void* w, void* y, const float* bias, const void* residual,
+                                  int N, int H, int W, int C, int K, int R, int S, int stride, int dil, int pad_h,
+                                  int pad_w, int P, int Q, int relu, void* stream) {
+  TDL_REQUIRE(C % 8 == 0 && K % 8 == 0, "channel counts must be multiples of 8 (16-byte TMA strides)");
+  TDL_REQUIRE(stride >= 1 && stride <= 8 && dil >= 1, "bad stride/dilation");
+  TDL_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(w) & 15) == 0 &&
+                  (reinterpret_cast<uintptr_t>(y) & 15) == 0,
+              "tensors must be 16-byte aligned");
+  Geometry g;
+  memset(&g, 0, sizeof(g));
+  const bool flat = (R == 1 && S == 1 && stride == 1 && pad_h == 0 && pad_w == 0);
+  if (flat) {  // pure GEMM: all pixels form one long row of width N*H*W
+    g.N = 1; g.H = 1; g.W = N * H * W; g.P = 1; g.Q = N * P * Q;
+  } else {
+    g.N = N; g.H = H; g.W = W; g.P = P; g.Q = Q;
+  }
+  g.C = C; g.K = K; g.R = R; g.S = S; g.stride = stride; g.dil = dil; g.pad_h = pad_h; g.pad_w = pad_w;
+  choose_patch(g.N, g.P, g.Q, kBlockM, stride, &g.TN, &g.TH, &g.TW);
+  g.tiles_n = (int)cdiv(g.N, g.TN);
+  g.tiles_h = (int)cdiv(g.P, g.TH);
+  g.tiles_w = (int)cdiv(g.Q, g.TW);
+  g.num_kb = (int)cdiv(C, kBlockK);
+  g.relu = relu; g.has_bias = bias != nullptr; g.has_res = residual != nullptr;
+  const int block_n = K > 128 ? 256 : (K > 64 ? 128 : 64);
+  g.n_tiles = (int)cdiv(K, block_n);
+
+  CUtensorMap tx, tw;
+  {
+    uint64_t dims[4] = {(uint64_t)C, (uint64_t)g.W, (uint64_t)g.H, (uint64_t)g.N};
+    uint32_t box[4] = {64, (uint32_t)(g.TW * stride), (uint32_t)(g.TH * stride), (uint32_t)g.TN};
+    uint32_t es[4] = {1, (uint32_t)stride, (uint32_t)stride, 1};
+    int rc = encode_bf16(&tx, x, 4, dims, box, es);
+    if (rc) return rc;
+  }
+  {
+    uint64_t dims[3] = {(uint64_t)C, (uint64_t)(R * S), (uint64_t)K};
+    uint32_t box[3] = {64, 1, (uint32_t)block_n};
+    uint32_t es[3] = {1, 1, 1};
+    int rc = encode_bf16(&tw, w, 3, dims, box, es);
+    if (rc) return rc;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (block_n == 256) return launch_fprop<256>(tx, tw, g, (bf16*)y, bias, (const bf16*)residual, st);
+  if (block_n == 128) return launch_fprop<128>(tx, tw, g, (bf16*)y, bias, (const bf16*)residual, st);
+  return launch_fprop<64>(tx, tw, g, (bf16*)y, bias, (const bf16*)residual, st);
+}
+
+// dw[K,R*S,C] (fp32) += sum over pixels of dy[N,P,Q,K]^T * shifted x[N,H,W,C].  Caller zeroes dw.
+TDL_API int tdl_conv2d_wgrad_bf16(const void* x, const void* dy, float* dw, int N, int H, int W, int C, int K, int R,
+                                  int S, int stride, int dil, int pad_h, int pad_w, int P, int Q, void* stream) {
+  TDL_REQUIRE(C % 8 == 0 && K % 8 == 0, "channel counts must be multiples of 8 (16-byte TMA strides)");
+  Geometry g;
+  memset(&g, 0, sizeof(g));
+  const bool flat = (R == 1 && S == 1 && stride == 1 && pad_h == 0 && pad_w == 0);
+  if (flat) {
+    g.N = 1; g.H = 1; g.W = N * H * W; g.P = 1; g.Q = N * P * Q;
+  } else {
+    g.N = N; g.H = H; g.W = W; g.P = P; g.Q = Q;
+  }
+  g.C = C; g.K = K; g.R = R; g.S = S; g.stride = stride; g.dil = dil; g.pad_h = pad_h; g.pad_w = pad_w;
+  choose_patch(g.N, g.P, g.Q, 64, stride, &g.TN, &g.TH, &g.TW);
+  g.tiles_n = (int)cdiv(g.N, g.TN);
+  g.tiles_h = (int)cdiv(g.P, g.TH);
+  g.tiles_w = (int)cdiv(g.Q, g.TW);
+  const int block_n = C > 64 ? 128 : 64;
+  CUtensorMap tdy, tx;
+  {
+    uint64_t dims[4] = {(uint64_t)K, (uint64_t)g.Q, (uint64_t)g.P, (uint64_t)g.N};
+    uint32_t box[4] = {64, (uint32_t)g.TW, (uint32_t)g.TH, (uint32_t)g.TN};
+    uint32_t es[4] = {1, 1, 1, 1};
+    int rc = encode_bf16(&tdy, dy, 4, dims, box, es);
+    if (rc) return rc;
+  }
+  {
+    uint64_t dims[4] = {(uint64_t)C, (uint64_t)g.W, (uint64_t)g.H, (uint64_t)g.N};
+    uint32_t box[4] = {64, (uint32_t)(g.TW * stride), (uint32_t)(g.TH * stride), (uint32_t)g.TN};
+    uint32_t es[4] = {1, (uint32_t)stride, (uint32_t)stride, 1};
+    int rc = encode_bf16(&tx, x, 4, dims, box, es);
+    if (rc) return rc;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (block_n == 128) return launch_wgrad<128>(tdy, tx, g, dw, st);
+  return launch_wgrad<64>(tdy, tx, g, dw, st);
+}
+
+// fp32 master weights -> bf16 compute copies (fprop layout and flipped/transposed dgrad layout)
+TDL_API int tdl_conv2d_weight_prep(const float* w, void* w_fprop, void* w_dgrad, int K, int taps, int C,
+                                   void* stream) {
+  const size_t total = (size_t)K * taps * C;
+  if (total == 0) return 0;
+  int blocks = (int)cdiv((int64_t)total, 256);
+  if (blocks > 4 * num_sms()) blocks = 4 * num_sms();
+  weight_prep_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(w, (bf16*)w_fprop, (bf16*)w_dgrad, K, taps, C);
+  TDL_LAUNCH_OK("weight_prep_kernel");
+  return 0;
+}

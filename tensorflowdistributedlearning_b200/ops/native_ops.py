@@ -1,0 +1,233 @@
+"""Thin tensor-level wrappers over the C ABI of ``libtdl_b200.so``.
+
+Each function validates shapes/dtypes, allocates outputs with torch (so CUDA-graph capture and
+the caching allocator keep working) and launches on the *current* torch stream.  Nothing here
+falls back to a torch implementation: if the library or the GPU is missing the call raises.
+The autograd glue lives in ``ops/functional.py``; the plain-torch oracles in ``ops/reference.py``.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional, Tuple
+
+import torch
+
+from .. import _native as N
+
+_i = ctypes.c_int
+_i64 = ctypes.c_int64
+_f = ctypes.c_float
+
+
+def _chk_bf16_nhwc(t: torch.Tensor, name: str):
+    if t.dtype != torch.bfloat16 or not t.is_cuda or not t.is_contiguous():
+        raise ValueError(f"{name} must be a contiguous CUDA bf16 tensor, got {t.dtype} {t.device} contiguous={t.is_contiguous()}")
+
+
+def same_pad(in_size: int, k: int, stride: int, dil: int = 1) -> Tuple[int, int, int]:
+    """TF 'SAME' geometry: (out, pad_before, pad_after).  """
+    out = -(-in_size // stride)
+    k_eff = (k - 1) * dil + 1
+    total = max((out - 1) * stride + k_eff - in_size, 0)
+    return out, total // 2, total - total // 2
+
+
+# --------------------------------------------------------------------------------------------
+# convolution (tcgen05)
+# --------------------------------------------------------------------------------------------
+def conv2d_fprop(x: torch.Tensor, w: torch.Tensor, *, R: int, S: int, stride: int = 1, dil: int = 1,
+                 pad_h: int = 0, pad_w: int = 0, out_hw: Optional[Tuple[int, int]] = None,
+                 bias: Optional[torch.Tensor] = None, residual: Optional[torch.Tensor] = None,
+                 relu: bool = False) -> torch.Tensor:
+    """y[N,P,Q,K] = conv(x[N,H,W,C], w[K, R*S, C]) with fused bias / residual / ReLU epilogue."""
+    _chk_bf16_nhwc(x, "x")
+    _chk_bf16_nhwc(w, "w")
+    n, h, wd, c = x.shape
+    k = w.shape[0]
+    assert w.numel() == k * R * S * c, (w.shape, k, R, S, c)
+    if out_hw is None:
+        p = (h + 2 * pad_h - ((R - 1) * dil + 1)) // stride + 1
+        q = (wd + 2 * pad_w - ((S - 1) * dil + 1)) // stride + 1
+    else:
+        p, q = out_hw
+    y = torch.empty((n, p, q, k), dtype=torch.bfloat16, device=x.device)
+    if residual is not None:
+        _chk_bf16_nhwc(residual, "residual")
+        assert residual.shape == y.shape
+    if bias is not None:
+        assert bias.dtype == torch.float32 and bias.numel() == k and bias.is_contiguous()
+    rc = N.lib().tdl_conv2d_fprop_bf16(N.ptr(x), N.ptr(w), N.ptr(y), N.ptr(bias), N.ptr(residual),
+                                       _i(n), _i(h), _i(wd), _i(c), _i(k), _i(R), _i(S), _i(stride), _i(dil),
+                                       _i(pad_h), _i(pad_w), _i(p), _i(q), _i(int(relu)), N.stream_ptr())
+    N.check(rc, "tdl_conv2d_fprop_bf16")
+    return y
+
+
+def conv2d_wgrad(x: torch.Tensor, dy: torch.Tensor, dw: torch.Tensor, *, R: int, S: int, stride: int = 1,
+                 dil: int = 1, pad_h: int = 0, pad_w: int = 0) -> torch.Tensor:
+    """dw[K, R*S, C] (fp32) += dy^T (*) x.  ``dw`` is accumulated into (zero it for a fresh gradient)."""
+    _chk_bf16_nhwc(x, "x")
+    _chk_bf16_nhwc(dy, "dy")
+    n, h, wd, c = x.shape
+    _, p, q, k = dy.shape
+    assert dw.dtype == torch.float32 and dw.is_contiguous() and dw.numel() == k * R * S * c
+    rc = N.lib().tdl_conv2d_wgrad_bf16(N.ptr(x), N.ptr(dy), N.ptr(dw), _i(n), _i(h), _i(wd), _i(c), _i(k), _i(R),
+                                       _i(S), _i(stride), _i(dil), _i(pad_h), _i(pad_w), _i(p), _i(q), N.stream_ptr())
+    N.check(rc, "tdl_conv2d_wgrad_bf16")
+    return dw
+
+
+def conv2d_weight_prep(w_master: torch.Tensor, w_fprop: Optional[torch.Tensor], w_dgrad: Optional[torch.Tensor],
+                       K: int, taps: int, C: int) -> None:
+    assert w_master.dtype == torch.float32 and w_master.is_contiguous()
+    rc = N.lib().tdl_conv2d_weight_prep(N.ptr(w_master), N.ptr(w_fprop), N.ptr(w_dgrad), _i(K), _i(taps), _i(C),
+                                        N.stream_ptr())
+    N.check(rc, "tdl_conv2d_weight_prep")
+
+
+# --------------------------------------------------------------------------------------------
+# batch norm
+# --------------------------------------------------------------------------------------------
+_scratch = {}
+
+
+def _bn_scratch(rows: int, C: int, device) -> torch.Tensor:
+    need = int(N.lib().tdl_bn_scratch_floats(_i64(rows), _i(C)))
+    if need < 0:
+        raise ValueError(f"BN kernels need C % 8 == 0, got {C}")
+    key = (device, torch.cuda.current_stream().cuda_stream)
+    buf = _scratch.get(key)
+    if buf is None or buf.numel() < need:
+        buf = torch.empty(max(need, 1 << 20), dtype=torch.float32, device=device)
+        _scratch[key] = buf
+    return buf
+
+
+def bn_fwd_stats(x2d: torch.Tensor, gamma, beta, running_mean, running_var, decay: float, eps: float):
+    """x2d: [rows, C] bf16.  Returns (mean, invstd, scale, shift) fp32 and updates the moving stats."""
+    rows, C = x2d.shape
+    dev = x2d.device
+    out = torch.empty((4, C), dtype=torch.float32, device=dev)
+    scratch = _bn_scratch(rows, C, dev)
+    rc = N.lib().tdl_bn_fwd_stats(N.ptr(x2d), _i64(rows), _i(C), N.ptr(scratch), _i64(scratch.numel()), N.ptr(gamma),
+                                  N.ptr(beta), N.ptr(running_mean), N.ptr(running_var), _f(decay), _f(eps),
+                                  N.ptr(out[0]), N.ptr(out[1]), N.ptr(out[2]), N.ptr(out[3]), N.stream_ptr())
+    N.check(rc, "tdl_bn_fwd_stats")
+    return out[0], out[1], out[2], out[3]
+
+
+def bn_infer_scale_shift(gamma, beta, running_mean, running_var, eps: float):
+    C = running_mean.numel()
+    out = torch.empty((2, C), dtype=torch.float32, device=running_mean.device)
+    rc = N.lib().tdl_bn_infer_scale_shift(N.ptr(gamma), N.ptr(beta), N.ptr(running_mean), N.ptr(running_var), _f(eps),
+                                          N.ptr(out[0]), N.ptr(out[1]), _i(C), N.stream_ptr())
+    N.check(rc, "tdl_bn_infer_scale_shift")
+    return out[0], out[1]
+
+
+def bn_apply(x2d, scale, shift, residual2d, relu: bool):
+    rows, C = x2d.shape
+    y = torch.empty_like(x2d)
+    rc = N.lib().tdl_bn_apply(N.ptr(x2d), N.ptr(scale), N.ptr(shift), N.ptr(residual2d), N.ptr(y), _i64(rows), _i(C),
+                              _i(int(relu)), N.stream_ptr())
+    N.check(rc, "tdl_bn_apply")
+    return y
+
+
+def bn_bwd(dz2d, x2d, z2d, scale, shift, mean, invstd, relu: bool, want_dres: bool,
+           acc_dgamma=None, acc_dbeta=None):
+    """Returns (dx, dres_or_None, dgamma, dbeta)."""
+    rows, C = x2d.shape
+    dev = x2d.device
+    scratch = _bn_scratch(rows, C, dev)
+    dgb = torch.empty((2, C), dtype=torch.float32, device=dev)
+    rc = N.lib().tdl_bn_bwd_reduce(N.ptr(dz2d), N.ptr(x2d), N.ptr(z2d), N.ptr(scale), N.ptr(shift), N.ptr(mean),
+                                   N.ptr(invstd), _i64(rows), _i(C), _i(int(relu)), N.ptr(scratch),
+                                   _i64(scratch.numel()), N.ptr(dgb[0]), N.ptr(dgb[1]), N.ptr(acc_dgamma),
+                                   N.ptr(acc_dbeta), N.stream_ptr())
+    N.check(rc, "tdl_bn_bwd_reduce")
+    dx = torch.empty_like(x2d)
+    dres = torch.empty_like(x2d) if want_dres else None
+    rc = N.lib().tdl_bn_bwd_apply(N.ptr(dz2d), N.ptr(x2d), N.ptr(z2d), N.ptr(scale), N.ptr(shift), N.ptr(mean),
+                                  N.ptr(invstd), N.ptr(dgb[0]), N.ptr(dgb[1]), N.ptr(dx), N.ptr(dres), _i64(rows),
+                                  _i(C), _i(int(relu)), N.stream_ptr())
+    N.check(rc, "tdl_bn_bwd_apply")
+    return dx, dres, dgb[0], dgb[1]
+
+
+# --------------------------------------------------------------------------------------------
+# optimizer
+# --------------------------------------------------------------------------------------------
+def lr_schedule_step(global_step: torch.Tensor, lr_state: torch.Tensor, base_lr: float, decay_rate: float = 1.0,
+                     decay_steps: float = 0.0, beta1: float = 0.9, beta2: float = 0.999) -> None:
+    assert global_step.dtype == torch.int64 and lr_state.dtype == torch.float32 and lr_state.numel() >= 2
+    rc = N.lib().tdl_lr_schedule_step(N.ptr(global_step), _f(base_lr), _f(decay_rate), _f(decay_steps), _f(beta1),
+                                      _f(beta2), N.ptr(lr_state), N.stream_ptr())
+    N.check(rc, "tdl_lr_schedule_step")
+
+
+def sgd_momentum_flat(param, grad, mom, shadow, lr_state, momentum: float, weight_decay: float = 0.0,
+                      grad_scale: float = 1.0, zero_grad: bool = True) -> None:
+    n = param.numel()
+    assert param.dtype == torch.float32 and mom.dtype == torch.float32 and grad.numel() == n
+    rc = N.lib().tdl_sgd_momentum_flat(N.ptr(param), N.ptr(grad), N.ptr(mom), N.ptr(shadow), _i64(n), N.ptr(lr_state),
+                                       _f(momentum), _f(weight_decay), _f(grad_scale),
+                                       _i(int(grad.dtype == torch.bfloat16)), _i(int(zero_grad)), N.stream_ptr())
+    N.check(rc, "tdl_sgd_momentum_flat")
+
+
+def adam_flat(param, grad, m1, m2, shadow, lr_state, beta1: float = 0.9, beta2: float = 0.999, eps: float = 1e-8,
+              grad_scale: float = 1.0, zero_grad: bool = True) -> None:
+    n = param.numel()
+    assert param.dtype == torch.float32 and grad.numel() == n
+    rc = N.lib().tdl_adam_flat(N.ptr(param), N.ptr(grad), N.ptr(m1), N.ptr(m2), N.ptr(shadow), _i64(n),
+                               N.ptr(lr_state), _f(beta1), _f(beta2), _f(eps), _f(grad_scale),
+                               _i(int(grad.dtype == torch.bfloat16)), _i(int(zero_grad)), N.stream_ptr())
+    N.check(rc, "tdl_adam_flat")
+
+
+def cast_f32_to_bf16(src: torch.Tensor, dst: torch.Tensor) -> None:
+    rc = N.lib().tdl_cast_f32_to_bf16(N.ptr(src), N.ptr(dst), _i64(src.numel()), N.stream_ptr())
+    N.check(rc, "tdl_cast_f32_to_bf16")
+
+
+# --------------------------------------------------------------------------------------------
+# losses / metrics
+# --------------------------------------------------------------------------------------------
+def lovasz_hinge(logits: torch.Tensor, labels: torch.Tensor, want_grad: bool = True, grad_scale: float = 1.0):
+    """logits, labels: [B, P] fp32.  Returns (loss_per_image[B], dlogits[B,P] or None)."""
+    B, P = logits.shape
+    logits = logits.contiguous().float()
+    labels = labels.contiguous().float()
+    loss = torch.empty(B, dtype=torch.float32, device=logits.device)
+    dl = torch.empty_like(logits) if want_grad else None
+    rc = N.lib().tdl_lovasz_hinge(N.ptr(logits), N.ptr(labels), _i(B), _i(P), _f(grad_scale), N.ptr(loss), N.ptr(dl),
+                                  N.stream_ptr())
+    N.check(rc, "tdl_lovasz_hinge")
+    return loss, dl
+
+
+def seg_metrics(logits: torch.Tensor, labels: torch.Tensor, logit_threshold: float = 0.0,
+                reference_compat: bool = True):
+    B, P = logits.shape
+    logits = logits.contiguous().float()
+    labels = labels.contiguous().float()
+    out = torch.empty((2, B), dtype=torch.float32, device=logits.device)
+    rc = N.lib().tdl_seg_metrics(N.ptr(logits), N.ptr(labels), _i(B), _i(P), _f(logit_threshold),
+                                 _i(int(reference_compat)), N.ptr(out[0]), N.ptr(out[1]), N.stream_ptr())
+    N.check(rc, "tdl_seg_metrics")
+    return out[0], out[1]
+
+
+def softmax_ce(logits: torch.Tensor, labels: torch.Tensor, want_grad: bool = True, grad_scale: float = 1.0,
+               topk: int = 5):
+    """logits [B, classes] fp32, labels [B] int64 -> (loss_rows, dlogits|None, top1, topk) all fp32."""
+    B, C = logits.shape
+    logits = logits.contiguous().float()
+    labels = labels.contiguous().to(torch.int64)
+    out = torch.empty((3, B), dtype=torch.float32, device=logits.device)
+    dl = torch.empty_like(logits) if want_grad else None
+    rc = N.lib().tdl_softmax_ce(N.ptr(logits), N.ptr(labels), _i(B), _i(C), _f(grad_scale), _i(topk), N.ptr(out[0]),
+                                N.ptr(dl), N.ptr(out[1]), N.ptr(out[2]), N.stream_ptr())
+    N.check(rc, "tdl_softmax_ce")
+    return out[0], dl, out[1], out[2]
