@@ -1,0 +1,502 @@
+// Memory-bound spatial ops for NHWC activations: max-pool, global average pool, depthwise
+// convolution, and the reference's `_upsample` (symmetric pad 1 + TF1 legacy bilinear + crop 2).
+//
+// reference call sites: core/resnet.py:241 (max_pool2d 3x3 s2 SAME), :246-248/:464-465 (mean pool),
+// core/layers.py:34-42 + core/xception.py:102-110 (depthwise), core/layers.py:82-109 (_upsample).
+// All kernels move 8 bf16 channels (16 bytes) per thread per access and accumulate in fp32.
+#include "tdl_common.cuh"
+
+namespace tdl {
+namespace spatial {
+
+constexpr int kThreads = 256;
+
+static int grid_for(int64_t work) {
+  int64_t b = cdiv(work, kThreads);
+  const int64_t cap = (int64_t)num_sms() * 16;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return (int)b;
+}
+
+// ------------------------------------------------------------------------------------------
+// max pool (padded cells never win); forward records the winning tap so backward is a gather
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads)
+maxpool_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, uint8_t* __restrict__ idx, int N, int H, int W,
+                   int C, int P, int Q, int k, int stride, int pad_h, int pad_w) {
+  const int c8 = C / 8;
+  const int64_t total = (int64_t)N * P * Q * c8;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int cv = (int)(i % c8);
+    int64_t t = i / c8;
+    const int q = (int)(t % Q); t /= Q;
+    const int p = (int)(t % P);
+    const int n = (int)(t / P);
+    float best[8];
+    int arg[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { best[j] = -INFINITY; arg[j] = 0; }
+    for (int r = 0; r < k; ++r) {
+      const int h = p * stride + r - pad_h;
+      if (h < 0 || h >= H) continue;
+      for (int s = 0; s < k; ++s) {
+        const int w = q * stride + s - pad_w;
+        if (w < 0 || w >= W) continue;
+        float f[8];
+        unpack8(ld8(x + (((int64_t)n * H + h) * W + w) * C + cv * 8), f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (f[j] > best[j]) { best[j] = f[j]; arg[j] = r * k + s; }
+      }
+    }
+    st8(y + i * 8, pack8(best));
+    uint2 packed;
+    packed.x = (uint32_t)arg[0] | ((uint32_t)arg[1] << 8) | ((uint32_t)arg[2] << 16) | ((uint32_t)arg[3] << 24);
+    packed.y = (uint32_t)arg[4] | ((uint32_t)arg[5] << 8) | ((uint32_t)arg[6] << 16) | ((uint32_t)arg[7] << 24);
+    *reinterpret_cast<uint2*>(idx + i * 8) = packed;
+  }
+}
+
+__global__ void __launch_bounds__(kThreads)
+maxpool_bwd_kernel(const bf16* __restrict__ dy, const uint8_t* __restrict__ idx, bf16* __restrict__ dx, int N, int H,
+                   int W, int C, int P, int Q, int k, int stride, int pad_h, int pad_w) {
+  const int c8 = C / 8;
+  const int64_t total = (int64_t)N * H * W * c8;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int cv = (int)(i % c8);
+    int64_t t = i / c8;
+    const int w = (int)(t % W); t /= W;
+    const int h = (int)(t % H);
+    const int n = (int)(t / H);
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    for (int r = 0; r < k; ++r) {
+      const int hp = h + pad_h - r;
+      if (hp < 0 || hp % stride) continue;
+      const int p = hp / stride;
+      if (p >= P) continue;
+      for (int s = 0; s < k; ++s) {
+        const int wq = w + pad_w - s;
+        if (wq < 0 || wq % stride) continue;
+        const int q = wq / stride;
+        if (q >= Q) continue;
+        const int64_t o = ((((int64_t)n * P + p) * Q + q) * c8 + cv) * 8;
+        const uint2 packed = *reinterpret_cast<const uint2*>(idx + o);
+        float g[8];
+        unpack8(ld8(dy + o), g);
+        const int tap = r * k + s;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const uint32_t a = j < 4 ? (packed.x >> (8 * j)) & 0xff : (packed.y >> (8 * (j - 4))) & 0xff;
+          if ((int)a == tap) acc[j] += g[j];
+        }
+      }
+    }
+    st8(dx + i * 8, pack8(acc));
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// global average pool
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads)
+gap_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, int HW, int C) {
+  __shared__ float sm[8][32][8];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c8 = C / 8;
+  const int cv = blockIdx.y * 32 + tx;
+  const int n = blockIdx.x;
+  float s[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s[j] = 0.f;
+  if (cv < c8)
+    for (int r = ty; r < HW; r += 8) {
+      float f[8];
+      unpack8(ld8(x + ((int64_t)n * HW + r) * C + cv * 8), f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s[j] += f[j];
+    }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) sm[ty][tx][j] = s[j];
+  __syncthreads();
+  if (ty == 0 && cv < c8) {
+    float o[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float a = 0.f;
+      for (int t = 0; t < 8; ++t) a += sm[t][tx][j];
+      o[j] = a / (float)HW;
+    }
+    st8(y + (int64_t)n * C + cv * 8, pack8(o));
+  }
+}
+
+__global__ void __launch_bounds__(kThreads)
+gap_bwd_kernel(const bf16* __restrict__ dy, bf16* __restrict__ dx, int64_t total_vec, int HW, int c8) {
+  const float inv = 1.f / (float)HW;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total_vec; i += (int64_t)gridDim.x * blockDim.x) {
+    const int cv = (int)(i % c8);
+    const int64_t n = i / ((int64_t)c8 * HW);
+    float g[8];
+    unpack8(ld8(dy + (n * c8 + cv) * 8), g);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) g[j] *= inv;
+    st8(dx + i * 8, pack8(g));
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// depthwise convolution, weights [R*S, C] fp32
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads)
+depthwise_fwd_kernel(const bf16* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
+                     bf16* __restrict__ y, int N, int H, int W, int C, int P, int Q, int R, int S, int stride,
+                     int dil, int pad_h, int pad_w, int relu) {
+  const int c8 = C / 8;
+  const int64_t total = (int64_t)N * P * Q * c8;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int cv = (int)(i % c8);
+    int64_t t = i / c8;
+    const int q = (int)(t % Q); t /= Q;
+    const int p = (int)(t % P);
+    const int n = (int)(t / P);
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = bias ? bias[cv * 8 + j] : 0.f;
+    for (int r = 0; r < R; ++r) {
+      const int h = p * stride + r * dil - pad_h;
+      if (h < 0 || h >= H) continue;
+      for (int s = 0; s < S; ++s) {
+        const int ww = q * stride + s * dil - pad_w;
+        if (ww < 0 || ww >= W) continue;
+        float f[8];
+        unpack8(ld8(x + (((int64_t)n * H + h) * W + ww) * C + cv * 8), f);
+        const float* wp = w + (int64_t)(r * S + s) * C + cv * 8;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = fmaf(f[j], wp[j], acc[j]);
+      }
+    }
+    if (relu) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] = fmaxf(acc[j], 0.f);
+    }
+    st8(y + i * 8, pack8(acc));
+  }
+}
+
+// dx = sum over taps of (dy masked by relu) * w
+__global__ void __launch_bounds__(kThreads)
+depthwise_bwd_data_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ y, const float* __restrict__ w,
+                          bf16* __restrict__ dx, int N, int H, int W, int C, int P, int Q, int R, int S, int stride,
+                          int dil, int pad_h, int pad_w, int relu) {
+  const int c8 = C / 8;
+  const int64_t total = (int64_t)N * H * W * c8;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int cv = (int)(i % c8);
+    int64_t t = i / c8;
+    const int ww = (int)(t % W); t /= W;
+    const int h = (int)(t % H);
+    const int n = (int)(t / H);
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    for (int r = 0; r < R; ++r) {
+      const int hp = h + pad_h - r * dil;
+      if (hp < 0 || hp % stride) continue;
+      const int p = hp / stride;
+      if (p >= P) continue;
+      for (int s = 0; s < S; ++s) {
+        const int wq = ww + pad_w - s * dil;
+        if (wq < 0 || wq % stride) continue;
+        const int q = wq / stride;
+        if (q >= Q) continue;
+        const int64_t o = ((((int64_t)n * P + p) * Q + q) * c8 + cv) * 8;
+        float g[8];
+        unpack8(ld8(dy + o), g);
+        if (relu) {
+          float yy[8];
+          unpack8(ld8(y + o), yy);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) g[j] = yy[j] > 0.f ? g[j] : 0.f;
+        }
+        const float* wp = w + (int64_t)(r * S + s) * C + cv * 8;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = fmaf(g[j], wp[j], acc[j]);
+      }
+    }
+    st8(dx + i * 8, pack8(acc));
+  }
+}
+
+// dw[tap, c] += sum_pixels dyv * x ; dbias[c] += sum_pixels dyv.  3x3 only (taps <= 9).
+__global__ void __launch_bounds__(kThreads)
+depthwise_bwd_weight_kernel(const bf16* __restrict__ x, const bf16* __restrict__ dy, const bf16* __restrict__ y,
+                            float* __restrict__ dw, float* __restrict__ dbias, int N, int H, int W, int C, int P,
+                            int Q, int R, int S, int stride, int dil, int pad_h, int pad_w, int relu, int tx, int ty) {
+  extern __shared__ float sm[];  // [ty][tx][8]
+  const int cx = threadIdx.x % tx;
+  const int ry = threadIdx.x / tx;
+  const int c8 = C / 8;
+  const int cv = blockIdx.y * tx + cx;
+  const int taps = R * S;
+  float acc[9][8];
+  float accb[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) accb[j] = 0.f;
+#pragma unroll
+  for (int t = 0; t < 9; ++t)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[t][j] = 0.f;
+  const int64_t pixels = (int64_t)N * P * Q;
+  if (cv < c8) {
+    for (int64_t px = (int64_t)blockIdx.x * ty + ry; px < pixels; px += (int64_t)gridDim.x * ty) {
+      const int q = (int)(px % Q);
+      const int p = (int)((px / Q) % P);
+      const int n = (int)(px / ((int64_t)Q * P));
+      float g[8];
+      unpack8(ld8(dy + px * C + cv * 8), g);
+      if (relu) {
+        float yy[8];
+        unpack8(ld8(y + px * C + cv * 8), yy);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) g[j] = yy[j] > 0.f ? g[j] : 0.f;
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) accb[j] += g[j];
+#pragma unroll
+      for (int t = 0; t < 9; ++t) {
+        if (t < taps) {
+          const int r = t / S, s = t - (t / S) * S;
+          const int h = p * stride + r * dil - pad_h;
+          const int ww = q * stride + s * dil - pad_w;
+          if (h >= 0 && h < H && ww >= 0 && ww < W) {
+            float f[8];
+            unpack8(ld8(x + (((int64_t)n * H + h) * W + ww) * C + cv * 8), f);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[t][j] = fmaf(g[j], f[j], acc[t][j]);
+          }
+        }
+      }
+    }
+  }
+  // reduce over ry through shared memory, one statistic (tap or bias) at a time
+  for (int t = 0; t <= taps; ++t) {
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float v = accb[j];
+#pragma unroll
+      for (int u = 0; u < 9; ++u)
+        if (u == t) v = acc[u][j];
+      sm[((size_t)ry * tx + cx) * 8 + j] = v;
+    }
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < tx * 8; idx += kThreads) {
+      const int col = idx >> 3, j = idx & 7;
+      const int cvv = blockIdx.y * tx + col;
+      if (cvv >= c8) continue;
+      float a = 0.f;
+      for (int u = 0; u < ty; ++u) a += sm[((size_t)u * tx + col) * 8 + j];
+      if (t < taps) atomicAdd(dw + (int64_t)t * C + cvv * 8 + j, a);
+      else if (dbias) atomicAdd(dbias + cvv * 8 + j, a);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// `_upsample`: symmetric pad 1 -> legacy bilinear to (OH+4, OW+4) -> crop 2
+// ------------------------------------------------------------------------------------------
+template <typename T> __device__ __forceinline__ float to_f(T v);
+template <> __device__ __forceinline__ float to_f<float>(float v) { return v; }
+template <> __device__ __forceinline__ float to_f<bf16>(bf16 v) { return __bfloat162float(v); }
+template <typename T> __device__ __forceinline__ T from_f(float v);
+template <> __device__ __forceinline__ float from_f<float>(float v) { return v; }
+template <> __device__ __forceinline__ bf16 from_f<bf16>(float v) { return __float2bfloat16(v); }
+
+struct UpCoord {
+  int lo, hi;
+  float w;
+};
+// o: output index in the cropped frame; in: unpadded input size; out: requested output size
+__device__ __forceinline__ UpCoord up_coord(int o, int in, int out) {
+  const int inp = in + 2;
+  const float scale = (float)inp / (float)(out + 4);
+  const float src = (float)(o + 2) * scale;
+  int lo = (int)floorf(src);
+  if (lo > inp - 1) lo = inp - 1;
+  int hi = lo + 1 < inp - 1 ? lo + 1 : inp - 1;
+  UpCoord c;
+  c.w = src - (float)lo;
+  // padded index -> source index (symmetric pad by one == edge replicate)
+  c.lo = min(max(lo - 1, 0), in - 1);
+  c.hi = min(max(hi - 1, 0), in - 1);
+  return c;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+upsample_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int N, int H, int W, int C, int OH, int OW) {
+  const int64_t total = (int64_t)N * OH * OW * C;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    int64_t t = i / C;
+    const int ox = (int)(t % OW); t /= OW;
+    const int oy = (int)(t % OH);
+    const int n = (int)(t / OH);
+    const UpCoord cy = up_coord(oy, H, OH), cx = up_coord(ox, W, OW);
+    const T* base = x + (int64_t)n * H * W * C + c;
+    const float tl = to_f<T>(base[((int64_t)cy.lo * W + cx.lo) * C]);
+    const float tr = to_f<T>(base[((int64_t)cy.lo * W + cx.hi) * C]);
+    const float bl = to_f<T>(base[((int64_t)cy.hi * W + cx.lo) * C]);
+    const float br = to_f<T>(base[((int64_t)cy.hi * W + cx.hi) * C]);
+    const float top = tl + (tr - tl) * cx.w;
+    const float bot = bl + (br - bl) * cx.w;
+    y[i] = from_f<T>(top + (bot - top) * cy.w);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+upsample_bwd_kernel(const T* __restrict__ dy, float* __restrict__ dx, int N, int H, int W, int C, int OH, int OW) {
+  const int64_t total = (int64_t)N * OH * OW * C;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    int64_t t = i / C;
+    const int ox = (int)(t % OW); t /= OW;
+    const int oy = (int)(t % OH);
+    const int n = (int)(t / OH);
+    const UpCoord cy = up_coord(oy, H, OH), cx = up_coord(ox, W, OW);
+    const float g = to_f<T>(dy[i]);
+    float* base = dx + (int64_t)n * H * W * C + c;
+    atomicAdd(base + ((int64_t)cy.lo * W + cx.lo) * C, g * (1.f - cy.w) * (1.f - cx.w));
+    atomicAdd(base + ((int64_t)cy.lo * W + cx.hi) * C, g * (1.f - cy.w) * cx.w);
+    atomicAdd(base + ((int64_t)cy.hi * W + cx.lo) * C, g * cy.w * (1.f - cx.w));
+    atomicAdd(base + ((int64_t)cy.hi * W + cx.hi) * C, g * cy.w * cx.w);
+  }
+}
+
+}  // namespace spatial
+}  // namespace tdl
+
+using namespace tdl;
+using namespace tdl::spatial;
+
+TDL_API int tdl_maxpool_fwd(const void* x, void* y, void* idx_u8, int N, int H, int W, int C, int P, int Q, int k,
+                            int stride, int pad_h, int pad_w, void* stream) {
+  TDL_REQUIRE(C % 8 == 0, "C must be a multiple of 8");
+  TDL_REQUIRE(k * k <= 255, "window too large");
+  const int64_t work = (int64_t)N * P * Q * (C / 8);
+  if (work == 0) return 0;
+  maxpool_fwd_kernel<<<grid_for(work), kThreads, 0, (cudaStream_t)stream>>>((const bf16*)x, (bf16*)y, (uint8_t*)idx_u8,
+                                                                            N, H, W, C, P, Q, k, stride, pad_h, pad_w);
+  TDL_LAUNCH_OK("maxpool_fwd_kernel");
+  return 0;
+}
+
+TDL_API int tdl_maxpool_bwd(const void* dy, const void* idx_u8, void* dx, int N, int H, int W, int C, int P, int Q,
+                            int k, int stride, int pad_h, int pad_w, void* stream) {
+  TDL_REQUIRE(C % 8 == 0, "C must be a multiple of 8");
+  const int64_t work = (int64_t)N * H * W * (C / 8);
+  if (work == 0) return 0;
+  maxpool_bwd_kernel<<<grid_for(work), kThreads, 0, (cudaStream_t)stream>>>((const bf16*)dy, (const uint8_t*)idx_u8,
+                                                                            (bf16*)dx, N, H, W, C, P, Q, k, stride,
+                                                                            pad_h, pad_w);
+  TDL_LAUNCH_OK("maxpool_bwd_kernel");
+  return 0;
+}
+
+TDL_API int tdl_gap_fwd(const void* x, void* y, int N, int HW, int C, void* stream) {
+  TDL_REQUIRE(C % 8 == 0, "C must be a multiple of 8");
+  if (N == 0) return 0;
+  dim3 grid(N, (unsigned)cdiv(C / 8, 32));
+  gap_fwd_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>((const bf16*)x, (bf16*)y, HW, C);
+  TDL_LAUNCH_OK("gap_fwd_kernel");
+  return 0;
+}
+
+TDL_API int tdl_gap_bwd(const void* dy, void* dx, int N, int HW, int C, void* stream) {
+  TDL_REQUIRE(C % 8 == 0, "C must be a multiple of 8");
+  const int64_t total = (int64_t)N * HW * (C / 8);
+  if (total == 0) return 0;
+  gap_bwd_kernel<<<grid_for(total), kThreads, 0, (cudaStream_t)stream>>>((const bf16*)dy, (bf16*)dx, total, HW, C / 8);
+  TDL_LAUNCH_OK("gap_bwd_kernel");
+  return 0;
+}
+
+TDL_API int tdl_depthwise_fwd(const void* x, const float* w, const float* bias, void* y, int N, int H, int W, int C,
+                              int P, int Q, int R, int S, int stride, int dil, int pad_h, int pad_w, int relu,
+                              void* stream) {
+  TDL_REQUIRE(C % 8 == 0, "C must be a multiple of 8");
+  const int64_t work = (int64_t)N * P * Q * (C / 8);
+  if (work == 0) return 0;
+  depthwise_fwd_kernel<<<grid_for(work), kThreads, 0, (cudaStream_t)stream>>>(
+      (const bf16*)x, w, bias, (bf16*)y, N, H, W, C, P, Q, R, S, stride, dil, pad_h, pad_w, relu);
+  TDL_LAUNCH_OK("depthwise_fwd_kernel");
+  return 0;
+}
+
+// dx written; dw[R*S, C] and dbias[C] are accumulated into (caller zeroes them).
+TDL_API int tdl_depthwise_bwd(const void* x, const float* w, const void* dy, const void* y, void* dx, float* dw,
+                              float* dbias, int N, int H, int W, int C, int P, int Q, int R, int S, int stride,
+                              int dil, int pad_h, int pad_w, int relu, void* stream) {
+  TDL_REQUIRE(C % 8 == 0, "C must be a multiple of 8");
+  TDL_REQUIRE(R * S <= 9, "depthwise weight gradient supports up to 9 taps");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dx) {
+    const int64_t work = (int64_t)N * H * W * (C / 8);
+    if (work)
+      depthwise_bwd_data_kernel<<<grid_for(work), kThreads, 0, st>>>((const bf16*)dy, (const bf16*)y, w, (bf16*)dx, N,
+                                                                     H, W, C, P, Q, R, S, stride, dil, pad_h, pad_w,
+                                                                     relu);
+    TDL_LAUNCH_OK("depthwise_bwd_data_kernel");
+  }
+  if (dw) {
+    const int c8 = C / 8;
+    int tx = 1;
+    while (tx < 32 && tx < c8) tx <<= 1;
+    const int ty = kThreads / tx;
+    const int gy = (int)cdiv(c8, tx);
+    const int64_t pixels = (int64_t)N * P * Q;
+    int64_t gx = cdiv(pixels, (int64_t)ty * 8);
+    const int64_t cap = (int64_t)num_sms() * 4 / gy > 0 ? (int64_t)num_sms() * 4 / gy : 1;
+    if (gx > cap) gx = cap;
+    if (gx < 1) gx = 1;
+    dim3 grid((unsigned)gx, gy);
+    depthwise_bwd_weight_kernel<<<grid, kThreads, kThreads * 8 * sizeof(float), st>>>(
+        (const bf16*)x, (const bf16*)dy, (const bf16*)y, dw, dbias, N, H, W, C, P, Q, R, S, stride, dil, pad_h, pad_w,
+        relu, tx, ty);
+    TDL_LAUNCH_OK("depthwise_bwd_weight_kernel");
+  }
+  return 0;
+}
+
+TDL_API int tdl_upsample_fwd(const void* x, void* y, int N, int H, int W, int C, int OH, int OW, int is_bf16,
+                             void* stream) {
+  const int64_t total = (int64_t)N * OH * OW * C;
+  if (total == 0) return 0;
+  if (is_bf16)
+    upsample_fwd_kernel<bf16><<<grid_for(total), kThreads, 0, (cudaStream_t)stream>>>((const bf16*)x, (bf16*)y, N, H, W,
+                                                                                     C, OH, OW);
+  else
+    upsample_fwd_kernel<float><<<grid_for(total), kThreads, 0, (cudaStream_t)stream>>>((const float*)x, (float*)y, N,
+                                                                                      H, W, C, OH, OW);
+  TDL_LAUNCH_OK("upsample_fwd_kernel");
+  return 0;
+}
+
+// dx (fp32, caller-zeroed) += scatter of dy through the same interpolation weights
+TDL_API int tdl_upsample_bwd(const void* dy, float* dx, int N, int H, int W, int C, int OH, int OW, int is_bf16,
+                             void* stream) {
+  const int64_t total = (int64_t)N * OH * OW * C;
+  if (total == 0) return 0;
+  if (is_bf16)
+    upsample_bwd_kernel<bf16><<<grid_for(total), kThreads, 0, (cudaStream_t)stream>>>((const bf16*)dy, dx, N, H, W, C,
+                                                                                     OH, OW);
+  else
+    upsample_bwd_kernel<float><<<grid_for(total), kThreads, 0, (cudaStream_t)stream>>>((const float*)dy, dx, N, H, W,
+                                                                                      C, OH, OW);
+  TDL_LAUNCH_OK("upsample_bwd_kernel");
+  return 0;
+}

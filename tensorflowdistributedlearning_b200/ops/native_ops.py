@@ -231,3 +231,95 @@ def softmax_ce(logits: torch.Tensor, labels: torch.Tensor, want_grad: bool = Tru
                                 N.ptr(dl), N.ptr(out[1]), N.ptr(out[2]), N.stream_ptr())
     N.check(rc, "tdl_softmax_ce")
     return out[0], dl, out[1], out[2]
+
+
+# --------------------------------------------------------------------------------------------
+# spatial ops
+# --------------------------------------------------------------------------------------------
+def maxpool_fwd(x, k, stride, pad_h, pad_w, out_hw):
+    _chk_bf16_nhwc(x, "x")
+    n, h, w, c = x.shape
+    p, q = out_hw
+    y = torch.empty((n, p, q, c), dtype=torch.bfloat16, device=x.device)
+    idx = torch.empty((n, p, q, c), dtype=torch.uint8, device=x.device)
+    rc = N.lib().tdl_maxpool_fwd(N.ptr(x), N.ptr(y), N.ptr(idx), _i(n), _i(h), _i(w), _i(c), _i(p), _i(q), _i(k),
+                                 _i(stride), _i(pad_h), _i(pad_w), N.stream_ptr())
+    N.check(rc, "tdl_maxpool_fwd")
+    return y, idx
+
+
+def maxpool_bwd(dy, idx, in_shape, k, stride, pad_h, pad_w):
+    n, h, w, c = in_shape
+    _, p, q, _ = dy.shape
+    dx = torch.empty(in_shape, dtype=torch.bfloat16, device=dy.device)
+    rc = N.lib().tdl_maxpool_bwd(N.ptr(dy), N.ptr(idx), N.ptr(dx), _i(n), _i(h), _i(w), _i(c), _i(p), _i(q), _i(k),
+                                 _i(stride), _i(pad_h), _i(pad_w), N.stream_ptr())
+    N.check(rc, "tdl_maxpool_bwd")
+    return dx
+
+
+def gap_fwd(x):
+    _chk_bf16_nhwc(x, "x")
+    n, h, w, c = x.shape
+    y = torch.empty((n, c), dtype=torch.bfloat16, device=x.device)
+    rc = N.lib().tdl_gap_fwd(N.ptr(x), N.ptr(y), _i(n), _i(h * w), _i(c), N.stream_ptr())
+    N.check(rc, "tdl_gap_fwd")
+    return y
+
+
+def gap_bwd(dy, in_shape):
+    n, h, w, c = in_shape
+    dx = torch.empty(in_shape, dtype=torch.bfloat16, device=dy.device)
+    rc = N.lib().tdl_gap_bwd(N.ptr(dy), N.ptr(dx), _i(n), _i(h * w), _i(c), N.stream_ptr())
+    N.check(rc, "tdl_gap_bwd")
+    return dx
+
+
+def depthwise_fwd(x, w_rsc, bias, stride, dil, pad_h, pad_w, out_hw, relu):
+    _chk_bf16_nhwc(x, "x")
+    n, h, w, c = x.shape
+    r, s, _ = w_rsc.shape
+    p, q = out_hw
+    wf = w_rsc.float().contiguous()
+    bf = None if bias is None else bias.float().contiguous()
+    y = torch.empty((n, p, q, c), dtype=torch.bfloat16, device=x.device)
+    rc = N.lib().tdl_depthwise_fwd(N.ptr(x), N.ptr(wf), N.ptr(bf), N.ptr(y), _i(n), _i(h), _i(w), _i(c), _i(p), _i(q),
+                                   _i(r), _i(s), _i(stride), _i(dil), _i(pad_h), _i(pad_w), _i(int(relu)),
+                                   N.stream_ptr())
+    N.check(rc, "tdl_depthwise_fwd")
+    return y
+
+
+def depthwise_bwd(x, w_rsc, dy, y, stride, dil, pad_h, pad_w, relu):
+    n, h, w, c = x.shape
+    r, s, _ = w_rsc.shape
+    _, p, q, _ = dy.shape
+    wf = w_rsc.float().contiguous()
+    dx = torch.empty_like(x)
+    dw = torch.zeros((r, s, c), dtype=torch.float32, device=x.device)
+    db = torch.zeros((c,), dtype=torch.float32, device=x.device)
+    rc = N.lib().tdl_depthwise_bwd(N.ptr(x), N.ptr(wf), N.ptr(dy), N.ptr(y), N.ptr(dx), N.ptr(dw), N.ptr(db), _i(n),
+                                   _i(h), _i(w), _i(c), _i(p), _i(q), _i(r), _i(s), _i(stride), _i(dil), _i(pad_h),
+                                   _i(pad_w), _i(int(relu)), N.stream_ptr())
+    N.check(rc, "tdl_depthwise_bwd")
+    return dx, dw, db
+
+
+def upsample_fwd(x, out_hw):
+    n, h, w, c = x.shape
+    oh, ow = out_hw
+    y = torch.empty((n, oh, ow, c), dtype=x.dtype, device=x.device)
+    rc = N.lib().tdl_upsample_fwd(N.ptr(x), N.ptr(y), _i(n), _i(h), _i(w), _i(c), _i(oh), _i(ow),
+                                  _i(int(x.dtype == torch.bfloat16)), N.stream_ptr())
+    N.check(rc, "tdl_upsample_fwd")
+    return y
+
+
+def upsample_bwd(dy, in_shape, out_hw):
+    n, h, w, c = in_shape
+    oh, ow = out_hw
+    dx = torch.zeros(in_shape, dtype=torch.float32, device=dy.device)
+    rc = N.lib().tdl_upsample_bwd(N.ptr(dy), N.ptr(dx), _i(n), _i(h), _i(w), _i(c), _i(oh), _i(ow),
+                                  _i(int(dy.dtype == torch.bfloat16)), N.stream_ptr())
+    N.check(rc, "tdl_upsample_bwd")
+    return dx.to(dy.dtype)

@@ -1,0 +1,81 @@
+"""Pooling ops (NHWC): 3x3/s2 SAME max-pool and global average pool.
+
+reference call sites: core/resnet.py:241 (max_pool2d SAME), :246-248 and :464-465 (reduce_mean).
+"""
+from __future__ import annotations
+
+import torch
+
+from . import functional as TF
+from . import reference as R
+
+
+class _MaxPoolNative(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, k, stride, pads, out_hw):
+        from . import native_ops as O
+
+        y, idx = O.maxpool_fwd(x, k, stride, pads[0], pads[2], out_hw)
+        TF._count(1)
+        ctx.save_for_backward(idx)
+        ctx.cfg = (k, stride, pads, tuple(x.shape))
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        from . import native_ops as O
+
+        (idx,) = ctx.saved_tensors
+        k, stride, pads, in_shape = ctx.cfg
+        dx = O.maxpool_bwd(dy.contiguous(), idx, in_shape, k, stride, pads[0], pads[2])
+        TF._count(1)
+        return dx, None, None, None, None
+
+
+def max_pool_same(x: torch.Tensor, k: int = 3, stride: int = 2) -> torch.Tensor:
+    n, h, w, c = x.shape
+    P, Q, pt, pb, pl, pr = TF.conv_pads(h, w, k, k, stride, 1, "SAME")
+    if TF._native_ok(x) and c % 8 == 0:
+        return _MaxPoolNative.apply(x.contiguous(), k, stride, (pt, pb, pl, pr), (P, Q))
+    return R.max_pool_same_nhwc(x, k, stride)
+
+
+class _GapNative(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        from . import native_ops as O
+
+        ctx.shape = x.shape
+        TF._count(1)
+        return O.gap_fwd(x)
+
+    @staticmethod
+    def backward(ctx, dy):
+        from . import native_ops as O
+
+        TF._count(1)
+        return O.gap_bwd(dy.contiguous(), ctx.shape)
+
+
+def global_avg_pool(x: torch.Tensor, keepdims: bool = True) -> torch.Tensor:
+    """mean over H, W of NHWC -> [N,1,1,C] (keepdims) or [N,C]."""
+    n, h, w, c = x.shape
+    if TF._native_ok(x) and c % 8 == 0:
+        y = _GapNative.apply(x.contiguous())
+    else:
+        y = x.float().mean((1, 2)).to(x.dtype)
+    return y.view(n, 1, 1, c) if keepdims else y
+
+
+def max_pool(x: torch.Tensor, k: int, stride: int, pads) -> torch.Tensor:
+    """Max-pool with explicit (top, bottom, left, right) padding (padded cells never win)."""
+    n, h, w, c = x.shape
+    pt, pb, pl, pr = pads
+    P = (h + pt + pb - k) // stride + 1
+    Q = (w + pl + pr - k) // stride + 1
+    if TF._native_ok(x) and c % 8 == 0:
+        return _MaxPoolNative.apply(x.contiguous(), k, stride, (pt, pb, pl, pr), (P, Q))
+    import torch.nn.functional as F
+
+    xin = F.pad(x.permute(0, 3, 1, 2), (pl, pr, pt, pb), value=float("-inf"))
+    return F.max_pool2d(xin, k, stride).permute(0, 2, 3, 1)
