@@ -1,0 +1,316 @@
+// Tower-gradient average fused with the optimizer, over NVLink peer memory.  No NCCL on this path.
+//
+// Replaces MirroredStrategy's packed NCCL all-reduce + per-mirror ApplyAdam
+// (reference: model.py:115-119,462-467; log line "batch_all_reduce ... nccl, num_packs = 1",
+// Test.ipynb:200).  Every rank maps every peer's gradient bucket, parameter bucket and signal pad
+// (cudaIpc handles exchanged once at start-up), then one kernel per bucket does:
+//
+//   one-shot (small buckets): barrier -> each rank reads all N peers' gradients (16-byte peer
+//       loads), sums in a fixed rank order in fp32, applies 1/N and the optimizer to its own
+//       replica -> barrier -> clears its gradient.  One signal round-trip of latency.
+//   two-shot (large buckets): barrier -> rank r reduces slice r from all peers (reduce-scatter),
+//       runs the optimizer on that slice only (optimizer state is touched shard-wise), and stores
+//       the updated fp32 weights straight into every peer's parameter bucket (all-gather) ->
+//       barrier -> clears its gradient.  Wire bytes per GPU and direction: (N-1)/N * bucket.
+//
+// Signals are per-(CTA, source-rank) epoch counters written with st.release.sys and polled with
+// ld.acquire.sys; epochs only ever grow, so there is no reset and no ABA, and they live in device
+// memory so a captured CUDA graph replays correctly.  A spin that exceeds ~2 s traps with the
+// rank / CTA / peer it was waiting for (failure detection instead of a silent hang).
+#include "tdl_common.cuh"
+
+namespace tdl {
+namespace p2p {
+
+constexpr int kMaxWorld = 8;
+constexpr int kMaxBlocks = 256;
+constexpr int kThreads = 512;
+
+struct Comm {
+  int world, rank;
+  float* grad[kMaxWorld];      // peer-mapped gradient buckets (fp32 or bf16 storage, same offsets everywhere)
+  float* param[kMaxWorld];     // peer-mapped fp32 master weights
+  uint32_t* flags[kMaxWorld];  // peer-mapped signal pads: [kMaxBlocks][kMaxWorld] u32
+  uint32_t* epoch;             // local: [kMaxBlocks] u32, last epoch used by each CTA
+  int emulate;                 // 1: all "peers" live on this GPU and ranks are launched one after another
+};
+
+enum OptKind { kNone = 0, kSgdMomentum = 1, kAdam = 2 };
+
+struct StepArgs {
+  int64_t offset;   // first element of the bucket inside the flat buffers
+  int64_t n;        // elements in the bucket
+  int kind;
+  int grad_is_bf16;
+  int zero_grad;
+  float* m1;        // momentum / Adam m (local, full-size flat buffer)
+  float* m2;        // Adam v
+  const float* lr_state;
+  float a, b, c;    // sgd: momentum, weight_decay, -    adam: beta1, beta2, eps
+  float grad_scale; // applied on top of the 1/N tower mean
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// CTA-level barrier across ranks: CTA b of every rank meets CTA b of every other rank.
+__device__ __forceinline__ void cross_rank_barrier(const Comm& cm, uint32_t epoch) {
+  __syncthreads();
+  if (!cm.emulate && threadIdx.x < cm.world) {
+    const int peer = threadIdx.x;
+    st_release_sys(cm.flags[peer] + (size_t)blockIdx.x * kMaxWorld + cm.rank, epoch);
+    const uint32_t* mine = cm.flags[cm.rank] + (size_t)blockIdx.x * kMaxWorld + peer;
+    long long t0 = clock64();
+    while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0) {
+      if (clock64() - t0 > 4000000000LL) {
+        printf("tdl_b200 p2p: rank %d CTA %d timed out waiting for rank %d (epoch %u)\n", cm.rank, (int)blockIdx.x,
+               peer, epoch);
+        __trap();
+      }
+    }
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ float4 ld_grad4(const Comm& cm, int r, int64_t i, int is_bf16) {
+  if (is_bf16) {
+    const uint2 raw = *reinterpret_cast<const uint2*>(reinterpret_cast<const bf16*>(cm.grad[r]) + i);
+    const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.x));
+    const float2 b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.y));
+    return make_float4(a.x, a.y, b.x, b.y);
+  }
+  return *reinterpret_cast<const float4*>(cm.grad[r] + i);
+}
+__device__ __forceinline__ float ld_grad1(const Comm& cm, int r, int64_t i, int is_bf16) {
+  return is_bf16 ? __bfloat162float(reinterpret_cast<const bf16*>(cm.grad[r])[i]) : cm.grad[r][i];
+}
+
+__device__ __forceinline__ float opt_update(const StepArgs& a, float w, float g, int64_t i, float lr, float lr_t) {
+  if (a.kind == kSgdMomentum) {
+    g += a.b * w;
+    const float m = a.a * a.m1[i] + g;
+    a.m1[i] = m;
+    return w - lr * m;
+  }
+  if (a.kind == kAdam) {
+    const float m = a.a * a.m1[i] + (1.f - a.a) * g;
+    const float v = a.b * a.m2[i] + (1.f - a.b) * g * g;
+    a.m1[i] = m;
+    a.m2[i] = v;
+    return w - lr_t * m / (sqrtf(v) + a.c);
+  }
+  return g;  // kNone: the "parameter" is the mean itself
+}
+
+__device__ __forceinline__ void zero_grad_range(const Comm& cm, const StepArgs& a, int64_t lo, int64_t hi) {
+  // clear my own gradient bucket [lo, hi) (element indices), grid-strided
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t nthr = (int64_t)gridDim.x * blockDim.x;
+  if (a.grad_is_bf16) {
+    bf16* g = reinterpret_cast<bf16*>(cm.grad[cm.rank]);
+    for (int64_t i = lo + tid; i < hi; i += nthr) g[i] = __float2bfloat16(0.f);
+  } else {
+    float* g = cm.grad[cm.rank];
+    for (int64_t i = lo + tid; i < hi; i += nthr) g[i] = 0.f;
+  }
+}
+
+// ---- one-shot ----
+__global__ void __launch_bounds__(kThreads)
+one_shot_kernel(const Comm cm, const StepArgs a) {
+  uint32_t epoch = cm.epoch[blockIdx.x];
+  cross_rank_barrier(cm, ++epoch);  // every rank's gradients for this bucket are complete
+  const float lr = a.lr_state ? a.lr_state[0] : 0.f;
+  const float lr_t = a.lr_state ? a.lr_state[1] : 0.f;
+  const float scale = a.grad_scale / (float)cm.world;
+  const int64_t lo = a.offset, hi = a.offset + a.n;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t nthr = (int64_t)gridDim.x * blockDim.x;
+  float* out = a.kind == kNone ? nullptr : cm.param[cm.rank];
+  // bucket offsets are multiples of 4 elements (16 bytes fp32 / 8 bytes bf16)
+  const int64_t n4 = a.n / 4;
+  // kNone writes the mean into the gradient buffer itself, which peers are still reading: stage in registers
+  // across the barrier is impossible for a grid-stride loop, so kNone results go to a.m1 (scratch) first.
+  float* mean_out = a.kind == kNone ? a.m1 : nullptr;
+  for (int64_t v = tid; v < n4; v += nthr) {
+    const int64_t i = lo + v * 4;
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 1
+    for (int r = 0; r < cm.world; ++r) {
+      const float4 g = ld_grad4(cm, r, i, a.grad_is_bf16);
+      s.x += g.x; s.y += g.y; s.z += g.z; s.w += g.w;
+    }
+    s.x *= scale; s.y *= scale; s.z *= scale; s.w *= scale;
+    if (a.kind == kNone) {
+      *reinterpret_cast<float4*>(mean_out + i) = s;
+    } else {
+      float4 w = *reinterpret_cast<const float4*>(out + i);
+      w.x = opt_update(a, w.x, s.x, i, lr, lr_t);
+      w.y = opt_update(a, w.y, s.y, i + 1, lr, lr_t);
+      w.z = opt_update(a, w.z, s.z, i + 2, lr, lr_t);
+      w.w = opt_update(a, w.w, s.w, i + 3, lr, lr_t);
+      *reinterpret_cast<float4*>(out + i) = w;
+    }
+  }
+  for (int64_t i = lo + n4 * 4 + tid; i < hi; i += nthr) {
+    float s = 0.f;
+    for (int r = 0; r < cm.world; ++r) s += ld_grad1(cm, r, i, a.grad_is_bf16);
+    s *= scale;
+    if (a.kind == kNone) mean_out[i] = s;
+    else out[i] = opt_update(a, out[i], s, i, lr, lr_t);
+  }
+  cross_rank_barrier(cm, ++epoch);  // all peers have finished reading my gradients
+  if (a.kind == kNone) {
+    // publish the mean in place (fp32 buckets only)
+    float* g = cm.grad[cm.rank];
+    for (int64_t i = lo + tid; i < hi; i += nthr) g[i] = mean_out[i];
+  } else if (a.zero_grad) {
+    zero_grad_range(cm, a, lo, hi);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) cm.epoch[blockIdx.x] = epoch;
+}
+
+// ---- two-shot: reduce-scatter -> shard-local optimizer -> all-gather by peer stores ----
+__global__ void __launch_bounds__(kThreads)
+two_shot_kernel(const Comm cm, const StepArgs a) {
+  uint32_t epoch = cm.epoch[blockIdx.x];
+  cross_rank_barrier(cm, ++epoch);
+  const float lr = a.lr_state[0];
+  const float lr_t = a.lr_state[1];
+  const float scale = a.grad_scale / (float)cm.world;
+  // slice boundaries in units of 4 elements so every access stays 16-byte aligned
+  const int64_t n4 = a.n / 4;
+  const int64_t per = (n4 + cm.world - 1) / cm.world;
+  const int64_t v_lo = per * cm.rank < n4 ? per * cm.rank : n4;
+  const int64_t v_hi = v_lo + per < n4 ? v_lo + per : n4;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t nthr = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t v = v_lo + tid; v < v_hi; v += nthr) {
+    const int64_t i = a.offset + v * 4;
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 1
+    for (int r = 0; r < cm.world; ++r) {
+      const float4 g = ld_grad4(cm, r, i, a.grad_is_bf16);
+      s.x += g.x; s.y += g.y; s.z += g.z; s.w += g.w;
+    }
+    float4 w = *reinterpret_cast<const float4*>(cm.param[cm.rank] + i);
+    w.x = opt_update(a, w.x, s.x * scale, i, lr, lr_t);
+    w.y = opt_update(a, w.y, s.y * scale, i + 1, lr, lr_t);
+    w.z = opt_update(a, w.z, s.z * scale, i + 2, lr, lr_t);
+    w.w = opt_update(a, w.w, s.w * scale, i + 3, lr, lr_t);
+#pragma unroll 1
+    for (int r = 0; r < cm.world; ++r) *reinterpret_cast<float4*>(cm.param[r] + i) = w;
+  }
+  // ragged tail (< 4 elements): owned by the last rank
+  if (cm.rank == cm.world - 1) {
+    for (int64_t i = a.offset + n4 * 4 + tid; i < a.offset + a.n; i += nthr) {
+      float s = 0.f;
+      for (int r = 0; r < cm.world; ++r) s += ld_grad1(cm, r, i, a.grad_is_bf16);
+      const float w = opt_update(a, cm.param[cm.rank][i], s * scale, i, lr, lr_t);
+      for (int r = 0; r < cm.world; ++r) cm.param[r][i] = w;
+    }
+  }
+  __threadfence_system();
+  cross_rank_barrier(cm, ++epoch);  // every slice has landed everywhere; every gradient has been read
+  if (a.zero_grad) zero_grad_range(cm, a, a.offset, a.offset + a.n);
+  __syncthreads();
+  if (threadIdx.x == 0) cm.epoch[blockIdx.x] = epoch;
+}
+
+}  // namespace p2p
+}  // namespace tdl
+
+using namespace tdl;
+using namespace tdl::p2p;
+
+// ---- symmetric heap: plain cudaMalloc allocations that can be exported through cudaIpc ----
+TDL_API int tdl_symm_alloc(int64_t bytes, void** out) {
+  TDL_REQUIRE(bytes > 0, "bytes must be positive");
+  void* p = nullptr;
+  TDL_CUDA_OK(cudaMalloc(&p, (size_t)bytes));
+  TDL_CUDA_OK(cudaMemset(p, 0, (size_t)bytes));
+  TDL_CUDA_OK(cudaDeviceSynchronize());
+  *out = p;
+  return 0;
+}
+TDL_API int tdl_symm_free(void* p) {
+  TDL_CUDA_OK(cudaFree(p));
+  return 0;
+}
+TDL_API int tdl_ipc_export(void* p, void* handle64) {
+  cudaIpcMemHandle_t h;
+  TDL_CUDA_OK(cudaIpcGetMemHandle(&h, p));
+  memcpy(handle64, &h, sizeof(h));
+  return 0;
+}
+TDL_API int tdl_ipc_open(const void* handle64, void** out) {
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, sizeof(h));
+  TDL_CUDA_OK(cudaIpcOpenMemHandle(out, h, cudaIpcMemLazyEnablePeerAccess));
+  return 0;
+}
+TDL_API int tdl_ipc_close(void* p) {
+  TDL_CUDA_OK(cudaIpcCloseMemHandle(p));
+  return 0;
+}
+TDL_API int tdl_p2p_flag_bytes() { return kMaxBlocks * kMaxWorld * (int)sizeof(uint32_t); }
+
+// Build a communicator from already-mapped pointers (index = rank).  `epoch_local` is kMaxBlocks u32, zeroed.
+TDL_API int tdl_p2p_comm_create(int world, int rank, void** grad_ptrs, void** param_ptrs, void** flag_ptrs,
+                                void* epoch_local, int emulate, void** out_comm) {
+  TDL_REQUIRE(world >= 1 && world <= kMaxWorld && rank >= 0 && rank < world, "bad world/rank");
+  Comm* c = new Comm();
+  memset(c, 0, sizeof(Comm));
+  c->world = world;
+  c->rank = rank;
+  c->emulate = emulate;
+  for (int r = 0; r < world; ++r) {
+    c->grad[r] = (float*)grad_ptrs[r];
+    c->param[r] = param_ptrs ? (float*)param_ptrs[r] : nullptr;
+    c->flags[r] = flag_ptrs ? (uint32_t*)flag_ptrs[r] : nullptr;
+  }
+  c->epoch = (uint32_t*)epoch_local;
+  *out_comm = c;
+  return 0;
+}
+TDL_API int tdl_p2p_comm_destroy(void* comm) {
+  delete (Comm*)comm;
+  return 0;
+}
+
+// Fused all-reduce(mean) + optimizer for one bucket.  mode: 1 = one-shot, 2 = two-shot, 0 = pick by size.
+// kind: 0 = plain mean written back into the gradient bucket (m1 = fp32 staging of >= offset+n elements),
+//       1 = momentum SGD (a = momentum, b = weight decay), 2 = TF Adam (a = beta1, b = beta2, c = eps).
+TDL_API int tdl_p2p_fused_step(void* comm, int64_t offset, int64_t n, int mode, int kind, int grad_is_bf16,
+                               int zero_grad, float* m1, float* m2, const float* lr_state, float a, float b, float c,
+                               float grad_scale, int max_blocks, void* stream) {
+  Comm* cm = (Comm*)comm;
+  TDL_REQUIRE(cm != nullptr, "null communicator");
+  TDL_REQUIRE(offset % 4 == 0, "bucket offsets must be multiples of 4 elements");
+  TDL_REQUIRE(!(kind == kNone && grad_is_bf16), "plain mean supports fp32 buckets only");
+  if (n <= 0) return 0;
+  StepArgs s;
+  s.offset = offset; s.n = n; s.kind = kind; s.grad_is_bf16 = grad_is_bf16; s.zero_grad = zero_grad;
+  s.m1 = m1; s.m2 = m2; s.lr_state = lr_state; s.a = a; s.b = b; s.c = c; s.grad_scale = grad_scale;
+  if (mode == 0) mode = (n * (grad_is_bf16 ? 2 : 4) <= (1 << 19) || kind == kNone) ? 1 : 2;
+  if (kind == kNone) mode = 1;
+  int64_t work = mode == 1 ? n / 4 : n / 4 / cm->world;
+  int blocks = (int)cdiv(work, (int64_t)kThreads * 4);
+  if (max_blocks <= 0) max_blocks = 64;
+  if (max_blocks > kMaxBlocks) max_blocks = kMaxBlocks;
+  if (max_blocks > num_sms()) max_blocks = num_sms();
+  if (blocks > max_blocks) blocks = max_blocks;
+  if (blocks < 1) blocks = 1;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (mode == 1) one_shot_kernel<<<blocks, kThreads, 0, st>>>(*cm, s);
+  else two_shot_kernel<<<blocks, kThreads, 0, st>>>(*cm, s);
+  TDL_LAUNCH_OK("p2p fused step");
+  return 0;
+}

@@ -500,3 +500,34 @@ TDL_API int tdl_upsample_bwd(const void* dy, float* dx, int N, int H, int W, int
   TDL_LAUNCH_OK("upsample_bwd_kernel");
   return 0;
 }
+
+// ------------------------------------------------------------------------------------------
+// input pipeline tail on the device: uint8 NHWC -> normalised bf16 NHWC (optionally channel-padded)
+// ------------------------------------------------------------------------------------------
+namespace tdl {
+namespace spatial {
+__global__ void __launch_bounds__(kThreads)
+u8_to_bf16_kernel(const uint8_t* __restrict__ x, bf16* __restrict__ y, int64_t pixels, int C, int Cpad,
+                  const float* __restrict__ mean, const float* __restrict__ inv_std) {
+  const int64_t total = pixels * Cpad;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % Cpad);
+    const int64_t px = i / Cpad;
+    float v = 0.f;
+    if (c < C) v = ((float)x[px * C + c] * (1.f / 255.f) - mean[c]) * inv_std[c];
+    y[i] = __float2bfloat16(v);
+  }
+}
+}  // namespace spatial
+}  // namespace tdl
+
+TDL_API int tdl_u8_to_bf16_normalize(const void* x_u8, void* y_bf16, int64_t pixels, int C, int Cpad,
+                                     const float* mean, const float* inv_std, void* stream) {
+  TDL_REQUIRE(Cpad >= C, "Cpad must be >= C");
+  const int64_t total = pixels * Cpad;
+  if (total == 0) return 0;
+  tdl::spatial::u8_to_bf16_kernel<<<tdl::spatial::grid_for(total), tdl::spatial::kThreads, 0, (cudaStream_t)stream>>>(
+      (const uint8_t*)x_u8, (tdl::bf16*)y_bf16, pixels, C, Cpad, mean, inv_std);
+  TDL_LAUNCH_OK("u8_to_bf16_kernel");
+  return 0;
+}

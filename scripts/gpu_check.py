@@ -369,6 +369,136 @@ def group_perf():
          apply_gbs=2 * gb / t_apply * 1e3, bwd_ms=t_bwd, bwd_gbs=5 * gb / t_bwd * 1e3)
 
 
+def group_spatial():
+    import torch
+    import torch.nn.functional as F
+    from tensorflowdistributedlearning_b200.ops import functional as TFn
+    from tensorflowdistributedlearning_b200.ops import pooling, depthwise, resize
+    from tensorflowdistributedlearning_b200.ops import reference as R
+
+    def run_pair(name, fn, inputs, tol=2e-2):
+        """fn(*tensors) -> output; compares native (bf16 cuda) against the torch oracle in fp32, fwd and bwd."""
+        torch.manual_seed(7)
+        nat_in = [t.clone().requires_grad_(t.is_floating_point()) for t in inputs]
+        ref_in = [t.float().clone().requires_grad_(t.is_floating_point()) for t in inputs]
+        TFn.force_reference(False)
+        y = fn(*nat_in)
+        g = torch.randn_like(y)
+        y.backward(g)
+        TFn.force_reference(True)
+        yr = fn(*ref_in)
+        yr.backward(g.float())
+        TFn.force_reference(False)
+        errs = {"fwd": rel_err(y, yr)}
+        for i, (a, b) in enumerate(zip(nat_in, ref_in)):
+            if a.grad is not None:
+                errs[f"g{i}"] = rel_err(a.grad, b.grad)
+        emit(group="spatial", case=name, ok=max(errs.values()) < tol, **errs)
+
+    x = torch.randn(4, 51, 51, 128, device="cuda").bfloat16()
+    run_pair("maxpool_same_51", lambda t: pooling.max_pool_same(t, 3, 2), [x])
+    x = torch.randn(4, 112, 112, 64, device="cuda").bfloat16().relu()
+    run_pair("maxpool_sym_112_ties", lambda t: pooling.max_pool(t, 3, 2, (1, 1, 1, 1)), [x])
+    x = torch.randn(8, 7, 7, 2048, device="cuda").bfloat16()
+    run_pair("gap", lambda t: pooling.global_avg_pool(t, True), [x])
+    for (H, C, st, dil) in [(13, 1024, 1, 2), (13, 1024, 1, 8), (38, 728, 1, 1), (75, 256, 2, 1), (19, 728, 2, 1)]:
+        x = torch.randn(2, H, H, C, device="cuda").bfloat16()
+        w = (torch.randn(3, 3, C, device="cuda") * 0.3)
+        b = torch.randn(C, device="cuda") * 0.1
+        run_pair(f"depthwise_{H}_{C}_s{st}_d{dil}",
+                 lambda t, ww, bb: depthwise.depthwise_conv2d(t, ww, bb, st, dil, "SAME", True), [x, w, b], tol=3e-2)
+    for (h, C, out, dt) in [(1, 256, 13, torch.bfloat16), (13, 256, 26, torch.bfloat16), (26, 1, 101, torch.float32)]:
+        x = torch.randn(2, h, h, C, device="cuda").to(dt)
+        run_pair(f"upsample_{h}_{out}", lambda t: resize.upsample(t, (out, out)), [x], tol=2e-2)
+
+
+def group_p2p_emulate():
+    """All 'ranks' on one GPU, launched one after another with barriers disabled: checks the reduce/optimizer math."""
+    import torch
+    from tensorflowdistributedlearning_b200.parallel.p2p import SymmetricBuffer, P2PComm
+
+    for world in (2, 4, 8):
+        for kind, n in ((1, 1_000_003 // 4 * 4 + 3), (2, 65_536 + 5), (2, 3_000_000)):
+            torch.manual_seed(world * 10 + kind)
+            gbuf = SymmetricBuffer(((n + 7) // 8 * 8) * 4, emulate_world=world)
+            pbuf = SymmetricBuffer(((n + 7) // 8 * 8) * 4, emulate_world=world)
+            grads = [torch.randn(n, device="cuda") for _ in range(world)]
+            p0 = torch.randn(n, device="cuda")
+            for r in range(world):
+                gbuf.tensor(torch.float32, r)[:n].copy_(grads[r])
+                pbuf.tensor(torch.float32, r)[:n].copy_(p0)
+            lr_state = torch.tensor([0.1, 0.05], device="cuda")
+            res = {}
+            for mode in (1, 2):
+                for r in range(world):
+                    pbuf.tensor(torch.float32, r)[:n].copy_(p0)
+                m1s = [torch.zeros(n + 8, device="cuda") for _ in range(world)]
+                m2s = [torch.zeros(n + 8, device="cuda") for _ in range(world)]
+                comms = [P2PComm(gbuf, pbuf, emulate_rank=r) for r in range(world)]
+                for r in range(world):
+                    comms[r].fused_step(0, n, kind=kind, grad_is_bf16=False, zero_grad=False, m1=m1s[r], m2=m2s[r],
+                                        lr_state=lr_state, a=0.9, b=(1e-4 if kind == 1 else 0.999), c=1e-8, mode=mode)
+                torch.cuda.synchronize()
+                g = sum(grads) / world
+                if kind == 1:
+                    gg = g + 1e-4 * p0
+                    ref = p0 - 0.1 * gg
+                else:
+                    m = 0.1 * g
+                    v = 0.001 * g * g
+                    ref = p0 - 0.05 * m / (v.sqrt() + 1e-8)
+                errs = [rel_err(pbuf.tensor(torch.float32, r)[:n], ref) for r in range(world)]
+                same = all(torch.equal(pbuf.tensor(torch.float32, r)[:n], pbuf.tensor(torch.float32, 0)[:n])
+                           for r in range(world))
+                res[f"mode{mode}"] = max(errs)
+                res[f"mode{mode}_mirrors_identical"] = same
+                for c in comms:
+                    c.close()
+            emit(group="p2p_emulate", world=world, kind=kind, n=n, ok=max(res["mode1"], res["mode2"]) < 1e-5 and
+                 res["mode1_mirrors_identical"] and res["mode2_mirrors_identical"], **res)
+            gbuf.close(); pbuf.close()
+
+
+def group_model():
+    """ResNet-50 (small input) one training step: native kernels vs the torch-op path on identical weights."""
+    import torch
+    from tensorflowdistributedlearning_b200 import models
+    from tensorflowdistributedlearning_b200.ops import functional as TFn
+
+    torch.manual_seed(11)
+    m = models.resnet50(num_classes=1000).cuda()
+    for mod in m.modules():  # make the zero-init gammas non-trivial so every branch carries signal
+        if hasattr(mod, "gamma") and mod.gamma is not None:
+            torch.nn.init.uniform_(mod.gamma, 0.5, 1.5)
+    x = torch.randn(16, 64, 64, 3, device="cuda").bfloat16()
+    y = torch.randint(0, 1000, (16,), device="cuda")
+    out = {}
+    for name, flag in (("native", False), ("torch", True)):
+        TFn.force_reference(flag)
+        m.zero_grad(set_to_none=True)
+        for mod in m.modules():
+            if hasattr(mod, "moving_mean"):
+                mod.moving_mean.zero_(); mod.moving_variance.fill_(1.0)
+        logits = m(x)
+        loss, t1, t5 = TFn.softmax_cross_entropy(logits.float(), y)
+        loss.backward()
+        out[name] = (float(loss), {n: p.grad.float().clone() for n, p in m.named_parameters()},
+                     logits.float().detach().clone())
+    TFn.force_reference(False)
+    gn, gt = out["native"][1], out["torch"][1]
+    worst, worst_name = 0.0, ""
+    import math
+    cos_min = 1.0
+    for n in gn:
+        a, b = gn[n].flatten(), gt[n].flatten()
+        cos = float(torch.dot(a, b) / (a.norm() * b.norm() + 1e-12))
+        if cos < cos_min:
+            cos_min, worst_name = cos, n
+    emit(group="model", loss_native=out["native"][0], loss_torch=out["torch"][0],
+         logits_rel_err=rel_err(out["native"][2], out["torch"][2]), min_grad_cosine=cos_min, worst=worst_name,
+         ok=abs(out["native"][0] - out["torch"][0]) < 0.05 and cos_min > 0.9)
+
+
 GROUPS = {
     "conv_fprop_basic": group_conv_fprop_basic,
     "conv_fprop_strided": group_conv_fprop_strided,
@@ -378,6 +508,9 @@ GROUPS = {
     "optim": group_optim,
     "loss": group_loss,
     "perf": group_perf,
+    "spatial": group_spatial,
+    "p2p_emulate": group_p2p_emulate,
+    "model": group_model,
 }
 
 

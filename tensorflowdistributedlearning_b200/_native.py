@@ -115,7 +115,14 @@ def lib() -> ctypes.CDLL:
     return _lib
 
 
+# kernels launched per C-ABI entry point (default 1); used for the bench's "gpu_launches" count
+_KERNELS_PER_CALL = {"tdl_bn_fwd_stats": 2, "tdl_bn_bwd_reduce": 2, "tdl_depthwise_bwd": 2}
+kernel_launches = 0
+
+
 def check(rc: int, what: str = "") -> None:
+    global kernel_launches
+    kernel_launches += _KERNELS_PER_CALL.get(what, 1)
     if rc != 0:
         msg = lib().tdl_last_error()
         raise NativeError(f"{what} failed (rc={rc}): {msg.decode() if msg else ''}")

@@ -323,3 +323,16 @@ def upsample_bwd(dy, in_shape, out_hw):
                                   _i(int(dy.dtype == torch.bfloat16)), N.stream_ptr())
     N.check(rc, "tdl_upsample_bwd")
     return dx.to(dy.dtype)
+
+
+def u8_to_bf16_normalize(x_u8: torch.Tensor, mean: torch.Tensor, inv_std: torch.Tensor, out: Optional[torch.Tensor] = None,
+                         c_pad: Optional[int] = None) -> torch.Tensor:
+    """uint8 NHWC -> (x/255 - mean) * inv_std as bf16 NHWC, optionally zero-padding channels to ``c_pad``."""
+    n, h, w, c = x_u8.shape
+    cp = c_pad or c
+    if out is None:
+        out = torch.empty((n, h, w, cp), dtype=torch.bfloat16, device=x_u8.device)
+    rc = N.lib().tdl_u8_to_bf16_normalize(N.ptr(x_u8), N.ptr(out), _i64(n * h * w), _i(c), _i(cp), N.ptr(mean),
+                                          N.ptr(inv_std), N.stream_ptr())
+    N.check(rc, "tdl_u8_to_bf16_normalize")
+    return out

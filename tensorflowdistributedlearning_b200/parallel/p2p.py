@@ -1,0 +1,129 @@
+"""Symmetric heap + peer-to-peer communicator (host side of ``csrc/p2p_allreduce.cu``).
+
+Every rank allocates identically-sized buffers from the native heap (plain ``cudaMalloc`` so they
+can be exported with ``cudaIpcGetMemHandle``), all-gathers the 64-byte handles through the
+bootstrap process group (the *only* use of torch.distributed on the gradient path) and maps every
+peer's buffer.  The resulting pointer tables feed the fused all-reduce + optimizer kernels.
+
+This replaces the variable mirroring and cross-tower plumbing that MirroredStrategy does inside
+TensorFlow for the reference (model.py:115-119).
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+from .. import _native as N
+
+
+class _RawCuda:
+    """Zero-copy view of a raw device pointer for torch.as_tensor."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+
+class SymmetricBuffer:
+    """One allocation per rank, same size everywhere, mapped into every peer."""
+
+    def __init__(self, nbytes: int, group=None, emulate_world: int = 0):
+        lib = N.lib()
+        self.nbytes = int(nbytes)
+        self.group = group
+        self.emulated = emulate_world > 0
+        self.world = emulate_world if self.emulated else (dist.get_world_size(group) if dist.is_initialized() else 1)
+        self.rank = 0 if self.emulated else (dist.get_rank(group) if dist.is_initialized() else 0)
+        self._own: List[int] = []
+        self._opened: List[int] = []
+        self.ptrs: List[int] = []
+        if self.emulated or self.world == 1:
+            for _ in range(self.world):
+                p = ctypes.c_void_p()
+                N.check(lib.tdl_symm_alloc(ctypes.c_int64(self.nbytes), ctypes.byref(p)), "tdl_symm_alloc")
+                self._own.append(p.value)
+            self.ptrs = list(self._own)
+        else:
+            p = ctypes.c_void_p()
+            N.check(lib.tdl_symm_alloc(ctypes.c_int64(self.nbytes), ctypes.byref(p)), "tdl_symm_alloc")
+            self._own.append(p.value)
+            h = (ctypes.c_ubyte * 64)()
+            N.check(lib.tdl_ipc_export(p, h), "tdl_ipc_export")
+            handles: List[Optional[bytes]] = [None] * self.world
+            dist.all_gather_object(handles, bytes(h), group=group)
+            for r in range(self.world):
+                if r == self.rank:
+                    self.ptrs.append(p.value)
+                else:
+                    q = ctypes.c_void_p()
+                    buf = (ctypes.c_ubyte * 64).from_buffer_copy(handles[r])
+                    N.check(lib.tdl_ipc_open(buf, ctypes.byref(q)), "tdl_ipc_open")
+                    self._opened.append(q.value)
+                    self.ptrs.append(q.value)
+        self._holders = [_RawCuda(p, self.nbytes) for p in self.ptrs]
+
+    def tensor(self, dtype=torch.float32, rank: Optional[int] = None) -> torch.Tensor:
+        """This rank's buffer (or, in emulation, the buffer of ``rank``) as a flat tensor of ``dtype``."""
+        r = self.rank if rank is None else rank
+        t = torch.as_tensor(self._holders[r], device=torch.device("cuda", torch.cuda.current_device()))
+        return t.view(dtype)
+
+    def ptr_table(self):
+        arr = (ctypes.c_void_p * self.world)()
+        for r, p in enumerate(self.ptrs):
+            arr[r] = p
+        return arr
+
+    def close(self):
+        lib = N.lib()
+        for q in self._opened:
+            lib.tdl_ipc_close(ctypes.c_void_p(q))
+        for p in self._own:
+            lib.tdl_symm_free(ctypes.c_void_p(p))
+        self._opened, self._own = [], []
+
+
+class P2PComm:
+    """Pointer tables + signal pads for the fused kernels.  ``emulate_rank`` selects which emulated rank
+    this communicator acts as when all buffers live on one GPU (single-GPU tests)."""
+
+    def __init__(self, grad: SymmetricBuffer, param: Optional[SymmetricBuffer], group=None,
+                 emulate_rank: Optional[int] = None):
+        lib = N.lib()
+        self.grad, self.param = grad, param
+        self.world = grad.world
+        self.emulated = grad.emulated
+        self.rank = emulate_rank if self.emulated else grad.rank
+        self.flags = SymmetricBuffer(int(lib.tdl_p2p_flag_bytes()), group, emulate_world=self.world if self.emulated else 0)
+        self.epoch = torch.zeros(256, dtype=torch.int32, device="cuda")
+        out = ctypes.c_void_p()
+        N.check(lib.tdl_p2p_comm_create(ctypes.c_int(self.world), ctypes.c_int(self.rank), grad.ptr_table(),
+                                        param.ptr_table() if param is not None else None, self.flags.ptr_table(),
+                                        N.ptr(self.epoch), ctypes.c_int(int(self.emulated)), ctypes.byref(out)),
+                "tdl_p2p_comm_create")
+        self.handle = out
+        if not self.emulated and dist.is_initialized() and self.world > 1:
+            torch.cuda.synchronize()
+            dist.barrier(group=group)
+
+    def fused_step(self, offset: int, n: int, *, kind: int, grad_is_bf16: bool, zero_grad: bool, m1, m2, lr_state,
+                   a: float, b: float, c: float, grad_scale: float = 1.0, mode: int = 0, max_blocks: int = 64):
+        rc = N.lib().tdl_p2p_fused_step(self.handle, ctypes.c_int64(offset), ctypes.c_int64(n), ctypes.c_int(mode),
+                                        ctypes.c_int(kind), ctypes.c_int(int(grad_is_bf16)),
+                                        ctypes.c_int(int(zero_grad)), N.ptr(m1), N.ptr(m2), N.ptr(lr_state),
+                                        ctypes.c_float(a), ctypes.c_float(b), ctypes.c_float(c),
+                                        ctypes.c_float(grad_scale), ctypes.c_int(max_blocks), N.stream_ptr())
+        N.check(rc, "tdl_p2p_fused_step")
+
+    def all_reduce_mean_(self, staging: torch.Tensor, offset: int, n: int, max_blocks: int = 8):
+        """In-place mean over ranks of grad[offset:offset+n] (fp32), one-shot.  ``staging`` is fp32 scratch."""
+        self.fused_step(offset, n, kind=0, grad_is_bf16=False, zero_grad=False, m1=staging, m2=None, lr_state=None,
+                        a=0.0, b=0.0, c=0.0, mode=1, max_blocks=max_blocks)
+
+    def close(self):
+        if self.handle is not None:
+            N.lib().tdl_p2p_comm_destroy(self.handle)
+            self.handle = None
+        self.flags.close()

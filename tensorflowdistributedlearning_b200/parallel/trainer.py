@@ -1,0 +1,161 @@
+"""One tower's training step: device-side input tail -> forward -> loss -> backward -> fused comm+optimizer,
+captured once into a CUDA graph and replayed.
+
+This is the hot loop that ``session.run(train_op)`` is for the reference, re-designed:
+the loss stays on the GPU (the reference pins it to the CPU, model.py:391), the learning-rate schedule
+and the Adam bias correction are device-resident, the whole step is one graph launch, the next batch's
+host->device copy runs on a copy stream under the current step, and the only per-step host
+synchronisation is the read of the scalar loss.
+"""
+from __future__ import annotations
+
+from typing import Callable, Optional, Tuple
+
+import torch
+
+from ..ops import functional as TF
+from .optimizer import DistributedOptimizer
+from .tower import TowerGroup
+
+
+def classification_loss(logits: torch.Tensor, labels: torch.Tensor):
+    loss, top1, top5 = TF.softmax_cross_entropy(logits.float(), labels)
+    return loss, {"top1": top1, "top5": top5}
+
+
+def segmentation_loss(logits: torch.Tensor, labels: torch.Tensor):
+    loss = TF.lovasz_loss(labels, logits)
+    iou, acc = TF.seg_metrics(logits, labels, 0.5, True)
+    return loss, {"iou": iou, "acc": acc}
+
+
+class TowerTrainer:
+    def __init__(self, model: torch.nn.Module, group: TowerGroup, *, batch: int, input_hwc: Tuple[int, int, int],
+                 label_shape: Tuple[int, ...] = (), label_dtype=torch.int64,
+                 loss_fn: Callable = classification_loss, compute_dtype=torch.bfloat16, use_graph: bool = True,
+                 mean=None, std=None, input_is_u8: bool = True, **opt_kw):
+        self.group = group
+        dev = group.device
+        self.device = dev
+        self.model = model.to(dev)
+        self.model.train()
+        self.loss_fn = loss_fn
+        self.compute_dtype = compute_dtype if dev.type == "cuda" else torch.float32
+        self.opt = DistributedOptimizer(self.model, group, **opt_kw)
+        h, w, c = input_hwc
+        self.input_is_u8 = input_is_u8
+        in_dtype = torch.uint8 if input_is_u8 else torch.float32
+        self.images = torch.zeros((batch, h, w, c), dtype=in_dtype, device=dev)
+        self.labels = torch.zeros((batch, *label_shape), dtype=label_dtype, device=dev)
+        self.mean = torch.tensor(mean if mean is not None else [0.0] * c, dtype=torch.float32, device=dev)
+        self.inv_std = 1.0 / torch.tensor(std if std is not None else [1.0] * c, dtype=torch.float32, device=dev)
+        self.loss = torch.zeros((), dtype=torch.float32, device=dev)
+        self.metrics = {}
+        self.use_graph = bool(use_graph and dev.type == "cuda")
+        self._graph: Optional[torch.cuda.CUDAGraph] = None
+        self._copy_stream = torch.cuda.Stream() if dev.type == "cuda" else None
+        self._copied = torch.cuda.Event() if dev.type == "cuda" else None
+        self._stage_free = torch.cuda.Event() if dev.type == "cuda" else None
+        self._stage_images = None
+        self._stage_labels = None
+        self._staged = False
+        self.launches_per_step = 0
+
+    # ---- the step body (eager; also what gets captured) ----
+    def _prepare_input(self) -> torch.Tensor:
+        if self.device.type == "cuda" and self.input_is_u8 and self.compute_dtype == torch.bfloat16:
+            from ..ops import native_ops as O
+
+            return O.u8_to_bf16_normalize(self.images, self.mean, self.inv_std)
+        x = self.images.float()
+        if self.input_is_u8:
+            x = x / 255.0
+        return ((x - self.mean) * self.inv_std).to(self.compute_dtype)
+
+    def _step_body(self) -> None:
+        x = self._prepare_input()
+        self.opt.begin_step()
+        out = self.model(x)
+        loss, metrics = self.loss_fn(out, self.labels)
+        loss.backward()
+        self.opt.step()
+        self.loss.copy_(loss.detach())
+        for k, v in metrics.items():
+            if k not in self.metrics:
+                self.metrics[k] = torch.zeros_like(v)
+            self.metrics[k].copy_(v)
+
+    def warmup_and_capture(self, warmup: int = 3) -> None:
+        """Eager warm-up steps (they train: they are real steps), then capture one step into a CUDA graph."""
+        from .. import _native as N
+
+        if self.device.type != "cuda":
+            return
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            for i in range(max(warmup, 1)):
+                before = N.kernel_launches
+                self._step_body()
+                self.launches_per_step = N.kernel_launches - before
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize()
+        if self.use_graph:
+            self.group.barrier()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._step_body()
+            self._graph = g
+            torch.cuda.synchronize()
+            self.group.barrier()
+
+    def run_step(self) -> None:
+        """One training step on whatever is in the device input buffers (no host traffic)."""
+        if self._graph is not None:
+            self._graph.replay()
+        else:
+            self._step_body()
+
+    # ---- public end-to-end call ----
+    def stage_batch(self, images_host: torch.Tensor, labels_host: torch.Tensor) -> None:
+        """Asynchronously copy a (pinned) host batch into the device *staging* buffers on the copy stream."""
+        if self.device.type != "cuda":
+            self.images.copy_(images_host)
+            self.labels.copy_(labels_host)
+            self._staged = True
+            return
+        if self._stage_images is None:
+            self._stage_images = torch.empty_like(self.images)
+            self._stage_labels = torch.empty_like(self.labels)
+        self._copy_stream.wait_event(self._stage_free)  # the previous staging contents have been consumed
+        with torch.cuda.stream(self._copy_stream):
+            self._stage_images.copy_(images_host, non_blocking=True)
+            self._stage_labels.copy_(labels_host, non_blocking=True)
+            self._copied.record(self._copy_stream)
+        self._staged = True
+
+    def train_step(self, images_host: torch.Tensor, labels_host: torch.Tensor, prefetch=None) -> float:
+        """Host batch in, scalar loss out.
+
+        The batch is copied host->device (pinned memory, copy stream), moved into the graph's input buffers,
+        one training step runs, and the scalar loss is read back.  ``prefetch=(images, labels)`` starts the
+        NEXT batch's host->device copy before this call blocks on the loss, so the copy hides under compute;
+        the next call must then be given that same batch.
+        """
+        if not self._staged:
+            self.stage_batch(images_host, labels_host)
+        self._staged = False
+        if self.device.type == "cuda":
+            cur = torch.cuda.current_stream()
+            cur.wait_event(self._copied)
+            self.images.copy_(self._stage_images, non_blocking=True)
+            self.labels.copy_(self._stage_labels, non_blocking=True)
+            self._stage_free.record(cur)
+        self.run_step()
+        if prefetch is not None:
+            self.stage_batch(*prefetch)
+        return float(self.loss.item())
+
+    def close(self) -> None:
+        self._graph = None
+        self.opt.close()
