@@ -1,0 +1,109 @@
+/* tdl_b200 -- C ABI of the sm_100a native library (tensorflowdistributedlearning_b200/lib/libtdl_b200.so).
+ *
+ * Conventions
+ *   - every function returns 0 on success; on failure the message is available from tdl_last_error()
+ *   - pointers are DEVICE pointers unless a parameter name says host; `stream` is a cudaStream_t
+ *   - activations are NHWC bf16, row-major, 16-byte aligned; C (channels) must be a multiple of 8
+ *   - nothing here allocates device memory except tdl_symm_alloc (the symmetric heap)
+ *
+ * The reference (gf712/TensorflowDistributedLearning) has no native code; each group cites the reference
+ * call site whose TensorFlow library kernel it replaces.
+ */
+#ifndef TDL_B200_H_
+#define TDL_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- library ---- */
+const char* tdl_last_error(void);
+int tdl_version(void);
+int tdl_num_sms(void);
+
+/* ---- convolution on tcgen05/TMEM/TMA (reference: slim.conv2d, core/resnet.py:79-85,130-144,164-166,449-492) ----
+ * x [N,H,W,C], w [K, R*S, C] (OHWI), y [N,P,Q,K]; pad_h/pad_w are the top/left padding, P/Q the output size.
+ * Optional fused epilogue: + bias[K] (fp32), + residual [N,P,Q,K] (bf16), ReLU. */
+int tdl_conv2d_fprop_bf16(const void* x, const void* w, void* y, const float* bias, const void* residual, int N,
+                          int H, int W, int C, int K, int R, int S, int stride, int dil, int pad_h, int pad_w, int P,
+                          int Q, int relu, void* stream);
+/* dw [K, R*S, C] fp32 is ACCUMULATED into (zero it first): dw += dy^T (*) x */
+int tdl_conv2d_wgrad_bf16(const void* x, const void* dy, float* dw, int N, int H, int W, int C, int K, int R, int S,
+                          int stride, int dil, int pad_h, int pad_w, int P, int Q, void* stream);
+/* fp32 master weights -> bf16 fprop copy [K,taps,C] and bf16 data-gradient copy [C,taps(flipped),K] (either may be NULL) */
+int tdl_conv2d_weight_prep(const float* w, void* w_fprop, void* w_dgrad, int K, int taps, int C, void* stream);
+
+/* ---- fused BatchNorm (+residual)(+ReLU) (reference: slim.batch_norm, core/resnet.py:71,126,242,373-387) ---- */
+int64_t tdl_bn_scratch_floats(int64_t rows, int C);
+int tdl_bn_fwd_stats(const void* x, int64_t rows, int C, float* scratch, int64_t scratch_floats, const float* gamma,
+                     const float* beta, float* running_mean, float* running_var, float decay, float eps, float* mean,
+                     float* invstd, float* scale, float* shift, void* stream);
+int tdl_bn_infer_scale_shift(const float* gamma, const float* beta, const float* running_mean,
+                             const float* running_var, float eps, float* scale, float* shift, int C, void* stream);
+int tdl_bn_apply(const void* x, const float* scale, const float* shift, const void* residual, void* y, int64_t rows,
+                 int C, int relu, void* stream);
+int tdl_bn_bwd_reduce(const void* dz, const void* x, const void* z, const float* scale, const float* shift,
+                      const float* mean, const float* invstd, int64_t rows, int C, int relu, float* scratch,
+                      int64_t scratch_floats, float* dgamma, float* dbeta, float* acc_dgamma, float* acc_dbeta,
+                      void* stream);
+int tdl_bn_bwd_apply(const void* dz, const void* x, const void* z, const float* scale, const float* shift,
+                     const float* mean, const float* invstd, const float* dgamma, const float* dbeta, void* dx,
+                     void* dres, int64_t rows, int C, int relu, void* stream);
+
+/* ---- spatial ops (reference: core/resnet.py:241,246-248,464-465; core/layers.py:34-42,82-109) ---- */
+int tdl_maxpool_fwd(const void* x, void* y, void* idx_u8, int N, int H, int W, int C, int P, int Q, int k, int stride,
+                    int pad_h, int pad_w, void* stream);
+int tdl_maxpool_bwd(const void* dy, const void* idx_u8, void* dx, int N, int H, int W, int C, int P, int Q, int k,
+                    int stride, int pad_h, int pad_w, void* stream);
+int tdl_gap_fwd(const void* x, void* y, int N, int HW, int C, void* stream);
+int tdl_gap_bwd(const void* dy, void* dx, int N, int HW, int C, void* stream);
+int tdl_depthwise_fwd(const void* x, const float* w, const float* bias, void* y, int N, int H, int W, int C, int P,
+                      int Q, int R, int S, int stride, int dil, int pad_h, int pad_w, int relu, void* stream);
+int tdl_depthwise_bwd(const void* x, const float* w, const void* dy, const void* y, void* dx, float* dw, float* dbias,
+                      int N, int H, int W, int C, int P, int Q, int R, int S, int stride, int dil, int pad_h, int pad_w,
+                      int relu, void* stream);
+int tdl_upsample_fwd(const void* x, void* y, int N, int H, int W, int C, int OH, int OW, int is_bf16, void* stream);
+int tdl_upsample_bwd(const void* dy, float* dx, int N, int H, int W, int C, int OH, int OW, int is_bf16, void* stream);
+int tdl_u8_to_bf16_normalize(const void* x_u8, void* y_bf16, int64_t pixels, int C, int Cpad, const float* mean,
+                             const float* inv_std, void* stream);
+
+/* ---- losses / metrics (reference: core/losses.py:5-92 pinned to CPU at model.py:391; core/metric.py:6-71) ---- */
+int tdl_lovasz_hinge(const float* logits, const float* labels, int B, int P, float grad_scale, float* loss_out,
+                     float* dlogits, void* stream);
+int tdl_seg_metrics(const float* logits, const float* labels, int B, int P, float logit_threshold,
+                    int reference_compat, float* iou_out, float* acc_out, void* stream);
+int tdl_softmax_ce(const float* logits, const void* labels_i64, int rows, int classes, float grad_scale, int topk,
+                   float* loss_rows, float* dlogits, float* top1, float* topk_out, void* stream);
+
+/* ---- optimizers + device-resident schedule (reference: model.py:457-467) ---- */
+int tdl_lr_schedule_step(void* global_step_i64, float base_lr, float decay_rate, float decay_steps, float beta1,
+                         float beta2, float* lr_state, void* stream);
+int tdl_sgd_momentum_flat(float* param, void* grad, float* mom, void* shadow_bf16, int64_t n, const float* lr_state,
+                          float momentum, float weight_decay, float grad_scale, int grad_is_bf16, int zero_grad,
+                          void* stream);
+int tdl_adam_flat(float* param, void* grad, float* m1, float* m2, void* shadow_bf16, int64_t n, const float* lr_state,
+                  float beta1, float beta2, float eps, float grad_scale, int grad_is_bf16, int zero_grad,
+                  void* stream);
+int tdl_cast_f32_to_bf16(const float* src, void* dst, int64_t n, void* stream);
+
+/* ---- symmetric heap + P2P fused all-reduce/optimizer over NVLink (reference: MirroredStrategy NCCL all-reduce,
+ *      model.py:115-119, Test.ipynb:200) ---- */
+int tdl_symm_alloc(int64_t bytes, void** out);
+int tdl_symm_free(void* p);
+int tdl_ipc_export(void* p, void* handle64);
+int tdl_ipc_open(const void* handle64, void** out);
+int tdl_ipc_close(void* p);
+int tdl_p2p_flag_bytes(void);
+int tdl_p2p_comm_create(int world, int rank, void** grad_ptrs, void** param_ptrs, void** flag_ptrs, void* epoch_local,
+                        int emulate, void** out_comm);
+int tdl_p2p_comm_destroy(void* comm);
+int tdl_p2p_fused_step(void* comm, int64_t offset, int64_t n, int mode, int kind, int grad_is_bf16, int zero_grad,
+                       float* m1, float* m2, const float* lr_state, float a, float b, float c, float grad_scale,
+                       int max_blocks, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TDL_B200_H_ */

@@ -1,0 +1,319 @@
+"""GPU numerics: every native kernel against a plain PyTorch fp32 reference of the same op (run with -m gpu)."""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def rel_err(a, b):
+    a, b = a.detach().float(), b.detach().float()
+    return float((a - b).abs().max() / (b.abs().max() + 1e-6))
+
+
+@pytest.fixture(scope="module")
+def O():
+    from tensorflowdistributedlearning_b200 import _native
+    from tensorflowdistributedlearning_b200.ops import native_ops
+
+    lib = _native.lib()  # raises if the sm_100a library is missing: no silent fallback on a GPU box
+    assert lib.tdl_version() >= 100
+    return native_ops
+
+
+def _ref_conv(x, w, R, S, stride, dil, pads, bias=None, res=None, relu=False):
+    K, C = w.shape[0], x.shape[-1]
+    w4 = w.float().view(K, R, S, C).permute(0, 3, 1, 2)
+    xin = F.pad(x.float().permute(0, 3, 1, 2), (pads[2], pads[3], pads[0], pads[1]))
+    y = F.conv2d(xin, w4, None, stride=stride, dilation=dil).permute(0, 2, 3, 1)
+    if bias is not None:
+        y = y + bias
+    if res is not None:
+        y = y + res.float()
+    return y.relu() if relu else y
+
+
+CONV_CASES = [
+    # N, H, C, K, R, stride, dil, bias, res, relu
+    (2, 16, 64, 64, 1, 1, 1, False, False, False),
+    (4, 14, 128, 512, 1, 1, 1, True, True, True),
+    (3, 13, 72, 40, 1, 1, 1, False, False, False),       # ragged channels (TMA zero fill on both operands)
+    (2, 56, 64, 64, 3, 1, 1, False, False, False),
+    (8, 7, 512, 512, 3, 1, 1, False, False, False),      # several images per GEMM tile
+    (2, 13, 128, 128, 3, 1, 8, False, False, False),     # dilation 8 on 13x13 (reference block4)
+    (2, 56, 128, 128, 3, 2, 1, False, False, False),     # stride 2 through TMA element strides
+    (2, 51, 64, 64, 3, 2, 1, False, False, False),       # odd size, TF SAME
+    (2, 56, 256, 512, 1, 2, 1, False, False, False),
+]
+
+
+@pytest.mark.parametrize("case", CONV_CASES)
+def test_conv_fprop_tcgen05(O, case):
+    N, H, C, K, R, stride, dil, bias, res, relu = case
+    torch.manual_seed(0)
+    x = torch.randn(N, H, H, C, device="cuda").bfloat16()
+    w = (torch.randn(K, R * R, C, device="cuda") / math.sqrt(R * R * C)).bfloat16()
+    P, pt, pb = O.same_pad(H, R, stride, dil)
+    b = torch.randn(K, device="cuda") if bias else None
+    r = torch.randn(N, P, P, K, device="cuda").bfloat16() if res else None
+    y = O.conv2d_fprop(x, w, R=R, S=R, stride=stride, dil=dil, pad_h=pt, pad_w=pt, out_hw=(P, P), bias=b, residual=r,
+                       relu=relu)
+    ref = _ref_conv(x, w, R, R, stride, dil, (pt, pb, pt, pb), b, r, relu)
+    assert rel_err(y, ref) < 2e-2
+
+
+@pytest.mark.parametrize("case", [(2, 16, 64, 64, 1, 1, 1), (3, 13, 72, 40, 1, 1, 1), (4, 14, 256, 256, 3, 1, 1),
+                                  (8, 7, 128, 128, 3, 1, 1), (2, 13, 128, 128, 3, 1, 2), (2, 56, 64, 128, 3, 2, 1),
+                                  (2, 28, 128, 256, 1, 2, 1)])
+def test_conv_wgrad_tcgen05(O, case):
+    N, H, C, K, R, stride, dil = case
+    torch.manual_seed(1)
+    x = torch.randn(N, H, H, C, device="cuda").bfloat16()
+    P, pt, pb = O.same_pad(H, R, stride, dil)
+    dy = torch.randn(N, P, P, K, device="cuda").bfloat16()
+    dw = torch.zeros(K, R * R, C, device="cuda")
+    O.conv2d_wgrad(x, dy, dw, R=R, S=R, stride=stride, dil=dil, pad_h=pt, pad_w=pt)
+    xin = F.pad(x.float().permute(0, 3, 1, 2), (pt, pb, pt, pb))
+    wr = torch.zeros(K, C, R, R, device="cuda", requires_grad=True)
+    (gw,) = torch.autograd.grad(F.conv2d(xin, wr, None, stride=stride, dilation=dil), wr,
+                                dy.float().permute(0, 3, 1, 2))
+    assert rel_err(dw, gw.permute(0, 2, 3, 1).reshape(K, R * R, C)) < 2e-2
+
+
+@pytest.mark.parametrize("case", [(2, 14, 256, 64, 1, 1), (2, 14, 128, 128, 3, 1), (2, 13, 64, 128, 3, 4)])
+def test_conv_dgrad_via_weight_prep(O, case):
+    N, H, C, K, R, dil = case
+    torch.manual_seed(2)
+    P, pt, pb = O.same_pad(H, R, 1, dil)
+    wm = torch.randn(K, R * R, C, device="cuda") / math.sqrt(R * R * C)
+    wf = torch.empty(K, R * R, C, device="cuda", dtype=torch.bfloat16)
+    wd = torch.empty(C, R * R, K, device="cuda", dtype=torch.bfloat16)
+    O.conv2d_weight_prep(wm, wf, wd, K, R * R, C)
+    assert torch.equal(wf, wm.bfloat16())
+    dy = torch.randn(N, P, P, K, device="cuda").bfloat16()
+    dx = O.conv2d_fprop(dy, wd, R=R, S=R, stride=1, dil=dil, pad_h=(R - 1) * dil - pt, pad_w=(R - 1) * dil - pt,
+                        out_hw=(H, H))
+    xr = torch.zeros(N, C, H + pt + pb, H + pt + pb, device="cuda", requires_grad=True)
+    w4 = wf.float().view(K, R, R, C).permute(0, 3, 1, 2)
+    (gx,) = torch.autograd.grad(F.conv2d(xr, w4, None, dilation=dil), xr, dy.float().permute(0, 3, 1, 2))
+    assert rel_err(dx, gx[:, :, pt:pt + H, pt:pt + H].permute(0, 2, 3, 1)) < 2e-2
+
+
+@pytest.mark.parametrize("rows,C,relu,res", [(4096, 64, True, False), (5000, 256, True, True), (777, 2048, False, False)])
+def test_batch_norm_fwd_bwd(O, rows, C, relu, res):
+    torch.manual_seed(3)
+    x = (torch.randn(rows, C, device="cuda") * 2 + 0.5).bfloat16()
+    gamma = torch.rand(C, device="cuda") + 0.5
+    beta = torch.randn(C, device="cuda") * 0.1
+    rm, rv = torch.zeros(C, device="cuda"), torch.ones(C, device="cuda")
+    r = torch.randn(rows, C, device="cuda").bfloat16() if res else None
+    mean, invstd, scale, shift = O.bn_fwd_stats(x, gamma, beta, rm, rv, 0.99, 1e-3)
+    z = O.bn_apply(x, scale, shift, r, relu)
+    xf = x.float()
+    m_ref, v_ref = xf.mean(0), xf.var(0, unbiased=False)
+    zr = (xf - m_ref) / torch.sqrt(v_ref + 1e-3) * gamma + beta
+    if res:
+        zr = zr + r.float()
+    if relu:
+        zr = zr.relu()
+    assert rel_err(mean, m_ref) < 1e-4
+    assert rel_err(1 / invstd ** 2 - 1e-3, v_ref) < 1e-3
+    assert rel_err(z, zr) < 1e-2
+    assert rel_err(rm, 0.01 * m_ref) < 1e-4
+    assert rel_err(rv, 0.99 + 0.01 * xf.var(0, unbiased=True)) < 1e-4
+    dz = torch.randn(rows, C, device="cuda").bfloat16()
+    dx, dres, dg, db = O.bn_bwd(dz, x, z if res else None, scale, shift, mean, invstd, relu, res)
+    xr = xf.clone().requires_grad_(True)
+    g_, b_ = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+    rr = r.float().clone().requires_grad_(True) if res else None
+    out = (xr - xr.mean(0)) / torch.sqrt(xr.var(0, unbiased=False) + 1e-3) * g_ + b_
+    if res:
+        out = out + rr
+    if relu:
+        out = out * (z.float() > 0).float()  # the kernel's own mask: bf16 rounding makes ~0 entries ambiguous
+    out.backward(dz.float())
+    assert rel_err(dx, xr.grad) < 1e-2
+    assert rel_err(dg, g_.grad) < 1e-3
+    assert rel_err(db, b_.grad) < 1e-3
+    if res:
+        assert rel_err(dres, rr.grad) < 1e-2
+
+
+def test_fused_optimizers_and_device_schedule(O):
+    n = 100_003
+    torch.manual_seed(4)
+    p0, g = torch.randn(n, device="cuda"), torch.randn(n, device="cuda")
+    for gd in (torch.float32, torch.bfloat16):
+        p, m = p0.clone(), torch.zeros(n, device="cuda")
+        sh = torch.empty(n, device="cuda", dtype=torch.bfloat16)
+        step = torch.zeros(1, dtype=torch.int64, device="cuda")
+        lr_state = torch.zeros(2, device="cuda")
+        pr, mr = p0.clone(), torch.zeros(n, device="cuda")
+        for it in range(3):
+            gg = g.to(gd).clone()
+            O.lr_schedule_step(step, lr_state, 0.1, 0.5, 10.0)
+            O.sgd_momentum_flat(p, gg, m, sh, lr_state, 0.9, 1e-4, 0.5, True)
+            assert float(gg.float().abs().max()) == 0.0  # gradient cleared in the same pass
+            mr = 0.9 * mr + (g.to(gd).float() * 0.5 + 1e-4 * pr)
+            pr = pr - 0.1 * 0.5 ** (it / 10.0) * mr
+        assert rel_err(p, pr) < 1e-5 and int(step.item()) == 3
+        assert rel_err(sh, pr) < 1e-2
+        p, m1, m2 = p0.clone(), torch.zeros(n, device="cuda"), torch.zeros(n, device="cuda")
+        step.zero_()
+        pr, a, b = p0.clone(), torch.zeros(n, device="cuda"), torch.zeros(n, device="cuda")
+        for it in range(3):
+            O.lr_schedule_step(step, lr_state, 1e-3, 0.5, 10000.0)
+            O.adam_flat(p, g.to(gd).clone(), m1, m2, None, lr_state, 0.9, 0.999, 1e-8, 1.0, True)
+            t = it + 1
+            lr_t = 1e-3 * 0.5 ** (it / 10000.0) * math.sqrt(1 - 0.999 ** t) / (1 - 0.9 ** t)
+            gr = g.to(gd).float()
+            a, b = 0.9 * a + 0.1 * gr, 0.999 * b + 0.001 * gr * gr
+            pr = pr - lr_t * a / (b.sqrt() + 1e-8)
+        assert rel_err(p, pr) < 1e-4
+
+
+@pytest.mark.parametrize("B,P", [(4, 10201), (2, 16384), (5, 77)])
+def test_lovasz_and_seg_metrics(O, B, P):
+    from tensorflowdistributedlearning_b200.ops import reference as R
+
+    torch.manual_seed(5)
+    logits = torch.randn(B, P, device="cuda") * 2
+    labels = (torch.rand(B, P, device="cuda") > 0.7).float()
+    labels[1] = 0
+    loss, dl = O.lovasz_hinge(logits, labels, True, 1.0 / B)
+    lg = logits.double().cpu().requires_grad_(True)
+    ref = R.lovasz_hinge_per_image(lg, labels.double().cpu())
+    ref.mean().backward()
+    assert rel_err(loss.cpu(), ref) < 1e-4
+    assert rel_err(dl.cpu(), lg.grad) < 1e-4
+    for compat in (True, False):
+        iou, acc = O.seg_metrics(logits, labels, 0.0, compat)
+        riou, racc = R.seg_metrics(logits.cpu(), labels.cpu(), 0.5, compat)
+        assert rel_err(iou.cpu(), riou) < 1e-5 and rel_err(acc.cpu(), racc) < 1e-5
+
+
+@pytest.mark.parametrize("B,C", [(256, 1000), (7, 10)])
+def test_softmax_ce_and_topk(O, B, C):
+    torch.manual_seed(6)
+    logits = torch.randn(B, C, device="cuda") * 3
+    labels = torch.randint(0, C, (B,), device="cuda")
+    loss, dl, t1, t5 = O.softmax_ce(logits, labels, True, 1.0 / B, 5)
+    lr = logits.clone().requires_grad_(True)
+    ref = F.cross_entropy(lr, labels, reduction="none")
+    ref.mean().backward()
+    assert rel_err(loss, ref) < 1e-4 and rel_err(dl, lr.grad) < 1e-3
+    assert torch.equal(t1, (logits.argmax(1) == labels).float())
+    assert torch.equal(t5, (logits.topk(min(5, C), 1).indices == labels[:, None]).any(1).float())
+
+
+def _native_vs_oracle(fn, inputs, tol):
+    from tensorflowdistributedlearning_b200.ops import functional as TFn
+
+    nat = [t.clone().requires_grad_(t.is_floating_point()) for t in inputs]
+    ref = [t.float().clone().requires_grad_(t.is_floating_point()) for t in inputs]
+    try:
+        TFn.force_reference(False)
+        y = fn(*nat)
+        g = torch.randn_like(y)
+        y.backward(g)
+        TFn.force_reference(True)
+        yr = fn(*ref)
+        yr.backward(g.float())
+    finally:
+        TFn.force_reference(False)
+    assert rel_err(y, yr) < tol
+    for a, b in zip(nat, ref):
+        if a.grad is not None:
+            assert rel_err(a.grad, b.grad) < tol
+
+
+def test_spatial_ops(O):
+    from tensorflowdistributedlearning_b200.ops import depthwise, pooling, resize
+
+    torch.manual_seed(7)
+    _native_vs_oracle(lambda t: pooling.max_pool_same(t, 3, 2), [torch.randn(4, 51, 51, 128, device="cuda").bfloat16()], 2e-2)
+    _native_vs_oracle(lambda t: pooling.max_pool(t, 3, 2, (1, 1, 1, 1)),
+                      [torch.randn(2, 56, 56, 64, device="cuda").bfloat16().relu()], 2e-2)  # ties after ReLU
+    _native_vs_oracle(lambda t: pooling.global_avg_pool(t, True), [torch.randn(8, 7, 7, 2048, device="cuda").bfloat16()], 2e-2)
+    for (H, C, st, dil) in [(13, 1024, 1, 8), (38, 728, 1, 1), (19, 728, 2, 1)]:
+        x = torch.randn(2, H, H, C, device="cuda").bfloat16()
+        w = torch.randn(3, 3, C, device="cuda") * 0.3
+        b = torch.randn(C, device="cuda") * 0.1
+        _native_vs_oracle(lambda t, ww, bb: depthwise.depthwise_conv2d(t, ww, bb, st, dil, "SAME", True), [x, w, b], 3e-2)
+    for (h, C, out, dt) in [(1, 256, 13, torch.bfloat16), (13, 256, 26, torch.bfloat16), (26, 1, 101, torch.float32)]:
+        _native_vs_oracle(lambda t: resize.upsample(t, (out, out)), [torch.randn(2, h, h, C, device="cuda").to(dt)], 2e-2)
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_p2p_fused_step_emulated_ranks(O, world):
+    """All ranks' buffers on one GPU, ranks launched back to back with the cross-rank barrier disabled
+    (kernels that spin on each other must not share a GPU): checks reduce / optimizer / all-gather indexing."""
+    from tensorflowdistributedlearning_b200.parallel.p2p import P2PComm, SymmetricBuffer
+
+    n = 300_003
+    torch.manual_seed(8)
+    gbuf = SymmetricBuffer((n + 5) * 4, emulate_world=world)
+    pbuf = SymmetricBuffer((n + 5) * 4, emulate_world=world)
+    grads = [torch.randn(n, device="cuda") for _ in range(world)]
+    p0 = torch.randn(n, device="cuda")
+    lr_state = torch.tensor([0.1, 0.05], device="cuda")
+    for kind in (1, 2):
+        for mode in (1, 2):
+            for r in range(world):
+                gbuf.tensor(torch.float32, r)[:n].copy_(grads[r])
+                pbuf.tensor(torch.float32, r)[:n].copy_(p0)
+            comms = [P2PComm(gbuf, pbuf, emulate_rank=r) for r in range(world)]
+            states = [(torch.zeros(n + 8, device="cuda"), torch.zeros(n + 8, device="cuda")) for _ in range(world)]
+            for r in range(world):
+                comms[r].fused_step(0, n, kind=kind, grad_is_bf16=False, zero_grad=False, m1=states[r][0],
+                                    m2=states[r][1], lr_state=lr_state, a=0.9, b=(1e-4 if kind == 1 else 0.999),
+                                    c=1e-8, mode=mode)
+            torch.cuda.synchronize()
+            g = sum(grads) / world
+            ref = (p0 - 0.1 * (g + 1e-4 * p0)) if kind == 1 else (p0 - 0.05 * (0.1 * g) / ((0.001 * g * g).sqrt() + 1e-8))
+            for r in range(world):
+                assert rel_err(pbuf.tensor(torch.float32, r)[:n], ref) < 1e-5
+                assert torch.equal(pbuf.tensor(torch.float32, r)[:n], pbuf.tensor(torch.float32, 0)[:n])
+            for c in comms:
+                c.close()
+    gbuf.close()
+    pbuf.close()
+
+
+def test_trainer_step_native_matches_torch_path_and_learns():
+    """Same weights, same batches: the native-kernel tower and the torch-op tower follow the same loss curve."""
+    from tensorflowdistributedlearning_b200 import _native as N
+    from tensorflowdistributedlearning_b200 import models
+    from tensorflowdistributedlearning_b200.ops import functional as TFn
+    from tensorflowdistributedlearning_b200.parallel.tower import TowerGroup
+    from tensorflowdistributedlearning_b200.parallel.trainer import TowerTrainer, classification_loss
+
+    group = TowerGroup(device="cuda")
+    curves = {}
+    for name, flag in (("native", False), ("torch", True)):
+        torch.manual_seed(9)
+        TFn.force_reference(flag)
+        try:
+            tr = TowerTrainer(models.resnet50(num_classes=16), group, batch=32, input_hwc=(96, 96, 3),
+                              loss_fn=classification_loss, use_graph=(not flag), kind="sgdm", lr=0.05, momentum=0.9)
+            gen = torch.Generator().manual_seed(1)
+            tr.images.copy_(torch.randint(0, 256, tr.images.shape, dtype=torch.uint8, generator=gen))
+            tr.labels.copy_(torch.randint(0, 16, tr.labels.shape, generator=gen))
+            before = N.kernel_launches
+            tr.warmup_and_capture(warmup=3)
+            losses = []
+            for _ in range(12):
+                tr.run_step()
+                losses.append(float(tr.loss.item()))
+            curves[name] = losses
+            if not flag:
+                assert N.kernel_launches - before > 300, "native kernels were not used"
+                assert tr._graph is not None
+            tr.close()
+        finally:
+            TFn.force_reference(False)
+    assert curves["native"][-1] < curves["native"][0] * 0.8, curves
+    assert abs(curves["native"][0] - curves["torch"][0]) < 0.15, curves
+    assert abs(curves["native"][-1] - curves["torch"][-1]) < 0.5, curves

@@ -1,0 +1,117 @@
+"""Model zoo structure: variable manifest, shape traces, atrous bookkeeping."""
+import pytest
+import torch
+
+from tensorflowdistributedlearning_b200 import models as M
+from tensorflowdistributedlearning_b200.models.resnet import Block, resnet_v2_beta_block, stack_blocks_plan
+from tensorflowdistributedlearning_b200.ops.layers import iter_tf_variables
+
+
+@pytest.fixture(scope="module")
+def seg():
+    torch.manual_seed(0)
+    return M.ResNetSegModel(model_name="model")
+
+
+def test_reference_manifest_counts(seg):
+    train = [(n, t) for n, t, k in iter_tf_variables(seg) if isinstance(t, torch.nn.Parameter)]
+    stats = [(n, t) for n, t, k in iter_tf_variables(seg) if not isinstance(t, torch.nn.Parameter)]
+    assert len(train) == 208
+    assert sum(t.numel() for _, t in train) == 41_814_025
+    assert len(stats) == 118
+    assert sum(t.numel() for _, t in stats) == 65_632
+    assert len({n for n, _ in train}) == 208  # names unique
+
+
+def test_reference_variable_names(seg):
+    names = {n for n, _, _ in iter_tf_variables(seg)}
+    for expect in [
+        "model/resnet_v2/conv1_1/weights", "model/resnet_v2/conv1_3/BatchNorm/moving_variance",
+        "model/resnet_v2/postnorm/gamma", "model/resnet_v2/block1/unit_1/bottleneck_v2/preact/beta",
+        "model/resnet_v2/block1/unit_1/bottleneck_v2/shortcut/biases",
+        "model/resnet_v2/block2/unit_3/bottleneck_v2/Conv/BatchNorm/beta",
+        "model/resnet_v2/block4/unit_2/bottleneck_v2/conv3/weights",
+        "model/assp/conv/conv_3x3_2_depthwise/depthwise_weights", "model/assp/conv/conv_3x3_2_depthwise/biases",
+        "model/assp/conv/conv_3x3_3_pointwise/BatchNorm/gamma", "model/assp/pooling/conv_1x1/weights",
+        "model/assp/conv_1x1/weights", "model/decoder/conv_1x1/BatchNorm/moving_mean",
+        "model/decoder/conv_3x3/biases",
+    ]:
+        assert expect in names, expect
+
+
+def test_reference_atrous_plan_and_shape_trace(seg):
+    assert seg.backbone.unit_plan == [[(1, 1), (1, 1), (2, 1)], [(1, 1)] * 4, [(1, 2)] * 6, [(1, 4), (1, 8), (1, 4)]]
+    seg.eval()
+    x = torch.randn(1, 101, 101, 2)
+    with torch.no_grad():
+        _, ep = seg.backbone(x, collect=True)
+        y = seg(x)
+    assert ep["model/resnet_v2/block1"].shape == (1, 13, 13, 512)
+    assert ep["model/resnet_v2/block1/unit_1/bottleneck_v2/conv3"].shape == (1, 26, 26, 512)
+    assert ep["model/resnet_v2/block2"].shape == (1, 13, 13, 1032)
+    assert ep["model/resnet_v2/block3"].shape == (1, 13, 13, 2048)
+    assert ep["model/resnet_v2/block4"].shape == (1, 13, 13, 1024)
+    assert y.shape == (1, 101, 101, 1)
+
+
+def test_stack_blocks_plan_errors():
+    blocks = [resnet_v2_beta_block("b1", 8, 2, 2, "bottleneck"), resnet_v2_beta_block("b2", 8, 2, 2, "bottleneck")]
+    assert stack_blocks_plan(blocks, None) == [[(1, 1), (2, 1)], [(1, 1), (2, 1)]]
+    assert stack_blocks_plan(blocks, 2) == [[(1, 1), (2, 1)], [(1, 1), (1, 1)]]
+    with pytest.raises(ValueError):
+        stack_blocks_plan(blocks, 8)
+
+
+def test_strided_unit_equals_conv_then_subsample():
+    """Defect 13: the reference convolves at full resolution and then subsamples; the strided conv is the same math."""
+    from tensorflowdistributedlearning_b200.ops import functional as TF
+    torch.manual_seed(0)
+    x = torch.randn(2, 13, 13, 4)
+    w = torch.randn(6, 3, 3, 4)
+    full = TF.conv2d(x, w, None, 1, 1, "SAME")[:, ::2, ::2, :]
+    strided = TF.conv2d(x, w, None, 2, 1, (1, 1, 1, 1))
+    assert torch.allclose(full, strided, atol=1e-5)
+
+
+def test_basic_block_variant_builds_and_runs():
+    m = M.ResNetSegModel(model_name="m", n_blocks=(1, 1, 1), block_type="basic_block", base_depth=32)
+    m.eval()
+    with torch.no_grad():
+        y = m(torch.randn(1, 101, 101, 2))
+    assert y.shape == (1, 101, 101, 1)
+
+
+def test_canonical_resnets_param_counts():
+    r50 = M.resnet50()
+    assert sum(p.numel() for p in r50.parameters()) == 25_557_032
+    assert len(list(r50.parameters())) == 161
+    r152 = M.resnet152()
+    assert sum(p.numel() for p in r152.parameters()) == 60_192_808
+    assert len(list(r152.parameters())) == 467
+
+
+def test_resnet50_forward_shape():
+    m = M.resnet50(num_classes=10)
+    y = m(torch.randn(2, 64, 64, 3))
+    assert y.shape == (2, 10)
+
+
+def test_xception41_trace_and_params():
+    m = M.xception_41(num_classes=1000)
+    n = sum(p.numel() for p in m.parameters())
+    assert 26.5e6 < n < 27.5e6
+    assert len(m.units) == 1 + 1 + 1 + 8 + 1 + 1  # all middle-flow units are built (reference indent bug fixed)
+    m.eval()
+    with torch.no_grad():
+        f = m.features(torch.randn(1, 299, 299, 3))
+        y = m(torch.randn(1, 299, 299, 3))
+    assert f.shape == (1, 10, 10, 2048)
+    assert y.shape == (1, 1000)
+
+
+def test_xception_output_stride_16():
+    m = M.xception_41(num_classes=None, output_stride=16, multi_grid=[1, 2, 4])
+    m.eval()
+    with torch.no_grad():
+        f = m(torch.randn(1, 129, 129, 3))
+    assert f.shape[1:3] == (9, 9)
