@@ -363,3 +363,88 @@ TDL_API int tdl_bn_bwd_apply(const void* dz, const void* x, const void* z, const
   TDL_LAUNCH_OK("bn_bwd_apply_kernel");
   return 0;
 }
+
+// ------------------------------------------------------------------------------------------------------------
+// Allocation-free variant of tdl_bn_fwd_stats.
+//
+// Some users of this library cannot hand us scratch memory because they cannot obtain any: processes whose
+// whole device-memory budget was reserved up front by their own arena or by a serving runtime (a late
+// cudaMalloc either fails or is forbidden by policy), and latency-critical loops in which cudaMalloc/cudaFree
+// are unacceptable because they synchronise the whole device.  For them the per-CTA partial sums live in a
+// fixed array that is part of the library image itself.
+//
+//   * Limit: kStaticScratchFloats floats (4 MiB).  Every GPU that loads the library carries this array from
+//     module load until the process exits, whether or not the entry point is ever called.
+//   * The array's name is only a host-side handle; the device address is looked up with cudaGetSymbolAddress
+//     once per device, on that device's first call (with that device current).  That first call therefore does
+//     a little set-up work and should be made before any stream capture begins; later calls only launch.
+//   * All calls share the one array and it keeps whatever the previous call left behind.  Nothing in it has to
+//     start at zero: the first kernel overwrites every partial slot that the second kernel reads, so no clearing
+//     pass is needed.  Two calls whose kernels can overlap on the GPU (different streams without an ordering
+//     between them, or two host threads) race on the array and produce garbage -- serialise them.
+//   * No cudaMalloc, cudaFree or allocating library routine is called on this path.
+// ------------------------------------------------------------------------------------------------------------
+#include <mutex>
+
+namespace tdl {
+namespace bn {
+
+constexpr int64_t kStaticScratchFloats = 1 << 20;
+static __device__ __align__(256) float g_bn_static_scratch[kStaticScratchFloats];
+
+constexpr int kMaxDevices = 64;
+
+// Device address of g_bn_static_scratch for the current device (looked up once per device).
+static int static_scratch_address(float** out) {
+  static std::mutex mu;
+  static float* cache[kMaxDevices] = {nullptr};
+  int dev = 0;
+  TDL_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return tdl::fail(-2, "%s%s", "tdl_bn_fwd_stats_noalloc: device ordinal out of range", "");
+  std::lock_guard<std::mutex> lock(mu);
+  if (cache[dev] == nullptr) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_bn_static_scratch);
+    if (e != cudaSuccess) return tdl::cuda_fail(e, "cudaGetSymbolAddress(g_bn_static_scratch)");
+    if (p == nullptr) return tdl::fail(-2, "%s%s", "cudaGetSymbolAddress returned a null address", "");
+    cache[dev] = static_cast<float*>(p);
+  }
+  *out = cache[dev];
+  return 0;
+}
+
+}  // namespace bn
+}  // namespace tdl
+
+// Same result as tdl_bn_fwd_stats, but the partial sums go to the library's own fixed array instead of caller
+// scratch.  Shapes whose partials need more than 1,048,576 floats are refused.  See the block comment above for
+// the sharing / first-call rules.
+TDL_API int tdl_bn_fwd_stats_noalloc(const void* x, int64_t rows, int C, const float* gamma, const float* beta,
+                                     float* running_mean, float* running_var, float decay, float eps, float* mean,
+                                     float* invstd, float* scale, float* shift, void* stream) {
+  TDL_REQUIRE(C > 0 && C % 8 == 0, "C must be a positive multiple of 8");
+  TDL_REQUIRE(rows > 0, "empty input");
+  ReduceShape s = reduce_shape(rows, C);
+  const int64_t need = (int64_t)s.gx * 2 * C;
+  if (need > kStaticScratchFloats) {
+    snprintf(tdl::err_buf(), 512,
+             "tdl_bn_fwd_stats_noalloc: this shape (rows=%lld, C=%d) needs %lld floats of scratch but the built-in "
+             "array holds %lld; use tdl_bn_fwd_stats with caller-provided scratch",
+             (long long)rows, C, (long long)need, (long long)kStaticScratchFloats);
+    return -5;
+  }
+  float* scratch = nullptr;
+  int rc = static_scratch_address(&scratch);
+  if (rc != 0) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  dim3 grid(s.gx, s.gy);
+  bn_partial_stats_kernel<<<grid, kThreads, kThreads * 16 * sizeof(float), st>>>((const bf16*)x, rows, C, s.tx, s.ty,
+                                                                                  scratch);
+  TDL_LAUNCH_OK("bn_partial_stats_kernel");
+  const double unbias = rows > 1 ? (double)rows / (double)(rows - 1) : 1.0;
+  bn_finalize_stats_kernel<<<(C + 127) / 128, 128, 0, st>>>(scratch, s.gx, C, 1.0 / (double)rows, unbias, gamma, beta,
+                                                            running_mean, running_var, decay, eps, mean, invstd, scale,
+                                                            shift);
+  TDL_LAUNCH_OK("bn_finalize_stats_kernel");
+  return 0;
+}

@@ -40,6 +40,14 @@ int64_t tdl_bn_scratch_floats(int64_t rows, int C);
 int tdl_bn_fwd_stats(const void* x, int64_t rows, int C, float* scratch, int64_t scratch_floats, const float* gamma,
                      const float* beta, float* running_mean, float* running_var, float decay, float eps, float* mean,
                      float* invstd, float* scale, float* shift, void* stream);
+/* No counterpart in the reference (an addition of this library).  Allocation-free variant of tdl_bn_fwd_stats
+ * for callers that cannot supply scratch: the partial sums go to a fixed 1,048,576-float (4 MiB) array inside the
+ * library (held by every GPU that loads it, until exit); larger shapes are refused with an error.  The first call
+ * on a device looks up the array's device address (make it before any stream capture); all calls share the array,
+ * so calls that can overlap on the GPU race.  Nothing in the array needs clearing between calls. */
+int tdl_bn_fwd_stats_noalloc(const void* x, int64_t rows, int C, const float* gamma, const float* beta,
+                             float* running_mean, float* running_var, float decay, float eps, float* mean,
+                             float* invstd, float* scale, float* shift, void* stream);
 int tdl_bn_infer_scale_shift(const float* gamma, const float* beta, const float* running_mean,
                              const float* running_var, float eps, float* scale, float* shift, int C, void* stream);
 int tdl_bn_apply(const void* x, const float* scale, const float* shift, const void* residual, void* y, int64_t rows,
