@@ -29,8 +29,8 @@ static ReduceShape reduce_shape(int64_t rows, int C) {
   while (s.tx < 32 && s.tx < c8) s.tx <<= 1;
   s.ty = kThreads / s.tx;
   s.gy = (int)cdiv(c8, s.tx);
-  int64_t want = cdiv(rows, (int64_t)s.ty * 4);
-  int64_t cap = (int64_t)num_sms() * 8 / s.gy;
+  int64_t want = cdiv(rows, (int64_t)s.ty * 8);
+  int64_t cap = (int64_t)num_sms() * 4 / s.gy;
   if (cap < 1) cap = 1;
   if (want > cap) want = cap;
   if (want < 1) want = 1;
@@ -54,15 +54,24 @@ bn_partial_stats_kernel(const bf16* __restrict__ x, int64_t rows, int C, int tx,
 #pragma unroll
   for (int j = 0; j < 8; ++j) s[j] = q[j] = 0.f;
   if (cv < c8) {
-    for (int64_t r = (int64_t)blockIdx.x * ty + ry; r < rows; r += (int64_t)gridDim.x * ty) {
+    const int64_t step = (int64_t)gridDim.x * ty;
+    const bf16* col = x + cv * 8;
+    int64_t r = (int64_t)blockIdx.x * ty + ry;
+    for (; r + 3 * step < rows; r += 4 * step) {  // four independent 16-byte loads in flight
+      const bf16x8 v0 = ld8(col + r * C), v1 = ld8(col + (r + step) * C), v2 = ld8(col + (r + 2 * step) * C),
+                   v3 = ld8(col + (r + 3 * step) * C);
       float f[8];
-      unpack8(ld8(x + r * C + cv * 8), f);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        s[j] += f[j];
-        q[j] = fmaf(f[j], f[j], q[j]);
-      }
+#define TDL_ACC(v)                    \
+  unpack8(v, f);                      \
+  _Pragma("unroll") for (int j = 0; j < 8; ++j) { s[j] += f[j]; q[j] = fmaf(f[j], f[j], q[j]); }
+      TDL_ACC(v0) TDL_ACC(v1) TDL_ACC(v2) TDL_ACC(v3)
     }
+    for (; r < rows; r += step) {
+      float f[8];
+      const bf16x8 v0 = ld8(col + r * C);
+      TDL_ACC(v0)
+    }
+#undef TDL_ACC
   }
   float* mine = sm + (size_t)(ry * tx + cx) * 16;
 #pragma unroll
@@ -85,19 +94,39 @@ bn_partial_stats_kernel(const bf16* __restrict__ x, int64_t rows, int C, int tx,
   }
 }
 
-__global__ void bn_finalize_stats_kernel(const float* __restrict__ partial, int nparts, int C, double inv_n,
-                                         double unbias, const float* __restrict__ gamma,
-                                         const float* __restrict__ beta, float* __restrict__ running_mean,
-                                         float* __restrict__ running_var, float decay, float eps,
-                                         float* __restrict__ mean_out, float* __restrict__ invstd_out,
-                                         float* __restrict__ scale_out, float* __restrict__ shift_out) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
+// Second-level reduce: 32 channels x 8 slices of the partial list per CTA, fp64 accumulation.
+constexpr int kFinThreads = 256;
+
+__device__ __forceinline__ void reduce_partials(const float* __restrict__ partial, int nparts, int C, int c,
+                                                double* s_out, double* q_out) {
+  __shared__ double sm_s[8][32], sm_q[8][32];
+  const int lane = threadIdx.x & 31, slice = threadIdx.x >> 5;
   double s = 0.0, q = 0.0;
-  for (int p = 0; p < nparts; ++p) {
-    s += (double)partial[((size_t)p * 2) * C + c];
-    q += (double)partial[((size_t)p * 2 + 1) * C + c];
-  }
+  if (c < C)
+    for (int p = slice; p < nparts; p += 8) {
+      s += (double)partial[((size_t)p * 2) * C + c];
+      q += (double)partial[((size_t)p * 2 + 1) * C + c];
+    }
+  sm_s[slice][lane] = s;
+  sm_q[slice][lane] = q;
+  __syncthreads();
+  s = 0.0; q = 0.0;
+  if (slice == 0)
+    for (int t = 0; t < 8; ++t) { s += sm_s[t][lane]; q += sm_q[t][lane]; }
+  *s_out = s;
+  *q_out = q;
+}
+
+__global__ void __launch_bounds__(kFinThreads)
+bn_finalize_stats_kernel(const float* __restrict__ partial, int nparts, int C, double inv_n, double unbias,
+                         const float* __restrict__ gamma, const float* __restrict__ beta,
+                         float* __restrict__ running_mean, float* __restrict__ running_var, float decay, float eps,
+                         float* __restrict__ mean_out, float* __restrict__ invstd_out, float* __restrict__ scale_out,
+                         float* __restrict__ shift_out) {
+  const int c = blockIdx.x * 32 + (threadIdx.x & 31);
+  double s, q;
+  reduce_partials(partial, nparts, C, c, &s, &q);
+  if ((threadIdx.x >> 5) != 0 || c >= C) return;
   const double m = s * inv_n;
   double var = q * inv_n - m * m;
   if (var < 0.0) var = 0.0;
@@ -126,32 +155,58 @@ __global__ void bn_infer_scale_shift_kernel(const float* __restrict__ gamma, con
 }
 
 // ---- forward apply: y = relu(x*scale + shift (+ residual)) ----
+// Every thread owns one 8-channel column for all of its rows: the per-channel constants are loaded once into
+// registers, the row loop keeps two independent 16-byte loads in flight.
 __global__ void __launch_bounds__(kThreads)
 bn_apply_kernel(const bf16* __restrict__ x, const float* __restrict__ scale, const float* __restrict__ shift,
-                const bf16* __restrict__ residual, bf16* __restrict__ y, int64_t nvec, int c8, int relu) {
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
-    const int cv = (int)(i % c8);
+                const bf16* __restrict__ residual, bf16* __restrict__ y, int64_t rows, int C, int tx, int ty,
+                int relu) {
+  const int cx = threadIdx.x % tx;
+  const int ry = threadIdx.x / tx;
+  const int cv = blockIdx.y * tx + cx;
+  if (cv >= C / 8) return;
+  float sc[8], sh[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { sc[j] = scale[cv * 8 + j]; sh[j] = shift[cv * 8 + j]; }
+  const int64_t step = (int64_t)gridDim.x * ty;
+  const int64_t col = (int64_t)cv * 8;
+  auto one = [&](int64_t r, const bf16x8& xv, const bf16x8* rv) {
     float f[8];
-    unpack8(ld8(x + i * 8), f);
-    const float4 s0 = *reinterpret_cast<const float4*>(scale + cv * 8);
-    const float4 s1 = *reinterpret_cast<const float4*>(scale + cv * 8 + 4);
-    const float4 h0 = *reinterpret_cast<const float4*>(shift + cv * 8);
-    const float4 h1 = *reinterpret_cast<const float4*>(shift + cv * 8 + 4);
-    const float sc[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
-    const float sh[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+    unpack8(xv, f);
 #pragma unroll
     for (int j = 0; j < 8; ++j) f[j] = bn_affine(f[j], sc[j], sh[j]);
-    if (residual) {
-      float r[8];
-      unpack8(ld8(residual + i * 8), r);
+    if (rv) {
+      float rr[8];
+      unpack8(*rv, rr);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) f[j] += r[j];
+      for (int j = 0; j < 8; ++j) f[j] += rr[j];
     }
     if (relu) {
 #pragma unroll
       for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
     }
-    st8(y + i * 8, pack8(f));
+    st8(y + r * C + col, pack8(f));
+  };
+  int64_t r = (int64_t)blockIdx.x * ty + ry;
+  for (; r + step < rows; r += 2 * step) {
+    const bf16x8 x0 = ld8(x + r * C + col), x1 = ld8(x + (r + step) * C + col);
+    if (residual) {
+      const bf16x8 r0 = ld8(residual + r * C + col), r1 = ld8(residual + (r + step) * C + col);
+      one(r, x0, &r0);
+      one(r + step, x1, &r1);
+    } else {
+      one(r, x0, nullptr);
+      one(r + step, x1, nullptr);
+    }
+  }
+  for (; r < rows; r += step) {
+    const bf16x8 x0 = ld8(x + r * C + col);
+    if (residual) {
+      const bf16x8 r0 = ld8(residual + r * C + col);
+      one(r, x0, &r0);
+    } else {
+      one(r, x0, nullptr);
+    }
   }
 }
 
@@ -170,22 +225,24 @@ bn_bwd_partial_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ x, c
 #pragma unroll
   for (int j = 0; j < 8; ++j) s[j] = q[j] = 0.f;
   if (cv < c8) {
-    float sc[8], sh[8], mu[8], is[8];
+    float sc[8], sh[8], mu[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       sc[j] = scale[cv * 8 + j];
       sh[j] = shift[cv * 8 + j];
       mu[j] = mean[cv * 8 + j];
-      is[j] = invstd[cv * 8 + j];
     }
-    for (int64_t r = (int64_t)blockIdx.x * ty + ry; r < rows; r += (int64_t)gridDim.x * ty) {
+    const int64_t step = (int64_t)gridDim.x * ty;
+    const int64_t col = (int64_t)cv * 8;
+    // q accumulates dy * (x - mean); the invstd factor is applied once at the end
+    auto one = [&](const bf16x8& gv, const bf16x8& xv, const bf16x8* zv) {
       float g[8], f[8];
-      unpack8(ld8(dz + r * C + cv * 8), g);
-      unpack8(ld8(x + r * C + cv * 8), f);
+      unpack8(gv, g);
+      unpack8(xv, f);
       if (relu) {
-        if (z) {
+        if (zv) {
           float zz[8];
-          unpack8(ld8(z + r * C + cv * 8), zz);
+          unpack8(*zv, zz);
 #pragma unroll
           for (int j = 0; j < 8; ++j) g[j] = zz[j] > 0.f ? g[j] : 0.f;
         } else {
@@ -196,9 +253,33 @@ bn_bwd_partial_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ x, c
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         s[j] += g[j];
-        q[j] = fmaf(g[j], (f[j] - mu[j]) * is[j], q[j]);
+        q[j] = fmaf(g[j], f[j] - mu[j], q[j]);
+      }
+    };
+    int64_t r = (int64_t)blockIdx.x * ty + ry;
+    for (; r + step < rows; r += 2 * step) {
+      const bf16x8 g0 = ld8(dz + r * C + col), g1 = ld8(dz + (r + step) * C + col);
+      const bf16x8 x0 = ld8(x + r * C + col), x1 = ld8(x + (r + step) * C + col);
+      if (relu && z) {
+        const bf16x8 z0 = ld8(z + r * C + col), z1 = ld8(z + (r + step) * C + col);
+        one(g0, x0, &z0);
+        one(g1, x1, &z1);
+      } else {
+        one(g0, x0, nullptr);
+        one(g1, x1, nullptr);
       }
     }
+    for (; r < rows; r += step) {
+      const bf16x8 g0 = ld8(dz + r * C + col), x0 = ld8(x + r * C + col);
+      if (relu && z) {
+        const bf16x8 z0 = ld8(z + r * C + col);
+        one(g0, x0, &z0);
+      } else {
+        one(g0, x0, nullptr);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) q[j] *= invstd[cv * 8 + j];
   }
   float* mine = sm + (size_t)(ry * tx + cx) * 16;
 #pragma unroll
@@ -207,7 +288,6 @@ bn_bwd_partial_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ x, c
     mine[8 + j] = q[j];
   }
   __syncthreads();
-  // tx*16 (column, value) pairs are each reduced over the ty row-threads by one thread
   for (int idx = threadIdx.x; idx < tx * 16; idx += kThreads) {
     const int col = idx >> 4;
     const int val = idx & 15;
@@ -215,22 +295,19 @@ bn_bwd_partial_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ x, c
     if (cvv >= c8) continue;
     float acc = 0.f;
     for (int t = 0; t < ty; ++t) acc += sm[(size_t)(t * tx + col) * 16 + val];
-    const int which = val >> 3;  // 0 = first statistic, 1 = second
+    const int which = val >> 3;
     const int ch = cvv * 8 + (val & 7);
     partial[((size_t)blockIdx.x * 2 + which) * C + ch] = acc;
   }
 }
 
-__global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int nparts, int C,
-                                       float* __restrict__ dbeta, float* __restrict__ dgamma,
-                                       float* __restrict__ acc_dbeta, float* __restrict__ acc_dgamma) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  double s = 0.0, q = 0.0;
-  for (int p = 0; p < nparts; ++p) {
-    s += (double)partial[((size_t)p * 2) * C + c];
-    q += (double)partial[((size_t)p * 2 + 1) * C + c];
-  }
+__global__ void __launch_bounds__(kFinThreads)
+bn_bwd_finalize_kernel(const float* __restrict__ partial, int nparts, int C, float* __restrict__ dbeta,
+                       float* __restrict__ dgamma, float* __restrict__ acc_dbeta, float* __restrict__ acc_dgamma) {
+  const int c = blockIdx.x * 32 + (threadIdx.x & 31);
+  double s, q;
+  reduce_partials(partial, nparts, C, c, &s, &q);
+  if ((threadIdx.x >> 5) != 0 || c >= C) return;
   dbeta[c] = (float)s;
   dgamma[c] = (float)q;
   if (acc_dbeta) acc_dbeta[c] += (float)s;
@@ -238,35 +315,83 @@ __global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int np
 }
 
 // ---- backward apply: dx = gamma*invstd*(dy - dbeta/n - xhat*dgamma/n); dres = dy ----
+// Folded per channel into dx = A*dy + B*x + D so the row loop is three FMAs per element.
 __global__ void __launch_bounds__(kThreads)
 bn_bwd_apply_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ x, const bf16* __restrict__ z,
                     const float* __restrict__ scale, const float* __restrict__ shift, const float* __restrict__ mean,
                     const float* __restrict__ invstd, const float* __restrict__ dbeta,
                     const float* __restrict__ dgamma, float inv_n, bf16* __restrict__ dx, bf16* __restrict__ dres,
-                    int64_t nvec, int c8, int relu) {
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
-    const int cv = (int)(i % c8);
-    float g[8], f[8];
-    unpack8(ld8(dz + i * 8), g);
-    unpack8(ld8(x + i * 8), f);
-    float zz[8];
-    if (relu && z) unpack8(ld8(z + i * 8), zz);
-    float o[8];
+                    int64_t rows, int C, int tx, int ty, int relu) {
+  const int cx = threadIdx.x % tx;
+  const int ry = threadIdx.x / tx;
+  const int cv = blockIdx.y * tx + cx;
+  if (cv >= C / 8) return;
+  float sc[8], sh[8], B[8], D[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const int c = cv * 8 + j;
-      const float sc = scale[c], sh = shift[c], mu = mean[c], is = invstd[c];
-      if (relu) {
-        const bool on = z ? (zz[j] > 0.f) : (bn_affine(f[j], sc, sh) > 0.f);
-        g[j] = on ? g[j] : 0.f;
-      }
-      const float xhat = (f[j] - mu) * is;
-      // scale == gamma * invstd
-      o[j] = sc * (g[j] - dbeta[c] * inv_n - xhat * dgamma[c] * inv_n);
-    }
-    st8(dx + i * 8, pack8(o));
-    if (dres) st8(dres + i * 8, pack8(g));
+  for (int j = 0; j < 8; ++j) {
+    const int c = cv * 8 + j;
+    sc[j] = scale[c];  // == gamma * invstd == A
+    sh[j] = shift[c];
+    const float k = sc[j] * invstd[c] * dgamma[c] * inv_n;
+    B[j] = -k;
+    D[j] = k * mean[c] - sc[j] * dbeta[c] * inv_n;
   }
+  const int64_t step = (int64_t)gridDim.x * ty;
+  const int64_t col = (int64_t)cv * 8;
+  auto one = [&](int64_t r, const bf16x8& gv, const bf16x8& xv, const bf16x8* zv) {
+    float g[8], f[8], o[8];
+    unpack8(gv, g);
+    unpack8(xv, f);
+    if (relu) {
+      if (zv) {
+        float zz[8];
+        unpack8(*zv, zz);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) g[j] = zz[j] > 0.f ? g[j] : 0.f;
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) g[j] = bn_affine(f[j], sc[j], sh[j]) > 0.f ? g[j] : 0.f;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = fmaf(sc[j], g[j], fmaf(B[j], f[j], D[j]));
+    st8(dx + r * C + col, pack8(o));
+    if (dres) st8(dres + r * C + col, pack8(g));
+  };
+  int64_t r = (int64_t)blockIdx.x * ty + ry;
+  for (; r + step < rows; r += 2 * step) {
+    const bf16x8 g0 = ld8(dz + r * C + col), g1 = ld8(dz + (r + step) * C + col);
+    const bf16x8 x0 = ld8(x + r * C + col), x1 = ld8(x + (r + step) * C + col);
+    if (relu && z) {
+      const bf16x8 z0 = ld8(z + r * C + col), z1 = ld8(z + (r + step) * C + col);
+      one(r, g0, x0, &z0);
+      one(r + step, g1, x1, &z1);
+    } else {
+      one(r, g0, x0, nullptr);
+      one(r + step, g1, x1, nullptr);
+    }
+  }
+  for (; r < rows; r += step) {
+    const bf16x8 g0 = ld8(dz + r * C + col), x0 = ld8(x + r * C + col);
+    if (relu && z) {
+      const bf16x8 z0 = ld8(z + r * C + col);
+      one(r, g0, x0, &z0);
+    } else {
+      one(r, g0, x0, nullptr);
+    }
+  }
+}
+
+// grid for the "thread owns a channel column" elementwise kernels
+static ReduceShape apply_shape(int64_t rows, int C) {
+  ReduceShape s = reduce_shape(rows, C);
+  int64_t want = cdiv(rows, (int64_t)s.ty * 4);
+  int64_t cap = (int64_t)num_sms() * 8 / s.gy;
+  if (cap < 1) cap = 1;
+  if (want > cap) want = cap;
+  if (want < 1) want = 1;
+  s.gx = (int)want;
+  return s;
 }
 
 static int ew_blocks(int64_t nvec) {
@@ -305,9 +430,9 @@ TDL_API int tdl_bn_fwd_stats(const void* x, int64_t rows, int C, float* scratch,
                                                                                   scratch);
   TDL_LAUNCH_OK("bn_partial_stats_kernel");
   const double unbias = rows > 1 ? (double)rows / (double)(rows - 1) : 1.0;
-  bn_finalize_stats_kernel<<<(C + 127) / 128, 128, 0, st>>>(scratch, s.gx, C, 1.0 / (double)rows, unbias, gamma, beta,
-                                                            running_mean, running_var, decay, eps, mean, invstd, scale,
-                                                            shift);
+  bn_finalize_stats_kernel<<<(C + 31) / 32, kFinThreads, 0, st>>>(scratch, s.gx, C, 1.0 / (double)rows, unbias, gamma,
+                                                                  beta, running_mean, running_var, decay, eps, mean,
+                                                                  invstd, scale, shift);
   TDL_LAUNCH_OK("bn_finalize_stats_kernel");
   return 0;
 }
@@ -325,10 +450,11 @@ TDL_API int tdl_bn_infer_scale_shift(const float* gamma, const float* beta, cons
 TDL_API int tdl_bn_apply(const void* x, const float* scale, const float* shift, const void* residual, void* y,
                          int64_t rows, int C, int relu, void* stream) {
   TDL_REQUIRE(C > 0 && C % 8 == 0, "C must be a positive multiple of 8");
-  const int64_t nvec = rows * (C / 8);
-  if (nvec == 0) return 0;
-  bn_apply_kernel<<<ew_blocks(nvec), kThreads, 0, (cudaStream_t)stream>>>(
-      (const bf16*)x, scale, shift, (const bf16*)residual, (bf16*)y, nvec, C / 8, relu);
+  if (rows == 0) return 0;
+  ReduceShape s = apply_shape(rows, C);
+  dim3 grid(s.gx, s.gy);
+  bn_apply_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>((const bf16*)x, scale, shift, (const bf16*)residual,
+                                                               (bf16*)y, rows, C, s.tx, s.ty, relu);
   TDL_LAUNCH_OK("bn_apply_kernel");
   return 0;
 }
@@ -346,7 +472,7 @@ TDL_API int tdl_bn_bwd_reduce(const void* dz, const void* x, const void* z, cons
   bn_bwd_partial_kernel<<<grid, kThreads, kThreads * 16 * sizeof(float), st>>>(
       (const bf16*)dz, (const bf16*)x, (const bf16*)z, scale, shift, mean, invstd, rows, C, s.tx, s.ty, relu, scratch);
   TDL_LAUNCH_OK("bn_bwd_partial_kernel");
-  bn_bwd_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(scratch, s.gx, C, dbeta, dgamma, acc_dbeta, acc_dgamma);
+  bn_bwd_finalize_kernel<<<(C + 31) / 32, kFinThreads, 0, st>>>(scratch, s.gx, C, dbeta, dgamma, acc_dbeta, acc_dgamma);
   TDL_LAUNCH_OK("bn_bwd_finalize_kernel");
   return 0;
 }
@@ -355,11 +481,12 @@ TDL_API int tdl_bn_bwd_apply(const void* dz, const void* x, const void* z, const
                              const float* mean, const float* invstd, const float* dgamma, const float* dbeta,
                              void* dx, void* dres, int64_t rows, int C, int relu, void* stream) {
   TDL_REQUIRE(C > 0 && C % 8 == 0, "C must be a positive multiple of 8");
-  const int64_t nvec = rows * (C / 8);
-  if (nvec == 0) return 0;
-  bn_bwd_apply_kernel<<<ew_blocks(nvec), kThreads, 0, (cudaStream_t)stream>>>(
-      (const bf16*)dz, (const bf16*)x, (const bf16*)z, scale, shift, mean, invstd, dbeta, dgamma,
-      1.f / (float)rows, (bf16*)dx, (bf16*)dres, nvec, C / 8, relu);
+  if (rows == 0) return 0;
+  ReduceShape s = apply_shape(rows, C);
+  dim3 grid(s.gx, s.gy);
+  bn_bwd_apply_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(
+      (const bf16*)dz, (const bf16*)x, (const bf16*)z, scale, shift, mean, invstd, dbeta, dgamma, 1.f / (float)rows,
+      (bf16*)dx, (bf16*)dres, rows, C, s.tx, s.ty, relu);
   TDL_LAUNCH_OK("bn_bwd_apply_kernel");
   return 0;
 }
@@ -442,9 +569,9 @@ TDL_API int tdl_bn_fwd_stats_noalloc(const void* x, int64_t rows, int C, const f
                                                                                   scratch);
   TDL_LAUNCH_OK("bn_partial_stats_kernel");
   const double unbias = rows > 1 ? (double)rows / (double)(rows - 1) : 1.0;
-  bn_finalize_stats_kernel<<<(C + 127) / 128, 128, 0, st>>>(scratch, s.gx, C, 1.0 / (double)rows, unbias, gamma, beta,
-                                                            running_mean, running_var, decay, eps, mean, invstd, scale,
-                                                            shift);
+  bn_finalize_stats_kernel<<<(C + 31) / 32, kFinThreads, 0, st>>>(scratch, s.gx, C, 1.0 / (double)rows, unbias, gamma,
+                                                                  beta, running_mean, running_var, decay, eps, mean,
+                                                                  invstd, scale, shift);
   TDL_LAUNCH_OK("bn_finalize_stats_kernel");
   return 0;
 }

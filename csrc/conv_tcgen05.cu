@@ -138,13 +138,14 @@ struct FpropCfg {
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kStages = (192 * 1024) / kStageBytes;
   static constexpr int kTmemCols = 2 * BLOCK_N;  // double-buffered accumulator
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int kOutBytes = 2 * kBlockM * 128;  // two 128-row x 64-channel bf16 staging tiles for TMA stores
+  static constexpr int kSmemBytes = kStages * kStageBytes + kOutBytes + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
 template <int BLOCK_N>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
-                  const Geometry g, bf16* __restrict__ y, const float* __restrict__ bias,
+                  const __grid_constant__ CUtensorMap tm_y, const Geometry g, const float* __restrict__ bias,
                   const bf16* __restrict__ residual) {
   using Cfg = FpropCfg<BLOCK_N>;
   constexpr int kStages = Cfg::kStages;
@@ -152,7 +153,8 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + kStages * kABytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes);
+  uint8_t* smem_out = smem + kStages * Cfg::kStageBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_out + Cfg::kOutBytes);
   uint64_t* full_bar = bars;
   uint64_t* empty_bar = bars + kStages;
   uint64_t* tmem_full = bars + 2 * kStages;
@@ -171,6 +173,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tm_x);
     ptx::prefetch_tmap(&tm_w);
+    ptx::prefetch_tmap(&tm_y);
   }
   if (warp == 1) {
     if (lane == 0) {
@@ -262,6 +265,8 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
     }
   } else {
     // ===================== epilogue warps =====================
+    // TMEM -> registers -> (bias / residual / ReLU) -> bf16 -> 128B-swizzled smem tile -> TMA store.
+    // The 4-D store box is the pixel patch, so TMA clips everything outside the image / channel range.
     const int quarter = warp & 3;  // TMEM lane quarter this warp may access
     const int row = quarter * 32 + lane;
     const int patch = g.TH * g.TW;
@@ -270,8 +275,10 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
     const int dh = rem / g.TW;
     const int dw = rem - dh * g.TW;
     const bool row_in_patch = row < g.TN * patch;
+    const bool issuer = (warp == kEpiWarp0 && lane == 0);
     int acc = 0;
     uint32_t acc_phase = 0;
+    uint32_t chunk_count = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const int n_tile = tile % g.n_tiles;
       const int m_tile = tile / g.n_tiles;
@@ -286,29 +293,36 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
       ptx::mbar_wait(&tmem_full[acc], acc_phase);
       ptx::tc_fence_after();
 #pragma unroll 1
-      for (int c = 0; c < BLOCK_N / 32; ++c) {
-        uint32_t v[32];
-        ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BLOCK_N + c * 32), v);
-        ptx::tmem_ld_wait();
-        const int co0 = n_tile * BLOCK_N + c * 32;
-        if (valid && co0 < g.K) {
-          bf16* dst = y + pix * g.K + co0;
-          const bf16* res = g.has_res ? residual + pix * g.K + co0 : nullptr;
+      for (int cc = 0; cc < BLOCK_N / 64; ++cc) {
+        const int co_chunk = n_tile * BLOCK_N + cc * 64;
+        if (co_chunk >= g.K) break;  // uniform across the CTA
+        uint8_t* out_tile = smem_out + (chunk_count & 1) * (kBlockM * 128);
+        ++chunk_count;
+        if (issuer) ptx::tma_store_wait_read<1>();  // the store that last read this staging tile has drained
+        ptx::named_bar_sync(1, 128);
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          uint32_t v[32];
+          ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) +
+                                 (uint32_t)(acc * BLOCK_N + cc * 64 + half * 32), v);
+          ptx::tmem_ld_wait();
+          const int co0 = co_chunk + half * 32;
 #pragma unroll
           for (int j8 = 0; j8 < 4; ++j8) {
-            if (co0 + j8 * 8 < g.K) {  // K is a multiple of 8
-              float f[8];
+            float f[8];
 #pragma unroll
-              for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(v[j8 * 8 + j]);
+            for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(v[j8 * 8 + j]);
+            const int co = co0 + j8 * 8;
+            if (co < g.K) {
               if (g.has_bias) {
-                const float4 b0 = *reinterpret_cast<const float4*>(bias + co0 + j8 * 8);
-                const float4 b1 = *reinterpret_cast<const float4*>(bias + co0 + j8 * 8 + 4);
+                const float4 b0 = *reinterpret_cast<const float4*>(bias + co);
+                const float4 b1 = *reinterpret_cast<const float4*>(bias + co + 4);
                 f[0] += b0.x; f[1] += b0.y; f[2] += b0.z; f[3] += b0.w;
                 f[4] += b1.x; f[5] += b1.y; f[6] += b1.z; f[7] += b1.w;
               }
-              if (g.has_res) {
+              if (g.has_res && valid) {
                 float rr[8];
-                unpack8(ld8(res + j8 * 8), rr);
+                unpack8(ld8(residual + pix * g.K + co), rr);
 #pragma unroll
                 for (int j = 0; j < 8; ++j) f[j] += rr[j];
               }
@@ -316,19 +330,30 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
 #pragma unroll
                 for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
               }
-              st8(dst + j8 * 8, pack8(f));
             }
+            const int chunk16 = half * 4 + j8;  // 16-byte chunk inside the 128-byte row
+            *reinterpret_cast<bf16x8*>(out_tile + row * 128 + ((chunk16 ^ (row & 7)) << 4)) = pack8(f);
           }
         }
+        if (cc == BLOCK_N / 64 - 1 || co_chunk + 64 >= g.K) {
+          // every tcgen05.ld of this accumulator has completed: hand the TMEM buffer back to the MMA warp
+          ptx::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(&tmem_empty[acc]);
+        }
+        ptx::fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the TMA (async proxy)
+        ptx::named_bar_sync(1, 128);
+        if (issuer) {
+          ptx::tma_store_4d(&tm_y, out_tile, co_chunk, tw_i * g.TW, th_i * g.TH, tn_i * g.TN);
+          ptx::tma_store_commit();
+        }
       }
-      ptx::tc_fence_before();
-      __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(&tmem_empty[acc]);
       if (++acc == 2) {
         acc = 0;
         acc_phase ^= 1;
       }
     }
+    if (issuer) ptx::tma_store_wait_all<0>();
   }
 
   ptx::tc_fence_before();
@@ -519,8 +544,8 @@ __global__ void weight_prep_kernel(const float* __restrict__ w, bf16* __restrict
 }
 
 template <int BLOCK_N>
-static int launch_fprop(const CUtensorMap& tx, const CUtensorMap& tw, const Geometry& g, bf16* y, const float* bias,
-                        const bf16* res, cudaStream_t st) {
+static int launch_fprop(const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& ty, const Geometry& g,
+                        const float* bias, const bf16* res, cudaStream_t st) {
   using Cfg = FpropCfg<BLOCK_N>;
   static bool attr_set = false;
   if (!attr_set) {
@@ -530,7 +555,7 @@ static int launch_fprop(const CUtensorMap& tx, const CUtensorMap& tw, const Geom
   }
   const int total = g.tiles_n * g.tiles_h * g.tiles_w * g.n_tiles;
   const int grid = total < tdl::num_sms() ? total : tdl::num_sms();
-  conv_fprop_kernel<BLOCK_N><<<grid, kThreads, Cfg::kSmemBytes, st>>>(tx, tw, g, y, bias, res);
+  conv_fprop_kernel<BLOCK_N><<<grid, kThreads, Cfg::kSmemBytes, st>>>(tx, tw, ty, g, bias, res);
   TDL_LAUNCH_OK("conv_fprop_kernel");
   return 0;
 }
@@ -605,10 +630,18 @@ TDL_API int tdl_conv2d_fprop_bf16(const void* x, const void* w, void* y, const f
     int rc = encode_bf16(&tw, w, 3, dims, box, es);
     if (rc) return rc;
   }
+  CUtensorMap ty;
+  {
+    uint64_t dims[4] = {(uint64_t)K, (uint64_t)g.Q, (uint64_t)g.P, (uint64_t)g.N};
+    uint32_t box[4] = {64, (uint32_t)g.TW, (uint32_t)g.TH, (uint32_t)g.TN};
+    uint32_t es[4] = {1, 1, 1, 1};
+    int rc = encode_bf16(&ty, y, 4, dims, box, es);
+    if (rc) return rc;
+  }
   cudaStream_t st = (cudaStream_t)stream;
-  if (block_n == 256) return launch_fprop<256>(tx, tw, g, (bf16*)y, bias, (const bf16*)residual, st);
-  if (block_n == 128) return launch_fprop<128>(tx, tw, g, (bf16*)y, bias, (const bf16*)residual, st);
-  return launch_fprop<64>(tx, tw, g, (bf16*)y, bias, (const bf16*)residual, st);
+  if (block_n == 256) return launch_fprop<256>(tx, tw, ty, g, bias, (const bf16*)residual, st);
+  if (block_n == 128) return launch_fprop<128>(tx, tw, ty, g, bias, (const bf16*)residual, st);
+  return launch_fprop<64>(tx, tw, ty, g, bias, (const bf16*)residual, st);
 }
 
 // dw[K,R*S,C] (fp32) += sum over pixels of dy[N,P,Q,K]^T * shifted x[N,H,W,C].  Caller zeroes dw.

@@ -1,0 +1,44 @@
+"""Worker for tests/test_towers.py: runs under torchrun with the gloo backend (CPU towers)."""
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+from tensorflowdistributedlearning_b200 import models  # noqa: E402
+from tensorflowdistributedlearning_b200.ops import functional as TF  # noqa: E402
+from tensorflowdistributedlearning_b200.parallel.optimizer import DistributedOptimizer  # noqa: E402
+from tensorflowdistributedlearning_b200.parallel.tower import TowerGroup  # noqa: E402
+
+
+def main():
+    out_dir, mode = sys.argv[1], sys.argv[2]
+    group = TowerGroup(device="cpu")
+    torch.manual_seed(100 + group.rank)  # different init per tower: the X2 broadcast must make them equal
+    model = models.SmallResNet(num_classes=10)
+    if mode == "frozen_bn":
+        model.eval()
+    else:
+        model.train()
+    opt = DistributedOptimizer(model, group, kind="adam", lr=1e-2, decay_steps=10000.0, decay_rate=0.5)
+    g = torch.Generator().manual_seed(7)
+    X = torch.randn(16, 32, 32, 3, generator=g)
+    Y = torch.randint(0, 10, (16,), generator=g)
+    per = 16 // group.world
+    xs, ys = X[group.rank * per:(group.rank + 1) * per], Y[group.rank * per:(group.rank + 1) * per]
+    hashes = []
+    for step in range(3):
+        opt.begin_step()
+        loss, _, _ = TF.softmax_cross_entropy(model(xs), ys)
+        loss.backward()
+        opt.step()
+        hashes.append(opt.flat.param_flat.clone())
+    torch.save({"params": opt.flat.param_flat.clone(), "stats": opt.flat.stats_flat.clone(), "per_step": hashes,
+                "step": int(opt.global_step.item()), "loss": float(loss)}, os.path.join(out_dir, f"{mode}_w{group.world}_r{group.rank}.pt"))
+    group.barrier()
+    group.shutdown()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,157 @@
+"""Integration (CPU): Model façade end-to-end, checkpoint layout with TF names, resume, K-fold dirs, export, TTA."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from tensorflowdistributedlearning_b200.data import folds as F
+from tensorflowdistributedlearning_b200.data import preprocessing as PP
+from tensorflowdistributedlearning_b200.estimator import checkpoint as ckpt
+from tensorflowdistributedlearning_b200.utils.misc import metric_comparison
+
+
+def _make_dataset(root, n=24, size=101, seed=0):
+    from PIL import Image
+
+    rng = np.random.RandomState(seed)
+    os.makedirs(os.path.join(root, "images"), exist_ok=True)
+    os.makedirs(os.path.join(root, "masks"), exist_ok=True)
+    ids, cov = [], []
+    yy, xx = np.mgrid[0:size, 0:size]
+    for i in range(n):
+        r = rng.uniform(5, 45) if i % 3 else 0
+        mask = (((yy - rng.uniform(20, 80)) ** 2 + (xx - rng.uniform(20, 80)) ** 2) < r * r)
+        img = np.clip(0.45 + 0.3 * mask + 0.08 * rng.randn(size, size), 0, 1)
+        Image.fromarray((img * 255).astype(np.uint8)).save(os.path.join(root, "images", f"id{i:03d}.png"))
+        Image.fromarray((mask * 255).astype(np.uint8)).save(os.path.join(root, "masks", f"id{i:03d}.png"))
+        ids.append(f"id{i:03d}")
+        cov.append(F.coverage_class(mask.astype(np.float32)))
+    return np.array(ids, dtype=object), np.array([min(c, 1) for c in cov])
+
+
+@pytest.fixture(scope="module")
+def trained(tmp_path_factory):
+    from model import Model
+
+    root = tmp_path_factory.mktemp("salt")
+    data_dir = str(root / "data")
+    X, y = _make_dataset(data_dir)
+    model_dir = str(root / "tinyseg")
+    m = Model(model_dir, data_dir, n_gpus=1, n_fold=2, device="cpu", n_blocks=(1, 1, 1), base_depth=16, workers=2,
+              save_checkpoints_steps=3, save_summary_steps=2, log_step_count_steps=2, throttle_secs=0)
+    res = m.train(X, y, batch_size=4, steps=6)
+    return m, model_dir, data_dir, X, y, res
+
+
+def test_fold_directories_and_symlinks(trained):
+    m, model_dir, data_dir, X, y, res = trained
+    for mode in ("train", "eval"):
+        for kind in ("images", "masks"):
+            for k in range(2):
+                assert os.path.isdir(os.path.join(model_dir, mode, kind, f"fold{k}"))
+    tr = F.list_fold(model_dir, "train", 0)
+    ev = F.list_fold(model_dir, "eval", 0)
+    assert len(tr) + len(ev) == len(X)
+    assert all(os.path.islink(p) and os.path.basename(p) == os.path.basename(q) for p, q in tr)
+    assert not ({os.path.basename(p) for p, _ in tr} & {os.path.basename(p) for p, _ in ev})
+
+
+def test_train_results_and_files(trained):
+    m, model_dir, *_rest, res = trained
+    assert set(res) == {0, 1}
+    for i in (0, 1):
+        r = res[i]
+        for k in ("metrics/mean_iou", "metrics/mean_acc", "loss/lovasz_loss", "loss", "global_step"):
+            assert k in r
+        assert r["global_step"] == 6
+        fold = os.path.join(model_dir, f"fold{i}")
+        assert ckpt.list_checkpoints(fold) == [0, 3, 6]
+        assert os.path.exists(os.path.join(fold, "checkpoint"))
+        assert os.path.exists(os.path.join(fold, "train", "summaries.jsonl"))
+        assert os.path.exists(os.path.join(fold, "eval", "summaries.jsonl"))
+        assert os.path.isdir(os.path.join(fold, "export", "best_exporter"))
+
+
+def test_checkpoint_has_tf_variable_names_and_layout(trained):
+    m, model_dir, *_ = trained
+    from safetensors.torch import load_file
+
+    t = load_file(os.path.join(model_dir, "fold0", "model.ckpt-6.safetensors"))
+    P = "tinyseg"
+    w = t[f"{P}/resnet_v2/conv1_1/weights"]
+    assert tuple(w.shape) == (3, 3, 2, 64)  # HWIO
+    assert f"{P}/resnet_v2/conv1_1/weights/Adam" in t and f"{P}/resnet_v2/conv1_1/weights/Adam_1" in t
+    assert tuple(t[f"{P}/assp/conv/conv_3x3_1_depthwise/depthwise_weights"].shape) == (3, 3, 1024, 1)
+    assert int(t["global_step"]) == 6
+    assert abs(float(t["beta1_power"]) - 0.9 ** 6) < 1e-6
+    assert f"{P}/resnet_v2/postnorm/moving_variance" in t
+
+
+def test_resume_equals_uninterrupted(tmp_path):
+    """train 4 steps == train 2, 'kill', resume 2 (same data order, CPU determinism)."""
+    from tensorflowdistributedlearning_b200 import models
+    from tensorflowdistributedlearning_b200.data.dataset import BatchLoader, SyntheticSegmentation
+    from tensorflowdistributedlearning_b200.estimator.config import OptimConfig, RunConfig
+    from tensorflowdistributedlearning_b200.estimator.estimator import Estimator
+    from tensorflowdistributedlearning_b200.parallel.tower import TowerGroup
+
+    group = TowerGroup(device="cpu")
+    ds = SyntheticSegmentation(16, input_shape=(33, 33))
+    batches = list(zip(range(4), iter(BatchLoader(ds, 4, shuffle=False, pin=False))))
+    batches = [b for _, b in batches]
+
+    def builder():
+        return models.ResNetSegModel(model_name="m", n_blocks=(1, 1, 1), base_depth=8, input_shape=(33, 33))
+
+    def run(model_dir, chunks):
+        for lo, hi in chunks:
+            est = Estimator(builder, model_dir, RunConfig(model_dir=model_dir, save_checkpoints_steps=100,
+                                                         save_summary_steps=0, log_step_count_steps=0),
+                            OptimConfig(lr=1e-3), group=group)
+            est.train(lambda: iter(batches[lo:hi]), max_steps=hi)
+        return est
+
+    a = run(str(tmp_path / "a"), [(0, 4)])
+    b = run(str(tmp_path / "b"), [(0, 2), (2, 4)])
+    assert a.global_step == b.global_step == 4
+    pa = torch.cat([p.detach().flatten() for p in a.model.parameters()])
+    pb = torch.cat([p.detach().flatten() for p in b.model.parameters()])
+    assert torch.allclose(pa, pb, atol=1e-6), float((pa - pb).abs().max())
+    sa = torch.cat([x.flatten() for x in a.model.buffers()])
+    sb = torch.cat([x.flatten() for x in b.model.buffers()])
+    assert torch.allclose(sa, sb, atol=1e-6)
+
+
+def test_predict_tta_average(trained):
+    m, model_dir, data_dir, X, *_ = trained
+    out = m.predict(os.path.join(data_dir, "images"), batch_size=8, tti=True)
+    assert out["probabilities"].shape == (len(X), 101, 101, 1)
+    assert len(out["ids"]) == len(X)
+    assert set(np.unique(out["mask"])) <= {0.0, 1.0}
+    assert 0.0 <= out["probabilities"].min() and out["probabilities"].max() <= 1.0
+
+
+def test_tta_transformations_are_involutions():
+    x = torch.randn(2, 5, 5, 3)
+    for t in PP.TRANSFORMATIONS:
+        y = PP.single_transformation_from_matrix(x, t)
+        assert torch.equal(PP.undo_transformation(y, t), x)
+    with pytest.raises(ValueError):
+        PP.single_transformation_from_matrix(x, "rot90")
+
+
+def test_metric_comparison_fixed_and_compat():
+    best, cur = {"metrics/mean_iou": 0.5}, {"metrics/mean_iou": 0.6}
+    assert metric_comparison(best, cur, "metrics/mean_iou", True) is True
+    assert metric_comparison(best, cur, "metrics/mean_iou", True, reference_compat=True) is False  # defect 4
+    with pytest.raises(ValueError):
+        metric_comparison({}, cur, "metrics/mean_iou")
+
+
+def test_model_validation_and_params():
+    from model import Model
+
+    with pytest.raises(ValueError):
+        Model("/tmp/x", "/tmp/y", data_format="NDHWC", device="cpu")

@@ -1,0 +1,54 @@
+"""Tower plumbing without GPUs (BASELINE config 1): 2 CPU towers over gloo, SmallResNet, 32x32x3, batch 16, 10 classes."""
+import os
+import socket
+import subprocess
+import sys
+
+import pytest
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _run(tmp, mode, world):
+    env = dict(os.environ, OMP_NUM_THREADS="2")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+           "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), os.path.join(HERE, "_tower_worker.py"),
+           str(tmp), mode]
+    r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    return [torch.load(os.path.join(tmp, f"{mode}_w{world}_r{k}.pt")) for k in range(world)]
+
+
+@pytest.fixture(scope="module")
+def runs(tmp_path_factory):
+    tmp = tmp_path_factory.mktemp("towers")
+    return {("frozen_bn", 2): _run(tmp, "frozen_bn", 2), ("frozen_bn", 1): _run(tmp, "frozen_bn", 1),
+            ("train_bn", 2): _run(tmp, "train_bn", 2)}
+
+
+def test_mirrors_bit_identical_after_every_step(runs):
+    for key in (("frozen_bn", 2), ("train_bn", 2)):
+        a, b = runs[key]
+        assert a["step"] == b["step"] == 3
+        for pa, pb in zip(a["per_step"], b["per_step"]):
+            assert torch.equal(pa, pb)
+
+
+def test_two_towers_equal_one_tower_on_the_same_global_batch(runs):
+    """Mean of per-tower mean-loss gradients == gradient of the global mean loss (BN frozen)."""
+    two, one = runs[("frozen_bn", 2)][0], runs[("frozen_bn", 1)][0]
+    assert torch.allclose(two["params"], one["params"], atol=2e-5), float((two["params"] - one["params"]).abs().max())
+
+
+def test_moving_statistics_are_the_tower_mean(runs):
+    a, b = runs[("train_bn", 2)]
+    assert torch.equal(a["stats"], b["stats"])          # synced (X3) ...
+    frozen = runs[("frozen_bn", 2)][0]["stats"]
+    assert not torch.equal(a["stats"], frozen)           # ... and actually updated by training-mode BN
