@@ -98,6 +98,66 @@ def reference_arm(args):
     return 0
 
 
+def proxy_arm(args):
+    """Labelled proxy baseline (NOT the reference, NOT this framework): stock PyTorch -- torchvision ResNet-50,
+    cuDNN/cuBLAS kernels, channels-last, bf16 autocast, fused SGD, DDP over NCCL -- same batch and input shape,
+    same timing rules.  'A path that only calls NCCL is the baseline, not the product.'"""
+    import torch
+    import torch.distributed as dist
+    import torchvision
+
+    from tensorflowdistributedlearning_b200.parallel.tower import TowerGroup
+
+    group = TowerGroup()
+    cfg = CONFIGS["resnet50"]
+    batch = args.batch or cfg["batch"]
+    warmup = max(args.warmup, 3)
+    torch.manual_seed(1234)
+    model = torchvision.models.resnet50(num_classes=1000).cuda().to(memory_format=torch.channels_last)
+    if group.distributed:
+        model = torch.nn.parallel.DistributedDataParallel(model, device_ids=[torch.cuda.current_device()],
+                                                          gradient_as_bucket_view=True)
+    opt = torch.optim.SGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4, fused=True)
+    x = torch.randn(batch, 3, 224, 224, device="cuda").to(memory_format=torch.channels_last)
+    y = torch.randint(0, 1000, (batch,), device="cuda")
+
+    def step():
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            loss = torch.nn.functional.cross_entropy(model(x), y)
+        loss.backward()
+        opt.step()
+        opt.zero_grad(set_to_none=True)
+        return loss
+
+    for _ in range(warmup):
+        step()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(torch.cuda.current_device())
+    sampler.start()
+    group.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        loss = step()
+    e1.record()
+    torch.cuda.synchronize()
+    group.barrier()
+    ms = group.max_over_ranks(e0.elapsed_time(e1)) / args.steps
+    clocks = sampler.stop()
+    gb = batch * group.world
+    if group.is_primary:
+        print(json.dumps({"metric": "training images/sec (ResNet-50, max over ranks)", "value": round(gb / ms * 1e3, 2),
+                          "unit": "images/s", "n_gpus": group.world, "steps": args.steps, "warmup": warmup,
+                          "ms_per_step": round(ms, 4), "higher_is_better": True, "scaling": "weak",
+                          "vs_baseline": None, "dtype": "bf16 autocast", "data": "synthetic (device-resident)",
+                          "impl": "proxy: torchvision resnet50 + cuDNN + DDP/NCCL (not the reference)",
+                          "config": {"model": "resnet50", "global_batch": gb, "parallelism": f"dp{group.world}"},
+                          "gpu_launches": 0, "clocks": clocks, "loss": round(float(loss), 4)}))
+    group.shutdown()
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -112,6 +172,8 @@ def main():
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm(args)
+    if args.impl == "proxy":
+        return proxy_arm(args)
 
     import torch
 
@@ -132,9 +194,7 @@ def main():
         if group.is_primary:
             print(f"warning: --gpus {args.gpus} but WORLD_SIZE={group.world}; using WORLD_SIZE", file=sys.stderr)
     n_gpus = group.world
-    proxy = args.impl == "proxy"
-    if proxy:
-        TF.force_reference(True)  # stock torch ops (cuDNN/cuBLAS) + NCCL all-reduce: the labelled proxy baseline
+    proxy = False
     torch.manual_seed(1234)
     h, w, c = cfg["hwc"]
     if cfg["task"] == "cls":

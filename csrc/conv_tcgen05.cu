@@ -48,7 +48,7 @@ static EncodeTiledFn get_encode_fn() {
 
 // dims/box/estr are innermost-first; strides are derived for a dense tensor.
 static int encode_bf16(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint32_t* box,
-                       const uint32_t* estr) {
+                       const uint32_t* estr, const uint64_t* strides_bytes = nullptr) {
   EncodeTiledFn fn = get_encode_fn();
   if (!fn) return tdl::fail(-3, "%s%s", "cuTensorMapEncodeTiled entry point unavailable", "");
   cuuint64_t gdim[5], gstr[5];
@@ -59,7 +59,7 @@ static int encode_bf16(CUtensorMap* m, const void* base, int rank, const uint64_
     b[i] = box[i];
     e[i] = estr[i];
     pitch *= dims[i];
-    if (i + 1 < rank) gstr[i] = pitch;  // stride of dimension i+1, bytes
+    if (i + 1 < rank) gstr[i] = strides_bytes ? strides_bytes[i] : pitch;  // stride of dimension i+1, bytes
   }
   CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gdim, gstr, b, e,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -136,9 +136,12 @@ template <int BLOCK_N>
 struct FpropCfg {
   static constexpr int kBBytes = BLOCK_N * kBlockK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStages = (192 * 1024) / kStageBytes;
   static constexpr int kTmemCols = 2 * BLOCK_N;  // double-buffered accumulator
-  static constexpr int kOutBytes = 2 * kBlockM * 128;  // two 128-row x 64-channel bf16 staging tiles for TMA stores
+  // four 128-row x 64-channel bf16 staging tiles: a TMA store takes ~1 us to release its source, so the epilogue
+  // needs several stores in flight to keep draining TMEM
+  static constexpr int kOutBufs = 4;
+  static constexpr int kOutBytes = kOutBufs * kBlockM * 128;
+  static constexpr int kStages = (227 * 1024 - kOutBytes - 1024 - 256) / kStageBytes;
   static constexpr int kSmemBytes = kStages * kStageBytes + kOutBytes + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
@@ -296,9 +299,9 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
       for (int cc = 0; cc < BLOCK_N / 64; ++cc) {
         const int co_chunk = n_tile * BLOCK_N + cc * 64;
         if (co_chunk >= g.K) break;  // uniform across the CTA
-        uint8_t* out_tile = smem_out + (chunk_count & 1) * (kBlockM * 128);
+        uint8_t* out_tile = smem_out + (chunk_count % Cfg::kOutBufs) * (kBlockM * 128);
         ++chunk_count;
-        if (issuer) ptx::tma_store_wait_read<1>();  // the store that last read this staging tile has drained
+        if (issuer) ptx::tma_store_wait_read<Cfg::kOutBufs - 1>();  // the store that last read this tile has drained
         ptx::named_bar_sync(1, 128);
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
@@ -369,30 +372,35 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
 // GEMM M = Cout (128), N = Cin (BLOCK_N), K = pixels (64 per stage).  Both operands are stored
 // with the GEMM-K (pixel) index as the *row* of a 128B-swizzled tile, i.e. MN-major.
 // ------------------------------------------------------------------------------------------
-constexpr int kWgradStages = 5;
-
-template <int BLOCK_N>
+// A CTA owns MT x 128 output channels x BLOCK_N input channels of one tap, i.e. up to a 256x256 tile held in all
+// 512 TMEM columns: the dY patch is fetched once for BLOCK_N input channels and the X patch once for MT*128 output
+// channels, which halves the L2->SMEM bytes per FLOP compared with a 128x128 tile.
+template <int MT, int BLOCK_N>
 struct WgradCfg {
-  static constexpr int kABytes = 128 * 64 * 2;        // 2 blocks of [64 px][64 co]
+  static constexpr int kABytes = MT * 128 * 64 * 2;   // MT * 2 blocks of [64 px][64 co]
   static constexpr int kBBytes = BLOCK_N * 64 * 2;    // BLOCK_N/64 blocks of [64 px][64 ci]
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kTmemCols = BLOCK_N < 32 ? 32 : BLOCK_N;
-  static constexpr int kSmemBytes = kWgradStages * kStageBytes + 1024 + 256;
+  static constexpr int kStages = (192 * 1024) / kStageBytes;
+  static constexpr int kTmemColsRaw = MT * BLOCK_N;
+  static constexpr int kTmemCols = kTmemColsRaw <= 32 ? 32 : kTmemColsRaw <= 64 ? 64 : kTmemColsRaw <= 128 ? 128
+                                   : kTmemColsRaw <= 256 ? 256 : 512;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256;
 };
 
-template <int BLOCK_N>
+template <int MT, int BLOCK_N>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_wgrad_kernel(const __grid_constant__ CUtensorMap tm_dy, const __grid_constant__ CUtensorMap tm_x,
                   const Geometry g, float* __restrict__ dw, int m_tiles_co, int n_tiles_ci) {
-  using Cfg = WgradCfg<BLOCK_N>;
+  using Cfg = WgradCfg<MT, BLOCK_N>;
+  constexpr int kStages = Cfg::kStages;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smem_a = smem;
-  uint8_t* smem_b = smem + kWgradStages * Cfg::kABytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kWgradStages * Cfg::kStageBytes);
+  uint8_t* smem_b = smem + kStages * Cfg::kABytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes);
   uint64_t* full_bar = bars;
-  uint64_t* empty_bar = bars + kWgradStages;
-  uint64_t* tmem_full = bars + 2 * kWgradStages;
+  uint64_t* empty_bar = bars + kStages;
+  uint64_t* tmem_full = bars + 2 * kStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
 
   const int warp = threadIdx.x >> 5;
@@ -412,10 +420,10 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tm_dy, const __grid_consta
   if (my_iters <= 0) return;  // uniform across the CTA
 
   // Pixel rows a TMA box does not cover must read as zero in BOTH operands for every stage.
-  {
+  if (g.TN * g.TH * g.TW < 64) {
     uint4 z = make_uint4(0, 0, 0, 0);
     uint4* p4 = reinterpret_cast<uint4*>(smem);
-    const int n16 = kWgradStages * Cfg::kStageBytes / 16;
+    const int n16 = kStages * Cfg::kStageBytes / 16;
     for (int i = threadIdx.x; i < n16; i += kThreads) p4[i] = z;
     ptx::fence_proxy_async_smem();
   }
@@ -426,7 +434,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tm_dy, const __grid_consta
   }
   if (warp == 1) {
     if (lane == 0) {
-      for (int i = 0; i < kWgradStages; ++i) {
+      for (int i = 0; i < kStages; ++i) {
         ptx::mbar_init(&full_bar[i], 1);
         ptx::mbar_init(&empty_bar[i], 1);
       }
@@ -441,8 +449,8 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tm_dy, const __grid_consta
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  const uint32_t px_bytes = (uint32_t)(g.TN * g.TH * g.TW) * 128u;                 // one 64-channel box
-  const uint32_t stage_tx = px_bytes * (uint32_t)(2 + BLOCK_N / 64);
+  const uint32_t px_bytes = (uint32_t)(g.TN * g.TH * g.TW) * 128u;  // one 64-channel box
+  const uint32_t stage_tx = px_bytes * (uint32_t)(2 * MT + BLOCK_N / 64);
 
   if (warp == 0) {
     if (lane == 0) {
@@ -458,15 +466,15 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tm_dy, const __grid_consta
         uint8_t* a = smem_a + stage * Cfg::kABytes;
         uint8_t* b = smem_b + stage * Cfg::kBBytes;
 #pragma unroll
-        for (int h = 0; h < 2; ++h)
-          ptx::tma_load_4d(a + h * 8192, &tm_dy, &full_bar[stage], co_tile * 128 + h * 64, tw_i * g.TW, th_i * g.TH,
-                           tn_i * g.TN);
+        for (int h = 0; h < 2 * MT; ++h)
+          ptx::tma_load_4d(a + h * 8192, &tm_dy, &full_bar[stage], co_tile * (128 * MT) + h * 64, tw_i * g.TW,
+                           th_i * g.TH, tn_i * g.TN);
 #pragma unroll
         for (int h = 0; h < BLOCK_N / 64; ++h)
           ptx::tma_load_4d(b + h * 8192, &tm_x, &full_bar[stage], ci_tile * BLOCK_N + h * 64,
                            tw_i * g.TW * g.stride + s * g.dil - g.pad_w,
                            th_i * g.TH * g.stride + r * g.dil - g.pad_h, tn_i * g.TN);
-        if (++stage == kWgradStages) {
+        if (++stage == kStages) {
           stage = 0;
           phase ^= 1;
         }
@@ -481,16 +489,20 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tm_dy, const __grid_consta
         ptx::mbar_wait(&full_bar[stage], phase);
         ptx::tc_fence_after();
         // MN-major SW128: 64-element MN blocks 8192 B apart (LBO), 8-pixel-row groups 1024 B apart (SBO)
-        const uint64_t a_desc = ptx::umma_smem_desc_sw128(ptx::smem_u32(smem_a + stage * Cfg::kABytes), 8192, 1024);
         const uint64_t b_desc = ptx::umma_smem_desc_sw128(ptx::smem_u32(smem_b + stage * Cfg::kBBytes), 8192, 1024);
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          // 16 pixel rows = 2048 bytes = +128 in 16-byte units
-          ptx::umma_bf16(tmem_base, a_desc + (uint64_t)(128 * k), b_desc + (uint64_t)(128 * k), idesc,
-                         (i > 0 || k > 0) ? 1u : 0u);
+        for (int mt = 0; mt < MT; ++mt) {
+          const uint64_t a_desc =
+              ptx::umma_smem_desc_sw128(ptx::smem_u32(smem_a + stage * Cfg::kABytes + mt * 16384), 8192, 1024);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            // 16 pixel rows = 2048 bytes = +128 in 16-byte units
+            ptx::umma_bf16(tmem_base + (uint32_t)(mt * BLOCK_N), a_desc + (uint64_t)(128 * k),
+                           b_desc + (uint64_t)(128 * k), idesc, (i > 0 || k > 0) ? 1u : 0u);
+          }
         }
         ptx::umma_commit(&empty_bar[stage]);
-        if (++stage == kWgradStages) {
+        if (++stage == kStages) {
           stage = 0;
           phase ^= 1;
         }
@@ -499,21 +511,28 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tm_dy, const __grid_consta
     }
   } else {
     const int quarter = warp & 3;
-    const int co = co_tile * 128 + quarter * 32 + lane;
     ptx::mbar_wait(tmem_full, 0);
     ptx::tc_fence_after();
     const int taps = g.R * g.S;
 #pragma unroll 1
-    for (int c = 0; c < BLOCK_N / 32; ++c) {
-      uint32_t v[32];
-      ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(c * 32), v);
-      ptx::tmem_ld_wait();
-      const int ci0 = ci_tile * BLOCK_N + c * 32;
-      if (co < g.K) {
-        float* dst = dw + ((size_t)co * taps + tap) * g.C + ci0;
+    for (int mt = 0; mt < MT; ++mt) {
+      const int co = co_tile * (128 * MT) + mt * 128 + quarter * 32 + lane;
+#pragma unroll 1
+      for (int c = 0; c < BLOCK_N / 32; ++c) {
+        uint32_t v[32];
+        ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(mt * BLOCK_N + c * 32), v);
+        ptx::tmem_ld_wait();
+        const int ci0 = ci_tile * BLOCK_N + c * 32;
+        if (co < g.K) {
+          float* dst = dw + ((size_t)co * taps + tap) * g.C + ci0;
 #pragma unroll
-        for (int j = 0; j < 32; ++j)
-          if (ci0 + j < g.C) atomicAdd(dst + j, __uint_as_float(v[j]));
+          for (int j = 0; j < 32; j += 4)
+            if (ci0 + j < g.C)  // C is a multiple of 8, so a 4-wide group is all-in or all-out
+              asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + j), "f"(__uint_as_float(v[j])),
+                           "f"(__uint_as_float(v[j + 1])), "f"(__uint_as_float(v[j + 2])),
+                           "f"(__uint_as_float(v[j + 3]))
+                           : "memory");
+        }
       }
     }
   }
@@ -560,24 +579,30 @@ static int launch_fprop(const CUtensorMap& tx, const CUtensorMap& tw, const CUte
   return 0;
 }
 
-template <int BLOCK_N>
+template <int MT, int BLOCK_N>
 static int launch_wgrad(const CUtensorMap& tdy, const CUtensorMap& tx, const Geometry& g, float* dw, cudaStream_t st) {
-  using Cfg = WgradCfg<BLOCK_N>;
+  using Cfg = WgradCfg<MT, BLOCK_N>;
   static bool attr_set = false;
   if (!attr_set) {
-    TDL_CUDA_OK(cudaFuncSetAttribute(conv_wgrad_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    TDL_CUDA_OK(cudaFuncSetAttribute(conv_wgrad_kernel<MT, BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      Cfg::kSmemBytes));
     attr_set = true;
   }
-  const int m_tiles = (int)tdl::cdiv(g.K, 128);
+  const int m_tiles = (int)tdl::cdiv(g.K, 128 * MT);
   const int n_tiles = (int)tdl::cdiv(g.C, BLOCK_N);
   const int items = m_tiles * n_tiles * g.R * g.S;
   const int patches = g.tiles_n * g.tiles_h * g.tiles_w;
-  int splits = (int)tdl::cdiv(2 * tdl::num_sms(), items);
+  // split the pixel patches so the grid is a whole number of waves (1 CTA per SM) with >= 8 patches per CTA
+  const int sms = tdl::num_sms();
+  // Every CTA ends with a full-tile fp32 reduction into dW, so few long CTAs beat many short ones: aim for one
+  // wave, take a second only while each CTA still keeps >= 32 pixel patches.
+  int splits = sms / items;
+  if (splits < 1) splits = 1;
+  if ((2 * sms) / items > splits && patches / ((2 * sms) / items) >= 32) splits = (2 * sms) / items;
   if (splits > patches) splits = patches;
   if (splits < 1) splits = 1;
   dim3 grid(splits, items);
-  conv_wgrad_kernel<BLOCK_N><<<grid, kThreads, Cfg::kSmemBytes, st>>>(tdy, tx, g, dw, m_tiles, n_tiles);
+  conv_wgrad_kernel<MT, BLOCK_N><<<grid, kThreads, Cfg::kSmemBytes, st>>>(tdy, tx, g, dw, m_tiles, n_tiles);
   TDL_LAUNCH_OK("conv_wgrad_kernel");
   return 0;
 }
@@ -588,18 +613,24 @@ static int launch_wgrad(const CUtensorMap& tdy, const CUtensorMap& tx, const Geo
 using namespace tdl;
 using namespace tdl::conv;
 
-// y[N,P,Q,K] = conv(x[N,H,W,C], w[K,R*S,C]) (+bias) (+residual) (ReLU)      bf16 in/out, fp32 accumulate
-TDL_API int tdl_conv2d_fprop_bf16(const void* x, const void* w, void* y, const float* bias, const void* residual,
-                                  int N, int H, int W, int C, int K, int R, int S, int stride, int dil, int pad_h,
-                                  int pad_w, int P, int Q, int relu, void* stream) {
+// Where the output pixel (n, p, q) lives: element ((n*full_h + p*step + off_h)*full_w + q*step + off_w)*K of `y`.
+// The plain convolution uses {P, Q, 1, 0, 0}; the strided data gradient writes one input-parity class at a time.
+struct OutView {
+  int full_h, full_w, step, off_h, off_w;
+};
+
+static int fprop_impl(const void* x, const void* w, void* y, const float* bias, const void* residual, int N, int H,
+                      int W, int C, int K, int R, int S, int stride, int dil, int pad_h, int pad_w, int P, int Q,
+                      int relu, const OutView* view, void* stream) {
   TDL_REQUIRE(C % 8 == 0 && K % 8 == 0, "channel counts must be multiples of 8 (16-byte TMA strides)");
   TDL_REQUIRE(stride >= 1 && stride <= 8 && dil >= 1, "bad stride/dilation");
   TDL_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(w) & 15) == 0 &&
                   (reinterpret_cast<uintptr_t>(y) & 15) == 0,
               "tensors must be 16-byte aligned");
+  TDL_REQUIRE(!(view && residual), "residual fusion is not available with a strided output view");
   Geometry g;
   memset(&g, 0, sizeof(g));
-  const bool flat = (R == 1 && S == 1 && stride == 1 && pad_h == 0 && pad_w == 0);
+  const bool flat = !view && (R == 1 && S == 1 && stride == 1 && pad_h == 0 && pad_w == 0);
   if (flat) {  // pure GEMM: all pixels form one long row of width N*H*W
     g.N = 1; g.H = 1; g.W = N * H * W; g.P = 1; g.Q = N * P * Q;
   } else {
@@ -635,13 +666,41 @@ TDL_API int tdl_conv2d_fprop_bf16(const void* x, const void* w, void* y, const f
     uint64_t dims[4] = {(uint64_t)K, (uint64_t)g.Q, (uint64_t)g.P, (uint64_t)g.N};
     uint32_t box[4] = {64, (uint32_t)g.TW, (uint32_t)g.TH, (uint32_t)g.TN};
     uint32_t es[4] = {1, 1, 1, 1};
-    int rc = encode_bf16(&ty, y, 4, dims, box, es);
+    int rc;
+    if (view) {
+      const uint64_t kb = (uint64_t)K * 2;
+      uint64_t strides[3] = {kb * view->step, kb * view->full_w * view->step, kb * view->full_w * view->full_h};
+      const char* base = (const char*)y + ((size_t)view->off_h * view->full_w + view->off_w) * kb;
+      rc = encode_bf16(&ty, base, 4, dims, box, es, strides);
+    } else {
+      rc = encode_bf16(&ty, y, 4, dims, box, es);
+    }
     if (rc) return rc;
   }
   cudaStream_t st = (cudaStream_t)stream;
   if (block_n == 256) return launch_fprop<256>(tx, tw, ty, g, bias, (const bf16*)residual, st);
   if (block_n == 128) return launch_fprop<128>(tx, tw, ty, g, bias, (const bf16*)residual, st);
   return launch_fprop<64>(tx, tw, ty, g, bias, (const bf16*)residual, st);
+}
+
+// y[N,P,Q,K] = conv(x[N,H,W,C], w[K,R*S,C]) (+bias) (+residual) (ReLU)      bf16 in/out, fp32 accumulate
+TDL_API int tdl_conv2d_fprop_bf16(const void* x, const void* w, void* y, const float* bias, const void* residual,
+                                  int N, int H, int W, int C, int K, int R, int S, int stride, int dil, int pad_h,
+                                  int pad_w, int P, int Q, int relu, void* stream) {
+  return fprop_impl(x, w, y, bias, residual, N, H, W, C, K, R, S, stride, dil, pad_h, pad_w, P, Q, relu, nullptr,
+                    stream);
+}
+
+// Stride-1 convolution whose output pixel (p, q) is stored at (p*y_step + y_off_h, q*y_step + y_off_w) of a
+// [N, y_full_h, y_full_w, K] tensor.  One call computes one input-parity class of a strided convolution's data
+// gradient (x = dy, w = the taps of that class, flipped and transposed; see ops/functional.py).
+TDL_API int tdl_conv2d_fprop_strided_out_bf16(const void* x, const void* w, void* y, int N, int H, int W, int C, int K,
+                                              int R, int S, int dil, int pad_h, int pad_w, int P, int Q, int y_full_h,
+                                              int y_full_w, int y_step, int y_off_h, int y_off_w, void* stream) {
+  OutView v = {y_full_h, y_full_w, y_step, y_off_h, y_off_w};
+  TDL_REQUIRE(y_step >= 1 && y_off_h >= 0 && y_off_w >= 0, "bad output view");
+  TDL_REQUIRE((P - 1) * y_step + y_off_h < y_full_h && (Q - 1) * y_step + y_off_w < y_full_w, "view exceeds tensor");
+  return fprop_impl(x, w, y, nullptr, nullptr, N, H, W, C, K, R, S, 1, dil, pad_h, pad_w, P, Q, 0, &v, stream);
 }
 
 // dw[K,R*S,C] (fp32) += sum over pixels of dy[N,P,Q,K]^T * shifted x[N,H,W,C].  Caller zeroes dw.
@@ -661,7 +720,8 @@ TDL_API int tdl_conv2d_wgrad_bf16(const void* x, const void* dy, float* dw, int 
   g.tiles_n = (int)cdiv(g.N, g.TN);
   g.tiles_h = (int)cdiv(g.P, g.TH);
   g.tiles_w = (int)cdiv(g.Q, g.TW);
-  const int block_n = C > 64 ? 128 : 64;
+  const int block_n = C >= 256 ? 256 : (C > 64 ? 128 : 64);
+  const int mt = K >= 256 ? 2 : 1;
   CUtensorMap tdy, tx;
   {
     uint64_t dims[4] = {(uint64_t)K, (uint64_t)g.Q, (uint64_t)g.P, (uint64_t)g.N};
@@ -678,8 +738,14 @@ TDL_API int tdl_conv2d_wgrad_bf16(const void* x, const void* dy, float* dw, int 
     if (rc) return rc;
   }
   cudaStream_t st = (cudaStream_t)stream;
-  if (block_n == 128) return launch_wgrad<128>(tdy, tx, g, dw, st);
-  return launch_wgrad<64>(tdy, tx, g, dw, st);
+  if (mt == 2) {
+    if (block_n == 256) return launch_wgrad<2, 256>(tdy, tx, g, dw, st);
+    if (block_n == 128) return launch_wgrad<2, 128>(tdy, tx, g, dw, st);
+    return launch_wgrad<2, 64>(tdy, tx, g, dw, st);
+  }
+  if (block_n == 256) return launch_wgrad<1, 256>(tdy, tx, g, dw, st);
+  if (block_n == 128) return launch_wgrad<1, 128>(tdy, tx, g, dw, st);
+  return launch_wgrad<1, 64>(tdy, tx, g, dw, st);
 }
 
 // fp32 master weights -> bf16 compute copies (fprop layout and flipped/transposed dgrad layout)

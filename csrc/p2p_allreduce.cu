@@ -87,6 +87,27 @@ __device__ __forceinline__ float4 ld_grad4(const Comm& cm, int r, int64_t i, int
   }
   return *reinterpret_cast<const float4*>(cm.grad[r] + i);
 }
+// Sum of `U` 4-element vectors (element offsets i[u]) over all ranks in rank order.  All U*world peer loads are
+// issued before the first add so that several NVLink round trips are in flight per thread.
+template <int U>
+__device__ __forceinline__ void gather_sum(const Comm& cm, const int64_t* i, int nvalid, int is_bf16, float4* acc) {
+#pragma unroll
+  for (int u = 0; u < U; ++u) acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+  for (int r = 0; r < kMaxWorld; ++r) {
+    if (r < cm.world) {
+      float4 g[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        g[u] = u < nvalid ? ld_grad4(cm, r, i[u], is_bf16) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        acc[u].x += g[u].x; acc[u].y += g[u].y; acc[u].z += g[u].z; acc[u].w += g[u].w;
+      }
+    }
+  }
+}
+
 __device__ __forceinline__ float ld_grad1(const Comm& cm, int r, int64_t i, int is_bf16) {
   return is_bf16 ? __bfloat162float(reinterpret_cast<const bf16*>(cm.grad[r])[i]) : cm.grad[r][i];
 }
@@ -138,24 +159,33 @@ one_shot_kernel(const Comm cm, const StepArgs a) {
   // kNone writes the mean into the gradient buffer itself, which peers are still reading: stage in registers
   // across the barrier is impossible for a grid-stride loop, so kNone results go to a.m1 (scratch) first.
   float* mean_out = a.kind == kNone ? a.m1 : nullptr;
-  for (int64_t v = tid; v < n4; v += nthr) {
-    const int64_t i = lo + v * 4;
-    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 1
-    for (int r = 0; r < cm.world; ++r) {
-      const float4 g = ld_grad4(cm, r, i, a.grad_is_bf16);
-      s.x += g.x; s.y += g.y; s.z += g.z; s.w += g.w;
+  constexpr int U = 4;
+  for (int64_t v0 = tid; v0 < n4; v0 += nthr * U) {
+    int64_t idx[U];
+    int nvalid = 0;
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      idx[u] = lo + (v0 + (int64_t)u * nthr) * 4;
+      if (v0 + (int64_t)u * nthr < n4) nvalid = u + 1;
     }
-    s.x *= scale; s.y *= scale; s.z *= scale; s.w *= scale;
-    if (a.kind == kNone) {
-      *reinterpret_cast<float4*>(mean_out + i) = s;
-    } else {
-      float4 w = *reinterpret_cast<const float4*>(out + i);
-      w.x = opt_update(a, w.x, s.x, i, lr, lr_t);
-      w.y = opt_update(a, w.y, s.y, i + 1, lr, lr_t);
-      w.z = opt_update(a, w.z, s.z, i + 2, lr, lr_t);
-      w.w = opt_update(a, w.w, s.w, i + 3, lr, lr_t);
-      *reinterpret_cast<float4*>(out + i) = w;
+    float4 acc[U];
+    gather_sum<U>(cm, idx, nvalid, a.grad_is_bf16, acc);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (u >= nvalid) break;
+      const int64_t i = idx[u];
+      float4 s = acc[u];
+      s.x *= scale; s.y *= scale; s.z *= scale; s.w *= scale;
+      if (a.kind == kNone) {
+        *reinterpret_cast<float4*>(mean_out + i) = s;
+      } else {
+        float4 w = *reinterpret_cast<const float4*>(out + i);
+        w.x = opt_update(a, w.x, s.x, i, lr, lr_t);
+        w.y = opt_update(a, w.y, s.y, i + 1, lr, lr_t);
+        w.z = opt_update(a, w.z, s.z, i + 2, lr, lr_t);
+        w.w = opt_update(a, w.w, s.w, i + 3, lr, lr_t);
+        *reinterpret_cast<float4*>(out + i) = w;
+      }
     }
   }
   for (int64_t i = lo + n4 * 4 + tid; i < hi; i += nthr) {
@@ -192,21 +222,37 @@ two_shot_kernel(const Comm cm, const StepArgs a) {
   const int64_t v_hi = v_lo + per < n4 ? v_lo + per : n4;
   const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int64_t nthr = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t v = v_lo + tid; v < v_hi; v += nthr) {
-    const int64_t i = a.offset + v * 4;
-    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 1
-    for (int r = 0; r < cm.world; ++r) {
-      const float4 g = ld_grad4(cm, r, i, a.grad_is_bf16);
-      s.x += g.x; s.y += g.y; s.z += g.z; s.w += g.w;
+  constexpr int U = 4;
+  for (int64_t v0 = v_lo + tid; v0 < v_hi; v0 += nthr * U) {
+    int64_t idx[U];
+    int nvalid = 0;
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      idx[u] = a.offset + (v0 + (int64_t)u * nthr) * 4;
+      if (v0 + (int64_t)u * nthr < v_hi) nvalid = u + 1;
     }
-    float4 w = *reinterpret_cast<const float4*>(cm.param[cm.rank] + i);
-    w.x = opt_update(a, w.x, s.x * scale, i, lr, lr_t);
-    w.y = opt_update(a, w.y, s.y * scale, i + 1, lr, lr_t);
-    w.z = opt_update(a, w.z, s.z * scale, i + 2, lr, lr_t);
-    w.w = opt_update(a, w.w, s.w * scale, i + 3, lr, lr_t);
-#pragma unroll 1
-    for (int r = 0; r < cm.world; ++r) *reinterpret_cast<float4*>(cm.param[r] + i) = w;
+    float4 acc[U];
+    gather_sum<U>(cm, idx, nvalid, a.grad_is_bf16, acc);
+    float4 wv[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (u >= nvalid) break;
+      const int64_t i = idx[u];
+      float4 w = *reinterpret_cast<const float4*>(cm.param[cm.rank] + i);
+      w.x = opt_update(a, w.x, acc[u].x * scale, i, lr, lr_t);
+      w.y = opt_update(a, w.y, acc[u].y * scale, i + 1, lr, lr_t);
+      w.z = opt_update(a, w.z, acc[u].z * scale, i + 2, lr, lr_t);
+      w.w = opt_update(a, w.w, acc[u].w * scale, i + 3, lr, lr_t);
+      wv[u] = w;
+    }
+#pragma unroll
+    for (int r = 0; r < kMaxWorld; ++r) {
+      if (r < cm.world) {
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+          if (u < nvalid) *reinterpret_cast<float4*>(cm.param[r] + idx[u]) = wv[u];
+      }
+    }
   }
   // ragged tail (< 4 elements): owned by the last rank
   if (cm.rank == cm.world - 1) {
@@ -302,8 +348,8 @@ TDL_API int tdl_p2p_fused_step(void* comm, int64_t offset, int64_t n, int mode, 
   if (mode == 0) mode = (n * (grad_is_bf16 ? 2 : 4) <= (1 << 19) || kind == kNone) ? 1 : 2;
   if (kind == kNone) mode = 1;
   int64_t work = mode == 1 ? n / 4 : n / 4 / cm->world;
-  int blocks = (int)cdiv(work, (int64_t)kThreads * 4);
-  if (max_blocks <= 0) max_blocks = 64;
+  int blocks = (int)cdiv(work, (int64_t)kThreads * 2);
+  if (max_blocks <= 0) max_blocks = 128;
   if (max_blocks > kMaxBlocks) max_blocks = kMaxBlocks;
   if (max_blocks > num_sms()) max_blocks = num_sms();
   if (blocks > max_blocks) blocks = max_blocks;

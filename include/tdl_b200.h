@@ -29,6 +29,11 @@ int tdl_num_sms(void);
 int tdl_conv2d_fprop_bf16(const void* x, const void* w, void* y, const float* bias, const void* residual, int N,
                           int H, int W, int C, int K, int R, int S, int stride, int dil, int pad_h, int pad_w, int P,
                           int Q, int relu, void* stream);
+/* stride-1 convolution whose output pixel (p,q) is written to (p*y_step+y_off_h, q*y_step+y_off_w) of a
+ * [N,y_full_h,y_full_w,K] tensor: one input-parity class of a strided convolution's data gradient per call */
+int tdl_conv2d_fprop_strided_out_bf16(const void* x, const void* w, void* y, int N, int H, int W, int C, int K, int R,
+                                      int S, int dil, int pad_h, int pad_w, int P, int Q, int y_full_h, int y_full_w,
+                                      int y_step, int y_off_h, int y_off_w, void* stream);
 /* dw [K, R*S, C] fp32 is ACCUMULATED into (zero it first): dw += dy^T (*) x */
 int tdl_conv2d_wgrad_bf16(const void* x, const void* dy, float* dw, int N, int H, int W, int C, int K, int R, int S,
                           int stride, int dil, int pad_h, int pad_w, int P, int Q, void* stream);
@@ -76,6 +81,11 @@ int tdl_upsample_fwd(const void* x, void* y, int N, int H, int W, int C, int OH,
 int tdl_upsample_bwd(const void* dy, float* dx, int N, int H, int W, int C, int OH, int OW, int is_bf16, void* stream);
 int tdl_u8_to_bf16_normalize(const void* x_u8, void* y_bf16, int64_t pixels, int C, int Cpad, const float* mean,
                              const float* inv_std, void* stream);
+
+/* ---- batch augmentation on the GPU (reference: preprocessing/preprocessing.py:112-246, host-side there) ---- */
+int tdl_augment_seg(const float* images, const float* masks, const float* transforms, const int* transposed,
+                    float* out, float* out_mask, int B, int H, int W, int pad, float mean, float stddev,
+                    int laplace_2d, void* stream);
 
 /* ---- losses / metrics (reference: core/losses.py:5-92 pinned to CPU at model.py:391; core/metric.py:6-71) ---- */
 int tdl_lovasz_hinge(const float* logits, const float* labels, int B, int P, float grad_scale, float* loss_out,

@@ -1,0 +1,225 @@
+"""Multi-GPU checks and the all-reduce+optimizer sweep (BASELINE config 5).  Run under torchrun, one rank per GPU:
+
+    python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 --master-port 29511 \
+        scripts/p2p_check.py [correctness] [stress] [sweep] [train]
+
+Every timing is CUDA-event device time, max over ranks.  Rank 0 appends JSON lines to gpurun_out/p2p_check.jsonl.
+"""
+from __future__ import annotations
+
+import json
+import os
+import sys
+import time
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+import torch
+import torch.distributed as dist
+
+from tensorflowdistributedlearning_b200.ops import native_ops as O
+from tensorflowdistributedlearning_b200.parallel.p2p import P2PComm, SymmetricBuffer
+from tensorflowdistributedlearning_b200.parallel.tower import TowerGroup
+
+OUT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+os.makedirs(OUT, exist_ok=True)
+group = TowerGroup(device="cuda")
+W, R = group.world, group.rank
+
+
+def emit(**kw):
+    if R == 0:
+        kw["world"] = W
+        line = json.dumps(kw)
+        print(line, flush=True)
+        with open(os.path.join(OUT, "p2p_check.jsonl"), "a") as f:
+            f.write(line + "\n")
+
+
+def rel_err(a, b):
+    return float((a.float() - b.float()).abs().max() / (b.float().abs().max() + 1e-6))
+
+
+def timed(fn, iters=20, warmup=5):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    dist.barrier()
+    ts = []
+    for _ in range(iters):
+        dist.barrier()
+        torch.cuda.synchronize()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        fn()
+        e.record()
+        torch.cuda.synchronize()
+        ts.append(group.max_over_ranks(s.elapsed_time(e)))
+    ts.sort()
+    return ts[len(ts) // 2]
+
+
+def correctness():
+    for n in (256, 1000 + 3, 65536 + 5, 1 << 20, (1 << 24) + 7):
+        for mode in (1, 2):
+            for kind in (1, 2):
+                npad = (n + 7) // 8 * 8
+                gbuf = SymmetricBuffer(npad * 4)
+                pbuf = SymmetricBuffer(npad * 4)
+                comm = P2PComm(gbuf, pbuf)
+                torch.manual_seed(1000 + R)
+                g = torch.randn(n, device="cuda")
+                torch.manual_seed(5)
+                p0 = torch.randn(n, device="cuda")
+                gbuf.tensor()[:n].copy_(g)
+                pbuf.tensor()[:n].copy_(p0)
+                m1, m2 = torch.zeros(npad, device="cuda"), torch.zeros(npad, device="cuda")
+                lr_state = torch.tensor([0.1, 0.05], device="cuda")
+                torch.cuda.synchronize()
+                dist.barrier()
+                comm.fused_step(0, n, kind=kind, grad_is_bf16=False, zero_grad=True, m1=m1, m2=m2, lr_state=lr_state,
+                                a=0.9, b=(1e-4 if kind == 1 else 0.999), c=1e-8, mode=mode)
+                torch.cuda.synchronize()
+                gm = g.clone()
+                dist.all_reduce(gm)
+                gm /= W
+                if kind == 1:
+                    ref = p0 - 0.1 * (gm + 1e-4 * p0)
+                else:
+                    ref = p0 - 0.05 * (0.1 * gm) / ((0.001 * gm * gm).sqrt() + 1e-8)
+                got = pbuf.tensor()[:n]
+                err = rel_err(got, ref)
+                # mirrors bit-identical across ranks
+                chk = got.clone()
+                dist.broadcast(chk, 0)
+                same = torch.tensor([float(torch.equal(chk, got))], device="cuda")
+                dist.all_reduce(same, op=dist.ReduceOp.MIN)
+                zeroed = float(gbuf.tensor()[:n].abs().max()) == 0.0
+                emit(test="correctness", n=n, mode=mode, kind=kind, rel_err=err, mirrors_identical=bool(same.item()),
+                     grad_zeroed=zeroed, ok=err < 1e-5 and bool(same.item()) and zeroed)
+                dist.barrier()
+                comm.close(); gbuf.close(); pbuf.close()
+    # plain mean (BN statistics path)
+    n = 65632
+    sbuf = SymmetricBuffer(((n + 7) // 8 * 8) * 4)
+    comm = P2PComm(sbuf, None)
+    torch.manual_seed(77 + R)
+    v = torch.randn(n, device="cuda")
+    sbuf.tensor()[:n].copy_(v)
+    staging = torch.zeros((n + 7) // 8 * 8, device="cuda")
+    torch.cuda.synchronize(); dist.barrier()
+    comm.all_reduce_mean_(staging, 0, n)
+    torch.cuda.synchronize()
+    ref = v.clone(); dist.all_reduce(ref); ref /= W
+    emit(test="mean_inplace", n=n, rel_err=rel_err(sbuf.tensor()[:n], ref), ok=rel_err(sbuf.tensor()[:n], ref) < 1e-6)
+    dist.barrier()
+    comm.close(); sbuf.close()
+
+
+def stress():
+    """Thousands of back-to-back small one-shots with changing payloads (signal-pad race stress)."""
+    n = 4096
+    gbuf, pbuf = SymmetricBuffer(n * 4), SymmetricBuffer(n * 4)
+    comm = P2PComm(gbuf, pbuf)
+    m1 = torch.zeros(n, device="cuda")
+    lr_state = torch.tensor([1.0, 1.0], device="cuda")
+    pbuf.tensor().zero_()
+    torch.cuda.synchronize(); dist.barrier()
+    iters = 3000
+    for it in range(iters):
+        gbuf.tensor().fill_(float((it % 7) + R))          # payload changes every iteration, differs per rank
+        comm.fused_step(0, n, kind=1, grad_is_bf16=False, zero_grad=True, m1=m1, m2=None, lr_state=lr_state,
+                        a=0.0, b=0.0, c=0.0, mode=1 + (it % 2), max_blocks=4)
+    torch.cuda.synchronize()
+    expect = -sum(((it % 7) + (W - 1) / 2.0) for it in range(iters))  # momentum 0, lr 1: p -= mean(grad)
+    got = pbuf.tensor()
+    ok = bool(torch.allclose(got, torch.full_like(got, expect), rtol=1e-4))
+    emit(test="stress", iters=iters, expect=expect, got=float(got[0]), ok=ok)
+    dist.barrier()
+    comm.close(); gbuf.close(); pbuf.close()
+
+
+def sweep():
+    """Fused all-reduce+SGD-momentum kernel vs ncclAllReduce + separate fused optimizer kernel, 1 KB .. 1 GB."""
+    sizes = [1 << k for k in range(10, 31, 2)] + [51_114_064, 167_256_100]  # bytes; + ResNet-50 bf16 / ref fp32 sizes
+    maxn = max(sizes) // 4
+    gbuf, pbuf = SymmetricBuffer(maxn * 4), SymmetricBuffer(maxn * 4)
+    comm = P2PComm(gbuf, pbuf)
+    m1 = torch.zeros(maxn, device="cuda")
+    lr_state = torch.tensor([1e-3, 1e-3], device="cuda")
+    gt, pt = gbuf.tensor(), pbuf.tensor()
+    gt.normal_()
+    for nbytes in sorted(sizes):
+        n = nbytes // 4
+        res = {}
+        for mode, blocks in ((1, 32), (2, 64), (2, 128), (2, 148)):
+            if mode == 1 and nbytes > (64 << 20):
+                continue
+            t = timed(lambda: comm.fused_step(0, n, kind=1, grad_is_bf16=False, zero_grad=False, m1=m1, m2=None,
+                                              lr_state=lr_state, a=0.9, b=0.0, c=0.0, mode=mode, max_blocks=blocks),
+                      iters=10 if nbytes > (256 << 20) else 20)
+            res[f"p2p_mode{mode}_b{blocks}_us"] = t * 1e3
+        g2, p2, mm = gt[:n], torch.zeros(n, device="cuda"), torch.zeros(n, device="cuda")
+
+        def nccl_path():
+            dist.all_reduce(g2)
+            O.sgd_momentum_flat(p2, g2, mm, None, lr_state, 0.9, 0.0, 1.0 / W, False)
+
+        t = timed(nccl_path, iters=10 if nbytes > (256 << 20) else 20)
+        res["nccl_plus_opt_us"] = t * 1e3
+        t = timed(lambda: dist.all_reduce(g2), iters=10 if nbytes > (256 << 20) else 20)
+        res["nccl_allreduce_us"] = t * 1e3
+        best = min(v for k, v in res.items() if k.startswith("p2p"))
+        # NVLink roofline for the fused two-shot path: each GPU pulls (W-1)/W of the gradient bytes and pushes
+        # (W-1)/W of the updated weights; directions are independent, so time >= (W-1)/W * bytes / link_bw.
+        wire = (W - 1) / W * nbytes
+        res.update(bytes=nbytes, best_p2p_us=best, speedup_vs_nccl_plus_opt=res["nccl_plus_opt_us"] / best,
+                   wire_gbs_per_dir=wire / best / 1e3, frac_of_770=wire / best / 1e3 / 770.0,
+                   frac_of_900=wire / best / 1e3 / 900.0)
+        emit(test="sweep", **res)
+        del g2, p2, mm
+    comm.close(); gbuf.close(); pbuf.close()
+
+
+def train():
+    """ResNet-50 (small images) for a few steps: p2p vs nccl gradient paths give the same weights; mirrors identical."""
+    from tensorflowdistributedlearning_b200 import models
+    from tensorflowdistributedlearning_b200.parallel.trainer import TowerTrainer, classification_loss
+
+    finals = {}
+    for comm_kind, graph, overlap in (("nccl", False, False), ("p2p", False, False), ("p2p", True, False), ("p2p", True, True)):
+        torch.manual_seed(3)
+        tr = TowerTrainer(models.resnet50(num_classes=32), group, batch=16, input_hwc=(64, 64, 3),
+                          loss_fn=classification_loss, use_graph=graph, kind="sgdm", lr=0.05, momentum=0.9,
+                          comm=comm_kind, overlap=overlap, bucket_cap_mb=8.0)
+        gen = torch.Generator().manual_seed(50 + R)
+        tr.images.copy_(torch.randint(0, 256, tr.images.shape, dtype=torch.uint8, generator=gen))
+        tr.labels.copy_(torch.randint(0, 32, tr.labels.shape, generator=gen))
+        tr.warmup_and_capture(warmup=2)
+        for _ in range(4):
+            tr.run_step()
+        torch.cuda.synchronize()
+        p = tr.opt.flat.param_flat.clone()
+        chk = p.clone()
+        dist.broadcast(chk, 0)
+        same = torch.tensor([float(torch.equal(chk, p))], device="cuda")
+        dist.all_reduce(same, op=dist.ReduceOp.MIN)
+        s = tr.opt.flat.stats_flat.clone(); s0 = s.clone(); dist.broadcast(s0, 0)
+        finals[(comm_kind, graph, overlap)] = p
+        emit(test="train", comm=comm_kind, graph=graph, overlap=overlap, loss=float(tr.loss.item()),
+             mirrors_identical=bool(same.item()), stats_identical=bool(torch.equal(s, s0)),
+             buckets=len(tr.opt.flat.buckets), ok=bool(same.item()))
+        tr.close()
+        dist.barrier()
+    base = finals[("nccl", False, False)]
+    for k, v in finals.items():
+        emit(test="train_vs_nccl", variant=list(k), rel_err=rel_err(v, base), ok=rel_err(v, base) < 5e-2)
+
+
+if __name__ == "__main__":
+    which = sys.argv[1:] or ["correctness", "stress", "train", "sweep"]
+    t0 = time.time()
+    for w in which:
+        {"correctness": correctness, "stress": stress, "sweep": sweep, "train": train}[w]()
+        emit(test=w, event="done", secs=round(time.time() - t0, 1))
+    group.shutdown()

@@ -166,25 +166,33 @@ def sample_augmentation(rng: np.random.RandomState, height: int, width: int, hor
     return {"transpose": do_transpose, "transform": t}
 
 
+def apply_augmentation(image: np.ndarray, mask: np.ndarray, params: Dict, reference_compat: bool = True, pad: int = 40):
+    """Deterministic part of the augmentation: normalise -> reflect pad -> (transpose) -> warp -> central crop ->
+    laplace channel, for given ``params`` = {'transpose': bool, 'transform': 8-vector}.  Oracle of the CUDA kernel."""
+    image = normalise(image)
+    h0 = image.shape[0]
+    image = np.pad(image, ((pad, pad), (pad, pad), (0, 0)), mode="reflect")
+    mask = np.pad(mask, ((pad, pad), (pad, pad), (0, 0)), mode="reflect")
+    h = image.shape[0]
+    if params["transpose"]:
+        image, mask = image.transpose(1, 0, 2), mask.transpose(1, 0, 2)
+    image = transform_image(image, params["transform"], "BILINEAR")
+    mask = transform_image(mask, params["transform"], "NEAREST")
+    image, mask = central_crop(image, h0 / h), central_crop(mask, h0 / h)
+    image = np.concatenate([image, laplace(image, reference_compat)], axis=-1).astype(np.float32)
+    return image, mask.astype(np.float32)
+
+
 def read_and_preprocess(image: np.ndarray, mask: np.ndarray, augment: bool = False,
                         rng: Optional[np.random.RandomState] = None, reference_compat: bool = True, **aug_kw):
     """image/mask: [H, W, 1] in [0,1].  Returns ({'images': [H,W,2]}, mask[H,W,1]) like the reference."""
-    image = normalise(image)
     if augment:
         rng = rng or np.random.RandomState()
-        h0, w0 = image.shape[:2]
         pad = 40
-        image = np.pad(image, ((pad, pad), (pad, pad), (0, 0)), mode="reflect")
-        mask = np.pad(mask, ((pad, pad), (pad, pad), (0, 0)), mode="reflect")
-        h, w = image.shape[:2]
-        p = sample_augmentation(rng, h, w, **aug_kw)
-        if p["transpose"]:
-            image = image.transpose(1, 0, 2)
-            mask = mask.transpose(1, 0, 2)
-        image = transform_image(image, p["transform"], "BILINEAR")
-        mask = transform_image(mask, p["transform"], "NEAREST")
-        image = central_crop(image, h0 / h)
-        mask = central_crop(mask, h0 / h)
+        p = sample_augmentation(rng, image.shape[0] + 2 * pad, image.shape[1] + 2 * pad, **aug_kw)
+        image, mask = apply_augmentation(image, mask, p, reference_compat, pad)
+        return {"images": image}, mask
+    image = normalise(image)
     image = np.concatenate([image, laplace(image, reference_compat)], axis=-1).astype(np.float32)
     return {"images": image}, mask.astype(np.float32)
 

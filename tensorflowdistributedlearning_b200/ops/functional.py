@@ -93,11 +93,9 @@ class _ConvNative(torch.autograd.Function):
                                     pad_w=(Sk - 1) * dil - pl, out_hw=(h, w))
                 _count(1)
             else:
-                # strided data gradient: cuDNN via aten (documented gap; few layers per network)
-                w4 = wsaved.view(K, Rk, Sk, C).permute(0, 3, 1, 2)
-                xin_shape = (n, C, h + pt + pb, w + pl + pr)
-                gx = torch.nn.grad.conv2d_input(xin_shape, w4, dy.permute(0, 3, 1, 2), stride=stride, dilation=dil)
-                dx = gx[:, :, pt:pt + h, pl:pl + w].permute(0, 2, 3, 1).contiguous()
+                # strided data gradient: one tcgen05 launch per input-parity class, strided TMA stores
+                dx = O.conv2d_dgrad_strided(dy, wsaved, (n, h, w, C), R=Rk, S=Sk, stride=stride, pad_h=pt, pad_w=pl)
+                _count(stride * stride)
         if ctx.needs_input_grad[1]:
             dw = torch.zeros((K, Rk * Sk, C), dtype=torch.float32, device=x.device)
             O.conv2d_wgrad(x, dy, dw, R=Rk, S=Sk, stride=stride, dil=dil, pad_h=pt, pad_w=pl)

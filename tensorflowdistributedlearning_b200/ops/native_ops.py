@@ -63,6 +63,46 @@ def conv2d_fprop(x: torch.Tensor, w: torch.Tensor, *, R: int, S: int, stride: in
     return y
 
 
+def conv2d_dgrad_strided(dy: torch.Tensor, wf: torch.Tensor, in_shape, *, R: int, S: int, stride: int, pad_h: int,
+                         pad_w: int) -> torch.Tensor:
+    """Data gradient of a stride-`stride` convolution (dilation 1) on the tcgen05 kernel.
+
+    dx is split into stride*stride input-parity classes; class (a, b) is a stride-1 convolution of dy with the
+    taps r = r0 + stride*i, s = s0 + stride*j (flipped, channel-transposed), written through a strided TMA store.
+    wf: bf16 [K, R*S, C] forward weights.
+    """
+    _chk_bf16_nhwc(dy, "dy")
+    n, h, w, c = in_shape
+    _, p, q, k = dy.shape
+    w4 = wf.view(k, R, S, c)
+    empty_class = False
+    classes = []
+    for a in range(stride):
+        r0 = (a + pad_h) % stride
+        nr = len(range(r0, R, stride))
+        for b in range(stride):
+            s0 = (b + pad_w) % stride
+            ns = len(range(s0, S, stride))
+            ha, wb = -(-(h - a) // stride), -(-(w - b) // stride)
+            if ha <= 0 or wb <= 0:
+                continue
+            if nr == 0 or ns == 0:
+                empty_class = True
+                continue
+            classes.append((a, b, r0, s0, nr, ns, ha, wb))
+    dx = (torch.zeros if empty_class else torch.empty)(in_shape, dtype=torch.bfloat16, device=dy.device)
+    for (a, b, r0, s0, nr, ns, ha, wb) in classes:
+        # Wd[c, r', s', k] = W[k, r0 + stride*(nr-1-r'), s0 + stride*(ns-1-s'), c]
+        wsub = w4[:, r0::stride, s0::stride, :].flip(1, 2).permute(3, 1, 2, 0).contiguous()
+        oh = (a + pad_h - r0) // stride
+        ow = (b + pad_w - s0) // stride
+        rc = N.lib().tdl_conv2d_fprop_strided_out_bf16(
+            N.ptr(dy), N.ptr(wsub), N.ptr(dx), _i(n), _i(p), _i(q), _i(k), _i(c), _i(nr), _i(ns), _i(1),
+            _i(nr - 1 - oh), _i(ns - 1 - ow), _i(ha), _i(wb), _i(h), _i(w), _i(stride), _i(a), _i(b), N.stream_ptr())
+        N.check(rc, "tdl_conv2d_fprop_strided_out_bf16")
+    return dx
+
+
 def conv2d_wgrad(x: torch.Tensor, dy: torch.Tensor, dw: torch.Tensor, *, R: int, S: int, stride: int = 1,
                  dil: int = 1, pad_h: int = 0, pad_w: int = 0) -> torch.Tensor:
     """dw[K, R*S, C] (fp32) += dy^T (*) x.  ``dw`` is accumulated into (zero it for a fresh gradient)."""

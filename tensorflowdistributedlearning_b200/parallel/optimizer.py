@@ -31,7 +31,7 @@ class DistributedOptimizer:
                  momentum: float = 0.9, weight_decay: float = 0.0, beta1: float = 0.9, beta2: float = 0.999,
                  eps: float = 1e-8, decay_steps: float = 0.0, decay_rate: float = 1.0, comm: Optional[str] = None,
                  bucket_cap_mb: float = 32.0, overlap: bool = True, sync_bn_stats: bool = True,
-                 comm_max_blocks: int = 64):
+                 comm_max_blocks: int = 128):
         if kind not in ("adam", "sgdm"):
             raise ValueError("kind must be 'adam' or 'sgdm'")
         self.group, self.kind = group, kind

@@ -101,6 +101,24 @@ def test_conv_dgrad_via_weight_prep(O, case):
     assert rel_err(dx, gx[:, :, pt:pt + H, pt:pt + H].permute(0, 2, 3, 1)) < 2e-2
 
 
+@pytest.mark.parametrize("case", [(2, 56, 128, 128, 3, 1), (2, 56, 256, 512, 1, 0), (2, 51, 64, 64, 3, 1),
+                                  (2, 56, 64, 128, 3, 0), (3, 13, 72, 40, 3, 1)])
+def test_conv_dgrad_strided_parity_classes(O, case):
+    N, H, C, K, R, pad = case
+    torch.manual_seed(12)
+    P = (H + 2 * pad - R) // 2 + 1 if pad else -(-H // 2)
+    pt = pad if pad else O.same_pad(H, R, 2)[1]
+    pb = (P - 1) * 2 + R - H - pt
+    wf = (torch.randn(K, R * R, C, device="cuda") / math.sqrt(R * R * C)).bfloat16()
+    dy = torch.randn(N, P, P, K, device="cuda").bfloat16()
+    dx = O.conv2d_dgrad_strided(dy, wf, (N, H, H, C), R=R, S=R, stride=2, pad_h=pt, pad_w=pt)
+    xr = torch.zeros(N, C, H + pt + max(pb, 0), H + pt + max(pb, 0), device="cuda", requires_grad=True)
+    w4 = wf.float().view(K, R, R, C).permute(0, 3, 1, 2)
+    yr = F.conv2d(xr, w4, None, stride=2)[:, :, :P, :P]
+    (gx,) = torch.autograd.grad(yr, xr, dy.float().permute(0, 3, 1, 2))
+    assert rel_err(dx, gx[:, :, pt:pt + H, pt:pt + H].permute(0, 2, 3, 1)) < 2e-2
+
+
 @pytest.mark.parametrize("rows,C,relu,res", [(4096, 64, True, False), (5000, 256, True, True), (777, 2048, False, False)])
 def test_batch_norm_fwd_bwd(O, rows, C, relu, res):
     torch.manual_seed(3)
@@ -317,3 +335,25 @@ def test_trainer_step_native_matches_torch_path_and_learns():
     assert curves["native"][-1] < curves["native"][0] * 0.8, curves
     assert abs(curves["native"][0] - curves["torch"][0]) < 0.15, curves
     assert abs(curves["native"][-1] - curves["torch"][-1]) < 0.5, curves
+
+
+def test_gpu_augmentation_matches_cpu_oracle(O):
+    import numpy as np
+
+    from tensorflowdistributedlearning_b200.data import preprocessing as PP
+    from tensorflowdistributedlearning_b200.data.gpu_augment import augment_batch, sample_batch_params
+
+    rng = np.random.RandomState(0)
+    B, H = 6, 101
+    imgs = rng.rand(B, H, H, 1).astype(np.float32)
+    yy, xx = np.mgrid[0:H, 0:H]
+    masks = np.stack([(((yy - 50) ** 2 + (xx - 40 - 3 * b) ** 2) < (10 + 4 * b) ** 2) for b in range(B)])[..., None].astype(np.float32)
+    params = sample_batch_params(np.random.RandomState(5), B, H, H)
+    for compat in (True, False):
+        out, om = augment_batch(torch.from_numpy(imgs).cuda(), torch.from_numpy(masks).cuda(), params,
+                                reference_compat=compat)
+        for b in range(B):
+            ri, rm = PP.apply_augmentation(imgs[b], masks[b], params[b], compat)
+            assert np.abs(out[b].cpu().numpy() - ri).max() < 5e-3 * max(1.0, np.abs(ri).max())
+            # NEAREST sampling may flip a pixel whose source coordinate sits on a .5 boundary (fp32 vs fp64)
+            assert (om[b].cpu().numpy() != rm).mean() < 2e-3
