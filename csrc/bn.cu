@@ -437,6 +437,20 @@ TDL_API int tdl_bn_fwd_stats(const void* x, int64_t rows, int C, float* scratch,
   return 0;
 }
 
+// Finish BatchNorm statistics from partial (sum, sumsq) rows produced elsewhere (tdl_conv2d_fprop_stats_bf16):
+// partial is [nparts][2][C] fp32 and `rows` is the number of pixels the sums cover.
+TDL_API int tdl_bn_finalize_partials(const float* partial, int nparts, int64_t rows, int C, const float* gamma,
+                                     const float* beta, float* running_mean, float* running_var, float decay,
+                                     float eps, float* mean, float* invstd, float* scale, float* shift, void* stream) {
+  TDL_REQUIRE(C > 0 && nparts > 0 && rows > 0, "bad arguments");
+  const double unbias = rows > 1 ? (double)rows / (double)(rows - 1) : 1.0;
+  bn_finalize_stats_kernel<<<(C + 31) / 32, kFinThreads, 0, (cudaStream_t)stream>>>(
+      partial, nparts, C, 1.0 / (double)rows, unbias, gamma, beta, running_mean, running_var, decay, eps, mean, invstd,
+      scale, shift);
+  TDL_LAUNCH_OK("bn_finalize_stats_kernel");
+  return 0;
+}
+
 TDL_API int tdl_bn_infer_scale_shift(const float* gamma, const float* beta, const float* running_mean,
                                      const float* running_var, float eps, float* scale, float* shift, int C,
                                      void* stream) {

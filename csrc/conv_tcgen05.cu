@@ -137,27 +137,52 @@ struct FpropCfg {
   static constexpr int kBBytes = BLOCK_N * kBlockK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kTmemCols = 2 * BLOCK_N;  // double-buffered accumulator
-  // four 128-row x 64-channel bf16 staging tiles: a TMA store takes ~1 us to release its source, so the epilogue
-  // needs several stores in flight to keep draining TMEM
-  static constexpr int kOutBufs = 4;
+  static constexpr int kOutBufs = 2;             // 128-row x 64-channel bf16 staging tiles for the TMA stores
   static constexpr int kOutBytes = kOutBufs * kBlockM * 128;
-  static constexpr int kStages = (227 * 1024 - kOutBytes - 1024 - 256) / kStageBytes;
-  static constexpr int kSmemBytes = kStages * kStageBytes + kOutBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int kStatBytes = 4 * 2 * 64 * 4;  // per-warp (sum, sumsq) partials of one 64-channel chunk
+  static constexpr int kBarBytes = 256;    // (2*kStages + 4) mbarriers + the TMEM slot
+  static constexpr int kAlignSlack = 384;  // the dynamic smem window is 1 KB aligned in practice; checked at run time
+  static constexpr int kStages = (227 * 1024 - kOutBytes - kStatBytes - kAlignSlack - kBarBytes) / kStageBytes;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kOutBytes + kStatBytes + kAlignSlack + kBarBytes;
+  static_assert((2 * kStages + 4) * 8 + 4 <= kBarBytes, "barrier region too small");
 };
 
-template <int BLOCK_N>
+// Column sums over the 32 rows held by a warp: lane l ends with the total of column l ("transpose-reduce": each
+// step halves the number of live columns, 31 shuffles for 32 columns).
+__device__ __forceinline__ float warp_column_sum(float (&v)[32], int lane) {
+#pragma unroll
+  for (int off = 16; off >= 1; off >>= 1) {
+    const bool upper = (lane & off) != 0;
+#pragma unroll
+    for (int i = 0; i < off; ++i) {
+      const float send = upper ? v[i] : v[i + off];
+      const float keep = upper ? v[i + off] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+    }
+  }
+  return v[0];
+}
+
+// kFused: bias / residual / ReLU present in the epilogue.  kStats: per-channel (sum, sum of squares) of the bf16
+// output accumulated into this CTA's slot of `stats` ([gridDim.x][2][K] fp32) for the BatchNorm that follows.
+template <int BLOCK_N, bool kFused, bool kStats>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
                   const __grid_constant__ CUtensorMap tm_y, const Geometry g, const float* __restrict__ bias,
-                  const bf16* __restrict__ residual) {
+                  const bf16* __restrict__ residual, float* __restrict__ stats) {
   using Cfg = FpropCfg<BLOCK_N>;
   constexpr int kStages = Cfg::kStages;
-  extern __shared__ uint8_t smem_raw[];
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  if (smem - smem_raw > Cfg::kAlignSlack) {
+    if (threadIdx.x == 0) printf("tdl_b200: dynamic shared memory base is misaligned by %d bytes\n", (int)(smem - smem_raw));
+    __trap();
+  }
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + kStages * kABytes;
   uint8_t* smem_out = smem + kStages * Cfg::kStageBytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_out + Cfg::kOutBytes);
+  float* smem_stat = reinterpret_cast<float*>(smem_out + Cfg::kOutBytes);  // [4 warps][2][64]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_out + Cfg::kOutBytes + Cfg::kStatBytes);
   uint64_t* full_bar = bars;
   uint64_t* empty_bar = bars + kStages;
   uint64_t* tmem_full = bars + 2 * kStages;
@@ -192,6 +217,10 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
     }
     __syncwarp();
     ptx::tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+  }
+  if constexpr (kStats) {  // this CTA's statistics slot starts at zero
+    float* slot = stats + (size_t)blockIdx.x * 2 * g.K;
+    for (int i = threadIdx.x; i < 2 * g.K; i += kThreads) slot[i] = 0.f;
   }
   ptx::tc_fence_before();
   __syncthreads();
@@ -279,6 +308,10 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
     const int dw = rem - dh * g.TW;
     const bool row_in_patch = row < g.TN * patch;
     const bool issuer = (warp == kEpiWarp0 && lane == 0);
+    const uint32_t row_off = (uint32_t)row * 128u;
+    const uint32_t sw = (uint32_t)(row & 7);
+    const uint32_t tmem_lane = tmem_base + ((uint32_t)(quarter * 32) << 16);
+    float* my_stat = smem_stat + quarter * 128;
     int acc = 0;
     uint32_t acc_phase = 0;
     uint32_t chunk_count = 0;
@@ -288,17 +321,21 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
       const int tw_i = m_tile % g.tiles_w;
       const int th_i = (m_tile / g.tiles_w) % g.tiles_h;
       const int tn_i = m_tile / (g.tiles_w * g.tiles_h);
-      const int n = tn_i * g.TN + dn;
-      const int p = th_i * g.TH + dh;
-      const int q = tw_i * g.TW + dw;
-      const bool valid = row_in_patch && n < g.N && p < g.P && q < g.Q;
-      const size_t pix = ((size_t)n * g.P + p) * g.Q + q;
+      bool valid = true;
+      size_t pix = 0;
+      if constexpr (kFused || kStats) {
+        const int n = tn_i * g.TN + dn;
+        const int p = th_i * g.TH + dh;
+        const int q = tw_i * g.TW + dw;
+        valid = row_in_patch && n < g.N && p < g.P && q < g.Q;
+        pix = ((size_t)n * g.P + p) * g.Q + q;
+      }
+      const int chunks = min(BLOCK_N / 64, (g.K - n_tile * BLOCK_N + 63) / 64);
       ptx::mbar_wait(&tmem_full[acc], acc_phase);
       ptx::tc_fence_after();
 #pragma unroll 1
-      for (int cc = 0; cc < BLOCK_N / 64; ++cc) {
+      for (int cc = 0; cc < chunks; ++cc) {
         const int co_chunk = n_tile * BLOCK_N + cc * 64;
-        if (co_chunk >= g.K) break;  // uniform across the CTA
         uint8_t* out_tile = smem_out + (chunk_count % Cfg::kOutBufs) * (kBlockM * 128);
         ++chunk_count;
         if (issuer) ptx::tma_store_wait_read<Cfg::kOutBufs - 1>();  // the store that last read this tile has drained
@@ -306,49 +343,88 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
           uint32_t v[32];
-          ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) +
-                                 (uint32_t)(acc * BLOCK_N + cc * 64 + half * 32), v);
+          ptx::tmem_ld_32x32(tmem_lane + (uint32_t)(acc * BLOCK_N + cc * 64 + half * 32), v);
           ptx::tmem_ld_wait();
+          if (half == 1 && cc == chunks - 1) {
+            // every tcgen05.ld of this accumulator has completed: hand the TMEM buffer back to the MMA warp
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(&tmem_empty[acc]);
+          }
           const int co0 = co_chunk + half * 32;
+          float f[32];
 #pragma unroll
-          for (int j8 = 0; j8 < 4; ++j8) {
-            float f[8];
+          for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+          if constexpr (kFused) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(v[j8 * 8 + j]);
-            const int co = co0 + j8 * 8;
-            if (co < g.K) {
-              if (g.has_bias) {
-                const float4 b0 = *reinterpret_cast<const float4*>(bias + co);
-                const float4 b1 = *reinterpret_cast<const float4*>(bias + co + 4);
-                f[0] += b0.x; f[1] += b0.y; f[2] += b0.z; f[3] += b0.w;
-                f[4] += b1.x; f[5] += b1.y; f[6] += b1.z; f[7] += b1.w;
-              }
-              if (g.has_res && valid) {
-                float rr[8];
-                unpack8(ld8(residual + pix * g.K + co), rr);
+            for (int j8 = 0; j8 < 4; ++j8) {
+              const int co = co0 + j8 * 8;
+              if (co < g.K) {
+                if (g.has_bias) {
+                  const float4 b0 = *reinterpret_cast<const float4*>(bias + co);
+                  const float4 b1 = *reinterpret_cast<const float4*>(bias + co + 4);
+                  f[j8 * 8 + 0] += b0.x; f[j8 * 8 + 1] += b0.y; f[j8 * 8 + 2] += b0.z; f[j8 * 8 + 3] += b0.w;
+                  f[j8 * 8 + 4] += b1.x; f[j8 * 8 + 5] += b1.y; f[j8 * 8 + 6] += b1.z; f[j8 * 8 + 7] += b1.w;
+                }
+                if (g.has_res && valid) {
+                  float rr[8];
+                  unpack8(ld8(residual + pix * g.K + co), rr);
 #pragma unroll
-                for (int j = 0; j < 8; ++j) f[j] += rr[j];
-              }
-              if (g.relu) {
+                  for (int j = 0; j < 8; ++j) f[j8 * 8 + j] += rr[j];
+                }
+                if (g.relu) {
 #pragma unroll
-                for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
+                  for (int j = 0; j < 8; ++j) f[j8 * 8 + j] = fmaxf(f[j8 * 8 + j], 0.f);
+                }
               }
             }
-            const int chunk16 = half * 4 + j8;  // 16-byte chunk inside the 128-byte row
-            *reinterpret_cast<bf16x8*>(out_tile + row * 128 + ((chunk16 ^ (row & 7)) << 4)) = pack8(f);
           }
-        }
-        if (cc == BLOCK_N / 64 - 1 || co_chunk + 64 >= g.K) {
-          // every tcgen05.ld of this accumulator has completed: hand the TMEM buffer back to the MMA warp
-          ptx::tc_fence_before();
-          __syncwarp();
-          if (lane == 0) ptx::mbar_arrive(&tmem_empty[acc]);
+          uint32_t packed[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const __nv_bfloat162 h2 = __floats2bfloat162_rn(f[2 * j], f[2 * j + 1]);
+            packed[j] = *reinterpret_cast<const uint32_t*>(&h2);
+            if constexpr (kStats) {  // statistics of the values as stored (after bf16 rounding)
+              const float2 back = __bfloat1622float2(h2);
+              f[2 * j] = valid ? back.x : 0.f;
+              f[2 * j + 1] = valid ? back.y : 0.f;
+            }
+          }
+#pragma unroll
+          for (int j8 = 0; j8 < 4; ++j8) {
+            const uint32_t chunk16 = (uint32_t)(half * 4 + j8);
+            *reinterpret_cast<uint4*>(out_tile + row_off + ((chunk16 ^ sw) << 4)) =
+                make_uint4(packed[j8 * 4], packed[j8 * 4 + 1], packed[j8 * 4 + 2], packed[j8 * 4 + 3]);
+          }
+          if constexpr (kStats) {
+            float sq[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) sq[j] = f[j] * f[j];
+            const float s1 = warp_column_sum(f, lane);
+            const float s2 = warp_column_sum(sq, lane);
+            my_stat[half * 32 + lane] = s1;
+            my_stat[64 + half * 32 + lane] = s2;
+          }
         }
         ptx::fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the TMA (async proxy)
         ptx::named_bar_sync(1, 128);
         if (issuer) {
           ptx::tma_store_4d(&tm_y, out_tile, co_chunk, tw_i * g.TW, th_i * g.TH, tn_i * g.TN);
           ptx::tma_store_commit();
+        }
+        if constexpr (kStats) {
+          if (warp == kEpiWarp0) {  // fold the four warps' partials into this CTA's global slot (no other writer)
+            float* slot = stats + (size_t)blockIdx.x * 2 * g.K;
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+              const int idx = t * 32 + lane;        // 0..127: [which][channel within chunk]
+              const int which = idx >> 6, ch = co_chunk + (idx & 63);
+              if (ch < g.K) {
+                const float tot = smem_stat[idx] + smem_stat[128 + idx] + smem_stat[256 + idx] + smem_stat[384 + idx];
+                slot[(size_t)which * g.K + ch] += tot;
+              }
+            }
+          }
         }
       }
       if (++acc == 2) {
@@ -562,21 +638,34 @@ __global__ void weight_prep_kernel(const float* __restrict__ w, bf16* __restrict
   }
 }
 
-template <int BLOCK_N>
-static int launch_fprop(const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& ty, const Geometry& g,
-                        const float* bias, const bf16* res, cudaStream_t st) {
+template <int BLOCK_N, bool kFused, bool kStats>
+static int launch_fprop_t(const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& ty, const Geometry& g,
+                          const float* bias, const bf16* res, float* stats, int* nparts, cudaStream_t st) {
   using Cfg = FpropCfg<BLOCK_N>;
   static bool attr_set = false;
   if (!attr_set) {
-    TDL_CUDA_OK(cudaFuncSetAttribute(conv_fprop_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     Cfg::kSmemBytes));
+    TDL_CUDA_OK(cudaFuncSetAttribute(conv_fprop_kernel<BLOCK_N, kFused, kStats>,
+                                     cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
     attr_set = true;
   }
   const int total = g.tiles_n * g.tiles_h * g.tiles_w * g.n_tiles;
   const int grid = total < tdl::num_sms() ? total : tdl::num_sms();
-  conv_fprop_kernel<BLOCK_N><<<grid, kThreads, Cfg::kSmemBytes, st>>>(tx, tw, ty, g, bias, res);
+  if (nparts) *nparts = grid;
+  conv_fprop_kernel<BLOCK_N, kFused, kStats><<<grid, kThreads, Cfg::kSmemBytes, st>>>(tx, tw, ty, g, bias, res, stats);
   TDL_LAUNCH_OK("conv_fprop_kernel");
   return 0;
+}
+
+template <int BLOCK_N>
+static int launch_fprop(const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& ty, const Geometry& g,
+                        const float* bias, const bf16* res, float* stats, int* nparts, cudaStream_t st) {
+  const bool fused = g.has_bias || g.has_res || g.relu;
+  if (stats) {
+    if (fused) return launch_fprop_t<BLOCK_N, true, true>(tx, tw, ty, g, bias, res, stats, nparts, st);
+    return launch_fprop_t<BLOCK_N, false, true>(tx, tw, ty, g, bias, res, stats, nparts, st);
+  }
+  if (fused) return launch_fprop_t<BLOCK_N, true, false>(tx, tw, ty, g, bias, res, stats, nparts, st);
+  return launch_fprop_t<BLOCK_N, false, false>(tx, tw, ty, g, bias, res, stats, nparts, st);
 }
 
 template <int MT, int BLOCK_N>
@@ -621,7 +710,7 @@ struct OutView {
 
 static int fprop_impl(const void* x, const void* w, void* y, const float* bias, const void* residual, int N, int H,
                       int W, int C, int K, int R, int S, int stride, int dil, int pad_h, int pad_w, int P, int Q,
-                      int relu, const OutView* view, void* stream) {
+                      int relu, const OutView* view, float* stats, int* nparts, void* stream) {
   TDL_REQUIRE(C % 8 == 0 && K % 8 == 0, "channel counts must be multiples of 8 (16-byte TMA strides)");
   TDL_REQUIRE(stride >= 1 && stride <= 8 && dil >= 1, "bad stride/dilation");
   TDL_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(w) & 15) == 0 &&
@@ -678,9 +767,9 @@ static int fprop_impl(const void* x, const void* w, void* y, const float* bias, 
     if (rc) return rc;
   }
   cudaStream_t st = (cudaStream_t)stream;
-  if (block_n == 256) return launch_fprop<256>(tx, tw, ty, g, bias, (const bf16*)residual, st);
-  if (block_n == 128) return launch_fprop<128>(tx, tw, ty, g, bias, (const bf16*)residual, st);
-  return launch_fprop<64>(tx, tw, ty, g, bias, (const bf16*)residual, st);
+  if (block_n == 256) return launch_fprop<256>(tx, tw, ty, g, bias, (const bf16*)residual, stats, nparts, st);
+  if (block_n == 128) return launch_fprop<128>(tx, tw, ty, g, bias, (const bf16*)residual, stats, nparts, st);
+  return launch_fprop<64>(tx, tw, ty, g, bias, (const bf16*)residual, stats, nparts, st);
 }
 
 // y[N,P,Q,K] = conv(x[N,H,W,C], w[K,R*S,C]) (+bias) (+residual) (ReLU)      bf16 in/out, fp32 accumulate
@@ -688,7 +777,18 @@ TDL_API int tdl_conv2d_fprop_bf16(const void* x, const void* w, void* y, const f
                                   int N, int H, int W, int C, int K, int R, int S, int stride, int dil, int pad_h,
                                   int pad_w, int P, int Q, int relu, void* stream) {
   return fprop_impl(x, w, y, bias, residual, N, H, W, C, K, R, S, stride, dil, pad_h, pad_w, P, Q, relu, nullptr,
-                    stream);
+                    nullptr, nullptr, stream);
+}
+
+// Same convolution, additionally producing per-CTA partial (sum, sum of squares) of the bf16 output per channel:
+// stats_partial is [tdl_num_sms()][2][K] fp32 (written, not accumulated); *nparts_host receives how many leading
+// slots are valid.  Feed both to tdl_bn_finalize_partials: the BatchNorm statistics pass costs no extra read.
+TDL_API int tdl_conv2d_fprop_stats_bf16(const void* x, const void* w, void* y, const float* bias, int N, int H, int W,
+                                        int C, int K, int R, int S, int stride, int dil, int pad_h, int pad_w, int P,
+                                        int Q, float* stats_partial, int* nparts_host, void* stream) {
+  TDL_REQUIRE(stats_partial != nullptr && nparts_host != nullptr, "stats buffers required");
+  return fprop_impl(x, w, y, bias, nullptr, N, H, W, C, K, R, S, stride, dil, pad_h, pad_w, P, Q, 0, nullptr,
+                    stats_partial, nparts_host, stream);
 }
 
 // Stride-1 convolution whose output pixel (p, q) is stored at (p*y_step + y_off_h, q*y_step + y_off_w) of a
@@ -700,7 +800,8 @@ TDL_API int tdl_conv2d_fprop_strided_out_bf16(const void* x, const void* w, void
   OutView v = {y_full_h, y_full_w, y_step, y_off_h, y_off_w};
   TDL_REQUIRE(y_step >= 1 && y_off_h >= 0 && y_off_w >= 0, "bad output view");
   TDL_REQUIRE((P - 1) * y_step + y_off_h < y_full_h && (Q - 1) * y_step + y_off_w < y_full_w, "view exceeds tensor");
-  return fprop_impl(x, w, y, nullptr, nullptr, N, H, W, C, K, R, S, 1, dil, pad_h, pad_w, P, Q, 0, &v, stream);
+  return fprop_impl(x, w, y, nullptr, nullptr, N, H, W, C, K, R, S, 1, dil, pad_h, pad_w, P, Q, 0, &v, nullptr, nullptr,
+                    stream);
 }
 
 // dw[K,R*S,C] (fp32) += sum over pixels of dy[N,P,Q,K]^T * shifted x[N,H,W,C].  Caller zeroes dw.

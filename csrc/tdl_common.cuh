@@ -164,13 +164,18 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 // GPU lease).  ~4e9 cycles is about two seconds at B200 clocks.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
-  long long t0 = clock64();
+  long long t0 = 0;
+  uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (clock64() - t0 > 4000000000LL) {
-      if ((threadIdx.x & 31) == 0)
-        printf("tdl_b200: mbarrier wait timed out (block %d,%d thread %d parity %u)\n", (int)blockIdx.x,
-               (int)blockIdx.y, (int)threadIdx.x, parity);
-      __trap();
+    if ((++spins & 0xFFFu) == 0) {  // the watchdog reads the clock only once per 4096 failed probes
+      const long long now = clock64();
+      if (t0 == 0) t0 = now;
+      if (now - t0 > 4000000000LL) {
+        if ((threadIdx.x & 31) == 0)
+          printf("tdl_b200: mbarrier wait timed out (block %d,%d thread %d parity %u)\n", (int)blockIdx.x,
+                 (int)blockIdx.y, (int)threadIdx.x, parity);
+        __trap();
+      }
     }
   }
 }

@@ -29,6 +29,11 @@ int tdl_num_sms(void);
 int tdl_conv2d_fprop_bf16(const void* x, const void* w, void* y, const float* bias, const void* residual, int N,
                           int H, int W, int C, int K, int R, int S, int stride, int dil, int pad_h, int pad_w, int P,
                           int Q, int relu, void* stream);
+/* fprop that also emits per-CTA partial BatchNorm statistics of its bf16 output: stats_partial [tdl_num_sms()][2][K]
+ * fp32 (written), *nparts_host = number of valid leading slots (host int); finish with tdl_bn_finalize_partials */
+int tdl_conv2d_fprop_stats_bf16(const void* x, const void* w, void* y, const float* bias, int N, int H, int W, int C,
+                                int K, int R, int S, int stride, int dil, int pad_h, int pad_w, int P, int Q,
+                                float* stats_partial, int* nparts_host, void* stream);
 /* stride-1 convolution whose output pixel (p,q) is written to (p*y_step+y_off_h, q*y_step+y_off_w) of a
  * [N,y_full_h,y_full_w,K] tensor: one input-parity class of a strided convolution's data gradient per call */
 int tdl_conv2d_fprop_strided_out_bf16(const void* x, const void* w, void* y, int N, int H, int W, int C, int K, int R,
@@ -53,6 +58,9 @@ int tdl_bn_fwd_stats(const void* x, int64_t rows, int C, float* scratch, int64_t
 int tdl_bn_fwd_stats_noalloc(const void* x, int64_t rows, int C, const float* gamma, const float* beta,
                              float* running_mean, float* running_var, float decay, float eps, float* mean,
                              float* invstd, float* scale, float* shift, void* stream);
+int tdl_bn_finalize_partials(const float* partial, int nparts, int64_t rows, int C, const float* gamma,
+                             const float* beta, float* running_mean, float* running_var, float decay, float eps,
+                             float* mean, float* invstd, float* scale, float* shift, void* stream);
 int tdl_bn_infer_scale_shift(const float* gamma, const float* beta, const float* running_mean,
                              const float* running_var, float eps, float* scale, float* shift, int C, void* stream);
 int tdl_bn_apply(const void* x, const float* scale, const float* shift, const void* residual, void* y, int64_t rows,

@@ -60,7 +60,7 @@ class _ConvNative(torch.autograd.Function):
     """tcgen05 implicit-GEMM forward; dgrad = same kernel on flipped/transposed weights; wgrad = MN-major kernel."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, stride, dil, pads, out_hw):
+    def forward(ctx, x, weight, bias, stride, dil, pads, out_hw, want_stats=False):
         from . import native_ops as O
 
         K, Rk, Sk, C = weight.shape
@@ -70,15 +70,24 @@ class _ConvNative(torch.autograd.Function):
         wd = torch.empty((C, taps, K), dtype=torch.bfloat16, device=x.device) if (need_dgrad and stride == 1) else None
         O.conv2d_weight_prep(weight.detach(), wf, wd, K, taps, C)
         pt, pb, pl, pr = pads
-        y = O.conv2d_fprop(x, wf, R=Rk, S=Sk, stride=stride, dil=dil, pad_h=pt, pad_w=pl, out_hw=out_hw,
-                           bias=None if bias is None else bias.detach())
+        partials = None
+        if want_stats:
+            y, partials, nparts = O.conv2d_fprop_stats(x, wf, R=Rk, S=Sk, stride=stride, dil=dil, pad_h=pt, pad_w=pl,
+                                                       out_hw=out_hw, bias=None if bias is None else bias.detach())
+            partials = partials[:nparts]
+        else:
+            y = O.conv2d_fprop(x, wf, R=Rk, S=Sk, stride=stride, dil=dil, pad_h=pt, pad_w=pl, out_hw=out_hw,
+                               bias=None if bias is None else bias.detach())
         _count(2)
         ctx.save_for_backward(x, wd if wd is not None else wf)
         ctx.cfg = (K, Rk, Sk, C, stride, dil, pads, tuple(x.shape), bias is not None, wd is not None)
+        if want_stats:
+            ctx.mark_non_differentiable(partials)
+            return y, partials
         return y
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy, *_unused):
         from . import native_ops as O
 
         x, wsaved = ctx.saved_tensors
@@ -103,17 +112,22 @@ class _ConvNative(torch.autograd.Function):
             dw = dw.view(K, Rk, Sk, C)
         if has_bias and ctx.needs_input_grad[2]:
             db = dy.float().sum((0, 1, 2))
-        return dx, dw, db, None, None, None, None
+        return dx, dw, db, None, None, None, None, None
 
 
 def conv2d(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None, stride: int = 1,
-           dil: int = 1, padding="SAME") -> torch.Tensor:
-    """NHWC convolution, weight [K, R, S, C] (fp32 master).  TF 'SAME' geometry by default."""
+           dil: int = 1, padding="SAME", want_stats: bool = False):
+    """NHWC convolution, weight [K, R, S, C] (fp32 master).  TF 'SAME' geometry by default.
+
+    ``want_stats=True`` returns ``(y, stats)`` where ``stats`` is either None (torch path) or the per-CTA partial
+    BatchNorm statistics the tcgen05 kernel accumulated in its epilogue; pass it to :func:`batch_norm`."""
     K, Rk, Sk, C = weight.shape
     n, h, w, c = x.shape
     assert c == C, f"channel mismatch: input {c} vs weight {C}"
     P, Q, pt, pb, pl, pr = conv_pads(h, w, Rk, Sk, stride, dil, padding)
     if _native_ok(x) and C % 8 == 0 and K % 8 == 0 and stride <= 2:
+        if want_stats:
+            return _ConvNative.apply(x.contiguous(), weight, bias, stride, dil, (pt, pb, pl, pr), (P, Q), True)
         return _ConvNative.apply(x.contiguous(), weight, bias, stride, dil, (pt, pb, pl, pr), (P, Q))
     # torch path (cuDNN on GPU through a channels-last view; plain CPU conv on CPU towers)
     wq = weight.to(x.dtype)
@@ -123,7 +137,8 @@ def conv2d(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] =
         y = F.conv2d(xin, wq.permute(0, 3, 1, 2), bq, stride=stride, padding=(pt, pl), dilation=dil)
     else:
         y = F.conv2d(F.pad(xin, (pl, pr, pt, pb)), wq.permute(0, 3, 1, 2), bq, stride=stride, dilation=dil)
-    return y.permute(0, 2, 3, 1)
+    y = y.permute(0, 2, 3, 1)
+    return (y, None) if want_stats else y
 
 
 # ---------------------------------------------------------------------------------------------
@@ -131,14 +146,18 @@ def conv2d(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] =
 # ---------------------------------------------------------------------------------------------
 class _BNNative(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, gamma, beta, running_mean, running_var, residual, decay, eps, relu, training):
+    def forward(ctx, x, gamma, beta, running_mean, running_var, residual, decay, eps, relu, training, partials=None):
         from . import native_ops as O
 
         shape = x.shape
         C = shape[-1]
         x2 = x.reshape(-1, C)
         r2 = None if residual is None else residual.reshape(-1, C)
-        if training:
+        if training and partials is not None:
+            mean, invstd, scale, shift = O.bn_finalize_partials(partials, partials.shape[0], x2.shape[0], gamma, beta,
+                                                                running_mean, running_var, decay, eps)
+            _count(1)
+        elif training:
             mean, invstd, scale, shift = O.bn_fwd_stats(x2, gamma, beta, running_mean, running_var, decay, eps)
             _count(2)
         else:
@@ -167,17 +186,19 @@ class _BNNative(torch.autograd.Function):
         _count(4)
         return (dx.view(shape), dgamma if ctx.needs_input_grad[1] else None,
                 dbeta if ctx.needs_input_grad[2] else None, None, None,
-                dres.view(shape) if has_res else None, None, None, None, None)
+                dres.view(shape) if has_res else None, None, None, None, None, None)
 
 
 def batch_norm(x: torch.Tensor, gamma, beta, running_mean, running_var, *, decay: float, eps: float,
-               training: bool, relu: bool = False, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """y = relu?(BN(x) + residual?) over the last (channel) axis with TF fused-BN semantics."""
+               training: bool, relu: bool = False, residual: Optional[torch.Tensor] = None,
+               stats: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """y = relu?(BN(x) + residual?) over the last (channel) axis with TF fused-BN semantics.
+    ``stats``: partial statistics of ``x`` from ``conv2d(..., want_stats=True)`` (skips the statistics pass)."""
     C = x.shape[-1]
     if _native_ok(x) and C % 8 == 0 and gamma is not None and beta is not None:
         res = None if residual is None else residual.contiguous()
         return _BNNative.apply(x.contiguous(), gamma, beta, running_mean, running_var, res, decay, eps, relu,
-                               training)
+                               training, stats if training else None)
     if training:
         y = R.batch_norm_train(x, gamma, beta, running_mean, running_var, decay, eps)
     else:

@@ -71,8 +71,8 @@ class Conv2d(TFModule):
             R.truncated_normal_(self.weight.data, init_std)
         self.bias = nn.Parameter(torch.zeros(cout)) if use_bias else None
 
-    def forward(self, x: torch.Tensor) -> torch.Tensor:
-        return TF.conv2d(x, self.weight, self.bias, self.stride, self.rate, self.padding)
+    def forward(self, x: torch.Tensor, want_stats: bool = False):
+        return TF.conv2d(x, self.weight, self.bias, self.stride, self.rate, self.padding, want_stats)
 
     def tf_variables(self):
         d = {f"{self.scope}/weights": (self.weight, "conv")}
@@ -93,9 +93,10 @@ class BatchNorm(TFModule):
         self.register_buffer("moving_mean", torch.zeros(c))
         self.register_buffer("moving_variance", torch.ones(c))
 
-    def forward(self, x: torch.Tensor, relu: bool = False, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+    def forward(self, x: torch.Tensor, relu: bool = False, residual: Optional[torch.Tensor] = None,
+                stats: Optional[torch.Tensor] = None) -> torch.Tensor:
         return TF.batch_norm(x, self.gamma, self.beta, self.moving_mean, self.moving_variance, decay=self.decay,
-                             eps=self.eps, training=self.training, relu=relu, residual=residual)
+                             eps=self.eps, training=self.training, relu=relu, residual=residual, stats=stats)
 
     def tf_variables(self):
         d = {f"{self.scope}/beta": (self.beta, "plain"),
@@ -126,6 +127,9 @@ class ConvBNAct(TFModule):
         self.relu = relu
 
     def forward(self, x, residual: Optional[torch.Tensor] = None):
+        if self.training:  # the conv epilogue accumulates the BatchNorm statistics of its own output
+            y, stats = self.conv(x, want_stats=True)
+            return self.bn(y, relu=self.relu, residual=residual, stats=stats)
         return self.bn(self.conv(x), relu=self.relu, residual=residual)
 
 

@@ -63,6 +63,36 @@ def conv2d_fprop(x: torch.Tensor, w: torch.Tensor, *, R: int, S: int, stride: in
     return y
 
 
+def conv2d_fprop_stats(x: torch.Tensor, w: torch.Tensor, *, R: int, S: int, stride: int = 1, dil: int = 1,
+                       pad_h: int = 0, pad_w: int = 0, out_hw=None, bias: Optional[torch.Tensor] = None):
+    """Convolution + per-CTA partial BatchNorm statistics of its (bf16) output in the same kernel.
+    Returns (y, partials [sms, 2, K] fp32, nparts)."""
+    _chk_bf16_nhwc(x, "x")
+    _chk_bf16_nhwc(w, "w")
+    n, h, wd, c = x.shape
+    k = w.shape[0]
+    p, q = out_hw
+    y = torch.empty((n, p, q, k), dtype=torch.bfloat16, device=x.device)
+    partials = torch.empty((int(N.lib().tdl_num_sms()), 2, k), dtype=torch.float32, device=x.device)
+    nparts = ctypes.c_int(0)
+    rc = N.lib().tdl_conv2d_fprop_stats_bf16(N.ptr(x), N.ptr(w), N.ptr(y), N.ptr(bias), _i(n), _i(h), _i(wd), _i(c),
+                                             _i(k), _i(R), _i(S), _i(stride), _i(dil), _i(pad_h), _i(pad_w), _i(p),
+                                             _i(q), N.ptr(partials), ctypes.byref(nparts), N.stream_ptr())
+    N.check(rc, "tdl_conv2d_fprop_stats_bf16")
+    return y, partials, int(nparts.value)
+
+
+def bn_finalize_partials(partials: torch.Tensor, nparts: int, rows: int, gamma, beta, running_mean, running_var,
+                         decay: float, eps: float):
+    C = partials.shape[-1]
+    out = torch.empty((4, C), dtype=torch.float32, device=partials.device)
+    rc = N.lib().tdl_bn_finalize_partials(N.ptr(partials), _i(nparts), _i64(rows), _i(C), N.ptr(gamma), N.ptr(beta),
+                                          N.ptr(running_mean), N.ptr(running_var), _f(decay), _f(eps), N.ptr(out[0]),
+                                          N.ptr(out[1]), N.ptr(out[2]), N.ptr(out[3]), N.stream_ptr())
+    N.check(rc, "tdl_bn_finalize_partials")
+    return out[0], out[1], out[2], out[3]
+
+
 def conv2d_dgrad_strided(dy: torch.Tensor, wf: torch.Tensor, in_shape, *, R: int, S: int, stride: int, pad_h: int,
                          pad_w: int) -> torch.Tensor:
     """Data gradient of a stride-`stride` convolution (dilation 1) on the tcgen05 kernel.

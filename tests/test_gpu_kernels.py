@@ -101,6 +101,28 @@ def test_conv_dgrad_via_weight_prep(O, case):
     assert rel_err(dx, gx[:, :, pt:pt + H, pt:pt + H].permute(0, 2, 3, 1)) < 2e-2
 
 
+@pytest.mark.parametrize("case", [(4, 28, 64, 256, 1, 1), (3, 13, 72, 40, 3, 1), (2, 56, 128, 128, 3, 2), (8, 7, 512, 1000, 1, 1)])
+def test_conv_fprop_with_fused_bn_statistics(O, case):
+    """The epilogue's per-CTA (sum, sumsq) partials equal the column statistics of the stored bf16 output."""
+    N, H, C, K, R, stride = case
+    torch.manual_seed(21)
+    x = torch.randn(N, H, H, C, device="cuda").bfloat16()
+    w = (torch.randn(K, R * R, C, device="cuda") / math.sqrt(R * R * C)).bfloat16()
+    P, pt, pb = O.same_pad(H, R, stride)
+    y, partials, nparts = O.conv2d_fprop_stats(x, w, R=R, S=R, stride=stride, pad_h=pt, pad_w=pt, out_hw=(P, P))
+    ref = _ref_conv(x, w, R, R, stride, 1, (pt, pb, pt, pb))
+    assert rel_err(y, ref) < 2e-2
+    yf = y.float().reshape(-1, K)
+    tot = partials[:nparts].double().sum(0)
+    assert rel_err(tot[0], yf.double().sum(0)) < 1e-4
+    assert rel_err(tot[1], (yf.double() ** 2).sum(0)) < 1e-4
+    gamma, beta = torch.ones(K, device="cuda"), torch.zeros(K, device="cuda")
+    mean, invstd, scale, shift = O.bn_finalize_partials(partials[:nparts], nparts, yf.shape[0], gamma, beta, None, None,
+                                                        0.99, 1e-3)
+    assert rel_err(mean, yf.mean(0)) < 1e-3
+    assert rel_err(1 / invstd ** 2 - 1e-3, yf.var(0, unbiased=False)) < 1e-3
+
+
 @pytest.mark.parametrize("case", [(2, 56, 128, 128, 3, 1), (2, 56, 256, 512, 1, 0), (2, 51, 64, 64, 3, 1),
                                   (2, 56, 64, 128, 3, 0), (3, 13, 72, 40, 3, 1)])
 def test_conv_dgrad_strided_parity_classes(O, case):
