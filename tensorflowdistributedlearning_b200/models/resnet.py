@@ -112,6 +112,9 @@ class BottleneckV1(TFModule):
                          ConvBNAct(depth_in, depth, 1, stride=stride, scope=f"{s}/shortcut", bn=bn, relu=False))
 
     def forward(self, x, end_points: Optional[dict] = None, prefix: str = ""):
+        # (ConvBNAct(want_tap=True) can fold the identity shortcut's gradient into conv1's data-gradient epilogue; it
+        #  measured slower than autograd's separate add on B200 -- the per-row residual loads stall the epilogue --
+        #  so the plain form is used.)
         sc = x if self.shortcut is None else self.shortcut(x)
         out = self.conv3(self.conv2(self.conv1(x)), residual=sc)  # relu(bn(conv3) + shortcut), one kernel
         if end_points is not None:
@@ -296,6 +299,11 @@ class ResNetClassifier(TFModule):
                                        stride_first=True) for i, n in enumerate(layers)]
         self.net = ResNetV2Beta(in_channels, blocks, num_classes=num_classes, global_pool=True, output_stride=None,
                                 root="7x7", scope=scope, bn=bn, postnorm=False, symmetric_padding=True)
+        # 3-channel images are zero-padded to 8 channels on the device (16-byte TMA rows) so that the 7x7 stem also
+        # runs on the tcgen05 kernel; the trainer reads this attribute
+        # (measured: with only 16 valid bytes per 128-byte TMA row the 7x7/s2 stem is TMA-row-bound on the generic
+        #  kernel -- 5.3 ms vs cuDNN's 1.5 ms -- so the stem stays on the cuDNN path until it has its own kernel)
+        self.input_channel_pad = None
         for m in self.modules():  # zero-init the last BN gamma of every unit (standard large-batch recipe)
             if isinstance(m, BottleneckV1) and m.conv3.bn.gamma is not None:
                 nn.init.zeros_(m.conv3.bn.gamma)

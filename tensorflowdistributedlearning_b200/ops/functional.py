@@ -19,6 +19,38 @@ _FORCE_REFERENCE = False  # flipped by tests / the proxy baseline to route every
 _LAUNCHES = 0             # native kernel launches issued through this module (bench "gpu_launches")
 
 
+# Parameters whose gradient the native backward kernels accumulate straight into ``param.grad`` (a view of the flat
+# gradient bucket) instead of returning it to autograd.  The distributed optimizer registers a callback per parameter
+# so bucket readiness is still signalled (autograd's post-accumulate hooks do not fire for these).
+_DIRECT_GRAD = False
+_GRAD_READY = {}
+
+
+def enable_direct_grad(flag: bool) -> None:
+    """When on, conv / BatchNorm backward write fp32 gradients directly into existing ``.grad`` buffers."""
+    global _DIRECT_GRAD
+    _DIRECT_GRAD = bool(flag)
+
+
+def register_grad_ready(param, fn) -> None:
+    _GRAD_READY[id(param)] = fn
+
+
+def unregister_grad_ready(param) -> None:
+    _GRAD_READY.pop(id(param), None)
+
+
+def _notify(param) -> None:
+    fn = _GRAD_READY.get(id(param))
+    if fn is not None:
+        fn(param)
+
+
+def _direct_ok(p) -> bool:
+    return (_DIRECT_GRAD and p is not None and p.grad is not None and p.grad.dtype == torch.float32
+            and p.grad.is_contiguous())
+
+
 def force_reference(flag: bool) -> None:
     global _FORCE_REFERENCE
     _FORCE_REFERENCE = bool(flag)
@@ -60,8 +92,10 @@ class _ConvNative(torch.autograd.Function):
     """tcgen05 implicit-GEMM forward; dgrad = same kernel on flipped/transposed weights; wgrad = MN-major kernel."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, stride, dil, pads, out_hw, want_stats=False):
+    def forward(ctx, x, weight, bias, stride, dil, pads, out_hw, want_stats=False, want_tap=False):
         from . import native_ops as O
+
+        ctx.weight_param, ctx.bias_param, ctx.want_tap = weight, bias, want_tap
 
         K, Rk, Sk, C = weight.shape
         taps = Rk * Sk
@@ -81,13 +115,20 @@ class _ConvNative(torch.autograd.Function):
         _count(2)
         ctx.save_for_backward(x, wd if wd is not None else wf)
         ctx.cfg = (K, Rk, Sk, C, stride, dil, pads, tuple(x.shape), bias is not None, wd is not None)
+        outs = [y]
         if want_stats:
             ctx.mark_non_differentiable(partials)
-            return y, partials
-        return y
+            outs.append(partials)
+        if want_tap:
+            # an alias of the input for an identity shortcut: its gradient comes back to THIS node, where the
+            # data-gradient kernel adds it in its epilogue instead of autograd launching a separate add
+            outs.append(x.view_as(x))
+        ctx.n_out = len(outs)
+        ctx.has_stats = want_stats
+        return outs[0] if len(outs) == 1 else tuple(outs)
 
     @staticmethod
-    def backward(ctx, dy, *_unused):
+    def backward(ctx, dy, *rest):
         from . import native_ops as O
 
         x, wsaved = ctx.saved_tensors
@@ -95,39 +136,73 @@ class _ConvNative(torch.autograd.Function):
         pt, pb, pl, pr = pads
         n, h, w, _ = xshape
         dy = dy.contiguous()
+        d_tap = rest[-1] if (ctx.want_tap and rest and rest[-1] is not None) else None
         dx = dw = db = None
         if ctx.needs_input_grad[0]:
             if has_wd:
                 dx = O.conv2d_fprop(dy, wsaved, R=Rk, S=Sk, stride=1, dil=dil, pad_h=(Rk - 1) * dil - pt,
-                                    pad_w=(Sk - 1) * dil - pl, out_hw=(h, w))
+                                    pad_w=(Sk - 1) * dil - pl, out_hw=(h, w),
+                                    residual=None if d_tap is None else d_tap.contiguous())
+                d_tap = None
                 _count(1)
             else:
                 # strided data gradient: one tcgen05 launch per input-parity class, strided TMA stores
                 dx = O.conv2d_dgrad_strided(dy, wsaved, (n, h, w, C), R=Rk, S=Sk, stride=stride, pad_h=pt, pad_w=pl)
                 _count(stride * stride)
-        if ctx.needs_input_grad[1]:
-            dw = torch.zeros((K, Rk * Sk, C), dtype=torch.float32, device=x.device)
-            O.conv2d_wgrad(x, dy, dw, R=Rk, S=Sk, stride=stride, dil=dil, pad_h=pt, pad_w=pl)
+        if d_tap is not None and dx is not None:
+            dx = dx + d_tap
+        if ctx.needs_input_grad[1] and C <= 16:
+            # tiny Cin (channel-padded RGB stem): a 128x64 tensor-core tile would be >90% padding, cuDNN's
+            # small-channel wgrad is the better tool for this one layer
+            w4 = wsaved.view(K, Rk, Sk, C).permute(0, 3, 1, 2)
+            xin = x.permute(0, 3, 1, 2)
+            if pt != pb or pl != pr:
+                xin = F.pad(xin, (pl, pr, pt, pb))
+                padding = [0, 0]
+            else:
+                padding = [pt, pl]
+            _, gw, _ = torch.ops.aten.convolution_backward(dy.permute(0, 3, 1, 2), xin, w4, None, [stride, stride],
+                                                           padding, [dil, dil], False, [0, 0], 1, [False, True, False])
+            dw = gw.permute(0, 2, 3, 1).float().contiguous()
+        elif ctx.needs_input_grad[1]:
+            wp = ctx.weight_param
+            if _direct_ok(wp):
+                O.conv2d_wgrad(x, dy, wp.grad.view(K, Rk * Sk, C), R=Rk, S=Sk, stride=stride, dil=dil, pad_h=pt, pad_w=pl)
+                _notify(wp)
+            else:
+                dw = torch.zeros((K, Rk * Sk, C), dtype=torch.float32, device=x.device)
+                O.conv2d_wgrad(x, dy, dw, R=Rk, S=Sk, stride=stride, dil=dil, pad_h=pt, pad_w=pl)
+                dw = dw.view(K, Rk, Sk, C)
             _count(1)
-            dw = dw.view(K, Rk, Sk, C)
         if has_bias and ctx.needs_input_grad[2]:
             db = dy.float().sum((0, 1, 2))
-        return dx, dw, db, None, None, None, None, None
+        return dx, dw, db, None, None, None, None, None, None
 
 
 def conv2d(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None, stride: int = 1,
-           dil: int = 1, padding="SAME", want_stats: bool = False):
+           dil: int = 1, padding="SAME", want_stats: bool = False, want_tap: bool = False):
     """NHWC convolution, weight [K, R, S, C] (fp32 master).  TF 'SAME' geometry by default.
 
     ``want_stats=True`` returns ``(y, stats)`` where ``stats`` is either None (torch path) or the per-CTA partial
-    BatchNorm statistics the tcgen05 kernel accumulated in its epilogue; pass it to :func:`batch_norm`."""
+    BatchNorm statistics the tcgen05 kernel accumulated in its epilogue; pass it to :func:`batch_norm`.
+    ``want_tap=True`` returns ``(y, stats_or_None, x_alias)``: feed ``x_alias`` to an identity shortcut and the
+    shortcut's gradient is added inside the data-gradient kernel's epilogue."""
     K, Rk, Sk, C = weight.shape
     n, h, w, c = x.shape
+    if c > C:  # channel-padded input (e.g. RGB padded to 8 for the TMA path): zero-pad the weight to match
+        weight = F.pad(weight, (0, c - C))
+        C = c
     assert c == C, f"channel mismatch: input {c} vs weight {C}"
     P, Q, pt, pb, pl, pr = conv_pads(h, w, Rk, Sk, stride, dil, padding)
     if _native_ok(x) and C % 8 == 0 and K % 8 == 0 and stride <= 2:
-        if want_stats:
-            return _ConvNative.apply(x.contiguous(), weight, bias, stride, dil, (pt, pb, pl, pr), (P, Q), True)
+        if want_stats or want_tap:
+            out = _ConvNative.apply(x.contiguous(), weight, bias, stride, dil, (pt, pb, pl, pr), (P, Q), want_stats,
+                                    want_tap)
+            if want_stats and want_tap:
+                return out
+            if want_tap:
+                return out[0], None, out[1]
+            return out
         return _ConvNative.apply(x.contiguous(), weight, bias, stride, dil, (pt, pb, pl, pr), (P, Q))
     # torch path (cuDNN on GPU through a channels-last view; plain CPU conv on CPU towers)
     wq = weight.to(x.dtype)
@@ -138,6 +213,8 @@ def conv2d(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] =
     else:
         y = F.conv2d(F.pad(xin, (pl, pr, pt, pb)), wq.permute(0, 3, 1, 2), bq, stride=stride, dilation=dil)
     y = y.permute(0, 2, 3, 1)
+    if want_tap:
+        return y, None, x
     return (y, None) if want_stats else y
 
 
@@ -148,6 +225,8 @@ class _BNNative(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, gamma, beta, running_mean, running_var, residual, decay, eps, relu, training, partials=None):
         from . import native_ops as O
+
+        ctx.gamma_param, ctx.beta_param = gamma, beta
 
         shape = x.shape
         C = shape[-1]
@@ -182,8 +261,15 @@ class _BNNative(torch.autograd.Function):
         x2, z2, scale, shift, mean, invstd = ctx.saved_tensors
         C = shape[-1]
         dz2 = dz.contiguous().view(-1, C)
-        dx, dres, dgamma, dbeta = O.bn_bwd(dz2, x2, z2, scale, shift, mean, invstd, relu, has_res)
+        g, b = ctx.gamma_param, ctx.beta_param
+        direct = _direct_ok(g) and _direct_ok(b)
+        dx, dres, dgamma, dbeta = O.bn_bwd(dz2, x2, z2, scale, shift, mean, invstd, relu, has_res,
+                                           acc_dgamma=g.grad if direct else None, acc_dbeta=b.grad if direct else None)
         _count(4)
+        if direct:
+            _notify(g)
+            _notify(b)
+            dgamma = dbeta = None
         return (dx.view(shape), dgamma if ctx.needs_input_grad[1] else None,
                 dbeta if ctx.needs_input_grad[2] else None, None, None,
                 dres.view(shape) if has_res else None, None, None, None, None, None)

@@ -71,8 +71,8 @@ class Conv2d(TFModule):
             R.truncated_normal_(self.weight.data, init_std)
         self.bias = nn.Parameter(torch.zeros(cout)) if use_bias else None
 
-    def forward(self, x: torch.Tensor, want_stats: bool = False):
-        return TF.conv2d(x, self.weight, self.bias, self.stride, self.rate, self.padding, want_stats)
+    def forward(self, x: torch.Tensor, want_stats: bool = False, want_tap: bool = False):
+        return TF.conv2d(x, self.weight, self.bias, self.stride, self.rate, self.padding, want_stats, want_tap)
 
     def tf_variables(self):
         d = {f"{self.scope}/weights": (self.weight, "conv")}
@@ -126,7 +126,12 @@ class ConvBNAct(TFModule):
         self.bn = BatchNorm(cout, bn.decay, bn.eps, bn.scale, scope=f"{scope}/BatchNorm")
         self.relu = relu
 
-    def forward(self, x, residual: Optional[torch.Tensor] = None):
+    def forward(self, x, residual: Optional[torch.Tensor] = None, want_tap: bool = False):
+        """``want_tap=True`` -> (out, x_alias): use x_alias as the identity shortcut of the enclosing unit so that its
+        gradient is added inside this convolution's data-gradient kernel."""
+        if want_tap:
+            y, stats, tap = self.conv(x, want_stats=self.training, want_tap=True)
+            return self.bn(y, relu=self.relu, residual=residual, stats=stats), tap
         if self.training:  # the conv epilogue accumulates the BatchNorm statistics of its own output
             y, stats = self.conv(x, want_stats=True)
             return self.bn(y, relu=self.relu, residual=residual, stats=stats)

@@ -80,9 +80,16 @@ class DistributedOptimizer:
         self._launched = [False] * len(self.flat.buckets)
         self._side = torch.cuda.Stream(priority=-1) if self.overlap else None
         self._hooks = []
+        if self.on_gpu:
+            from ..ops import functional as TF
+
+            TF.enable_direct_grad(True)  # native backward kernels accumulate straight into the flat gradient buckets
         if self.overlap:
+            from ..ops import functional as TF
+
             for p in self.flat.params:
                 self._hooks.append(p.register_post_accumulate_grad_hook(self._on_grad_ready))
+                TF.register_grad_ready(p, self._on_grad_ready)
         self._lr_ready = False
 
     # ---- schedule ----
@@ -191,8 +198,12 @@ class DistributedOptimizer:
         return float(self.lr_state[0].item())
 
     def close(self) -> None:
+        from ..ops import functional as TF
+
         for h in self._hooks:
             h.remove()
+        for p in self.flat.params:
+            TF.unregister_grad_ready(p)
         for c in (self._p2p, self._p2p_stats):
             if c is not None:
                 c.close()

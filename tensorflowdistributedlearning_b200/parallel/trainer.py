@@ -63,14 +63,18 @@ class TowerTrainer:
 
     # ---- the step body (eager; also what gets captured) ----
     def _prepare_input(self) -> torch.Tensor:
+        c_pad = getattr(self.model, "input_channel_pad", None) if self.device.type == "cuda" else None
         if self.device.type == "cuda" and self.input_is_u8 and self.compute_dtype == torch.bfloat16:
             from ..ops import native_ops as O
 
-            return O.u8_to_bf16_normalize(self.images, self.mean, self.inv_std)
+            return O.u8_to_bf16_normalize(self.images, self.mean, self.inv_std, c_pad=c_pad)
         x = self.images.float()
         if self.input_is_u8:
             x = x / 255.0
-        return ((x - self.mean) * self.inv_std).to(self.compute_dtype)
+        x = ((x - self.mean) * self.inv_std).to(self.compute_dtype)
+        if c_pad and c_pad > x.shape[-1]:
+            x = torch.nn.functional.pad(x, (0, c_pad - x.shape[-1]))
+        return x
 
     def _step_body(self) -> None:
         x = self._prepare_input()
