@@ -33,6 +33,8 @@ struct Comm {
   uint32_t* flags[kMaxWorld];  // peer-mapped signal pads: [kMaxBlocks][kMaxWorld] u32
   uint32_t* epoch;             // local: [kMaxBlocks] u32, last epoch used by each CTA
   int emulate;                 // 1: all "peers" live on this GPU and ranks are launched one after another
+  float* mc_grad;              // NVLS multicast address of the gradient buckets (nullptr when not available)
+  float* mc_param;             // NVLS multicast address of the parameter buckets
 };
 
 enum OptKind { kNone = 0, kSgdMomentum = 1, kAdam = 2 };
@@ -129,16 +131,25 @@ __device__ __forceinline__ float opt_update(const StepArgs& a, float w, float g,
   return g;  // kNone: the "parameter" is the mean itself
 }
 
-__device__ __forceinline__ void zero_grad_range(const Comm& cm, const StepArgs& a, int64_t lo, int64_t hi) {
-  // clear my own gradient bucket [lo, hi) (element indices), grid-strided
+// Clearing the gradient must mirror the READ pattern: the second cross-rank barrier is per CTA index, so CTA b may
+// only clear elements that CTA b of the peers read.  `first`/`count` are in 4-element vectors; vector k of the range
+// belongs to global thread (k mod nthr) -- exactly how the reduction loops assign vectors to threads.
+__device__ __forceinline__ void zero_vectors(const Comm& cm, const StepArgs& a, int64_t first_vec_elem, int64_t count) {
   const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int64_t nthr = (int64_t)gridDim.x * blockDim.x;
   if (a.grad_is_bf16) {
-    bf16* g = reinterpret_cast<bf16*>(cm.grad[cm.rank]);
-    for (int64_t i = lo + tid; i < hi; i += nthr) g[i] = __float2bfloat16(0.f);
+    bf16* g = reinterpret_cast<bf16*>(cm.grad[cm.rank]) + first_vec_elem;
+    for (int64_t v = tid; v < count; v += nthr) *reinterpret_cast<uint2*>(g + v * 4) = make_uint2(0u, 0u);
   } else {
-    float* g = cm.grad[cm.rank];
-    for (int64_t i = lo + tid; i < hi; i += nthr) g[i] = 0.f;
+    float* g = cm.grad[cm.rank] + first_vec_elem;
+    for (int64_t v = tid; v < count; v += nthr) *reinterpret_cast<float4*>(g + v * 4) = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+}
+__device__ __forceinline__ void zero_tail(const Comm& cm, const StepArgs& a, int64_t first, int64_t hi) {
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // the tail is read by global threads 0..2
+  if (first + tid < hi) {
+    if (a.grad_is_bf16) reinterpret_cast<bf16*>(cm.grad[cm.rank])[first + tid] = __float2bfloat16(0.f);
+    else cm.grad[cm.rank][first + tid] = 0.f;
   }
 }
 
@@ -199,9 +210,12 @@ one_shot_kernel(const Comm cm, const StepArgs a) {
   if (a.kind == kNone) {
     // publish the mean in place (fp32 buckets only)
     float* g = cm.grad[cm.rank];
-    for (int64_t i = lo + tid; i < hi; i += nthr) g[i] = mean_out[i];
+    for (int64_t v = tid; v < n4; v += nthr)  // same vector -> thread assignment as the reads above
+      *reinterpret_cast<float4*>(g + lo + v * 4) = *reinterpret_cast<const float4*>(mean_out + lo + v * 4);
+    if (lo + n4 * 4 + tid < hi) g[lo + n4 * 4 + tid] = mean_out[lo + n4 * 4 + tid];
   } else if (a.zero_grad) {
-    zero_grad_range(cm, a, lo, hi);
+    zero_vectors(cm, a, lo, n4);
+    zero_tail(cm, a, lo + n4 * 4, hi);
   }
   __syncthreads();
   if (threadIdx.x == 0) cm.epoch[blockIdx.x] = epoch;
@@ -265,7 +279,84 @@ two_shot_kernel(const Comm cm, const StepArgs a) {
   }
   __threadfence_system();
   cross_rank_barrier(cm, ++epoch);  // every slice has landed everywhere; every gradient has been read
-  if (a.zero_grad) zero_grad_range(cm, a, a.offset, a.offset + a.n);
+  if (a.zero_grad) {
+    // slice s of MY bucket was read by rank s with the same (CTA, thread) -> vector assignment used above
+    for (int sl = 0; sl < cm.world; ++sl) {
+      const int64_t s_lo = per * sl < n4 ? per * sl : n4;
+      const int64_t s_hi = s_lo + per < n4 ? s_lo + per : n4;
+      zero_vectors(cm, a, a.offset + s_lo * 4, s_hi - s_lo);
+    }
+    zero_tail(cm, a, a.offset + n4 * 4, a.offset + a.n);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) cm.epoch[blockIdx.x] = epoch;
+}
+
+// ---- NVLS: the reduction happens inside NVSwitch, the all-gather is one multicast store ----
+// multimem.ld_reduce on the multicast address returns the sum over every GPU's copy of the addressed gradient
+// (reduced in the switch, fp32), multimem.st writes the updated weights into every GPU's parameter bucket at once.
+// Per GPU and direction the links carry about S instead of 2(W-1)/W * S for the two-shot path.
+__device__ __forceinline__ float4 multimem_ld_reduce_add(const float* mc) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(mc)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st(float* mc, const float4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(v.x), "f"(v.y),
+               "f"(v.z), "f"(v.w)
+               : "memory");
+}
+
+__global__ void __launch_bounds__(kThreads)
+nvls_kernel(const Comm cm, const StepArgs a) {
+  uint32_t epoch = cm.epoch[blockIdx.x];
+  cross_rank_barrier(cm, ++epoch);
+  const float lr = a.lr_state[0];
+  const float lr_t = a.lr_state[1];
+  const float scale = a.grad_scale / (float)cm.world;
+  const int64_t n4 = a.n / 4;  // the host guarantees n % 4 == 0 on this path
+  const int64_t per = (n4 + cm.world - 1) / cm.world;
+  const int64_t v_lo = per * cm.rank < n4 ? per * cm.rank : n4;
+  const int64_t v_hi = v_lo + per < n4 ? v_lo + per : n4;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t nthr = (int64_t)gridDim.x * blockDim.x;
+  constexpr int U = 4;
+  for (int64_t v0 = v_lo + tid; v0 < v_hi; v0 += nthr * U) {
+    float4 acc[U];
+    int64_t idx[U];
+    int nvalid = 0;
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      idx[u] = a.offset + (v0 + (int64_t)u * nthr) * 4;
+      if (v0 + (int64_t)u * nthr < v_hi) nvalid = u + 1;
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      if (u < nvalid) acc[u] = multimem_ld_reduce_add(cm.mc_grad + idx[u]);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (u >= nvalid) break;
+      const int64_t i = idx[u];
+      float4 w = *reinterpret_cast<const float4*>(cm.param[cm.rank] + i);
+      w.x = opt_update(a, w.x, acc[u].x * scale, i, lr, lr_t);
+      w.y = opt_update(a, w.y, acc[u].y * scale, i + 1, lr, lr_t);
+      w.z = opt_update(a, w.z, acc[u].z * scale, i + 2, lr, lr_t);
+      w.w = opt_update(a, w.w, acc[u].w * scale, i + 3, lr, lr_t);
+      multimem_st(cm.mc_param + i, w);
+    }
+  }
+  __threadfence_system();
+  cross_rank_barrier(cm, ++epoch);
+  if (a.zero_grad) {
+    for (int sl = 0; sl < cm.world; ++sl) {
+      const int64_t s_lo = per * sl < n4 ? per * sl : n4;
+      const int64_t s_hi = s_lo + per < n4 ? s_lo + per : n4;
+      zero_vectors(cm, a, a.offset + s_lo * 4, s_hi - s_lo);
+    }
+  }
   __syncthreads();
   if (threadIdx.x == 0) cm.epoch[blockIdx.x] = epoch;
 }
@@ -326,12 +417,21 @@ TDL_API int tdl_p2p_comm_create(int world, int rank, void** grad_ptrs, void** pa
   *out_comm = c;
   return 0;
 }
+// Attach NVLS multicast addresses (from a CUDA multicast object bound to the same buffers) to a communicator.
+TDL_API int tdl_p2p_comm_set_multicast(void* comm, void* mc_grad, void* mc_param) {
+  Comm* c = (Comm*)comm;
+  TDL_REQUIRE(c != nullptr, "null communicator");
+  c->mc_grad = (float*)mc_grad;
+  c->mc_param = (float*)mc_param;
+  return 0;
+}
 TDL_API int tdl_p2p_comm_destroy(void* comm) {
   delete (Comm*)comm;
   return 0;
 }
 
-// Fused all-reduce(mean) + optimizer for one bucket.  mode: 1 = one-shot, 2 = two-shot, 0 = pick by size.
+// Fused all-reduce(mean) + optimizer for one bucket.  mode: 1 = one-shot, 2 = two-shot, 3 = NVLS multimem,
+// 0 = pick one-/two-shot by size.
 // kind: 0 = plain mean written back into the gradient bucket (m1 = fp32 staging of >= offset+n elements),
 //       1 = momentum SGD (a = momentum, b = weight decay), 2 = TF Adam (a = beta1, b = beta2, c = eps).
 TDL_API int tdl_p2p_fused_step(void* comm, int64_t offset, int64_t n, int mode, int kind, int grad_is_bf16,
@@ -347,7 +447,12 @@ TDL_API int tdl_p2p_fused_step(void* comm, int64_t offset, int64_t n, int mode, 
   s.m1 = m1; s.m2 = m2; s.lr_state = lr_state; s.a = a; s.b = b; s.c = c; s.grad_scale = grad_scale;
   if (mode == 0) mode = (n * (grad_is_bf16 ? 2 : 4) <= (1 << 19) || kind == kNone) ? 1 : 2;
   if (kind == kNone) mode = 1;
+  if (mode == 3) {
+    TDL_REQUIRE(cm->mc_grad && cm->mc_param, "NVLS mode needs multicast addresses (tdl_p2p_comm_set_multicast)");
+    TDL_REQUIRE(!grad_is_bf16 && n % 4 == 0 && kind != kNone, "NVLS mode: fp32 buckets, n % 4 == 0, with optimizer");
+  }
   int64_t work = mode == 1 ? n / 4 : n / 4 / cm->world;
+  if (mode == 3) work /= 2;  // one switch-reduced load replaces W peer loads: fewer CTAs saturate the links
   int blocks = (int)cdiv(work, (int64_t)kThreads * 2);
   if (max_blocks <= 0) max_blocks = 128;
   if (max_blocks > kMaxBlocks) max_blocks = kMaxBlocks;
@@ -356,6 +461,7 @@ TDL_API int tdl_p2p_fused_step(void* comm, int64_t offset, int64_t n, int mode, 
   if (blocks < 1) blocks = 1;
   cudaStream_t st = (cudaStream_t)stream;
   if (mode == 1) one_shot_kernel<<<blocks, kThreads, 0, st>>>(*cm, s);
+  else if (mode == 3) nvls_kernel<<<blocks, kThreads, 0, st>>>(*cm, s);
   else two_shot_kernel<<<blocks, kThreads, 0, st>>>(*cm, s);
   TDL_LAUNCH_OK("p2p fused step");
   return 0;

@@ -51,11 +51,24 @@ class DistributedOptimizer:
         self._p2p_stats = None
         alloc = None
         self._symm = {}
+        self.nvls = False
+        if comm == "nvls":  # p2p with the reduction inside NVSwitch (multimem); falls back to plain p2p if unavailable
+            comm, self.nvls = "p2p", True
+            self.comm = "p2p"
         if comm == "p2p":
             from .p2p import SymmetricBuffer
 
             def alloc(n, dtype, tag):  # noqa: E306
-                buf = SymmetricBuffer(n * torch.empty((), dtype=dtype).element_size())
+                want_mc = self.nvls and tag in ("param", "grad")
+                try:
+                    buf = SymmetricBuffer(n * torch.empty((), dtype=dtype).element_size(), multicast=want_mc)
+                except Exception as e:  # noqa: BLE001
+                    if not want_mc:
+                        raise
+                    if group.is_primary:
+                        print(f"WARNING: NVLS symmetric memory unavailable ({type(e).__name__}: {e}); using two-shot P2P")
+                    self.nvls = False
+                    buf = SymmetricBuffer(n * torch.empty((), dtype=dtype).element_size())
                 self._symm[tag] = buf
                 return buf.tensor(dtype)
 
@@ -72,6 +85,7 @@ class DistributedOptimizer:
             from .p2p import P2PComm
 
             self._p2p = P2PComm(self._symm["grad"], self._symm["param"])
+            self.nvls = self.nvls and self._p2p.has_multicast
             self._p2p_stats = P2PComm(self._symm["stats"], None)
             self._stats_staging = torch.zeros_like(self.flat.stats_flat)
         # overlap machinery
@@ -123,6 +137,7 @@ class DistributedOptimizer:
                     else (self.beta1, self.beta2, self.eps))
         self._p2p.fused_step(b.offset, b.numel, kind=1 if self.kind == "sgdm" else 2, grad_is_bf16=False,
                              zero_grad=True, m1=self.m1, m2=self.m2, lr_state=self.lr_state, a=a, b=bb, c=c,
+                             mode=3 if (self.nvls and b.numel * 4 > (1 << 19)) else 0,
                              max_blocks=self.comm_max_blocks)
 
     def _on_grad_ready(self, p) -> None:

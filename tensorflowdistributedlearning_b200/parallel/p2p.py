@@ -29,11 +29,35 @@ class _RawCuda:
 class SymmetricBuffer:
     """One allocation per rank, same size everywhere, mapped into every peer."""
 
-    def __init__(self, nbytes: int, group=None, emulate_world: int = 0):
+    def __init__(self, nbytes: int, group=None, emulate_world: int = 0, multicast: bool = False):
+        """``multicast=True`` allocates through torch's CUDA-VMM symmetric memory so that the buffer also gets an
+        NVLS multicast mapping (``self.mc_ptr``; 0 when the driver / fabric does not expose one).  The default path
+        is this library's own cudaIpc heap."""
         lib = N.lib()
         self.nbytes = int(nbytes)
         self.group = group
         self.emulated = emulate_world > 0
+        self.mc_ptr = 0
+        self._torch_tensor = None
+        self._torch_handle = None
+        if multicast and not self.emulated and dist.is_initialized() and dist.get_world_size(group) > 1:
+            import torch.distributed._symmetric_memory as symm
+
+            self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+            t = symm.empty(self.nbytes, dtype=torch.uint8, device=torch.device("cuda", torch.cuda.current_device()))
+            hdl = symm.rendezvous(t, group if group is not None else dist.group.WORLD)
+            t.zero_()
+            self._torch_tensor, self._torch_handle = t, hdl
+            self.ptrs = [int(p) for p in hdl.buffer_ptrs]
+            try:
+                self.mc_ptr = int(hdl.multicast_ptr)
+            except Exception:  # noqa: BLE001
+                self.mc_ptr = 0
+            self._own, self._opened = [], []
+            self._holders = [_RawCuda(p, self.nbytes) for p in self.ptrs]
+            torch.cuda.synchronize()
+            dist.barrier(group=group)
+            return
         self.world = emulate_world if self.emulated else (dist.get_world_size(group) if dist.is_initialized() else 1)
         self.rank = 0 if self.emulated else (dist.get_rank(group) if dist.is_initialized() else 0)
         self._own: List[int] = []
@@ -67,6 +91,8 @@ class SymmetricBuffer:
     def tensor(self, dtype=torch.float32, rank: Optional[int] = None) -> torch.Tensor:
         """This rank's buffer (or, in emulation, the buffer of ``rank``) as a flat tensor of ``dtype``."""
         r = self.rank if rank is None else rank
+        if self._torch_tensor is not None and r == self.rank:
+            return self._torch_tensor.view(dtype)
         t = torch.as_tensor(self._holders[r], device=torch.device("cuda", torch.cuda.current_device()))
         return t.view(dtype)
 
@@ -104,6 +130,10 @@ class P2PComm:
                                         N.ptr(self.epoch), ctypes.c_int(int(self.emulated)), ctypes.byref(out)),
                 "tdl_p2p_comm_create")
         self.handle = out
+        self.has_multicast = bool(grad.mc_ptr and param is not None and param.mc_ptr)
+        if self.has_multicast:
+            N.check(lib.tdl_p2p_comm_set_multicast(self.handle, ctypes.c_void_p(grad.mc_ptr),
+                                                   ctypes.c_void_p(param.mc_ptr)), "tdl_p2p_comm_set_multicast")
         if not self.emulated and dist.is_initialized() and self.world > 1:
             torch.cuda.synchronize()
             dist.barrier(group=group)
