@@ -180,6 +180,8 @@ class Model:
     @property
     def params(self) -> int:
         if self.n_params is None:
-            self.n_params = sum(p.numel() for p in self._build_model().state_dict().values()
-                                if p.is_floating_point())
+            from .ops.layers import iter_tf_variables
+
+            # every variable in scope, moving statistics included, at its logical (checkpoint) shape
+            self.n_params = sum(t.numel() for _, t, _ in iter_tf_variables(self._build_model()))
         return self.n_params

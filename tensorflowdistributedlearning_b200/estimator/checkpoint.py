@@ -14,7 +14,7 @@ from typing import Dict, List, Optional
 
 import torch
 
-from ..ops.layers import from_tf_layout, iter_tf_variables, to_tf_layout
+from ..ops.layers import _unpad, from_tf_layout, iter_tf_variables, iter_tf_variables_ex, to_tf_layout
 
 STATE_FILE = "checkpoint"
 
@@ -62,15 +62,17 @@ def save_checkpoint(model_dir: str, model: torch.nn.Module, optimizer=None, step
         step = sd["global_step"] if step is None else step
         flat = optimizer.flat
         slot1, slot2 = ("Adam", "Adam_1") if sd["kind"] == "adam" else ("Momentum", None)
-        by_id = {id(t): (name, kind) for name, t, kind in iter_tf_variables(optimizer.flat.model)}
+        by_id = {id(t): (name, kind, shape) for name, t, kind, shape in iter_tf_variables_ex(optimizer.flat.model)}
         for p in flat.params:
             if id(p) not in by_id:
                 continue
-            name, kind = by_id[id(p)]
+            name, kind, shape = by_id[id(p)]
             o = flat.offsets[id(p)]
-            tensors[f"{name}/{slot1}"] = to_tf_layout(sd["m1"][o:o + p.numel()].view(p.shape), kind).float().cpu().contiguous()
+            tensors[f"{name}/{slot1}"] = to_tf_layout(_unpad(sd["m1"][o:o + p.numel()].view(p.shape), shape),
+                                                      kind).float().cpu().contiguous()
             if slot2 and sd["m2"] is not None:
-                tensors[f"{name}/{slot2}"] = to_tf_layout(sd["m2"][o:o + p.numel()].view(p.shape), kind).float().cpu().contiguous()
+                tensors[f"{name}/{slot2}"] = to_tf_layout(_unpad(sd["m2"][o:o + p.numel()].view(p.shape), shape),
+                                                          kind).float().cpu().contiguous()
         if sd["kind"] == "adam":
             tensors["beta1_power"] = torch.tensor(optimizer.beta1 ** step, dtype=torch.float32)
             tensors["beta2_power"] = torch.tensor(optimizer.beta2 ** step, dtype=torch.float32)
@@ -117,16 +119,18 @@ def load_checkpoint(prefix: str, model: torch.nn.Module, optimizer=None, strict:
     if optimizer is not None:
         flat = optimizer.flat
         slot1, slot2 = ("Adam", "Adam_1") if optimizer.kind == "adam" else ("Momentum", None)
-        by_id = {id(t): (name, kind) for name, t, kind in iter_tf_variables(flat.model)}
+        by_id = {id(t): (name, kind, shape) for name, t, kind, shape in iter_tf_variables_ex(flat.model)}
         with torch.no_grad():
             for p in flat.params:
                 if id(p) not in by_id:
                     continue
-                name, kind = by_id[id(p)]
+                name, kind, shape = by_id[id(p)]
                 o = flat.offsets[id(p)]
                 if f"{name}/{slot1}" in tensors:
-                    optimizer.m1[o:o + p.numel()].copy_(from_tf_layout(tensors[f"{name}/{slot1}"], kind).reshape(-1))
+                    _unpad(optimizer.m1[o:o + p.numel()].view(p.shape), shape).copy_(
+                        from_tf_layout(tensors[f"{name}/{slot1}"], kind))
                 if slot2 and optimizer.m2 is not None and f"{name}/{slot2}" in tensors:
-                    optimizer.m2[o:o + p.numel()].copy_(from_tf_layout(tensors[f"{name}/{slot2}"], kind).reshape(-1))
+                    _unpad(optimizer.m2[o:o + p.numel()].view(p.shape), shape).copy_(
+                        from_tf_layout(tensors[f"{name}/{slot2}"], kind))
             optimizer.global_step.fill_(step)
     return step

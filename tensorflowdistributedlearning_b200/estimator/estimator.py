@@ -85,8 +85,11 @@ class Estimator:
             torch.manual_seed(self.config.seed)
             self.model = self.model_builder().to(self.group.device)
             # reference counts ALL variables in scope, moving statistics included (model.py:444-445)
-            self.n_params = sum(p.numel() for p in self.model.parameters()) + sum(
-                b.numel() for b in self.model.buffers() if b.is_floating_point())
+            from ..ops.layers import iter_tf_variables
+
+            n = sum(t.numel() for _, t, _ in iter_tf_variables(self.model))
+            self.n_params = n or (sum(p.numel() for p in self.model.parameters()) + sum(
+                b.numel() for b in self.model.buffers() if b.is_floating_point()))
         return self.model
 
     def _ensure_trainer(self, images: torch.Tensor, labels: torch.Tensor) -> TowerTrainer:

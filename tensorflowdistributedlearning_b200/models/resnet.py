@@ -46,13 +46,15 @@ class Bottleneck(TFModule):
         self.shortcut = (None if depth == depth_in else
                          Conv2d(depth_in, depth, 1, stride, use_bias=True, scope=f"{s}/shortcut",
                                 weight_decay=bn.weight_decay))
-        self.conv1 = ConvBNAct(depth_in, depth_bottleneck, 1, scope=f"{s}/conv1", bn=bn)
+        # The bottleneck width may not be a multiple of 8 (the reference's 258): it is stored channel-padded inside
+        # the unit (zeros), which keeps every tensor 16-byte aligned for TMA without touching checkpoint shapes.
+        self.conv1 = ConvBNAct(depth_in, depth_bottleneck, 1, scope=f"{s}/conv1", bn=bn, pad_out=True)
         # the reference runs this 3x3 at full resolution and then keeps every stride-th pixel; a strided conv
         # whose padding is the stride-1 SAME padding produces exactly those pixels.
         self.conv2 = ConvBNAct(depth_bottleneck, depth_bottleneck, 3, stride=stride, rate=rate,
-                               padding=(rate, rate, rate, rate), scope=f"{s}/Conv", bn=bn)
+                               padding=(rate, rate, rate, rate), scope=f"{s}/Conv", bn=bn, pad_in=True, pad_out=True)
         self.conv3 = Conv2d(depth_bottleneck, depth, 1, use_bias=True, scope=f"{s}/conv3",
-                            weight_decay=bn.weight_decay)
+                            weight_decay=bn.weight_decay, pad_in=True)
 
     def forward(self, x, end_points: Optional[dict] = None, prefix: str = ""):
         pre = self.preact(x, relu=True)

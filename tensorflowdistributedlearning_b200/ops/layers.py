@@ -31,11 +31,31 @@ class TFModule(nn.Module):
         return {}
 
 
-def iter_tf_variables(model: nn.Module) -> Iterator[Tuple[str, torch.Tensor, str]]:
+def _unpad(t: torch.Tensor, shape) -> torch.Tensor:
+    """Leading sub-block of ``t`` with the logical (checkpoint) ``shape``; ``t`` itself when nothing is padded."""
+    if shape is None or tuple(t.shape) == tuple(shape):
+        return t
+    return t[tuple(slice(0, n) for n in shape)]
+
+
+def iter_tf_variables_ex(model: nn.Module):
+    """(name, storage tensor, kind, logical shape).  Storage may be channel-padded to a multiple of 8 for the TMA /
+    vector kernels (e.g. the reference's 258-channel block); the logical shape is what checkpoints hold."""
     for m in model.modules():
         if isinstance(m, TFModule):
-            for name, (t, kind) in m.tf_variables().items():
-                yield name, t, kind
+            for name, v in m.tf_variables().items():
+                t, kind = v[0], v[1]
+                yield name, t, kind, (v[2] if len(v) > 2 else None)
+
+
+def iter_tf_variables(model: nn.Module) -> Iterator[Tuple[str, torch.Tensor, str]]:
+    """(name, tensor with its logical shape, kind) -- a view when the storage is channel-padded."""
+    for name, t, kind, shape in iter_tf_variables_ex(model):
+        yield name, _unpad(t, shape), kind
+
+
+def pad8(c: int) -> int:
+    return (c + 7) // 8 * 8
 
 
 def to_tf_layout(t: torch.Tensor, kind: str) -> torch.Tensor:
@@ -59,25 +79,33 @@ class Conv2d(TFModule):
 
     def __init__(self, cin: int, cout: int, k: int, stride: int = 1, rate: int = 1, padding: str = "SAME",
                  use_bias: bool = False, scope: str = "Conv", init_std: Optional[float] = None,
-                 weight_decay: float = 0.0):
+                 weight_decay: float = 0.0, pad_in: bool = False, pad_out: bool = False):
+        """``pad_in`` / ``pad_out`` store the weight with Cin / Cout rounded up to a multiple of 8 (zero filled), for
+        producers / consumers that keep channel-padded activations.  Padded entries see zero activations and zero
+        gradients, so they stay exactly zero; checkpoints hold the logical [cout, k, k, cin] block only."""
         super().__init__()
         self.cin, self.cout, self.k, self.stride, self.rate, self.padding = cin, cout, k, stride, rate, padding
         self.scope = scope
         self.weight_decay = weight_decay  # recorded like slim's regulariser; see ParamStore for its use
-        self.weight = nn.Parameter(torch.empty(cout, k, k, cin))
+        self.cin_p = pad8(cin) if pad_in else cin
+        self.cout_p = pad8(cout) if pad_out else cout
+        w = torch.empty(cout, k, k, cin)
         if init_std is None:
-            R.variance_scaling_(self.weight.data)
+            R.variance_scaling_(w)
         else:
-            R.truncated_normal_(self.weight.data, init_std)
-        self.bias = nn.Parameter(torch.zeros(cout)) if use_bias else None
+            R.truncated_normal_(w, init_std)
+        full = torch.zeros(self.cout_p, k, k, self.cin_p)
+        full[:cout, :, :, :cin] = w
+        self.weight = nn.Parameter(full)
+        self.bias = nn.Parameter(torch.zeros(self.cout_p)) if use_bias else None
 
     def forward(self, x: torch.Tensor, want_stats: bool = False, want_tap: bool = False):
         return TF.conv2d(x, self.weight, self.bias, self.stride, self.rate, self.padding, want_stats, want_tap)
 
     def tf_variables(self):
-        d = {f"{self.scope}/weights": (self.weight, "conv")}
+        d = {f"{self.scope}/weights": (self.weight, "conv", (self.cout, self.k, self.k, self.cin))}
         if self.bias is not None:
-            d[f"{self.scope}/biases"] = (self.bias, "plain")
+            d[f"{self.scope}/biases"] = (self.bias, "plain", (self.cout,))
         return d
 
 
@@ -85,13 +113,16 @@ class BatchNorm(TFModule):
     """slim.batch_norm (fused): beta, optional gamma, moving_mean, moving_variance; optional fused
     residual add and ReLU.  ``decay`` is TF's moving-average decay (reference default 0.99)."""
 
-    def __init__(self, c: int, decay: float = 0.99, eps: float = 1e-3, scale: bool = True, scope: str = "BatchNorm"):
+    def __init__(self, c: int, decay: float = 0.99, eps: float = 1e-3, scale: bool = True, scope: str = "BatchNorm",
+                 pad: bool = False):
         super().__init__()
         self.c, self.decay, self.eps, self.scope = c, decay, eps, scope
-        self.beta = nn.Parameter(torch.zeros(c))
-        self.gamma = nn.Parameter(torch.ones(c)) if scale else None
-        self.register_buffer("moving_mean", torch.zeros(c))
-        self.register_buffer("moving_variance", torch.ones(c))
+        cp = pad8(c) if pad else c  # padded channels carry zeros in, zeros out (beta 0) and zero gradients
+        self.c_p = cp
+        self.beta = nn.Parameter(torch.zeros(cp))
+        self.gamma = nn.Parameter(torch.ones(cp)) if scale else None
+        self.register_buffer("moving_mean", torch.zeros(cp))
+        self.register_buffer("moving_variance", torch.ones(cp))
 
     def forward(self, x: torch.Tensor, relu: bool = False, residual: Optional[torch.Tensor] = None,
                 stats: Optional[torch.Tensor] = None) -> torch.Tensor:
@@ -99,11 +130,11 @@ class BatchNorm(TFModule):
                              eps=self.eps, training=self.training, relu=relu, residual=residual, stats=stats)
 
     def tf_variables(self):
-        d = {f"{self.scope}/beta": (self.beta, "plain"),
-             f"{self.scope}/moving_mean": (self.moving_mean, "plain"),
-             f"{self.scope}/moving_variance": (self.moving_variance, "plain")}
+        d = {f"{self.scope}/beta": (self.beta, "plain", (self.c,)),
+             f"{self.scope}/moving_mean": (self.moving_mean, "plain", (self.c,)),
+             f"{self.scope}/moving_variance": (self.moving_variance, "plain", (self.c,))}
         if self.gamma is not None:
-            d[f"{self.scope}/gamma"] = (self.gamma, "plain")
+            d[f"{self.scope}/gamma"] = (self.gamma, "plain", (self.c,))
         return d
 
 
@@ -118,12 +149,12 @@ class ConvBNAct(TFModule):
     """slim.conv2d under the resnet arg scope: conv (no bias) -> BatchNorm -> ReLU."""
 
     def __init__(self, cin, cout, k, stride=1, rate=1, padding="SAME", scope="Conv", bn: Optional[BNConfig] = None,
-                 relu: bool = True, init_std: Optional[float] = None):
+                 relu: bool = True, init_std: Optional[float] = None, pad_in: bool = False, pad_out: bool = False):
         super().__init__()
         bn = bn or BNConfig()
         self.conv = Conv2d(cin, cout, k, stride, rate, padding, use_bias=False, scope=scope, init_std=init_std,
-                           weight_decay=bn.weight_decay)
-        self.bn = BatchNorm(cout, bn.decay, bn.eps, bn.scale, scope=f"{scope}/BatchNorm")
+                           weight_decay=bn.weight_decay, pad_in=pad_in, pad_out=pad_out)
+        self.bn = BatchNorm(cout, bn.decay, bn.eps, bn.scale, scope=f"{scope}/BatchNorm", pad=pad_out)
         self.relu = relu
 
     def forward(self, x, residual: Optional[torch.Tensor] = None, want_tap: bool = False):

@@ -14,8 +14,8 @@ def seg():
 
 
 def test_reference_manifest_counts(seg):
-    train = [(n, t) for n, t, k in iter_tf_variables(seg) if isinstance(t, torch.nn.Parameter)]
-    stats = [(n, t) for n, t, k in iter_tf_variables(seg) if not isinstance(t, torch.nn.Parameter)]
+    train = [(n, t) for n, t, k in iter_tf_variables(seg) if t.requires_grad]
+    stats = [(n, t) for n, t, k in iter_tf_variables(seg) if not t.requires_grad]
     assert len(train) == 208
     assert sum(t.numel() for _, t in train) == 41_814_025
     assert len(stats) == 118
