@@ -169,6 +169,7 @@ def main():
     ap.add_argument("--comm", default=None, choices=[None, "p2p", "nccl"], help="gradient path (default p2p)")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-overlap", action="store_true")
+    ap.add_argument("--no-async-wgrad", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm(args)
@@ -206,7 +207,8 @@ def main():
     opt_kw = dict(kind=cfg["opt"], lr=0.1 if cfg["opt"] == "sgdm" else 1e-3, momentum=0.9,
                   weight_decay=1e-4 if cfg["opt"] == "sgdm" else 0.0,
                   decay_steps=0.0 if cfg["opt"] == "sgdm" else 10000.0, decay_rate=0.5,
-                  comm=("nccl" if proxy else args.comm), overlap=not args.no_overlap)
+                  comm=("nccl" if proxy else args.comm), overlap=not args.no_overlap,
+                  async_wgrad=not args.no_async_wgrad)
     trainer = TowerTrainer(model, group, batch=batch, input_hwc=(h, w, c), label_shape=label_shape,
                            label_dtype=label_dtype, loss_fn=loss_fn, use_graph=not args.no_graph,
                            mean=[0.485, 0.456, 0.406][:c] if c == 3 else [0.47194585] * c,

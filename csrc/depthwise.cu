@@ -1,0 +1,741 @@
+// 3x3 depthwise convolution for NHWC bf16 (forward, data gradient, weight gradient), memory-roofline oriented.
+//
+// reference call sites: core/xception.py:102-110 (every Xception separable conv, stride 1/2, rate from the atrous
+// bookkeeping) and core/layers.py:34-42 (ASPP, rates 2/4/8, bias + ReLU).  Depthwise conv has no reuse across
+// channels, so tensor cores are pointless; the job is to touch each activation byte once and keep the instruction
+// count per element under the ~20 lane-instructions that the HBM roofline allows:
+//   * a thread owns 4 channels for all of its pixels: the 9x4 filter taps (and bias) sit in registers
+//   * it produces strips of 4 horizontally adjacent outputs, so for stride 1 / rate 1 each input row is loaded
+//     as 6 vectors that feed 12 tap uses (instead of 12 loads)
+//   * the Xception pre-activation ReLU is applied on load (`relu_in`), the ASPP ReLU on store (`relu_out`)
+//   * weight gradient: same strip walk, 36+4 accumulators per thread, block reduction in shared memory, one fp32
+//     atomic per (tap, channel) per CTA.
+#include "tdl_common.cuh"
+
+namespace tdl {
+namespace dw {
+
+constexpr int kThreads = 256;
+constexpr int kStrip = 4;
+
+struct Shape {
+  int N, H, W, C, P, Q, stride, dil, pad_h, pad_w;
+};
+
+__device__ __forceinline__ void ld4(const bf16* p, float* f, bool relu) {
+  const uint2 raw = *reinterpret_cast<const uint2*>(p);
+  const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.x));
+  const float2 b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&raw.y));
+  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y;
+  if (relu) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) f[j] = fmaxf(f[j], 0.f);
+  }
+}
+__device__ __forceinline__ void zero4(float* f) { f[0] = f[1] = f[2] = f[3] = 0.f; }
+__device__ __forceinline__ void st4(bf16* p, const float* f) {
+  const __nv_bfloat162 a = __floats2bfloat162_rn(f[0], f[1]), b = __floats2bfloat162_rn(f[2], f[3]);
+  uint2 raw;
+  raw.x = *reinterpret_cast<const uint32_t*>(&a);
+  raw.y = *reinterpret_cast<const uint32_t*>(&b);
+  *reinterpret_cast<uint2*>(p) = raw;
+}
+
+// kDense: stride 1 and dilation 1 (input columns of neighbouring outputs overlap -> 6 loads per row per strip)
+// out = relu_out?( bias + sum_taps w[tap] * relu_in?(x) ), optionally zeroed where mask <= 0 (data-gradient use)
+template <bool kDense>
+__global__ void __launch_bounds__(kThreads)
+depthwise3x3_kernel(const bf16* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
+                    const bf16* __restrict__ mask, bf16* __restrict__ y, Shape s, int tx, int ty, int relu_in,
+                    int relu_out) {
+  const int cx = threadIdx.x % tx, sy = threadIdx.x / tx;
+  const int c4 = s.C / 4;
+  const int cv = blockIdx.y * tx + cx;
+  if (cv >= c4) return;
+  float wt[9][4], b4[4];
+#pragma unroll
+  for (int t = 0; t < 9; ++t) {
+    const float4 v = *reinterpret_cast<const float4*>(w + (size_t)t * s.C + cv * 4);
+    wt[t][0] = v.x; wt[t][1] = v.y; wt[t][2] = v.z; wt[t][3] = v.w;
+  }
+  if (bias) {
+    const float4 v = *reinterpret_cast<const float4*>(bias + cv * 4);
+    b4[0] = v.x; b4[1] = v.y; b4[2] = v.z; b4[3] = v.w;
+  } else {
+    zero4(b4);
+  }
+  const int qs = (s.Q + kStrip - 1) / kStrip;
+  const int64_t strips = (int64_t)s.N * s.P * qs;
+  for (int64_t st = (int64_t)blockIdx.x * ty + sy; st < strips; st += (int64_t)gridDim.x * ty) {
+    const int q0 = (int)(st % qs) * kStrip;
+    const int p = (int)((st / qs) % s.P);
+    const int n = (int)(st / ((int64_t)qs * s.P));
+    float acc[kStrip][4];
+#pragma unroll
+    for (int j = 0; j < kStrip; ++j) {
+#pragma unroll
+      for (int c = 0; c < 4; ++c) acc[j][c] = b4[c];
+    }
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      const int h = p * s.stride + r * s.dil - s.pad_h;
+      if (h < 0 || h >= s.H) continue;
+      const bf16* row = x + (((int64_t)n * s.H + h) * s.W) * s.C + cv * 4;
+      if (kDense) {
+        float v[kStrip + 2][4];
+#pragma unroll
+        for (int c = 0; c < kStrip + 2; ++c) {
+          const int col = q0 + c - s.pad_w;
+          if (col >= 0 && col < s.W) ld4(row + (int64_t)col * s.C, v[c], relu_in);
+          else zero4(v[c]);
+        }
+#pragma unroll
+        for (int j = 0; j < kStrip; ++j)
+#pragma unroll
+          for (int t = 0; t < 3; ++t)
+#pragma unroll
+            for (int c = 0; c < 4; ++c) acc[j][c] = fmaf(v[j + t][c], wt[r * 3 + t][c], acc[j][c]);
+      } else {
+#pragma unroll
+        for (int j = 0; j < kStrip; ++j)
+#pragma unroll
+          for (int t = 0; t < 3; ++t) {
+            const int col = (q0 + j) * s.stride + t * s.dil - s.pad_w;
+            if (col >= 0 && col < s.W) {
+              float v[4];
+              ld4(row + (int64_t)col * s.C, v, relu_in);
+#pragma unroll
+              for (int c = 0; c < 4; ++c) acc[j][c] = fmaf(v[c], wt[r * 3 + t][c], acc[j][c]);
+            }
+          }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < kStrip; ++j) {
+      const int q = q0 + j;
+      if (q >= s.Q) break;
+      const int64_t o = ((((int64_t)n * s.P + p) * s.Q + q) * s.C) + cv * 4;
+      if (relu_out) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) acc[j][c] = fmaxf(acc[j][c], 0.f);
+      }
+      if (mask) {
+        float m[4];
+        ld4(mask + o, m, false);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) acc[j][c] = m[c] > 0.f ? acc[j][c] : 0.f;
+      }
+      st4(y + o, acc[j]);
+    }
+  }
+}
+
+// dw[tap][c] += sum_pixels dyv * relu_in?(x shifted);  dbias[c] += sum dyv;  dyv = dy * (ymask > 0 if given)
+template <bool kDense>
+__global__ void __launch_bounds__(kThreads)
+depthwise3x3_wgrad_kernel(const bf16* __restrict__ x, const bf16* __restrict__ dy, const bf16* __restrict__ ymask,
+                          float* __restrict__ dw, float* __restrict__ dbias, Shape s, int tx, int ty, int relu_in) {
+  extern __shared__ float sm[];  // [ty][tx][4]
+  const int cx = threadIdx.x % tx, sy = threadIdx.x / tx;
+  const int c4 = s.C / 4;
+  const int cv = blockIdx.y * tx + cx;
+  float acc[9][4], accb[4];
+#pragma unroll
+  for (int t = 0; t < 9; ++t) zero4(acc[t]);
+  zero4(accb);
+  if (cv < c4) {
+    const int qs = (s.Q + kStrip - 1) / kStrip;
+    const int64_t strips = (int64_t)s.N * s.P * qs;
+    for (int64_t st = (int64_t)blockIdx.x * ty + sy; st < strips; st += (int64_t)gridDim.x * ty) {
+      const int q0 = (int)(st % qs) * kStrip;
+      const int p = (int)((st / qs) % s.P);
+      const int n = (int)(st / ((int64_t)qs * s.P));
+      float g[kStrip][4];
+#pragma unroll
+      for (int j = 0; j < kStrip; ++j) {
+        const int q = q0 + j;
+        if (q < s.Q) {
+          const int64_t o = ((((int64_t)n * s.P + p) * s.Q + q) * s.C) + cv * 4;
+          ld4(dy + o, g[j], false);
+          if (ymask) {
+            float m[4];
+            ld4(ymask + o, m, false);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) g[j][c] = m[c] > 0.f ? g[j][c] : 0.f;
+          }
+#pragma unroll
+          for (int c = 0; c < 4; ++c) accb[c] += g[j][c];
+        } else {
+          zero4(g[j]);
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+        const int h = p * s.stride + r * s.dil - s.pad_h;
+        if (h < 0 || h >= s.H) continue;
+        const bf16* row = x + (((int64_t)n * s.H + h) * s.W) * s.C + cv * 4;
+        if (kDense) {
+          float v[kStrip + 2][4];
+#pragma unroll
+          for (int c = 0; c < kStrip + 2; ++c) {
+            const int col = q0 + c - s.pad_w;
+            if (col >= 0 && col < s.W) ld4(row + (int64_t)col * s.C, v[c], relu_in);
+            else zero4(v[c]);
+          }
+#pragma unroll
+          for (int j = 0; j < kStrip; ++j)
+#pragma unroll
+            for (int t = 0; t < 3; ++t)
+#pragma unroll
+              for (int c = 0; c < 4; ++c) acc[r * 3 + t][c] = fmaf(g[j][c], v[j + t][c], acc[r * 3 + t][c]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < kStrip; ++j)
+#pragma unroll
+            for (int t = 0; t < 3; ++t) {
+              const int col = (q0 + j) * s.stride + t * s.dil - s.pad_w;
+              if (col >= 0 && col < s.W) {
+                float v[4];
+                ld4(row + (int64_t)col * s.C, v, relu_in);
+#pragma unroll
+                for (int c = 0; c < 4; ++c) acc[r * 3 + t][c] = fmaf(g[j][c], v[c], acc[r * 3 + t][c]);
+              }
+            }
+        }
+      }
+    }
+  }
+  // reduce the ty strip-threads of every channel vector through shared memory, one statistic at a time
+  for (int t = 0; t <= 9; ++t) {
+    __syncthreads();
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      float v = accb[c];
+#pragma unroll
+      for (int u = 0; u < 9; ++u)
+        if (u == t) v = acc[u][c];
+      sm[((size_t)sy * tx + cx) * 4 + c] = v;
+    }
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < tx * 4; idx += kThreads) {
+      const int col = idx >> 2, c = idx & 3;
+      const int cvv = blockIdx.y * tx + col;
+      if (cvv >= c4) continue;
+      float a = 0.f;
+      for (int u = 0; u < ty; ++u) a += sm[((size_t)u * tx + col) * 4 + c];
+      if (t < 9) atomicAdd(dw + (size_t)t * s.C + cvv * 4 + c, a);
+      else if (dbias) atomicAdd(dbias + cvv * 4 + c, a);
+    }
+  }
+}
+
+struct Launch {
+  int tx, ty, gx, gy;
+};
+static Launch plan(const Shape& s, int blocks_per_sm) {
+  Launch l;
+  const int c4 = s.C / 4;
+  l.tx = 1;
+  while (l.tx < 64 && l.tx < c4) l.tx <<= 1;
+  l.ty = kThreads / l.tx;
+  l.gy = (int)cdiv(c4, l.tx);
+  const int64_t strips = (int64_t)s.N * s.P * cdiv(s.Q, kStrip);
+  int64_t want = cdiv(strips, (int64_t)l.ty * 2);
+  int64_t cap = (int64_t)num_sms() * blocks_per_sm / l.gy;
+  if (cap < 1) cap = 1;
+  if (want > cap) want = cap;
+  if (want < 1) want = 1;
+  l.gx = (int)want;
+  return l;
+}
+
+}  // namespace dw
+}  // namespace tdl
+
+using namespace tdl;
+using namespace tdl::dw;
+
+// y = relu_out?(bias + depthwise3x3(relu_in?(x)));  w is [9, C] fp32 (tap-major), C % 4 == 0.
+// `mask` (same shape as y, may be NULL) zeroes outputs where mask <= 0: used when this kernel computes a data
+// gradient (x := dy, w := flipped taps, mask := the forward input of a pre-activation ReLU).
+TDL_API int tdl_depthwise3x3_fwd(const void* x, const float* w, const float* bias, const void* mask, void* y, int N,
+                                 int H, int W, int C, int P, int Q, int stride, int dil, int pad_h, int pad_w,
+                                 int relu_in, int relu_out, void* stream) {
+  TDL_REQUIRE(C % 4 == 0, "C must be a multiple of 4");
+  if ((int64_t)N * P * Q == 0) return 0;
+  Shape s = {N, H, W, C, P, Q, stride, dil, pad_h, pad_w};
+  Launch l = plan(s, 8);
+  dim3 grid(l.gx, l.gy);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (stride == 1 && dil == 1)
+    depthwise3x3_kernel<true><<<grid, kThreads, 0, st>>>((const bf16*)x, w, bias, (const bf16*)mask, (bf16*)y, s, l.tx,
+                                                         l.ty, relu_in, relu_out);
+  else
+    depthwise3x3_kernel<false><<<grid, kThreads, 0, st>>>((const bf16*)x, w, bias, (const bf16*)mask, (bf16*)y, s, l.tx,
+                                                          l.ty, relu_in, relu_out);
+  TDL_LAUNCH_OK("depthwise3x3_kernel");
+  return 0;
+}
+
+// dw [9, C] and dbias [C] (may be NULL) are accumulated into (caller zeroes them); ymask (may be NULL) masks dy where
+// the forward output was <= 0 (fused output ReLU).
+TDL_API int tdl_depthwise3x3_wgrad(const void* x, const void* dy, const void* ymask, float* dw, float* dbias, int N,
+                                   int H, int W, int C, int P, int Q, int stride, int dil, int pad_h, int pad_w,
+                                   int relu_in, void* stream) {
+  TDL_REQUIRE(C % 4 == 0, "C must be a multiple of 4");
+  if ((int64_t)N * P * Q == 0) return 0;
+  Shape s = {N, H, W, C, P, Q, stride, dil, pad_h, pad_w};
+  Launch l = plan(s, 4);
+  dim3 grid(l.gx, l.gy);
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t smem = (size_t)kThreads * 4 * sizeof(float);
+  if (stride == 1 && dil == 1)
+    depthwise3x3_wgrad_kernel<true><<<grid, kThreads, smem, st>>>((const bf16*)x, (const bf16*)dy, (const bf16*)ymask,
+                                                                  dw, dbias, s, l.tx, l.ty, relu_in);
+  else
+    depthwise3x3_wgrad_kernel<false><<<grid, kThreads, smem, st>>>((const bf16*)x, (const bf16*)dy, (const bf16*)ymask,
+                                                                   dw, dbias, s, l.tx, l.ty, relu_in);
+  TDL_LAUNCH_OK("depthwise3x3_wgrad_kernel");
+  return 0;
+}
+
+// ================================================================================================================
+// TMA-tiled variant (stride 1/2, dilation 1/2): the haloed input patch of a (TH x TW) output tile and 64 channels is
+// fetched by ONE 4-D TMA box into 128B-swizzled shared memory (out-of-bounds zero fill = the padding), double
+// buffered; 256 threads then compute from shared memory -- 8 channels x a strip of 4 outputs per thread, the 9x8
+// filter taps of the thread's channels in registers.  All global traffic is TMA loads + 16-byte stores.
+// ================================================================================================================
+#include <cudaTypedefs.h>
+
+namespace tdl {
+namespace dwt {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn) return fn;
+  void* p = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+      q != cudaDriverEntryPointSuccess)
+    return nullptr;
+  fn = reinterpret_cast<EncodeTiledFn>(p);
+  return fn;
+}
+static int encode_nhwc(CUtensorMap* m, const void* base, int N, int H, int W, int C, int bw, int bh) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return tdl::fail(-3, "%s%s", "cuTensorMapEncodeTiled entry point unavailable", "");
+  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t str[3] = {(cuuint64_t)C * 2, (cuuint64_t)C * W * 2, (cuuint64_t)C * W * H * 2};
+  cuuint32_t box[4] = {64, (cuuint32_t)bw, (cuuint32_t)bh, 1};
+  cuuint32_t es[4] = {1, 1, 1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, str, box, es,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return tdl::fail(-4, "%s%s", "cuTensorMapEncodeTiled failed (depthwise)", "");
+  return 0;
+}
+
+// Output tile (TH x TW, TW a multiple of 4, TH*TW <= 128 so that 32 thread groups x 4-wide strips cover it): pick the
+// shape that needs the fewest tiles for a P x Q map -- 19x19 is 4 tiles of 5x20 instead of 6 tiles of 8x16.
+static void choose_tile(int P, int Q, int stride, int* th, int* tw) {
+  const int max_out = stride == 1 ? 128 : 64;  // the strided input box is ~4x larger per output
+  long best = -1;
+  int bh = 8, bw = 16;
+  for (int w = 8; w <= 32; w += 4) {
+    int h = max_out / w;
+    if (h > P) h = P;
+    if (h < 1) continue;
+    // a shorter tile that still needs the same number of tile rows wastes fewer threads
+    const int rows = (int)tdl::cdiv(P, h);
+    h = (int)tdl::cdiv(P, rows);
+    const long tiles = (long)rows * tdl::cdiv(Q, w);
+    const long cost = tiles * 1000 + (h * w);  // fewest tiles first, then the smaller box
+    if (best < 0 || cost < best) {
+      best = cost;
+      bh = h;
+      bw = w;
+    }
+  }
+  *th = bh;
+  *tw = bw;
+}
+
+struct TShape {
+  int N, H, W, C, P, Q, stride, dil, pad_h, pad_w;
+  int TH, TW, BH, BW;          // output tile, input box
+  int tiles_h, tiles_w;
+};
+
+constexpr int kT = 512;  // 16 warps: 16 channel-quads x 32 strip groups
+
+// 4 channels (8 bytes) of pixel-row `lrow` of a 128B-swizzled [rows][64 ch] tile; cq = channel quad 0..15
+__device__ __forceinline__ void lds4(const uint8_t* tile, int lrow, int cq, float* f, bool relu) {
+  const uint2 raw = *reinterpret_cast<const uint2*>(tile + lrow * 128 + (((cq >> 1) ^ (lrow & 7)) << 4) + ((cq & 1) << 3));
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const float2 v = __bfloat1622float2(h[i]);
+    f[2 * i] = relu ? fmaxf(v.x, 0.f) : v.x;
+    f[2 * i + 1] = relu ? fmaxf(v.y, 0.f) : v.y;
+  }
+}
+
+constexpr int kMaxStages = 4;
+
+template <int STRIDE, int DIL>
+__global__ void __launch_bounds__(kT)
+depthwise3x3_tma_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_mask,
+                        const float* __restrict__ w, const float* __restrict__ bias, int has_mask,
+                        bf16* __restrict__ y, const TShape s, int stages, int relu_in, int relu_out) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int x_bytes = ((s.BH * s.BW * 128 + 1023) / 1024) * 1024;
+  const int m_bytes = has_mask ? ((s.TH * s.TW * 128 + 1023) / 1024) * 1024 : 0;
+  const int stage_bytes = x_bytes + m_bytes;
+  __shared__ uint64_t full[kMaxStages];
+  const int tid = threadIdx.x;
+  const int cvec = tid & 15, grp = tid >> 4;
+  const int c0 = blockIdx.y * 64;
+  const int ch = c0 + cvec * 4;
+  const bool ch_ok = ch < s.C;
+  if (tid == 0) {
+    ptx::prefetch_tmap(&tm_x);
+    for (int i = 0; i < kMaxStages; ++i) ptx::mbar_init(&full[i], 1);
+    ptx::fence_mbar_init();
+  }
+  __syncthreads();
+  float wt[9][4], b8[4];
+#pragma unroll
+  for (int t = 0; t < 9; ++t)
+#pragma unroll
+    for (int c = 0; c < 4; ++c) wt[t][c] = ch_ok ? w[(size_t)t * s.C + ch + c] : 0.f;
+#pragma unroll
+  for (int c = 0; c < 4; ++c) b8[c] = (bias && ch_ok) ? bias[ch + c] : 0.f;
+
+  const int tiles = s.N * s.tiles_h * s.tiles_w;
+  const uint32_t tx_bytes = (uint32_t)(s.BH * s.BW + (has_mask ? s.TH * s.TW : 0)) * 128u;
+  auto issue = [&](int tile, int stage) {
+    const int tw_i = tile % s.tiles_w;
+    const int th_i = (tile / s.tiles_w) % s.tiles_h;
+    const int n = tile / (s.tiles_w * s.tiles_h);
+    ptx::mbar_expect_tx(&full[stage], tx_bytes);
+    ptx::tma_load_4d(smem + stage * stage_bytes, &tm_x, &full[stage], c0, tw_i * s.TW * STRIDE - s.pad_w,
+                     th_i * s.TH * STRIDE - s.pad_h, n);
+    if (has_mask)
+      ptx::tma_load_4d(smem + stage * stage_bytes + x_bytes, &tm_mask, &full[stage], c0, tw_i * s.TW, th_i * s.TH, n);
+  };
+  if (tid == 0)
+    for (int i = 0; i < stages - 1; ++i) {
+      const int t0 = blockIdx.x + i * gridDim.x;
+      if (t0 < tiles) issue(t0, i);
+    }
+  const int strips_w = s.TW / 4;
+  const int strips = s.TH * strips_w;
+  // everything that depends only on the thread's strip is loop invariant: tile-local row indices of the taps
+  const int ph = grp / strips_w, pw0 = (grp % strips_w) * 4;
+  const bool active = grp < strips && ch_ok;
+  int it = 0, stage = 0;
+  uint32_t parity = 0;
+  for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
+    const int ahead = tile + (stages - 1) * gridDim.x;
+    if (tid == 0 && ahead < tiles) issue(ahead, stage == 0 ? stages - 1 : stage - 1);  // consumed in iteration it-1
+    ptx::mbar_wait(&full[stage], parity);
+    const uint8_t* in = smem + stage * stage_bytes;
+    const uint8_t* min_ = in + x_bytes;
+    if (++stage == stages) {
+      stage = 0;
+      parity ^= 1;
+    }
+    if (active) {
+      const int tw_i = tile % s.tiles_w;
+      const int th_i = (tile / s.tiles_w) % s.tiles_h;
+      const int n = tile / (s.tiles_w * s.tiles_h);
+      float acc[4][4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) acc[j][c] = b8[c];
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+        const int lrow0 = (ph * STRIDE + r * DIL) * s.BW + pw0 * STRIDE;
+        if (STRIDE == 1 && DIL == 1) {
+          float v[6][4];
+#pragma unroll
+          for (int c = 0; c < 6; ++c) lds4(in, lrow0 + c, cvec, v[c], relu_in);
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int t = 0; t < 3; ++t)
+#pragma unroll
+              for (int c = 0; c < 4; ++c) acc[j][c] = fmaf(v[j + t][c], wt[r * 3 + t][c], acc[j][c]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int t = 0; t < 3; ++t) {
+              float v[4];
+              lds4(in, lrow0 + j * STRIDE + t * DIL, cvec, v, relu_in);
+#pragma unroll
+              for (int c = 0; c < 4; ++c) acc[j][c] = fmaf(v[c], wt[r * 3 + t][c], acc[j][c]);
+            }
+        }
+      }
+      const int p = th_i * s.TH + ph;
+      if (p < s.P) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int q = tw_i * s.TW + pw0 + j;
+          if (q >= s.Q) break;
+          const int64_t o = ((((int64_t)n * s.P + p) * s.Q + q) * s.C) + ch;
+          if (relu_out) {
+#pragma unroll
+            for (int c = 0; c < 4; ++c) acc[j][c] = fmaxf(acc[j][c], 0.f);
+          }
+          if (has_mask) {
+            float m[4];
+            lds4(min_, ph * s.TW + pw0 + j, cvec, m, false);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) acc[j][c] = m[c] > 0.f ? acc[j][c] : 0.f;
+          }
+          tdl::dw::st4(y + o, acc[j]);
+        }
+      }
+    }
+    __syncthreads();  // everyone is done reading this stage before it is refilled
+  }
+}
+
+// Weight gradient on the same tiling: the haloed x patch and the dy tile arrive by TMA (zero fill outside the
+// maps, so no bounds logic), every thread keeps 9x8 + 8 accumulators for its 8 channels across all of its CTA's
+// tiles, and one shared-memory reduction + fp32 atomics per CTA finish the job.
+template <int STRIDE, int DIL>
+__global__ void __launch_bounds__(kT)
+depthwise3x3_tma_wgrad_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_dy,
+                              float* __restrict__ dw, float* __restrict__ dbias, const TShape s, int stages,
+                              int relu_in) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int x_bytes = ((s.BH * s.BW * 128 + 1023) / 1024) * 1024;
+  const int g_bytes = ((s.TH * s.TW * 128 + 1023) / 1024) * 1024;
+  const int stage_bytes = x_bytes + g_bytes;
+  __shared__ uint64_t full[kMaxStages];
+  const int tid = threadIdx.x;
+  const int cvec = tid & 15, grp = tid >> 4;
+  const int c0 = blockIdx.y * 64;
+  const int ch = c0 + cvec * 4;
+  const bool ch_ok = ch < s.C;
+  if (tid == 0) {
+    ptx::prefetch_tmap(&tm_x);
+    ptx::prefetch_tmap(&tm_dy);
+    for (int i = 0; i < kMaxStages; ++i) ptx::mbar_init(&full[i], 1);
+    ptx::fence_mbar_init();
+  }
+  __syncthreads();
+  float acc[9][4], accb[4];
+#pragma unroll
+  for (int t = 0; t < 9; ++t)
+#pragma unroll
+    for (int c = 0; c < 4; ++c) acc[t][c] = 0.f;
+#pragma unroll
+  for (int c = 0; c < 4; ++c) accb[c] = 0.f;
+
+  const int tiles = s.N * s.tiles_h * s.tiles_w;
+  const uint32_t tx_bytes = (uint32_t)(s.BH * s.BW + s.TH * s.TW) * 128u;
+  auto issue = [&](int tile, int stage) {
+    const int tw_i = tile % s.tiles_w;
+    const int th_i = (tile / s.tiles_w) % s.tiles_h;
+    const int n = tile / (s.tiles_w * s.tiles_h);
+    ptx::mbar_expect_tx(&full[stage], tx_bytes);
+    ptx::tma_load_4d(smem + stage * stage_bytes, &tm_x, &full[stage], c0, tw_i * s.TW * STRIDE - s.pad_w,
+                     th_i * s.TH * STRIDE - s.pad_h, n);
+    ptx::tma_load_4d(smem + stage * stage_bytes + x_bytes, &tm_dy, &full[stage], c0, tw_i * s.TW, th_i * s.TH, n);
+  };
+  int it = 0;
+  if (tid == 0)
+    for (int i = 0; i < stages - 1; ++i) {
+      const int t0 = blockIdx.x + i * gridDim.x;
+      if (t0 < tiles) issue(t0, i);
+    }
+  const int strips_w = s.TW / 4;
+  const int strips = s.TH * strips_w;
+  for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
+    const int stage = it % stages;
+    const int ahead = tile + (stages - 1) * gridDim.x;
+    if (tid == 0 && ahead < tiles) issue(ahead, (it + stages - 1) % stages);
+    ptx::mbar_wait(&full[stage], (uint32_t)((it / stages) & 1));
+    const uint8_t* in = smem + stage * stage_bytes;
+    const uint8_t* gin = in + x_bytes;
+    if (grp < strips && ch_ok) {
+      const int ph = grp / strips_w, pw0 = (grp % strips_w) * 4;
+      float g[4][4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        lds4(gin, ph * s.TW + pw0 + j, cvec, g[j], false);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) accb[c] += g[j][c];
+      }
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+        const int lrow0 = (ph * STRIDE + r * DIL) * s.BW + pw0 * STRIDE;
+        if (STRIDE == 1 && DIL == 1) {
+          float v[6][4];
+#pragma unroll
+          for (int c = 0; c < 6; ++c) lds4(in, lrow0 + c, cvec, v[c], relu_in);
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int t = 0; t < 3; ++t)
+#pragma unroll
+              for (int c = 0; c < 4; ++c) acc[r * 3 + t][c] = fmaf(g[j][c], v[j + t][c], acc[r * 3 + t][c]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int t = 0; t < 3; ++t) {
+              float v[4];
+              lds4(in, lrow0 + j * STRIDE + t * DIL, cvec, v, relu_in);
+#pragma unroll
+              for (int c = 0; c < 4; ++c) acc[r * 3 + t][c] = fmaf(g[j][c], v[c], acc[r * 3 + t][c]);
+            }
+        }
+      }
+    }
+    __syncthreads();
+  }
+  // CTA reduction: for each of the 10 statistics, 32 groups x 64 channels -> 64 sums -> one atomic each
+  float* red = reinterpret_cast<float*>(smem);  // 512 x 4 floats = 8 KB (the stages are idle now)
+  for (int t = 0; t <= 9; ++t) {
+    __syncthreads();
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      float v = accb[c];
+#pragma unroll
+      for (int u = 0; u < 9; ++u)
+        if (u == t) v = acc[u][c];
+      red[(grp * 16 + cvec) * 4 + c] = v;
+    }
+    __syncthreads();
+    if (tid < 64) {
+      const int cc = c0 + tid;  // channel
+      if (cc < s.C) {
+        float a = 0.f;
+        for (int gidx = 0; gidx < 32; ++gidx) a += red[gidx * 64 + tid];
+        if (t < 9) atomicAdd(dw + (size_t)t * s.C + cc, a);
+        else if (dbias) atomicAdd(dbias + cc, a);
+      }
+    }
+  }
+}
+
+}  // namespace dwt
+}  // namespace tdl
+
+// dw [9, C] / dbias [C] accumulated into; TMA-tiled (no output-ReLU mask on this path).
+TDL_API int tdl_depthwise3x3_tma_wgrad(const void* x, const void* dy, float* dw, float* dbias, int N, int H, int W,
+                                       int C, int P, int Q, int stride, int dil, int pad_h, int pad_w, int relu_in,
+                                       void* stream) {
+  using namespace tdl::dwt;
+  TDL_REQUIRE(C % 8 == 0, "C must be a multiple of 8");
+  TDL_REQUIRE((stride == 1 || stride == 2) && (dil == 1 || dil == 2) && !(stride == 2 && dil == 2),
+              "TMA depthwise supports stride 1/2 with dilation 1, or stride 1 with dilation 2");
+  if ((int64_t)N * P * Q == 0) return 0;
+  TShape s;
+  s.N = N; s.H = H; s.W = W; s.C = C; s.P = P; s.Q = Q; s.stride = stride; s.dil = dil; s.pad_h = pad_h; s.pad_w = pad_w;
+  choose_tile(P, Q, stride, &s.TH, &s.TW);
+  s.BW = (s.TW - 1) * stride + 2 * dil + 1;
+  s.BH = (s.TH - 1) * stride + 2 * dil + 1;
+  s.tiles_h = (int)tdl::cdiv(P, s.TH);
+  s.tiles_w = (int)tdl::cdiv(Q, s.TW);
+  CUtensorMap tmx, tmg;
+  int rc = encode_nhwc(&tmx, x, N, H, W, C, s.BW, s.BH);
+  if (rc) return rc;
+  rc = encode_nhwc(&tmg, dy, N, P, Q, C, s.TW, s.TH);
+  if (rc) return rc;
+  const int x_bytes = ((s.BH * s.BW * 128 + 1023) / 1024) * 1024;
+  const int g_bytes = ((s.TH * s.TW * 128 + 1023) / 1024) * 1024;
+  int stages = (150 * 1024) / (x_bytes + g_bytes);
+  if (stages > kMaxStages) stages = kMaxStages;
+  if (stages < 2) stages = 2;
+  int smem = stages * (x_bytes + g_bytes) + 1024;
+  if (smem < 8192 + 1024) smem = 8192 + 1024;
+  const int tiles = N * s.tiles_h * s.tiles_w;
+  const int gy = (int)tdl::cdiv(C, 64);
+  int gx = (tdl::num_sms() * 2) / gy;
+  if (gx < 1) gx = 1;
+  if (gx > tiles) gx = tiles;
+  dim3 grid(gx, gy);
+  cudaStream_t st = (cudaStream_t)stream;
+#define TDL_DWW_LAUNCH(S, D)                                                                                         \
+  do {                                                                                                               \
+    static bool attr = false;                                                                                        \
+    if (!attr) {                                                                                                     \
+      TDL_CUDA_OK(cudaFuncSetAttribute(depthwise3x3_tma_wgrad_kernel<S, D>,                                          \
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));                    \
+      attr = true;                                                                                                   \
+    }                                                                                                                \
+    depthwise3x3_tma_wgrad_kernel<S, D><<<grid, kT, smem, st>>>(tmx, tmg, dw, dbias, s, stages, relu_in);             \
+  } while (0)
+  if (stride == 1 && dil == 1) TDL_DWW_LAUNCH(1, 1);
+  else if (stride == 1) TDL_DWW_LAUNCH(1, 2);
+  else TDL_DWW_LAUNCH(2, 1);
+#undef TDL_DWW_LAUNCH
+  TDL_LAUNCH_OK("depthwise3x3_tma_wgrad_kernel");
+  return 0;
+}
+
+// Same contract as tdl_depthwise3x3_fwd; requires C % 8 == 0, stride in {1,2}, dilation in {1,2}.
+TDL_API int tdl_depthwise3x3_tma_fwd(const void* x, const float* w, const float* bias, const void* mask, void* y,
+                                     int N, int H, int W, int C, int P, int Q, int stride, int dil, int pad_h,
+                                     int pad_w, int relu_in, int relu_out, void* stream) {
+  using namespace tdl::dwt;
+  TDL_REQUIRE(C % 8 == 0, "C must be a multiple of 8");
+  TDL_REQUIRE((stride == 1 || stride == 2) && (dil == 1 || dil == 2) && !(stride == 2 && dil == 2),
+              "TMA depthwise supports stride 1/2 with dilation 1, or stride 1 with dilation 2");
+  if ((int64_t)N * P * Q == 0) return 0;
+  TShape s;
+  s.N = N; s.H = H; s.W = W; s.C = C; s.P = P; s.Q = Q; s.stride = stride; s.dil = dil; s.pad_h = pad_h; s.pad_w = pad_w;
+  choose_tile(P, Q, stride, &s.TH, &s.TW);
+  s.BW = (s.TW - 1) * stride + 2 * dil + 1;
+  s.BH = (s.TH - 1) * stride + 2 * dil + 1;
+  s.tiles_h = (int)tdl::cdiv(P, s.TH);
+  s.tiles_w = (int)tdl::cdiv(Q, s.TW);
+  CUtensorMap tm, tmm;
+  int rc = encode_nhwc(&tm, x, N, H, W, C, s.BW, s.BH);
+  if (rc) return rc;
+  const int has_mask = mask != nullptr;
+  rc = encode_nhwc(&tmm, has_mask ? mask : x, N, has_mask ? P : H, has_mask ? Q : W, C, s.TW, s.TH);
+  if (rc) return rc;
+  const int x_bytes = ((s.BH * s.BW * 128 + 1023) / 1024) * 1024;
+  const int m_bytes = has_mask ? ((s.TH * s.TW * 128 + 1023) / 1024) * 1024 : 0;
+  int stages = (150 * 1024) / (x_bytes + m_bytes);
+  if (stages > kMaxStages) stages = kMaxStages;
+  if (stages < 2) stages = 2;
+  const int smem = stages * (x_bytes + m_bytes) + 1024;
+  const int tiles = N * s.tiles_h * s.tiles_w;
+  const int gy = (int)tdl::cdiv(C, 64);
+  int gx = (tdl::num_sms() * 2) / gy;
+  if (gx < 1) gx = 1;
+  if (gx > tiles) gx = tiles;
+  dim3 grid(gx, gy);
+  cudaStream_t st = (cudaStream_t)stream;
+#define TDL_DW_LAUNCH(S, D)                                                                                          \
+  do {                                                                                                               \
+    static bool attr = false;                                                                                        \
+    if (!attr) {                                                                                                     \
+      TDL_CUDA_OK(cudaFuncSetAttribute(depthwise3x3_tma_kernel<S, D>, cudaFuncAttributeMaxDynamicSharedMemorySize,   \
+                                       200 * 1024));                                                                 \
+      attr = true;                                                                                                   \
+    }                                                                                                                \
+    depthwise3x3_tma_kernel<S, D><<<grid, kT, smem, st>>>(tm, tmm, w, bias, has_mask, (tdl::bf16*)y, s, stages,       \
+                                                          relu_in, relu_out);                                        \
+  } while (0)
+  if (stride == 1 && dil == 1) TDL_DW_LAUNCH(1, 1);
+  else if (stride == 1) TDL_DW_LAUNCH(1, 2);
+  else TDL_DW_LAUNCH(2, 1);
+#undef TDL_DW_LAUNCH
+  TDL_LAUNCH_OK("depthwise3x3_tma_kernel");
+  return 0;
+}

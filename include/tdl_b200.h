@@ -85,6 +85,21 @@ int tdl_depthwise_fwd(const void* x, const float* w, const float* bias, void* y,
 int tdl_depthwise_bwd(const void* x, const float* w, const void* dy, const void* y, void* dx, float* dw, float* dbias,
                       int N, int H, int W, int C, int P, int Q, int R, int S, int stride, int dil, int pad_h, int pad_w,
                       int relu, void* stream);
+/* fast 3x3 depthwise (strip kernels): w [9,C] fp32; relu_in = ReLU on load, relu_out = ReLU on store;
+ * mask (NULL ok) zeroes outputs where mask <= 0 -- the data gradient is this kernel on dy with flipped taps */
+int tdl_depthwise3x3_fwd(const void* x, const float* w, const float* bias, const void* mask, void* y, int N, int H,
+                         int W, int C, int P, int Q, int stride, int dil, int pad_h, int pad_w, int relu_in,
+                         int relu_out, void* stream);
+/* TMA-tiled variant of tdl_depthwise3x3_fwd (haloed input patch via one 4-D TMA box into swizzled smem);
+ * C % 8 == 0, stride 1/2 with dilation 1, or stride 1 with dilation 2 */
+int tdl_depthwise3x3_tma_fwd(const void* x, const float* w, const float* bias, const void* mask, void* y, int N,
+                             int H, int W, int C, int P, int Q, int stride, int dil, int pad_h, int pad_w,
+                             int relu_in, int relu_out, void* stream);
+int tdl_depthwise3x3_tma_wgrad(const void* x, const void* dy, float* dw, float* dbias, int N, int H, int W, int C,
+                               int P, int Q, int stride, int dil, int pad_h, int pad_w, int relu_in, void* stream);
+int tdl_depthwise3x3_wgrad(const void* x, const void* dy, const void* ymask, float* dw, float* dbias, int N, int H,
+                           int W, int C, int P, int Q, int stride, int dil, int pad_h, int pad_w, int relu_in,
+                           void* stream);
 int tdl_upsample_fwd(const void* x, void* y, int N, int H, int W, int C, int OH, int OW, int is_bf16, void* stream);
 int tdl_upsample_bwd(const void* dy, float* dx, int N, int H, int W, int C, int OH, int OW, int is_bf16, void* stream);
 int tdl_u8_to_bf16_normalize(const void* x_u8, void* y_bf16, int64_t pixels, int C, int Cpad, const float* mean,

@@ -499,6 +499,23 @@ def group_model():
          ok=abs(out["native"][0] - out["torch"][0]) < 0.05 and cos_min > 0.9)
 
 
+def group_perf_depthwise():
+    """Depthwise 3x3 kernels on Xception-41 shapes (batch 64): achieved GB/s of algorithmic traffic."""
+    import torch
+    from tensorflowdistributedlearning_b200.ops import native_ops as O
+
+    for (H, C) in [(19, 728), (38, 728), (75, 256), (150, 128)]:
+        x = torch.randn(64, H, H, C, device="cuda").bfloat16()
+        w = torch.randn(9, C, device="cuda")
+        dy = torch.randn(64, H, H, C, device="cuda").bfloat16()
+        gb = x.numel() * 2 / 1e9
+        t_f = time_cuda(lambda: O.depthwise3x3_fwd(x, w, None, None, 1, 1, 1, 1, (H, H), True, False))
+        t_d = time_cuda(lambda: O.depthwise3x3_fwd(dy, w, None, x, 1, 1, 1, 1, (H, H), False, False))
+        t_w = time_cuda(lambda: O.depthwise3x3_wgrad(x, dy, None, 1, 1, 1, 1, True, False))
+        emit(group="perf_depthwise", H=H, C=C, fwd_us=t_f * 1e3, fwd_gbs=2 * gb / t_f * 1e3, dgrad_us=t_d * 1e3,
+             dgrad_gbs=3 * gb / t_d * 1e3, wgrad_us=t_w * 1e3, wgrad_gbs=2 * gb / t_w * 1e3)
+
+
 GROUPS = {
     "conv_fprop_basic": group_conv_fprop_basic,
     "conv_fprop_strided": group_conv_fprop_strided,
@@ -511,6 +528,7 @@ GROUPS = {
     "spatial": group_spatial,
     "p2p_emulate": group_p2p_emulate,
     "model": group_model,
+    "perf_depthwise": group_perf_depthwise,
 }
 
 

@@ -43,11 +43,11 @@ class SeparableConv2dSame(TFModule):
     explicit symmetric-first padding when strided (core/xception.py:38-128)."""
 
     def __init__(self, cin: int, cout: int, kernel_size: int, stride: int, rate: int, scope: str, bn: BNConfig,
-                 relu: bool):
+                 relu: bool, relu_in: bool = False):
         super().__init__()
         padding = "SAME" if stride == 1 else _explicit_pads(kernel_size, rate)
         self.depthwise = DepthwiseConv2d(cin, kernel_size, stride, rate, padding, use_bias=False, relu=False,
-                                         scope=f"{scope}_depthwise", init_std=0.33)
+                                         scope=f"{scope}_depthwise", init_std=0.33, relu_in=relu_in)
         self.dw_bn = BatchNorm(cin, bn.decay, bn.eps, bn.scale, scope=f"{scope}_depthwise/BatchNorm")
         self.pointwise = ConvBNAct(cin, cout, 1, scope=f"{scope}_pointwise", bn=bn, relu=relu, init_std=0.06)
         self.relu = relu
@@ -68,8 +68,11 @@ class XceptionModule(TFModule):
         self.scope, self.skip, self.act_in_sep = s, skip, act_in_sep
         convs, c = [], cin
         for i in range(3):
+            # without activation inside the separable conv, the module applies ReLU *before* each one
+            # (core/xception.py:184-210); that pre-activation is folded into the depthwise kernel's load
             convs.append(SeparableConv2dSame(c, depth_list[i], 3, stride if i == 2 else 1, rate * unit_rate_list[i],
-                                             scope=f"{s}/separable_conv{i + 1}", bn=bn, relu=act_in_sep))
+                                             scope=f"{s}/separable_conv{i + 1}", bn=bn, relu=act_in_sep,
+                                             relu_in=not act_in_sep))
             c = depth_list[i]
         self.convs = nn.ModuleList(convs)
         self.shortcut = (ConvBNAct(cin, depth_list[-1], 1, stride=stride, scope=f"{s}/shortcut", bn=bn, relu=False)
@@ -79,8 +82,6 @@ class XceptionModule(TFModule):
     def forward(self, x):
         r = x
         for m in self.convs:
-            if not self.act_in_sep:
-                r = F.relu(r)
             r = m(r)
         if self.skip == "conv":
             return r + self.shortcut(x)

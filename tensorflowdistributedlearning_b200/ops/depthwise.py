@@ -2,6 +2,10 @@
 
 reference call sites: core/layers.py:34-42 (ASPP, dilated, bias+ReLU) and
 core/xception.py:102-110 (Xception separable convs, stride 1/2).
+
+3x3 filters (every use in the reference) take the strip kernels of ``csrc/depthwise.cu``: the pre-activation ReLU of
+the Xception module can be folded into the load (``relu_in``) and the ASPP ReLU into the store (``relu``); the data
+gradient of a stride-1 layer is the same kernel on flipped taps.
 """
 from __future__ import annotations
 
@@ -16,14 +20,21 @@ from . import reference as R
 
 class _DepthwiseNative(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, stride, dil, pads, out_hw, relu):
+    def forward(ctx, x, weight, bias, stride, dil, pads, out_hw, relu, relu_in):
         from . import native_ops as O
 
-        y = O.depthwise_fwd(x, weight.detach(), None if bias is None else bias.detach(), stride, dil, pads[0], pads[2],
-                            out_hw, relu)
+        kh, kw, C = weight.shape
+        fast = kh == 3 and kw == 3
+        wd = weight.detach().float().contiguous()
+        bd = None if bias is None else bias.detach().float().contiguous()
+        if fast:
+            y = O.depthwise3x3_fwd(x, wd.view(9, C), bd, None, stride, dil, pads[0], pads[2], out_hw, relu_in, relu)
+        else:
+            xin = torch.relu(x) if relu_in else x
+            y = O.depthwise_fwd(xin, wd, bd, stride, dil, pads[0], pads[2], out_hw, relu)
         TF._count(1)
         ctx.save_for_backward(x, weight, y if relu else None)
-        ctx.cfg = (stride, dil, pads, relu, bias is not None)
+        ctx.cfg = (stride, dil, pads, relu, relu_in, bias is not None, fast)
         return y
 
     @staticmethod
@@ -31,20 +42,42 @@ class _DepthwiseNative(torch.autograd.Function):
         from . import native_ops as O
 
         x, weight, y = ctx.saved_tensors
-        stride, dil, pads, relu, has_bias = ctx.cfg
+        stride, dil, pads, relu, relu_in, has_bias, fast = ctx.cfg
         dy = dy.contiguous()
-        dx, dw, db = O.depthwise_bwd(x, weight.detach(), dy, y, stride, dil, pads[0], pads[2], relu)
-        TF._count(2)
-        return dx, dw, (db if has_bias else None), None, None, None, None, None
+        kh, kw, C = weight.shape
+        wd = weight.detach().float().contiguous()
+        if fast:
+            dw, db = O.depthwise3x3_wgrad(x, dy, y if relu else None, stride, dil, pads[0], pads[2], relu_in, has_bias)
+            dw = dw.view(3, 3, C)
+            TF._count(1)
+            dx = None
+            if ctx.needs_input_grad[0]:
+                if stride == 1 and not relu:
+                    n, h, w, _ = x.shape
+                    dx = O.depthwise3x3_fwd(dy, wd.flip(0, 1).contiguous().view(9, C), None, x if relu_in else None, 1,
+                                            dil, 2 * dil - pads[0], 2 * dil - pads[2], (h, w), False, False)
+                else:
+                    dx, _, _ = O.depthwise_bwd(x, wd, dy, y, stride, dil, pads[0], pads[2], relu)
+                    if relu_in:
+                        dx = dx * (x > 0)
+                TF._count(1)
+        else:
+            xin = torch.relu(x) if relu_in else x
+            dx, dw, db = O.depthwise_bwd(xin, wd, dy, y, stride, dil, pads[0], pads[2], relu)
+            if relu_in:
+                dx = dx * (x > 0)
+            TF._count(2)
+        return dx, dw, (db if has_bias else None), None, None, None, None, None, None
 
 
 def depthwise_conv2d(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None, stride: int = 1,
-                     dil: int = 1, padding="SAME", relu: bool = False) -> torch.Tensor:
-    """x [N,H,W,C], weight [kh,kw,C] -> [N,P,Q,C]; optional fused bias + ReLU."""
+                     dil: int = 1, padding="SAME", relu: bool = False, relu_in: bool = False) -> torch.Tensor:
+    """x [N,H,W,C], weight [kh,kw,C] -> [N,P,Q,C]; optional ReLU on the input, fused bias + ReLU on the output."""
     kh, kw, C = weight.shape
     n, h, w, c = x.shape
     P, Q, pt, pb, pl, pr = TF.conv_pads(h, w, kh, kw, stride, dil, padding)
     if TF._native_ok(x) and C % 8 == 0:
-        return _DepthwiseNative.apply(x.contiguous(), weight, bias, stride, dil, (pt, pb, pl, pr), (P, Q), relu)
-    y = R.depthwise_conv2d_nhwc(x, weight.to(x.dtype), stride, dil, (pt, pb, pl, pr), bias)
+        return _DepthwiseNative.apply(x.contiguous(), weight, bias, stride, dil, (pt, pb, pl, pr), (P, Q), relu, relu_in)
+    xin = F.relu(x) if relu_in else x
+    y = R.depthwise_conv2d_nhwc(xin, weight.to(x.dtype), stride, dil, (pt, pb, pl, pr), bias)
     return F.relu(y) if relu else y

@@ -46,6 +46,40 @@ def _notify(param) -> None:
         fn(param)
 
 
+# Weight-gradient kernels only feed the optimizer step, so they can leave the critical path: with async wgrad on,
+# they are launched on a side stream (forked after dy is ready) and overlap the memory-bound BatchNorm-backward /
+# data-gradient chain that continues on the main stream.  `join_side_streams()` re-joins before the optimizer.
+_ASYNC_WGRAD = False
+_SIDE = {}
+_SIDE_DIRTY = False
+
+
+def enable_async_wgrad(flag: bool) -> None:
+    global _ASYNC_WGRAD
+    _ASYNC_WGRAD = bool(flag)
+
+
+def _side_stream():
+    dev = torch.cuda.current_device()
+    st = _SIDE.get(dev)
+    if st is None:
+        st = _SIDE[dev] = torch.cuda.Stream(device=dev)
+    return st
+
+
+def join_side_streams(waiter=None) -> None:
+    """Make ``waiter`` (default: the current stream) wait for every wgrad launched on the side stream."""
+    global _SIDE_DIRTY
+    if not _SIDE:
+        return
+    w = waiter or torch.cuda.current_stream()
+    st = _SIDE.get(torch.cuda.current_device())
+    if st is not None:
+        w.wait_stream(st)
+    if waiter is None:
+        _SIDE_DIRTY = False
+
+
 def _direct_ok(p) -> bool:
     return (_DIRECT_GRAD and p is not None and p.grad is not None and p.grad.dtype == torch.float32
             and p.grad.is_contiguous())
@@ -167,7 +201,19 @@ class _ConvNative(torch.autograd.Function):
         elif ctx.needs_input_grad[1]:
             wp = ctx.weight_param
             if _direct_ok(wp):
-                O.conv2d_wgrad(x, dy, wp.grad.view(K, Rk * Sk, C), R=Rk, S=Sk, stride=stride, dil=dil, pad_h=pt, pad_w=pl)
+                if _ASYNC_WGRAD:
+                    global _SIDE_DIRTY
+                    side = _side_stream()
+                    side.wait_stream(torch.cuda.current_stream())  # dy (and x) are complete on the main stream
+                    with torch.cuda.stream(side):
+                        O.conv2d_wgrad(x, dy, wp.grad.view(K, Rk * Sk, C), R=Rk, S=Sk, stride=stride, dil=dil,
+                                       pad_h=pt, pad_w=pl)
+                    x.record_stream(side)   # keep the operands alive until the side stream is done with them
+                    dy.record_stream(side)
+                    _SIDE_DIRTY = True
+                else:
+                    O.conv2d_wgrad(x, dy, wp.grad.view(K, Rk * Sk, C), R=Rk, S=Sk, stride=stride, dil=dil, pad_h=pt,
+                                   pad_w=pl)
                 _notify(wp)
             else:
                 dw = torch.zeros((K, Rk * Sk, C), dtype=torch.float32, device=x.device)

@@ -173,9 +173,10 @@ class DepthwiseConv2d(TFModule):
     """slim.separable_conv2d(num_outputs=None): depthwise kxk (+bias) (+ReLU), depth multiplier 1."""
 
     def __init__(self, c: int, k: int = 3, stride: int = 1, rate: int = 1, padding="SAME", use_bias: bool = True,
-                 relu: bool = True, scope: str = "depthwise", init_std: float = 0.33):
+                 relu: bool = True, scope: str = "depthwise", init_std: float = 0.33, relu_in: bool = False):
         super().__init__()
         self.c, self.k, self.stride, self.rate, self.padding, self.relu, self.scope = c, k, stride, rate, padding, relu, scope
+        self.relu_in = relu_in  # apply ReLU to the input inside the kernel (Xception's pre-activation)
         self.weight = nn.Parameter(torch.empty(k, k, c))
         R.truncated_normal_(self.weight.data, init_std)
         self.bias = nn.Parameter(torch.zeros(c)) if use_bias else None
@@ -183,7 +184,8 @@ class DepthwiseConv2d(TFModule):
     def forward(self, x):
         from . import depthwise as DW
 
-        return DW.depthwise_conv2d(x, self.weight, self.bias, self.stride, self.rate, self.padding, self.relu)
+        return DW.depthwise_conv2d(x, self.weight, self.bias, self.stride, self.rate, self.padding, self.relu,
+                                   self.relu_in)
 
     def tf_variables(self):
         d = {f"{self.scope}/depthwise_weights": (self.weight, "depthwise")}

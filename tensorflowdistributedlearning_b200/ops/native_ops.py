@@ -406,3 +406,36 @@ def u8_to_bf16_normalize(x_u8: torch.Tensor, mean: torch.Tensor, inv_std: torch.
                                           N.ptr(inv_std), N.stream_ptr())
     N.check(rc, "tdl_u8_to_bf16_normalize")
     return out
+
+
+def depthwise3x3_fwd(x, w9c, bias, mask, stride, dil, pad_h, pad_w, out_hw, relu_in, relu_out):
+    """Fast 3x3 depthwise: x [N,H,W,C] bf16, w9c [9, C] fp32 (tap-major).  ``mask``: zero outputs where mask <= 0."""
+    _chk_bf16_nhwc(x, "x")
+    n, h, w, c = x.shape
+    p, q = out_hw
+    y = torch.empty((n, p, q, c), dtype=torch.bfloat16, device=x.device)
+    tma_ok = c % 8 == 0 and ((stride in (1, 2) and dil == 1) or (stride == 1 and dil == 2))
+    fn = N.lib().tdl_depthwise3x3_tma_fwd if tma_ok else N.lib().tdl_depthwise3x3_fwd
+    rc = fn(N.ptr(x), N.ptr(w9c), N.ptr(bias), N.ptr(mask), N.ptr(y), _i(n), _i(h), _i(w), _i(c), _i(p), _i(q),
+            _i(stride), _i(dil), _i(pad_h), _i(pad_w), _i(int(relu_in)), _i(int(relu_out)), N.stream_ptr())
+    N.check(rc, "tdl_depthwise3x3_tma_fwd" if tma_ok else "tdl_depthwise3x3_fwd")
+    return y
+
+
+def depthwise3x3_wgrad(x, dy, ymask, stride, dil, pad_h, pad_w, relu_in, want_bias):
+    n, h, w, c = x.shape
+    _, p, q, _ = dy.shape
+    dw = torch.zeros((9, c), dtype=torch.float32, device=x.device)
+    db = torch.zeros((c,), dtype=torch.float32, device=x.device) if want_bias else None
+    tma_ok = ymask is None and c % 8 == 0 and ((stride in (1, 2) and dil == 1) or (stride == 1 and dil == 2))
+    if tma_ok:
+        rc = N.lib().tdl_depthwise3x3_tma_wgrad(N.ptr(x), N.ptr(dy), N.ptr(dw), N.ptr(db), _i(n), _i(h), _i(w), _i(c),
+                                                _i(p), _i(q), _i(stride), _i(dil), _i(pad_h), _i(pad_w),
+                                                _i(int(relu_in)), N.stream_ptr())
+        N.check(rc, "tdl_depthwise3x3_tma_wgrad")
+        return dw, db
+    rc = N.lib().tdl_depthwise3x3_wgrad(N.ptr(x), N.ptr(dy), N.ptr(ymask), N.ptr(dw), N.ptr(db), _i(n), _i(h), _i(w),
+                                        _i(c), _i(p), _i(q), _i(stride), _i(dil), _i(pad_h), _i(pad_w),
+                                        _i(int(relu_in)), N.stream_ptr())
+    N.check(rc, "tdl_depthwise3x3_wgrad")
+    return dw, db

@@ -31,7 +31,7 @@ class DistributedOptimizer:
                  momentum: float = 0.9, weight_decay: float = 0.0, beta1: float = 0.9, beta2: float = 0.999,
                  eps: float = 1e-8, decay_steps: float = 0.0, decay_rate: float = 1.0, comm: Optional[str] = None,
                  bucket_cap_mb: float = 32.0, overlap: bool = True, sync_bn_stats: bool = True,
-                 comm_max_blocks: int = 128):
+                 comm_max_blocks: int = 128, async_wgrad: bool = True):
         if kind not in ("adam", "sgdm"):
             raise ValueError("kind must be 'adam' or 'sgdm'")
         self.group, self.kind = group, kind
@@ -98,6 +98,7 @@ class DistributedOptimizer:
             from ..ops import functional as TF
 
             TF.enable_direct_grad(True)  # native backward kernels accumulate straight into the flat gradient buckets
+            TF.enable_async_wgrad(async_wgrad)
         if self.overlap:
             from ..ops import functional as TF
 
@@ -154,6 +155,10 @@ class DistributedOptimizer:
             if self._pending[b.index] != 0:
                 break
             self._side.wait_stream(torch.cuda.current_stream())
+            if self.on_gpu:
+                from ..ops import functional as TF
+
+                TF.join_side_streams(self._side)  # weight gradients may still be in flight on the wgrad stream
             with torch.cuda.stream(self._side):
                 self._launch_bucket(b)
             self._launched[b.index] = True
@@ -164,6 +169,10 @@ class DistributedOptimizer:
         if not self._lr_ready:
             self._advance_schedule()
         self._lr_ready = False
+        if self.on_gpu:
+            from ..ops import functional as TF
+
+            TF.join_side_streams()  # side-stream weight gradients must have landed in the flat buckets
         f = self.flat
         if self.comm == "p2p":
             if self.overlap:

@@ -277,11 +277,18 @@ def test_spatial_ops(O):
     _native_vs_oracle(lambda t: pooling.max_pool(t, 3, 2, (1, 1, 1, 1)),
                       [torch.randn(2, 56, 56, 64, device="cuda").bfloat16().relu()], 2e-2)  # ties after ReLU
     _native_vs_oracle(lambda t: pooling.global_avg_pool(t, True), [torch.randn(8, 7, 7, 2048, device="cuda").bfloat16()], 2e-2)
-    for (H, C, st, dil) in [(13, 1024, 1, 8), (38, 728, 1, 1), (19, 728, 2, 1)]:
+    for (H, C, st, dil, relu, relu_in) in [(13, 1024, 1, 8, True, False), (38, 728, 1, 1, False, True),
+                                           (19, 728, 2, 1, False, True), (37, 128, 1, 1, True, True),
+                                           (150, 64, 2, 1, False, False), (10, 1536, 1, 2, False, False)]:
         x = torch.randn(2, H, H, C, device="cuda").bfloat16()
         w = torch.randn(3, 3, C, device="cuda") * 0.3
         b = torch.randn(C, device="cuda") * 0.1
-        _native_vs_oracle(lambda t, ww, bb: depthwise.depthwise_conv2d(t, ww, bb, st, dil, "SAME", True), [x, w, b], 3e-2)
+        _native_vs_oracle(lambda t, ww, bb: depthwise.depthwise_conv2d(t, ww, bb, st, dil, "SAME", relu, relu_in),
+                          [x, w, b], 3e-2)
+    # explicit (symmetric-first) padding as used by the strided Xception separable convs
+    x = torch.randn(2, 75, 75, 256, device="cuda").bfloat16()
+    w = torch.randn(3, 3, 256, device="cuda") * 0.3
+    _native_vs_oracle(lambda t, ww: depthwise.depthwise_conv2d(t, ww, None, 2, 1, (1, 1, 1, 1), False, True), [x, w], 3e-2)
     for (h, C, out, dt) in [(1, 256, 13, torch.bfloat16), (13, 256, 26, torch.bfloat16), (26, 1, 101, torch.float32)]:
         _native_vs_oracle(lambda t: resize.upsample(t, (out, out)), [torch.randn(2, h, h, C, device="cuda").to(dt)], 2e-2)
 
