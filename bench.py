@@ -166,7 +166,7 @@ def main():
     ap.add_argument("--model", default="resnet50", choices=sorted(CONFIGS))
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "proxy"])
     ap.add_argument("--batch", type=int, default=0, help="per-tower batch (default: config's)")
-    ap.add_argument("--comm", default=None, choices=[None, "p2p", "nccl"], help="gradient path (default p2p)")
+    ap.add_argument("--comm", default=None, choices=[None, "p2p", "nvls", "nccl"], help="gradient path (default p2p)")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-overlap", action="store_true")
     ap.add_argument("--no-async-wgrad", action="store_true")
@@ -280,7 +280,7 @@ def main():
         "impl": "ours" if not proxy else "proxy(pytorch-cudnn-nccl)",
         "config": {"model": args.model, "global_batch": global_batch, "per_tower_batch": batch,
                    "image": f"{h}x{w}x{c}", "seq_len": None, "parallelism": f"dp{n_gpus}",
-                   "optimizer": cfg["opt"], "grad_comm": trainer.opt.comm, "cuda_graph": trainer._graph is not None,
+                   "optimizer": cfg["opt"], "grad_comm": trainer.opt.comm, "nvls": bool(getattr(trainer.opt, "nvls", False)), "cuda_graph": trainer._graph is not None,
                    "overlap": trainer.opt.overlap,
                    "l2": "no flush needed: each step streams far more than the 126 MB L2 (activations >> L2)",
                    "weights": "random init", "loss_after_timed_steps": round(loss_dev, 4)},

@@ -22,7 +22,7 @@ struct ReduceShape {
   int gy;       // CTAs across channel-vectors
 };
 
-static ReduceShape reduce_shape(int64_t rows, int C) {
+static ReduceShape reduce_shape(int64_t rows, int C, int ctas_per_sm = 4) {
   ReduceShape s;
   const int c8 = C / 8;
   s.tx = 1;
@@ -30,7 +30,7 @@ static ReduceShape reduce_shape(int64_t rows, int C) {
   s.ty = kThreads / s.tx;
   s.gy = (int)cdiv(c8, s.tx);
   int64_t want = cdiv(rows, (int64_t)s.ty * 8);
-  int64_t cap = (int64_t)num_sms() * 4 / s.gy;
+  int64_t cap = (int64_t)num_sms() * ctas_per_sm / s.gy;  // one full wave of resident CTAs
   if (cap < 1) cap = 1;
   if (want > cap) want = cap;
   if (want < 1) want = 1;
@@ -94,25 +94,42 @@ bn_partial_stats_kernel(const bf16* __restrict__ x, int64_t rows, int C, int tx,
   }
 }
 
-// Second-level reduce: 32 channels x 8 slices of the partial list per CTA, fp64 accumulation.
-constexpr int kFinThreads = 256;
+// Second-level reduce: kFinCh channels x kFinSlices slices of the partial list per CTA, fp64 accumulation.  The
+// partial list is short (<= a few hundred rows) so the kernel is pure latency: many slices and four independent
+// loads in flight per thread keep it to a couple of memory round trips.
+constexpr int kFinThreads = 512;
+constexpr int kFinCh = 8;
+constexpr int kFinSlices = kFinThreads / kFinCh;
 
 __device__ __forceinline__ void reduce_partials(const float* __restrict__ partial, int nparts, int C, int c,
                                                 double* s_out, double* q_out) {
-  __shared__ double sm_s[8][32], sm_q[8][32];
-  const int lane = threadIdx.x & 31, slice = threadIdx.x >> 5;
+  __shared__ double sm_s[kFinSlices][kFinCh], sm_q[kFinSlices][kFinCh];
+  const int lane = threadIdx.x % kFinCh, slice = threadIdx.x / kFinCh;
   double s = 0.0, q = 0.0;
-  if (c < C)
-    for (int p = slice; p < nparts; p += 8) {
+  if (c < C) {
+    int p = slice;
+    for (; p + 3 * kFinSlices < nparts; p += 4 * kFinSlices) {
+      float a[4], b[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        a[u] = partial[((size_t)(p + u * kFinSlices) * 2) * C + c];
+        b[u] = partial[((size_t)(p + u * kFinSlices) * 2 + 1) * C + c];
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) { s += (double)a[u]; q += (double)b[u]; }
+    }
+    for (; p < nparts; p += kFinSlices) {
       s += (double)partial[((size_t)p * 2) * C + c];
       q += (double)partial[((size_t)p * 2 + 1) * C + c];
     }
+  }
   sm_s[slice][lane] = s;
   sm_q[slice][lane] = q;
   __syncthreads();
   s = 0.0; q = 0.0;
   if (slice == 0)
-    for (int t = 0; t < 8; ++t) { s += sm_s[t][lane]; q += sm_q[t][lane]; }
+#pragma unroll
+    for (int t = 0; t < kFinSlices; ++t) { s += sm_s[t][lane]; q += sm_q[t][lane]; }
   *s_out = s;
   *q_out = q;
 }
@@ -123,10 +140,10 @@ bn_finalize_stats_kernel(const float* __restrict__ partial, int nparts, int C, d
                          float* __restrict__ running_mean, float* __restrict__ running_var, float decay, float eps,
                          float* __restrict__ mean_out, float* __restrict__ invstd_out, float* __restrict__ scale_out,
                          float* __restrict__ shift_out) {
-  const int c = blockIdx.x * 32 + (threadIdx.x & 31);
+  const int c = blockIdx.x * kFinCh + (threadIdx.x % kFinCh);
   double s, q;
   reduce_partials(partial, nparts, C, c, &s, &q);
-  if ((threadIdx.x >> 5) != 0 || c >= C) return;
+  if (threadIdx.x >= kFinCh || c >= C) return;
   const double m = s * inv_n;
   double var = q * inv_n - m * m;
   if (var < 0.0) var = 0.0;
@@ -304,10 +321,10 @@ bn_bwd_partial_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ x, c
 __global__ void __launch_bounds__(kFinThreads)
 bn_bwd_finalize_kernel(const float* __restrict__ partial, int nparts, int C, float* __restrict__ dbeta,
                        float* __restrict__ dgamma, float* __restrict__ acc_dbeta, float* __restrict__ acc_dgamma) {
-  const int c = blockIdx.x * 32 + (threadIdx.x & 31);
+  const int c = blockIdx.x * kFinCh + (threadIdx.x % kFinCh);
   double s, q;
   reduce_partials(partial, nparts, C, c, &s, &q);
-  if ((threadIdx.x >> 5) != 0 || c >= C) return;
+  if (threadIdx.x >= kFinCh || c >= C) return;
   dbeta[c] = (float)s;
   dgamma[c] = (float)q;
   if (acc_dbeta) acc_dbeta[c] += (float)s;
@@ -402,6 +419,23 @@ static int ew_blocks(int64_t nvec) {
   return (int)b;
 }
 
+// Resident CTAs per SM of a reduction kernel (registers + its 16 KB of shared memory decide): the grid is sized to
+// exactly one wave of them, a 4-per-SM grid of a 3-per-SM kernel would run a second, one-third-full wave.
+constexpr int kMaxReduceCtasPerSm = 8;
+template <typename Kern>
+static int resident_ctas(Kern kernel, int* cache) {
+  if (*cache == 0) {
+    int n = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, kThreads, kThreads * 16 * sizeof(float)) != cudaSuccess)
+      n = 0;
+    if (n < 1) n = 1;
+    if (n > kMaxReduceCtasPerSm) n = kMaxReduceCtasPerSm;
+    *cache = n;
+  }
+  return *cache;
+}
+static int g_fwd_stats_ctas = 0, g_bwd_partial_ctas = 0;
+
 }  // namespace bn
 }  // namespace tdl
 
@@ -411,7 +445,7 @@ using namespace tdl::bn;
 // Number of fp32 scratch elements tdl_bn_fwd_stats / tdl_bn_bwd_reduce need for this shape.
 TDL_API int64_t tdl_bn_scratch_floats(int64_t rows, int C) {
   if (C <= 0 || C % 8) return -1;
-  ReduceShape s = reduce_shape(rows, C);
+  ReduceShape s = reduce_shape(rows, C, kMaxReduceCtasPerSm);  // upper bound over the reduction kernels
   return (int64_t)s.gx * 2 * C;
 }
 
@@ -422,7 +456,7 @@ TDL_API int tdl_bn_fwd_stats(const void* x, int64_t rows, int C, float* scratch,
                              void* stream) {
   TDL_REQUIRE(C > 0 && C % 8 == 0, "C must be a positive multiple of 8");
   TDL_REQUIRE(rows > 0, "empty input");
-  ReduceShape s = reduce_shape(rows, C);
+  ReduceShape s = reduce_shape(rows, C, resident_ctas(bn_partial_stats_kernel, &g_fwd_stats_ctas));
   TDL_REQUIRE(scratch_floats >= (int64_t)s.gx * 2 * C, "scratch too small (see tdl_bn_scratch_floats)");
   cudaStream_t st = (cudaStream_t)stream;
   dim3 grid(s.gx, s.gy);
@@ -430,9 +464,9 @@ TDL_API int tdl_bn_fwd_stats(const void* x, int64_t rows, int C, float* scratch,
                                                                                   scratch);
   TDL_LAUNCH_OK("bn_partial_stats_kernel");
   const double unbias = rows > 1 ? (double)rows / (double)(rows - 1) : 1.0;
-  bn_finalize_stats_kernel<<<(C + 31) / 32, kFinThreads, 0, st>>>(scratch, s.gx, C, 1.0 / (double)rows, unbias, gamma,
-                                                                  beta, running_mean, running_var, decay, eps, mean,
-                                                                  invstd, scale, shift);
+  bn_finalize_stats_kernel<<<(C + kFinCh - 1) / kFinCh, kFinThreads, 0, st>>>(
+      scratch, s.gx, C, 1.0 / (double)rows, unbias, gamma, beta, running_mean, running_var, decay, eps, mean, invstd,
+      scale, shift);
   TDL_LAUNCH_OK("bn_finalize_stats_kernel");
   return 0;
 }
@@ -444,7 +478,7 @@ TDL_API int tdl_bn_finalize_partials(const float* partial, int nparts, int64_t r
                                      float eps, float* mean, float* invstd, float* scale, float* shift, void* stream) {
   TDL_REQUIRE(C > 0 && nparts > 0 && rows > 0, "bad arguments");
   const double unbias = rows > 1 ? (double)rows / (double)(rows - 1) : 1.0;
-  bn_finalize_stats_kernel<<<(C + 31) / 32, kFinThreads, 0, (cudaStream_t)stream>>>(
+  bn_finalize_stats_kernel<<<(C + kFinCh - 1) / kFinCh, kFinThreads, 0, (cudaStream_t)stream>>>(
       partial, nparts, C, 1.0 / (double)rows, unbias, gamma, beta, running_mean, running_var, decay, eps, mean, invstd,
       scale, shift);
   TDL_LAUNCH_OK("bn_finalize_stats_kernel");
@@ -479,14 +513,15 @@ TDL_API int tdl_bn_bwd_reduce(const void* dz, const void* x, const void* z, cons
                               int64_t scratch_floats, float* dgamma, float* dbeta, float* acc_dgamma,
                               float* acc_dbeta, void* stream) {
   TDL_REQUIRE(C > 0 && C % 8 == 0, "C must be a positive multiple of 8");
-  ReduceShape s = reduce_shape(rows, C);
+  ReduceShape s = reduce_shape(rows, C, resident_ctas(bn_bwd_partial_kernel, &g_bwd_partial_ctas));
   TDL_REQUIRE(scratch_floats >= (int64_t)s.gx * 2 * C, "scratch too small (see tdl_bn_scratch_floats)");
   cudaStream_t st = (cudaStream_t)stream;
   dim3 grid(s.gx, s.gy);
   bn_bwd_partial_kernel<<<grid, kThreads, kThreads * 16 * sizeof(float), st>>>(
       (const bf16*)dz, (const bf16*)x, (const bf16*)z, scale, shift, mean, invstd, rows, C, s.tx, s.ty, relu, scratch);
   TDL_LAUNCH_OK("bn_bwd_partial_kernel");
-  bn_bwd_finalize_kernel<<<(C + 31) / 32, kFinThreads, 0, st>>>(scratch, s.gx, C, dbeta, dgamma, acc_dbeta, acc_dgamma);
+  bn_bwd_finalize_kernel<<<(C + kFinCh - 1) / kFinCh, kFinThreads, 0, st>>>(scratch, s.gx, C, dbeta, dgamma, acc_dbeta,
+                                                                            acc_dgamma);
   TDL_LAUNCH_OK("bn_bwd_finalize_kernel");
   return 0;
 }
@@ -583,7 +618,7 @@ TDL_API int tdl_bn_fwd_stats_noalloc(const void* x, int64_t rows, int C, const f
                                                                                   scratch);
   TDL_LAUNCH_OK("bn_partial_stats_kernel");
   const double unbias = rows > 1 ? (double)rows / (double)(rows - 1) : 1.0;
-  bn_finalize_stats_kernel<<<(C + 31) / 32, kFinThreads, 0, st>>>(scratch, s.gx, C, 1.0 / (double)rows, unbias, gamma,
+  bn_finalize_stats_kernel<<<(C + kFinCh - 1) / kFinCh, kFinThreads, 0, st>>>(scratch, s.gx, C, 1.0 / (double)rows, unbias, gamma,
                                                                   beta, running_mean, running_var, decay, eps, mean,
                                                                   invstd, scale, shift);
   TDL_LAUNCH_OK("bn_finalize_stats_kernel");

@@ -310,8 +310,10 @@ __device__ __forceinline__ void multimem_st(float* mc, const float4& v) {
                : "memory");
 }
 
+template <int U>
 __global__ void __launch_bounds__(kThreads)
 nvls_kernel(const Comm cm, const StepArgs a) {
+  // U switch-reduced 16-byte loads in flight per thread: a multimem round trip is about twice a peer load
   uint32_t epoch = cm.epoch[blockIdx.x];
   cross_rank_barrier(cm, ++epoch);
   const float lr = a.lr_state[0];
@@ -323,7 +325,6 @@ nvls_kernel(const Comm cm, const StepArgs a) {
   const int64_t v_hi = v_lo + per < n4 ? v_lo + per : n4;
   const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int64_t nthr = (int64_t)gridDim.x * blockDim.x;
-  constexpr int U = 4;
   for (int64_t v0 = v_lo + tid; v0 < v_hi; v0 += nthr * U) {
     float4 acc[U];
     int64_t idx[U];
@@ -430,8 +431,8 @@ TDL_API int tdl_p2p_comm_destroy(void* comm) {
   return 0;
 }
 
-// Fused all-reduce(mean) + optimizer for one bucket.  mode: 1 = one-shot, 2 = two-shot, 3 = NVLS multimem,
-// 0 = pick one-/two-shot by size.
+// Fused all-reduce(mean) + optimizer for one bucket.  mode: 1 = one-shot, 2 = two-shot, 3 = NVLS multimem
+// (4 loads in flight per thread), 4 = NVLS multimem (8 in flight), 0 = pick one-/two-shot by size.
 // kind: 0 = plain mean written back into the gradient bucket (m1 = fp32 staging of >= offset+n elements),
 //       1 = momentum SGD (a = momentum, b = weight decay), 2 = TF Adam (a = beta1, b = beta2, c = eps).
 TDL_API int tdl_p2p_fused_step(void* comm, int64_t offset, int64_t n, int mode, int kind, int grad_is_bf16,
@@ -447,12 +448,12 @@ TDL_API int tdl_p2p_fused_step(void* comm, int64_t offset, int64_t n, int mode, 
   s.m1 = m1; s.m2 = m2; s.lr_state = lr_state; s.a = a; s.b = b; s.c = c; s.grad_scale = grad_scale;
   if (mode == 0) mode = (n * (grad_is_bf16 ? 2 : 4) <= (1 << 19) || kind == kNone) ? 1 : 2;
   if (kind == kNone) mode = 1;
-  if (mode == 3) {
+  if (mode == 3 || mode == 4) {
     TDL_REQUIRE(cm->mc_grad && cm->mc_param, "NVLS mode needs multicast addresses (tdl_p2p_comm_set_multicast)");
     TDL_REQUIRE(!grad_is_bf16 && n % 4 == 0 && kind != kNone, "NVLS mode: fp32 buckets, n % 4 == 0, with optimizer");
   }
   int64_t work = mode == 1 ? n / 4 : n / 4 / cm->world;
-  if (mode == 3) work /= 2;  // one switch-reduced load replaces W peer loads: fewer CTAs saturate the links
+  if (mode == 3 || mode == 4) work /= 2;  // one switch-reduced load replaces W peer loads: fewer CTAs saturate the links
   int blocks = (int)cdiv(work, (int64_t)kThreads * 2);
   if (max_blocks <= 0) max_blocks = 128;
   if (max_blocks > kMaxBlocks) max_blocks = kMaxBlocks;
@@ -461,7 +462,8 @@ TDL_API int tdl_p2p_fused_step(void* comm, int64_t offset, int64_t n, int mode, 
   if (blocks < 1) blocks = 1;
   cudaStream_t st = (cudaStream_t)stream;
   if (mode == 1) one_shot_kernel<<<blocks, kThreads, 0, st>>>(*cm, s);
-  else if (mode == 3) nvls_kernel<<<blocks, kThreads, 0, st>>>(*cm, s);
+  else if (mode == 3) nvls_kernel<4><<<blocks, kThreads, 0, st>>>(*cm, s);
+  else if (mode == 4) nvls_kernel<8><<<blocks, kThreads, 0, st>>>(*cm, s);
   else two_shot_kernel<<<blocks, kThreads, 0, st>>>(*cm, s);
   TDL_LAUNCH_OK("p2p fused step");
   return 0;

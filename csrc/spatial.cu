@@ -98,6 +98,107 @@ maxpool_bwd_kernel(const bf16* __restrict__ dy, const uint8_t* __restrict__ idx,
   }
 }
 
+// Compile-time window/stride variants, one CTA per (image, row): no 64-bit index arithmetic or runtime divisions in
+// the inner loop (the generic kernels above spend most of their issue slots on those), all window loads in flight
+// at once.  Used for the 3x3 stride-2 pool of the ResNet root (core/resnet.py:241).
+template <int K, int S>
+__global__ void __launch_bounds__(kThreads)
+maxpool_fwd_rows_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, uint8_t* __restrict__ idx, int H, int W,
+                        int C, int P, int Q, int pad_h, int pad_w) {
+  const int c8 = C >> 3;
+  const int n = blockIdx.x / P;
+  const int p = blockIdx.x - n * P;
+  const bf16* xn = x + (int64_t)n * H * W * C;
+  const int64_t orow = ((int64_t)n * P + p) * Q * C;
+  const int h0 = p * S - pad_h;
+  for (int i = threadIdx.x; i < Q * c8; i += kThreads) {
+    const int q = i / c8;
+    const int cv = i - q * c8;
+    const int w0 = q * S - pad_w;
+    bf16x8 v[K * K];
+    bool ok[K * K];
+#pragma unroll
+    for (int r = 0; r < K; ++r)
+#pragma unroll
+      for (int t = 0; t < K; ++t) {
+        const int h = h0 + r, w = w0 + t;
+        ok[r * K + t] = h >= 0 && h < H && w >= 0 && w < W;
+        if (ok[r * K + t]) v[r * K + t] = ld8(xn + ((int64_t)h * W + w) * C + cv * 8);
+      }
+    float best[8];
+    int arg[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { best[j] = -INFINITY; arg[j] = 0; }
+#pragma unroll
+    for (int tap = 0; tap < K * K; ++tap) {
+      if (!ok[tap]) continue;
+      float f[8];
+      unpack8(v[tap], f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (f[j] > best[j]) { best[j] = f[j]; arg[j] = tap; }
+    }
+    st8(y + orow + (int64_t)i * 8, pack8(best));
+    uint2 packed;
+    packed.x = (uint32_t)arg[0] | ((uint32_t)arg[1] << 8) | ((uint32_t)arg[2] << 16) | ((uint32_t)arg[3] << 24);
+    packed.y = (uint32_t)arg[4] | ((uint32_t)arg[5] << 8) | ((uint32_t)arg[6] << 16) | ((uint32_t)arg[7] << 24);
+    *reinterpret_cast<uint2*>(idx + orow + (int64_t)i * 8) = packed;
+  }
+}
+
+template <int K, int S>
+__global__ void __launch_bounds__(kThreads)
+maxpool_bwd_rows_kernel(const bf16* __restrict__ dy, const uint8_t* __restrict__ idx, bf16* __restrict__ dx, int H,
+                        int W, int C, int P, int Q, int pad_h, int pad_w) {
+  constexpr int kCells = (K + S - 1) / S;  // output cells per axis whose window can cover one input pixel
+  const int c8 = C >> 3;
+  const int n = blockIdx.x / H;
+  const int h = blockIdx.x - n * H;
+  const int64_t obase = (int64_t)n * P * Q * C;
+  const int64_t irow = ((int64_t)n * H + h) * W * C;
+  const int hp = h + pad_h;
+  const int p_hi = hp / S;  // the last output row whose window starts at or above this input row
+  for (int i = threadIdx.x; i < W * c8; i += kThreads) {
+    const int w = i / c8;
+    const int cv = i - w * c8;
+    const int wq = w + pad_w;
+    const int q_hi = wq / S;
+    bf16x8 g[kCells * kCells];
+    uint2 a[kCells * kCells];
+    int tapv[kCells * kCells];
+#pragma unroll
+    for (int a_ = 0; a_ < kCells; ++a_)
+#pragma unroll
+      for (int b_ = 0; b_ < kCells; ++b_) {
+        const int p = p_hi - a_, q = q_hi - b_;
+        const int r = hp - p * S, t = wq - q * S;  // tap inside that window
+        const int c = a_ * kCells + b_;
+        const bool ok = p >= 0 && p < P && q >= 0 && q < Q && r < K && t < K;
+        tapv[c] = ok ? r * K + t : -1;
+        if (ok) {
+          const int64_t o = obase + (((int64_t)p * Q + q) * c8 + cv) * 8;
+          g[c] = ld8(dy + o);
+          a[c] = *reinterpret_cast<const uint2*>(idx + o);
+        }
+      }
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+#pragma unroll
+    for (int c = 0; c < kCells * kCells; ++c) {
+      if (tapv[c] < 0) continue;
+      float f[8];
+      unpack8(g[c], f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const uint32_t win = j < 4 ? (a[c].x >> (8 * j)) & 0xff : (a[c].y >> (8 * (j - 4))) & 0xff;
+        if ((int)win == tapv[c]) acc[j] += f[j];
+      }
+    }
+    st8(dx + irow + (int64_t)i * 8, pack8(acc));
+  }
+}
+
 // ------------------------------------------------------------------------------------------
 // global average pool
 // ------------------------------------------------------------------------------------------
@@ -389,8 +490,13 @@ TDL_API int tdl_maxpool_fwd(const void* x, void* y, void* idx_u8, int N, int H, 
   TDL_REQUIRE(k * k <= 255, "window too large");
   const int64_t work = (int64_t)N * P * Q * (C / 8);
   if (work == 0) return 0;
-  maxpool_fwd_kernel<<<grid_for(work), kThreads, 0, (cudaStream_t)stream>>>((const bf16*)x, (bf16*)y, (uint8_t*)idx_u8,
-                                                                            N, H, W, C, P, Q, k, stride, pad_h, pad_w);
+  if (k == 3 && stride == 2 && (int64_t)N * P < (1ll << 31))
+    maxpool_fwd_rows_kernel<3, 2><<<N * P, kThreads, 0, (cudaStream_t)stream>>>((const bf16*)x, (bf16*)y,
+                                                                               (uint8_t*)idx_u8, H, W, C, P, Q, pad_h,
+                                                                               pad_w);
+  else
+    maxpool_fwd_kernel<<<grid_for(work), kThreads, 0, (cudaStream_t)stream>>>((const bf16*)x, (bf16*)y, (uint8_t*)idx_u8,
+                                                                              N, H, W, C, P, Q, k, stride, pad_h, pad_w);
   TDL_LAUNCH_OK("maxpool_fwd_kernel");
   return 0;
 }
@@ -400,9 +506,13 @@ TDL_API int tdl_maxpool_bwd(const void* dy, const void* idx_u8, void* dx, int N,
   TDL_REQUIRE(C % 8 == 0, "C must be a multiple of 8");
   const int64_t work = (int64_t)N * H * W * (C / 8);
   if (work == 0) return 0;
-  maxpool_bwd_kernel<<<grid_for(work), kThreads, 0, (cudaStream_t)stream>>>((const bf16*)dy, (const uint8_t*)idx_u8,
-                                                                            (bf16*)dx, N, H, W, C, P, Q, k, stride,
-                                                                            pad_h, pad_w);
+  if (k == 3 && stride == 2 && (int64_t)N * H < (1ll << 31))
+    maxpool_bwd_rows_kernel<3, 2><<<N * H, kThreads, 0, (cudaStream_t)stream>>>(
+        (const bf16*)dy, (const uint8_t*)idx_u8, (bf16*)dx, H, W, C, P, Q, pad_h, pad_w);
+  else
+    maxpool_bwd_kernel<<<grid_for(work), kThreads, 0, (cudaStream_t)stream>>>((const bf16*)dy, (const uint8_t*)idx_u8,
+                                                                              (bf16*)dx, N, H, W, C, P, Q, k, stride,
+                                                                              pad_h, pad_w);
   TDL_LAUNCH_OK("maxpool_bwd_kernel");
   return 0;
 }

@@ -100,6 +100,14 @@ int tdl_depthwise3x3_tma_wgrad(const void* x, const void* dy, float* dw, float* 
 int tdl_depthwise3x3_wgrad(const void* x, const void* dy, const void* ymask, float* dw, float* dbias, int N, int H,
                            int W, int C, int P, int Q, int stride, int dil, int pad_h, int pad_w, int relu_in,
                            void* stream);
+/* Convolution with 1..4 output channels (decoder 3x3 -> 1 logit).  CUDA-core dot products; weight is the
+ * fp32 master [K,R,S,C]; stride 1; dw / dbias are accumulated into. */
+int tdl_conv2d_smallk_fwd(const void* x, const float* w, const float* bias, void* y, int N, int H, int W, int C, int K,
+                          int R, int S, int dil, int pad_h, int pad_w, int P, int Q, void* stream);
+int tdl_conv2d_smallk_bwd_data(const void* dy, const float* w, void* dx, int N, int H, int W, int C, int K, int R,
+                               int S, int dil, int pad_h, int pad_w, int P, int Q, void* stream);
+int tdl_conv2d_smallk_bwd_weight(const void* x, const void* dy, float* dw, float* dbias, int N, int H, int W, int C,
+                                 int K, int R, int S, int dil, int pad_h, int pad_w, int P, int Q, void* stream);
 int tdl_upsample_fwd(const void* x, void* y, int N, int H, int W, int C, int OH, int OW, int is_bf16, void* stream);
 int tdl_upsample_bwd(const void* dy, float* dx, int N, int H, int W, int C, int OH, int OW, int is_bf16, void* stream);
 int tdl_u8_to_bf16_normalize(const void* x_u8, void* y_bf16, int64_t pixels, int C, int Cpad, const float* mean,

@@ -160,16 +160,18 @@ def nvls():
     for nbytes in sizes:
         nn = nbytes // 4
         res = {}
-        for blocks in (32, 64, 128):
-            t = timed(lambda: comm.fused_step(0, nn, kind=1, grad_is_bf16=False, zero_grad=False, m1=m1, m2=None,
-                                              lr_state=lr_state, a=0.9, b=0.0, c=0.0, mode=3, max_blocks=blocks),
-                      iters=10)
-            res[f"nvls_b{blocks}_us"] = t * 1e3
+        for mode in (3, 4):
+            for blocks in (32, 64, 128):
+                t = timed(lambda: comm.fused_step(0, nn, kind=1, grad_is_bf16=False, zero_grad=False, m1=m1, m2=None,
+                                                  lr_state=lr_state, a=0.9, b=0.0, c=0.0, mode=mode,
+                                                  max_blocks=blocks), iters=10)
+                res[f"nvls_u{4 if mode == 3 else 8}_b{blocks}_us"] = t * 1e3
         t2 = timed(lambda: comm.fused_step(0, nn, kind=1, grad_is_bf16=False, zero_grad=False, m1=m1, m2=None,
                                            lr_state=lr_state, a=0.9, b=0.0, c=0.0, mode=2, max_blocks=128), iters=10)
         g2 = gbuf.tensor()[:nn]
         tn = timed(lambda: dist.all_reduce(g2), iters=10)
         best = min(res.values())
+        res["best_cfg"] = min(res, key=res.get)
         # NVLS roofline: each direction of a GPU's links carries ~bytes (S/W pulled + (W-1)/W*S multicast in, and the mirror out)
         res.update(bytes=nbytes, best_nvls_us=best, two_shot_us=t2 * 1e3, nccl_allreduce_us=tn * 1e3,
                    speedup_vs_two_shot=t2 * 1e3 / best, speedup_vs_nccl_allreduce=tn * 1e3 / best,

@@ -225,6 +225,60 @@ class _ConvNative(torch.autograd.Function):
         return dx, dw, db, None, None, None, None, None, None
 
 
+class _ConvSmallK(torch.autograd.Function):
+    """1..4 output channels, stride 1: CUDA-core dot-product kernels (csrc/smallk_conv.cu; SURVEY K4 -- the
+    decoder's 3x3 conv to one logit channel, core/resnet.py:487-492)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, dil, pads, out_hw):
+        from . import native_ops as O
+
+        ctx.weight_param, ctx.bias_param = weight, bias
+        pt, pb, pl, pr = pads
+        wd = weight.detach().contiguous()
+        y = O.conv2d_smallk_fwd(x, wd, None if bias is None else bias.detach(), dil, pt, pl, out_hw)
+        _count(1)
+        ctx.save_for_backward(x, wd)
+        ctx.cfg = (dil, pt, pl, tuple(x.shape))
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        from . import native_ops as O
+
+        x, wd = ctx.saved_tensors
+        dil, pt, pl, xshape = ctx.cfg
+        dy = dy.contiguous()
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dx = O.conv2d_smallk_bwd_data(dy, wd, xshape, dil, pt, pl)
+            _count(1)
+        wp, bp = ctx.weight_param, ctx.bias_param
+        want_w = ctx.needs_input_grad[1]
+        want_b = bp is not None and ctx.needs_input_grad[2]
+        if want_w:
+            direct_w = _direct_ok(wp)
+            direct_b = want_b and _direct_ok(bp)
+            gw = wp.grad if direct_w else torch.zeros_like(wd)
+            gb = None
+            if want_b:
+                gb = bp.grad if direct_b else torch.zeros(wd.shape[0], dtype=torch.float32, device=x.device)
+            O.conv2d_smallk_bwd_weight(x, dy, gw, gb, dil, pt, pl)
+            _count(1)
+            if direct_w:
+                _notify(wp)
+            else:
+                dw = gw
+            if want_b:
+                if direct_b:
+                    _notify(bp)
+                else:
+                    db = gb
+        elif want_b:
+            db = dy.float().sum((0, 1, 2))
+        return dx, dw, db, None, None, None
+
+
 def conv2d(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None, stride: int = 1,
            dil: int = 1, padding="SAME", want_stats: bool = False, want_tap: bool = False):
     """NHWC convolution, weight [K, R, S, C] (fp32 master).  TF 'SAME' geometry by default.
@@ -240,6 +294,9 @@ def conv2d(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] =
         C = c
     assert c == C, f"channel mismatch: input {c} vs weight {C}"
     P, Q, pt, pb, pl, pr = conv_pads(h, w, Rk, Sk, stride, dil, padding)
+    if (_native_ok(x) and K <= 4 and stride == 1 and Rk * Sk <= 9 and C % 8 == 0 and C <= 2048
+            and not (want_stats or want_tap)):
+        return _ConvSmallK.apply(x.contiguous(), weight, bias, dil, (pt, pb, pl, pr), (P, Q))
     if _native_ok(x) and C % 8 == 0 and K % 8 == 0 and stride <= 2:
         if want_stats or want_tap:
             out = _ConvNative.apply(x.contiguous(), weight, bias, stride, dil, (pt, pb, pl, pr), (P, Q), want_stats,

@@ -439,3 +439,39 @@ def depthwise3x3_wgrad(x, dy, ymask, stride, dil, pad_h, pad_w, relu_in, want_bi
                                         _i(int(relu_in)), N.stream_ptr())
     N.check(rc, "tdl_depthwise3x3_wgrad")
     return dw, db
+
+
+def conv2d_smallk_fwd(x, w_krsc, bias, dil, pad_h, pad_w, out_hw):
+    """K <= 4 output channels, stride 1 (csrc/smallk_conv.cu); ``w_krsc`` is the fp32 master weight."""
+    _chk_bf16_nhwc(x, "x")
+    n, h, w, c = x.shape
+    K, R, S, _ = w_krsc.shape
+    P, Q = out_hw
+    y = torch.empty((n, P, Q, K), dtype=torch.bfloat16, device=x.device)
+    rc = N.lib().tdl_conv2d_smallk_fwd(N.ptr(x), N.ptr(w_krsc), N.ptr(bias), N.ptr(y),
+                                       _i(n), _i(h), _i(w), _i(c), _i(K), _i(R), _i(S), _i(dil), _i(pad_h), _i(pad_w),
+                                       _i(P), _i(Q), N.stream_ptr())
+    N.check(rc, "tdl_conv2d_smallk_fwd")
+    return y
+
+
+def conv2d_smallk_bwd_data(dy, w_krsc, in_shape, dil, pad_h, pad_w):
+    n, h, w, c = in_shape
+    K, R, S, _ = w_krsc.shape
+    P, Q = dy.shape[1], dy.shape[2]
+    dx = torch.empty(in_shape, dtype=torch.bfloat16, device=dy.device)
+    rc = N.lib().tdl_conv2d_smallk_bwd_data(N.ptr(dy), N.ptr(w_krsc), N.ptr(dx), _i(n), _i(h), _i(w), _i(c), _i(K),
+                                            _i(R), _i(S), _i(dil), _i(pad_h), _i(pad_w), _i(P), _i(Q), N.stream_ptr())
+    N.check(rc, "tdl_conv2d_smallk_bwd_data")
+    return dx
+
+
+def conv2d_smallk_bwd_weight(x, dy, dw, dbias, dil, pad_h, pad_w):
+    """Accumulates into ``dw`` (fp32 [K,R,S,C]) and, when given, ``dbias`` (fp32 [K])."""
+    n, h, w, c = x.shape
+    K, R, S, _ = dw.shape
+    P, Q = dy.shape[1], dy.shape[2]
+    rc = N.lib().tdl_conv2d_smallk_bwd_weight(N.ptr(x), N.ptr(dy), N.ptr(dw), N.ptr(dbias),
+                                              _i(n), _i(h), _i(w), _i(c), _i(K), _i(R), _i(S), _i(dil), _i(pad_h),
+                                              _i(pad_w), _i(P), _i(Q), N.stream_ptr())
+    N.check(rc, "tdl_conv2d_smallk_bwd_weight")

@@ -141,6 +141,34 @@ def test_conv_dgrad_strided_parity_classes(O, case):
     assert rel_err(dx, gx[:, :, pt:pt + H, pt:pt + H].permute(0, 2, 3, 1)) < 2e-2
 
 
+@pytest.mark.parametrize("case", [(4, 26, 512, 1, 3, 1, True), (2, 13, 264, 2, 3, 2, False), (3, 9, 64, 4, 1, 1, True)])
+def test_conv_small_k_decoder_head(O, case):
+    """K <= 4 output channels (the decoder's 3x3 -> 1 logit, core/resnet.py:487-492): CUDA-core kernels, fwd + both grads."""
+    from tensorflowdistributedlearning_b200.ops import functional as Fn
+
+    N, H, C, K, R, dil, use_bias = case
+    torch.manual_seed(3)
+    x = torch.randn(N, H, H, C, device="cuda").bfloat16().requires_grad_(True)
+    w = (torch.randn(K, R, R, C, device="cuda") / math.sqrt(R * R * C)).requires_grad_(True)
+    b = torch.randn(K, device="cuda").requires_grad_(True) if use_bias else None
+    y = Fn.conv2d(x, w, b, stride=1, dil=dil)
+    assert "ConvSmallK" in type(y.grad_fn).__name__
+    g = torch.randn_like(y)
+    y.backward(g)
+    xr = x.detach().float().requires_grad_(True)
+    wr = w.detach().bfloat16().float().requires_grad_(True)
+    br = b.detach().clone().requires_grad_(True) if use_bias else None
+    pad = dil * (R - 1) // 2
+    yr = F.conv2d(xr.permute(0, 3, 1, 2), wr.permute(0, 3, 1, 2), br, padding=pad, dilation=dil).permute(0, 2, 3, 1)
+    yr.backward(g.float())
+    assert y.shape == yr.shape
+    assert rel_err(y, yr) < 1e-2
+    assert rel_err(x.grad, xr.grad) < 1e-2
+    assert rel_err(w.grad, wr.grad) < 1e-2
+    if use_bias:
+        assert rel_err(b.grad, br.grad) < 1e-2
+
+
 @pytest.mark.parametrize("rows,C,relu,res", [(4096, 64, True, False), (5000, 256, True, True), (777, 2048, False, False)])
 def test_batch_norm_fwd_bwd(O, rows, C, relu, res):
     torch.manual_seed(3)
@@ -274,6 +302,7 @@ def test_spatial_ops(O):
 
     torch.manual_seed(7)
     _native_vs_oracle(lambda t: pooling.max_pool_same(t, 3, 2), [torch.randn(4, 51, 51, 128, device="cuda").bfloat16()], 2e-2)
+    _native_vs_oracle(lambda t: pooling.max_pool_same(t, 3, 2), [torch.randn(2, 112, 112, 64, device="cuda").bfloat16()], 2e-2)
     _native_vs_oracle(lambda t: pooling.max_pool(t, 3, 2, (1, 1, 1, 1)),
                       [torch.randn(2, 56, 56, 64, device="cuda").bfloat16().relu()], 2e-2)  # ties after ReLU
     _native_vs_oracle(lambda t: pooling.global_avg_pool(t, True), [torch.randn(8, 7, 7, 2048, device="cuda").bfloat16()], 2e-2)
