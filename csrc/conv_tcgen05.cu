@@ -47,13 +47,14 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 // dims/box/estr are innermost-first; strides are derived for a dense tensor.
-static int encode_bf16(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint32_t* box,
-                       const uint32_t* estr, const uint64_t* strides_bytes = nullptr) {
+static int encode_map(CUtensorMap* m, CUtensorMapDataType dtype, int elem_bytes, CUtensorMapSwizzle swizzle,
+                      const void* base, int rank, const uint64_t* dims, const uint32_t* box, const uint32_t* estr,
+                      const uint64_t* strides_bytes) {
   EncodeTiledFn fn = get_encode_fn();
   if (!fn) return tdl::fail(-3, "%s%s", "cuTensorMapEncodeTiled entry point unavailable", "");
   cuuint64_t gdim[5], gstr[5];
   cuuint32_t b[5], e[5];
-  uint64_t pitch = 2;
+  uint64_t pitch = (uint64_t)elem_bytes;
   for (int i = 0; i < rank; ++i) {
     gdim[i] = dims[i];
     b[i] = box[i];
@@ -61,9 +62,8 @@ static int encode_bf16(CUtensorMap* m, const void* base, int rank, const uint64_
     pitch *= dims[i];
     if (i + 1 < rank) gstr[i] = strides_bytes ? strides_bytes[i] : pitch;  // stride of dimension i+1, bytes
   }
-  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gdim, gstr, b, e,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUresult r = fn(m, dtype, (cuuint32_t)rank, const_cast<void*>(base), gdim, gstr, b, e, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     snprintf(tdl::err_buf(), 512,
              "cuTensorMapEncodeTiled failed (%d): rank %d dims [%llu,%llu,%llu,%llu] box [%u,%u,%u,%u]", (int)r, rank,
@@ -73,6 +73,12 @@ static int encode_bf16(CUtensorMap* m, const void* base, int rank, const uint64_
     return -4;
   }
   return 0;
+}
+
+static int encode_bf16(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint32_t* box,
+                       const uint32_t* estr, const uint64_t* strides_bytes = nullptr) {
+  return encode_map(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, CU_TENSOR_MAP_SWIZZLE_128B, base, rank, dims, box, estr,
+                    strides_bytes);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -88,6 +94,8 @@ struct Geometry {
   int num_kb;              // ceil(C / 64)
   int n_tiles;             // Cout tiles (fprop)
   int relu, has_bias, has_res;
+  // first-layer ("stem") mode only: byte pitches of the haloed space-to-depth patch in shared memory
+  int sp_plane, sp_row, sp_tx, sp_wbytes;
 };
 
 // Pick the (TN, TH, TW) pixel patch with the best row utilisation for `rows` GEMM rows.
@@ -136,7 +144,10 @@ template <int BLOCK_N>
 struct FpropCfg {
   static constexpr int kBBytes = BLOCK_N * kBlockK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kTmemCols = 2 * BLOCK_N;  // double-buffered accumulator
+  // accumulator ring in TMEM: narrow tiles finish in a few hundred ns, so four buffers keep the MMA warp from waiting
+  // on the epilogue's hand-back latency every other tile
+  static constexpr int kAccBufs = BLOCK_N <= 128 ? 4 : 2;
+  static constexpr int kTmemCols = kAccBufs * BLOCK_N;
   static constexpr int kOutBufs = 2;             // 128-row x 64-channel bf16 staging tiles for the TMA stores
   static constexpr int kOutBytes = kOutBufs * kBlockM * 128;
   static constexpr int kStatBytes = 4 * 2 * 64 * 4;  // per-warp (sum, sumsq) partials of one 64-channel chunk
@@ -144,7 +155,7 @@ struct FpropCfg {
   static constexpr int kAlignSlack = 384;  // the dynamic smem window is 1 KB aligned in practice; checked at run time
   static constexpr int kStages = (227 * 1024 - kOutBytes - kStatBytes - kAlignSlack - kBarBytes) / kStageBytes;
   static constexpr int kSmemBytes = kStages * kStageBytes + kOutBytes + kStatBytes + kAlignSlack + kBarBytes;
-  static_assert((2 * kStages + 4) * 8 + 4 <= kBarBytes, "barrier region too small");
+  static_assert((2 * kStages + 2 * kAccBufs + 1) * 8 + 4 <= kBarBytes, "barrier region too small");
 };
 
 // Column sums over the 32 rows held by a warp: lane l ends with the total of column l ("transpose-reduce": each
@@ -165,7 +176,16 @@ __device__ __forceinline__ float warp_column_sum(float (&v)[32], int lane) {
 
 // kFused: bias / residual / ReLU present in the epilogue.  kStats: per-channel (sum, sum of squares) of the bf16
 // output accumulated into this CTA's slot of `stats` ([gridDim.x][2][K] fp32) for the BatchNorm that follows.
-template <int BLOCK_N, bool kFused, bool kStats>
+//
+// kStem: first-layer mode for a stride-2 convolution on <= 4 input channels (7x7/3x3 roots: core/resnet.py:219-224,
+// :164, core/xception.py:352).  The image arrives space-to-depth packed as two 8-channel planes
+// [N][H/2][plane][W/2][8] (tdl_conv_stem_pack), which turns the stride-2 RxS conv into a stride-1 (R/2+1)^2-tap conv on
+// 16 channels.  A GEMM tile is ONE output row (<= 120 pixels): one TMA box brings the haloed patch
+// [taps_h][plane][TW + taps_w - 1 pixels][8 ch] into shared memory un-swizzled, and because a pixel is exactly one
+// 16-byte core-matrix row, every tap's A operand is just that patch at a shifted start address (K-major "interleave"
+// descriptor: SBO = 8 pixels, LBO = plane pitch).  No im2col, no per-tap loads; the whole weight tensor
+// [K][taps*16] stays resident in shared memory.
+template <int BLOCK_N, bool kFused, bool kStats, bool kStem = false>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
                   const __grid_constant__ CUtensorMap tm_y, const Geometry g, const float* __restrict__ bias,
@@ -186,15 +206,17 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
   uint64_t* full_bar = bars;
   uint64_t* empty_bar = bars + kStages;
   uint64_t* tmem_full = bars + 2 * kStages;
-  uint64_t* tmem_empty = tmem_full + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  constexpr int kAcc = Cfg::kAccBufs;
+  uint64_t* tmem_empty = tmem_full + kAcc;
+  uint64_t* w_bar = tmem_empty + kAcc;  // stem mode: resident weights have landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_bar + 1);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
   const int m_tiles = g.tiles_n * g.tiles_h * g.tiles_w;
   const int total_tiles = m_tiles * g.n_tiles;
-  const int k_iters = g.R * g.S * g.num_kb;
+  const int k_iters = kStem ? 1 : g.R * g.S * g.num_kb;
   const uint32_t a_tx = (uint32_t)(g.TN * g.TH * g.TW) * 128u;
   const uint32_t stage_tx = a_tx + (uint32_t)Cfg::kBBytes;
 
@@ -209,10 +231,11 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
         ptx::mbar_init(&full_bar[i], 1);
         ptx::mbar_init(&empty_bar[i], 1);
       }
-      for (int i = 0; i < 2; ++i) {
+      for (int i = 0; i < kAcc; ++i) {
         ptx::mbar_init(&tmem_full[i], 1);
         ptx::mbar_init(&tmem_empty[i], 4);  // one arrival per epilogue warp
       }
+      ptx::mbar_init(w_bar, 1);
       ptx::fence_mbar_init();
     }
     __syncwarp();
@@ -232,12 +255,28 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
+      if constexpr (kStem) {
+        ptx::mbar_expect_tx(w_bar, (uint32_t)g.sp_wbytes);
+        for (int a = 0; a * 8192 < g.sp_wbytes; ++a) ptx::tma_load_2d(smem_b + a * 8192, &tm_w, w_bar, a * 64, 0);
+      }
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const int n_tile = tile % g.n_tiles;
         const int m_tile = tile / g.n_tiles;
         const int tw_i = m_tile % g.tiles_w;
         const int th_i = (m_tile / g.tiles_w) % g.tiles_h;
         const int tn_i = m_tile / (g.tiles_w * g.tiles_h);
+        if constexpr (kStem) {
+          // coordinates: (8-byte units along the plane line, plane, packed row, image); out-of-range = zero padding
+          ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+          ptx::mbar_expect_tx(&full_bar[stage], (uint32_t)g.sp_tx);
+          ptx::tma_load_4d(smem_a + stage * kABytes, &tm_x, &full_bar[stage], (tw_i * g.TW - g.pad_w) * 2, 0,
+                           th_i - g.pad_h, tn_i);
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+          continue;
+        }
         const int w_in = tw_i * g.TW * g.stride - g.pad_w;
         const int h_in = th_i * g.TH * g.stride - g.pad_h;
         const int n_in = tn_i * g.TN;
@@ -267,6 +306,9 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
+      if constexpr (kStem) {
+        if (blockIdx.x < total_tiles) ptx::mbar_wait(w_bar, 0);
+      }
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         ptx::mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
         ptx::tc_fence_after();
@@ -274,6 +316,26 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
         for (int it = 0; it < k_iters; ++it) {
           ptx::mbar_wait(&full_bar[stage], phase);
           ptx::tc_fence_after();
+          if constexpr (kStem) {
+            const uint32_t a_base = ptx::smem_u32(smem_a + stage * kABytes);
+            const uint32_t b_base = ptx::smem_u32(smem_b);
+            const int taps = g.R * g.S;
+            for (int t = 0; t < taps; ++t) {
+              const int r2 = t / g.S;
+              const int s2 = t - r2 * g.S;
+              const uint64_t a_desc = ptx::umma_smem_desc_nosw(a_base + (uint32_t)(r2 * g.sp_row + s2 * 16),
+                                                               (uint32_t)g.sp_plane, 128);
+              const uint64_t b_desc =
+                  ptx::umma_smem_desc_sw128(b_base + (uint32_t)((t >> 2) * 8192), 16, 1024) + (uint64_t)(2 * (t & 3));
+              ptx::umma_bf16(d_tmem, a_desc, b_desc, idesc, t > 0 ? 1u : 0u);
+            }
+            ptx::umma_commit(&empty_bar[stage]);
+            if (++stage == kStages) {
+              stage = 0;
+              phase ^= 1;
+            }
+            continue;
+          }
           const uint64_t a_desc = ptx::umma_smem_desc_sw128(ptx::smem_u32(smem_a + stage * kABytes), 16, 1024);
           const uint64_t b_desc = ptx::umma_smem_desc_sw128(ptx::smem_u32(smem_b + stage * Cfg::kBBytes), 16, 1024);
 #pragma unroll
@@ -289,7 +351,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
           }
         }
         ptx::umma_commit(&tmem_full[acc]);  // accumulator complete -> epilogue
-        if (++acc == 2) {
+        if (++acc == kAcc) {
           acc = 0;
           acc_phase ^= 1;
         }
@@ -421,13 +483,15 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
               const int which = idx >> 6, ch = co_chunk + (idx & 63);
               if (ch < g.K) {
                 const float tot = smem_stat[idx] + smem_stat[128 + idx] + smem_stat[256 + idx] + smem_stat[384 + idx];
-                slot[(size_t)which * g.K + ch] += tot;
+                // fire-and-forget reduction (RED): a load-add-store here would stall this warp, and through the
+                // next named barrier the whole epilogue, for an L2 round trip per 64-channel chunk
+                atomicAdd(&slot[(size_t)which * g.K + ch], tot);
               }
             }
           }
         }
       }
-      if (++acc == 2) {
+      if (++acc == kAcc) {
         acc = 0;
         acc_phase ^= 1;
       }
@@ -636,6 +700,80 @@ __global__ void weight_prep_kernel(const float* __restrict__ w, bf16* __restrict
     if (w_fprop) w_fprop[i] = v;
     if (w_dgrad) w_dgrad[((size_t)c * taps + (taps - 1 - t)) * K + k] = v;
   }
+}
+
+// ------------------------------------------------------------------------------------------
+// first-layer ("stem") helpers
+// ------------------------------------------------------------------------------------------
+// x [N,H,W,C] bf16 (C <= 4)  ->  planes [N][H2][2][W2][8] bf16, packed channel cp = (dy*2 + dx)*C + c holds
+// x[2*h2 + dy][2*w2 + dx][c]; lanes >= 4*C and pixels beyond an odd H/W are zero.
+__global__ void stem_pack_kernel(const bf16* __restrict__ x, bf16* __restrict__ planes, int N, int H, int W, int C,
+                                 int H2, int W2) {
+  const int64_t total = (int64_t)N * H2 * 2 * W2;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int w2 = (int)(i % W2);
+    const int plane = (int)((i / W2) & 1);
+    const int64_t nh = i / (2 * W2);
+    const int h2 = (int)(nh % H2);
+    const int n = (int)(nh / H2);
+    bf16x8 out;
+    bf16* o = reinterpret_cast<bf16*>(&out);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int cp = plane * 8 + j;
+      bf16 v = __float2bfloat16(0.f);
+      if (cp < 4 * C) {
+        const int blk = cp / C;
+        const int c = cp - blk * C;
+        const int h = 2 * h2 + (blk >> 1);
+        const int w = 2 * w2 + (blk & 1);
+        if (h < H && w < W) v = x[(((int64_t)n * H + h) * W + w) * C + c];
+      }
+      o[j] = v;
+    }
+    st8(planes + i * 8, out);
+  }
+}
+
+// fp32 master [K, R, S, C]  ->  bf16 [K][Th*Tw][16] for the space-to-depth problem: packed tap (r2, s2), channel
+// cp = (dy*2+dx)*C + c  <-  original tap r = 2*(r2 - pad2_h) + dy + pad_h (same for s), zero when outside the filter.
+__global__ void stem_weight_prep_kernel(const float* __restrict__ w, bf16* __restrict__ out, int K, int R, int S, int C,
+                                        int Th, int Tw, int pad_h, int pad_w, int pad2_h, int pad2_w) {
+  const int total = K * Th * Tw * 16;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int cp = i & 15;
+    const int t = (i >> 4) % (Th * Tw);
+    const int k = (i >> 4) / (Th * Tw);
+    float v = 0.f;
+    if (cp < 4 * C) {
+      const int blk = cp / C;
+      const int c = cp - blk * C;
+      const int r = 2 * (t / Tw - pad2_h) + (blk >> 1) + pad_h;
+      const int sx = 2 * (t % Tw - pad2_w) + (blk & 1) + pad_w;
+      if (r >= 0 && r < R && sx >= 0 && sx < S) v = w[(((size_t)k * R + r) * S + sx) * C + c];
+    }
+    out[i] = __float2bfloat16(v);
+  }
+}
+
+template <bool kStats>
+static int launch_stem(const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& ty, const Geometry& g,
+                       float* stats, int* nparts, cudaStream_t st) {
+  using Cfg = FpropCfg<64>;
+  static_assert(Cfg::kStages * Cfg::kBBytes >= 4 * 8192, "resident stem weights need 32 KB of the B region");
+  static bool attr_set = false;
+  if (!attr_set) {
+    TDL_CUDA_OK(cudaFuncSetAttribute(conv_fprop_kernel<64, false, kStats, true>,
+                                     cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    attr_set = true;
+  }
+  const int total = g.tiles_n * g.tiles_h * g.tiles_w;
+  const int grid = total < tdl::num_sms() ? total : tdl::num_sms();
+  if (nparts) *nparts = grid;
+  conv_fprop_kernel<64, false, kStats, true><<<grid, kThreads, Cfg::kSmemBytes, st>>>(tx, tw, ty, g, nullptr, nullptr,
+                                                                                      stats);
+  TDL_LAUNCH_OK("conv_fprop_kernel(stem)");
+  return 0;
 }
 
 template <int BLOCK_N, bool kFused, bool kStats>
@@ -859,4 +997,103 @@ TDL_API int tdl_conv2d_weight_prep(const float* w, void* w_fprop, void* w_dgrad,
   weight_prep_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(w, (bf16*)w_fprop, (bf16*)w_dgrad, K, taps, C);
   TDL_LAUNCH_OK("weight_prep_kernel");
   return 0;
+}
+
+// ---- first layer (stride-2 conv on <= 4 channels) -------------------------------------------------------------
+static void stem_taps(int R, int pad, int* taps, int* pad2) {
+  *pad2 = (pad + 1) / 2;
+  const int hi = (R - 1 - pad) >= 0 ? (R - 1 - pad) / 2 : -((pad - R + 2) / 2);
+  *taps = hi + *pad2 + 1;
+}
+
+// x [N,H,W,C] bf16 -> planes [N][ceil(H/2)][2][ceil(W/2)][8] bf16 (space-to-depth, two 8-channel planes)
+TDL_API int tdl_conv_stem_pack(const void* x, void* planes, int N, int H, int W, int C, void* stream) {
+  TDL_REQUIRE(C >= 1 && C <= 4, "stem pack handles 1..4 input channels");
+  const int H2 = (H + 1) / 2, W2 = (W + 1) / 2;
+  const int64_t total = (int64_t)N * H2 * 2 * W2;
+  if (total == 0) return 0;
+  int64_t blocks = cdiv(total, 256);
+  if (blocks > (int64_t)num_sms() * 16) blocks = (int64_t)num_sms() * 16;
+  stem_pack_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>((const bf16*)x, (bf16*)planes, N, H, W, C, H2, W2);
+  TDL_LAUNCH_OK("stem_pack_kernel");
+  return 0;
+}
+
+// Number of bf16 elements of the packed weight tensor [K][Th*Tw][16] for this filter / padding.
+TDL_API int tdl_conv_stem_weight_elems(int K, int R, int S, int pad_h, int pad_w) {
+  int th, tw, p2h, p2w;
+  stem_taps(R, pad_h, &th, &p2h);
+  stem_taps(S, pad_w, &tw, &p2w);
+  return K * th * tw * 16;
+}
+
+TDL_API int tdl_conv_stem_weight_prep(const float* w, void* w_packed, int K, int R, int S, int C, int pad_h, int pad_w,
+                                      void* stream) {
+  TDL_REQUIRE(C >= 1 && C <= 4, "stem handles 1..4 input channels");
+  int th, tw, p2h, p2w;
+  stem_taps(R, pad_h, &th, &p2h);
+  stem_taps(S, pad_w, &tw, &p2w);
+  const int total = K * th * tw * 16;
+  stem_weight_prep_kernel<<<(int)cdiv(total, 256), 256, 0, (cudaStream_t)stream>>>(w, (bf16*)w_packed, K, R, S, C, th,
+                                                                                tw, pad_h, pad_w, p2h, p2w);
+  TDL_LAUNCH_OK("stem_weight_prep_kernel");
+  return 0;
+}
+
+// y[N,P,Q,K] = stride-2 conv of the packed image with the packed weights.  (H, W) are the ORIGINAL image size.
+// stats_partial / nparts_host as in tdl_conv2d_fprop_stats_bf16 (both null = no statistics).
+TDL_API int tdl_conv_stem_fprop(const void* planes, const void* w_packed, void* y, int N, int H, int W, int K, int R,
+                                int S, int pad_h, int pad_w, int P, int Q, float* stats_partial, int* nparts_host,
+                                void* stream) {
+  TDL_REQUIRE(K % 8 == 0 && K >= 8 && K <= 64, "stem kernel handles 8..64 output channels (multiple of 8)");
+  TDL_REQUIRE((stats_partial == nullptr) == (nparts_host == nullptr), "stats buffers come in pairs");
+  int th, tw, p2h, p2w;
+  stem_taps(R, pad_h, &th, &p2h);
+  stem_taps(S, pad_w, &tw, &p2w);
+  TDL_REQUIRE(th >= 1 && tw >= 1 && th * tw <= 16, "stem kernel handles at most 16 packed taps (filters up to 7x7)");
+  const int H2 = (H + 1) / 2, W2 = (W + 1) / 2;
+  Geometry g;
+  memset(&g, 0, sizeof(g));
+  g.N = N; g.H = H2; g.W = W2; g.C = 16; g.P = P; g.Q = Q; g.K = K; g.R = th; g.S = tw; g.stride = 1; g.dil = 1;
+  g.pad_h = p2h; g.pad_w = p2w;
+  g.TN = 1; g.TH = 1;
+  const int w_tiles = (int)cdiv(Q, 120);
+  g.TW = (int)cdiv(Q, w_tiles);
+  g.tiles_n = N; g.tiles_h = P; g.tiles_w = (int)cdiv(Q, g.TW);
+  g.num_kb = 1; g.n_tiles = 1;
+  const int box_px = g.TW + tw - 1;
+  g.sp_plane = box_px * 16;
+  g.sp_row = 2 * g.sp_plane;
+  g.sp_tx = th * g.sp_row;
+  g.sp_wbytes = (int)cdiv(th * tw * 16, 64) * 8192;
+  TDL_REQUIRE(box_px * 2 <= 256, "stem tile too wide for one TMA box");
+  TDL_REQUIRE((th - 1) * g.sp_row + g.sp_plane + (tw - 1) * 16 + 2048 <= kABytes, "stem patch exceeds its smem stage");
+  CUtensorMap tx, tmw, ty;
+  {
+    // the plane line of W2 pixels x 16 bytes is addressed in 8-byte units so one box row can span the whole tile
+    uint64_t dims[4] = {(uint64_t)W2 * 2, 2, (uint64_t)H2, (uint64_t)N};
+    uint64_t strides[3] = {(uint64_t)W2 * 16, (uint64_t)W2 * 32, (uint64_t)W2 * 32 * H2};
+    uint32_t box[4] = {(uint32_t)box_px * 2, 2, (uint32_t)th, 1};
+    uint32_t es[4] = {1, 1, 1, 1};
+    int rc = encode_map(&tx, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, CU_TENSOR_MAP_SWIZZLE_NONE, planes, 4, dims, box, es,
+                        strides);
+    if (rc) return rc;
+  }
+  {
+    uint64_t dims[2] = {(uint64_t)(th * tw * 16), (uint64_t)K};
+    uint32_t box[2] = {64, 64};
+    uint32_t es[2] = {1, 1};
+    int rc = encode_bf16(&tmw, w_packed, 2, dims, box, es);
+    if (rc) return rc;
+  }
+  {
+    uint64_t dims[4] = {(uint64_t)K, (uint64_t)Q, (uint64_t)P, (uint64_t)N};
+    uint32_t box[4] = {64, (uint32_t)g.TW, 1, 1};
+    uint32_t es[4] = {1, 1, 1, 1};
+    int rc = encode_bf16(&ty, y, 4, dims, box, es);
+    if (rc) return rc;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (stats_partial) return launch_stem<true>(tx, tmw, ty, g, stats_partial, nparts_host, st);
+  return launch_stem<false>(tx, tmw, ty, g, nullptr, nullptr, st);
 }

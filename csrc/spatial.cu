@@ -98,22 +98,24 @@ maxpool_bwd_kernel(const bf16* __restrict__ dy, const uint8_t* __restrict__ idx,
   }
 }
 
-// Compile-time window/stride variants, one CTA per (image, row): no 64-bit index arithmetic or runtime divisions in
-// the inner loop (the generic kernels above spend most of their issue slots on those), all window loads in flight
+// Compile-time window/stride variants, one thread per (pixel, 8 channels) with blockIdx.y = image: no 64-bit index
+// arithmetic or runtime-stride divisions (the generic kernels above spend most of their issue slots on those), all window loads in flight
 // at once.  Used for the 3x3 stride-2 pool of the ResNet root (core/resnet.py:241).
 template <int K, int S>
 __global__ void __launch_bounds__(kThreads)
 maxpool_fwd_rows_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, uint8_t* __restrict__ idx, int H, int W,
                         int C, int P, int Q, int pad_h, int pad_w) {
   const int c8 = C >> 3;
-  const int n = blockIdx.x / P;
-  const int p = blockIdx.x - n * P;
+  const int n = blockIdx.y;
   const bf16* xn = x + (int64_t)n * H * W * C;
-  const int64_t orow = ((int64_t)n * P + p) * Q * C;
-  const int h0 = p * S - pad_h;
-  for (int i = threadIdx.x; i < Q * c8; i += kThreads) {
-    const int q = i / c8;
-    const int cv = i - q * c8;
+  const int64_t orow = (int64_t)n * P * Q * C;
+  const int i = blockIdx.x * kThreads + threadIdx.x;  // (p, q, cv) inside image n, 32-bit arithmetic only
+  if (i < P * Q * c8) {
+    const int pq = i / c8;
+    const int cv = i - pq * c8;
+    const int p = pq / Q;
+    const int q = pq - p * Q;
+    const int h0 = p * S - pad_h;
     const int w0 = q * S - pad_w;
     bf16x8 v[K * K];
     bool ok[K * K];
@@ -152,15 +154,17 @@ maxpool_bwd_rows_kernel(const bf16* __restrict__ dy, const uint8_t* __restrict__
                         int W, int C, int P, int Q, int pad_h, int pad_w) {
   constexpr int kCells = (K + S - 1) / S;  // output cells per axis whose window can cover one input pixel
   const int c8 = C >> 3;
-  const int n = blockIdx.x / H;
-  const int h = blockIdx.x - n * H;
+  const int n = blockIdx.y;
   const int64_t obase = (int64_t)n * P * Q * C;
-  const int64_t irow = ((int64_t)n * H + h) * W * C;
-  const int hp = h + pad_h;
-  const int p_hi = hp / S;  // the last output row whose window starts at or above this input row
-  for (int i = threadIdx.x; i < W * c8; i += kThreads) {
-    const int w = i / c8;
-    const int cv = i - w * c8;
+  const int64_t irow = (int64_t)n * H * W * C;
+  const int i = blockIdx.x * kThreads + threadIdx.x;  // (h, w, cv) inside image n
+  if (i < H * W * c8) {
+    const int hw = i / c8;
+    const int cv = i - hw * c8;
+    const int h = hw / W;
+    const int w = hw - h * W;
+    const int hp = h + pad_h;
+    const int p_hi = hp / S;  // the last output row whose window starts at or above this input row
     const int wq = w + pad_w;
     const int q_hi = wq / S;
     bf16x8 g[kCells * kCells];
@@ -490,8 +494,9 @@ TDL_API int tdl_maxpool_fwd(const void* x, void* y, void* idx_u8, int N, int H, 
   TDL_REQUIRE(k * k <= 255, "window too large");
   const int64_t work = (int64_t)N * P * Q * (C / 8);
   if (work == 0) return 0;
-  if (k == 3 && stride == 2 && (int64_t)N * P < (1ll << 31))
-    maxpool_fwd_rows_kernel<3, 2><<<N * P, kThreads, 0, (cudaStream_t)stream>>>((const bf16*)x, (bf16*)y,
+  if (k == 3 && stride == 2 && N <= 65535 && (int64_t)P * Q * C < (1ll << 31))
+    maxpool_fwd_rows_kernel<3, 2><<<dim3((unsigned)cdiv((int64_t)P * Q * (C / 8), kThreads), N), kThreads, 0,
+                                    (cudaStream_t)stream>>>((const bf16*)x, (bf16*)y,
                                                                                (uint8_t*)idx_u8, H, W, C, P, Q, pad_h,
                                                                                pad_w);
   else
@@ -506,8 +511,9 @@ TDL_API int tdl_maxpool_bwd(const void* dy, const void* idx_u8, void* dx, int N,
   TDL_REQUIRE(C % 8 == 0, "C must be a multiple of 8");
   const int64_t work = (int64_t)N * H * W * (C / 8);
   if (work == 0) return 0;
-  if (k == 3 && stride == 2 && (int64_t)N * H < (1ll << 31))
-    maxpool_bwd_rows_kernel<3, 2><<<N * H, kThreads, 0, (cudaStream_t)stream>>>(
+  if (k == 3 && stride == 2 && N <= 65535 && (int64_t)H * W * C < (1ll << 31))
+    maxpool_bwd_rows_kernel<3, 2><<<dim3((unsigned)cdiv((int64_t)H * W * (C / 8), kThreads), N), kThreads, 0,
+                                    (cudaStream_t)stream>>>(
         (const bf16*)dy, (const uint8_t*)idx_u8, (bf16*)dx, H, W, C, P, Q, pad_h, pad_w);
   else
     maxpool_bwd_kernel<<<grid_for(work), kThreads, 0, (cudaStream_t)stream>>>((const bf16*)dy, (const uint8_t*)idx_u8,

@@ -285,6 +285,16 @@ __device__ __forceinline__ uint64_t umma_smem_desc_sw128(uint32_t smem_addr, uin
   d |= (uint64_t)2 << 61;
   return d;
 }
+// Same descriptor without swizzling ("interleave" canonical layout), K-major: rows of a core matrix are 16 bytes
+// apart, 8-row groups are `sbo_bytes` apart, the two 16-byte K halves of one K=16 step are `lbo_bytes` apart.
+__device__ __forceinline__ uint64_t umma_smem_desc_nosw(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  return d;
+}
 // Instruction descriptor for kind::f16 with bf16 inputs and fp32 accumulation.
 //   [4,6) D format (1 = f32), [7,10) A format (1 = bf16), [10,13) B format, bit 15 A major (1 = MN),
 //   bit 16 B major, [17,23) N >> 3, [24,29) M >> 4.

@@ -100,6 +100,16 @@ int tdl_depthwise3x3_tma_wgrad(const void* x, const void* dy, float* dw, float* 
 int tdl_depthwise3x3_wgrad(const void* x, const void* dy, const void* ymask, float* dw, float* dbias, int N, int H,
                            int W, int C, int P, int Q, int stride, int dil, int pad_h, int pad_w, int relu_in,
                            void* stream);
+/* First layer: stride-2 RxS convolution on 1..4 input channels (7x7 / 3x3 roots) on the tensor cores.  The image is
+ * packed space-to-depth into two 8-channel planes [N][ceil(H/2)][2][ceil(W/2)][8]; the weights into [K][taps*16]
+ * (tdl_conv_stem_weight_elems gives the element count).  K <= 64.  Optional fused BatchNorm partial statistics as in
+ * tdl_conv2d_fprop_stats_bf16 (pass both stats pointers or neither). */
+int tdl_conv_stem_pack(const void* x, void* planes, int N, int H, int W, int C, void* stream);
+int tdl_conv_stem_weight_elems(int K, int R, int S, int pad_h, int pad_w);
+int tdl_conv_stem_weight_prep(const float* w, void* w_packed, int K, int R, int S, int C, int pad_h, int pad_w,
+                              void* stream);
+int tdl_conv_stem_fprop(const void* planes, const void* w_packed, void* y, int N, int H, int W, int K, int R, int S,
+                        int pad_h, int pad_w, int P, int Q, float* stats_partial, int* nparts_host, void* stream);
 /* Convolution with 1..4 output channels (decoder 3x3 -> 1 logit).  CUDA-core dot products; weight is the
  * fp32 master [K,R,S,C]; stride 1; dw / dbias are accumulated into. */
 int tdl_conv2d_smallk_fwd(const void* x, const float* w, const float* bias, void* y, int N, int H, int W, int C, int K,

@@ -516,6 +516,40 @@ def group_perf_depthwise():
              dgrad_gbs=3 * gb / t_d * 1e3, wgrad_us=t_w * 1e3, wgrad_gbs=2 * gb / t_w * 1e3)
 
 
+def group_perf_stem():
+    """First-layer kernels (pack, weight prep, tcgen05 stem with fused statistics) vs cuDNN on the ResNet-50 /
+    Xception-41 / reference roots; max-pool 3x3 s2 fwd/bwd on the ResNet-50 shape."""
+    import torch
+    import torch.nn.functional as F
+    from tensorflowdistributedlearning_b200.ops import native_ops as O
+    from tensorflowdistributedlearning_b200.ops import functional as Fn
+
+    for (N, H, C, K, R, padding) in [(256, 224, 3, 64, 7, (3, 3, 3, 3)), (64, 299, 3, 32, 3, (1, 1, 1, 1)),
+                                     (32, 101, 2, 64, 3, "SAME")]:
+        x = torch.randn(N, H, H, C, device="cuda").bfloat16()
+        w = torch.randn(K, R, R, C, device="cuda") / (R * R * C) ** 0.5
+        P, Q, pt, pb, pl, pr = Fn.conv_pads(H, H, R, R, 2, 1, padding)
+        planes = O.conv_stem_pack(x)
+        wp = O.conv_stem_weight_prep(w, pt, pl)
+        t_pack = time_cuda(lambda: O.conv_stem_pack(x))
+        t_prep = time_cuda(lambda: O.conv_stem_weight_prep(w, pt, pl))
+        t_conv = time_cuda(lambda: O.conv_stem_fprop(planes, wp, (H, H), K, R, R, pt, pl, (P, Q), True))
+        xin = F.pad(x.permute(0, 3, 1, 2), (pl, pr, pt, pb))
+        w4 = w.bfloat16().permute(0, 3, 1, 2)
+        t_cudnn = time_cuda(lambda: F.conv2d(xin, w4, None, stride=2))
+        out_gb = N * P * Q * K * 2 / 1e9
+        emit(group="perf_stem", N=N, H=H, C=C, K=K, R=R, pack_us=t_pack * 1e3, wprep_us=t_prep * 1e3,
+             stem_us=t_conv * 1e3, stem_out_gbs=out_gb / t_conv * 1e3, cudnn_fprop_us=t_cudnn * 1e3)
+    x = torch.randn(256, 112, 112, 64, device="cuda").bfloat16()
+    y, idx = O.maxpool_fwd(x, 3, 2, 0, 0, (56, 56))
+    dy = torch.randn_like(y)
+    t_f = time_cuda(lambda: O.maxpool_fwd(x, 3, 2, 0, 0, (56, 56)))
+    t_b = time_cuda(lambda: O.maxpool_bwd(dy, idx, tuple(x.shape), 3, 2, 0, 0))
+    gb = x.numel() * 2 / 1e9
+    emit(group="perf_stem", op="maxpool3x3s2", fwd_us=t_f * 1e3, fwd_gbs=(gb * 1.25 + gb / 8) / t_f * 1e3,
+         bwd_us=t_b * 1e3, bwd_gbs=(gb * 1.25 + gb / 8) / t_b * 1e3)
+
+
 GROUPS = {
     "conv_fprop_basic": group_conv_fprop_basic,
     "conv_fprop_strided": group_conv_fprop_strided,
@@ -529,6 +563,7 @@ GROUPS = {
     "p2p_emulate": group_p2p_emulate,
     "model": group_model,
     "perf_depthwise": group_perf_depthwise,
+    "perf_stem": group_perf_stem,
 }
 
 

@@ -15,6 +15,7 @@ import torch.nn.functional as F
 
 from . import reference as R
 
+_STEM_NATIVE = True       # first-layer tcgen05 kernel (off = cuDNN for the C<=4 stem, used for A/B timing)
 _FORCE_REFERENCE = False  # flipped by tests / the proxy baseline to route everything through torch ops
 _LAUNCHES = 0             # native kernel launches issued through this module (bench "gpu_launches")
 
@@ -225,6 +226,55 @@ class _ConvNative(torch.autograd.Function):
         return dx, dw, db, None, None, None, None, None, None
 
 
+class _ConvStem(torch.autograd.Function):
+    """First layer: stride-2 conv on <= 4 input channels (7x7 / 3x3 roots, core/resnet.py:164,219-224;
+    core/xception.py:352).  Forward = space-to-depth pack + tcgen05 kernel with the haloed patch resident in shared
+    memory (csrc/conv_tcgen05.cu, kStem); BatchNorm partial statistics optionally fused.  The weight gradient of this
+    one layer (K*R*S*C <= 9408 values reduced over all pixels) stays on cuDNN's small-channel wgrad."""
+
+    @staticmethod
+    def forward(ctx, x, weight, pads, out_hw, want_stats):
+        from . import native_ops as O
+
+        K, Rk, Sk, C = weight.shape
+        pt, pb, pl, pr = pads
+        planes = O.conv_stem_pack(x)
+        wp = O.conv_stem_weight_prep(weight.detach().contiguous(), pt, pl)
+        res = O.conv_stem_fprop(planes, wp, (x.shape[1], x.shape[2]), K, Rk, Sk, pt, pl, out_hw, want_stats)
+        _count(3)
+        ctx.save_for_backward(x, weight)
+        ctx.cfg = (pads, want_stats)
+        if want_stats:
+            y, partials, nparts = res
+            partials = partials[:nparts]
+            ctx.mark_non_differentiable(partials)
+            return y, partials
+        return res
+
+    @staticmethod
+    def backward(ctx, dy, *rest):
+        x, weight = ctx.saved_tensors
+        (pt, pb, pl, pr), _ = ctx.cfg
+        K, Rk, Sk, C = weight.shape
+        need_dx, need_dw = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        w4 = weight.detach().to(x.dtype).permute(0, 3, 1, 2)
+        xin = x.permute(0, 3, 1, 2)
+        if pt != pb or pl != pr:
+            xin = F.pad(xin, (pl, pr, pt, pb))
+            padding = [0, 0]
+        else:
+            padding = [pt, pl]
+        gx, gw, _ = torch.ops.aten.convolution_backward(dy.contiguous().permute(0, 3, 1, 2), xin, w4, None, [2, 2], padding,
+                                                        [1, 1], False, [0, 0], 1, [need_dx, need_dw, False])
+        dx = dw = None
+        if need_dx:
+            gx = gx[:, :, pt:pt + x.shape[1], pl:pl + x.shape[2]] if padding == [0, 0] else gx
+            dx = gx.permute(0, 2, 3, 1).contiguous()
+        if need_dw:
+            dw = gw.permute(0, 2, 3, 1).float().contiguous()
+        return dx, dw, None, None, None
+
+
 class _ConvSmallK(torch.autograd.Function):
     """1..4 output channels, stride 1: CUDA-core dot-product kernels (csrc/smallk_conv.cu; SURVEY K4 -- the
     decoder's 3x3 conv to one logit channel, core/resnet.py:487-492)."""
@@ -294,6 +344,10 @@ def conv2d(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] =
         C = c
     assert c == C, f"channel mismatch: input {c} vs weight {C}"
     P, Q, pt, pb, pl, pr = conv_pads(h, w, Rk, Sk, stride, dil, padding)
+    if (_native_ok(x) and c <= 4 and stride == 2 and dil == 1 and bias is None and K % 8 == 0 and K <= 64
+            and max(Rk, Sk) <= 7 and not want_tap and _STEM_NATIVE):
+        out = _ConvStem.apply(x.contiguous(), weight, (pt, pb, pl, pr), (P, Q), want_stats)
+        return out
     if (_native_ok(x) and K <= 4 and stride == 1 and Rk * Sk <= 9 and C % 8 == 0 and C <= 2048
             and not (want_stats or want_tap)):
         return _ConvSmallK.apply(x.contiguous(), weight, bias, dil, (pt, pb, pl, pr), (P, Q))

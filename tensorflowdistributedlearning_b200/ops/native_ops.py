@@ -475,3 +475,45 @@ def conv2d_smallk_bwd_weight(x, dy, dw, dbias, dil, pad_h, pad_w):
                                               _i(n), _i(h), _i(w), _i(c), _i(K), _i(R), _i(S), _i(dil), _i(pad_h),
                                               _i(pad_w), _i(P), _i(Q), N.stream_ptr())
     N.check(rc, "tdl_conv2d_smallk_bwd_weight")
+
+
+def conv_stem_pack(x: torch.Tensor) -> torch.Tensor:
+    """[N,H,W,C<=4] bf16 -> space-to-depth planes [N, ceil(H/2), 2, ceil(W/2), 8] bf16 for the first-layer kernel."""
+    _chk_bf16_nhwc(x, "x")
+    n, h, w, c = x.shape
+    planes = torch.empty((n, (h + 1) // 2, 2, (w + 1) // 2, 8), dtype=torch.bfloat16, device=x.device)
+    rc = N.lib().tdl_conv_stem_pack(N.ptr(x), N.ptr(planes), _i(n), _i(h), _i(w), _i(c), N.stream_ptr())
+    N.check(rc, "tdl_conv_stem_pack")
+    return planes
+
+
+def conv_stem_weight_prep(w_krsc: torch.Tensor, pad_h: int, pad_w: int) -> torch.Tensor:
+    """fp32 master [K,R,S,C] -> bf16 [K, taps*16] for the space-to-depth problem."""
+    K, R, S, C = w_krsc.shape
+    elems = int(N.lib().tdl_conv_stem_weight_elems(_i(K), _i(R), _i(S), _i(pad_h), _i(pad_w)))
+    out = torch.empty((K, elems // K), dtype=torch.bfloat16, device=w_krsc.device)
+    rc = N.lib().tdl_conv_stem_weight_prep(N.ptr(w_krsc), N.ptr(out), _i(K), _i(R), _i(S), _i(C), _i(pad_h), _i(pad_w),
+                                           N.stream_ptr())
+    N.check(rc, "tdl_conv_stem_weight_prep")
+    return out
+
+
+def conv_stem_fprop(planes: torch.Tensor, w_packed: torch.Tensor, image_hw, K: int, R: int, S: int, pad_h: int,
+                    pad_w: int, out_hw, want_stats: bool = False):
+    """Stride-2 first-layer convolution on the tensor cores.  Returns y or (y, partials, nparts)."""
+    n = planes.shape[0]
+    h, w = image_hw
+    p, q = out_hw
+    y = torch.empty((n, p, q, K), dtype=torch.bfloat16, device=planes.device)
+    if want_stats:
+        partials = torch.empty((int(N.lib().tdl_num_sms()), 2, K), dtype=torch.float32, device=planes.device)
+        nparts = ctypes.c_int(0)
+        rc = N.lib().tdl_conv_stem_fprop(N.ptr(planes), N.ptr(w_packed), N.ptr(y), _i(n), _i(h), _i(w), _i(K), _i(R),
+                                         _i(S), _i(pad_h), _i(pad_w), _i(p), _i(q), N.ptr(partials),
+                                         ctypes.byref(nparts), N.stream_ptr())
+        N.check(rc, "tdl_conv_stem_fprop")
+        return y, partials, int(nparts.value)
+    rc = N.lib().tdl_conv_stem_fprop(N.ptr(planes), N.ptr(w_packed), N.ptr(y), _i(n), _i(h), _i(w), _i(K), _i(R), _i(S),
+                                     _i(pad_h), _i(pad_w), _i(p), _i(q), N.ptr(None), N.ptr(None), N.stream_ptr())
+    N.check(rc, "tdl_conv_stem_fprop")
+    return y

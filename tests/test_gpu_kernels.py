@@ -141,6 +141,33 @@ def test_conv_dgrad_strided_parity_classes(O, case):
     assert rel_err(dx, gx[:, :, pt:pt + H, pt:pt + H].permute(0, 2, 3, 1)) < 2e-2
 
 
+@pytest.mark.parametrize("case", [(2, 224, 3, 64, 7, "SAME"), (2, 224, 3, 64, 7, (3, 3, 3, 3)), (2, 299, 3, 32, 3, (1, 1, 1, 1)),
+                                  (3, 101, 2, 64, 3, "SAME"), (2, 64, 4, 40, 5, "SAME")])
+def test_conv_stem_space_to_depth_tcgen05(O, case):
+    """First-layer stride-2 conv on <= 4 channels: packed image + resident haloed patch (kStem), with fused BN statistics."""
+    from tensorflowdistributedlearning_b200.ops import functional as Fn
+
+    N, H, C, K, R, padding = case
+    torch.manual_seed(11)
+    x = torch.randn(N, H, H, C, device="cuda").bfloat16()
+    w = (torch.randn(K, R, R, C, device="cuda") / math.sqrt(R * R * C)).requires_grad_(True)
+    y, partials = Fn.conv2d(x, w, None, stride=2, padding=padding, want_stats=True)
+    assert "ConvStem" in type(y.grad_fn).__name__ and partials is not None
+    P, Q, pt, pb, pl, pr = Fn.conv_pads(H, H, R, R, 2, 1, padding)
+    xr = F.pad(x.float().permute(0, 3, 1, 2), (pl, pr, pt, pb))
+    wr = w.detach().bfloat16().float().permute(0, 3, 1, 2).requires_grad_(True)
+    yr = F.conv2d(xr, wr, None, stride=2).permute(0, 2, 3, 1)
+    assert tuple(y.shape) == tuple(yr.shape) == (N, P, Q, K)
+    assert rel_err(y, yr) < 1e-2
+    yf = y.detach().float().reshape(-1, K)
+    assert rel_err(partials[:, 0].sum(0), yf.sum(0)) < 1e-3
+    assert rel_err(partials[:, 1].sum(0), (yf * yf).sum(0)) < 1e-3
+    g = torch.randn_like(y)
+    y.backward(g)
+    yr.backward(g.float())
+    assert rel_err(w.grad, wr.grad.permute(0, 2, 3, 1)) < 2e-2
+
+
 @pytest.mark.parametrize("case", [(4, 26, 512, 1, 3, 1, True), (2, 13, 264, 2, 3, 2, False), (3, 9, 64, 4, 1, 1, True)])
 def test_conv_small_k_decoder_head(O, case):
     """K <= 4 output channels (the decoder's 3x3 -> 1 logit, core/resnet.py:487-492): CUDA-core kernels, fwd + both grads."""
