@@ -14,7 +14,7 @@
 //     128B-swizzled shared memory feeding tcgen05.mma (M=128, N=BLOCK_N, K=16), fp32
 //     accumulators in TMEM, double buffered so the epilogue of tile i overlaps tile i+1.
 //   * Warp roles: warp 0 = TMA producer, warp 1 = TMEM owner + single-thread MMA issuer,
-//     warps 2-5 = epilogue (tcgen05.ld -> bias / residual / ReLU -> bf16 -> global).
+//     warps 2-9 = epilogue (tcgen05.ld -> bias / residual / ReLU -> bf16 -> smem -> TMA store), two per TMEM lane quarter.
 //   * Persistent: grid = #SMs, static round-robin tile schedule with the Cout tile fastest so
 //     CTAs running together share the activation patch in L2.
 //   * wgrad is the transposed problem: both operands are "MN-major" (pixel index is the GEMM K
@@ -137,7 +137,9 @@ static void choose_patch(int N, int P, int Q, int rows, int stride, int* tn, int
 constexpr int kBlockM = 128;
 constexpr int kBlockK = 64;                       // bf16 elements = 128 bytes = one swizzle row
 constexpr int kABytes = kBlockM * kBlockK * 2;    // 16 KB
-constexpr int kThreads = 192;                     // 6 warps
+constexpr int kThreads = 192;                     // wgrad: 6 warps
+constexpr int kFpropThreads = 320;                // fprop: TMA warp, MMA warp, 8 epilogue warps
+constexpr int kEpiThreads = 256;
 constexpr int kEpiWarp0 = 2;
 
 template <int BLOCK_N>
@@ -186,7 +188,7 @@ __device__ __forceinline__ float warp_column_sum(float (&v)[32], int lane) {
 // descriptor: SBO = 8 pixels, LBO = plane pitch).  No im2col, no per-tap loads; the whole weight tensor
 // [K][taps*16] stays resident in shared memory.
 template <int BLOCK_N, bool kFused, bool kStats, bool kStem = false>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kFpropThreads, 1)
 conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
                   const __grid_constant__ CUtensorMap tm_y, const Geometry g, const float* __restrict__ bias,
                   const bf16* __restrict__ residual, float* __restrict__ stats) {
@@ -233,7 +235,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
       }
       for (int i = 0; i < kAcc; ++i) {
         ptx::mbar_init(&tmem_full[i], 1);
-        ptx::mbar_init(&tmem_empty[i], 4);  // one arrival per epilogue warp
+        ptx::mbar_init(&tmem_empty[i], 8);  // one arrival per epilogue warp
       }
       ptx::mbar_init(w_bar, 1);
       ptx::fence_mbar_init();
@@ -243,7 +245,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
   }
   if constexpr (kStats) {  // this CTA's statistics slot starts at zero
     float* slot = stats + (size_t)blockIdx.x * 2 * g.K;
-    for (int i = threadIdx.x; i < 2 * g.K; i += kThreads) slot[i] = 0.f;
+    for (int i = threadIdx.x; i < 2 * g.K; i += kFpropThreads) slot[i] = 0.f;
   }
   ptx::tc_fence_before();
   __syncthreads();
@@ -280,11 +282,8 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
         const int w_in = tw_i * g.TW * g.stride - g.pad_w;
         const int h_in = th_i * g.TH * g.stride - g.pad_h;
         const int n_in = tn_i * g.TN;
+        int tap = 0, kb = 0, r = 0, s = 0;  // advanced incrementally: no divisions on the TMA-issue path
         for (int it = 0; it < k_iters; ++it) {
-          const int tap = it / g.num_kb;
-          const int kb = it - tap * g.num_kb;
-          const int r = tap / g.S;
-          const int s = tap - r * g.S;
           ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
           ptx::mbar_expect_tx(&full_bar[stage], stage_tx);
           ptx::tma_load_4d(smem_a + stage * kABytes, &tm_x, &full_bar[stage], kb * kBlockK, w_in + s * g.dil,
@@ -294,6 +293,14 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
           if (++stage == kStages) {
             stage = 0;
             phase ^= 1;
+          }
+          if (++kb == g.num_kb) {
+            kb = 0;
+            ++tap;
+            if (++s == g.S) {
+              s = 0;
+              ++r;
+            }
           }
         }
       }
@@ -306,7 +313,10 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
+      uint64_t stem_a0 = 0, stem_b0 = 0;
       if constexpr (kStem) {
+        stem_a0 = ptx::umma_smem_desc_nosw(ptx::smem_u32(smem_a), (uint32_t)g.sp_plane, 128);
+        stem_b0 = ptx::umma_smem_desc_sw128(ptx::smem_u32(smem_b), 16, 1024);
         if (blockIdx.x < total_tiles) ptx::mbar_wait(w_bar, 0);
       }
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
@@ -317,17 +327,19 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
           ptx::mbar_wait(&full_bar[stage], phase);
           ptx::tc_fence_after();
           if constexpr (kStem) {
-            const uint32_t a_base = ptx::smem_u32(smem_a + stage * kABytes);
-            const uint32_t b_base = ptx::smem_u32(smem_b);
+            // one MMA per packed tap
+            // (descriptor offsets advance with counters: this thread's own instruction stream is the critical
+            // path, a division per tap cost more than the MMA itself)
+            const uint64_t a0 = stem_a0 + (uint64_t)((uint32_t)(stage * kABytes) >> 4);
             const int taps = g.R * g.S;
+            uint32_t a_row = 0, a_col = 0;  // in 16-byte units
             for (int t = 0; t < taps; ++t) {
-              const int r2 = t / g.S;
-              const int s2 = t - r2 * g.S;
-              const uint64_t a_desc = ptx::umma_smem_desc_nosw(a_base + (uint32_t)(r2 * g.sp_row + s2 * 16),
-                                                               (uint32_t)g.sp_plane, 128);
-              const uint64_t b_desc =
-                  ptx::umma_smem_desc_sw128(b_base + (uint32_t)((t >> 2) * 8192), 16, 1024) + (uint64_t)(2 * (t & 3));
-              ptx::umma_bf16(d_tmem, a_desc, b_desc, idesc, t > 0 ? 1u : 0u);
+              const uint32_t b_off = (uint32_t)((t >> 2) * 512 + (t & 3) * 2);
+              ptx::umma_bf16(d_tmem, a0 + (uint64_t)(a_row + a_col), stem_b0 + (uint64_t)b_off, idesc, t > 0 ? 1u : 0u);
+              if (++a_col == (uint32_t)g.S) {
+                a_col = 0;
+                a_row += (uint32_t)g.sp_row >> 4;
+              }
             }
             ptx::umma_commit(&empty_bar[stage]);
             if (++stage == kStages) {
@@ -361,7 +373,11 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
     // ===================== epilogue warps =====================
     // TMEM -> registers -> (bias / residual / ReLU) -> bf16 -> 128B-swizzled smem tile -> TMA store.
     // The 4-D store box is the pixel patch, so TMA clips everything outside the image / channel range.
+    // Eight warps: warp w may touch TMEM lanes 32*(w%4)..+31, so two warps share each lane quarter and split every
+    // 64-column chunk into its two 32-column halves.  (With one warp per scheduler the epilogue's dependent chains --
+    // tcgen05.ld, conversions, the statistics butterflies -- ran latency-bound and set the pace of narrow tiles.)
     const int quarter = warp & 3;  // TMEM lane quarter this warp may access
+    const int half = (warp - kEpiWarp0) >> 2;  // which 32 columns of each chunk
     const int row = quarter * 32 + lane;
     const int patch = g.TH * g.TW;
     const int dn = row / patch;
@@ -373,11 +389,50 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
     const uint32_t row_off = (uint32_t)row * 128u;
     const uint32_t sw = (uint32_t)(row & 7);
     const uint32_t tmem_lane = tmem_base + ((uint32_t)(quarter * 32) << 16);
-    float* my_stat = smem_stat + quarter * 128;
+    // ---- fused BatchNorm statistics (kStats) ----
+    // The bf16 tile staged for the TMA store doubles as the transpose: after the store is issued every thread reads
+    // ONE channel pair (4 bytes) of 16 rows back from shared memory -- a warp reads a whole 128-byte row per
+    // instruction, conflict-free under the swizzle -- and keeps (sum, sum of squares) of its two channels in
+    // registers across all tiles of the current Cout tile.  The eight row groups are folded through the staging
+    // buffers only when the Cout tile changes and at the end (`flush_stats`).  (The first version reduced the
+    // accumulator registers across lanes with shuffle butterflies: ~500 of the ~1000 epilogue instructions per
+    // tile, which made the stats variant 2.8x slower than the plain kernel on output-heavy layers.)
+    constexpr int kChunks = BLOCK_N / 64;
+    const int ewarp = warp - kEpiWarp0;       // 0..7: rows 16*ewarp .. 16*ewarp+15 in the reduction phase
+    const int etid = ewarp * 32 + lane;
+    uint32_t* vmask = reinterpret_cast<uint32_t*>(smem_stat);  // [2 tile parities][4 quarters] valid-row masks
+    float sacc[kChunks][4];
+#pragma unroll
+    for (int c = 0; c < kChunks; ++c) sacc[c][0] = sacc[c][1] = sacc[c][2] = sacc[c][3] = 0.f;
+    int stat_n_tile = -1;
+    auto flush_stats = [&](int nt) {
+      if (issuer) ptx::tma_store_wait_read<0>();  // nobody is reading the staging buffers any more
+      ptx::named_bar_sync(1, kEpiThreads);
+      float* st = reinterpret_cast<float*>(smem_out);  // [8 row groups][kChunks][4][32 lanes]
+#pragma unroll
+      for (int c = 0; c < kChunks; ++c)
+#pragma unroll
+        for (int v = 0; v < 4; ++v) {
+          st[((ewarp * kChunks + c) * 4 + v) * 32 + lane] = sacc[c][v];
+          sacc[c][v] = 0.f;
+        }
+      ptx::named_bar_sync(1, kEpiThreads);
+      float* slot = stats + (size_t)blockIdx.x * 2 * g.K;
+      for (int idx = etid; idx < kChunks * 128; idx += kEpiThreads) {
+        const int c = idx >> 7, v = (idx >> 5) & 3, ln = idx & 31;
+        float tot = 0.f;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) tot += st[((e * kChunks + c) * 4 + v) * 32 + ln];
+        const int ch = nt * BLOCK_N + c * 64 + 2 * ln + (v >> 1);  // v: 0 = sum ch0, 1 = sumsq ch0, 2 = sum ch1, 3 = sumsq ch1
+        if (ch < g.K) atomicAdd(&slot[(size_t)(v & 1) * g.K + ch], tot);
+      }
+      ptx::named_bar_sync(1, kEpiThreads);  // staging buffers are free again
+    };
     int acc = 0;
     uint32_t acc_phase = 0;
     uint32_t chunk_count = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+    uint32_t tile_count = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tile_count) {
       const int n_tile = tile % g.n_tiles;
       const int m_tile = tile / g.n_tiles;
       const int tw_i = m_tile % g.tiles_w;
@@ -393,21 +448,30 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
         pix = ((size_t)n * g.P + p) * g.Q + q;
       }
       const int chunks = min(BLOCK_N / 64, (g.K - n_tile * BLOCK_N + 63) / 64);
+      uint32_t* tile_vmask = vmask + (tile_count & 1) * 4;
+      if constexpr (kStats) {
+        if (n_tile != stat_n_tile) {
+          if (stat_n_tile >= 0) flush_stats(stat_n_tile);
+          stat_n_tile = n_tile;
+        }
+        const uint32_t vm = __ballot_sync(0xffffffffu, valid);
+        if (half == 0 && lane == 0) tile_vmask[quarter] = vm;  // read after this tile's first barrier
+      }
       ptx::mbar_wait(&tmem_full[acc], acc_phase);
       ptx::tc_fence_after();
-#pragma unroll 1
-      for (int cc = 0; cc < chunks; ++cc) {
+#pragma unroll
+      for (int cc = 0; cc < kChunks; ++cc) {
+        if (cc >= chunks) break;
         const int co_chunk = n_tile * BLOCK_N + cc * 64;
         uint8_t* out_tile = smem_out + (chunk_count % Cfg::kOutBufs) * (kBlockM * 128);
         ++chunk_count;
         if (issuer) ptx::tma_store_wait_read<Cfg::kOutBufs - 1>();  // the store that last read this tile has drained
-        ptx::named_bar_sync(1, 128);
-#pragma unroll
-        for (int half = 0; half < 2; ++half) {
+        ptx::named_bar_sync(1, kEpiThreads);
+        {
           uint32_t v[32];
           ptx::tmem_ld_32x32(tmem_lane + (uint32_t)(acc * BLOCK_N + cc * 64 + half * 32), v);
           ptx::tmem_ld_wait();
-          if (half == 1 && cc == chunks - 1) {
+          if (cc == chunks - 1) {
             // every tcgen05.ld of this accumulator has completed: hand the TMEM buffer back to the MMA warp
             ptx::tc_fence_before();
             __syncwarp();
@@ -446,11 +510,6 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
           for (int j = 0; j < 16; ++j) {
             const __nv_bfloat162 h2 = __floats2bfloat162_rn(f[2 * j], f[2 * j + 1]);
             packed[j] = *reinterpret_cast<const uint32_t*>(&h2);
-            if constexpr (kStats) {  // statistics of the values as stored (after bf16 rounding)
-              const float2 back = __bfloat1622float2(h2);
-              f[2 * j] = valid ? back.x : 0.f;
-              f[2 * j + 1] = valid ? back.y : 0.f;
-            }
           }
 #pragma unroll
           for (int j8 = 0; j8 < 4; ++j8) {
@@ -458,43 +517,46 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
             *reinterpret_cast<uint4*>(out_tile + row_off + ((chunk16 ^ sw) << 4)) =
                 make_uint4(packed[j8 * 4], packed[j8 * 4 + 1], packed[j8 * 4 + 2], packed[j8 * 4 + 3]);
           }
-          if constexpr (kStats) {
-            float sq[32];
-#pragma unroll
-            for (int j = 0; j < 32; ++j) sq[j] = f[j] * f[j];
-            const float s1 = warp_column_sum(f, lane);
-            const float s2 = warp_column_sum(sq, lane);
-            my_stat[half * 32 + lane] = s1;
-            my_stat[64 + half * 32 + lane] = s2;
-          }
         }
         ptx::fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the TMA (async proxy)
-        ptx::named_bar_sync(1, 128);
+        ptx::named_bar_sync(1, kEpiThreads);
         if (issuer) {
           ptx::tma_store_4d(&tm_y, out_tile, co_chunk, tw_i * g.TW, th_i * g.TH, tn_i * g.TN);
           ptx::tma_store_commit();
         }
         if constexpr (kStats) {
-          if (warp == kEpiWarp0) {  // fold the four warps' partials into this CTA's global slot (no other writer)
-            float* slot = stats + (size_t)blockIdx.x * 2 * g.K;
+          // statistics of the values as stored (bf16), rows outside the image masked out
+          const uint32_t vm16 = (tile_vmask[ewarp >> 1] >> ((ewarp & 1) * 16)) & 0xffffu;
+          const uint8_t* rows = out_tile + (uint32_t)(ewarp * 16) * 128u + ((uint32_t)(lane & 3) << 2);
+          const uint32_t c16 = (uint32_t)(lane >> 2);
+          uint32_t wv[16];
 #pragma unroll
-            for (int t = 0; t < 4; ++t) {
-              const int idx = t * 32 + lane;        // 0..127: [which][channel within chunk]
-              const int which = idx >> 6, ch = co_chunk + (idx & 63);
-              if (ch < g.K) {
-                const float tot = smem_stat[idx] + smem_stat[128 + idx] + smem_stat[256 + idx] + smem_stat[384 + idx];
-                // fire-and-forget reduction (RED): a load-add-store here would stall this warp, and through the
-                // next named barrier the whole epilogue, for an L2 round trip per 64-channel chunk
-                atomicAdd(&slot[(size_t)which * g.K + ch], tot);
-              }
-            }
+          for (int i = 0; i < 16; ++i)
+            wv[i] = *reinterpret_cast<const uint32_t*>(rows + i * 128 + ((c16 ^ (uint32_t)(i & 7)) << 4));
+          float s0 = 0.f, q0 = 0.f, s1 = 0.f, q1 = 0.f;
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const bool ok = (vm16 >> i) & 1u;
+            const float f0 = ok ? __uint_as_float(wv[i] << 16) : 0.f;
+            const float f1 = ok ? __uint_as_float(wv[i] & 0xffff0000u) : 0.f;
+            s0 += f0;
+            q0 = fmaf(f0, f0, q0);
+            s1 += f1;
+            q1 = fmaf(f1, f1, q1);
           }
+          sacc[cc][0] += s0;
+          sacc[cc][1] += q0;
+          sacc[cc][2] += s1;
+          sacc[cc][3] += q1;
         }
       }
       if (++acc == kAcc) {
         acc = 0;
         acc_phase ^= 1;
       }
+    }
+    if constexpr (kStats) {
+      if (stat_n_tile >= 0) flush_stats(stat_n_tile);
     }
     if (issuer) ptx::tma_store_wait_all<0>();
   }
@@ -770,7 +832,7 @@ static int launch_stem(const CUtensorMap& tx, const CUtensorMap& tw, const CUten
   const int total = g.tiles_n * g.tiles_h * g.tiles_w;
   const int grid = total < tdl::num_sms() ? total : tdl::num_sms();
   if (nparts) *nparts = grid;
-  conv_fprop_kernel<64, false, kStats, true><<<grid, kThreads, Cfg::kSmemBytes, st>>>(tx, tw, ty, g, nullptr, nullptr,
+  conv_fprop_kernel<64, false, kStats, true><<<grid, kFpropThreads, Cfg::kSmemBytes, st>>>(tx, tw, ty, g, nullptr, nullptr,
                                                                                       stats);
   TDL_LAUNCH_OK("conv_fprop_kernel(stem)");
   return 0;
@@ -789,7 +851,7 @@ static int launch_fprop_t(const CUtensorMap& tx, const CUtensorMap& tw, const CU
   const int total = g.tiles_n * g.tiles_h * g.tiles_w * g.n_tiles;
   const int grid = total < tdl::num_sms() ? total : tdl::num_sms();
   if (nparts) *nparts = grid;
-  conv_fprop_kernel<BLOCK_N, kFused, kStats><<<grid, kThreads, Cfg::kSmemBytes, st>>>(tx, tw, ty, g, bias, res, stats);
+  conv_fprop_kernel<BLOCK_N, kFused, kStats><<<grid, kFpropThreads, Cfg::kSmemBytes, st>>>(tx, tw, ty, g, bias, res, stats);
   TDL_LAUNCH_OK("conv_fprop_kernel");
   return 0;
 }

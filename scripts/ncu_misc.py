@@ -1,4 +1,4 @@
-"""Driver for ncu captures of the memory-bound kernels: python scripts/ncu_misc.py bn|lovasz|optim"""
+"""Driver for ncu captures of single kernels: python scripts/ncu_misc.py bn|lovasz|optim|stem|stats1x1|depthwise"""
 import os
 import sys
 
@@ -31,5 +31,25 @@ elif kind == "optim":
     for _ in range(3):
         O.lr_schedule_step(st, lr, 0.1)
         O.sgd_momentum_flat(p, gr, m, None, lr, 0.9, 1e-4, 1.0, True)
+elif kind == "stem":
+    from tensorflowdistributedlearning_b200.ops import functional as Fn
+
+    x = torch.randn(256, 224, 224, 3, device="cuda").bfloat16()
+    w = torch.randn(64, 7, 7, 3, device="cuda") / 12.0
+    planes = O.conv_stem_pack(x)
+    wp = O.conv_stem_weight_prep(w, 3, 3)
+    for _ in range(3):
+        O.conv_stem_fprop(planes, wp, (224, 224), 64, 7, 7, 3, 3, (112, 112), True)
+elif kind == "stats1x1":
+    x = torch.randn(256, 56, 56, 64, device="cuda").bfloat16()
+    w = (torch.randn(256, 1, 64, device="cuda") / 8).bfloat16()
+    for _ in range(3):
+        O.conv2d_fprop_stats(x, w, R=1, S=1, out_hw=(56, 56))
+        O.conv2d_fprop(x, w, R=1, S=1, out_hw=(56, 56))
+elif kind == "depthwise":
+    x = torch.randn(64, 38, 38, 728, device="cuda").bfloat16()
+    w = torch.randn(9, 728, device="cuda")
+    for _ in range(3):
+        O.depthwise3x3_fwd(x, w, None, None, 1, 1, 1, 1, (38, 38), True, False)
 torch.cuda.synchronize()
 print("ok")
