@@ -138,8 +138,7 @@ constexpr int kBlockM = 128;
 constexpr int kBlockK = 64;                       // bf16 elements = 128 bytes = one swizzle row
 constexpr int kABytes = kBlockM * kBlockK * 2;    // 16 KB
 constexpr int kThreads = 192;                     // wgrad: 6 warps
-constexpr int kFpropThreads = 320;                // fprop: TMA warp, MMA warp, 8 epilogue warps
-constexpr int kEpiThreads = 256;
+constexpr int kFpropThreads = 320;                // fprop: TMA warp, MMA warp, 2 x 4 epilogue warps
 constexpr int kEpiWarp0 = 2;
 
 template <int BLOCK_N>
@@ -150,7 +149,7 @@ struct FpropCfg {
   // on the epilogue's hand-back latency every other tile
   static constexpr int kAccBufs = BLOCK_N <= 128 ? 4 : 2;
   static constexpr int kTmemCols = kAccBufs * BLOCK_N;
-  static constexpr int kOutBufs = 2;             // 128-row x 64-channel bf16 staging tiles for the TMA stores
+  static constexpr int kOutBufs = 2;             // 128-row x 64-channel bf16 staging tile per epilogue group
   static constexpr int kOutBytes = kOutBufs * kBlockM * 128;
   static constexpr int kStatBytes = 4 * 2 * 64 * 4;  // per-warp (sum, sumsq) partials of one 64-channel chunk
   static constexpr int kBarBytes = 256;    // (2*kStages + 4) mbarriers + the TMEM slot
@@ -159,22 +158,6 @@ struct FpropCfg {
   static constexpr int kSmemBytes = kStages * kStageBytes + kOutBytes + kStatBytes + kAlignSlack + kBarBytes;
   static_assert((2 * kStages + 2 * kAccBufs + 1) * 8 + 4 <= kBarBytes, "barrier region too small");
 };
-
-// Column sums over the 32 rows held by a warp: lane l ends with the total of column l ("transpose-reduce": each
-// step halves the number of live columns, 31 shuffles for 32 columns).
-__device__ __forceinline__ float warp_column_sum(float (&v)[32], int lane) {
-#pragma unroll
-  for (int off = 16; off >= 1; off >>= 1) {
-    const bool upper = (lane & off) != 0;
-#pragma unroll
-    for (int i = 0; i < off; ++i) {
-      const float send = upper ? v[i] : v[i + off];
-      const float keep = upper ? v[i + off] : v[i];
-      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
-    }
-  }
-  return v[0];
-}
 
 // kFused: bias / residual / ReLU present in the epilogue.  kStats: per-channel (sum, sum of squares) of the bf16
 // output accumulated into this CTA's slot of `stats` ([gridDim.x][2][K] fp32) for the BatchNorm that follows.
@@ -235,7 +218,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
       }
       for (int i = 0; i < kAcc; ++i) {
         ptx::mbar_init(&tmem_full[i], 1);
-        ptx::mbar_init(&tmem_empty[i], 8);  // one arrival per epilogue warp
+        ptx::mbar_init(&tmem_empty[i], 4);  // one arrival per warp of the epilogue group that drains the tile
       }
       ptx::mbar_init(w_bar, 1);
       ptx::fence_mbar_init();
@@ -373,11 +356,14 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
     // ===================== epilogue warps =====================
     // TMEM -> registers -> (bias / residual / ReLU) -> bf16 -> 128B-swizzled smem tile -> TMA store.
     // The 4-D store box is the pixel patch, so TMA clips everything outside the image / channel range.
-    // Eight warps: warp w may touch TMEM lanes 32*(w%4)..+31, so two warps share each lane quarter and split every
-    // 64-column chunk into its two 32-column halves.  (With one warp per scheduler the epilogue's dependent chains --
-    // tcgen05.ld, conversions, the statistics butterflies -- ran latency-bound and set the pace of narrow tiles.)
+    //
+    // Two independent groups of four warps (a warp may touch TMEM lanes 32*(warp%4)..+31, so each group covers all
+    // 128 lanes).  Group 0 drains the even tiles of this CTA, group 1 the odd ones, each with its own staging
+    // buffer, named barrier and TMA-store issuer, so the dependent chain of one tile (accumulator wait, tcgen05.ld,
+    // convert, stage, store, statistics) overlaps the chain of the next tile instead of adding to it.
+    const int ewarp = warp - kEpiWarp0;  // 0..7
+    const int group = ewarp >> 2;
     const int quarter = warp & 3;  // TMEM lane quarter this warp may access
-    const int half = (warp - kEpiWarp0) >> 2;  // which 32 columns of each chunk
     const int row = quarter * 32 + lane;
     const int patch = g.TH * g.TW;
     const int dn = row / patch;
@@ -385,54 +371,52 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
     const int dh = rem / g.TW;
     const int dw = rem - dh * g.TW;
     const bool row_in_patch = row < g.TN * patch;
-    const bool issuer = (warp == kEpiWarp0 && lane == 0);
+    const bool issuer = ((ewarp & 3) == 0 && lane == 0);
+    const int bar_id = 1 + group;
     const uint32_t row_off = (uint32_t)row * 128u;
     const uint32_t sw = (uint32_t)(row & 7);
     const uint32_t tmem_lane = tmem_base + ((uint32_t)(quarter * 32) << 16);
+    uint8_t* out_tile = smem_out + group * (kBlockM * 128);
     // ---- fused BatchNorm statistics (kStats) ----
     // The bf16 tile staged for the TMA store doubles as the transpose: after the store is issued every thread reads
-    // ONE channel pair (4 bytes) of 16 rows back from shared memory -- a warp reads a whole 128-byte row per
-    // instruction, conflict-free under the swizzle -- and keeps (sum, sum of squares) of its two channels in
-    // registers across all tiles of the current Cout tile.  The eight row groups are folded through the staging
-    // buffers only when the Cout tile changes and at the end (`flush_stats`).  (The first version reduced the
+    // ONE channel pair (4 bytes) of its warp's 32 rows back from shared memory -- a warp reads a whole 128-byte row
+    // per instruction, conflict-free under the swizzle -- and keeps (sum, sum of squares) of its two channels in
+    // registers across all tiles of the current Cout tile.  The four row groups are folded through the staging
+    // buffer only when the Cout tile changes and at the end (`flush_stats`).  (The first version reduced the
     // accumulator registers across lanes with shuffle butterflies: ~500 of the ~1000 epilogue instructions per
     // tile, which made the stats variant 2.8x slower than the plain kernel on output-heavy layers.)
     constexpr int kChunks = BLOCK_N / 64;
-    const int ewarp = warp - kEpiWarp0;       // 0..7: rows 16*ewarp .. 16*ewarp+15 in the reduction phase
-    const int etid = ewarp * 32 + lane;
-    uint32_t* vmask = reinterpret_cast<uint32_t*>(smem_stat);  // [2 tile parities][4 quarters] valid-row masks
     float sacc[kChunks][4];
 #pragma unroll
     for (int c = 0; c < kChunks; ++c) sacc[c][0] = sacc[c][1] = sacc[c][2] = sacc[c][3] = 0.f;
     int stat_n_tile = -1;
     auto flush_stats = [&](int nt) {
-      if (issuer) ptx::tma_store_wait_read<0>();  // nobody is reading the staging buffers any more
-      ptx::named_bar_sync(1, kEpiThreads);
-      float* st = reinterpret_cast<float*>(smem_out);  // [8 row groups][kChunks][4][32 lanes]
+      if (issuer) ptx::tma_store_wait_read<0>();  // nobody is reading the staging buffer any more
+      ptx::named_bar_sync(bar_id, 128);
+      float* st = reinterpret_cast<float*>(out_tile);  // [4 row groups][kChunks][4][32 lanes]
 #pragma unroll
       for (int c = 0; c < kChunks; ++c)
 #pragma unroll
         for (int v = 0; v < 4; ++v) {
-          st[((ewarp * kChunks + c) * 4 + v) * 32 + lane] = sacc[c][v];
+          st[((quarter * kChunks + c) * 4 + v) * 32 + lane] = sacc[c][v];
           sacc[c][v] = 0.f;
         }
-      ptx::named_bar_sync(1, kEpiThreads);
+      ptx::named_bar_sync(bar_id, 128);
       float* slot = stats + (size_t)blockIdx.x * 2 * g.K;
-      for (int idx = etid; idx < kChunks * 128; idx += kEpiThreads) {
+      for (int idx = quarter * 32 + lane; idx < kChunks * 128; idx += 128) {
         const int c = idx >> 7, v = (idx >> 5) & 3, ln = idx & 31;
         float tot = 0.f;
 #pragma unroll
-        for (int e = 0; e < 8; ++e) tot += st[((e * kChunks + c) * 4 + v) * 32 + ln];
+        for (int e = 0; e < 4; ++e) tot += st[((e * kChunks + c) * 4 + v) * 32 + ln];
         const int ch = nt * BLOCK_N + c * 64 + 2 * ln + (v >> 1);  // v: 0 = sum ch0, 1 = sumsq ch0, 2 = sum ch1, 3 = sumsq ch1
-        if (ch < g.K) atomicAdd(&slot[(size_t)(v & 1) * g.K + ch], tot);
+        if (ch < g.K) atomicAdd(&slot[(size_t)(v & 1) * g.K + ch], tot);  // both groups add into the CTA's slot
       }
-      ptx::named_bar_sync(1, kEpiThreads);  // staging buffers are free again
+      ptx::named_bar_sync(bar_id, 128);  // the staging buffer is free again
     };
-    int acc = 0;
-    uint32_t acc_phase = 0;
-    uint32_t chunk_count = 0;
-    uint32_t tile_count = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tile_count) {
+    uint32_t tile_count = (uint32_t)group;
+    for (int tile = blockIdx.x + group * gridDim.x; tile < total_tiles; tile += 2 * gridDim.x, tile_count += 2) {
+      const int acc = (int)(tile_count % kAcc);
+      const uint32_t acc_phase = (tile_count / kAcc) & 1u;
       const int n_tile = tile % g.n_tiles;
       const int m_tile = tile / g.n_tiles;
       const int tw_i = m_tile % g.tiles_w;
@@ -448,14 +432,13 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
         pix = ((size_t)n * g.P + p) * g.Q + q;
       }
       const int chunks = min(BLOCK_N / 64, (g.K - n_tile * BLOCK_N + 63) / 64);
-      uint32_t* tile_vmask = vmask + (tile_count & 1) * 4;
+      uint32_t vm = 0xffffffffu;  // which of this warp's 32 rows are real output pixels
       if constexpr (kStats) {
         if (n_tile != stat_n_tile) {
           if (stat_n_tile >= 0) flush_stats(stat_n_tile);
           stat_n_tile = n_tile;
         }
-        const uint32_t vm = __ballot_sync(0xffffffffu, valid);
-        if (half == 0 && lane == 0) tile_vmask[quarter] = vm;  // read after this tile's first barrier
+        vm = __ballot_sync(0xffffffffu, valid);
       }
       ptx::mbar_wait(&tmem_full[acc], acc_phase);
       ptx::tc_fence_after();
@@ -463,15 +446,14 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
       for (int cc = 0; cc < kChunks; ++cc) {
         if (cc >= chunks) break;
         const int co_chunk = n_tile * BLOCK_N + cc * 64;
-        uint8_t* out_tile = smem_out + (chunk_count % Cfg::kOutBufs) * (kBlockM * 128);
-        ++chunk_count;
-        if (issuer) ptx::tma_store_wait_read<Cfg::kOutBufs - 1>();  // the store that last read this tile has drained
-        ptx::named_bar_sync(1, kEpiThreads);
-        {
+        if (issuer) ptx::tma_store_wait_read<0>();  // the previous store of this group has drained the buffer
+        ptx::named_bar_sync(bar_id, 128);
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
           uint32_t v[32];
           ptx::tmem_ld_32x32(tmem_lane + (uint32_t)(acc * BLOCK_N + cc * 64 + half * 32), v);
           ptx::tmem_ld_wait();
-          if (cc == chunks - 1) {
+          if (half == 1 && cc == chunks - 1) {
             // every tcgen05.ld of this accumulator has completed: hand the TMEM buffer back to the MMA warp
             ptx::tc_fence_before();
             __syncwarp();
@@ -519,40 +501,38 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
           }
         }
         ptx::fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the TMA (async proxy)
-        ptx::named_bar_sync(1, kEpiThreads);
+        ptx::named_bar_sync(bar_id, 128);
         if (issuer) {
           ptx::tma_store_4d(&tm_y, out_tile, co_chunk, tw_i * g.TW, th_i * g.TH, tn_i * g.TN);
           ptx::tma_store_commit();
         }
         if constexpr (kStats) {
-          // statistics of the values as stored (bf16), rows outside the image masked out
-          const uint32_t vm16 = (tile_vmask[ewarp >> 1] >> ((ewarp & 1) * 16)) & 0xffffu;
-          const uint8_t* rows = out_tile + (uint32_t)(ewarp * 16) * 128u + ((uint32_t)(lane & 3) << 2);
+          // statistics of the values as stored (bf16) over this warp's 32 rows, rows outside the image masked out
+          const uint8_t* rows = out_tile + (uint32_t)(quarter * 32) * 128u + ((uint32_t)(lane & 3) << 2);
           const uint32_t c16 = (uint32_t)(lane >> 2);
-          uint32_t wv[16];
-#pragma unroll
-          for (int i = 0; i < 16; ++i)
-            wv[i] = *reinterpret_cast<const uint32_t*>(rows + i * 128 + ((c16 ^ (uint32_t)(i & 7)) << 4));
           float s0 = 0.f, q0 = 0.f, s1 = 0.f, q1 = 0.f;
 #pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            const bool ok = (vm16 >> i) & 1u;
-            const float f0 = ok ? __uint_as_float(wv[i] << 16) : 0.f;
-            const float f1 = ok ? __uint_as_float(wv[i] & 0xffff0000u) : 0.f;
-            s0 += f0;
-            q0 = fmaf(f0, f0, q0);
-            s1 += f1;
-            q1 = fmaf(f1, f1, q1);
+          for (int i0 = 0; i0 < 32; i0 += 16) {
+            uint32_t wv[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i)
+              wv[i] = *reinterpret_cast<const uint32_t*>(rows + (i0 + i) * 128 + ((c16 ^ (uint32_t)(i & 7)) << 4));
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              const bool ok = (vm >> (i0 + i)) & 1u;
+              const float f0 = ok ? __uint_as_float(wv[i] << 16) : 0.f;
+              const float f1 = ok ? __uint_as_float(wv[i] & 0xffff0000u) : 0.f;
+              s0 += f0;
+              q0 = fmaf(f0, f0, q0);
+              s1 += f1;
+              q1 = fmaf(f1, f1, q1);
+            }
           }
           sacc[cc][0] += s0;
           sacc[cc][1] += q0;
           sacc[cc][2] += s1;
           sacc[cc][3] += q1;
         }
-      }
-      if (++acc == kAcc) {
-        acc = 0;
-        acc_phase ^= 1;
       }
     }
     if constexpr (kStats) {
