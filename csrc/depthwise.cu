@@ -249,6 +249,64 @@ static Launch plan(const Shape& s, int blocks_per_sm) {
   return l;
 }
 
+// Data gradient of a STRIDED 3x3 depthwise conv (dilation 1): a gather over the <= ceil(3/S)^2 output pixels whose
+// window covers this input pixel, one thread per (input pixel, 8 channels), blockIdx.y = image.  The pre-activation
+// ReLU mask (xmask <= 0 -> 0) is applied on the store, so no separate mask pass runs (core/xception.py:184-210).
+template <int S>
+__global__ void __launch_bounds__(kThreads)
+depthwise3x3_dgrad_strided_kernel(const bf16* __restrict__ dy, const float* __restrict__ w, const bf16* __restrict__ xmask,
+                                  bf16* __restrict__ dx, int H, int W, int C, int P, int Q, int pad_h, int pad_w) {
+  constexpr int kCells = (3 + S - 1) / S;
+  const int c8 = C >> 3;
+  const int n = blockIdx.y;
+  const int i = blockIdx.x * kThreads + threadIdx.x;
+  if (i >= H * W * c8) return;
+  const int hw = i / c8;
+  const int cv = i - hw * c8;
+  const int h = hw / W;
+  const int wq = hw - h * W;
+  const int hp = h + pad_h, wp = wq + pad_w;
+  const int p_hi = hp / S, q_hi = wp / S;
+  const bf16* dyn = dy + (int64_t)n * P * Q * C + cv * 8;
+  const int64_t xoff = ((int64_t)n * H * W + hw) * C + cv * 8;
+  bf16x8 g[kCells * kCells];
+  int tap[kCells * kCells];
+#pragma unroll
+  for (int a = 0; a < kCells; ++a)
+#pragma unroll
+    for (int b = 0; b < kCells; ++b) {
+      const int p = p_hi - a, q = q_hi - b;
+      const int r = hp - p * S, t = wp - q * S;
+      const bool ok = p >= 0 && p < P && q >= 0 && q < Q && r < 3 && t < 3;
+      tap[a * kCells + b] = ok ? r * 3 + t : -1;
+      if (ok) g[a * kCells + b] = ld8(dyn + ((int64_t)p * Q + q) * C);
+    }
+  bf16x8 xm;
+  if (xmask) xm = ld8(xmask + xoff);
+  float acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+#pragma unroll
+  for (int c = 0; c < kCells * kCells; ++c) {
+    if (tap[c] < 0) continue;
+    float gv[8];
+    unpack8(g[c], gv);
+    const float4 w0 = __ldg(reinterpret_cast<const float4*>(w + (int64_t)tap[c] * C + cv * 8));
+    const float4 w1 = __ldg(reinterpret_cast<const float4*>(w + (int64_t)tap[c] * C + cv * 8 + 4));
+    acc[0] = fmaf(gv[0], w0.x, acc[0]); acc[1] = fmaf(gv[1], w0.y, acc[1]);
+    acc[2] = fmaf(gv[2], w0.z, acc[2]); acc[3] = fmaf(gv[3], w0.w, acc[3]);
+    acc[4] = fmaf(gv[4], w1.x, acc[4]); acc[5] = fmaf(gv[5], w1.y, acc[5]);
+    acc[6] = fmaf(gv[6], w1.z, acc[6]); acc[7] = fmaf(gv[7], w1.w, acc[7]);
+  }
+  if (xmask) {
+    float mv[8];
+    unpack8(xm, mv);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = mv[j] > 0.f ? acc[j] : 0.f;
+  }
+  st8(dx + xoff, pack8(acc));
+}
+
 }  // namespace dw
 }  // namespace tdl
 
@@ -274,6 +332,20 @@ TDL_API int tdl_depthwise3x3_fwd(const void* x, const float* w, const float* bia
     depthwise3x3_kernel<false><<<grid, kThreads, 0, st>>>((const bf16*)x, w, bias, (const bf16*)mask, (bf16*)y, s, l.tx,
                                                           l.ty, relu_in, relu_out);
   TDL_LAUNCH_OK("depthwise3x3_kernel");
+  return 0;
+}
+
+// dx[N,H,W,C] = data gradient of a stride-2 3x3 depthwise conv (dilation 1) with weights w [9, C] (NOT flipped);
+// xmask (may be NULL) zeroes dx where the forward input of a pre-activation ReLU was <= 0.
+TDL_API int tdl_depthwise3x3_dgrad_s2(const void* dy, const float* w, const void* xmask, void* dx, int N, int H, int W,
+                                      int C, int P, int Q, int pad_h, int pad_w, void* stream) {
+  TDL_REQUIRE(C % 8 == 0, "C must be a multiple of 8");
+  TDL_REQUIRE(N <= 65535 && (int64_t)H * W * C < (1ll << 31), "shape too large for the strided depthwise dgrad kernel");
+  if ((int64_t)N * H * W == 0) return 0;
+  dim3 grid((unsigned)cdiv((int64_t)H * W * (C / 8), kThreads), (unsigned)N);
+  depthwise3x3_dgrad_strided_kernel<2><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
+      (const bf16*)dy, w, (const bf16*)xmask, (bf16*)dx, H, W, C, P, Q, pad_h, pad_w);
+  TDL_LAUNCH_OK("depthwise3x3_dgrad_strided_kernel");
   return 0;
 }
 

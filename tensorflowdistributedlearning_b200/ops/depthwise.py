@@ -56,6 +56,9 @@ class _DepthwiseNative(torch.autograd.Function):
                     n, h, w, _ = x.shape
                     dx = O.depthwise3x3_fwd(dy, wd.flip(0, 1).contiguous().view(9, C), None, x if relu_in else None, 1,
                                             dil, 2 * dil - pads[0], 2 * dil - pads[2], (h, w), False, False)
+                elif stride == 2 and dil == 1 and not relu:
+                    dx = O.depthwise3x3_dgrad_s2(dy, wd.view(9, C), x if relu_in else None, tuple(x.shape), pads[0],
+                                                 pads[2])
                 else:
                     dx, _, _ = O.depthwise_bwd(x, wd, dy, y, stride, dil, pads[0], pads[2], relu)
                     if relu_in:

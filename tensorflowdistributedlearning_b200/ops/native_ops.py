@@ -517,3 +517,14 @@ def conv_stem_fprop(planes: torch.Tensor, w_packed: torch.Tensor, image_hw, K: i
                                      _i(pad_h), _i(pad_w), _i(p), _i(q), N.ptr(None), N.ptr(None), N.stream_ptr())
     N.check(rc, "tdl_conv_stem_fprop")
     return y
+
+
+def depthwise3x3_dgrad_s2(dy, w9c, xmask, in_shape, pad_h, pad_w):
+    """Data gradient of a stride-2 3x3 depthwise conv; ``xmask`` (the forward input of a pre-activation ReLU) masks it."""
+    n, h, w, c = in_shape
+    _, p, q, _ = dy.shape
+    dx = torch.empty(in_shape, dtype=torch.bfloat16, device=dy.device)
+    rc = N.lib().tdl_depthwise3x3_dgrad_s2(N.ptr(dy), N.ptr(w9c), N.ptr(xmask), N.ptr(dx), _i(n), _i(h), _i(w), _i(c),
+                                           _i(p), _i(q), _i(pad_h), _i(pad_w), N.stream_ptr())
+    N.check(rc, "tdl_depthwise3x3_dgrad_s2")
+    return dx
