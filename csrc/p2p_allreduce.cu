@@ -362,6 +362,29 @@ nvls_kernel(const Comm cm, const StepArgs a) {
   if (threadIdx.x == 0) cm.epoch[blockIdx.x] = epoch;
 }
 
+// ---- broadcast (X2: tower `src`'s parameters become everyone's) ----
+// Pull model: every rank copies [offset, offset+n) of `src`'s parameter buffer into its own over NVLink; the
+// barriers keep `src` from touching the range while peers are still reading it.
+__global__ void __launch_bounds__(kThreads)
+broadcast_kernel(const Comm cm, int src, int64_t offset, int64_t n) {
+  uint32_t epoch = cm.epoch[blockIdx.x];
+  cross_rank_barrier(cm, ++epoch);
+  if (cm.rank != src) {
+    const float* from = cm.param[src] + offset;
+    float* to = cm.param[cm.rank] + offset;
+    const int64_t n4 = n / 4;
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t nthr = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t v = tid; v < n4; v += nthr)
+      reinterpret_cast<float4*>(to)[v] = reinterpret_cast<const float4*>(from)[v];
+    for (int64_t i = n4 * 4 + tid; i < n; i += nthr) to[i] = from[i];
+  }
+  __threadfence_system();
+  cross_rank_barrier(cm, ++epoch);
+  __syncthreads();
+  if (threadIdx.x == 0) cm.epoch[blockIdx.x] = epoch;
+}
+
 }  // namespace p2p
 }  // namespace tdl
 
@@ -466,5 +489,24 @@ TDL_API int tdl_p2p_fused_step(void* comm, int64_t offset, int64_t n, int mode, 
   else if (mode == 4) nvls_kernel<8><<<blocks, kThreads, 0, st>>>(*cm, s);
   else two_shot_kernel<<<blocks, kThreads, 0, st>>>(*cm, s);
   TDL_LAUNCH_OK("p2p fused step");
+  return 0;
+}
+
+// Mirror rank `src`'s parameters [offset, offset+n) into every rank's parameter buffer (all ranks call this).
+TDL_API int tdl_p2p_broadcast(void* comm, int src, int64_t offset, int64_t n, int max_blocks, void* stream) {
+  Comm* cm = (Comm*)comm;
+  TDL_REQUIRE(cm != nullptr, "null communicator");
+  TDL_REQUIRE(src >= 0 && src < cm->world, "source rank out of range");
+  TDL_REQUIRE(offset % 4 == 0, "offset must be a multiple of 4 elements");
+  TDL_REQUIRE(!cm->emulate, "broadcast is not available for the single-GPU emulation communicator");
+  if (n <= 0) return 0;
+  int blocks = (int)cdiv(n / 4 + 1, (int64_t)kThreads * 4);
+  if (max_blocks <= 0) max_blocks = 64;
+  if (max_blocks > kMaxBlocks) max_blocks = kMaxBlocks;
+  if (max_blocks > num_sms()) max_blocks = num_sms();
+  if (blocks > max_blocks) blocks = max_blocks;
+  if (blocks < 1) blocks = 1;
+  broadcast_kernel<<<blocks, kThreads, 0, (cudaStream_t)stream>>>(*cm, src, offset, n);
+  TDL_LAUNCH_OK("p2p broadcast");
   return 0;
 }

@@ -161,6 +161,7 @@ int tdl_p2p_comm_create(int world, int rank, void** grad_ptrs, void** param_ptrs
                         int emulate, void** out_comm);
 int tdl_p2p_comm_set_multicast(void* comm, void* mc_grad, void* mc_param); /* NVLS multicast addresses, mode 3 */
 int tdl_p2p_comm_destroy(void* comm);
+int tdl_p2p_broadcast(void* comm, int src, int64_t offset, int64_t n, int max_blocks, void* stream); /* param mirror */
 int tdl_p2p_fused_step(void* comm, int64_t offset, int64_t n, int mode, int kind, int grad_is_bf16, int zero_grad,
                        float* m1, float* m2, const float* lr_state, float a, float b, float c, float grad_scale,
                        int max_blocks, void* stream);

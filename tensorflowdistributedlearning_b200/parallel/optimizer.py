@@ -78,9 +78,8 @@ class DistributedOptimizer:
         self.m2 = torch.zeros(n, dtype=torch.float32, device=dev) if kind == "adam" else None
         self.global_step = torch.zeros(1, dtype=torch.int64, device=dev)
         self.lr_state = torch.zeros(2, dtype=torch.float32, device=dev)
-        # X2: tower 0's initial values everywhere
-        group.broadcast_(self.flat.param_flat)
-        group.broadcast_(self.flat.stats_flat)
+        # X2: tower 0's initial values everywhere (parameters over the P2P kernel when the symmetric heap exists,
+        # the small statistics buffer and every non-P2P configuration through the process group)
         if comm == "p2p":
             from .p2p import P2PComm
 
@@ -88,6 +87,11 @@ class DistributedOptimizer:
             self.nvls = self.nvls and self._p2p.has_multicast
             self._p2p_stats = P2PComm(self._symm["stats"], None)
             self._stats_staging = torch.zeros_like(self.flat.stats_flat)
+            self._p2p.broadcast_params_(self.flat.total)
+            torch.cuda.synchronize()
+        else:
+            group.broadcast_(self.flat.param_flat)
+        group.broadcast_(self.flat.stats_flat)
         # overlap machinery
         self.overlap = bool(overlap and comm == "p2p")
         self._pending = [0] * len(self.flat.buckets)

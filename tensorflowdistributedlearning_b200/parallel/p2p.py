@@ -147,6 +147,13 @@ class P2PComm:
                                         ctypes.c_float(grad_scale), ctypes.c_int(max_blocks), N.stream_ptr())
         N.check(rc, "tdl_p2p_fused_step")
 
+    def broadcast_params_(self, n: int, src: int = 0, offset: int = 0, max_blocks: int = 64) -> None:
+        """X2 (initial parameter mirror) over NVLink: every rank pulls ``src``'s parameters with a copy kernel bracketed
+        by the signal-pad barriers (``tdl_p2p_broadcast``); all ranks must call it."""
+        rc = N.lib().tdl_p2p_broadcast(self.handle, ctypes.c_int(src), ctypes.c_int64(offset), ctypes.c_int64(n),
+                                       ctypes.c_int(max_blocks), N.stream_ptr())
+        N.check(rc, "tdl_p2p_broadcast")
+
     def all_reduce_mean_(self, staging: torch.Tensor, offset: int, n: int, max_blocks: int = 8):
         """In-place mean over ranks of grad[offset:offset+n] (fp32), one-shot.  ``staging`` is fp32 scratch."""
         self.fused_step(offset, n, kind=0, grad_is_bf16=False, zero_grad=False, m1=staging, m2=None, lr_state=None,

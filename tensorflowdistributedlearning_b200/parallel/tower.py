@@ -17,7 +17,11 @@ import torch.distributed as dist
 
 
 class TowerGroup:
-    def __init__(self, device: Optional[str] = None, backend: Optional[str] = None, timeout_s: int = 600):
+    def __init__(self, device: Optional[str] = None, backend: Optional[str] = None, timeout_s: Optional[int] = None):
+        # collective timeout = the failure detector of the host-side path: a tower that dies or hangs makes its
+        # peers raise after this many seconds instead of waiting forever (TDL_COLLECTIVE_TIMEOUT_S overrides)
+        if timeout_s is None:
+            timeout_s = int(os.environ.get("TDL_COLLECTIVE_TIMEOUT_S", "600"))
         self.rank = int(os.environ.get("RANK", "0"))
         self.world = int(os.environ.get("WORLD_SIZE", "1"))
         self.local_rank = int(os.environ.get("LOCAL_RANK", str(self.rank)))

@@ -9,6 +9,8 @@ synchronisation is the read of the scalar loss.
 """
 from __future__ import annotations
 
+import os
+
 from typing import Callable, Optional, Tuple
 
 import torch
@@ -52,6 +54,7 @@ class TowerTrainer:
         self.loss = torch.zeros((), dtype=torch.float32, device=dev)
         self.metrics = {}
         self.use_graph = bool(use_graph and dev.type == "cuda")
+        self._nvtx = os.environ.get("TDL_NVTX", "0") == "1"
         self._graph: Optional[torch.cuda.CUDAGraph] = None
         self._copy_stream = torch.cuda.Stream() if dev.type == "cuda" else None
         self._copied = torch.cuda.Event() if dev.type == "cuda" else None
@@ -77,12 +80,25 @@ class TowerTrainer:
         return x
 
     def _step_body(self) -> None:
+        # NVTX ranges per phase (TDL_NVTX=1): eager steps only -- inside a captured graph the ranges would mark the
+        # capture, not the replays (`scripts/profile_step.py` gives the per-kernel table)
+        nvtx = self._nvtx and self.device.type == "cuda" and not torch.cuda.is_current_stream_capturing()
+        mark = torch.cuda.nvtx.range_push if nvtx else (lambda *_: None)
+        done = torch.cuda.nvtx.range_pop if nvtx else (lambda: None)
+        mark("tdl/input")
         x = self._prepare_input()
+        done()
         self.opt.begin_step()
+        mark("tdl/forward")
         out = self.model(x)
         loss, metrics = self.loss_fn(out, self.labels)
+        done()
+        mark("tdl/backward+bucket_allreduce")
         loss.backward()
+        done()
+        mark("tdl/optimizer_tail")
         self.opt.step()
+        done()
         self.loss.copy_(loss.detach())
         for k, v in metrics.items():
             if k not in self.metrics:

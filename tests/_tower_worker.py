@@ -29,6 +29,8 @@ def main():
     xs, ys = X[group.rank * per:(group.rank + 1) * per], Y[group.rank * per:(group.rank + 1) * per]
     hashes = []
     for step in range(3):
+        if mode == "rank1_dies" and group.rank == 1 and step == 1:
+            os._exit(17)  # fault injection: a tower disappears mid-run without any goodbye
         opt.begin_step()
         loss, _, _ = TF.softmax_cross_entropy(model(xs), ys)
         loss.backward()

@@ -157,3 +157,25 @@ def test_model_validation_and_params():
 
     with pytest.raises(ValueError):
         Model("/tmp/x", "/tmp/y", data_format="NDHWC", device="cpu")
+
+
+def test_nan_loss_is_fatal_and_summaries_keep_the_reference_tags(tmp_path):
+    """a non-finite loss stops the run with the step and tower in the message; the summary hook
+    writes the reference's scalar tags (model.py:449-454) to ``<dir>/summaries.jsonl`` every ``save_steps`` steps."""
+    import json
+    import types
+
+    from tensorflowdistributedlearning_b200.estimator.hooks import NanLossHook, SummarySaverHook
+
+    est = types.SimpleNamespace(group=types.SimpleNamespace(rank=3, is_primary=True))
+    NanLossHook().after_step(est, 7, {"loss": 0.25})
+    with pytest.raises(FloatingPointError, match="step 7 on tower 3"):
+        NanLossHook().after_step(est, 7, {"loss": float("nan")})
+    hook = SummarySaverHook(str(tmp_path / "train"), save_steps=20)
+    hook.begin(est)
+    for step in (19, 20, 40):
+        hook.after_step(est, step, {"loss/lovasz_loss": 1.0 / step, "metrics/mean_iou": 0.5, "metrics/mean_acc": 0.9})
+    hook.end(est, 40)
+    recs = [json.loads(l) for l in open(tmp_path / "train" / "summaries.jsonl")]
+    assert [r["step"] for r in recs] == [20, 40]
+    assert set(recs[0]) == {"step", "loss/lovasz_loss", "metrics/mean_iou", "metrics/mean_acc"}

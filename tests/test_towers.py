@@ -52,3 +52,15 @@ def test_moving_statistics_are_the_tower_mean(runs):
     assert torch.equal(a["stats"], b["stats"])          # synced (X3) ...
     frozen = runs[("frozen_bn", 2)][0]["stats"]
     assert not torch.equal(a["stats"], frozen)           # ... and actually updated by training-mode BN
+
+
+def test_a_dead_tower_is_detected_not_waited_for(tmp_path):
+    """Fault injection: tower 1 exits abruptly before step 1; tower 0 must fail with an error from the
+    collective (peer closed / timeout) instead of hanging, and the launcher must report a non-zero exit."""
+    env = dict(os.environ, OMP_NUM_THREADS="2", TDL_COLLECTIVE_TIMEOUT_S="15")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+           "127.0.0.1", "--master-port", str(_free_port()), os.path.join(HERE, "_tower_worker.py"), str(tmp_path),
+           "rank1_dies"]
+    r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=300)
+    assert r.returncode != 0
+    assert not os.path.exists(os.path.join(tmp_path, "rank1_dies_w2_r0.pt"))  # tower 0 never reported success
