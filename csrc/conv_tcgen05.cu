@@ -96,6 +96,7 @@ struct Geometry {
   int relu, has_bias, has_res;
   // first-layer ("stem") mode only: byte pitches of the haloed space-to-depth patch in shared memory
   int sp_plane, sp_row, sp_tx, sp_wbytes;
+  int res_mma;  // residual tile added on the tensor core (extra K iterations against an identity block)
 };
 
 // Pick the (TN, TH, TW) pixel patch with the best row utilisation for `rows` GEMM rows.
@@ -170,10 +171,18 @@ struct FpropCfg {
 // 16-byte core-matrix row, every tap's A operand is just that patch at a shifted start address (K-major "interleave"
 // descriptor: SBO = 8 pixels, LBO = plane pitch).  No im2col, no per-tap loads; the whole weight tensor
 // [K][taps*16] stays resident in shared memory.
-template <int BLOCK_N, bool kFused, bool kStats, bool kStem = false>
+//
+// kResMma: `y = conv(x) + residual` with the residual added ON THE TENSOR CORE: after the real K iterations the
+// producer streams the residual tile (same pixel patch, 64 channels at a time) through the normal smem pipeline as an
+// A operand and the MMA warp multiplies it by a 64x64 identity block into the matching 64 accumulator columns
+// (bf16 x 1.0 accumulates exactly in fp32).  The epilogue stays the lean one, and the residual read is prefetched by
+// the same mbarrier pipeline as everything else.  Used by the data gradient of a unit's first conv to absorb the
+// identity-shortcut gradient (otherwise a separate 3-pass elementwise add per residual unit).
+template <int BLOCK_N, bool kFused, bool kStats, bool kStem = false, bool kResMma = false>
 __global__ void __launch_bounds__(kFpropThreads, 1)
 conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
-                  const __grid_constant__ CUtensorMap tm_y, const Geometry g, const float* __restrict__ bias,
+                  const __grid_constant__ CUtensorMap tm_y, const __grid_constant__ CUtensorMap tm_res,
+                  const __grid_constant__ CUtensorMap tm_id, const Geometry g, const float* __restrict__ bias,
                   const bf16* __restrict__ residual, float* __restrict__ stats) {
   using Cfg = FpropCfg<BLOCK_N>;
   constexpr int kStages = Cfg::kStages;
@@ -209,6 +218,10 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
     ptx::prefetch_tmap(&tm_x);
     ptx::prefetch_tmap(&tm_w);
     ptx::prefetch_tmap(&tm_y);
+    if constexpr (kResMma) {
+      ptx::prefetch_tmap(&tm_res);
+      ptx::prefetch_tmap(&tm_id);
+    }
   }
   if (warp == 1) {
     if (lane == 0) {
@@ -286,6 +299,20 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
             }
           }
         }
+        if constexpr (kResMma) {
+          const int res_chunks = min(BLOCK_N / 64, (g.K - n_tile * BLOCK_N + 63) / 64);
+          for (int j = 0; j < res_chunks; ++j) {
+            ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+            ptx::mbar_expect_tx(&full_bar[stage], a_tx + 8192u);
+            ptx::tma_load_4d(smem_a + stage * kABytes, &tm_res, &full_bar[stage], n_tile * BLOCK_N + j * 64,
+                             tw_i * g.TW, th_i * g.TH, tn_i * g.TN);
+            ptx::tma_load_2d(smem_b + stage * Cfg::kBBytes, &tm_id, &full_bar[stage], 0, 0);
+            if (++stage == kStages) {
+              stage = 0;
+              phase ^= 1;
+            }
+          }
+        }
       }
     }
   } else if (warp == 1) {
@@ -343,6 +370,26 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
           if (++stage == kStages) {
             stage = 0;
             phase ^= 1;
+          }
+        }
+        if constexpr (kResMma) {
+          constexpr uint32_t idesc64 = ptx::umma_idesc_bf16(kBlockM, 64, 0, 0);
+          const int n_tile = tile % g.n_tiles;
+          const int res_chunks = min(BLOCK_N / 64, (g.K - n_tile * BLOCK_N + 63) / 64);
+          for (int j = 0; j < res_chunks; ++j) {
+            ptx::mbar_wait(&full_bar[stage], phase);
+            ptx::tc_fence_after();
+            const uint64_t a_desc = ptx::umma_smem_desc_sw128(ptx::smem_u32(smem_a + stage * kABytes), 16, 1024);
+            const uint64_t b_desc = ptx::umma_smem_desc_sw128(ptx::smem_u32(smem_b + stage * Cfg::kBBytes), 16, 1024);
+#pragma unroll
+            for (int k = 0; k < kBlockK / 16; ++k)
+              ptx::umma_bf16(d_tmem + (uint32_t)(j * 64), a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc64,
+                             1u);
+            ptx::umma_commit(&empty_bar[stage]);
+            if (++stage == kStages) {
+              stage = 0;
+              phase ^= 1;
+            }
           }
         }
         ptx::umma_commit(&tmem_full[acc]);  // accumulator complete -> epilogue
@@ -812,40 +859,66 @@ static int launch_stem(const CUtensorMap& tx, const CUtensorMap& tw, const CUten
   const int total = g.tiles_n * g.tiles_h * g.tiles_w;
   const int grid = total < tdl::num_sms() ? total : tdl::num_sms();
   if (nparts) *nparts = grid;
-  conv_fprop_kernel<64, false, kStats, true><<<grid, kFpropThreads, Cfg::kSmemBytes, st>>>(tx, tw, ty, g, nullptr, nullptr,
-                                                                                      stats);
+  conv_fprop_kernel<64, false, kStats, true><<<grid, kFpropThreads, Cfg::kSmemBytes, st>>>(tx, tw, ty, ty, ty, g, nullptr,
+                                                                                           nullptr, stats);
   TDL_LAUNCH_OK("conv_fprop_kernel(stem)");
   return 0;
 }
 
-template <int BLOCK_N, bool kFused, bool kStats>
-static int launch_fprop_t(const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& ty, const Geometry& g,
-                          const float* bias, const bf16* res, float* stats, int* nparts, cudaStream_t st) {
+template <int BLOCK_N, bool kFused, bool kStats, bool kResMma = false>
+static int launch_fprop_t(const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& ty, const CUtensorMap& tres,
+                          const CUtensorMap& tid, const Geometry& g, const float* bias, const bf16* res, float* stats,
+                          int* nparts, cudaStream_t st) {
   using Cfg = FpropCfg<BLOCK_N>;
   static bool attr_set = false;
   if (!attr_set) {
-    TDL_CUDA_OK(cudaFuncSetAttribute(conv_fprop_kernel<BLOCK_N, kFused, kStats>,
+    TDL_CUDA_OK(cudaFuncSetAttribute(conv_fprop_kernel<BLOCK_N, kFused, kStats, false, kResMma>,
                                      cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
     attr_set = true;
   }
   const int total = g.tiles_n * g.tiles_h * g.tiles_w * g.n_tiles;
   const int grid = total < tdl::num_sms() ? total : tdl::num_sms();
   if (nparts) *nparts = grid;
-  conv_fprop_kernel<BLOCK_N, kFused, kStats><<<grid, kFpropThreads, Cfg::kSmemBytes, st>>>(tx, tw, ty, g, bias, res, stats);
+  conv_fprop_kernel<BLOCK_N, kFused, kStats, false, kResMma><<<grid, kFpropThreads, Cfg::kSmemBytes, st>>>(
+      tx, tw, ty, tres, tid, g, bias, res, stats);
   TDL_LAUNCH_OK("conv_fprop_kernel");
   return 0;
 }
 
 template <int BLOCK_N>
-static int launch_fprop(const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& ty, const Geometry& g,
-                        const float* bias, const bf16* res, float* stats, int* nparts, cudaStream_t st) {
+static int launch_fprop(const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& ty, const CUtensorMap& tres,
+                        const CUtensorMap& tid, const Geometry& g, const float* bias, const bf16* res, float* stats,
+                        int* nparts, cudaStream_t st) {
+  if (g.res_mma) return launch_fprop_t<BLOCK_N, false, false, true>(tx, tw, ty, tres, tid, g, bias, res, stats, nparts, st);
   const bool fused = g.has_bias || g.has_res || g.relu;
   if (stats) {
-    if (fused) return launch_fprop_t<BLOCK_N, true, true>(tx, tw, ty, g, bias, res, stats, nparts, st);
-    return launch_fprop_t<BLOCK_N, false, true>(tx, tw, ty, g, bias, res, stats, nparts, st);
+    if (fused) return launch_fprop_t<BLOCK_N, true, true>(tx, tw, ty, tres, tid, g, bias, res, stats, nparts, st);
+    return launch_fprop_t<BLOCK_N, false, true>(tx, tw, ty, tres, tid, g, bias, res, stats, nparts, st);
   }
-  if (fused) return launch_fprop_t<BLOCK_N, true, false>(tx, tw, ty, g, bias, res, stats, nparts, st);
-  return launch_fprop_t<BLOCK_N, false, false>(tx, tw, ty, g, bias, res, stats, nparts, st);
+  if (fused) return launch_fprop_t<BLOCK_N, true, false>(tx, tw, ty, tres, tid, g, bias, res, stats, nparts, st);
+  return launch_fprop_t<BLOCK_N, false, false>(tx, tw, ty, tres, tid, g, bias, res, stats, nparts, st);
+}
+
+// 64x64 bf16 identity block in global memory (the B operand of the residual-on-the-tensor-core iterations)
+__device__ __align__(1024) bf16 g_identity64[64 * 64];
+__global__ void identity64_init_kernel() {
+  for (int i = threadIdx.x; i < 64 * 64; i += blockDim.x) g_identity64[i] = __float2bfloat16((i >> 6) == (i & 63) ? 1.f : 0.f);
+}
+static int identity64_address(const void** out, cudaStream_t st) {
+  constexpr int kMaxDev = 64;
+  static void* addr[kMaxDev] = {nullptr};
+  int dev = 0;
+  TDL_CUDA_OK(cudaGetDevice(&dev));
+  TDL_REQUIRE(dev >= 0 && dev < kMaxDev, "device ordinal out of range");
+  if (addr[dev] == nullptr) {
+    void* p = nullptr;
+    TDL_CUDA_OK(cudaGetSymbolAddress(&p, g_identity64));
+    identity64_init_kernel<<<1, 256, 0, st>>>();  // ordered before the first consumer on the same stream
+    TDL_LAUNCH_OK("identity64_init_kernel");
+    addr[dev] = p;
+  }
+  *out = addr[dev];
+  return 0;
 }
 
 template <int MT, int BLOCK_N>
@@ -912,6 +985,9 @@ static int fprop_impl(const void* x, const void* w, void* y, const float* bias, 
   g.tiles_w = (int)cdiv(g.Q, g.TW);
   g.num_kb = (int)cdiv(C, kBlockK);
   g.relu = relu; g.has_bias = bias != nullptr; g.has_res = residual != nullptr;
+  // plain "+ residual" (no bias / ReLU / statistics / strided view): add it on the tensor core, keep the lean epilogue
+  g.res_mma = (residual != nullptr && bias == nullptr && !relu && stats == nullptr && view == nullptr) ? 1 : 0;
+  if (g.res_mma) g.has_res = 0;
   const int block_n = K > 128 ? 256 : (K > 64 ? 128 : 64);
   g.n_tiles = (int)cdiv(K, block_n);
 
@@ -947,9 +1023,25 @@ static int fprop_impl(const void* x, const void* w, void* y, const float* bias, 
     if (rc) return rc;
   }
   cudaStream_t st = (cudaStream_t)stream;
-  if (block_n == 256) return launch_fprop<256>(tx, tw, ty, g, bias, (const bf16*)residual, stats, nparts, st);
-  if (block_n == 128) return launch_fprop<128>(tx, tw, ty, g, bias, (const bf16*)residual, stats, nparts, st);
-  return launch_fprop<64>(tx, tw, ty, g, bias, (const bf16*)residual, stats, nparts, st);
+  CUtensorMap tres = ty, tid = ty;
+  if (g.res_mma) {
+    TDL_REQUIRE((reinterpret_cast<uintptr_t>(residual) & 15) == 0, "residual must be 16-byte aligned");
+    uint64_t dims[4] = {(uint64_t)K, (uint64_t)g.Q, (uint64_t)g.P, (uint64_t)g.N};
+    uint32_t box[4] = {64, (uint32_t)g.TW, (uint32_t)g.TH, (uint32_t)g.TN};
+    uint32_t es[4] = {1, 1, 1, 1};
+    int rc = encode_bf16(&tres, residual, 4, dims, box, es);
+    if (rc) return rc;
+    const void* ident = nullptr;
+    rc = identity64_address(&ident, st);
+    if (rc) return rc;
+    uint64_t idims[2] = {64, 64};
+    uint32_t ibox[2] = {64, 64};
+    rc = encode_bf16(&tid, ident, 2, idims, ibox, es);
+    if (rc) return rc;
+  }
+  if (block_n == 256) return launch_fprop<256>(tx, tw, ty, tres, tid, g, bias, (const bf16*)residual, stats, nparts, st);
+  if (block_n == 128) return launch_fprop<128>(tx, tw, ty, tres, tid, g, bias, (const bf16*)residual, stats, nparts, st);
+  return launch_fprop<64>(tx, tw, ty, tres, tid, g, bias, (const bf16*)residual, stats, nparts, st);
 }
 
 // y[N,P,Q,K] = conv(x[N,H,W,C], w[K,R*S,C]) (+bias) (+residual) (ReLU)      bf16 in/out, fp32 accumulate

@@ -114,11 +114,15 @@ class BottleneckV1(TFModule):
                          ConvBNAct(depth_in, depth, 1, stride=stride, scope=f"{s}/shortcut", bn=bn, relu=False))
 
     def forward(self, x, end_points: Optional[dict] = None, prefix: str = ""):
-        # (ConvBNAct(want_tap=True) can fold the identity shortcut's gradient into conv1's data-gradient epilogue; it
-        #  measured slower than autograd's separate add on B200 -- the per-row residual loads stall the epilogue --
-        #  so the plain form is used.)
-        sc = x if self.shortcut is None else self.shortcut(x)
-        out = self.conv3(self.conv2(self.conv1(x)), residual=sc)  # relu(bn(conv3) + shortcut), one kernel
+        if self.shortcut is None and self.training and torch.is_grad_enabled():
+            # identity shortcut: take it from conv1's input alias, so that in backward the shortcut's gradient reaches
+            # conv1's node and is added inside its data-gradient kernel (on the tensor core, csrc/conv_tcgen05.cu
+            # kResMma) instead of by a separate elementwise add
+            h, sc = self.conv1(x, want_tap=True)
+        else:
+            h = self.conv1(x)
+            sc = x if self.shortcut is None else self.shortcut(x)
+        out = self.conv3(self.conv2(h), residual=sc)  # relu(bn(conv3) + shortcut), one kernel
         if end_points is not None:
             end_points[f"{prefix}{self.scope}"] = out
         return out

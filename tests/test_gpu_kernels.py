@@ -46,6 +46,8 @@ CONV_CASES = [
     (2, 56, 128, 128, 3, 2, 1, False, False, False),     # stride 2 through TMA element strides
     (2, 51, 64, 64, 3, 2, 1, False, False, False),       # odd size, TF SAME
     (2, 56, 256, 512, 1, 2, 1, False, False, False),
+    (4, 28, 128, 512, 1, 1, 1, False, True, False),      # residual only: added on the tensor core (identity-block MMA)
+    (3, 14, 256, 72, 3, 1, 1, False, True, False),       # same, 3x3 with a ragged last channel chunk
 ]
 
 
