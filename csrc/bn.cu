@@ -176,8 +176,8 @@ __global__ void bn_infer_scale_shift_kernel(const float* __restrict__ gamma, con
 // registers, the row loop keeps two independent 16-byte loads in flight.
 __global__ void __launch_bounds__(kThreads)
 bn_apply_kernel(const bf16* __restrict__ x, const float* __restrict__ scale, const float* __restrict__ shift,
-                const bf16* __restrict__ residual, bf16* __restrict__ y, int64_t rows, int C, int tx, int ty,
-                int relu) {
+                const bf16* __restrict__ residual, bf16* __restrict__ y, uint8_t* __restrict__ mask_out, int64_t rows,
+                int C, int tx, int ty, int relu) {
   const int cx = threadIdx.x % tx;
   const int ry = threadIdx.x / tx;
   const int cv = blockIdx.y * tx + cx;
@@ -199,6 +199,12 @@ bn_apply_kernel(const bf16* __restrict__ x, const float* __restrict__ scale, con
       for (int j = 0; j < 8; ++j) f[j] += rr[j];
     }
     if (relu) {
+      if (mask_out) {  // one bit per element: the backward pass reads this instead of the whole activation
+        uint32_t m = 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) m |= (f[j] > 0.f ? 1u : 0u) << j;
+        mask_out[r * (C >> 3) + cv] = (uint8_t)m;
+      }
 #pragma unroll
       for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
     }
@@ -232,7 +238,7 @@ __global__ void __launch_bounds__(kThreads)
 bn_bwd_partial_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ x, const bf16* __restrict__ z,
                       const float* __restrict__ scale, const float* __restrict__ shift,
                       const float* __restrict__ mean, const float* __restrict__ invstd, int64_t rows, int C, int tx,
-                      int ty, int relu, float* __restrict__ partial) {
+                      int ty, int relu, int z_bits, float* __restrict__ partial) {
   extern __shared__ float sm[];
   const int cx = threadIdx.x % tx;
   const int ry = threadIdx.x / tx;
@@ -252,12 +258,15 @@ bn_bwd_partial_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ x, c
     const int64_t step = (int64_t)gridDim.x * ty;
     const int64_t col = (int64_t)cv * 8;
     // q accumulates dy * (x - mean); the invstd factor is applied once at the end
-    auto one = [&](const bf16x8& gv, const bf16x8& xv, const bf16x8* zv) {
+    auto one = [&](const bf16x8& gv, const bf16x8& xv, const bf16x8* zv, int mb) {
       float g[8], f[8];
       unpack8(gv, g);
       unpack8(xv, f);
       if (relu) {
-        if (zv) {
+        if (mb >= 0) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) g[j] = ((mb >> j) & 1) ? g[j] : 0.f;
+        } else if (zv) {
           float zz[8];
           unpack8(*zv, zz);
 #pragma unroll
@@ -277,22 +286,29 @@ bn_bwd_partial_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ x, c
     for (; r + step < rows; r += 2 * step) {
       const bf16x8 g0 = ld8(dz + r * C + col), g1 = ld8(dz + (r + step) * C + col);
       const bf16x8 x0 = ld8(x + r * C + col), x1 = ld8(x + (r + step) * C + col);
-      if (relu && z) {
+      if (relu && z && z_bits) {
+        const uint8_t* zb = reinterpret_cast<const uint8_t*>(z);
+        const int m0 = zb[r * c8 + cv], m1 = zb[(r + step) * c8 + cv];
+        one(g0, x0, nullptr, m0);
+        one(g1, x1, nullptr, m1);
+      } else if (relu && z) {
         const bf16x8 z0 = ld8(z + r * C + col), z1 = ld8(z + (r + step) * C + col);
-        one(g0, x0, &z0);
-        one(g1, x1, &z1);
+        one(g0, x0, &z0, -1);
+        one(g1, x1, &z1, -1);
       } else {
-        one(g0, x0, nullptr);
-        one(g1, x1, nullptr);
+        one(g0, x0, nullptr, -1);
+        one(g1, x1, nullptr, -1);
       }
     }
     for (; r < rows; r += step) {
       const bf16x8 g0 = ld8(dz + r * C + col), x0 = ld8(x + r * C + col);
-      if (relu && z) {
+      if (relu && z && z_bits) {
+        one(g0, x0, nullptr, (int)reinterpret_cast<const uint8_t*>(z)[r * c8 + cv]);
+      } else if (relu && z) {
         const bf16x8 z0 = ld8(z + r * C + col);
-        one(g0, x0, &z0);
+        one(g0, x0, &z0, -1);
       } else {
-        one(g0, x0, nullptr);
+        one(g0, x0, nullptr, -1);
       }
     }
 #pragma unroll
@@ -338,7 +354,7 @@ bn_bwd_apply_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ x, con
                     const float* __restrict__ scale, const float* __restrict__ shift, const float* __restrict__ mean,
                     const float* __restrict__ invstd, const float* __restrict__ dbeta,
                     const float* __restrict__ dgamma, float inv_n, bf16* __restrict__ dx, bf16* __restrict__ dres,
-                    int64_t rows, int C, int tx, int ty, int relu) {
+                    int64_t rows, int C, int tx, int ty, int relu, int z_bits) {
   const int cx = threadIdx.x % tx;
   const int ry = threadIdx.x / tx;
   const int cv = blockIdx.y * tx + cx;
@@ -355,12 +371,15 @@ bn_bwd_apply_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ x, con
   }
   const int64_t step = (int64_t)gridDim.x * ty;
   const int64_t col = (int64_t)cv * 8;
-  auto one = [&](int64_t r, const bf16x8& gv, const bf16x8& xv, const bf16x8* zv) {
+  auto one = [&](int64_t r, const bf16x8& gv, const bf16x8& xv, const bf16x8* zv, int mb) {
     float g[8], f[8], o[8];
     unpack8(gv, g);
     unpack8(xv, f);
     if (relu) {
-      if (zv) {
+      if (mb >= 0) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) g[j] = ((mb >> j) & 1) ? g[j] : 0.f;
+      } else if (zv) {
         float zz[8];
         unpack8(*zv, zz);
 #pragma unroll
@@ -379,22 +398,29 @@ bn_bwd_apply_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ x, con
   for (; r + step < rows; r += 2 * step) {
     const bf16x8 g0 = ld8(dz + r * C + col), g1 = ld8(dz + (r + step) * C + col);
     const bf16x8 x0 = ld8(x + r * C + col), x1 = ld8(x + (r + step) * C + col);
-    if (relu && z) {
+    if (relu && z && z_bits) {
+      const uint8_t* zb = reinterpret_cast<const uint8_t*>(z);
+      const int m0 = zb[r * (C >> 3) + cv], m1 = zb[(r + step) * (C >> 3) + cv];
+      one(r, g0, x0, nullptr, m0);
+      one(r + step, g1, x1, nullptr, m1);
+    } else if (relu && z) {
       const bf16x8 z0 = ld8(z + r * C + col), z1 = ld8(z + (r + step) * C + col);
-      one(r, g0, x0, &z0);
-      one(r + step, g1, x1, &z1);
+      one(r, g0, x0, &z0, -1);
+      one(r + step, g1, x1, &z1, -1);
     } else {
-      one(r, g0, x0, nullptr);
-      one(r + step, g1, x1, nullptr);
+      one(r, g0, x0, nullptr, -1);
+      one(r + step, g1, x1, nullptr, -1);
     }
   }
   for (; r < rows; r += step) {
     const bf16x8 g0 = ld8(dz + r * C + col), x0 = ld8(x + r * C + col);
-    if (relu && z) {
+    if (relu && z && z_bits) {
+      one(r, g0, x0, nullptr, (int)reinterpret_cast<const uint8_t*>(z)[r * (C >> 3) + cv]);
+    } else if (relu && z) {
       const bf16x8 z0 = ld8(z + r * C + col);
-      one(r, g0, x0, &z0);
+      one(r, g0, x0, &z0, -1);
     } else {
-      one(r, g0, x0, nullptr);
+      one(r, g0, x0, nullptr, -1);
     }
   }
 }
@@ -495,21 +521,24 @@ TDL_API int tdl_bn_infer_scale_shift(const float* gamma, const float* beta, cons
 }
 
 // y = relu?(x*scale + shift (+ residual))
+// mask_out (may be NULL; only meaningful with relu): [rows][C/8] bytes, bit j of byte (r, c/8) = (pre-ReLU value of
+// channel 8*(c/8)+j was > 0).  Pass it as `z` with z_is_bitmask = 1 to the backward entry points.
 TDL_API int tdl_bn_apply(const void* x, const float* scale, const float* shift, const void* residual, void* y,
-                         int64_t rows, int C, int relu, void* stream) {
+                         void* mask_out, int64_t rows, int C, int relu, void* stream) {
   TDL_REQUIRE(C > 0 && C % 8 == 0, "C must be a positive multiple of 8");
   if (rows == 0) return 0;
   ReduceShape s = apply_shape(rows, C);
   dim3 grid(s.gx, s.gy);
   bn_apply_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>((const bf16*)x, scale, shift, (const bf16*)residual,
-                                                               (bf16*)y, rows, C, s.tx, s.ty, relu);
+                                                               (bf16*)y, (uint8_t*)mask_out, rows, C, s.tx, s.ty, relu);
   TDL_LAUNCH_OK("bn_apply_kernel");
   return 0;
 }
 
 // dbeta/dgamma for this layer (written), optionally also accumulated into acc_* (the flat gradient slots).
-TDL_API int tdl_bn_bwd_reduce(const void* dz, const void* x, const void* z, const float* scale, const float* shift,
-                              const float* mean, const float* invstd, int64_t rows, int C, int relu, float* scratch,
+TDL_API int tdl_bn_bwd_reduce(const void* dz, const void* x, const void* z, int z_is_bitmask, const float* scale,
+                              const float* shift, const float* mean, const float* invstd, int64_t rows, int C, int relu,
+                              float* scratch,
                               int64_t scratch_floats, float* dgamma, float* dbeta, float* acc_dgamma,
                               float* acc_dbeta, void* stream) {
   TDL_REQUIRE(C > 0 && C % 8 == 0, "C must be a positive multiple of 8");
@@ -518,7 +547,8 @@ TDL_API int tdl_bn_bwd_reduce(const void* dz, const void* x, const void* z, cons
   cudaStream_t st = (cudaStream_t)stream;
   dim3 grid(s.gx, s.gy);
   bn_bwd_partial_kernel<<<grid, kThreads, kThreads * 16 * sizeof(float), st>>>(
-      (const bf16*)dz, (const bf16*)x, (const bf16*)z, scale, shift, mean, invstd, rows, C, s.tx, s.ty, relu, scratch);
+      (const bf16*)dz, (const bf16*)x, (const bf16*)z, scale, shift, mean, invstd, rows, C, s.tx, s.ty, relu,
+      z_is_bitmask, scratch);
   TDL_LAUNCH_OK("bn_bwd_partial_kernel");
   bn_bwd_finalize_kernel<<<(C + kFinCh - 1) / kFinCh, kFinThreads, 0, st>>>(scratch, s.gx, C, dbeta, dgamma, acc_dbeta,
                                                                             acc_dgamma);
@@ -526,8 +556,8 @@ TDL_API int tdl_bn_bwd_reduce(const void* dz, const void* x, const void* z, cons
   return 0;
 }
 
-TDL_API int tdl_bn_bwd_apply(const void* dz, const void* x, const void* z, const float* scale, const float* shift,
-                             const float* mean, const float* invstd, const float* dgamma, const float* dbeta,
+TDL_API int tdl_bn_bwd_apply(const void* dz, const void* x, const void* z, int z_is_bitmask, const float* scale,
+                             const float* shift, const float* mean, const float* invstd, const float* dgamma, const float* dbeta,
                              void* dx, void* dres, int64_t rows, int C, int relu, void* stream) {
   TDL_REQUIRE(C > 0 && C % 8 == 0, "C must be a positive multiple of 8");
   if (rows == 0) return 0;
@@ -535,7 +565,7 @@ TDL_API int tdl_bn_bwd_apply(const void* dz, const void* x, const void* z, const
   dim3 grid(s.gx, s.gy);
   bn_bwd_apply_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(
       (const bf16*)dz, (const bf16*)x, (const bf16*)z, scale, shift, mean, invstd, dbeta, dgamma, 1.f / (float)rows,
-      (bf16*)dx, (bf16*)dres, rows, C, s.tx, s.ty, relu);
+      (bf16*)dx, (bf16*)dres, rows, C, s.tx, s.ty, relu, z_is_bitmask);
   TDL_LAUNCH_OK("bn_bwd_apply_kernel");
   return 0;
 }

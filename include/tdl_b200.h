@@ -63,15 +63,18 @@ int tdl_bn_finalize_partials(const float* partial, int nparts, int64_t rows, int
                              float* mean, float* invstd, float* scale, float* shift, void* stream);
 int tdl_bn_infer_scale_shift(const float* gamma, const float* beta, const float* running_mean,
                              const float* running_var, float eps, float* scale, float* shift, int C, void* stream);
-int tdl_bn_apply(const void* x, const float* scale, const float* shift, const void* residual, void* y, int64_t rows,
-                 int C, int relu, void* stream);
-int tdl_bn_bwd_reduce(const void* dz, const void* x, const void* z, const float* scale, const float* shift,
-                      const float* mean, const float* invstd, int64_t rows, int C, int relu, float* scratch,
-                      int64_t scratch_floats, float* dgamma, float* dbeta, float* acc_dgamma, float* acc_dbeta,
-                      void* stream);
-int tdl_bn_bwd_apply(const void* dz, const void* x, const void* z, const float* scale, const float* shift,
-                     const float* mean, const float* invstd, const float* dgamma, const float* dbeta, void* dx,
-                     void* dres, int64_t rows, int C, int relu, void* stream);
+/* mask_out (may be NULL): [rows][C/8] bytes, one bit per element = "pre-ReLU value > 0".  The backward entry points
+ * take either the activation z (bf16, z_is_bitmask = 0), that bit mask (z_is_bitmask = 1), or NULL (mask recomputed
+ * from x, scale, shift -- only valid without a residual). */
+int tdl_bn_apply(const void* x, const float* scale, const float* shift, const void* residual, void* y, void* mask_out,
+                 int64_t rows, int C, int relu, void* stream);
+int tdl_bn_bwd_reduce(const void* dz, const void* x, const void* z, int z_is_bitmask, const float* scale,
+                      const float* shift, const float* mean, const float* invstd, int64_t rows, int C, int relu,
+                      float* scratch, int64_t scratch_floats, float* dgamma, float* dbeta, float* acc_dgamma,
+                      float* acc_dbeta, void* stream);
+int tdl_bn_bwd_apply(const void* dz, const void* x, const void* z, int z_is_bitmask, const float* scale,
+                     const float* shift, const float* mean, const float* invstd, const float* dgamma,
+                     const float* dbeta, void* dx, void* dres, int64_t rows, int C, int relu, void* stream);
 
 /* ---- spatial ops (reference: core/resnet.py:241,246-248,464-465; core/layers.py:34-42,82-109) ---- */
 int tdl_maxpool_fwd(const void* x, void* y, void* idx_u8, int N, int H, int W, int C, int P, int Q, int k, int stride,

@@ -400,11 +400,16 @@ class _BNNative(torch.autograd.Function):
             scale, shift = O.bn_infer_scale_shift(gamma, beta, running_mean, running_var, eps)
             mean = invstd = None
             _count(1)
-        z = O.bn_apply(x2, scale, shift, r2, relu)
+        need_z = training and relu and residual is not None
+        if need_z:
+            # with a residual the ReLU mask cannot be recomputed from x alone: keep it as 1 bit per element (written by
+            # the same kernel) instead of making both backward kernels re-read the whole activation
+            z, zmask = O.bn_apply(x2, scale, shift, r2, relu, want_mask=True)
+        else:
+            z, zmask = O.bn_apply(x2, scale, shift, r2, relu), None
         _count(1)
         if training:
-            need_z = relu and residual is not None
-            ctx.save_for_backward(x2, z if need_z else None, scale, shift, mean, invstd)
+            ctx.save_for_backward(x2, zmask, scale, shift, mean, invstd)
         ctx.cfg = (relu, residual is not None, training, shape)
         return z.view(shape)
 

@@ -195,13 +195,16 @@ def bn_infer_scale_shift(gamma, beta, running_mean, running_var, eps: float):
     return out[0], out[1]
 
 
-def bn_apply(x2d, scale, shift, residual2d, relu: bool):
+def bn_apply(x2d, scale, shift, residual2d, relu: bool, want_mask: bool = False):
+    """y = relu(x*scale + shift (+ residual)).  ``want_mask`` additionally returns the 1-bit-per-element ReLU mask
+    ([rows, C/8] uint8) that the backward kernels accept in place of the activation."""
     rows, C = x2d.shape
     y = torch.empty_like(x2d)
-    rc = N.lib().tdl_bn_apply(N.ptr(x2d), N.ptr(scale), N.ptr(shift), N.ptr(residual2d), N.ptr(y), _i64(rows), _i(C),
-                              _i(int(relu)), N.stream_ptr())
+    mask = torch.empty((rows, C // 8), dtype=torch.uint8, device=x2d.device) if (want_mask and relu) else None
+    rc = N.lib().tdl_bn_apply(N.ptr(x2d), N.ptr(scale), N.ptr(shift), N.ptr(residual2d), N.ptr(y), N.ptr(mask),
+                              _i64(rows), _i(C), _i(int(relu)), N.stream_ptr())
     N.check(rc, "tdl_bn_apply")
-    return y
+    return (y, mask) if want_mask else y
 
 
 def bn_bwd(dz2d, x2d, z2d, scale, shift, mean, invstd, relu: bool, want_dres: bool,
@@ -211,15 +214,16 @@ def bn_bwd(dz2d, x2d, z2d, scale, shift, mean, invstd, relu: bool, want_dres: bo
     dev = x2d.device
     scratch = _bn_scratch(rows, C, dev)
     dgb = torch.empty((2, C), dtype=torch.float32, device=dev)
-    rc = N.lib().tdl_bn_bwd_reduce(N.ptr(dz2d), N.ptr(x2d), N.ptr(z2d), N.ptr(scale), N.ptr(shift), N.ptr(mean),
-                                   N.ptr(invstd), _i64(rows), _i(C), _i(int(relu)), N.ptr(scratch),
+    zbits = int(z2d is not None and z2d.dtype == torch.uint8)  # the 1-bit ReLU mask written by bn_apply
+    rc = N.lib().tdl_bn_bwd_reduce(N.ptr(dz2d), N.ptr(x2d), N.ptr(z2d), _i(zbits), N.ptr(scale), N.ptr(shift),
+                                   N.ptr(mean), N.ptr(invstd), _i64(rows), _i(C), _i(int(relu)), N.ptr(scratch),
                                    _i64(scratch.numel()), N.ptr(dgb[0]), N.ptr(dgb[1]), N.ptr(acc_dgamma),
                                    N.ptr(acc_dbeta), N.stream_ptr())
     N.check(rc, "tdl_bn_bwd_reduce")
     dx = torch.empty_like(x2d)
     dres = torch.empty_like(x2d) if want_dres else None
-    rc = N.lib().tdl_bn_bwd_apply(N.ptr(dz2d), N.ptr(x2d), N.ptr(z2d), N.ptr(scale), N.ptr(shift), N.ptr(mean),
-                                  N.ptr(invstd), N.ptr(dgb[0]), N.ptr(dgb[1]), N.ptr(dx), N.ptr(dres), _i64(rows),
+    rc = N.lib().tdl_bn_bwd_apply(N.ptr(dz2d), N.ptr(x2d), N.ptr(z2d), _i(zbits), N.ptr(scale), N.ptr(shift),
+                                  N.ptr(mean), N.ptr(invstd), N.ptr(dgb[0]), N.ptr(dgb[1]), N.ptr(dx), N.ptr(dres), _i64(rows),
                                   _i(C), _i(int(relu)), N.stream_ptr())
     N.check(rc, "tdl_bn_bwd_apply")
     return dx, dres, dgb[0], dgb[1]

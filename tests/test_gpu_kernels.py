@@ -236,6 +236,15 @@ def test_batch_norm_fwd_bwd(O, rows, C, relu, res):
     assert rel_err(db, b_.grad) < 1e-3
     if res:
         assert rel_err(dres, rr.grad) < 1e-2
+    if res and relu:
+        # the 1-bit ReLU mask written by the apply kernel must give the same gradients as re-reading the activation
+        z2, zmask = O.bn_apply(x, scale, shift, r, relu, want_mask=True)
+        assert torch.equal(z2, z) and zmask.dtype == torch.uint8 and tuple(zmask.shape) == (rows, C // 8)
+        bits = ((zmask.unsqueeze(-1) >> torch.arange(8, device="cuda", dtype=torch.uint8)) & 1).reshape(rows, C).bool()
+        assert torch.equal(bits, z > 0)
+        dx2, dres2, dg2, db2 = O.bn_bwd(dz, x, zmask, scale, shift, mean, invstd, relu, res)
+        assert torch.equal(dx2, dx) and torch.equal(dres2, dres)
+        assert rel_err(dg2, dg) < 1e-6 and rel_err(db2, db) < 1e-6
 
 
 def test_fused_optimizers_and_device_schedule(O):
