@@ -97,6 +97,7 @@ struct Geometry {
   // first-layer ("stem") mode only: byte pitches of the haloed space-to-depth patch in shared memory
   int sp_plane, sp_row, sp_tx, sp_wbytes;
   int res_mma;  // residual tile added on the tensor core (extra K iterations against an identity block)
+  int has_mask; // res_mma only: zero outputs whose bit in a [pixels][K/8] byte mask is clear (fused ReLU backward)
 };
 
 // Pick the (TN, TH, TW) pixel patch with the best row utilisation for `rows` GEMM rows.
@@ -471,7 +472,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
       const int tn_i = m_tile / (g.tiles_w * g.tiles_h);
       bool valid = true;
       size_t pix = 0;
-      if constexpr (kFused || kStats) {
+      if constexpr (kFused || kStats || kResMma) {
         const int n = tn_i * g.TN + dn;
         const int p = th_i * g.TH + dh;
         const int q = tw_i * g.TW + dw;
@@ -532,6 +533,15 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
                   for (int j = 0; j < 8; ++j) f[j8 * 8 + j] = fmaxf(f[j8 * 8 + j], 0.f);
                 }
               }
+            }
+          }
+          if constexpr (kResMma) {
+            // fused ReLU backward of the tensor this gradient belongs to: bit j of byte (pixel, c/8) = "was > 0"
+            if (g.has_mask && valid && co0 < g.K) {
+              const uint8_t* mrow = reinterpret_cast<const uint8_t*>(residual) + pix * (size_t)(g.K >> 3) + (co0 >> 3);
+              const uint32_t mbits = *reinterpret_cast<const uint32_t*>(mrow);
+#pragma unroll
+              for (int j = 0; j < 32; ++j) f[j] = ((mbits >> j) & 1u) ? f[j] : 0.f;
             }
           }
           uint32_t packed[16];
@@ -963,7 +973,8 @@ struct OutView {
 
 static int fprop_impl(const void* x, const void* w, void* y, const float* bias, const void* residual, int N, int H,
                       int W, int C, int K, int R, int S, int stride, int dil, int pad_h, int pad_w, int P, int Q,
-                      int relu, const OutView* view, float* stats, int* nparts, void* stream) {
+                      int relu, const OutView* view, float* stats, int* nparts, void* stream,
+                      const void* out_mask = nullptr) {
   TDL_REQUIRE(C % 8 == 0 && K % 8 == 0, "channel counts must be multiples of 8 (16-byte TMA strides)");
   TDL_REQUIRE(stride >= 1 && stride <= 8 && dil >= 1, "bad stride/dilation");
   TDL_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(w) & 15) == 0 &&
@@ -988,6 +999,11 @@ static int fprop_impl(const void* x, const void* w, void* y, const float* bias, 
   // plain "+ residual" (no bias / ReLU / statistics / strided view): add it on the tensor core, keep the lean epilogue
   g.res_mma = (residual != nullptr && bias == nullptr && !relu && stats == nullptr && view == nullptr) ? 1 : 0;
   if (g.res_mma) g.has_res = 0;
+  if (out_mask) {
+    TDL_REQUIRE(g.res_mma, "the output mask is only available together with a plain residual");
+    TDL_REQUIRE(K % 32 == 0, "the output mask needs K % 32 == 0");
+    g.has_mask = 1;
+  }
   const int block_n = K > 128 ? 256 : (K > 64 ? 128 : 64);
   g.n_tiles = (int)cdiv(K, block_n);
 
@@ -1039,9 +1055,11 @@ static int fprop_impl(const void* x, const void* w, void* y, const float* bias, 
     rc = encode_bf16(&tid, ident, 2, idims, ibox, es);
     if (rc) return rc;
   }
-  if (block_n == 256) return launch_fprop<256>(tx, tw, ty, tres, tid, g, bias, (const bf16*)residual, stats, nparts, st);
-  if (block_n == 128) return launch_fprop<128>(tx, tw, ty, tres, tid, g, bias, (const bf16*)residual, stats, nparts, st);
-  return launch_fprop<64>(tx, tw, ty, tres, tid, g, bias, (const bf16*)residual, stats, nparts, st);
+  // in res_mma mode the residual arrives through its tensor map; the pointer slot carries the optional output mask
+  const bf16* aux = g.res_mma ? (const bf16*)out_mask : (const bf16*)residual;
+  if (block_n == 256) return launch_fprop<256>(tx, tw, ty, tres, tid, g, bias, aux, stats, nparts, st);
+  if (block_n == 128) return launch_fprop<128>(tx, tw, ty, tres, tid, g, bias, aux, stats, nparts, st);
+  return launch_fprop<64>(tx, tw, ty, tres, tid, g, bias, aux, stats, nparts, st);
 }
 
 // y[N,P,Q,K] = conv(x[N,H,W,C], w[K,R*S,C]) (+bias) (+residual) (ReLU)      bf16 in/out, fp32 accumulate
@@ -1050,6 +1068,18 @@ TDL_API int tdl_conv2d_fprop_bf16(const void* x, const void* w, void* y, const f
                                   int pad_w, int P, int Q, int relu, void* stream) {
   return fprop_impl(x, w, y, bias, residual, N, H, W, C, K, R, S, stride, dil, pad_h, pad_w, P, Q, relu, nullptr,
                     nullptr, nullptr, stream);
+}
+
+// y = (conv(x, w) + residual) with outputs zeroed where the bit mask says so: out_mask is [N*P*Q][K/8] bytes, bit j of
+// byte (pixel, c/8) set = keep channel 8*(c/8)+j.  This is the data gradient of a residual unit's first conv with the
+// identity-shortcut gradient (residual) and the ReLU backward of the unit's input (mask, as written by tdl_bn_apply)
+// folded in; the residual is added on the tensor core.  K % 32 == 0.
+TDL_API int tdl_conv2d_fprop_res_mask_bf16(const void* x, const void* w, void* y, const void* residual,
+                                           const void* out_mask, int N, int H, int W, int C, int K, int R, int S,
+                                           int stride, int dil, int pad_h, int pad_w, int P, int Q, void* stream) {
+  TDL_REQUIRE(residual != nullptr, "residual required");
+  return fprop_impl(x, w, y, nullptr, residual, N, H, W, C, K, R, S, stride, dil, pad_h, pad_w, P, Q, 0, nullptr,
+                    nullptr, nullptr, stream, out_mask);
 }
 
 // Same convolution, additionally producing per-CTA partial (sum, sum of squares) of the bf16 output per channel:

@@ -31,6 +31,11 @@ int tdl_conv2d_fprop_bf16(const void* x, const void* w, void* y, const float* bi
                           int Q, int relu, void* stream);
 /* fprop that also emits per-CTA partial BatchNorm statistics of its bf16 output: stats_partial [tdl_num_sms()][2][K]
  * fp32 (written), *nparts_host = number of valid leading slots (host int); finish with tdl_bn_finalize_partials */
+/* y = mask(conv(x, w) + residual): residual added on the tensor core, out_mask = [N*P*Q][K/8] bytes (1 bit per element,
+ * layout of tdl_bn_apply's mask_out; may be NULL).  K % 32 == 0 when a mask is given. */
+int tdl_conv2d_fprop_res_mask_bf16(const void* x, const void* w, void* y, const void* residual, const void* out_mask,
+                                   int N, int H, int W, int C, int K, int R, int S, int stride, int dil, int pad_h,
+                                   int pad_w, int P, int Q, void* stream);
 int tdl_conv2d_fprop_stats_bf16(const void* x, const void* w, void* y, const float* bias, int N, int H, int W, int C,
                                 int K, int R, int S, int stride, int dil, int pad_h, int pad_w, int P, int Q,
                                 float* stats_partial, int* nparts_host, void* stream);

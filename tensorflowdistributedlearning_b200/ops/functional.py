@@ -15,6 +15,18 @@ import torch.nn.functional as F
 
 from . import reference as R
 
+# A data gradient that already carries the ReLU backward of the tensor it belongs to (applied in the conv epilogue):
+# data_ptr of the gradient -> data_ptr of the 1-bit mask that was applied.  Consumed by that tensor's BatchNorm backward,
+# which then skips its own masking and returns the gradient itself for the residual input.
+_PREMASKED = {}
+_LAST_RELU_MASK = None
+
+
+def begin_step() -> None:
+    """Drop per-step bookkeeping (call at the start of every training step)."""
+    _PREMASKED.clear()
+
+
 _STEM_NATIVE = True       # first-layer tcgen05 kernel (off = cuDNN for the C<=4 stem, used for A/B timing)
 _FORCE_REFERENCE = False  # flipped by tests / the proxy baseline to route everything through torch ops
 _LAUNCHES = 0             # native kernel launches issued through this module (bench "gpu_launches")
@@ -131,6 +143,8 @@ class _ConvNative(torch.autograd.Function):
         from . import native_ops as O
 
         ctx.weight_param, ctx.bias_param, ctx.want_tap = weight, bias, want_tap
+        # the 1-bit ReLU mask of the input tensor, when its producer left one (BatchNorm + residual + ReLU)
+        ctx.in_mask = getattr(x, "_tdl_relu_mask", None) if want_tap else None
 
         K, Rk, Sk, C = weight.shape
         taps = Rk * Sk
@@ -175,9 +189,12 @@ class _ConvNative(torch.autograd.Function):
         dx = dw = db = None
         if ctx.needs_input_grad[0]:
             if has_wd:
+                mask = ctx.in_mask if (d_tap is not None and C % 32 == 0) else None
                 dx = O.conv2d_fprop(dy, wsaved, R=Rk, S=Sk, stride=1, dil=dil, pad_h=(Rk - 1) * dil - pt,
                                     pad_w=(Sk - 1) * dil - pl, out_hw=(h, w),
-                                    residual=None if d_tap is None else d_tap.contiguous())
+                                    residual=None if d_tap is None else d_tap.contiguous(), out_mask=mask)
+                if mask is not None:  # this IS the total gradient of x (tap), with x's ReLU backward already applied
+                    _PREMASKED[dx.data_ptr()] = mask.data_ptr()
                 d_tap = None
                 _count(1)
             else:
@@ -411,6 +428,8 @@ class _BNNative(torch.autograd.Function):
         if training:
             ctx.save_for_backward(x2, zmask, scale, shift, mean, invstd)
         ctx.cfg = (relu, residual is not None, training, shape)
+        global _LAST_RELU_MASK
+        _LAST_RELU_MASK = zmask
         return z.view(shape)
 
     @staticmethod
@@ -425,8 +444,18 @@ class _BNNative(torch.autograd.Function):
         dz2 = dz.contiguous().view(-1, C)
         g, b = ctx.gamma_param, ctx.beta_param
         direct = _direct_ok(g) and _direct_ok(b)
-        dx, dres, dgamma, dbeta = O.bn_bwd(dz2, x2, z2, scale, shift, mean, invstd, relu, has_res,
-                                           acc_dgamma=g.grad if direct else None, acc_dbeta=b.grad if direct else None)
+        premasked = (z2 is not None and has_res and _PREMASKED.pop(dz2.data_ptr(), None) == z2.data_ptr())
+        if premasked:
+            # the consumer's data-gradient kernel already applied this layer's ReLU mask: no masking here, and the
+            # residual branch's gradient is the incoming gradient itself (nothing to write)
+            dx, _, dgamma, dbeta = O.bn_bwd(dz2, x2, None, scale, shift, mean, invstd, False, False,
+                                            acc_dgamma=g.grad if direct else None,
+                                            acc_dbeta=b.grad if direct else None)
+            dres = dz2
+        else:
+            dx, dres, dgamma, dbeta = O.bn_bwd(dz2, x2, z2, scale, shift, mean, invstd, relu, has_res,
+                                               acc_dgamma=g.grad if direct else None,
+                                               acc_dbeta=b.grad if direct else None)
         _count(4)
         if direct:
             _notify(g)
@@ -445,8 +474,15 @@ def batch_norm(x: torch.Tensor, gamma, beta, running_mean, running_var, *, decay
     C = x.shape[-1]
     if _native_ok(x) and C % 8 == 0 and gamma is not None and beta is not None:
         res = None if residual is None else residual.contiguous()
-        return _BNNative.apply(x.contiguous(), gamma, beta, running_mean, running_var, res, decay, eps, relu,
-                               training, stats if training else None)
+        global _LAST_RELU_MASK
+        _LAST_RELU_MASK = None
+        out = _BNNative.apply(x.contiguous(), gamma, beta, running_mean, running_var, res, decay, eps, relu,
+                              training, stats if training else None)
+        if _LAST_RELU_MASK is not None:
+            # lets the next convolution's data-gradient kernel apply this ReLU's backward (see _ConvNative)
+            out._tdl_relu_mask = _LAST_RELU_MASK
+            _LAST_RELU_MASK = None
+        return out
     if training:
         y = R.batch_norm_train(x, gamma, beta, running_mean, running_var, decay, eps)
     else:

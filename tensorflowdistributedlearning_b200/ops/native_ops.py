@@ -38,8 +38,11 @@ def same_pad(in_size: int, k: int, stride: int, dil: int = 1) -> Tuple[int, int,
 def conv2d_fprop(x: torch.Tensor, w: torch.Tensor, *, R: int, S: int, stride: int = 1, dil: int = 1,
                  pad_h: int = 0, pad_w: int = 0, out_hw: Optional[Tuple[int, int]] = None,
                  bias: Optional[torch.Tensor] = None, residual: Optional[torch.Tensor] = None,
-                 relu: bool = False) -> torch.Tensor:
-    """y[N,P,Q,K] = conv(x[N,H,W,C], w[K, R*S, C]) with fused bias / residual / ReLU epilogue."""
+                 relu: bool = False, out_mask: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """y[N,P,Q,K] = conv(x[N,H,W,C], w[K, R*S, C]) with fused bias / residual / ReLU epilogue.
+
+    ``out_mask`` ([N*P*Q, K/8] uint8, the 1-bit ReLU mask written by ``bn_apply``; needs ``residual``, no bias/ReLU):
+    outputs whose bit is clear are zeroed -- the ReLU backward of the tensor this data gradient belongs to."""
     _chk_bf16_nhwc(x, "x")
     _chk_bf16_nhwc(w, "w")
     n, h, wd, c = x.shape
@@ -56,6 +59,14 @@ def conv2d_fprop(x: torch.Tensor, w: torch.Tensor, *, R: int, S: int, stride: in
         assert residual.shape == y.shape
     if bias is not None:
         assert bias.dtype == torch.float32 and bias.numel() == k and bias.is_contiguous()
+    if out_mask is not None:
+        assert residual is not None and bias is None and not relu and out_mask.dtype == torch.uint8
+        assert out_mask.numel() == n * p * q * (k // 8) and k % 32 == 0
+        rc = N.lib().tdl_conv2d_fprop_res_mask_bf16(N.ptr(x), N.ptr(w), N.ptr(y), N.ptr(residual), N.ptr(out_mask),
+                                                    _i(n), _i(h), _i(wd), _i(c), _i(k), _i(R), _i(S), _i(stride),
+                                                    _i(dil), _i(pad_h), _i(pad_w), _i(p), _i(q), N.stream_ptr())
+        N.check(rc, "tdl_conv2d_fprop_res_mask_bf16")
+        return y
     rc = N.lib().tdl_conv2d_fprop_bf16(N.ptr(x), N.ptr(w), N.ptr(y), N.ptr(bias), N.ptr(residual),
                                        _i(n), _i(h), _i(wd), _i(c), _i(k), _i(R), _i(S), _i(stride), _i(dil),
                                        _i(pad_h), _i(pad_w), _i(p), _i(q), _i(int(relu)), N.stream_ptr())

@@ -85,6 +85,10 @@ class TowerTrainer:
         nvtx = self._nvtx and self.device.type == "cuda" and not torch.cuda.is_current_stream_capturing()
         mark = torch.cuda.nvtx.range_push if nvtx else (lambda *_: None)
         done = torch.cuda.nvtx.range_pop if nvtx else (lambda: None)
+        if self.device.type == "cuda":
+            from ..ops import functional as TF
+
+            TF.begin_step()
         mark("tdl/input")
         x = self._prepare_input()
         done()

@@ -143,6 +143,57 @@ def test_conv_dgrad_strided_parity_classes(O, case):
     assert rel_err(dx, gx[:, :, pt:pt + H, pt:pt + H].permute(0, 2, 3, 1)) < 2e-2
 
 
+def test_conv_residual_on_tensor_core_with_relu_mask(O):
+    """dx = mask * (conv(dy) + residual): the residual goes through the MMA pipeline, the 1-bit mask through the epilogue."""
+    torch.manual_seed(5)
+    N_, H, C, K = 3, 14, 64, 256
+    x = torch.randn(N_, H, H, C, device="cuda").bfloat16()
+    w = (torch.randn(K, 1, C, device="cuda") / 8).bfloat16()
+    res = torch.randn(N_, H, H, K, device="cuda").bfloat16()
+    keep = torch.rand(N_ * H * H, K, device="cuda") > 0.4
+    mask = (keep.view(-1, K // 8, 8).to(torch.uint8) << torch.arange(8, device="cuda", dtype=torch.uint8)).sum(-1).to(torch.uint8)
+    y = O.conv2d_fprop(x, w, R=1, S=1, out_hw=(H, H), residual=res, out_mask=mask.contiguous())
+    ref = (_ref_conv(x, w, 1, 1, 1, 1, (0, 0, 0, 0)) + res.float()) * keep.view(N_, H, H, K)
+    assert rel_err(y, ref) < 1e-2
+    assert bool(((y == 0) | keep.view(N_, H, H, K)).all())
+
+
+def test_residual_units_backward_with_premasked_gradients():
+    """Three stacked v1.5 bottleneck units: the identity-shortcut gradient is added inside conv1's data gradient and
+    the previous unit's ReLU backward is applied in the same epilogue; parameter and input gradients must match the
+    plain-torch path."""
+    from tensorflowdistributedlearning_b200.models.resnet import BottleneckV1
+    from tensorflowdistributedlearning_b200.ops import functional as Fn
+    from tensorflowdistributedlearning_b200.ops.layers import BNConfig
+
+    torch.manual_seed(2)
+    bn = BNConfig()
+    units = torch.nn.ModuleList([BottleneckV1(64, 256, 64, 1, 1, "u0", bn), BottleneckV1(256, 256, 64, 1, 1, "u1", bn),
+                                 BottleneckV1(256, 256, 64, 1, 1, "u2", bn)]).cuda().train()
+    x0 = torch.randn(4, 16, 16, 64, device="cuda").bfloat16()
+    g0 = torch.randn(4, 16, 16, 256, device="cuda").bfloat16()
+    grads = {}
+    for name, flag in (("native", False), ("torch", True)):
+        Fn.force_reference(flag)
+        try:
+            Fn.begin_step()
+            for p in units.parameters():
+                p.grad = None
+            x = x0.clone().requires_grad_(True)
+            h = x
+            for u in units:
+                h = u(h)
+            h.backward(g0)
+            grads[name] = [x.grad.float().clone()] + [p.grad.float().clone() for p in units.parameters()]
+        finally:
+            Fn.force_reference(False)
+    if not grads["native"]:
+        pytest.fail("no gradients")
+    for a, b in zip(grads["native"], grads["torch"]):
+        cos = torch.nn.functional.cosine_similarity(a.flatten(), b.flatten(), dim=0)
+        assert float(cos) > 0.98, (a.shape, float(cos))
+
+
 @pytest.mark.parametrize("case", [(2, 224, 3, 64, 7, "SAME"), (2, 224, 3, 64, 7, (3, 3, 3, 3)), (2, 299, 3, 32, 3, (1, 1, 1, 1)),
                                   (3, 101, 2, 64, 3, "SAME"), (2, 64, 4, 40, 5, "SAME")])
 def test_conv_stem_space_to_depth_tcgen05(O, case):
