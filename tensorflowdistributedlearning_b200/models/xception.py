@@ -52,8 +52,9 @@ class SeparableConv2dSame(TFModule):
         self.pointwise = ConvBNAct(cin, cout, 1, scope=f"{scope}_pointwise", bn=bn, relu=relu, init_std=0.06)
         self.relu = relu
 
-    def forward(self, x):
-        return self.pointwise(self.dw_bn(self.depthwise(x), relu=self.relu))
+    def forward(self, x, residual=None):
+        """``residual`` (the module's skip branch) is added inside the pointwise BatchNorm kernel."""
+        return self.pointwise(self.dw_bn(self.depthwise(x), relu=self.relu), residual=residual)
 
 
 class XceptionModule(TFModule):
@@ -80,14 +81,18 @@ class XceptionModule(TFModule):
         self.out_depth = depth_list[-1]
 
     def forward(self, x):
-        r = x
-        for m in self.convs:
-            r = m(r)
-        if self.skip == "conv":
-            return r + self.shortcut(x)
-        if self.skip == "sum":
-            return r + x
-        return r
+        # the skip connection (core/xception.py:211-222) rides into the last pointwise conv's BatchNorm kernel as its
+        # residual input instead of a separate elementwise add (that conv has no activation when there is a skip...
+        skip = self.shortcut(x) if self.skip == "conv" else (x if self.skip == "sum" else None)
+        if skip is not None and self.act_in_sep:
+            # ...unless the unit applies ReLU inside its separable convs: then the sum must stay outside the activation
+            r = x
+            for m in self.convs:
+                r = m(r)
+            return r + skip
+        r = self.convs[0](x)
+        r = self.convs[1](r)
+        return self.convs[2](r, residual=skip)
 
 
 def xception_block(scope, depth_list, skip_connection_type, activation_fn_in_separable_conv, num_units, stride,

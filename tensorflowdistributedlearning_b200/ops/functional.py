@@ -452,6 +452,12 @@ class _BNNative(torch.autograd.Function):
                                             acc_dgamma=g.grad if direct else None,
                                             acc_dbeta=b.grad if direct else None)
             dres = dz2
+        elif has_res and not relu:
+            # no activation after the sum: the residual branch's gradient is the incoming gradient, nothing to write
+            dx, _, dgamma, dbeta = O.bn_bwd(dz2, x2, None, scale, shift, mean, invstd, False, False,
+                                            acc_dgamma=g.grad if direct else None,
+                                            acc_dbeta=b.grad if direct else None)
+            dres = dz2
         else:
             dx, dres, dgamma, dbeta = O.bn_bwd(dz2, x2, z2, scale, shift, mean, invstd, relu, has_res,
                                                acc_dgamma=g.grad if direct else None,
