@@ -455,6 +455,27 @@ __device__ __forceinline__ void lds4(const uint8_t* tile, int lrow, int cq, floa
   }
 }
 
+// Same access through a precomputed 32-bit shared-space address (tile base + loop-invariant offset): no 64-bit
+// generic address arithmetic and no swizzle math in the tile loop; the pre-activation ReLU is one packed bf16x2 max.
+__device__ __forceinline__ uint32_t swz_off(int lrow, int cq) {
+  return (uint32_t)(lrow * 128 + (((cq >> 1) ^ (lrow & 7)) << 4) + ((cq & 1) << 3));
+}
+__device__ __forceinline__ void lds4_at(uint32_t addr, float* f, bool relu) {
+  uint32_t a, b;
+  asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(a), "=r"(b) : "r"(addr));
+  if (relu) {
+    const __nv_bfloat162 z = __floats2bfloat162_rn(0.f, 0.f);
+    __nv_bfloat162 ha = __hmax2(*reinterpret_cast<__nv_bfloat162*>(&a), z);
+    __nv_bfloat162 hb = __hmax2(*reinterpret_cast<__nv_bfloat162*>(&b), z);
+    a = *reinterpret_cast<uint32_t*>(&ha);
+    b = *reinterpret_cast<uint32_t*>(&hb);
+  }
+  f[0] = __uint_as_float(a << 16);
+  f[1] = __uint_as_float(a & 0xffff0000u);
+  f[2] = __uint_as_float(b << 16);
+  f[3] = __uint_as_float(b & 0xffff0000u);
+}
+
 constexpr int kMaxStages = 4;
 
 template <int STRIDE, int DIL>
@@ -509,6 +530,17 @@ depthwise3x3_tma_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
   // everything that depends only on the thread's strip is loop invariant: tile-local row indices of the taps
   const int ph = grp / strips_w, pw0 = (grp % strips_w) * 4;
   const bool active = grp < strips && ch_ok;
+  // dense case: the 18 input and 4 mask addresses of this thread relative to the stage base never change
+  uint32_t xoff[3][6], moff[4];
+  if (STRIDE == 1 && DIL == 1) {
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+#pragma unroll
+      for (int c = 0; c < 6; ++c) xoff[r][c] = swz_off((ph + r) * s.BW + pw0 + c, cvec);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) moff[j] = (uint32_t)x_bytes + swz_off(ph * s.TW + pw0 + j, cvec);
+  }
+  const uint32_t smem_base = ptx::smem_u32(smem);
   int it = 0, stage = 0;
   uint32_t parity = 0;
   for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
@@ -517,6 +549,7 @@ depthwise3x3_tma_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
     ptx::mbar_wait(&full[stage], parity);
     const uint8_t* in = smem + stage * stage_bytes;
     const uint8_t* min_ = in + x_bytes;
+    const uint32_t in_a = smem_base + (uint32_t)(stage * stage_bytes);
     if (++stage == stages) {
       stage = 0;
       parity ^= 1;
@@ -536,7 +569,7 @@ depthwise3x3_tma_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
         if (STRIDE == 1 && DIL == 1) {
           float v[6][4];
 #pragma unroll
-          for (int c = 0; c < 6; ++c) lds4(in, lrow0 + c, cvec, v[c], relu_in);
+          for (int c = 0; c < 6; ++c) lds4_at(in_a + xoff[r][c], v[c], relu_in);
 #pragma unroll
           for (int j = 0; j < 4; ++j)
 #pragma unroll
@@ -557,22 +590,23 @@ depthwise3x3_tma_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
       }
       const int p = th_i * s.TH + ph;
       if (p < s.P) {
+        const int q0 = tw_i * s.TW + pw0;
+        bf16* orow = y + ((((int64_t)n * s.P + p) * s.Q + q0) * s.C) + ch;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          const int q = tw_i * s.TW + pw0 + j;
-          if (q >= s.Q) break;
-          const int64_t o = ((((int64_t)n * s.P + p) * s.Q + q) * s.C) + ch;
+          if (q0 + j >= s.Q) break;
           if (relu_out) {
 #pragma unroll
             for (int c = 0; c < 4; ++c) acc[j][c] = fmaxf(acc[j][c], 0.f);
           }
           if (has_mask) {
             float m[4];
-            lds4(min_, ph * s.TW + pw0 + j, cvec, m, false);
+            if (STRIDE == 1 && DIL == 1) lds4_at(in_a + moff[j], m, false);
+            else lds4(min_, ph * s.TW + pw0 + j, cvec, m, false);
 #pragma unroll
             for (int c = 0; c < 4; ++c) acc[j][c] = m[c] > 0.f ? acc[j][c] : 0.f;
           }
-          tdl::dw::st4(y + o, acc[j]);
+          tdl::dw::st4(orow + (int64_t)j * s.C, acc[j]);
         }
       }
     }
@@ -633,19 +667,35 @@ depthwise3x3_tma_wgrad_kernel(const __grid_constant__ CUtensorMap tm_x, const __
     }
   const int strips_w = s.TW / 4;
   const int strips = s.TH * strips_w;
+  const int ph = grp / strips_w, pw0 = (grp % strips_w) * 4;
+  // loop-invariant shared-memory offsets of this thread's gradient strip and (dense case) input patch
+  uint32_t xoff[3][6], goff[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) goff[j] = (uint32_t)x_bytes + swz_off(ph * s.TW + pw0 + j, cvec);
+  if (STRIDE == 1 && DIL == 1) {
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+#pragma unroll
+      for (int c = 0; c < 6; ++c) xoff[r][c] = swz_off((ph + r) * s.BW + pw0 + c, cvec);
+  }
+  const uint32_t smem_base = ptx::smem_u32(smem);
+  int stage = 0;
+  uint32_t parity = 0;
   for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
-    const int stage = it % stages;
     const int ahead = tile + (stages - 1) * gridDim.x;
-    if (tid == 0 && ahead < tiles) issue(ahead, (it + stages - 1) % stages);
-    ptx::mbar_wait(&full[stage], (uint32_t)((it / stages) & 1));
+    if (tid == 0 && ahead < tiles) issue(ahead, stage == 0 ? stages - 1 : stage - 1);
+    ptx::mbar_wait(&full[stage], parity);
     const uint8_t* in = smem + stage * stage_bytes;
-    const uint8_t* gin = in + x_bytes;
+    const uint32_t in_a = smem_base + (uint32_t)(stage * stage_bytes);
+    if (++stage == stages) {
+      stage = 0;
+      parity ^= 1;
+    }
     if (grp < strips && ch_ok) {
-      const int ph = grp / strips_w, pw0 = (grp % strips_w) * 4;
       float g[4][4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        lds4(gin, ph * s.TW + pw0 + j, cvec, g[j], false);
+        lds4_at(in_a + goff[j], g[j], false);
 #pragma unroll
         for (int c = 0; c < 4; ++c) accb[c] += g[j][c];
       }
@@ -655,7 +705,7 @@ depthwise3x3_tma_wgrad_kernel(const __grid_constant__ CUtensorMap tm_x, const __
         if (STRIDE == 1 && DIL == 1) {
           float v[6][4];
 #pragma unroll
-          for (int c = 0; c < 6; ++c) lds4(in, lrow0 + c, cvec, v[c], relu_in);
+          for (int c = 0; c < 6; ++c) lds4_at(in_a + xoff[r][c], v[c], relu_in);
 #pragma unroll
           for (int j = 0; j < 4; ++j)
 #pragma unroll

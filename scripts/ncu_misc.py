@@ -46,6 +46,15 @@ elif kind == "stats1x1":
     for _ in range(3):
         O.conv2d_fprop_stats(x, w, R=1, S=1, out_hw=(56, 56))
         O.conv2d_fprop(x, w, R=1, S=1, out_hw=(56, 56))
+elif kind == "resmma":
+    # data gradient of a unit's first 1x1 conv (64 -> 256 @56x56) with the identity gradient added on the tensor core
+    # and the previous unit's ReLU mask applied in the epilogue
+    dy = torch.randn(256, 56, 56, 64, device="cuda").bfloat16()
+    wd = (torch.randn(256, 1, 64, device="cuda") / 8).bfloat16()
+    res = torch.randn(256, 56, 56, 256, device="cuda").bfloat16()
+    mask = torch.randint(0, 256, (256 * 56 * 56, 32), dtype=torch.uint8, device="cuda")
+    for _ in range(3):
+        O.conv2d_fprop(dy, wd, R=1, S=1, out_hw=(56, 56), residual=res, out_mask=mask)
 elif kind == "depthwise":
     x = torch.randn(64, 38, 38, 728, device="cuda").bfloat16()
     w = torch.randn(9, 728, device="cuda")
