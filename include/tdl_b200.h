@@ -22,6 +22,7 @@ extern "C" {
 const char* tdl_last_error(void);
 int tdl_version(void);
 int tdl_num_sms(void);
+uint32_t tdl_crc32c(const void* data, uint64_t n, uint32_t crc); /* host: CRC-32C for TF tensor-bundle checkpoints */
 
 /* ---- convolution on tcgen05/TMEM/TMA (reference: slim.conv2d, core/resnet.py:79-85,130-144,164-166,449-492) ----
  * x [N,H,W,C], w [K, R*S, C] (OHWI), y [N,P,Q,K]; pad_h/pad_w are the top/left padding, P/Q the output size.

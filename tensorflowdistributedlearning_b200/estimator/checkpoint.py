@@ -4,6 +4,10 @@ A checkpoint is ``model.ckpt-{step}.safetensors`` (tensors in TF layout: conv we
 [kh,kw,C,1]) + ``model.ckpt-{step}.json`` (manifest: names, shapes, dtypes, global_step), and a TF-style
 ``checkpoint`` state file naming the latest.  Optimizer slots use TF's names: ``<var>/Adam``, ``<var>/Adam_1``
 (or ``<var>/Momentum``), ``beta1_power``, ``beta2_power``, ``global_step``.  Tower 0 writes (X7); every tower reads.
+
+TensorFlow's own V2 format is supported as well (``estimator/tf_bundle.py``): ``load_checkpoint`` accepts a prefix
+whose files are ``<prefix>.index`` + ``<prefix>.data-00000-of-00001`` (e.g. a checkpoint written by the reference),
+and ``save_checkpoint(..., tf_bundle=True)`` writes that pair next to the safetensors file.
 """
 from __future__ import annotations
 
@@ -27,10 +31,10 @@ def list_checkpoints(model_dir: str) -> List[int]:
     steps = []
     if os.path.isdir(model_dir):
         for f in os.listdir(model_dir):
-            m = re.fullmatch(r"model\.ckpt-(\d+)\.safetensors", f)
+            m = re.fullmatch(r"model\.ckpt-(\d+)\.(?:safetensors|index)", f)
             if m:
                 steps.append(int(m.group(1)))
-    return sorted(steps)
+    return sorted(set(steps))
 
 
 def latest_checkpoint(model_dir: str) -> Optional[str]:
@@ -41,7 +45,7 @@ def latest_checkpoint(model_dir: str) -> Optional[str]:
         if m:
             p = m.group(1)
             p = p if os.path.isabs(p) else os.path.join(model_dir, p)
-            if os.path.exists(p + ".safetensors"):
+            if os.path.exists(p + ".safetensors") or os.path.exists(p + ".index"):
                 return p
     steps = list_checkpoints(model_dir)
     return _ckpt_prefix(model_dir, steps[-1]) if steps else None
@@ -52,7 +56,7 @@ def model_tf_state(model: torch.nn.Module) -> Dict[str, torch.Tensor]:
 
 
 def save_checkpoint(model_dir: str, model: torch.nn.Module, optimizer=None, step: Optional[int] = None,
-                    keep: int = 5, extra: Optional[dict] = None) -> str:
+                    keep: int = 5, extra: Optional[dict] = None, tf_bundle: bool = False) -> str:
     from safetensors.torch import save_file
 
     os.makedirs(model_dir, exist_ok=True)
@@ -81,6 +85,10 @@ def save_checkpoint(model_dir: str, model: torch.nn.Module, optimizer=None, step
     prefix = _ckpt_prefix(model_dir, step)
     save_file(tensors, prefix + ".safetensors.tmp")
     os.replace(prefix + ".safetensors.tmp", prefix + ".safetensors")
+    if tf_bundle:  # the same variables as a TensorFlow V2 checkpoint (readable by tf.train.Saver / the reference)
+        from .tf_bundle import write_bundle
+
+        write_bundle(prefix, {k: v.numpy() for k, v in tensors.items()})
     manifest = {"global_step": step, "variables": {k: {"shape": list(v.shape), "dtype": str(v.dtype)} for k, v in tensors.items()}}
     if extra:
         manifest["extra"] = extra
@@ -88,7 +96,7 @@ def save_checkpoint(model_dir: str, model: torch.nn.Module, optimizer=None, step
         json.dump(manifest, f, indent=1)
     steps = list_checkpoints(model_dir)
     for old in steps[:-keep] if keep and len(steps) > keep else []:
-        for ext in (".safetensors", ".json"):
+        for ext in (".safetensors", ".json", ".index", ".data-00000-of-00001"):
             try:
                 os.unlink(_ckpt_prefix(model_dir, old) + ext)
             except OSError:
@@ -103,9 +111,14 @@ def save_checkpoint(model_dir: str, model: torch.nn.Module, optimizer=None, step
 
 def load_checkpoint(prefix: str, model: torch.nn.Module, optimizer=None, strict: bool = True) -> int:
     """Restore weights, moving statistics, optimizer slots and global_step.  Returns the step."""
-    from safetensors.torch import load_file
+    if os.path.exists(prefix + ".safetensors"):
+        from safetensors.torch import load_file
 
-    tensors = load_file(prefix + ".safetensors")
+        tensors = load_file(prefix + ".safetensors")
+    else:  # a TensorFlow V2 checkpoint (<prefix>.index + <prefix>.data-*), e.g. one trained with the reference
+        from .tf_bundle import read_bundle
+
+        tensors = {k: torch.from_numpy(v) for k, v in read_bundle(prefix).items()}
     missing = []
     with torch.no_grad():
         for name, t, kind in iter_tf_variables(model):
