@@ -97,6 +97,9 @@ struct Geometry {
   // first-layer ("stem") mode only: byte pitches of the haloed space-to-depth patch in shared memory
   int sp_plane, sp_row, sp_tx, sp_wbytes;
   int res_mma;  // residual tile added on the tensor core (extra K iterations against an identity block)
+  // halo mode (stride-1 RxS > 1x1): the haloed input patch of a K block is loaded ONCE and every tap reads it at a row
+  // shift instead of re-fetching a shifted copy per tap (the tap-shifted form is bound by L2->smem bandwidth there)
+  int halo, halo_pw, halo_pbytes, halo_ptx, halo_nb, halo_bo;
   int has_mask; // res_mma only: zero outputs whose bit in a [pixels][K/8] byte mask is clear (fused ReLU backward)
 };
 
@@ -158,7 +161,7 @@ struct FpropCfg {
   static constexpr int kAlignSlack = 384;  // the dynamic smem window is 1 KB aligned in practice; checked at run time
   static constexpr int kStages = (227 * 1024 - kOutBytes - kStatBytes - kAlignSlack - kBarBytes) / kStageBytes;
   static constexpr int kSmemBytes = kStages * kStageBytes + kOutBytes + kStatBytes + kAlignSlack + kBarBytes;
-  static_assert((2 * kStages + 2 * kAccBufs + 1) * 8 + 4 <= kBarBytes, "barrier region too small");
+  static_assert((2 * kStages + 2 * kAccBufs + 1 + 4) * 8 + 4 <= kBarBytes, "barrier region too small");
 };
 
 // kFused: bias / residual / ReLU present in the epilogue.  kStats: per-channel (sum, sum of squares) of the bf16
@@ -204,7 +207,10 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
   constexpr int kAcc = Cfg::kAccBufs;
   uint64_t* tmem_empty = tmem_full + kAcc;
   uint64_t* w_bar = tmem_empty + kAcc;  // stem mode: resident weights have landed
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_bar + 1);
+  uint64_t* patch_full = w_bar + 1;     // halo mode: two input-patch buffers
+  uint64_t* patch_empty = patch_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(patch_empty + 2);
+  uint8_t* smem_bh = smem + 2 * g.halo_pbytes;  // halo mode: weight-tile ring behind the two patch buffers
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -235,6 +241,10 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
         ptx::mbar_init(&tmem_empty[i], 4);  // one arrival per warp of the epilogue group that drains the tile
       }
       ptx::mbar_init(w_bar, 1);
+      for (int i = 0; i < 2; ++i) {
+        ptx::mbar_init(&patch_full[i], 1);
+        ptx::mbar_init(&patch_empty[i], 1);
+      }
       ptx::fence_mbar_init();
     }
     __syncwarp();
@@ -251,12 +261,21 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
 
   if (warp == 0) {
     // ===================== TMA producer =====================
-    if (lane == 0) {
+    // The whole warp walks the (warp-uniform) schedule and only the issue instructions run on one elected lane:
+    // with the loop itself inside `if (lane == 0)` ptxas cannot treat the descriptors / coordinates as uniform and
+    // wraps every TMA and MMA issue in an elect-and-broadcast loop (tens of instructions per issue, which made the
+    // issuing thread -- not the tensor core -- the limit of narrow tiles).  Elected once: elect.sync is a warp
+    // synchronisation, re-electing per instruction cost more than it saved.
+    const bool leader = ptx::elect_one();
+    {
       int stage = 0;
       uint32_t phase = 0;
+      int pb = 0;           // halo mode: patch buffer index / parity
+      uint32_t pphase = 0;
       if constexpr (kStem) {
-        ptx::mbar_expect_tx(w_bar, (uint32_t)g.sp_wbytes);
-        for (int a = 0; a * 8192 < g.sp_wbytes; ++a) ptx::tma_load_2d(smem_b + a * 8192, &tm_w, w_bar, a * 64, 0);
+        if (leader) ptx::mbar_expect_tx(w_bar, (uint32_t)g.sp_wbytes);
+        for (int a = 0; a * 8192 < g.sp_wbytes; ++a)
+          if (leader) ptx::tma_load_2d(smem_b + a * 8192, &tm_w, w_bar, a * 64, 0);
       }
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const int n_tile = tile % g.n_tiles;
@@ -267,9 +286,11 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
         if constexpr (kStem) {
           // coordinates: (8-byte units along the plane line, plane, packed row, image); out-of-range = zero padding
           ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
-          ptx::mbar_expect_tx(&full_bar[stage], (uint32_t)g.sp_tx);
-          ptx::tma_load_4d(smem_a + stage * kABytes, &tm_x, &full_bar[stage], (tw_i * g.TW - g.pad_w) * 2, 0,
-                           th_i - g.pad_h, tn_i);
+          if (leader) {
+            ptx::mbar_expect_tx(&full_bar[stage], (uint32_t)g.sp_tx);
+            ptx::tma_load_4d(smem_a + stage * kABytes, &tm_x, &full_bar[stage], (tw_i * g.TW - g.pad_w) * 2, 0,
+                             th_i - g.pad_h, tn_i);
+          }
           if (++stage == kStages) {
             stage = 0;
             phase ^= 1;
@@ -279,14 +300,36 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
         const int w_in = tw_i * g.TW * g.stride - g.pad_w;
         const int h_in = th_i * g.TH * g.stride - g.pad_h;
         const int n_in = tn_i * g.TN;
+        if (!kStem && !kResMma && g.halo) {
+          const int taps = g.R * g.S;
+          for (int kb2 = 0; kb2 < g.num_kb; ++kb2) {
+            ptx::mbar_wait(&patch_empty[pb], pphase ^ 1);
+            if (leader) ptx::mbar_expect_tx(&patch_full[pb], (uint32_t)g.halo_ptx);
+            if (leader) ptx::tma_load_4d(smem + pb * g.halo_pbytes, &tm_x, &patch_full[pb], kb2 * kBlockK, w_in, h_in, n_in);
+            if ((pb ^= 1) == 0) pphase ^= 1;
+            for (int t = 0; t < taps; ++t) {
+              ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+              if (leader) ptx::mbar_expect_tx(&full_bar[stage], (uint32_t)Cfg::kBBytes);
+              if (leader) ptx::tma_load_3d(smem_bh + stage * Cfg::kBBytes, &tm_w, &full_bar[stage], kb2 * kBlockK, t,
+                               n_tile * BLOCK_N);
+              if (++stage == g.halo_nb) {
+                stage = 0;
+                phase ^= 1;
+              }
+            }
+          }
+          continue;
+        }
         int tap = 0, kb = 0, r = 0, s = 0;  // advanced incrementally: no divisions on the TMA-issue path
         for (int it = 0; it < k_iters; ++it) {
           ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
-          ptx::mbar_expect_tx(&full_bar[stage], stage_tx);
-          ptx::tma_load_4d(smem_a + stage * kABytes, &tm_x, &full_bar[stage], kb * kBlockK, w_in + s * g.dil,
-                           h_in + r * g.dil, n_in);
-          ptx::tma_load_3d(smem_b + stage * Cfg::kBBytes, &tm_w, &full_bar[stage], kb * kBlockK, tap,
-                           n_tile * BLOCK_N);
+          if (leader) {
+            ptx::mbar_expect_tx(&full_bar[stage], stage_tx);
+            ptx::tma_load_4d(smem_a + stage * kABytes, &tm_x, &full_bar[stage], kb * kBlockK, w_in + s * g.dil,
+                             h_in + r * g.dil, n_in);
+            ptx::tma_load_3d(smem_b + stage * Cfg::kBBytes, &tm_w, &full_bar[stage], kb * kBlockK, tap,
+                             n_tile * BLOCK_N);
+          }
           if (++stage == kStages) {
             stage = 0;
             phase ^= 1;
@@ -304,10 +347,12 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
           const int res_chunks = min(BLOCK_N / 64, (g.K - n_tile * BLOCK_N + 63) / 64);
           for (int j = 0; j < res_chunks; ++j) {
             ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
-            ptx::mbar_expect_tx(&full_bar[stage], a_tx + 8192u);
-            ptx::tma_load_4d(smem_a + stage * kABytes, &tm_res, &full_bar[stage], n_tile * BLOCK_N + j * 64,
-                             tw_i * g.TW, th_i * g.TH, tn_i * g.TN);
-            ptx::tma_load_2d(smem_b + stage * Cfg::kBBytes, &tm_id, &full_bar[stage], 0, 0);
+            if (leader) {
+              ptx::mbar_expect_tx(&full_bar[stage], a_tx + 8192u);
+              ptx::tma_load_4d(smem_a + stage * kABytes, &tm_res, &full_bar[stage], n_tile * BLOCK_N + j * 64,
+                               tw_i * g.TW, th_i * g.TH, tn_i * g.TN);
+              ptx::tma_load_2d(smem_b + stage * Cfg::kBBytes, &tm_id, &full_bar[stage], 0, 0);
+            }
             if (++stage == kStages) {
               stage = 0;
               phase ^= 1;
@@ -317,13 +362,16 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer (one thread) =====================
-    if (lane == 0) {
+    // ===================== MMA issuer (whole warp walks the schedule, one elected lane issues) =====================
+    const bool leader = ptx::elect_one();
+    {
       constexpr uint32_t idesc = ptx::umma_idesc_bf16(kBlockM, BLOCK_N, 0, 0);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
+      int hpb = 0;  // halo mode: patch buffer index / parity
+      uint32_t hpphase = 0;
       uint64_t stem_a0 = 0, stem_b0 = 0;
       if constexpr (kStem) {
         stem_a0 = ptx::umma_smem_desc_nosw(ptx::smem_u32(smem_a), (uint32_t)g.sp_plane, 128);
@@ -334,6 +382,46 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
         ptx::mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
         ptx::tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BLOCK_N);
+        if (!kStem && !kResMma && g.halo) {
+          const uint32_t sbo = (uint32_t)g.halo_pw * 128u;  // one tile row (8 pixels) per 8-row group of the M tile
+          bool first = true;
+          for (int kb2 = 0; kb2 < g.num_kb; ++kb2) {
+            ptx::mbar_wait(&patch_full[hpb], hpphase);
+            ptx::tc_fence_after();
+            const uint32_t a_patch = ptx::smem_u32(smem + hpb * g.halo_pbytes);
+            uint32_t row_off = 0;  // r * dil * patch width, in pixels
+            for (int r = 0; r < g.R; ++r, row_off += (uint32_t)(g.dil * g.halo_pw)) {
+              for (int sx = 0; sx < g.S; ++sx) {
+                ptx::mbar_wait(&full_bar[stage], phase);
+                ptx::tc_fence_after();
+                const uint32_t shift = (uint32_t)(sx * g.dil);
+                const uint64_t a_desc = ptx::umma_smem_desc_sw128_bo(a_patch + (row_off + shift) * 128u, 16, sbo,
+                                                                     g.halo_bo ? shift : 0u);
+                const uint64_t b_desc =
+                    ptx::umma_smem_desc_sw128(ptx::smem_u32(smem_bh + stage * Cfg::kBBytes), 16, 1024);
+#pragma unroll
+                for (int k = 0; k < kBlockK / 16; ++k) {
+                  if (leader) ptx::umma_bf16(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc,
+                                 (first && k == 0) ? 0u : 1u);
+                }
+                first = false;
+                if (leader) ptx::umma_commit(&empty_bar[stage]);
+                if (++stage == g.halo_nb) {
+                  stage = 0;
+                  phase ^= 1;
+                }
+              }
+            }
+            if (leader) ptx::umma_commit(&patch_empty[hpb]);  // the patch may be overwritten once these MMAs retire
+            if ((hpb ^= 1) == 0) hpphase ^= 1;
+          }
+          if (leader) ptx::umma_commit(&tmem_full[acc]);
+          if (++acc == kAcc) {
+            acc = 0;
+            acc_phase ^= 1;
+          }
+          continue;
+        }
         for (int it = 0; it < k_iters; ++it) {
           ptx::mbar_wait(&full_bar[stage], phase);
           ptx::tc_fence_after();
@@ -343,16 +431,18 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
             // path, a division per tap cost more than the MMA itself)
             const uint64_t a0 = stem_a0 + (uint64_t)((uint32_t)(stage * kABytes) >> 4);
             const int taps = g.R * g.S;
-            uint32_t a_row = 0, a_col = 0;  // in 16-byte units
-            for (int t = 0; t < taps; ++t) {
-              const uint32_t b_off = (uint32_t)((t >> 2) * 512 + (t & 3) * 2);
-              ptx::umma_bf16(d_tmem, a0 + (uint64_t)(a_row + a_col), stem_b0 + (uint64_t)b_off, idesc, t > 0 ? 1u : 0u);
-              if (++a_col == (uint32_t)g.S) {
-                a_col = 0;
-                a_row += (uint32_t)g.sp_row >> 4;
+            if (leader) {  // one divergent region per stage, not one per instruction
+              uint32_t a_row = 0, a_col = 0;  // in 16-byte units
+              for (int t = 0; t < taps; ++t) {
+                const uint32_t b_off = (uint32_t)((t >> 2) * 512 + (t & 3) * 2);
+                ptx::umma_bf16(d_tmem, a0 + (uint64_t)(a_row + a_col), stem_b0 + (uint64_t)b_off, idesc, t > 0 ? 1u : 0u);
+                if (++a_col == (uint32_t)g.S) {
+                  a_col = 0;
+                  a_row += (uint32_t)g.sp_row >> 4;
+                }
               }
+              ptx::umma_commit(&empty_bar[stage]);
             }
-            ptx::umma_commit(&empty_bar[stage]);
             if (++stage == kStages) {
               stage = 0;
               phase ^= 1;
@@ -361,13 +451,15 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
           }
           const uint64_t a_desc = ptx::umma_smem_desc_sw128(ptx::smem_u32(smem_a + stage * kABytes), 16, 1024);
           const uint64_t b_desc = ptx::umma_smem_desc_sw128(ptx::smem_u32(smem_b + stage * Cfg::kBBytes), 16, 1024);
+          if (leader) {
 #pragma unroll
-          for (int k = 0; k < kBlockK / 16; ++k) {
-            // advance 16 bf16 (32 bytes) along K inside the 128B swizzle row: +2 in 16-byte units
-            ptx::umma_bf16(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc,
-                           (it > 0 || k > 0) ? 1u : 0u);
+            for (int k = 0; k < kBlockK / 16; ++k) {
+              // advance 16 bf16 (32 bytes) along K inside the 128B swizzle row: +2 in 16-byte units
+              ptx::umma_bf16(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc,
+                             (it > 0 || k > 0) ? 1u : 0u);
+            }
+            ptx::umma_commit(&empty_bar[stage]);  // frees the smem stage when these MMAs retire
           }
-          ptx::umma_commit(&empty_bar[stage]);  // frees the smem stage when these MMAs retire
           if (++stage == kStages) {
             stage = 0;
             phase ^= 1;
@@ -382,18 +474,20 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
             ptx::tc_fence_after();
             const uint64_t a_desc = ptx::umma_smem_desc_sw128(ptx::smem_u32(smem_a + stage * kABytes), 16, 1024);
             const uint64_t b_desc = ptx::umma_smem_desc_sw128(ptx::smem_u32(smem_b + stage * Cfg::kBBytes), 16, 1024);
+            if (leader) {
 #pragma unroll
-            for (int k = 0; k < kBlockK / 16; ++k)
-              ptx::umma_bf16(d_tmem + (uint32_t)(j * 64), a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc64,
-                             1u);
-            ptx::umma_commit(&empty_bar[stage]);
+              for (int k = 0; k < kBlockK / 16; ++k)
+                ptx::umma_bf16(d_tmem + (uint32_t)(j * 64), a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k),
+                               idesc64, 1u);
+              ptx::umma_commit(&empty_bar[stage]);
+            }
             if (++stage == kStages) {
               stage = 0;
               phase ^= 1;
             }
           }
         }
-        ptx::umma_commit(&tmem_full[acc]);  // accumulator complete -> epilogue
+        if (leader) ptx::umma_commit(&tmem_full[acc]);  // accumulator complete -> epilogue
         if (++acc == kAcc) {
           acc = 0;
           acc_phase ^= 1;
@@ -692,7 +786,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tm_dy, const __grid_consta
   const uint32_t stage_tx = px_bytes * (uint32_t)(2 * MT + BLOCK_N / 64);
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (lane == 0) {  // (the elected-lane form of conv_fprop_kernel measured slower here: few, long stages)
       int stage = 0;
       uint32_t phase = 0;
       for (int i = 0; i < my_iters; ++i) {
@@ -971,6 +1065,8 @@ struct OutView {
   int full_h, full_w, step, off_h, off_w;
 };
 
+static int g_halo_mode = -1;  // -1 = read TDL_HALO on first use, 0 = off (default), 1 = on, 2 = on with base offsets
+
 static int fprop_impl(const void* x, const void* w, void* y, const float* bias, const void* residual, int N, int H,
                       int W, int C, int K, int R, int S, int stride, int dil, int pad_h, int pad_w, int P, int Q,
                       int relu, const OutView* view, float* stats, int* nparts, void* stream,
@@ -995,6 +1091,41 @@ static int fprop_impl(const void* x, const void* w, void* y, const float* bias, 
   g.tiles_h = (int)cdiv(g.P, g.TH);
   g.tiles_w = (int)cdiv(g.Q, g.TW);
   g.num_kb = (int)cdiv(C, kBlockK);
+  const int block_n_pre = K > 128 ? 256 : (K > 64 ? 128 : 64);
+  {
+    // halo mode: stride-1 filters with taps, maps at least 12 pixels high and wide, dilation <= 2.  Tile = TH rows x 8
+    // columns so that every 8-row group of the M tile is one tile row and the groups sit SBO = patch-row bytes apart.
+    // Measured on B200: (1) the unit derives the 128B-swizzle XOR from the absolute shared-memory address of every
+    // row, exactly like the TMA write did, so a start address shifted by whole 128-byte rows needs NO "matrix base
+    // offset" (setting it to (addr >> 7) & 7 breaks the result; g_halo_mode 2 keeps that interpretation testable);
+    // (2) the halo form is numerically right but SLOWER than the tap-shifted form (3x3 64->64 @56x56: 130 us vs
+    // 101 us, 128->128 @28x28: 79 vs 62 us): those layers are bound by per-stage issue overhead of narrow tiles, not
+    // by L2->smem bytes.  It therefore stays off unless tdl_conv2d_set_halo_mode(1) / TDL_HALO=1 asks for it.
+    if (g_halo_mode < 0) {
+      const char* e = getenv("TDL_HALO");
+      g_halo_mode = (e != nullptr) ? atoi(e) : 0;
+    }
+    const int enabled = g_halo_mode != 0, use_bo = g_halo_mode == 2;
+    if (enabled && !flat && !view && residual == nullptr && R * S > 1 && stride == 1 && dil <= 2 && P >= 12 &&
+        Q >= 12) {
+      const int th_tiles = (int)cdiv(P, 16);
+      const int th = (int)cdiv(P, th_tiles);
+      const int pw = (int)cdiv(8 + (S - 1) * dil, 8) * 8;
+      const int ph = th + (R - 1) * dil;
+      const int pbytes = (int)cdiv((int64_t)pw * ph * 128, 1024) * 1024;
+      const int bbytes = block_n_pre * kBlockK * 2;
+      const int ring = 192 * 1024 - 2 * pbytes;  // every BLOCK_N configuration has 192 KB of pipeline stages
+      int nb = ring / bbytes;
+      const int max_nb = block_n_pre == 256 ? 4 : (block_n_pre == 128 ? 6 : 8);
+      if (nb > max_nb) nb = max_nb;
+      if (nb >= 2) {
+        g.halo = 1; g.halo_pw = pw; g.halo_pbytes = pbytes; g.halo_ptx = pw * ph * 128; g.halo_nb = nb;
+        g.halo_bo = use_bo;
+        g.TN = 1; g.TH = th; g.TW = 8;
+        g.tiles_n = g.N; g.tiles_h = (int)cdiv(g.P, g.TH); g.tiles_w = (int)cdiv(g.Q, 8);
+      }
+    }
+  }
   g.relu = relu; g.has_bias = bias != nullptr; g.has_res = residual != nullptr;
   // plain "+ residual" (no bias / ReLU / statistics / strided view): add it on the tensor core, keep the lean epilogue
   g.res_mma = (residual != nullptr && bias == nullptr && !relu && stats == nullptr && view == nullptr) ? 1 : 0;
@@ -1012,6 +1143,11 @@ static int fprop_impl(const void* x, const void* w, void* y, const float* bias, 
     uint64_t dims[4] = {(uint64_t)C, (uint64_t)g.W, (uint64_t)g.H, (uint64_t)g.N};
     uint32_t box[4] = {64, (uint32_t)(g.TW * stride), (uint32_t)(g.TH * stride), (uint32_t)g.TN};
     uint32_t es[4] = {1, (uint32_t)stride, (uint32_t)stride, 1};
+    if (g.halo) {  // the whole haloed patch of one 64-channel block
+      box[1] = (uint32_t)g.halo_pw;
+      box[2] = (uint32_t)(g.TH + (R - 1) * dil);
+      box[3] = 1;
+    }
     int rc = encode_bf16(&tx, x, 4, dims, box, es);
     if (rc) return rc;
   }
@@ -1260,4 +1396,12 @@ TDL_API int tdl_conv_stem_fprop(const void* planes, const void* w_packed, void* 
   cudaStream_t st = (cudaStream_t)stream;
   if (stats_partial) return launch_stem<true>(tx, tmw, ty, g, stats_partial, nparts_host, st);
   return launch_stem<false>(tx, tmw, ty, g, nullptr, nullptr, st);
+}
+
+// Experimental: 0 = tap-shifted loads (default), 1 = halo reuse for stride-1 RxS filters on maps >= 12x12 (one patch load
+// per 64-channel block, taps read it at a row shift), 2 = the same with "matrix base offset" set (known wrong on B200).
+TDL_API int tdl_conv2d_set_halo_mode(int mode) {
+  TDL_REQUIRE(mode >= 0 && mode <= 2, "halo mode must be 0, 1 or 2");
+  g_halo_mode = mode;
+  return 0;
 }

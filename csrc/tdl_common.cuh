@@ -123,6 +123,9 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
 
+// One lane of a fully converged warp (always the same one for a full mask).  Branching on THIS predicate -- rather than
+// on `lane == 0` -- lets ptxas see a single-lane region, so operands of TMA / tcgen05 instructions move to uniform
+// registers directly instead of through an elect-and-broadcast loop per instruction.
 __device__ __forceinline__ bool elect_one() {
   uint32_t pred = 0;
   asm volatile(
@@ -284,6 +287,13 @@ __device__ __forceinline__ uint64_t umma_smem_desc_sw128(uint32_t smem_addr, uin
   d |= (uint64_t)1 << 46;
   d |= (uint64_t)2 << 61;
   return d;
+}
+// 128-byte-swizzle descriptor whose start address is a whole number of 128-byte rows past a 1024-byte boundary:
+// bits [49,52) "matrix base offset" = (start address >> 7) & 7 tells the unit where in the 8-row swizzle period the
+// first row sits.  Lets one resident tile be read at a row shift (halo reuse for shifted convolution taps).
+__device__ __forceinline__ uint64_t umma_smem_desc_sw128_bo(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes,
+                                                            uint32_t base_offset) {
+  return umma_smem_desc_sw128(smem_addr, lbo_bytes, sbo_bytes) | ((uint64_t)(base_offset & 7u) << 49);
 }
 // Same descriptor without swizzling ("interleave" canonical layout), K-major: rows of a core matrix are 16 bytes
 // apart, 8-row groups are `sbo_bytes` apart, the two 16-byte K halves of one K=16 step are `lbo_bytes` apart.

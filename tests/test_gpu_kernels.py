@@ -46,13 +46,27 @@ CONV_CASES = [
     (2, 56, 128, 128, 3, 2, 1, False, False, False),     # stride 2 through TMA element strides
     (2, 51, 64, 64, 3, 2, 1, False, False, False),       # odd size, TF SAME
     (2, 56, 256, 512, 1, 2, 1, False, False, False),
+    (3, 28, 128, 128, 3, 1, 1, False, False, False),     # halo mode: patch loaded once, taps read it at a row shift
+    (3, 14, 256, 256, 3, 1, 1, True, False, True),       # halo mode with several K blocks and a fused epilogue
+    (2, 13, 128, 128, 3, 1, 2, False, False, False),     # halo mode, dilation 2, odd size
+    (2, 19, 72, 40, 3, 1, 1, False, False, False),       # halo mode, ragged channels on both operands
     (4, 28, 128, 512, 1, 1, 1, False, True, False),      # residual only: added on the tensor core (identity-block MMA)
     (3, 14, 256, 72, 3, 1, 1, False, True, False),       # same, 3x3 with a ragged last channel chunk
 ]
 
 
+@pytest.fixture(params=[0, 1], ids=["tap_shifted", "halo_reuse"])
+def halo_mode(request):
+    """Run the convolution cases with both main loops (the halo-reuse one is off by default: correct but slower)."""
+    from tensorflowdistributedlearning_b200 import _native
+
+    assert _native.lib().tdl_conv2d_set_halo_mode(request.param) == 0
+    yield request.param
+    _native.lib().tdl_conv2d_set_halo_mode(0)
+
+
 @pytest.mark.parametrize("case", CONV_CASES)
-def test_conv_fprop_tcgen05(O, case):
+def test_conv_fprop_tcgen05(O, case, halo_mode):
     N, H, C, K, R, stride, dil, bias, res, relu = case
     torch.manual_seed(0)
     x = torch.randn(N, H, H, C, device="cuda").bfloat16()
