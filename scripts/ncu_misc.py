@@ -55,6 +55,14 @@ elif kind == "resmma":
     mask = torch.randint(0, 256, (256 * 56 * 56, 32), dtype=torch.uint8, device="cuda")
     for _ in range(3):
         O.conv2d_fprop(dy, wd, R=1, S=1, out_hw=(56, 56), residual=res, out_mask=mask)
+elif kind in ("conv3x3", "conv3x3_halo"):
+    from tensorflowdistributedlearning_b200 import _native
+
+    _native.lib().tdl_conv2d_set_halo_mode(1 if kind.endswith("halo") else 0)
+    x = torch.randn(256, 56, 56, 64, device="cuda").bfloat16()
+    w = (torch.randn(64, 9, 64, device="cuda") / 24).bfloat16()
+    for _ in range(3):
+        O.conv2d_fprop(x, w, R=3, S=3, pad_h=1, pad_w=1, out_hw=(56, 56))
 elif kind == "depthwise":
     x = torch.randn(64, 38, 38, 728, device="cuda").bfloat16()
     w = torch.randn(9, 728, device="cuda")
