@@ -708,23 +708,28 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
 // A CTA owns MT x 128 output channels x BLOCK_N input channels of one tap, i.e. up to a 256x256 tile held in all
 // 512 TMEM columns: the dY patch is fetched once for BLOCK_N input channels and the X patch once for MT*128 output
 // channels, which halves the L2->SMEM bytes per FLOP compared with a 128x128 tile.
-template <int MT, int BLOCK_N>
+// TP > 1 ("taps per CTA", narrow layers only): the CTA computes TP filter taps at once.  The dY tile is fetched once
+// and the B operand is TP differently shifted X tiles side by side, so ONE MMA of N = TP*BLOCK_N covers them all:
+// 3x3 64->64 goes from nine N=64 problems that each re-read dY to three N=192 problems (wider, fewer MMAs per byte).
+template <int MT, int BLOCK_N, int TP = 1>
 struct WgradCfg {
-  static constexpr int kABytes = MT * 128 * 64 * 2;   // MT * 2 blocks of [64 px][64 co]
-  static constexpr int kBBytes = BLOCK_N * 64 * 2;    // BLOCK_N/64 blocks of [64 px][64 ci]
+  static_assert(TP == 1 || MT == 1, "taps-per-CTA packing is for single-M-tile layers");
+  static_assert(BLOCK_N * TP <= 256, "one MMA covers at most 256 columns");
+  static constexpr int kABytes = MT * 128 * 64 * 2;       // MT * 2 blocks of [64 px][64 co]
+  static constexpr int kBBytes = TP * BLOCK_N * 64 * 2;   // TP * BLOCK_N/64 blocks of [64 px][64 ci]
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kStages = (192 * 1024) / kStageBytes;
-  static constexpr int kTmemColsRaw = MT * BLOCK_N;
+  static constexpr int kTmemColsRaw = MT * BLOCK_N * TP;
   static constexpr int kTmemCols = kTmemColsRaw <= 32 ? 32 : kTmemColsRaw <= 64 ? 64 : kTmemColsRaw <= 128 ? 128
                                    : kTmemColsRaw <= 256 ? 256 : 512;
   static constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256;
 };
 
-template <int MT, int BLOCK_N>
+template <int MT, int BLOCK_N, int TP = 1>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_wgrad_kernel(const __grid_constant__ CUtensorMap tm_dy, const __grid_constant__ CUtensorMap tm_x,
                   const Geometry g, float* __restrict__ dw, int m_tiles_co, int n_tiles_ci) {
-  using Cfg = WgradCfg<MT, BLOCK_N>;
+  using Cfg = WgradCfg<MT, BLOCK_N, TP>;
   constexpr int kStages = Cfg::kStages;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -744,7 +749,8 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tm_dy, const __grid_consta
   const int ci_tile = wi % n_tiles_ci;
   wi /= n_tiles_ci;
   const int co_tile = wi % m_tiles_co;
-  const int tap = wi / m_tiles_co;
+  const int tap = (wi / m_tiles_co) * TP;  // first tap of this CTA's group
+  const int ntaps = min(TP, g.R * g.S - tap);
   const int r = tap / g.S;
   const int s = tap - r * g.S;
 
@@ -783,7 +789,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tm_dy, const __grid_consta
   const uint32_t tmem_base = *tmem_slot;
 
   const uint32_t px_bytes = (uint32_t)(g.TN * g.TH * g.TW) * 128u;  // one 64-channel box
-  const uint32_t stage_tx = px_bytes * (uint32_t)(2 * MT + BLOCK_N / 64);
+  const uint32_t stage_tx = px_bytes * (uint32_t)(2 * MT + ntaps * (BLOCK_N / 64));
 
   if (warp == 0) {
     if (lane == 0) {  // (the elected-lane form of conv_fprop_kernel measured slower here: few, long stages)
@@ -802,11 +808,26 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tm_dy, const __grid_consta
         for (int h = 0; h < 2 * MT; ++h)
           ptx::tma_load_4d(a + h * 8192, &tm_dy, &full_bar[stage], co_tile * (128 * MT) + h * 64, tw_i * g.TW,
                            th_i * g.TH, tn_i * g.TN);
+        if (TP == 1) {
 #pragma unroll
-        for (int h = 0; h < BLOCK_N / 64; ++h)
-          ptx::tma_load_4d(b + h * 8192, &tm_x, &full_bar[stage], ci_tile * BLOCK_N + h * 64,
-                           tw_i * g.TW * g.stride + s * g.dil - g.pad_w,
-                           th_i * g.TH * g.stride + r * g.dil - g.pad_h, tn_i * g.TN);
+          for (int h = 0; h < BLOCK_N / 64; ++h)
+            ptx::tma_load_4d(b + h * 8192, &tm_x, &full_bar[stage], ci_tile * BLOCK_N + h * 64,
+                             tw_i * g.TW * g.stride + s * g.dil - g.pad_w,
+                             th_i * g.TH * g.stride + r * g.dil - g.pad_h, tn_i * g.TN);
+        } else {
+          int rr = r, ss = s;
+          for (int t = 0; t < ntaps; ++t) {  // one shifted X tile per tap, side by side along N
+#pragma unroll
+            for (int h = 0; h < BLOCK_N / 64; ++h)
+              ptx::tma_load_4d(b + (t * (BLOCK_N / 64) + h) * 8192, &tm_x, &full_bar[stage], ci_tile * BLOCK_N + h * 64,
+                               tw_i * g.TW * g.stride + ss * g.dil - g.pad_w,
+                               th_i * g.TH * g.stride + rr * g.dil - g.pad_h, tn_i * g.TN);
+            if (++ss == g.S) {
+              ss = 0;
+              ++rr;
+            }
+          }
+        }
         if (++stage == kStages) {
           stage = 0;
           phase ^= 1;
@@ -815,7 +836,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tm_dy, const __grid_consta
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      constexpr uint32_t idesc = ptx::umma_idesc_bf16(128, BLOCK_N, 1, 1);
+      constexpr uint32_t idesc = ptx::umma_idesc_bf16(128, BLOCK_N * TP, 1, 1);
       int stage = 0;
       uint32_t phase = 0;
       for (int i = 0; i < my_iters; ++i) {
@@ -851,13 +872,14 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tm_dy, const __grid_consta
     for (int mt = 0; mt < MT; ++mt) {
       const int co = co_tile * (128 * MT) + mt * 128 + quarter * 32 + lane;
 #pragma unroll 1
-      for (int c = 0; c < BLOCK_N / 32; ++c) {
+      for (int c = 0; c < ntaps * (BLOCK_N / 32); ++c) {
         uint32_t v[32];
-        ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(mt * BLOCK_N + c * 32), v);
+        ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(mt * BLOCK_N * TP + c * 32), v);
         ptx::tmem_ld_wait();
-        const int ci0 = ci_tile * BLOCK_N + c * 32;
+        const int t_local = c / (BLOCK_N / 32);  // accumulator columns are [tap in group][input channel]
+        const int ci0 = ci_tile * BLOCK_N + (c - t_local * (BLOCK_N / 32)) * 32;
         if (co < g.K) {
-          float* dst = dw + ((size_t)co * taps + tap) * g.C + ci0;
+          float* dst = dw + ((size_t)co * taps + tap + t_local) * g.C + ci0;
 #pragma unroll
           for (int j = 0; j < 32; j += 4)
             if (ci0 + j < g.C)  // C is a multiple of 8, so a 4-wide group is all-in or all-out
@@ -1025,18 +1047,18 @@ static int identity64_address(const void** out, cudaStream_t st) {
   return 0;
 }
 
-template <int MT, int BLOCK_N>
+template <int MT, int BLOCK_N, int TP = 1>
 static int launch_wgrad(const CUtensorMap& tdy, const CUtensorMap& tx, const Geometry& g, float* dw, cudaStream_t st) {
-  using Cfg = WgradCfg<MT, BLOCK_N>;
+  using Cfg = WgradCfg<MT, BLOCK_N, TP>;
   static bool attr_set = false;
   if (!attr_set) {
-    TDL_CUDA_OK(cudaFuncSetAttribute(conv_wgrad_kernel<MT, BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    TDL_CUDA_OK(cudaFuncSetAttribute(conv_wgrad_kernel<MT, BLOCK_N, TP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      Cfg::kSmemBytes));
     attr_set = true;
   }
   const int m_tiles = (int)tdl::cdiv(g.K, 128 * MT);
   const int n_tiles = (int)tdl::cdiv(g.C, BLOCK_N);
-  const int items = m_tiles * n_tiles * g.R * g.S;
+  const int items = m_tiles * n_tiles * (int)tdl::cdiv(g.R * g.S, TP);
   const int patches = g.tiles_n * g.tiles_h * g.tiles_w;
   // split the pixel patches so the grid is a whole number of waves (1 CTA per SM) with >= 8 patches per CTA
   const int sms = tdl::num_sms();
@@ -1048,7 +1070,7 @@ static int launch_wgrad(const CUtensorMap& tdy, const CUtensorMap& tx, const Geo
   if (splits > patches) splits = patches;
   if (splits < 1) splits = 1;
   dim3 grid(splits, items);
-  conv_wgrad_kernel<MT, BLOCK_N><<<grid, kThreads, Cfg::kSmemBytes, st>>>(tdy, tx, g, dw, m_tiles, n_tiles);
+  conv_wgrad_kernel<MT, BLOCK_N, TP><<<grid, kThreads, Cfg::kSmemBytes, st>>>(tdy, tx, g, dw, m_tiles, n_tiles);
   TDL_LAUNCH_OK("conv_wgrad_kernel");
   return 0;
 }
@@ -1283,8 +1305,10 @@ TDL_API int tdl_conv2d_wgrad_bf16(const void* x, const void* dy, float* dw, int 
     return launch_wgrad<2, 64>(tdy, tx, g, dw, st);
   }
   if (block_n == 256) return launch_wgrad<1, 256>(tdy, tx, g, dw, st);
-  if (block_n == 128) return launch_wgrad<1, 128>(tdy, tx, g, dw, st);
-  return launch_wgrad<1, 64>(tdy, tx, g, dw, st);
+  // narrow filters with taps: several taps per CTA share the dY tile and one wide MMA (see WgradCfg)
+  const bool pack = R * S >= 2 && C <= 128;
+  if (block_n == 128) return pack ? launch_wgrad<1, 128, 2>(tdy, tx, g, dw, st) : launch_wgrad<1, 128>(tdy, tx, g, dw, st);
+  return pack ? launch_wgrad<1, 64, 3>(tdy, tx, g, dw, st) : launch_wgrad<1, 64>(tdy, tx, g, dw, st);
 }
 
 // fp32 master weights -> bf16 compute copies (fprop layout and flipped/transposed dgrad layout)

@@ -82,7 +82,10 @@ def test_conv_fprop_tcgen05(O, case, halo_mode):
 
 @pytest.mark.parametrize("case", [(2, 16, 64, 64, 1, 1, 1), (3, 13, 72, 40, 1, 1, 1), (4, 14, 256, 256, 3, 1, 1),
                                   (8, 7, 128, 128, 3, 1, 1), (2, 13, 128, 128, 3, 1, 2), (2, 56, 64, 128, 3, 2, 1),
-                                  (2, 28, 128, 256, 1, 2, 1)])
+                                  (2, 28, 128, 256, 1, 2, 1),
+                                  # narrow filters with taps: three / two taps per CTA in one wide MMA
+                                  (3, 28, 64, 64, 3, 1, 1), (2, 19, 40, 72, 3, 1, 2), (2, 29, 128, 128, 3, 2, 1),
+                                  (2, 14, 104, 128, 3, 1, 1), (2, 16, 64, 64, 2, 1, 1)])
 def test_conv_wgrad_tcgen05(O, case):
     N, H, C, K, R, stride, dil = case
     torch.manual_seed(1)
