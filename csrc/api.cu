@@ -4,7 +4,7 @@
 TDL_API const char* tdl_last_error() { return tdl::err_buf(); }
 
 // Encodes the ABI revision; bump when an existing signature changes.
-TDL_API int tdl_version() { return 100; }
+TDL_API int tdl_version() { return 101; }  // 101: tdl_bn_apply gained mask_out, tdl_bn_bwd_* gained z_is_bitmask
 
 // Number of SMs of the current device as the kernels' launch heuristics see it.
 TDL_API int tdl_num_sms() { return tdl::num_sms(); }

@@ -482,7 +482,8 @@ template <int STRIDE, int DIL>
 __global__ void __launch_bounds__(kT)
 depthwise3x3_tma_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_mask,
                         const float* __restrict__ w, const float* __restrict__ bias, int has_mask,
-                        bf16* __restrict__ y, const TShape s, int stages, int relu_in, int relu_out) {
+                        bf16* __restrict__ y, const TShape s, int stages, int relu_in, int relu_out,
+                        float* __restrict__ stats) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int x_bytes = ((s.BH * s.BW * 128 + 1023) / 1024) * 1024;
@@ -507,6 +508,9 @@ depthwise3x3_tma_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
     for (int c = 0; c < 4; ++c) wt[t][c] = ch_ok ? w[(size_t)t * s.C + ch + c] : 0.f;
 #pragma unroll
   for (int c = 0; c < 4; ++c) b8[c] = (bias && ch_ok) ? bias[ch + c] : 0.f;
+  // optional fused BatchNorm statistics of the (bf16-rounded) output: a thread's four channels never change, so the
+  // sums live in registers for the whole kernel and are folded once at the end into this CTA's partial row
+  float ssum[4] = {0.f, 0.f, 0.f, 0.f}, ssq[4] = {0.f, 0.f, 0.f, 0.f};
 
   const int tiles = s.N * s.tiles_h * s.tiles_w;
   const uint32_t tx_bytes = (uint32_t)(s.BH * s.BW + (has_mask ? s.TH * s.TW : 0)) * 128u;
@@ -607,10 +611,34 @@ depthwise3x3_tma_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
             for (int c = 0; c < 4; ++c) acc[j][c] = m[c] > 0.f ? acc[j][c] : 0.f;
           }
           tdl::dw::st4(orow + (int64_t)j * s.C, acc[j]);
+          if (stats) {
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+              const float v = __bfloat162float(__float2bfloat16_rn(acc[j][c]));  // the value as stored
+              ssum[c] += v;
+              ssq[c] = fmaf(v, v, ssq[c]);
+            }
+          }
         }
       }
     }
     __syncthreads();  // everyone is done reading this stage before it is refilled
+  }
+  if (stats) {
+    // 32 pixel groups x 16 channel quads -> 64 channel sums, twice (sum, sum of squares); the stages are idle now
+    float* red = reinterpret_cast<float*>(smem);
+#pragma unroll
+    for (int which = 0; which < 2; ++which) {
+      __syncthreads();
+#pragma unroll
+      for (int c = 0; c < 4; ++c) red[(grp * 16 + cvec) * 4 + c] = which ? ssq[c] : ssum[c];
+      __syncthreads();
+      if (tid < 64 && c0 + tid < s.C) {
+        float a = 0.f;
+        for (int gidx = 0; gidx < kT / 16; ++gidx) a += red[gidx * 64 + tid];
+        stats[((size_t)blockIdx.x * 2 + which) * s.C + c0 + tid] = a;
+      }
+    }
   }
 }
 
@@ -808,10 +836,9 @@ TDL_API int tdl_depthwise3x3_tma_wgrad(const void* x, const void* dy, float* dw,
   return 0;
 }
 
-// Same contract as tdl_depthwise3x3_fwd; requires C % 8 == 0, stride in {1,2}, dilation in {1,2}.
-TDL_API int tdl_depthwise3x3_tma_fwd(const void* x, const float* w, const float* bias, const void* mask, void* y,
+static int depthwise3x3_tma_fwd_impl(const void* x, const float* w, const float* bias, const void* mask, void* y,
                                      int N, int H, int W, int C, int P, int Q, int stride, int dil, int pad_h,
-                                     int pad_w, int relu_in, int relu_out, void* stream) {
+                                     int pad_w, int relu_in, int relu_out, float* stats, int* nparts, void* stream) {
   using namespace tdl::dwt;
   TDL_REQUIRE(C % 8 == 0, "C must be a multiple of 8");
   TDL_REQUIRE((stride == 1 || stride == 2) && (dil == 1 || dil == 2) && !(stride == 2 && dil == 2),
@@ -842,6 +869,7 @@ TDL_API int tdl_depthwise3x3_tma_fwd(const void* x, const float* w, const float*
   if (gx < 1) gx = 1;
   if (gx > tiles) gx = tiles;
   dim3 grid(gx, gy);
+  if (nparts) *nparts = gx;
   cudaStream_t st = (cudaStream_t)stream;
 #define TDL_DW_LAUNCH(S, D)                                                                                          \
   do {                                                                                                               \
@@ -852,7 +880,7 @@ TDL_API int tdl_depthwise3x3_tma_fwd(const void* x, const float* w, const float*
       attr = true;                                                                                                   \
     }                                                                                                                \
     depthwise3x3_tma_kernel<S, D><<<grid, kT, smem, st>>>(tm, tmm, w, bias, has_mask, (tdl::bf16*)y, s, stages,       \
-                                                          relu_in, relu_out);                                        \
+                                                          relu_in, relu_out, stats);                                 \
   } while (0)
   if (stride == 1 && dil == 1) TDL_DW_LAUNCH(1, 1);
   else if (stride == 1) TDL_DW_LAUNCH(1, 2);
@@ -860,4 +888,24 @@ TDL_API int tdl_depthwise3x3_tma_fwd(const void* x, const float* w, const float*
 #undef TDL_DW_LAUNCH
   TDL_LAUNCH_OK("depthwise3x3_tma_kernel");
   return 0;
+}
+
+// Same contract as tdl_depthwise3x3_fwd; requires C % 8 == 0, stride in {1,2}, dilation in {1,2}.
+TDL_API int tdl_depthwise3x3_tma_fwd(const void* x, const float* w, const float* bias, const void* mask, void* y,
+                                     int N, int H, int W, int C, int P, int Q, int stride, int dil, int pad_h,
+                                     int pad_w, int relu_in, int relu_out, void* stream) {
+  return depthwise3x3_tma_fwd_impl(x, w, bias, mask, y, N, H, W, C, P, Q, stride, dil, pad_h, pad_w, relu_in, relu_out,
+                                   nullptr, nullptr, stream);
+}
+
+// Forward + per-CTA partial BatchNorm statistics of the bf16 output (for the BatchNorm that follows the depthwise conv in
+// the Xception separable convolution): stats_partial is [2 * tdl_num_sms()][2][C] fp32, *nparts_host receives the number
+// of valid leading rows; feed both to tdl_bn_finalize_partials.
+TDL_API int tdl_depthwise3x3_tma_fwd_stats(const void* x, const float* w, const float* bias, void* y, int N, int H,
+                                           int W, int C, int P, int Q, int stride, int dil, int pad_h, int pad_w,
+                                           int relu_in, int relu_out, float* stats_partial, int* nparts_host,
+                                           void* stream) {
+  TDL_REQUIRE(stats_partial != nullptr && nparts_host != nullptr, "stats buffers required");
+  return depthwise3x3_tma_fwd_impl(x, w, bias, nullptr, y, N, H, W, C, P, Q, stride, dil, pad_h, pad_w, relu_in,
+                                   relu_out, stats_partial, nparts_host, stream);
 }

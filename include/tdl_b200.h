@@ -105,6 +105,9 @@ int tdl_depthwise3x3_fwd(const void* x, const float* w, const float* bias, const
 int tdl_depthwise3x3_tma_fwd(const void* x, const float* w, const float* bias, const void* mask, void* y, int N,
                              int H, int W, int C, int P, int Q, int stride, int dil, int pad_h, int pad_w,
                              int relu_in, int relu_out, void* stream);
+int tdl_depthwise3x3_tma_fwd_stats(const void* x, const float* w, const float* bias, void* y, int N, int H, int W, int C,
+                                   int P, int Q, int stride, int dil, int pad_h, int pad_w, int relu_in, int relu_out,
+                                   float* stats_partial /* [2*tdl_num_sms()][2][C] */, int* nparts_host, void* stream);
 int tdl_depthwise3x3_dgrad_s2(const void* dy, const float* w, const void* xmask, void* dx, int N, int H, int W, int C,
                               int P, int Q, int pad_h, int pad_w, void* stream);
 int tdl_depthwise3x3_tma_wgrad(const void* x, const void* dy, float* dw, float* dbias, int N, int H, int W, int C,

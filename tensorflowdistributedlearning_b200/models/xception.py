@@ -54,6 +54,9 @@ class SeparableConv2dSame(TFModule):
 
     def forward(self, x, residual=None):
         """``residual`` (the module's skip branch) is added inside the pointwise BatchNorm kernel."""
+        if self.training:  # the depthwise kernel accumulates the statistics of its own output for dw_bn
+            y, stats = self.depthwise(x, want_stats=True)
+            return self.pointwise(self.dw_bn(y, relu=self.relu, stats=stats), residual=residual)
         return self.pointwise(self.dw_bn(self.depthwise(x), relu=self.relu), residual=residual)
 
 

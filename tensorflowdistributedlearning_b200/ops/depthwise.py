@@ -20,14 +20,18 @@ from . import reference as R
 
 class _DepthwiseNative(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, stride, dil, pads, out_hw, relu, relu_in):
+    def forward(ctx, x, weight, bias, stride, dil, pads, out_hw, relu, relu_in, want_stats=False):
         from . import native_ops as O
 
         kh, kw, C = weight.shape
         fast = kh == 3 and kw == 3
         wd = weight.detach().float().contiguous()
         bd = None if bias is None else bias.detach().float().contiguous()
-        if fast:
+        partials = None
+        if fast and want_stats:
+            y, partials = O.depthwise3x3_fwd(x, wd.view(9, C), bd, None, stride, dil, pads[0], pads[2], out_hw, relu_in,
+                                             relu, want_stats=True)
+        elif fast:
             y = O.depthwise3x3_fwd(x, wd.view(9, C), bd, None, stride, dil, pads[0], pads[2], out_hw, relu_in, relu)
         else:
             xin = torch.relu(x) if relu_in else x
@@ -35,10 +39,15 @@ class _DepthwiseNative(torch.autograd.Function):
         TF._count(1)
         ctx.save_for_backward(x, weight, y if relu else None)
         ctx.cfg = (stride, dil, pads, relu, relu_in, bias is not None, fast)
+        if want_stats:
+            if partials is None:  # shape not served by the fused kernel: an empty marker the caller maps to "no stats"
+                partials = torch.empty(0, device=x.device)
+            ctx.mark_non_differentiable(partials)
+            return y, partials
         return y
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy, *_):
         from . import native_ops as O
 
         x, weight, y = ctx.saved_tensors
@@ -70,17 +79,25 @@ class _DepthwiseNative(torch.autograd.Function):
             if relu_in:
                 dx = dx * (x > 0)
             TF._count(2)
-        return dx, dw, (db if has_bias else None), None, None, None, None, None, None
+        return dx, dw, (db if has_bias else None), None, None, None, None, None, None, None
 
 
 def depthwise_conv2d(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None, stride: int = 1,
-                     dil: int = 1, padding="SAME", relu: bool = False, relu_in: bool = False) -> torch.Tensor:
-    """x [N,H,W,C], weight [kh,kw,C] -> [N,P,Q,C]; optional ReLU on the input, fused bias + ReLU on the output."""
+                     dil: int = 1, padding="SAME", relu: bool = False, relu_in: bool = False, want_stats: bool = False):
+    """x [N,H,W,C], weight [kh,kw,C] -> [N,P,Q,C]; optional ReLU on the input, fused bias + ReLU on the output.
+
+    ``want_stats=True`` returns ``(y, stats)``: ``stats`` are the partial BatchNorm statistics of ``y`` accumulated by the
+    depthwise kernel itself (pass them to :func:`ops.functional.batch_norm`), or None when they were not produced."""
     kh, kw, C = weight.shape
     n, h, w, c = x.shape
     P, Q, pt, pb, pl, pr = TF.conv_pads(h, w, kh, kw, stride, dil, padding)
     if TF._native_ok(x) and C % 8 == 0:
+        if want_stats:
+            y, st = _DepthwiseNative.apply(x.contiguous(), weight, bias, stride, dil, (pt, pb, pl, pr), (P, Q), relu,
+                                           relu_in, True)
+            return y, (st if st.numel() else None)
         return _DepthwiseNative.apply(x.contiguous(), weight, bias, stride, dil, (pt, pb, pl, pr), (P, Q), relu, relu_in)
     xin = F.relu(x) if relu_in else x
     y = R.depthwise_conv2d_nhwc(xin, weight.to(x.dtype), stride, dil, (pt, pb, pl, pr), bias)
-    return F.relu(y) if relu else y
+    y = F.relu(y) if relu else y
+    return (y, None) if want_stats else y

@@ -181,11 +181,11 @@ class DepthwiseConv2d(TFModule):
         R.truncated_normal_(self.weight.data, init_std)
         self.bias = nn.Parameter(torch.zeros(c)) if use_bias else None
 
-    def forward(self, x):
+    def forward(self, x, want_stats: bool = False):
         from . import depthwise as DW
 
         return DW.depthwise_conv2d(x, self.weight, self.bias, self.stride, self.rate, self.padding, self.relu,
-                                   self.relu_in)
+                                   self.relu_in, want_stats)
 
     def tf_variables(self):
         d = {f"{self.scope}/depthwise_weights": (self.weight, "depthwise")}

@@ -423,18 +423,29 @@ def u8_to_bf16_normalize(x_u8: torch.Tensor, mean: torch.Tensor, inv_std: torch.
     return out
 
 
-def depthwise3x3_fwd(x, w9c, bias, mask, stride, dil, pad_h, pad_w, out_hw, relu_in, relu_out):
-    """Fast 3x3 depthwise: x [N,H,W,C] bf16, w9c [9, C] fp32 (tap-major).  ``mask``: zero outputs where mask <= 0."""
+def depthwise3x3_fwd(x, w9c, bias, mask, stride, dil, pad_h, pad_w, out_hw, relu_in, relu_out, want_stats=False):
+    """Fast 3x3 depthwise: x [N,H,W,C] bf16, w9c [9, C] fp32 (tap-major).  ``mask``: zero outputs where mask <= 0.
+    ``want_stats``: also return per-CTA partial BatchNorm statistics of the output, ``(y, partials[nparts,2,C])``, or
+    ``(y, None)`` when the shape is not served by the TMA kernel."""
     _chk_bf16_nhwc(x, "x")
     n, h, w, c = x.shape
     p, q = out_hw
     y = torch.empty((n, p, q, c), dtype=torch.bfloat16, device=x.device)
     tma_ok = c % 8 == 0 and ((stride in (1, 2) and dil == 1) or (stride == 1 and dil == 2))
+    if want_stats and tma_ok and mask is None:
+        partials = torch.empty((2 * int(N.lib().tdl_num_sms()), 2, c), dtype=torch.float32, device=x.device)
+        nparts = ctypes.c_int(0)
+        rc = N.lib().tdl_depthwise3x3_tma_fwd_stats(N.ptr(x), N.ptr(w9c), N.ptr(bias), N.ptr(y), _i(n), _i(h), _i(w),
+                                                    _i(c), _i(p), _i(q), _i(stride), _i(dil), _i(pad_h), _i(pad_w),
+                                                    _i(int(relu_in)), _i(int(relu_out)), N.ptr(partials),
+                                                    ctypes.byref(nparts), N.stream_ptr())
+        N.check(rc, "tdl_depthwise3x3_tma_fwd_stats")
+        return y, partials[:int(nparts.value)]
     fn = N.lib().tdl_depthwise3x3_tma_fwd if tma_ok else N.lib().tdl_depthwise3x3_fwd
     rc = fn(N.ptr(x), N.ptr(w9c), N.ptr(bias), N.ptr(mask), N.ptr(y), _i(n), _i(h), _i(w), _i(c), _i(p), _i(q),
             _i(stride), _i(dil), _i(pad_h), _i(pad_w), _i(int(relu_in)), _i(int(relu_out)), N.stream_ptr())
     N.check(rc, "tdl_depthwise3x3_tma_fwd" if tma_ok else "tdl_depthwise3x3_fwd")
-    return y
+    return (y, None) if want_stats else y
 
 
 def depthwise3x3_wgrad(x, dy, ymask, stride, dil, pad_h, pad_w, relu_in, want_bias):

@@ -428,6 +428,22 @@ def test_spatial_ops(O):
         _native_vs_oracle(lambda t: resize.upsample(t, (out, out)), [torch.randn(2, h, h, C, device="cuda").to(dt)], 2e-2)
 
 
+@pytest.mark.parametrize("case", [(4, 38, 728, 1), (3, 75, 256, 2), (2, 19, 1024, 1)])
+def test_depthwise_fused_bn_statistics(O, case):
+    """The depthwise forward kernel's per-CTA partial sums must equal the statistics of its own bf16 output."""
+    N_, H, C, stride = case
+    torch.manual_seed(8)
+    x = torch.randn(N_, H, H, C, device="cuda").bfloat16()
+    w = torch.randn(9, C, device="cuda") * 0.3
+    P, pt, _ = O.same_pad(H, 3, stride, 1)
+    y, partials = O.depthwise3x3_fwd(x, w, None, None, stride, 1, pt, pt, (P, P), True, False, want_stats=True)
+    y_plain = O.depthwise3x3_fwd(x, w, None, None, stride, 1, pt, pt, (P, P), True, False)
+    assert torch.equal(y, y_plain) and partials is not None and partials.shape[1:] == (2, C)
+    yf = y.float().reshape(-1, C)
+    assert rel_err(partials[:, 0].sum(0), yf.sum(0)) < 1e-3
+    assert rel_err(partials[:, 1].sum(0), (yf * yf).sum(0)) < 1e-3
+
+
 @pytest.mark.parametrize("world", [2, 8])
 def test_p2p_fused_step_emulated_ranks(O, world):
     """All ranks' buffers on one GPU, ranks launched back to back with the cross-rank barrier disabled
