@@ -15,6 +15,8 @@ Moving BatchNorm statistics are averaged over towers every step (X3) through the
 """
 from __future__ import annotations
 
+import os
+
 import math
 from typing import Optional
 
@@ -31,7 +33,7 @@ class DistributedOptimizer:
                  momentum: float = 0.9, weight_decay: float = 0.0, beta1: float = 0.9, beta2: float = 0.999,
                  eps: float = 1e-8, decay_steps: float = 0.0, decay_rate: float = 1.0, comm: Optional[str] = None,
                  bucket_cap_mb: float = 32.0, overlap: bool = True, sync_bn_stats: bool = True,
-                 comm_max_blocks: int = 128, async_wgrad: bool = True):
+                 comm_max_blocks: int = 64, async_wgrad: bool = True):
         if kind not in ("adam", "sgdm"):
             raise ValueError("kind must be 'adam' or 'sgdm'")
         self.group, self.kind = group, kind
@@ -39,7 +41,8 @@ class DistributedOptimizer:
         self.beta1, self.beta2, self.eps = beta1, beta2, eps
         self.decay_steps, self.decay_rate = decay_steps, decay_rate
         self.sync_bn_stats = sync_bn_stats
-        self.comm_max_blocks = comm_max_blocks
+        # CTAs per bucket kernel: they share the SMs with the backward pass they overlap (TDL_COMM_MAX_BLOCKS overrides)
+        self.comm_max_blocks = int(os.environ.get("TDL_COMM_MAX_BLOCKS", comm_max_blocks))
         dev = group.device
         self.on_gpu = dev.type == "cuda"
         if comm is None:
