@@ -114,11 +114,12 @@ class BottleneckV1(TFModule):
                          ConvBNAct(depth_in, depth, 1, stride=stride, scope=f"{s}/shortcut", bn=bn, relu=False))
 
     def forward(self, x, end_points: Optional[dict] = None, prefix: str = ""):
-        if self.shortcut is None and self.training and torch.is_grad_enabled():
-            # identity shortcut: take it from conv1's input alias, so that in backward the shortcut's gradient reaches
-            # conv1's node and is added inside its data-gradient kernel (on the tensor core, csrc/conv_tcgen05.cu
-            # kResMma) instead of by a separate elementwise add
-            h, sc = self.conv1(x, want_tap=True)
+        if self.training and torch.is_grad_enabled():
+            # the shortcut branch (identity or projection) starts from conv1's input alias, so that in backward its
+            # gradient reaches conv1's node and is added inside conv1's data-gradient kernel (on the tensor core,
+            # csrc/conv_tcgen05.cu kResMma) instead of by a separate elementwise add
+            h, xa = self.conv1(x, want_tap=True)
+            sc = xa if self.shortcut is None else self.shortcut(xa)
         else:
             h = self.conv1(x)
             sc = x if self.shortcut is None else self.shortcut(x)
