@@ -647,3 +647,69 @@ TDL_API int tdl_u8_to_bf16_normalize(const void* x_u8, void* y_bf16, int64_t pix
   TDL_LAUNCH_OK("u8_to_bf16_kernel");
   return 0;
 }
+
+// ------------------------------------------------------------------------------------------
+// bias gradient: out[c] += sum over rows of dy[rows, C] (bf16 in, fp32 accumulate, red.add per CTA)
+// ------------------------------------------------------------------------------------------
+namespace tdl {
+namespace spatial {
+__global__ void __launch_bounds__(kThreads)
+colsum_kernel(const bf16* __restrict__ dy, float* __restrict__ out, int64_t rows, int C, int tx, int ty) {
+  extern __shared__ float sm[];  // [ty][tx][8]
+  const int c8 = C >> 3;
+  const int cx = threadIdx.x % tx, ry = threadIdx.x / tx;
+  const int cv = blockIdx.y * tx + cx;
+  float s[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s[j] = 0.f;
+  if (cv < c8) {
+    const int64_t step = (int64_t)gridDim.x * ty;
+    int64_t r = (int64_t)blockIdx.x * ty + ry;
+    for (; r + step < rows; r += 2 * step) {  // two independent 16-byte loads in flight
+      float a[8], b[8];
+      unpack8(ld8(dy + r * C + cv * 8), a);
+      unpack8(ld8(dy + (r + step) * C + cv * 8), b);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s[j] += a[j] + b[j];
+    }
+    for (; r < rows; r += step) {
+      float a[8];
+      unpack8(ld8(dy + r * C + cv * 8), a);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s[j] += a[j];
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) sm[(ry * tx + cx) * 8 + j] = s[j];
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < tx * 8; idx += kThreads) {
+    const int col = idx >> 3;
+    const int cvv = blockIdx.y * tx + col;
+    if (cvv >= c8) continue;
+    float acc = 0.f;
+    for (int t = 0; t < ty; ++t) acc += sm[(t * tx + col) * 8 + (idx & 7)];
+    atomicAdd(out + cvv * 8 + (idx & 7), acc);
+  }
+}
+}  // namespace spatial
+}  // namespace tdl
+
+// out[C] (fp32) += column sums of dy[rows, C] (bf16): the bias gradient of a convolution.  Caller zeroes `out` if needed.
+TDL_API int tdl_colsum_bf16(const void* dy, float* out, int64_t rows, int C, void* stream) {
+  using namespace tdl::spatial;
+  TDL_REQUIRE(C > 0 && C % 8 == 0, "C must be a positive multiple of 8");
+  if (rows <= 0) return 0;
+  const int c8 = C / 8;
+  int tx = 1;
+  while (tx < 32 && tx < c8) tx <<= 1;
+  const int ty = kThreads / tx;
+  const int gy = (int)tdl::cdiv(c8, tx);
+  int64_t gx = tdl::cdiv(rows, (int64_t)ty * 8);
+  const int64_t cap = (int64_t)tdl::num_sms() * 4 / gy;
+  if (gx > cap) gx = cap;
+  if (gx < 1) gx = 1;
+  colsum_kernel<<<dim3((unsigned)gx, (unsigned)gy), kThreads, kThreads * 8 * sizeof(float), (cudaStream_t)stream>>>(
+      (const tdl::bf16*)dy, out, rows, C, tx, ty);
+  TDL_LAUNCH_OK("colsum_kernel");
+  return 0;
+}

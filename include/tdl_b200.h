@@ -133,6 +133,7 @@ int tdl_conv2d_smallk_bwd_data(const void* dy, const float* w, void* dx, int N, 
                                int S, int dil, int pad_h, int pad_w, int P, int Q, void* stream);
 int tdl_conv2d_smallk_bwd_weight(const void* x, const void* dy, float* dw, float* dbias, int N, int H, int W, int C,
                                  int K, int R, int S, int dil, int pad_h, int pad_w, int P, int Q, void* stream);
+int tdl_colsum_bf16(const void* dy, float* out, int64_t rows, int C, void* stream); /* out[C] += column sums (bias gradient) */
 int tdl_upsample_fwd(const void* x, void* y, int N, int H, int W, int C, int OH, int OW, int is_bf16, void* stream);
 int tdl_upsample_bwd(const void* dy, float* dx, int N, int H, int W, int C, int OH, int OW, int is_bf16, void* stream);
 int tdl_u8_to_bf16_normalize(const void* x_u8, void* y_bf16, int64_t pixels, int C, int Cpad, const float* mean,

@@ -23,11 +23,22 @@ ap.add_argument("--out", default="gpurun_out/profile_step.txt")
 args = ap.parse_args()
 
 group = TowerGroup(device="cuda")
-model = models.build(args.model, num_classes=1000)
-tr = TowerTrainer(model, group, batch=args.batch, input_hwc=(args.size, args.size, 3), loss_fn=classification_loss,
-                  use_graph=False, kind="sgdm", lr=0.1, momentum=0.9, weight_decay=1e-4)
-tr.images.copy_(torch.randint(0, 256, tr.images.shape, dtype=torch.uint8))
-tr.labels.copy_(torch.randint(0, 1000, tr.labels.shape))
+if args.model == "refseg":  # the reference's own network: 101x101x2 input, Lovasz hinge, Adam
+    from tensorflowdistributedlearning_b200.parallel.trainer import segmentation_loss
+
+    model = models.build("refseg", model_name="model")
+    tr = TowerTrainer(model, group, batch=args.batch, input_hwc=(101, 101, 2), label_shape=(101, 101, 1),
+                      label_dtype=torch.float32, loss_fn=segmentation_loss, use_graph=False, kind="adam", lr=1e-3,
+                      mean=[0.47194585] * 2, std=[0.16105755] * 2)
+    tr.images.copy_(torch.randint(0, 256, tr.images.shape, dtype=torch.uint8))
+    tr.labels.copy_((torch.rand(tr.labels.shape) > 0.6).float())
+else:
+    model = models.build(args.model, num_classes=1000)
+    tr = TowerTrainer(model, group, batch=args.batch, input_hwc=(args.size, args.size, 3),
+                      loss_fn=classification_loss, use_graph=False, kind="sgdm", lr=0.1, momentum=0.9,
+                      weight_decay=1e-4)
+    tr.images.copy_(torch.randint(0, 256, tr.images.shape, dtype=torch.uint8))
+    tr.labels.copy_(torch.randint(0, 1000, tr.labels.shape))
 for _ in range(3):
     tr.run_step()
 torch.cuda.synchronize()

@@ -239,7 +239,16 @@ class _ConvNative(torch.autograd.Function):
                 dw = dw.view(K, Rk, Sk, C)
             _count(1)
         if has_bias and ctx.needs_input_grad[2]:
-            db = dy.float().sum((0, 1, 2))
+            bp = ctx.bias_param
+            if K % 8 == 0:  # one pass over dy (bf16 -> fp32 column sums) instead of a cast plus a generic reduction
+                if _direct_ok(bp):
+                    O.colsum_(dy.view(-1, K), bp.grad)
+                    _notify(bp)
+                else:
+                    db = O.colsum_(dy.view(-1, K), torch.zeros(K, dtype=torch.float32, device=dy.device))
+                _count(1)
+            else:
+                db = dy.float().sum((0, 1, 2))
         return dx, dw, db, None, None, None, None, None, None
 
 

@@ -554,3 +554,11 @@ def depthwise3x3_dgrad_s2(dy, w9c, xmask, in_shape, pad_h, pad_w):
                                            _i(p), _i(q), _i(pad_h), _i(pad_w), N.stream_ptr())
     N.check(rc, "tdl_depthwise3x3_dgrad_s2")
     return dx
+
+
+def colsum_(dy2d: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+    """out[C] (fp32) += column sums of dy2d [rows, C] (bf16): a convolution's bias gradient in one pass."""
+    rows, C = dy2d.shape
+    rc = N.lib().tdl_colsum_bf16(N.ptr(dy2d), N.ptr(out), _i64(rows), _i(C), N.stream_ptr())
+    N.check(rc, "tdl_colsum_bf16")
+    return out
