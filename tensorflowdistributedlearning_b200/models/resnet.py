@@ -30,6 +30,16 @@ from ..ops.layers import BNConfig, BatchNorm, Conv2d, ConvBNAct, SplitSeparableC
 _DEFAULT_MULTI_GRID = [2, 2, 2]  # reference: core/resnet.py multi_grid default
 
 
+class EndPoints(dict):
+    """End-point collection (core/resnet.py:171-257 ``end_points_collection``).  ``wanted`` names the pre-activation
+    tensors a caller will read; units whose ``.../conv3`` output is not wanted fuse the shortcut add and the ReLU
+    into that convolution and never materialise it."""
+
+    def __init__(self, wanted=()):
+        super().__init__()
+        self.wanted = frozenset(wanted)
+
+
 # ---------------------------------------------------------------------------------------------
 # units
 # ---------------------------------------------------------------------------------------------
@@ -61,10 +71,15 @@ class Bottleneck(TFModule):
         sc = L.subsample(x, self.stride) if self.shortcut is None else self.shortcut(pre)
         r = self.conv1(pre)
         r = self.conv2(r)
-        r = self.conv3(r)
-        out = F.relu(sc + r)
-        if end_points is not None:
+        want_r = end_points is not None and f"{prefix}{self.scope}/conv3" in getattr(end_points, "wanted", ())
+        if end_points is None or (hasattr(end_points, "wanted") and not want_r):
+            # relu(shortcut + conv3(.)) inside conv3's epilogue: no separate add / ReLU kernels
+            out = self.conv3(r, residual=sc, relu=True)
+        else:
+            r = self.conv3(r)
+            out = F.relu(sc + r)
             end_points[f"{prefix}{self.scope}/conv3"] = r
+        if end_points is not None:
             end_points[f"{prefix}{self.scope}"] = out
         return out
 
@@ -244,8 +259,11 @@ class ResNetV2Beta(TFModule):
         self.logits = (Conv2d(depth, num_classes, 1, use_bias=True, scope=f"{scope}/logits",
                               weight_decay=bn.weight_decay) if num_classes is not None else None)
 
-    def forward(self, x, collect: bool = True):
-        end_points: Optional[Dict[str, torch.Tensor]] = {} if collect else None
+    def forward(self, x, collect: bool = True, wanted=None):
+        """``wanted`` (optional): the only pre-activation end points the caller needs; see :class:`EndPoints`."""
+        end_points: Optional[Dict[str, torch.Tensor]] = None
+        if collect:
+            end_points = {} if wanted is None else EndPoints(wanted)
         net = self.root(x)
         if self.symmetric_padding:
             from ..ops import pooling as P
@@ -387,7 +405,7 @@ class ResNetSegModel(TFModule):
                               weight_decay=weight_decay)
 
     def forward(self, x):
-        _, ep = self.backbone(x, collect=True)
+        _, ep = self.backbone(x, collect=True, wanted=(self.low_key,))
         feat = ep[self.block4_key]
         size = feat.shape[1:3]
         branches = [self.aspp_1x1(feat)] + [m(feat) for m in self.aspp_sep]

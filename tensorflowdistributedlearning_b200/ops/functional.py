@@ -139,10 +139,12 @@ class _ConvNative(torch.autograd.Function):
     """tcgen05 implicit-GEMM forward; dgrad = same kernel on flipped/transposed weights; wgrad = MN-major kernel."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, stride, dil, pads, out_hw, want_stats=False, want_tap=False):
+    def forward(ctx, x, weight, bias, stride, dil, pads, out_hw, want_stats=False, want_tap=False, residual=None,
+                relu_out=False):
         from . import native_ops as O
 
         ctx.weight_param, ctx.bias_param, ctx.want_tap = weight, bias, want_tap
+        ctx.relu_out, ctx.has_residual = bool(relu_out), residual is not None
         # the 1-bit ReLU mask of the input tensor, when its producer left one (BatchNorm + residual + ReLU)
         ctx.in_mask = getattr(x, "_tdl_relu_mask", None) if want_tap else None
 
@@ -159,10 +161,12 @@ class _ConvNative(torch.autograd.Function):
                                                        out_hw=out_hw, bias=None if bias is None else bias.detach())
             partials = partials[:nparts]
         else:
+            # (+ residual) (+ ReLU) in the epilogue: the reference unit's relu(shortcut + conv3(...)), core/resnet.py:148
             y = O.conv2d_fprop(x, wf, R=Rk, S=Sk, stride=stride, dil=dil, pad_h=pt, pad_w=pl, out_hw=out_hw,
-                               bias=None if bias is None else bias.detach())
+                               bias=None if bias is None else bias.detach(),
+                               residual=None if residual is None else residual.detach().contiguous(), relu=relu_out)
         _count(2)
-        ctx.save_for_backward(x, wd if wd is not None else wf)
+        ctx.save_for_backward(x, wd if wd is not None else wf, y if relu_out else None)
         ctx.cfg = (K, Rk, Sk, C, stride, dil, pads, tuple(x.shape), bias is not None, wd is not None)
         outs = [y]
         if want_stats:
@@ -180,11 +184,13 @@ class _ConvNative(torch.autograd.Function):
     def backward(ctx, dy, *rest):
         from . import native_ops as O
 
-        x, wsaved = ctx.saved_tensors
+        x, wsaved, y_relu = ctx.saved_tensors
         K, Rk, Sk, C, stride, dil, pads, xshape, has_bias, has_wd = ctx.cfg
         pt, pb, pl, pr = pads
         n, h, w, _ = xshape
         dy = dy.contiguous()
+        if ctx.relu_out:  # backward of the fused output ReLU: everything below, and the residual branch, sees dy * (y > 0)
+            dy = torch.ops.aten.threshold_backward(dy, y_relu, 0)
         d_tap = rest[-1] if (ctx.want_tap and rest and rest[-1] is not None) else None
         dx = dw = db = None
         if ctx.needs_input_grad[0]:
@@ -249,7 +255,7 @@ class _ConvNative(torch.autograd.Function):
                 _count(1)
             else:
                 db = dy.float().sum((0, 1, 2))
-        return dx, dw, db, None, None, None, None, None, None
+        return dx, dw, db, None, None, None, None, None, None, (dy if ctx.has_residual else None), None
 
 
 class _ConvStem(torch.autograd.Function):
@@ -356,8 +362,12 @@ class _ConvSmallK(torch.autograd.Function):
 
 
 def conv2d(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None, stride: int = 1,
-           dil: int = 1, padding="SAME", want_stats: bool = False, want_tap: bool = False):
+           dil: int = 1, padding="SAME", want_stats: bool = False, want_tap: bool = False,
+           residual: Optional[torch.Tensor] = None, relu: bool = False):
     """NHWC convolution, weight [K, R, S, C] (fp32 master).  TF 'SAME' geometry by default.
+
+    ``residual`` / ``relu``: ``relu?(conv(x) + bias + residual)`` in the convolution's own epilogue (not combinable
+    with ``want_stats`` / ``want_tap``).
 
     ``want_stats=True`` returns ``(y, stats)`` where ``stats`` is either None (torch path) or the per-CTA partial
     BatchNorm statistics the tcgen05 kernel accumulated in its epilogue; pass it to :func:`batch_norm`.
@@ -371,11 +381,11 @@ def conv2d(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] =
     assert c == C, f"channel mismatch: input {c} vs weight {C}"
     P, Q, pt, pb, pl, pr = conv_pads(h, w, Rk, Sk, stride, dil, padding)
     if (_native_ok(x) and c <= 4 and stride == 2 and dil == 1 and bias is None and K % 8 == 0 and K <= 64
-            and max(Rk, Sk) <= 7 and not want_tap and _STEM_NATIVE):
+            and max(Rk, Sk) <= 7 and not want_tap and _STEM_NATIVE and residual is None and not relu):
         out = _ConvStem.apply(x.contiguous(), weight, (pt, pb, pl, pr), (P, Q), want_stats)
         return out
     if (_native_ok(x) and K <= 4 and stride == 1 and Rk * Sk <= 9 and C % 8 == 0 and C <= 2048
-            and not (want_stats or want_tap)):
+            and not (want_stats or want_tap) and residual is None and not relu):
         return _ConvSmallK.apply(x.contiguous(), weight, bias, dil, (pt, pb, pl, pr), (P, Q))
     if _native_ok(x) and C % 8 == 0 and K % 8 == 0 and stride <= 2:
         if want_stats or want_tap:
@@ -386,6 +396,9 @@ def conv2d(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] =
             if want_tap:
                 return out[0], None, out[1]
             return out
+        if residual is not None or relu:
+            return _ConvNative.apply(x.contiguous(), weight, bias, stride, dil, (pt, pb, pl, pr), (P, Q), False, False,
+                                     residual, relu)
         return _ConvNative.apply(x.contiguous(), weight, bias, stride, dil, (pt, pb, pl, pr), (P, Q))
     # torch path (cuDNN on GPU through a channels-last view; plain CPU conv on CPU towers)
     wq = weight.to(x.dtype)
@@ -396,6 +409,10 @@ def conv2d(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] =
     else:
         y = F.conv2d(F.pad(xin, (pl, pr, pt, pb)), wq.permute(0, 3, 1, 2), bq, stride=stride, dilation=dil)
     y = y.permute(0, 2, 3, 1)
+    if residual is not None:
+        y = y + residual
+    if relu:
+        y = F.relu(y)
     if want_tap:
         return y, None, x
     return (y, None) if want_stats else y

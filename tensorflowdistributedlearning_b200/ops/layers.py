@@ -99,8 +99,10 @@ class Conv2d(TFModule):
         self.weight = nn.Parameter(full)
         self.bias = nn.Parameter(torch.zeros(self.cout_p)) if use_bias else None
 
-    def forward(self, x: torch.Tensor, want_stats: bool = False, want_tap: bool = False):
-        return TF.conv2d(x, self.weight, self.bias, self.stride, self.rate, self.padding, want_stats, want_tap)
+    def forward(self, x: torch.Tensor, want_stats: bool = False, want_tap: bool = False,
+                residual: Optional[torch.Tensor] = None, relu: bool = False):
+        return TF.conv2d(x, self.weight, self.bias, self.stride, self.rate, self.padding, want_stats, want_tap,
+                         residual, relu)
 
     def tf_variables(self):
         d = {f"{self.scope}/weights": (self.weight, "conv", (self.cout, self.k, self.k, self.cin))}

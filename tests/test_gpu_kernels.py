@@ -175,6 +175,33 @@ def test_conv_residual_on_tensor_core_with_relu_mask(O):
     assert bool(((y == 0) | keep.view(N_, H, H, K)).all())
 
 
+def test_conv_fused_residual_relu_forward_and_gradients():
+    """relu(conv(x) + b + shortcut) in one epilogue (reference bottleneck tail, core/resnet.py:148-150) against fp32."""
+    from tensorflowdistributedlearning_b200.ops import functional as Fn
+
+    torch.manual_seed(11)
+    N_, H, C, K = 2, 20, 128, 256
+    x0 = torch.randn(N_, H, H, C, device="cuda").bfloat16()
+    r0 = torch.randn(N_, H, H, K, device="cuda").bfloat16()
+    w = (torch.randn(K, 1, 1, C, device="cuda") / 11).requires_grad_(True)
+    b = torch.randn(K, device="cuda").requires_grad_(True)
+    g = torch.randn(N_, H, H, K, device="cuda").bfloat16()
+    x, r = x0.clone().requires_grad_(True), r0.clone().requires_grad_(True)
+    Fn.begin_step()
+    y = Fn.conv2d(x, w, b, residual=r, relu=True)
+    y.backward(g)
+    xf, rf = x0.float().requires_grad_(True), r0.float().requires_grad_(True)
+    wf = w.detach().bfloat16().float().requires_grad_(True)
+    bf = b.detach().clone().requires_grad_(True)
+    yf = torch.relu(torch.einsum("nhwc,kc->nhwk", xf, wf[:, 0, 0]) + bf + rf)
+    yf.backward(g.float())
+    assert rel_err(y, yf) < 1e-2
+    assert rel_err(x.grad, xf.grad) < 2e-2
+    assert rel_err(r.grad, rf.grad) < 2e-2
+    assert rel_err(w.grad, wf.grad) < 2e-2
+    assert rel_err(b.grad, bf.grad) < 2e-2
+
+
 def test_residual_units_backward_with_premasked_gradients():
     """Three stacked v1.5 bottleneck units: the identity-shortcut gradient is added inside conv1's data gradient and
     the previous unit's ReLU backward is applied in the same epilogue; parameter and input gradients must match the
