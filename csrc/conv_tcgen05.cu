@@ -1015,8 +1015,192 @@ static int launch_stem(const CUtensorMap& tx, const CUtensorMap& tw, const CUten
   return 0;
 }
 
+// ------------------------------------------------------------------------------------------
+// first-layer weight gradient on the packed image:
+//   dWp[co][tap (r2, s2)][cp] = sum over (n, p, q) dY[n, p, q, co] * planes[n, p - pad2_h + r2, cp / 8, q - pad2_w + s2, cp % 8]
+// GEMM M = Cout (128 rows, the upper 64 a resident zero block), K = the pixels of ONE output row (16 per MMA),
+// N = packed taps x channels.  The dY row is a 128B-swizzled MN-major A tile exactly as in conv_wgrad_kernel.  The
+// haloed image patch [taps_h][plane][TWB + taps_w - 1 pixels][8 ch] sits un-swizzled in shared memory, one pixel per
+// 16-byte core-matrix row, so as an MN-major "interleave" B operand its 8-channel groups may start at ANY pixel:
+// with a group stride (SBO) of ONE pixel the taps_w column taps of a (row tap, plane) pair become one MMA of
+// N = 8 * taps_w whose column groups overlap in shared memory.  No im2col, each byte of dY and of the image is
+// fetched once; the packed gradient stays in TMEM for the whole kernel and leaves through red.global.add.
+//   variant 0: M = 128 (upper half zero)      variant 1: M = 64
+// ------------------------------------------------------------------------------------------
+struct StemWgradGeo {
+  int N, P, Q, K, th, tw, pad2_h, pad2_w;
+  int TWB, tiles_w, sp_plane, sp_row;
+  int a_block, b_off, stage_bytes, stages, tx_bytes;
+  int ncols, nblocks, variant;
+};
+
+template <int NBLK>  // NBLK = 2 * row taps
+__global__ void __launch_bounds__(kThreads, 1)
+stem_wgrad_kernel(const __grid_constant__ CUtensorMap tm_dy, const __grid_constant__ CUtensorMap tm_x,
+                  const StemWgradGeo g, float* __restrict__ dwp) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + g.stages * g.stage_bytes);
+  uint64_t* full_bar = bars;
+  uint64_t* empty_bar = bars + g.stages;
+  uint64_t* tmem_full = bars + 2 * g.stages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int total_tiles = g.N * g.P * g.tiles_w;
+  const int my_iters = (total_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+  if (my_iters <= 0) return;
+
+  {  // the upper 64 rows of A and the slack behind each patch must read as zero for every stage
+    uint4 z = make_uint4(0, 0, 0, 0);
+    uint4* p4 = reinterpret_cast<uint4*>(smem);
+    const int n16 = g.stages * g.stage_bytes / 16;
+    for (int i = threadIdx.x; i < n16; i += kThreads) p4[i] = z;
+    ptx::fence_proxy_async_smem();
+  }
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tm_dy);
+    ptx::prefetch_tmap(&tm_x);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int i = 0; i < g.stages; ++i) {
+        ptx::mbar_init(&full_bar[i], 1);
+        ptx::mbar_init(&empty_bar[i], 1);
+      }
+      ptx::mbar_init(tmem_full, 1);
+      ptx::fence_mbar_init();
+    }
+    __syncwarp();
+    ptx::tmem_alloc<256>(tmem_slot);
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  // Both issuing warps walk their schedule as a whole warp and one elected lane issues (see conv_fprop_kernel).
+  if (warp == 0) {
+    const bool leader = ptx::elect_one();
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int i = 0; i < my_iters; ++i) {
+      const int tile = (int)blockIdx.x + i * (int)gridDim.x;
+      const int tw_i = tile % g.tiles_w;
+      const int p = (tile / g.tiles_w) % g.P;
+      const int n = tile / (g.tiles_w * g.P);
+      ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+      uint8_t* a = smem + stage * g.stage_bytes;
+      if (leader) {
+        ptx::mbar_expect_tx(&full_bar[stage], (uint32_t)g.tx_bytes);
+        ptx::tma_load_4d(a, &tm_dy, &full_bar[stage], 0, tw_i * g.TWB, p, n);
+        ptx::tma_load_4d(a + g.b_off, &tm_x, &full_bar[stage], (tw_i * g.TWB - g.pad2_w) * 2, 0, p - g.pad2_h, n);
+      }
+      if (++stage == g.stages) {
+        stage = 0;
+        phase ^= 1;
+      }
+    }
+  } else if (warp == 1) {
+    const bool leader = ptx::elect_one();
+    {
+      // variant 1: M = 64 (no zero upper half to read; rows land in lanes 0..15 of each TMEM quarter)
+      const uint32_t idesc = ptx::umma_idesc_bf16(g.variant == 1 ? 64 : 128, g.ncols, 1, 1);
+      const int ksteps = g.TWB >> 4;
+      // Everything an MMA needs is a 64-bit add away: block offsets (16-byte units) and TMEM columns are hoisted, so
+      // the single issuing thread spends a handful of instructions per tcgen05.mma, not a descriptor rebuild.
+      uint32_t boff[NBLK];
+#pragma unroll
+      for (int blk = 0; blk < NBLK; ++blk) boff[blk] = (uint32_t)((blk >> 1) * g.sp_row + (blk & 1) * g.sp_plane) >> 4;
+      const uint64_t b_desc0 = ptx::umma_smem_desc_nosw(0, 128, 16);  // K groups 128 B apart, column-tap groups 16 B
+      const uint64_t a_desc0 = ptx::umma_smem_desc_sw128(0, (uint32_t)g.a_block, 1024);
+      const uint32_t ncols = (uint32_t)g.ncols;
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int i = 0; i < my_iters; ++i) {
+        ptx::mbar_wait(&full_bar[stage], phase);
+        ptx::tc_fence_after();
+        const uint32_t a_addr = ptx::smem_u32(smem + stage * g.stage_bytes);
+        uint64_t a_k = a_desc0 + (uint64_t)(a_addr >> 4);
+        uint64_t b_k = b_desc0 + (uint64_t)((a_addr + (uint32_t)g.b_off) >> 4);
+        uint32_t acc = i > 0 ? 1u : 0u;
+        for (int ks = 0; ks < ksteps; ++ks) {
+          if (leader) {
+#pragma unroll
+            for (int blk = 0; blk < NBLK; ++blk)  // blk = r2 * 2 + plane
+              ptx::umma_bf16(tmem_base + (uint32_t)blk * ncols, a_k, b_k + boff[blk], idesc, acc);
+          }
+          a_k += 128;  // 16 pixel rows of 128 bytes
+          b_k += 16;   // 16 pixels of 16 bytes
+          acc = 1u;
+        }
+        if (leader) ptx::umma_commit(&empty_bar[stage]);
+        if (++stage == g.stages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      if (leader) ptx::umma_commit(tmem_full);
+    }
+  } else {
+    const int quarter = warp & 3;
+    ptx::mbar_wait(tmem_full, 0);
+    ptx::tc_fence_after();
+    const int co = g.variant == 1 ? (lane < 16 ? quarter * 16 + lane : g.K) : quarter * 32 + lane;
+    const int T = g.th * g.tw;
+    const int total_cols = g.nblocks * g.ncols;
+#pragma unroll 1
+    for (int c = 0; c < total_cols; c += 32) {
+      uint32_t v[32];
+      ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)c, v);
+      ptx::tmem_ld_wait();
+      if (co < g.K) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+          const int col = c + j;
+          const int blk = col / g.ncols, within = col - blk * g.ncols;
+          const int s2 = within >> 3;
+          if (s2 >= g.tw) continue;  // columns added to round N up to a multiple of 16
+          const int t = (blk >> 1) * g.tw + s2;
+          const int cp = (blk & 1) * 8 + (within & 7);
+          float* dst = dwp + ((size_t)co * T + t) * 16 + cp;
+          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "f"(__uint_as_float(v[j])),
+                       "f"(__uint_as_float(v[j + 1])), "f"(__uint_as_float(v[j + 2])), "f"(__uint_as_float(v[j + 3]))
+                       : "memory");
+        }
+      }
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc<256>(tmem_base);
+  }
+}
+
+// dWp [K][Th*Tw][16] (packed problem)  ->  dW [K, R, S, C] fp32 (inverse of stem_weight_prep_kernel's index map)
+__global__ void stem_wgrad_unpack_kernel(const float* __restrict__ dwp, float* __restrict__ dw, int K, int R, int S,
+                                         int C, int Th, int Tw, int pad_h, int pad_w, int pad2_h, int pad2_w,
+                                         int accumulate) {
+  const int total = K * R * S * C;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int c = i % C;
+    const int s = (i / C) % S;
+    const int r = (i / (C * S)) % R;
+    const int k = i / (C * S * R);
+    const int rr = r - pad_h, ss = s - pad_w;
+    const int rq = rr >= 0 ? rr / 2 : -((1 - rr) / 2), sq = ss >= 0 ? ss / 2 : -((1 - ss) / 2);  // floor division
+    const int cp = ((rr - 2 * rq) * 2 + (ss - 2 * sq)) * C + c;
+    const float v = dwp[((size_t)k * Th * Tw + (rq + pad2_h) * Tw + (sq + pad2_w)) * 16 + cp];
+    dw[i] = accumulate ? dw[i] + v : v;
+  }
+}
+
 template <int BLOCK_N, bool kFused, bool kStats, bool kResMma = false>
-static int launch_fprop_t(const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& ty, const CUtensorMap& tres,
+static int launch_fprop_t(
+const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& ty, const CUtensorMap& tres,
                           const CUtensorMap& tid, const Geometry& g, const float* bias, const bf16* res, float* stats,
                           int* nparts, cudaStream_t st) {
   using Cfg = FpropCfg<BLOCK_N>;
@@ -1450,6 +1634,75 @@ TDL_API int tdl_conv_stem_fprop(const void* planes, const void* w_packed, void* 
   cudaStream_t st = (cudaStream_t)stream;
   if (stats_partial) return launch_stem<true>(tx, tmw, ty, g, stats_partial, nparts_host, st);
   return launch_stem<false>(tx, tmw, ty, g, nullptr, nullptr, st);
+}
+
+// Weight gradient of the first layer from the packed image (see stem_wgrad_kernel).  `dwp_scratch` holds
+// tdl_conv_stem_weight_elems() floats; dw is the fp32 [K, R, S, C] gradient (overwritten, or added to if accumulate).
+TDL_API int tdl_conv_stem_wgrad(const void* planes, const void* dy, float* dwp_scratch, float* dw, int N, int H, int W,
+                                int C, int K, int R, int S, int pad_h, int pad_w, int P, int Q, int accumulate,
+                                int variant, void* stream) {
+  TDL_REQUIRE(K % 8 == 0 && K >= 8 && K <= 64, "stem kernel handles 8..64 output channels (multiple of 8)");
+  TDL_REQUIRE(C >= 1 && C <= 4, "stem handles 1..4 input channels");
+  TDL_REQUIRE(variant == 0 || variant == 1, "variant is 0 or 1");
+  int th, tw, p2h, p2w;
+  stem_taps(R, pad_h, &th, &p2h);
+  stem_taps(S, pad_w, &tw, &p2w);
+  TDL_REQUIRE(th >= 1 && tw >= 1 && th * tw <= 16, "stem kernel handles at most 16 packed taps (filters up to 7x7)");
+  const int H2 = (H + 1) / 2, W2 = (W + 1) / 2;
+  StemWgradGeo g;
+  memset(&g, 0, sizeof(g));
+  g.N = N; g.P = P; g.Q = Q; g.K = K; g.th = th; g.tw = tw; g.pad2_h = p2h; g.pad2_w = p2w; g.variant = variant;
+  g.ncols = (8 * tw + 15) / 16 * 16;
+  g.nblocks = 2 * th;
+  TDL_REQUIRE(g.nblocks * g.ncols <= 256, "packed gradient exceeds 256 TMEM columns");
+  const int halo = g.ncols / 8 - 1;  // pixels read past the last output pixel (including rounded-up column groups)
+  const int max_twb = (128 - halo) / 16 * 16;
+  const int w_tiles = (int)cdiv(Q, max_twb);
+  g.TWB = (int)cdiv(cdiv(Q, w_tiles), 16) * 16;
+  g.tiles_w = (int)cdiv(Q, g.TWB);
+  const int box_px = g.TWB + halo;
+  g.sp_plane = box_px * 16;
+  g.sp_row = 2 * g.sp_plane;
+  g.a_block = g.TWB * 128;
+  g.b_off = 2 * g.a_block;
+  g.tx_bytes = g.a_block + th * g.sp_row;
+  g.stage_bytes = (int)cdiv(g.b_off + th * g.sp_row + 256, 1024) * 1024;
+  g.stages = (200 * 1024) / g.stage_bytes;
+  if (g.stages > 8) g.stages = 8;
+  TDL_REQUIRE(g.stages >= 2, "stem wgrad stage does not fit twice in shared memory");
+  const int smem_bytes = g.stages * g.stage_bytes + 1024 + 256;
+  CUtensorMap tdy, tx;
+  {
+    uint64_t dims[4] = {(uint64_t)K, (uint64_t)Q, (uint64_t)P, (uint64_t)N};
+    uint32_t box[4] = {64, (uint32_t)g.TWB, 1, 1};
+    uint32_t es[4] = {1, 1, 1, 1};
+    int rc = encode_bf16(&tdy, dy, 4, dims, box, es);
+    if (rc) return rc;
+  }
+  {
+    uint64_t dims[4] = {(uint64_t)W2 * 2, 2, (uint64_t)H2, (uint64_t)N};
+    uint64_t strides[3] = {(uint64_t)W2 * 16, (uint64_t)W2 * 32, (uint64_t)W2 * 32 * H2};
+    uint32_t box[4] = {(uint32_t)box_px * 2, 2, (uint32_t)th, 1};
+    uint32_t es[4] = {1, 1, 1, 1};
+    int rc = encode_map(&tx, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 8, CU_TENSOR_MAP_SWIZZLE_NONE, planes, 4, dims, box, es,
+                        strides);
+    if (rc) return rc;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  void (*kern)(CUtensorMap, CUtensorMap, StemWgradGeo, float*) =
+      th == 1 ? stem_wgrad_kernel<2> : th == 2 ? stem_wgrad_kernel<4> : th == 3 ? stem_wgrad_kernel<6>
+                                                                                 : stem_wgrad_kernel<8>;
+  TDL_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  TDL_CUDA_OK(cudaMemsetAsync(dwp_scratch, 0, sizeof(float) * (size_t)K * th * tw * 16, st));
+  const int total = N * P * g.tiles_w;
+  const int grid = total < tdl::num_sms() ? total : tdl::num_sms();
+  kern<<<grid, kThreads, smem_bytes, st>>>(tdy, tx, g, dwp_scratch);
+  TDL_LAUNCH_OK("stem_wgrad_kernel");
+  const int n_out = K * R * S * C;
+  stem_wgrad_unpack_kernel<<<(int)cdiv(n_out, 256), 256, 0, st>>>(dwp_scratch, dw, K, R, S, C, th, tw, pad_h, pad_w,
+                                                                 p2h, p2w, accumulate);
+  TDL_LAUNCH_OK("stem_wgrad_unpack_kernel");
+  return 0;
 }
 
 // Experimental: 0 = tap-shifted loads (default), 1 = halo reuse for stride-1 RxS filters on maps >= 12x12 (one patch load

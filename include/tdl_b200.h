@@ -125,6 +125,12 @@ int tdl_conv_stem_weight_prep(const float* w, void* w_packed, int K, int R, int 
                               void* stream);
 int tdl_conv_stem_fprop(const void* planes, const void* w_packed, void* y, int N, int H, int W, int K, int R, int S,
                         int pad_h, int pad_w, int P, int Q, float* stats_partial, int* nparts_host, void* stream);
+/* First-layer weight gradient from the packed image (tcgen05; one output row per GEMM K slab).  dwp_scratch holds
+ * tdl_conv_stem_weight_elems() floats; dw is fp32 [K,R,S,C], overwritten or (accumulate != 0) added to.
+ * One MMA per (row tap, plane) with overlapping column-tap groups; variant 0: M = 128, 1: M = 64. */
+int tdl_conv_stem_wgrad(const void* planes, const void* dy, float* dwp_scratch, float* dw, int N, int H, int W, int C,
+                        int K, int R, int S, int pad_h, int pad_w, int P, int Q, int accumulate, int variant,
+                        void* stream);
 /* Convolution with 1..4 output channels (decoder 3x3 -> 1 logit).  CUDA-core dot products; weight is the
  * fp32 master [K,R,S,C]; stride 1; dw / dbias are accumulated into. */
 int tdl_conv2d_smallk_fwd(const void* x, const float* w, const float* bias, void* y, int N, int H, int W, int C, int K,

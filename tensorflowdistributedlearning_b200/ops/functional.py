@@ -261,8 +261,9 @@ class _ConvNative(torch.autograd.Function):
 class _ConvStem(torch.autograd.Function):
     """First layer: stride-2 conv on <= 4 input channels (7x7 / 3x3 roots, core/resnet.py:164,219-224;
     core/xception.py:352).  Forward = space-to-depth pack + tcgen05 kernel with the haloed patch resident in shared
-    memory (csrc/conv_tcgen05.cu, kStem); BatchNorm partial statistics optionally fused.  The weight gradient of this
-    one layer (K*R*S*C <= 9408 values reduced over all pixels) stays on cuDNN's small-channel wgrad."""
+    memory (csrc/conv_tcgen05.cu, kStem); BatchNorm partial statistics optionally fused.  The weight gradient runs on
+    the same packed image (stem_wgrad_kernel: one output row per GEMM-K slab, column taps as overlapping operand
+    groups); only a requested INPUT gradient (never the case for an image) falls back to the library."""
 
     @staticmethod
     def forward(ctx, x, weight, pads, out_hw, want_stats):
@@ -274,7 +275,8 @@ class _ConvStem(torch.autograd.Function):
         wp = O.conv_stem_weight_prep(weight.detach().contiguous(), pt, pl)
         res = O.conv_stem_fprop(planes, wp, (x.shape[1], x.shape[2]), K, Rk, Sk, pt, pl, out_hw, want_stats)
         _count(3)
-        ctx.save_for_backward(x, weight)
+        ctx.save_for_backward(x, weight, planes)
+        ctx.weight_param = weight
         ctx.cfg = (pads, want_stats)
         if want_stats:
             y, partials, nparts = res
@@ -285,10 +287,22 @@ class _ConvStem(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dy, *rest):
-        x, weight = ctx.saved_tensors
+        x, weight, planes = ctx.saved_tensors
         (pt, pb, pl, pr), _ = ctx.cfg
         K, Rk, Sk, C = weight.shape
         need_dx, need_dw = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        if need_dw and not need_dx:
+            from . import native_ops as O
+
+            wp = ctx.weight_param
+            dy = dy.contiguous()
+            hw = (x.shape[1], x.shape[2])
+            _count(3)
+            if _direct_ok(wp):
+                O.conv_stem_wgrad(planes, dy, hw, C, Rk, Sk, pt, pl, dw=wp.grad)
+                _notify(wp)
+                return None, None, None, None, None
+            return None, O.conv_stem_wgrad(planes, dy, hw, C, Rk, Sk, pt, pl), None, None, None
         w4 = weight.detach().to(x.dtype).permute(0, 3, 1, 2)
         xin = x.permute(0, 3, 1, 2)
         if pt != pb or pl != pr:

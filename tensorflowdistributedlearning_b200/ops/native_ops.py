@@ -545,6 +545,25 @@ def conv_stem_fprop(planes: torch.Tensor, w_packed: torch.Tensor, image_hw, K: i
     return y
 
 
+def conv_stem_wgrad(planes: torch.Tensor, dy: torch.Tensor, image_hw, C: int, R: int, S: int, pad_h: int, pad_w: int,
+                    dw: Optional[torch.Tensor] = None, variant: int = 1) -> torch.Tensor:
+    """First-layer weight gradient on the tensor cores from the packed image.  Returns fp32 [K,R,S,C]; when ``dw``
+    is given the gradient is ADDED to it."""
+    _chk_bf16_nhwc(dy, "dy")
+    n, p, q, K = dy.shape
+    h, w = image_hw
+    elems = int(N.lib().tdl_conv_stem_weight_elems(_i(K), _i(R), _i(S), _i(pad_h), _i(pad_w)))
+    scratch = torch.empty((elems,), dtype=torch.float32, device=dy.device)
+    acc = dw is not None
+    if dw is None:
+        dw = torch.empty((K, R, S, C), dtype=torch.float32, device=dy.device)
+    rc = N.lib().tdl_conv_stem_wgrad(N.ptr(planes), N.ptr(dy), N.ptr(scratch), N.ptr(dw), _i(n), _i(h), _i(w), _i(C),
+                                     _i(K), _i(R), _i(S), _i(pad_h), _i(pad_w), _i(p), _i(q), _i(1 if acc else 0),
+                                     _i(variant), N.stream_ptr())
+    N.check(rc, "tdl_conv_stem_wgrad")
+    return dw
+
+
 def depthwise3x3_dgrad_s2(dy, w9c, xmask, in_shape, pad_h, pad_w):
     """Data gradient of a stride-2 3x3 depthwise conv; ``xmask`` (the forward input of a pre-activation ReLU) masks it."""
     n, h, w, c = in_shape

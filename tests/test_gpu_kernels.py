@@ -265,6 +265,28 @@ def test_conv_stem_space_to_depth_tcgen05(O, case):
     assert rel_err(w.grad, wr.grad.permute(0, 2, 3, 1)) < 2e-2
 
 
+@pytest.mark.parametrize("variant", [0, 1])
+def test_conv_stem_wgrad_variants_and_accumulate(O, variant):
+    """tdl_conv_stem_wgrad with M = 128 / M = 64 accumulators, overwrite and accumulate forms, odd image size."""
+    from tensorflowdistributedlearning_b200.ops import functional as Fn
+
+    torch.manual_seed(4)
+    N, H, C, K, R = 3, 99, 3, 48, 7
+    x = torch.randn(N, H, H, C, device="cuda").bfloat16()
+    P, Q, pt, pb, pl, pr = Fn.conv_pads(H, H, R, R, 2, 1, "SAME")
+    dy = torch.randn(N, P, Q, K, device="cuda").bfloat16()
+    planes = O.conv_stem_pack(x)
+    dw = O.conv_stem_wgrad(planes, dy, (H, H), C, R, R, pt, pl, variant=variant)
+    xr = F.pad(x.float().permute(0, 3, 1, 2), (pl, pr, pt, pb))
+    wr = torch.zeros(K, C, R, R, device="cuda", requires_grad=True)
+    F.conv2d(xr, wr, None, stride=2).backward(dy.float().permute(0, 3, 1, 2))
+    ref = wr.grad.permute(0, 2, 3, 1)
+    assert rel_err(dw, ref) < 1e-3
+    acc = torch.full_like(dw, 2.0)
+    O.conv_stem_wgrad(planes, dy, (H, H), C, R, R, pt, pl, dw=acc, variant=variant)
+    assert rel_err(acc, ref + 2.0) < 1e-3
+
+
 @pytest.mark.parametrize("case", [(4, 26, 512, 1, 3, 1, True), (2, 13, 264, 2, 3, 2, False), (3, 9, 64, 4, 1, 1, True)])
 def test_conv_small_k_decoder_head(O, case):
     """K <= 4 output channels (the decoder's 3x3 -> 1 logit, core/resnet.py:487-492): CUDA-core kernels, fwd + both grads."""
