@@ -556,6 +556,17 @@ TDL_API int tdl_bn_bwd_reduce(const void* dz, const void* x, const void* z, int 
   return 0;
 }
 
+// BatchNorm-backward sums that were already reduced per CTA elsewhere (the data-gradient kernel's epilogue,
+// tdl_conv2d_dgrad_bnstats_bf16): partial is [nparts][2][C] = (sum dz, sum dz * xhat).
+TDL_API int tdl_bn_bwd_finalize_partials(const float* partial, int nparts, int C, float* dgamma, float* dbeta,
+                                         float* acc_dgamma, float* acc_dbeta, void* stream) {
+  TDL_REQUIRE(C > 0 && nparts > 0, "bad shape");
+  bn_bwd_finalize_kernel<<<(C + kFinCh - 1) / kFinCh, kFinThreads, 0, (cudaStream_t)stream>>>(
+      partial, nparts, C, dbeta, dgamma, acc_dbeta, acc_dgamma);
+  TDL_LAUNCH_OK("bn_bwd_finalize_kernel");
+  return 0;
+}
+
 TDL_API int tdl_bn_bwd_apply(const void* dz, const void* x, const void* z, int z_is_bitmask, const float* scale,
                              const float* shift, const float* mean, const float* invstd, const float* dgamma, const float* dbeta,
                              void* dx, void* dres, int64_t rows, int C, int relu, void* stream) {

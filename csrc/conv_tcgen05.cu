@@ -96,6 +96,10 @@ struct Geometry {
   int relu, has_bias, has_res;
   // first-layer ("stem") mode only: byte pitches of the haloed space-to-depth patch in shared memory
   int sp_plane, sp_row, sp_tx, sp_wbytes;
+  // kBwdStats: the BatchNorm whose output gradient this (data-gradient) launch produces
+  const void* bn_x;
+  const float* bn_mean;
+  const float* bn_invstd;
   int res_mma;  // residual tile added on the tensor core (extra K iterations against an identity block)
   // halo mode (stride-1 RxS > 1x1): the haloed input patch of a K block is loaded ONCE and every tap reads it at a row
   // shift instead of re-fetching a shifted copy per tap (the tap-shifted form is bound by L2->smem bandwidth there)
@@ -182,7 +186,7 @@ struct FpropCfg {
 // (bf16 x 1.0 accumulates exactly in fp32).  The epilogue stays the lean one, and the residual read is prefetched by
 // the same mbarrier pipeline as everything else.  Used by the data gradient of a unit's first conv to absorb the
 // identity-shortcut gradient (otherwise a separate 3-pass elementwise add per residual unit).
-template <int BLOCK_N, bool kFused, bool kStats, bool kStem = false, bool kResMma = false>
+template <int BLOCK_N, bool kFused, bool kStats, bool kStem = false, bool kResMma = false, bool kBwdStats = false>
 __global__ void __launch_bounds__(kFpropThreads, 1)
 conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
                   const __grid_constant__ CUtensorMap tm_y, const __grid_constant__ CUtensorMap tm_res,
@@ -250,7 +254,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
     __syncwarp();
     ptx::tmem_alloc<Cfg::kTmemCols>(tmem_slot);
   }
-  if constexpr (kStats) {  // this CTA's statistics slot starts at zero
+  if constexpr (kStats || kBwdStats) {  // this CTA's statistics slot starts at zero
     float* slot = stats + (size_t)blockIdx.x * 2 * g.K;
     for (int i = threadIdx.x; i < 2 * g.K; i += kFpropThreads) slot[i] = 0.f;
   }
@@ -529,8 +533,9 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
     // tile, which made the stats variant 2.8x slower than the plain kernel on output-heavy layers.)
     constexpr int kChunks = BLOCK_N / 64;
     float sacc[kChunks][4];
+    float mu[kChunks][2];  // kBwdStats: batch means of this thread's two channels per 64-channel chunk
 #pragma unroll
-    for (int c = 0; c < kChunks; ++c) sacc[c][0] = sacc[c][1] = sacc[c][2] = sacc[c][3] = 0.f;
+    for (int c = 0; c < kChunks; ++c) sacc[c][0] = sacc[c][1] = sacc[c][2] = sacc[c][3] = mu[c][0] = mu[c][1] = 0.f;
     int stat_n_tile = -1;
     auto flush_stats = [&](int nt) {
       if (issuer) ptx::tma_store_wait_read<0>();  // nobody is reading the staging buffer any more
@@ -551,7 +556,12 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
 #pragma unroll
         for (int e = 0; e < 4; ++e) tot += st[((e * kChunks + c) * 4 + v) * 32 + ln];
         const int ch = nt * BLOCK_N + c * 64 + 2 * ln + (v >> 1);  // v: 0 = sum ch0, 1 = sumsq ch0, 2 = sum ch1, 3 = sumsq ch1
-        if (ch < g.K) atomicAdd(&slot[(size_t)(v & 1) * g.K + ch], tot);  // both groups add into the CTA's slot
+        if (ch < g.K) {
+          if constexpr (kBwdStats) {
+            if (v & 1) tot *= g.bn_invstd[ch];  // sum dz * (x - mean)  ->  sum dz * xhat
+          }
+          atomicAdd(&slot[(size_t)(v & 1) * g.K + ch], tot);  // both groups add into the CTA's slot
+        }
       }
       ptx::named_bar_sync(bar_id, 128);  // the staging buffer is free again
     };
@@ -566,7 +576,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
       const int tn_i = m_tile / (g.tiles_w * g.tiles_h);
       bool valid = true;
       size_t pix = 0;
-      if constexpr (kFused || kStats || kResMma) {
+      if constexpr (kFused || kStats || kResMma || kBwdStats) {
         const int n = tn_i * g.TN + dn;
         const int p = th_i * g.TH + dh;
         const int q = tw_i * g.TW + dw;
@@ -575,10 +585,18 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
       }
       const int chunks = min(BLOCK_N / 64, (g.K - n_tile * BLOCK_N + 63) / 64);
       uint32_t vm = 0xffffffffu;  // which of this warp's 32 rows are real output pixels
-      if constexpr (kStats) {
+      if constexpr (kStats || kBwdStats) {
         if (n_tile != stat_n_tile) {
           if (stat_n_tile >= 0) flush_stats(stat_n_tile);
           stat_n_tile = n_tile;
+          if constexpr (kBwdStats) {
+#pragma unroll
+            for (int c = 0; c < kChunks; ++c) {
+              const int ch = n_tile * BLOCK_N + c * 64 + (lane >> 2) * 8 + (lane & 3) * 2;
+              mu[c][0] = ch < g.K ? g.bn_mean[ch] : 0.f;
+              mu[c][1] = ch < g.K ? g.bn_mean[ch + 1] : 0.f;
+            }
+          }
         }
         vm = __ballot_sync(0xffffffffu, valid);
       }
@@ -629,7 +647,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
               }
             }
           }
-          if constexpr (kResMma) {
+          if constexpr (kResMma || kBwdStats) {
             // fused ReLU backward of the tensor this gradient belongs to: bit j of byte (pixel, c/8) = "was > 0"
             if (g.has_mask && valid && co0 < g.K) {
               const uint8_t* mrow = reinterpret_cast<const uint8_t*>(residual) + pix * (size_t)(g.K >> 3) + (co0 >> 3);
@@ -656,6 +674,40 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
         if (issuer) {
           ptx::tma_store_4d(&tm_y, out_tile, co_chunk, tw_i * g.TW, th_i * g.TH, tn_i * g.TN);
           ptx::tma_store_commit();
+        }
+        if constexpr (kBwdStats) {
+          // BatchNorm-backward reductions of the gradient as stored (masked, bf16): per channel sum(dz) and
+          // sum(dz * (x - mean)), x = the BatchNorm's input at the same pixel, fetched here one 128-byte row per warp
+          // instruction.  Replaces the separate reduction pass over (dz, x) (tdl_bn_bwd_reduce).
+          const uint8_t* rows = out_tile + (uint32_t)(quarter * 32) * 128u + ((uint32_t)(lane & 3) << 2);
+          const uint32_t c16 = (uint32_t)(lane >> 2);
+          const int ch0 = co_chunk + (int)c16 * 8 + (lane & 3) * 2;
+          const bf16* xcol = reinterpret_cast<const bf16*>(g.bn_x) + ch0;
+          const bool ch_ok = ch0 < g.K;
+          const uint32_t pix32 = (uint32_t)pix;
+          uint32_t xv[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const uint32_t pi = __shfl_sync(0xffffffffu, pix32, i);
+            xv[i] = (ch_ok && ((vm >> i) & 1u)) ? __ldg(reinterpret_cast<const uint32_t*>(xcol + (size_t)pi * g.K)) : 0u;
+          }
+          float s0 = 0.f, q0 = 0.f, s1 = 0.f, q1 = 0.f;
+          const float m0 = mu[cc][0], m1 = mu[cc][1];
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const uint32_t wv = *reinterpret_cast<const uint32_t*>(rows + i * 128 + ((c16 ^ (uint32_t)(i & 7)) << 4));
+            const bool ok = (vm >> i) & 1u;
+            const float f0 = ok ? __uint_as_float(wv << 16) : 0.f;
+            const float f1 = ok ? __uint_as_float(wv & 0xffff0000u) : 0.f;
+            s0 += f0;
+            q0 = fmaf(f0, __uint_as_float(xv[i] << 16) - m0, q0);
+            s1 += f1;
+            q1 = fmaf(f1, __uint_as_float(xv[i] & 0xffff0000u) - m1, q1);
+          }
+          sacc[cc][0] += s0;
+          sacc[cc][1] += q0;
+          sacc[cc][2] += s1;
+          sacc[cc][3] += q1;
         }
         if constexpr (kStats) {
           // statistics of the values as stored (bf16) over this warp's 32 rows, rows outside the image masked out
@@ -686,7 +738,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
         }
       }
     }
-    if constexpr (kStats) {
+    if constexpr (kStats || kBwdStats) {
       if (stat_n_tile >= 0) flush_stats(stat_n_tile);
     }
     if (issuer) ptx::tma_store_wait_all<0>();
@@ -1198,7 +1250,7 @@ __global__ void stem_wgrad_unpack_kernel(const float* __restrict__ dwp, float* _
   }
 }
 
-template <int BLOCK_N, bool kFused, bool kStats, bool kResMma = false>
+template <int BLOCK_N, bool kFused, bool kStats, bool kResMma = false, bool kBwdStats = false>
 static int launch_fprop_t(
 const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& ty, const CUtensorMap& tres,
                           const CUtensorMap& tid, const Geometry& g, const float* bias, const bf16* res, float* stats,
@@ -1206,14 +1258,14 @@ const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& ty, const CUten
   using Cfg = FpropCfg<BLOCK_N>;
   static bool attr_set = false;
   if (!attr_set) {
-    TDL_CUDA_OK(cudaFuncSetAttribute(conv_fprop_kernel<BLOCK_N, kFused, kStats, false, kResMma>,
+    TDL_CUDA_OK(cudaFuncSetAttribute(conv_fprop_kernel<BLOCK_N, kFused, kStats, false, kResMma, kBwdStats>,
                                      cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
     attr_set = true;
   }
   const int total = g.tiles_n * g.tiles_h * g.tiles_w * g.n_tiles;
   const int grid = total < tdl::num_sms() ? total : tdl::num_sms();
   if (nparts) *nparts = grid;
-  conv_fprop_kernel<BLOCK_N, kFused, kStats, false, kResMma><<<grid, kFpropThreads, Cfg::kSmemBytes, st>>>(
+  conv_fprop_kernel<BLOCK_N, kFused, kStats, false, kResMma, kBwdStats><<<grid, kFpropThreads, Cfg::kSmemBytes, st>>>(
       tx, tw, ty, tres, tid, g, bias, res, stats);
   TDL_LAUNCH_OK("conv_fprop_kernel");
   return 0;
@@ -1223,6 +1275,11 @@ template <int BLOCK_N>
 static int launch_fprop(const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& ty, const CUtensorMap& tres,
                         const CUtensorMap& tid, const Geometry& g, const float* bias, const bf16* res, float* stats,
                         int* nparts, cudaStream_t st) {
+  if (g.bn_x) {  // data gradient that also reduces the BatchNorm-backward sums of the tensor it produces
+    if (g.res_mma)
+      return launch_fprop_t<BLOCK_N, false, false, true, true>(tx, tw, ty, tres, tid, g, bias, res, stats, nparts, st);
+    return launch_fprop_t<BLOCK_N, false, false, false, true>(tx, tw, ty, tres, tid, g, bias, res, stats, nparts, st);
+  }
   if (g.res_mma) return launch_fprop_t<BLOCK_N, false, false, true>(tx, tw, ty, tres, tid, g, bias, res, stats, nparts, st);
   const bool fused = g.has_bias || g.has_res || g.relu;
   if (stats) {
@@ -1295,12 +1352,19 @@ struct OutView {
   int full_h, full_w, step, off_h, off_w;
 };
 
+// The BatchNorm a data-gradient launch reduces for (kBwdStats): its input tensor and batch statistics.
+struct BnBwd {
+  const void* x;
+  const float* mean;
+  const float* invstd;
+};
+
 static int g_halo_mode = -1;  // -1 = read TDL_HALO on first use, 0 = off (default), 1 = on, 2 = on with base offsets
 
 static int fprop_impl(const void* x, const void* w, void* y, const float* bias, const void* residual, int N, int H,
                       int W, int C, int K, int R, int S, int stride, int dil, int pad_h, int pad_w, int P, int Q,
                       int relu, const OutView* view, float* stats, int* nparts, void* stream,
-                      const void* out_mask = nullptr) {
+                      const void* out_mask = nullptr, const BnBwd* bnb = nullptr) {
   TDL_REQUIRE(C % 8 == 0 && K % 8 == 0, "channel counts must be multiples of 8 (16-byte TMA strides)");
   TDL_REQUIRE(stride >= 1 && stride <= 8 && dil >= 1, "bad stride/dilation");
   TDL_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(w) & 15) == 0 &&
@@ -1336,7 +1400,7 @@ static int fprop_impl(const void* x, const void* w, void* y, const float* bias, 
       g_halo_mode = (e != nullptr) ? atoi(e) : 0;
     }
     const int enabled = g_halo_mode != 0, use_bo = g_halo_mode == 2;
-    if (enabled && !flat && !view && residual == nullptr && R * S > 1 && stride == 1 && dil <= 2 && P >= 12 &&
+    if (enabled && !flat && !view && residual == nullptr && bnb == nullptr && R * S > 1 && stride == 1 && dil <= 2 && P >= 12 &&
         Q >= 12) {
       const int th_tiles = (int)cdiv(P, 16);
       const int th = (int)cdiv(P, th_tiles);
@@ -1358,10 +1422,17 @@ static int fprop_impl(const void* x, const void* w, void* y, const float* bias, 
   }
   g.relu = relu; g.has_bias = bias != nullptr; g.has_res = residual != nullptr;
   // plain "+ residual" (no bias / ReLU / statistics / strided view): add it on the tensor core, keep the lean epilogue
-  g.res_mma = (residual != nullptr && bias == nullptr && !relu && stats == nullptr && view == nullptr) ? 1 : 0;
+  g.res_mma = (residual != nullptr && bias == nullptr && !relu && (stats == nullptr || bnb) && view == nullptr) ? 1 : 0;
   if (g.res_mma) g.has_res = 0;
+  if (bnb) {
+    TDL_REQUIRE(stats && nparts && !view && bias == nullptr && !relu && stride == 1,
+                "BatchNorm-backward sums: plain stride-1 data gradient only");
+    TDL_REQUIRE(bnb->x && bnb->mean && bnb->invstd, "BatchNorm tensors required");
+    TDL_REQUIRE((int64_t)N * P * Q < ((int64_t)1 << 31), "pixel index exceeds 32 bits");
+    g.bn_x = bnb->x; g.bn_mean = bnb->mean; g.bn_invstd = bnb->invstd;
+  }
   if (out_mask) {
-    TDL_REQUIRE(g.res_mma, "the output mask is only available together with a plain residual");
+    TDL_REQUIRE(g.res_mma || bnb, "the output mask needs a plain residual or the BatchNorm-backward sums");
     TDL_REQUIRE(K % 32 == 0, "the output mask needs K % 32 == 0");
     g.has_mask = 1;
   }
@@ -1422,7 +1493,7 @@ static int fprop_impl(const void* x, const void* w, void* y, const float* bias, 
     if (rc) return rc;
   }
   // in res_mma mode the residual arrives through its tensor map; the pointer slot carries the optional output mask
-  const bf16* aux = g.res_mma ? (const bf16*)out_mask : (const bf16*)residual;
+  const bf16* aux = (g.res_mma || bnb) ? (const bf16*)out_mask : (const bf16*)residual;
   if (block_n == 256) return launch_fprop<256>(tx, tw, ty, tres, tid, g, bias, aux, stats, nparts, st);
   if (block_n == 128) return launch_fprop<128>(tx, tw, ty, tres, tid, g, bias, aux, stats, nparts, st);
   return launch_fprop<64>(tx, tw, ty, tres, tid, g, bias, aux, stats, nparts, st);
@@ -1446,6 +1517,20 @@ TDL_API int tdl_conv2d_fprop_res_mask_bf16(const void* x, const void* w, void* y
   TDL_REQUIRE(residual != nullptr, "residual required");
   return fprop_impl(x, w, y, nullptr, residual, N, H, W, C, K, R, S, stride, dil, pad_h, pad_w, P, Q, 0, nullptr,
                     nullptr, nullptr, stream, out_mask);
+}
+
+// Data gradient (a stride-1 convolution of dy with the flipped weights) that ALSO reduces, for the BatchNorm whose
+// output gradient it produces, the per-channel sums BatchNorm backward needs: stats_partial [tdl_num_sms()][2][K]
+// = per-CTA (sum dz, sum dz * xhat) with dz the stored (optionally masked / residual-added) output and
+// xhat = (bn_x - mean) * invstd.  Feed to tdl_bn_bwd_finalize_partials; tdl_bn_bwd_reduce's pass over (dz, x) is gone.
+TDL_API int tdl_conv2d_dgrad_bnstats_bf16(const void* x, const void* w, void* y, const void* residual,
+                                          const void* out_mask, const void* bn_x, const float* bn_mean,
+                                          const float* bn_invstd, int N, int H, int W, int C, int K, int R, int S,
+                                          int dil, int pad_h, int pad_w, int P, int Q, float* stats_partial,
+                                          int* nparts_host, void* stream) {
+  BnBwd b = {bn_x, bn_mean, bn_invstd};
+  return fprop_impl(x, w, y, nullptr, residual, N, H, W, C, K, R, S, 1, dil, pad_h, pad_w, P, Q, 0, nullptr,
+                    stats_partial, nparts_host, stream, out_mask, &b);
 }
 
 // Same convolution, additionally producing per-CTA partial (sum, sum of squares) of the bf16 output per channel:

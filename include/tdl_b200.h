@@ -79,6 +79,8 @@ int tdl_bn_bwd_reduce(const void* dz, const void* x, const void* z, int z_is_bit
                       const float* shift, const float* mean, const float* invstd, int64_t rows, int C, int relu,
                       float* scratch, int64_t scratch_floats, float* dgamma, float* dbeta, float* acc_dgamma,
                       float* acc_dbeta, void* stream);
+int tdl_bn_bwd_finalize_partials(const float* partial, int nparts, int C, float* dgamma, float* dbeta,
+                                 float* acc_dgamma, float* acc_dbeta, void* stream);
 int tdl_bn_bwd_apply(const void* dz, const void* x, const void* z, int z_is_bitmask, const float* scale,
                      const float* shift, const float* mean, const float* invstd, const float* dgamma,
                      const float* dbeta, void* dx, void* dres, int64_t rows, int C, int relu, void* stream);
@@ -131,6 +133,13 @@ int tdl_conv_stem_fprop(const void* planes, const void* w_packed, void* y, int N
 int tdl_conv_stem_wgrad(const void* planes, const void* dy, float* dwp_scratch, float* dw, int N, int H, int W, int C,
                         int K, int R, int S, int pad_h, int pad_w, int P, int Q, int accumulate, int variant,
                         void* stream);
+/* Stride-1 data gradient that also reduces the BatchNorm-backward sums (sum dz, sum dz * xhat) of the tensor it
+ * produces, in its epilogue; residual / out_mask optional (as tdl_conv2d_fprop_res_mask_bf16).  stats_partial is
+ * [tdl_num_sms()][2][K]; feed it to tdl_bn_bwd_finalize_partials. */
+int tdl_conv2d_dgrad_bnstats_bf16(const void* x, const void* w, void* y, const void* residual, const void* out_mask,
+                                  const void* bn_x, const float* bn_mean, const float* bn_invstd, int N, int H, int W,
+                                  int C, int K, int R, int S, int dil, int pad_h, int pad_w, int P, int Q,
+                                  float* stats_partial, int* nparts_host, void* stream);
 /* Convolution with 1..4 output channels (decoder 3x3 -> 1 logit).  CUDA-core dot products; weight is the
  * fp32 master [K,R,S,C]; stride 1; dw / dbias are accumulated into. */
 int tdl_conv2d_smallk_fwd(const void* x, const float* w, const float* bias, void* y, int N, int H, int W, int C, int K,

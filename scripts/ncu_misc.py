@@ -1,4 +1,4 @@
-"""Driver for ncu captures of single kernels: python scripts/ncu_misc.py bn|lovasz|optim|stem|stats1x1|depthwise"""
+"""Driver for ncu captures of single kernels: python scripts/ncu_misc.py bn|lovasz|optim|stem|stemwgrad|stats1x1|depthwise"""
 import os
 import sys
 
@@ -40,6 +40,12 @@ elif kind == "stem":
     wp = O.conv_stem_weight_prep(w, 3, 3)
     for _ in range(3):
         O.conv_stem_fprop(planes, wp, (224, 224), 64, 7, 7, 3, 3, (112, 112), True)
+elif kind == "stemwgrad":
+    x = torch.randn(256, 224, 224, 3, device="cuda").bfloat16()
+    dy = torch.randn(256, 112, 112, 64, device="cuda").bfloat16()
+    planes = O.conv_stem_pack(x)
+    for _ in range(3):
+        O.conv_stem_wgrad(planes, dy, (224, 224), 3, 7, 7, 3, 3)
 elif kind == "stats1x1":
     x = torch.randn(256, 56, 56, 64, device="cuda").bfloat16()
     w = (torch.randn(256, 1, 64, device="cuda") / 8).bfloat16()

@@ -74,6 +74,35 @@ def conv2d_fprop(x: torch.Tensor, w: torch.Tensor, *, R: int, S: int, stride: in
     return y
 
 
+def conv2d_dgrad_bnstats(dy: torch.Tensor, w: torch.Tensor, *, R: int, S: int, dil: int = 1, pad_h: int = 0,
+                         pad_w: int = 0, out_hw, bn_x: torch.Tensor, bn_mean: torch.Tensor, bn_invstd: torch.Tensor,
+                         residual: Optional[torch.Tensor] = None, out_mask: Optional[torch.Tensor] = None):
+    """Stride-1 data gradient dx = conv(dy, w) (+ residual) (* mask) that also reduces, in its epilogue, the sums
+    BatchNorm backward needs for the BatchNorm that produced this tensor (``bn_x`` = that BatchNorm's input).
+    Returns (dx, partials [nparts, 2, K]) with partials = per-CTA (sum dz, sum dz * xhat)."""
+    _chk_bf16_nhwc(dy, "dy")
+    _chk_bf16_nhwc(w, "w")
+    n, h, wd, c = dy.shape
+    k = w.shape[0]
+    p, q = out_hw
+    assert w.numel() == k * R * S * c and bn_x.is_contiguous() and bn_x.numel() == n * p * q * k
+    assert bn_x.dtype == torch.bfloat16 and bn_mean.dtype == torch.float32 and bn_invstd.dtype == torch.float32
+    dx = torch.empty((n, p, q, k), dtype=torch.bfloat16, device=dy.device)
+    if residual is not None:
+        _chk_bf16_nhwc(residual, "residual")
+        assert residual.shape == dx.shape
+    if out_mask is not None:
+        assert out_mask.dtype == torch.uint8 and out_mask.numel() == n * p * q * (k // 8) and k % 32 == 0
+    partials = torch.empty((int(N.lib().tdl_num_sms()), 2, k), dtype=torch.float32, device=dy.device)
+    nparts = ctypes.c_int(0)
+    rc = N.lib().tdl_conv2d_dgrad_bnstats_bf16(N.ptr(dy), N.ptr(w), N.ptr(dx), N.ptr(residual), N.ptr(out_mask),
+                                               N.ptr(bn_x), N.ptr(bn_mean), N.ptr(bn_invstd), _i(n), _i(h), _i(wd),
+                                               _i(c), _i(k), _i(R), _i(S), _i(dil), _i(pad_h), _i(pad_w), _i(p), _i(q),
+                                               N.ptr(partials), ctypes.byref(nparts), N.stream_ptr())
+    N.check(rc, "tdl_conv2d_dgrad_bnstats_bf16")
+    return dx, partials[:int(nparts.value)]
+
+
 def conv2d_fprop_stats(x: torch.Tensor, w: torch.Tensor, *, R: int, S: int, stride: int = 1, dil: int = 1,
                        pad_h: int = 0, pad_w: int = 0, out_hw=None, bias: Optional[torch.Tensor] = None):
     """Convolution + per-CTA partial BatchNorm statistics of its (bf16) output in the same kernel.
@@ -219,18 +248,21 @@ def bn_apply(x2d, scale, shift, residual2d, relu: bool, want_mask: bool = False)
 
 
 def bn_bwd(dz2d, x2d, z2d, scale, shift, mean, invstd, relu: bool, want_dres: bool,
-           acc_dgamma=None, acc_dbeta=None):
-    """Returns (dx, dres_or_None, dgamma, dbeta)."""
+           acc_dgamma=None, acc_dbeta=None, partials=None):
+    """Returns (dx, dres_or_None, dgamma, dbeta).  ``partials`` ([nparts, 2, C], from ``conv2d_dgrad_bnstats``):
+    the reduction over (dz, x) has already been done by the kernel that produced dz."""
     rows, C = x2d.shape
     dev = x2d.device
-    scratch = _bn_scratch(rows, C, dev)
     dgb = torch.empty((2, C), dtype=torch.float32, device=dev)
     zbits = int(z2d is not None and z2d.dtype == torch.uint8)  # the 1-bit ReLU mask written by bn_apply
-    rc = N.lib().tdl_bn_bwd_reduce(N.ptr(dz2d), N.ptr(x2d), N.ptr(z2d), _i(zbits), N.ptr(scale), N.ptr(shift),
-                                   N.ptr(mean), N.ptr(invstd), _i64(rows), _i(C), _i(int(relu)), N.ptr(scratch),
-                                   _i64(scratch.numel()), N.ptr(dgb[0]), N.ptr(dgb[1]), N.ptr(acc_dgamma),
-                                   N.ptr(acc_dbeta), N.stream_ptr())
-    N.check(rc, "tdl_bn_bwd_reduce")
+    if partials is not None:
+        assert partials.dtype == torch.float32 and partials.shape[1:] == (2, C) and partials.is_contiguous()
+        rc = N.lib().tdl_bn_bwd_finalize_partials(N.ptr(partials), _i(partials.shape[0]), _i(C), N.ptr(dgb[0]),
+                                                  N.ptr(dgb[1]), N.ptr(acc_dgamma), N.ptr(acc_dbeta), N.stream_ptr())
+        N.check(rc, "tdl_bn_bwd_finalize_partials")
+    else:
+        rc = _bn_bwd_reduce(dz2d, x2d, z2d, zbits, scale, shift, mean, invstd, rows, C, relu, dgb, acc_dgamma,
+                            acc_dbeta)
     dx = torch.empty_like(x2d)
     dres = torch.empty_like(x2d) if want_dres else None
     rc = N.lib().tdl_bn_bwd_apply(N.ptr(dz2d), N.ptr(x2d), N.ptr(z2d), _i(zbits), N.ptr(scale), N.ptr(shift),
@@ -238,6 +270,16 @@ def bn_bwd(dz2d, x2d, z2d, scale, shift, mean, invstd, relu: bool, want_dres: bo
                                   _i(C), _i(int(relu)), N.stream_ptr())
     N.check(rc, "tdl_bn_bwd_apply")
     return dx, dres, dgb[0], dgb[1]
+
+
+def _bn_bwd_reduce(dz2d, x2d, z2d, zbits, scale, shift, mean, invstd, rows, C, relu, dgb, acc_dgamma, acc_dbeta):
+    scratch = _bn_scratch(rows, C, x2d.device)
+    rc = N.lib().tdl_bn_bwd_reduce(N.ptr(dz2d), N.ptr(x2d), N.ptr(z2d), _i(zbits), N.ptr(scale), N.ptr(shift),
+                                   N.ptr(mean), N.ptr(invstd), _i64(rows), _i(C), _i(int(relu)), N.ptr(scratch),
+                                   _i64(scratch.numel()), N.ptr(dgb[0]), N.ptr(dgb[1]), N.ptr(acc_dgamma),
+                                   N.ptr(acc_dbeta), N.stream_ptr())
+    N.check(rc, "tdl_bn_bwd_reduce")
+    return rc
 
 
 # --------------------------------------------------------------------------------------------

@@ -175,6 +175,38 @@ def test_conv_residual_on_tensor_core_with_relu_mask(O):
     assert bool(((y == 0) | keep.view(N_, H, H, K)).all())
 
 
+@pytest.mark.parametrize("case", [(3, 14, 64, 256, 1, True, True), (2, 20, 64, 64, 3, False, True),
+                                  (2, 12, 128, 128, 1, False, False), (2, 9, 32, 96, 3, True, True),
+                                  (4, 28, 256, 512, 1, True, True)])
+def test_conv_dgrad_with_fused_bn_backward_sums(O, case):
+    """Data gradient whose epilogue also reduces (sum dz, sum dz * xhat) for the BatchNorm that produced the tensor."""
+    N_, H, C, K, R, use_res, use_mask = case
+    torch.manual_seed(9)
+    dy = torch.randn(N_, H, H, C, device="cuda").bfloat16()
+    w = (torch.randn(K, R * R, C, device="cuda") / math.sqrt(R * R * C)).bfloat16()
+    bn_x = (torch.randn(N_, H, H, K, device="cuda") * 2 + 0.5).bfloat16()
+    mean = torch.randn(K, device="cuda") * 0.3 + 0.5
+    invstd = torch.rand(K, device="cuda") + 0.5
+    res = torch.randn(N_, H, H, K, device="cuda").bfloat16() if use_res else None
+    keep = torch.rand(N_ * H * H, K, device="cuda") > 0.45
+    mask = None
+    if use_mask:
+        mask = (keep.view(-1, K // 8, 8).to(torch.uint8) << torch.arange(8, device="cuda", dtype=torch.uint8)).sum(-1).to(torch.uint8).contiguous()
+    pad = (R - 1) // 2
+    dx, partials = O.conv2d_dgrad_bnstats(dy, w, R=R, S=R, pad_h=pad, pad_w=pad, out_hw=(H, H), bn_x=bn_x, bn_mean=mean,
+                                          bn_invstd=invstd, residual=res, out_mask=mask)
+    ref = _ref_conv(dy, w, R, R, 1, 1, (pad, pad, pad, pad))
+    if use_res:
+        ref = ref + res.float()
+    if use_mask:
+        ref = ref * keep.view(N_, H, H, K)
+    assert rel_err(dx, ref) < 1e-2
+    dz = dx.float().reshape(-1, K)
+    xhat = (bn_x.float().reshape(-1, K) - mean) * invstd
+    assert rel_err(partials[:, 0].sum(0), dz.sum(0)) < 2e-3
+    assert rel_err(partials[:, 1].sum(0), (dz * xhat).sum(0)) < 2e-3
+
+
 def test_conv_fused_residual_relu_forward_and_gradients():
     """relu(conv(x) + b + shortcut) in one epilogue (reference bottleneck tail, core/resnet.py:148-150) against fp32."""
     from tensorflowdistributedlearning_b200.ops import functional as Fn
