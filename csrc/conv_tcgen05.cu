@@ -100,6 +100,8 @@ struct Geometry {
   const void* bn_x;
   const float* bn_mean;
   const float* bn_invstd;
+  const float* bn_scale;  // non-null: the BatchNorm ends in a ReLU whose mask is recomputed as x * scale + shift > 0
+  const float* bn_shift;  //           (the stored gradient stays unmasked; only the sums see the mask)
   int res_mma;  // residual tile added on the tensor core (extra K iterations against an identity block)
   // halo mode (stride-1 RxS > 1x1): the haloed input patch of a K block is loaded ONCE and every tap reads it at a row
   // shift instead of re-fetching a shifted copy per tap (the tap-shifted form is bound by L2->smem bandwidth there)
@@ -150,7 +152,7 @@ constexpr int kThreads = 192;                     // wgrad: 6 warps
 constexpr int kFpropThreads = 320;                // fprop: TMA warp, MMA warp, 2 x 4 epilogue warps
 constexpr int kEpiWarp0 = 2;
 
-template <int BLOCK_N>
+template <int BLOCK_N, bool kBwd = false>
 struct FpropCfg {
   static constexpr int kBBytes = BLOCK_N * kBlockK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
@@ -160,12 +162,15 @@ struct FpropCfg {
   static constexpr int kTmemCols = kAccBufs * BLOCK_N;
   static constexpr int kOutBufs = 2;             // 128-row x 64-channel bf16 staging tile per epilogue group
   static constexpr int kOutBytes = kOutBufs * kBlockM * 128;
+  // kBwd (BatchNorm-backward sums in the epilogue): one more 128-row x 64-channel tile per epilogue group, the
+  // BatchNorm input at the output tile's position, prefetched by TMA while the accumulator is drained
+  static constexpr int kXBytes = kBwd ? kOutBufs * kBlockM * 128 : 0;
   static constexpr int kStatBytes = 4 * 2 * 64 * 4;  // per-warp (sum, sumsq) partials of one 64-channel chunk
   static constexpr int kBarBytes = 256;    // (2*kStages + 4) mbarriers + the TMEM slot
   static constexpr int kAlignSlack = 384;  // the dynamic smem window is 1 KB aligned in practice; checked at run time
-  static constexpr int kStages = (227 * 1024 - kOutBytes - kStatBytes - kAlignSlack - kBarBytes) / kStageBytes;
-  static constexpr int kSmemBytes = kStages * kStageBytes + kOutBytes + kStatBytes + kAlignSlack + kBarBytes;
-  static_assert((2 * kStages + 2 * kAccBufs + 1 + 4) * 8 + 4 <= kBarBytes, "barrier region too small");
+  static constexpr int kStages = (227 * 1024 - kOutBytes - kXBytes - kStatBytes - kAlignSlack - kBarBytes) / kStageBytes;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kOutBytes + kXBytes + kStatBytes + kAlignSlack + kBarBytes;
+  static_assert((2 * kStages + 2 * kAccBufs + 1 + 4 + 2) * 8 + 4 <= kBarBytes, "barrier region too small");
 };
 
 // kFused: bias / residual / ReLU present in the epilogue.  kStats: per-channel (sum, sum of squares) of the bf16
@@ -190,9 +195,10 @@ template <int BLOCK_N, bool kFused, bool kStats, bool kStem = false, bool kResMm
 __global__ void __launch_bounds__(kFpropThreads, 1)
 conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
                   const __grid_constant__ CUtensorMap tm_y, const __grid_constant__ CUtensorMap tm_res,
-                  const __grid_constant__ CUtensorMap tm_id, const Geometry g, const float* __restrict__ bias,
-                  const bf16* __restrict__ residual, float* __restrict__ stats) {
-  using Cfg = FpropCfg<BLOCK_N>;
+                  const __grid_constant__ CUtensorMap tm_id, const __grid_constant__ CUtensorMap tm_bx,
+                  const Geometry g, const float* __restrict__ bias, const bf16* __restrict__ residual,
+                  float* __restrict__ stats) {
+  using Cfg = FpropCfg<BLOCK_N, kBwdStats>;
   constexpr int kStages = Cfg::kStages;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -203,8 +209,9 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + kStages * kABytes;
   uint8_t* smem_out = smem + kStages * Cfg::kStageBytes;
-  float* smem_stat = reinterpret_cast<float*>(smem_out + Cfg::kOutBytes);  // [4 warps][2][64]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_out + Cfg::kOutBytes + Cfg::kStatBytes);
+  uint8_t* smem_x = smem_out + Cfg::kOutBytes;  // kBwdStats: BatchNorm-input tile per epilogue group
+  float* smem_stat = reinterpret_cast<float*>(smem_x + Cfg::kXBytes);  // [4 warps][2][64]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_x + Cfg::kXBytes + Cfg::kStatBytes);
   uint64_t* full_bar = bars;
   uint64_t* empty_bar = bars + kStages;
   uint64_t* tmem_full = bars + 2 * kStages;
@@ -213,7 +220,8 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
   uint64_t* w_bar = tmem_empty + kAcc;  // stem mode: resident weights have landed
   uint64_t* patch_full = w_bar + 1;     // halo mode: two input-patch buffers
   uint64_t* patch_empty = patch_full + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(patch_empty + 2);
+  uint64_t* x_bar = patch_empty + 2;    // kBwdStats: the group's BatchNorm-input tile has landed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(x_bar + 2);
   uint8_t* smem_bh = smem + 2 * g.halo_pbytes;  // halo mode: weight-tile ring behind the two patch buffers
 
   const int warp = threadIdx.x >> 5;
@@ -233,6 +241,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
       ptx::prefetch_tmap(&tm_res);
       ptx::prefetch_tmap(&tm_id);
     }
+    if constexpr (kBwdStats) ptx::prefetch_tmap(&tm_bx);
   }
   if (warp == 1) {
     if (lane == 0) {
@@ -248,6 +257,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
       for (int i = 0; i < 2; ++i) {
         ptx::mbar_init(&patch_full[i], 1);
         ptx::mbar_init(&patch_empty[i], 1);
+        ptx::mbar_init(&x_bar[i], 1);
       }
       ptx::fence_mbar_init();
     }
@@ -523,6 +533,8 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
     const uint32_t sw = (uint32_t)(row & 7);
     const uint32_t tmem_lane = tmem_base + ((uint32_t)(quarter * 32) << 16);
     uint8_t* out_tile = smem_out + group * (kBlockM * 128);
+    uint8_t* x_tile = smem_x + group * (kBlockM * 128);
+    uint32_t x_phase = 0;
     // ---- fused BatchNorm statistics (kStats) ----
     // The bf16 tile staged for the TMA store doubles as the transpose: after the store is issued every thread reads
     // ONE channel pair (4 bytes) of its warp's 32 rows back from shared memory -- a warp reads a whole 128-byte row
@@ -533,9 +545,8 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
     // tile, which made the stats variant 2.8x slower than the plain kernel on output-heavy layers.)
     constexpr int kChunks = BLOCK_N / 64;
     float sacc[kChunks][4];
-    float mu[kChunks][2];  // kBwdStats: batch means of this thread's two channels per 64-channel chunk
 #pragma unroll
-    for (int c = 0; c < kChunks; ++c) sacc[c][0] = sacc[c][1] = sacc[c][2] = sacc[c][3] = mu[c][0] = mu[c][1] = 0.f;
+    for (int c = 0; c < kChunks; ++c) sacc[c][0] = sacc[c][1] = sacc[c][2] = sacc[c][3] = 0.f;
     int stat_n_tile = -1;
     auto flush_stats = [&](int nt) {
       if (issuer) ptx::tma_store_wait_read<0>();  // nobody is reading the staging buffer any more
@@ -589,14 +600,6 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
         if (n_tile != stat_n_tile) {
           if (stat_n_tile >= 0) flush_stats(stat_n_tile);
           stat_n_tile = n_tile;
-          if constexpr (kBwdStats) {
-#pragma unroll
-            for (int c = 0; c < kChunks; ++c) {
-              const int ch = n_tile * BLOCK_N + c * 64 + (lane >> 2) * 8 + (lane & 3) * 2;
-              mu[c][0] = ch < g.K ? g.bn_mean[ch] : 0.f;
-              mu[c][1] = ch < g.K ? g.bn_mean[ch + 1] : 0.f;
-            }
-          }
         }
         vm = __ballot_sync(0xffffffffu, valid);
       }
@@ -608,6 +611,14 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
         const int co_chunk = n_tile * BLOCK_N + cc * 64;
         if (issuer) ptx::tma_store_wait_read<0>();  // the previous store of this group has drained the buffer
         ptx::named_bar_sync(bar_id, 128);
+        if constexpr (kBwdStats) {
+          // every thread of the group is past the previous chunk's read-back: fetch the BatchNorm input at this
+          // chunk's position now, it lands while the accumulator is drained, converted and stored
+          if (issuer) {
+            ptx::mbar_expect_tx(&x_bar[group], a_tx);
+            ptx::tma_load_4d(x_tile, &tm_bx, &x_bar[group], co_chunk, tw_i * g.TW, th_i * g.TH, tn_i * g.TN);
+          }
+        }
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
           uint32_t v[32];
@@ -677,32 +688,47 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
         }
         if constexpr (kBwdStats) {
           // BatchNorm-backward reductions of the gradient as stored (masked, bf16): per channel sum(dz) and
-          // sum(dz * (x - mean)), x = the BatchNorm's input at the same pixel, fetched here one 128-byte row per warp
-          // instruction.  Replaces the separate reduction pass over (dz, x) (tdl_bn_bwd_reduce).
-          const uint8_t* rows = out_tile + (uint32_t)(quarter * 32) * 128u + ((uint32_t)(lane & 3) << 2);
+          // sum(dz * (x - mean)), x = the BatchNorm's input at the same pixels (the TMA tile fetched at chunk start,
+          // same swizzled layout as the staged tile).  Replaces the separate pass over (dz, x) (tdl_bn_bwd_reduce).
+          const uint32_t roff = (uint32_t)(quarter * 32) * 128u + ((uint32_t)(lane & 3) << 2);
+          const uint8_t* rows = out_tile + roff;
+          const uint8_t* xrows = x_tile + roff;
           const uint32_t c16 = (uint32_t)(lane >> 2);
-          const int ch0 = co_chunk + (int)c16 * 8 + (lane & 3) * 2;
-          const bf16* xcol = reinterpret_cast<const bf16*>(g.bn_x) + ch0;
-          const bool ch_ok = ch0 < g.K;
-          const uint32_t pix32 = (uint32_t)pix;
-          uint32_t xv[32];
-#pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            const uint32_t pi = __shfl_sync(0xffffffffu, pix32, i);
-            xv[i] = (ch_ok && ((vm >> i) & 1u)) ? __ldg(reinterpret_cast<const uint32_t*>(xcol + (size_t)pi * g.K)) : 0u;
+          // per-channel constants of this thread's two channels: fetched per chunk (L1 hits) rather than held in
+          // registers for the whole kernel -- the epilogue is at the register ceiling of a 320-thread CTA
+          const int ch0 = co_chunk + 2 * lane;
+          const bool relu_rc = g.bn_scale != nullptr;
+          float m0 = 0.f, m1 = 0.f, a0 = 0.f, b0 = 0.f, a1 = 0.f, b1 = 0.f;
+          if (ch0 < g.K) {
+            const float2 mm = __ldg(reinterpret_cast<const float2*>(g.bn_mean + ch0));
+            m0 = mm.x;
+            m1 = mm.y;
+            if (relu_rc) {
+              const float2 aa = __ldg(reinterpret_cast<const float2*>(g.bn_scale + ch0));
+              const float2 bb = __ldg(reinterpret_cast<const float2*>(g.bn_shift + ch0));
+              a0 = aa.x; a1 = aa.y; b0 = bb.x; b1 = bb.y;
+            }
           }
+          ptx::mbar_wait(&x_bar[group], x_phase);
+          x_phase ^= 1u;
           float s0 = 0.f, q0 = 0.f, s1 = 0.f, q1 = 0.f;
-          const float m0 = mu[cc][0], m1 = mu[cc][1];
-#pragma unroll
+#pragma unroll 8
           for (int i = 0; i < 32; ++i) {
-            const uint32_t wv = *reinterpret_cast<const uint32_t*>(rows + i * 128 + ((c16 ^ (uint32_t)(i & 7)) << 4));
+            const uint32_t so = (uint32_t)i * 128u + ((c16 ^ (uint32_t)(i & 7)) << 4);
+            const uint32_t wv = *reinterpret_cast<const uint32_t*>(rows + so);
             const bool ok = (vm >> i) & 1u;
-            const float f0 = ok ? __uint_as_float(wv << 16) : 0.f;
-            const float f1 = ok ? __uint_as_float(wv & 0xffff0000u) : 0.f;
+            // rows past the patch are never written by the TMA load: whatever shared memory held must not reach the sums
+            const uint32_t xw = ok ? *reinterpret_cast<const uint32_t*>(xrows + so) : 0u;
+            const float x0 = __uint_as_float(xw << 16), x1 = __uint_as_float(xw & 0xffff0000u);
+            // recomputed mask: fmaf(x, scale, shift) > 0, the same expression bn_apply evaluated in the forward pass
+            const bool k0 = ok && (!relu_rc || fmaf(x0, a0, b0) > 0.f);
+            const bool k1 = ok && (!relu_rc || fmaf(x1, a1, b1) > 0.f);
+            const float f0 = k0 ? __uint_as_float(wv << 16) : 0.f;
+            const float f1 = k1 ? __uint_as_float(wv & 0xffff0000u) : 0.f;
             s0 += f0;
-            q0 = fmaf(f0, __uint_as_float(xv[i] << 16) - m0, q0);
+            q0 = fmaf(f0, x0 - m0, q0);
             s1 += f1;
-            q1 = fmaf(f1, __uint_as_float(xv[i] & 0xffff0000u) - m1, q1);
+            q1 = fmaf(f1, x1 - m1, q1);
           }
           sacc[cc][0] += s0;
           sacc[cc][1] += q0;
@@ -1061,7 +1087,7 @@ static int launch_stem(const CUtensorMap& tx, const CUtensorMap& tw, const CUten
   const int total = g.tiles_n * g.tiles_h * g.tiles_w;
   const int grid = total < tdl::num_sms() ? total : tdl::num_sms();
   if (nparts) *nparts = grid;
-  conv_fprop_kernel<64, false, kStats, true><<<grid, kFpropThreads, Cfg::kSmemBytes, st>>>(tx, tw, ty, ty, ty, g, nullptr,
+  conv_fprop_kernel<64, false, kStats, true><<<grid, kFpropThreads, Cfg::kSmemBytes, st>>>(tx, tw, ty, ty, ty, ty, g, nullptr,
                                                                                            nullptr, stats);
   TDL_LAUNCH_OK("conv_fprop_kernel(stem)");
   return 0;
@@ -1253,9 +1279,9 @@ __global__ void stem_wgrad_unpack_kernel(const float* __restrict__ dwp, float* _
 template <int BLOCK_N, bool kFused, bool kStats, bool kResMma = false, bool kBwdStats = false>
 static int launch_fprop_t(
 const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& ty, const CUtensorMap& tres,
-                          const CUtensorMap& tid, const Geometry& g, const float* bias, const bf16* res, float* stats,
+                          const CUtensorMap& tid, const CUtensorMap& tbx, const Geometry& g, const float* bias, const bf16* res, float* stats,
                           int* nparts, cudaStream_t st) {
-  using Cfg = FpropCfg<BLOCK_N>;
+  using Cfg = FpropCfg<BLOCK_N, kBwdStats>;
   static bool attr_set = false;
   if (!attr_set) {
     TDL_CUDA_OK(cudaFuncSetAttribute(conv_fprop_kernel<BLOCK_N, kFused, kStats, false, kResMma, kBwdStats>,
@@ -1266,28 +1292,28 @@ const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& ty, const CUten
   const int grid = total < tdl::num_sms() ? total : tdl::num_sms();
   if (nparts) *nparts = grid;
   conv_fprop_kernel<BLOCK_N, kFused, kStats, false, kResMma, kBwdStats><<<grid, kFpropThreads, Cfg::kSmemBytes, st>>>(
-      tx, tw, ty, tres, tid, g, bias, res, stats);
+      tx, tw, ty, tres, tid, tbx, g, bias, res, stats);
   TDL_LAUNCH_OK("conv_fprop_kernel");
   return 0;
 }
 
 template <int BLOCK_N>
 static int launch_fprop(const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& ty, const CUtensorMap& tres,
-                        const CUtensorMap& tid, const Geometry& g, const float* bias, const bf16* res, float* stats,
+                        const CUtensorMap& tid, const CUtensorMap& tbx, const Geometry& g, const float* bias, const bf16* res, float* stats,
                         int* nparts, cudaStream_t st) {
   if (g.bn_x) {  // data gradient that also reduces the BatchNorm-backward sums of the tensor it produces
     if (g.res_mma)
-      return launch_fprop_t<BLOCK_N, false, false, true, true>(tx, tw, ty, tres, tid, g, bias, res, stats, nparts, st);
-    return launch_fprop_t<BLOCK_N, false, false, false, true>(tx, tw, ty, tres, tid, g, bias, res, stats, nparts, st);
+      return launch_fprop_t<BLOCK_N, false, false, true, true>(tx, tw, ty, tres, tid, tbx, g, bias, res, stats, nparts, st);
+    return launch_fprop_t<BLOCK_N, false, false, false, true>(tx, tw, ty, tres, tid, tbx, g, bias, res, stats, nparts, st);
   }
-  if (g.res_mma) return launch_fprop_t<BLOCK_N, false, false, true>(tx, tw, ty, tres, tid, g, bias, res, stats, nparts, st);
+  if (g.res_mma) return launch_fprop_t<BLOCK_N, false, false, true>(tx, tw, ty, tres, tid, tbx, g, bias, res, stats, nparts, st);
   const bool fused = g.has_bias || g.has_res || g.relu;
   if (stats) {
-    if (fused) return launch_fprop_t<BLOCK_N, true, true>(tx, tw, ty, tres, tid, g, bias, res, stats, nparts, st);
-    return launch_fprop_t<BLOCK_N, false, true>(tx, tw, ty, tres, tid, g, bias, res, stats, nparts, st);
+    if (fused) return launch_fprop_t<BLOCK_N, true, true>(tx, tw, ty, tres, tid, tbx, g, bias, res, stats, nparts, st);
+    return launch_fprop_t<BLOCK_N, false, true>(tx, tw, ty, tres, tid, tbx, g, bias, res, stats, nparts, st);
   }
-  if (fused) return launch_fprop_t<BLOCK_N, true, false>(tx, tw, ty, tres, tid, g, bias, res, stats, nparts, st);
-  return launch_fprop_t<BLOCK_N, false, false>(tx, tw, ty, tres, tid, g, bias, res, stats, nparts, st);
+  if (fused) return launch_fprop_t<BLOCK_N, true, false>(tx, tw, ty, tres, tid, tbx, g, bias, res, stats, nparts, st);
+  return launch_fprop_t<BLOCK_N, false, false>(tx, tw, ty, tres, tid, tbx, g, bias, res, stats, nparts, st);
 }
 
 // 64x64 bf16 identity block in global memory (the B operand of the residual-on-the-tensor-core iterations)
@@ -1357,6 +1383,8 @@ struct BnBwd {
   const void* x;
   const float* mean;
   const float* invstd;
+  const float* scale;  // both null, or both set = "recompute the ReLU mask from x for the sums"
+  const float* shift;
 };
 
 static int g_halo_mode = -1;  // -1 = read TDL_HALO on first use, 0 = off (default), 1 = on, 2 = on with base offsets
@@ -1429,7 +1457,9 @@ static int fprop_impl(const void* x, const void* w, void* y, const float* bias, 
                 "BatchNorm-backward sums: plain stride-1 data gradient only");
     TDL_REQUIRE(bnb->x && bnb->mean && bnb->invstd, "BatchNorm tensors required");
     TDL_REQUIRE((int64_t)N * P * Q < ((int64_t)1 << 31), "pixel index exceeds 32 bits");
-    g.bn_x = bnb->x; g.bn_mean = bnb->mean; g.bn_invstd = bnb->invstd;
+    TDL_REQUIRE((bnb->scale == nullptr) == (bnb->shift == nullptr), "scale and shift come together");
+    TDL_REQUIRE(!(bnb->scale && out_mask), "either a stored mask or a recomputed one");
+    g.bn_x = bnb->x; g.bn_mean = bnb->mean; g.bn_invstd = bnb->invstd; g.bn_scale = bnb->scale; g.bn_shift = bnb->shift;
   }
   if (out_mask) {
     TDL_REQUIRE(g.res_mma || bnb, "the output mask needs a plain residual or the BatchNorm-backward sums");
@@ -1494,9 +1524,18 @@ static int fprop_impl(const void* x, const void* w, void* y, const float* bias, 
   }
   // in res_mma mode the residual arrives through its tensor map; the pointer slot carries the optional output mask
   const bf16* aux = (g.res_mma || bnb) ? (const bf16*)out_mask : (const bf16*)residual;
-  if (block_n == 256) return launch_fprop<256>(tx, tw, ty, tres, tid, g, bias, aux, stats, nparts, st);
-  if (block_n == 128) return launch_fprop<128>(tx, tw, ty, tres, tid, g, bias, aux, stats, nparts, st);
-  return launch_fprop<64>(tx, tw, ty, tres, tid, g, bias, aux, stats, nparts, st);
+  CUtensorMap tbx = ty;
+  if (bnb) {  // the BatchNorm input, tiled exactly like the output
+    TDL_REQUIRE((reinterpret_cast<uintptr_t>(bnb->x) & 15) == 0, "bn_x must be 16-byte aligned");
+    uint64_t dims[4] = {(uint64_t)K, (uint64_t)g.Q, (uint64_t)g.P, (uint64_t)g.N};
+    uint32_t box[4] = {64, (uint32_t)g.TW, (uint32_t)g.TH, (uint32_t)g.TN};
+    uint32_t es[4] = {1, 1, 1, 1};
+    int rc = encode_bf16(&tbx, bnb->x, 4, dims, box, es);
+    if (rc) return rc;
+  }
+  if (block_n == 256) return launch_fprop<256>(tx, tw, ty, tres, tid, tbx, g, bias, aux, stats, nparts, st);
+  if (block_n == 128) return launch_fprop<128>(tx, tw, ty, tres, tid, tbx, g, bias, aux, stats, nparts, st);
+  return launch_fprop<64>(tx, tw, ty, tres, tid, tbx, g, bias, aux, stats, nparts, st);
 }
 
 // y[N,P,Q,K] = conv(x[N,H,W,C], w[K,R*S,C]) (+bias) (+residual) (ReLU)      bf16 in/out, fp32 accumulate
@@ -1522,13 +1561,15 @@ TDL_API int tdl_conv2d_fprop_res_mask_bf16(const void* x, const void* w, void* y
 // Data gradient (a stride-1 convolution of dy with the flipped weights) that ALSO reduces, for the BatchNorm whose
 // output gradient it produces, the per-channel sums BatchNorm backward needs: stats_partial [tdl_num_sms()][2][K]
 // = per-CTA (sum dz, sum dz * xhat) with dz the stored (optionally masked / residual-added) output and
-// xhat = (bn_x - mean) * invstd.  Feed to tdl_bn_bwd_finalize_partials; tdl_bn_bwd_reduce's pass over (dz, x) is gone.
+// xhat = (bn_x - mean) * invstd.  bn_scale / bn_shift (optional, not with out_mask): the BatchNorm ends in a ReLU
+// whose mask fmaf(x, scale, shift) > 0 is applied to the SUMS only (the stored gradient stays unmasked, as
+// tdl_bn_bwd_apply re-derives the same mask).  Feed to tdl_bn_bwd_finalize_partials; tdl_bn_bwd_reduce's pass over (dz, x) is gone.
 TDL_API int tdl_conv2d_dgrad_bnstats_bf16(const void* x, const void* w, void* y, const void* residual,
                                           const void* out_mask, const void* bn_x, const float* bn_mean,
-                                          const float* bn_invstd, int N, int H, int W, int C, int K, int R, int S,
+                                          const float* bn_invstd, const float* bn_scale, const float* bn_shift, int N, int H, int W, int C, int K, int R, int S,
                                           int dil, int pad_h, int pad_w, int P, int Q, float* stats_partial,
                                           int* nparts_host, void* stream) {
-  BnBwd b = {bn_x, bn_mean, bn_invstd};
+  BnBwd b = {bn_x, bn_mean, bn_invstd, bn_scale, bn_shift};
   return fprop_impl(x, w, y, nullptr, residual, N, H, W, C, K, R, S, 1, dil, pad_h, pad_w, P, Q, 0, nullptr,
                     stats_partial, nparts_host, stream, out_mask, &b);
 }

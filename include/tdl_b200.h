@@ -135,10 +135,11 @@ int tdl_conv_stem_wgrad(const void* planes, const void* dy, float* dwp_scratch, 
                         void* stream);
 /* Stride-1 data gradient that also reduces the BatchNorm-backward sums (sum dz, sum dz * xhat) of the tensor it
  * produces, in its epilogue; residual / out_mask optional (as tdl_conv2d_fprop_res_mask_bf16).  stats_partial is
- * [tdl_num_sms()][2][K]; feed it to tdl_bn_bwd_finalize_partials. */
+ * [tdl_num_sms()][2][K]; feed it to tdl_bn_bwd_finalize_partials.  bn_scale / bn_shift (optional, not together with
+ * out_mask): the sums see the ReLU mask fmaf(x, scale, shift) > 0, the stored gradient stays unmasked. */
 int tdl_conv2d_dgrad_bnstats_bf16(const void* x, const void* w, void* y, const void* residual, const void* out_mask,
-                                  const void* bn_x, const float* bn_mean, const float* bn_invstd, int N, int H, int W,
-                                  int C, int K, int R, int S, int dil, int pad_h, int pad_w, int P, int Q,
+                                  const void* bn_x, const float* bn_mean, const float* bn_invstd, const float* bn_scale,
+                                  const float* bn_shift, int N, int H, int W, int C, int K, int R, int S, int dil, int pad_h, int pad_w, int P, int Q,
                                   float* stats_partial, int* nparts_host, void* stream);
 /* Convolution with 1..4 output channels (decoder 3x3 -> 1 logit).  CUDA-core dot products; weight is the
  * fp32 master [K,R,S,C]; stride 1; dw / dbias are accumulated into. */

@@ -46,6 +46,17 @@ elif kind == "stemwgrad":
     planes = O.conv_stem_pack(x)
     for _ in range(3):
         O.conv_stem_wgrad(planes, dy, (224, 224), 3, 7, 7, 3, 3)
+elif kind == "bnfuse":
+    # data gradient 64 -> 256 @56x56 with residual + mask AND the fused BatchNorm-backward sums (kBwdStats)
+    dy = torch.randn(256, 56, 56, 64, device="cuda").bfloat16()
+    wd = (torch.randn(256, 1, 64, device="cuda") / 8).bfloat16()
+    res = torch.randn(256, 56, 56, 256, device="cuda").bfloat16()
+    bx = torch.randn(256, 56, 56, 256, device="cuda").bfloat16()
+    mean, invstd = torch.randn(256, device="cuda"), torch.rand(256, device="cuda") + 0.5
+    mask = torch.randint(0, 256, (256 * 56 * 56, 32), dtype=torch.uint8, device="cuda")
+    for _ in range(3):
+        O.conv2d_dgrad_bnstats(dy, wd, R=1, S=1, out_hw=(56, 56), bn_x=bx, bn_mean=mean, bn_invstd=invstd,
+                               residual=res, out_mask=mask)
 elif kind == "stats1x1":
     x = torch.randn(256, 56, 56, 64, device="cuda").bfloat16()
     w = (torch.randn(256, 1, 64, device="cuda") / 8).bfloat16()

@@ -8,6 +8,7 @@ plain-torch restatement in ``ops.reference``.  On a GPU the native library is ma
 """
 from __future__ import annotations
 
+import os
 from typing import Optional, Tuple
 
 import torch
@@ -20,11 +21,33 @@ from . import reference as R
 # which then skips its own masking and returns the gradient itself for the residual input.
 _PREMASKED = {}
 _LAST_RELU_MASK = None
+# BatchNorm -> consumer convolution hand-off for the fused backward reductions: the BatchNorm's output tensor carries
+# ``_tdl_bn_src`` (its input, batch statistics, affine, mask); the consumer's data-gradient kernel reduces
+# (sum dz, sum dz * xhat) in its epilogue and leaves them here, keyed by the gradient's address and guarded by the
+# tensor's version counter (autograd accumulating another consumer's gradient in place bumps it) and by the
+# BatchNorm input's address.
+_BN_PARTIALS = {}
+_LAST_BN_SRC = None
+_FUSE_BN_BWD = os.environ.get("TDL_FUSE_BN_BWD", "0") == "1"  # measured slower on B200: off by default
+
+
+_FUSED_BN_HITS = 0
+
+
+def enable_fused_bn_backward(flag: bool) -> None:
+    global _FUSE_BN_BWD
+    _FUSE_BN_BWD = bool(flag)
+
+
+def fused_bn_backward_hits() -> int:
+    """How many BatchNorm backward passes took their reductions from the producing data-gradient kernel."""
+    return _FUSED_BN_HITS
 
 
 def begin_step() -> None:
     """Drop per-step bookkeeping (call at the start of every training step)."""
     _PREMASKED.clear()
+    _BN_PARTIALS.clear()
 
 
 _STEM_NATIVE = True       # first-layer tcgen05 kernel (off = cuDNN for the C<=4 stem, used for A/B timing)
@@ -147,6 +170,7 @@ class _ConvNative(torch.autograd.Function):
         ctx.relu_out, ctx.has_residual = bool(relu_out), residual is not None
         # the 1-bit ReLU mask of the input tensor, when its producer left one (BatchNorm + residual + ReLU)
         ctx.in_mask = getattr(x, "_tdl_relu_mask", None) if want_tap else None
+        ctx.bn_src = getattr(x, "_tdl_bn_src", None) if _FUSE_BN_BWD else None
 
         K, Rk, Sk, C = weight.shape
         taps = Rk * Sk
@@ -196,9 +220,22 @@ class _ConvNative(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             if has_wd:
                 mask = ctx.in_mask if (d_tap is not None and C % 32 == 0) else None
-                dx = O.conv2d_fprop(dy, wsaved, R=Rk, S=Sk, stride=1, dil=dil, pad_h=(Rk - 1) * dil - pt,
-                                    pad_w=(Sk - 1) * dil - pl, out_hw=(h, w),
-                                    residual=None if d_tap is None else d_tap.contiguous(), out_mask=mask)
+                src = ctx.bn_src
+                geo = dict(R=Rk, S=Sk, dil=dil, pad_h=(Rk - 1) * dil - pt, pad_w=(Sk - 1) * dil - pl, out_hw=(h, w))
+                res = None if d_tap is None else d_tap.contiguous()
+                partials = None
+                if src is not None and src["x"].numel() == n * h * w * C and (ctx.want_tap == (mask is not None)):
+                    # the tensor this gradient belongs to came straight out of a BatchNorm: reduce that BatchNorm's
+                    # backward sums here, in the epilogue (tap path: mask applied; plain chain: mask recomputed)
+                    rc = src["relu"] and not src["has_res"] and mask is None
+                    if mask is not None or rc or not src["relu"]:
+                        dx, partials = O.conv2d_dgrad_bnstats(dy, wsaved, bn_x=src["x"], bn_mean=src["mean"],
+                                                              bn_invstd=src["invstd"], residual=res, out_mask=mask,
+                                                              bn_scale=src["scale"] if rc else None,
+                                                              bn_shift=src["shift"] if rc else None, **geo)
+                        _BN_PARTIALS[dx.data_ptr()] = (dx._version, src["x"].data_ptr(), partials, mask is not None)
+                if partials is None:
+                    dx = O.conv2d_fprop(dy, wsaved, stride=1, residual=res, out_mask=mask, **geo)
                 if mask is not None:  # this IS the total gradient of x (tap), with x's ReLU backward already applied
                     _PREMASKED[dx.data_ptr()] = mask.data_ptr()
                 d_tap = None
@@ -468,8 +505,10 @@ class _BNNative(torch.autograd.Function):
         if training:
             ctx.save_for_backward(x2, zmask, scale, shift, mean, invstd)
         ctx.cfg = (relu, residual is not None, training, shape)
-        global _LAST_RELU_MASK
+        global _LAST_RELU_MASK, _LAST_BN_SRC
         _LAST_RELU_MASK = zmask
+        _LAST_BN_SRC = (dict(x=x2, mean=mean, invstd=invstd, scale=scale, shift=shift, relu=bool(relu),
+                             has_res=residual is not None) if training else None)
         return z.view(shape)
 
     @staticmethod
@@ -485,24 +524,30 @@ class _BNNative(torch.autograd.Function):
         g, b = ctx.gamma_param, ctx.beta_param
         direct = _direct_ok(g) and _direct_ok(b)
         premasked = (z2 is not None and has_res and _PREMASKED.pop(dz2.data_ptr(), None) == z2.data_ptr())
+        partials = None
+        ent = _BN_PARTIALS.pop(dz2.data_ptr(), None)
+        if ent is not None and ent[0] == dz2._version and ent[1] == x2.data_ptr() and ent[3] == premasked:
+            partials = ent[2]  # the kernel that produced dz already reduced (sum dz, sum dz * xhat)
+            global _FUSED_BN_HITS
+            _FUSED_BN_HITS += 1
         if premasked:
             # the consumer's data-gradient kernel already applied this layer's ReLU mask: no masking here, and the
             # residual branch's gradient is the incoming gradient itself (nothing to write)
             dx, _, dgamma, dbeta = O.bn_bwd(dz2, x2, None, scale, shift, mean, invstd, False, False,
                                             acc_dgamma=g.grad if direct else None,
-                                            acc_dbeta=b.grad if direct else None)
+                                            acc_dbeta=b.grad if direct else None, partials=partials)
             dres = dz2
         elif has_res and not relu:
             # no activation after the sum: the residual branch's gradient is the incoming gradient, nothing to write
             dx, _, dgamma, dbeta = O.bn_bwd(dz2, x2, None, scale, shift, mean, invstd, False, False,
                                             acc_dgamma=g.grad if direct else None,
-                                            acc_dbeta=b.grad if direct else None)
+                                            acc_dbeta=b.grad if direct else None, partials=partials)
             dres = dz2
         else:
             dx, dres, dgamma, dbeta = O.bn_bwd(dz2, x2, z2, scale, shift, mean, invstd, relu, has_res,
                                                acc_dgamma=g.grad if direct else None,
-                                               acc_dbeta=b.grad if direct else None)
-        _count(4)
+                                               acc_dbeta=b.grad if direct else None, partials=partials)
+        _count(3 if partials is not None else 4)
         if direct:
             _notify(g)
             _notify(b)
@@ -520,14 +565,18 @@ def batch_norm(x: torch.Tensor, gamma, beta, running_mean, running_var, *, decay
     C = x.shape[-1]
     if _native_ok(x) and C % 8 == 0 and gamma is not None and beta is not None:
         res = None if residual is None else residual.contiguous()
-        global _LAST_RELU_MASK
-        _LAST_RELU_MASK = None
+        global _LAST_RELU_MASK, _LAST_BN_SRC
+        _LAST_RELU_MASK = _LAST_BN_SRC = None
         out = _BNNative.apply(x.contiguous(), gamma, beta, running_mean, running_var, res, decay, eps, relu,
                               training, stats if training else None)
         if _LAST_RELU_MASK is not None:
             # lets the next convolution's data-gradient kernel apply this ReLU's backward (see _ConvNative)
             out._tdl_relu_mask = _LAST_RELU_MASK
             _LAST_RELU_MASK = None
+        if _LAST_BN_SRC is not None:
+            # lets the consumer convolution's data-gradient kernel reduce this BatchNorm's backward sums (_ConvNative)
+            out._tdl_bn_src = _LAST_BN_SRC
+            _LAST_BN_SRC = None
         return out
     if training:
         y = R.batch_norm_train(x, gamma, beta, running_mean, running_var, decay, eps)

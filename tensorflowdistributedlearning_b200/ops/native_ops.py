@@ -76,10 +76,12 @@ def conv2d_fprop(x: torch.Tensor, w: torch.Tensor, *, R: int, S: int, stride: in
 
 def conv2d_dgrad_bnstats(dy: torch.Tensor, w: torch.Tensor, *, R: int, S: int, dil: int = 1, pad_h: int = 0,
                          pad_w: int = 0, out_hw, bn_x: torch.Tensor, bn_mean: torch.Tensor, bn_invstd: torch.Tensor,
-                         residual: Optional[torch.Tensor] = None, out_mask: Optional[torch.Tensor] = None):
+                         residual: Optional[torch.Tensor] = None, out_mask: Optional[torch.Tensor] = None,
+                         bn_scale: Optional[torch.Tensor] = None, bn_shift: Optional[torch.Tensor] = None):
     """Stride-1 data gradient dx = conv(dy, w) (+ residual) (* mask) that also reduces, in its epilogue, the sums
     BatchNorm backward needs for the BatchNorm that produced this tensor (``bn_x`` = that BatchNorm's input).
-    Returns (dx, partials [nparts, 2, K]) with partials = per-CTA (sum dz, sum dz * xhat)."""
+    Returns (dx, partials [nparts, 2, K]) with partials = per-CTA (sum dz, sum dz * xhat).  With ``bn_scale`` /
+    ``bn_shift`` the sums see the recomputed ReLU mask ``x * scale + shift > 0`` while dx is stored unmasked."""
     _chk_bf16_nhwc(dy, "dy")
     _chk_bf16_nhwc(w, "w")
     n, h, wd, c = dy.shape
@@ -96,7 +98,8 @@ def conv2d_dgrad_bnstats(dy: torch.Tensor, w: torch.Tensor, *, R: int, S: int, d
     partials = torch.empty((int(N.lib().tdl_num_sms()), 2, k), dtype=torch.float32, device=dy.device)
     nparts = ctypes.c_int(0)
     rc = N.lib().tdl_conv2d_dgrad_bnstats_bf16(N.ptr(dy), N.ptr(w), N.ptr(dx), N.ptr(residual), N.ptr(out_mask),
-                                               N.ptr(bn_x), N.ptr(bn_mean), N.ptr(bn_invstd), _i(n), _i(h), _i(wd),
+                                               N.ptr(bn_x), N.ptr(bn_mean), N.ptr(bn_invstd), N.ptr(bn_scale),
+                                               N.ptr(bn_shift), _i(n), _i(h), _i(wd),
                                                _i(c), _i(k), _i(R), _i(S), _i(dil), _i(pad_h), _i(pad_w), _i(p), _i(q),
                                                N.ptr(partials), ctypes.byref(nparts), N.stream_ptr())
     N.check(rc, "tdl_conv2d_dgrad_bnstats_bf16")

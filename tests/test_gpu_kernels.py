@@ -270,6 +270,42 @@ def test_residual_units_backward_with_premasked_gradients():
         assert float(cos) > 0.98, (a.shape, float(cos))
 
 
+def test_bn_backward_sums_taken_from_the_producing_dgrad_kernel():
+    """Residual units with the BatchNorm-backward reductions fused into the data-gradient epilogues give the same
+    gradients as the separate reduction pass (same kernels otherwise), and the fused path is really taken."""
+    from tensorflowdistributedlearning_b200.models.resnet import BottleneckV1
+    from tensorflowdistributedlearning_b200.ops import functional as Fn
+    from tensorflowdistributedlearning_b200.ops.layers import BNConfig
+
+    torch.manual_seed(6)
+    bn = BNConfig()
+    units = torch.nn.ModuleList([BottleneckV1(64, 256, 64, 1, 1, "u0", bn), BottleneckV1(256, 256, 64, 1, 1, "u1", bn),
+                                 BottleneckV1(256, 512, 128, 2, 1, "u2", bn),
+                                 BottleneckV1(512, 512, 128, 1, 1, "u3", bn)]).cuda().train()
+    x0 = torch.randn(4, 16, 16, 64, device="cuda").bfloat16()
+    g0 = torch.randn(4, 8, 8, 512, device="cuda").bfloat16()
+    grads, hits = {}, {}
+    try:
+        for flag in (False, True):
+            Fn.enable_fused_bn_backward(flag)
+            Fn.begin_step()
+            for p in units.parameters():
+                p.grad = None
+            before = Fn.fused_bn_backward_hits()
+            x = x0.clone().requires_grad_(True)
+            h = x
+            for u in units:
+                h = u(h)
+            h.backward(g0)
+            hits[flag] = Fn.fused_bn_backward_hits() - before
+            grads[flag] = [x.grad.float().clone()] + [p.grad.float().clone() for p in units.parameters()]
+    finally:
+        Fn.enable_fused_bn_backward(False)  # the default: measured slower end to end (DESIGN.md)
+    assert hits[False] == 0 and hits[True] >= 9, hits
+    for a, b in zip(grads[True], grads[False]):
+        assert rel_err(a, b) < 2e-2, (a.shape, rel_err(a, b))
+
+
 @pytest.mark.parametrize("case", [(2, 224, 3, 64, 7, "SAME"), (2, 224, 3, 64, 7, (3, 3, 3, 3)), (2, 299, 3, 32, 3, (1, 1, 1, 1)),
                                   (3, 101, 2, 64, 3, "SAME"), (2, 64, 4, 40, 5, "SAME")])
 def test_conv_stem_space_to_depth_tcgen05(O, case):
