@@ -1359,6 +1359,24 @@ static int launch_wgrad(const CUtensorMap& tdy, const CUtensorMap& tx, const Geo
   if (splits < 1) splits = 1;
   if ((2 * sms) / items > splits && patches / ((2 * sms) / items) >= 32) splits = (2 * sms) / items;
   if (splits > patches) splits = patches;
+  {
+    // Split count from a two-term cost model (measured on B200, profiles/README.md): a CTA spends
+    // patches/splits x t_patch in its main loop and then adds its whole fp32 tile into dW with red.global.add, and
+    // those adds (all CTAs finish together) drain at ~0.55 TB/s.  Both terms scale with the tile size, so the
+    // optimum depends only on patches / items: splits* = sqrt(1.1 * patches / items).  More splits than that just
+    // moves time from the tensor core into atomics (13x13 / 7x7 layers: 9 -> 2-4 splits, -10 % step time on the
+    // reference network); fewer, longer CTAs also leave SMs to the main stream the wgrad overlaps with.
+    static int model_on = -1;
+    if (model_on < 0) {
+      const char* e = getenv("TDL_WGRAD_SPLIT_MODEL");
+      model_on = e ? atoi(e) : 1;
+    }
+    if (model_on) {
+      int s_model = (int)(sqrtf(1.1f * (float)patches / (float)items) + 0.5f);
+      if (s_model < 1) s_model = 1;
+      if (splits > s_model) splits = s_model;
+    }
+  }
   if (splits < 1) splits = 1;
   dim3 grid(splits, items);
   conv_wgrad_kernel<MT, BLOCK_N, TP><<<grid, kThreads, Cfg::kSmemBytes, st>>>(tdy, tx, g, dw, m_tiles, n_tiles);

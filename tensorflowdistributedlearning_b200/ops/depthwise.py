@@ -61,6 +61,12 @@ class _DepthwiseNative(torch.autograd.Function):
             TF._count(1)
             dx = None
             if ctx.needs_input_grad[0]:
+                if relu and (stride == 1 or (stride == 2 and dil == 1)):
+                    # backward of the fused output ReLU (reference split_separable_conv2d: depthwise + bias + ReLU,
+                    # core/layers.py:6-49), then the same fast data-gradient kernels as the no-activation case
+                    dy = torch.ops.aten.threshold_backward(dy, y, 0)
+                    relu = False
+                    TF._count(1)
                 if stride == 1 and not relu:
                     n, h, w, _ = x.shape
                     dx = O.depthwise3x3_fwd(dy, wd.flip(0, 1).contiguous().view(9, C), None, x if relu_in else None, 1,
