@@ -1366,13 +1366,13 @@ static int launch_wgrad(const CUtensorMap& tdy, const CUtensorMap& tx, const Geo
     // optimum depends only on patches / items: splits* = sqrt(1.1 * patches / items).  More splits than that just
     // moves time from the tensor core into atomics (13x13 / 7x7 layers: 9 -> 2-4 splits, -10 % step time on the
     // reference network); fewer, longer CTAs also leave SMs to the main stream the wgrad overlaps with.
-    static int model_on = -1;
-    if (model_on < 0) {
+    static float model_k = -1.f;  // TDL_WGRAD_SPLIT_MODEL: the constant of the model (0 = off)
+    if (model_k < 0.f) {
       const char* e = getenv("TDL_WGRAD_SPLIT_MODEL");
-      model_on = e ? atoi(e) : 1;
+      model_k = e ? (float)atof(e) : 1.1f;
     }
-    if (model_on) {
-      int s_model = (int)(sqrtf(1.1f * (float)patches / (float)items) + 0.5f);
+    if (model_k > 0.f) {
+      int s_model = (int)(sqrtf(model_k * (float)patches / (float)items) + 0.5f);
       if (s_model < 1) s_model = 1;
       if (splits > s_model) splits = s_model;
     }
