@@ -1306,7 +1306,11 @@ static int launch_fprop(const CUtensorMap& tx, const CUtensorMap& tw, const CUte
       return launch_fprop_t<BLOCK_N, false, false, true, true>(tx, tw, ty, tres, tid, tbx, g, bias, res, stats, nparts, st);
     return launch_fprop_t<BLOCK_N, false, false, false, true>(tx, tw, ty, tres, tid, tbx, g, bias, res, stats, nparts, st);
   }
-  if (g.res_mma) return launch_fprop_t<BLOCK_N, false, false, true>(tx, tw, ty, tres, tid, tbx, g, bias, res, stats, nparts, st);
+  if (g.res_mma) {
+    if (g.has_bias || g.relu)
+      return launch_fprop_t<BLOCK_N, true, false, true>(tx, tw, ty, tres, tid, tbx, g, bias, res, stats, nparts, st);
+    return launch_fprop_t<BLOCK_N, false, false, true>(tx, tw, ty, tres, tid, tbx, g, bias, res, stats, nparts, st);
+  }
   const bool fused = g.has_bias || g.has_res || g.relu;
   if (stats) {
     if (fused) return launch_fprop_t<BLOCK_N, true, true>(tx, tw, ty, tres, tid, tbx, g, bias, res, stats, nparts, st);
@@ -1467,8 +1471,9 @@ static int fprop_impl(const void* x, const void* w, void* y, const float* bias, 
     }
   }
   g.relu = relu; g.has_bias = bias != nullptr; g.has_res = residual != nullptr;
-  // plain "+ residual" (no bias / ReLU / statistics / strided view): add it on the tensor core, keep the lean epilogue
-  g.res_mma = (residual != nullptr && bias == nullptr && !relu && (stats == nullptr || bnb) && view == nullptr) ? 1 : 0;
+  // "+ residual" without statistics / strided view: add it on the tensor core (an extra A operand x identity block);
+  // the epilogue then never waits on a global load of the residual -- bias and ReLU, if any, stay in the epilogue
+  g.res_mma = (residual != nullptr && (stats == nullptr || bnb) && view == nullptr && (!bnb || (!bias && !relu))) ? 1 : 0;
   if (g.res_mma) g.has_res = 0;
   if (bnb) {
     TDL_REQUIRE(stats && nparts && !view && bias == nullptr && !relu && stride == 1,
@@ -1482,6 +1487,7 @@ static int fprop_impl(const void* x, const void* w, void* y, const float* bias, 
   if (out_mask) {
     TDL_REQUIRE(g.res_mma || bnb, "the output mask needs a plain residual or the BatchNorm-backward sums");
     TDL_REQUIRE(K % 32 == 0, "the output mask needs K % 32 == 0");
+    TDL_REQUIRE(bias == nullptr && !relu, "the output mask excludes bias / ReLU");
     g.has_mask = 1;
   }
   const int block_n = K > 128 ? 256 : (K > 64 ? 128 : 64);
