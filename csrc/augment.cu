@@ -64,6 +64,8 @@ __global__ void __launch_bounds__(256)
 augment_seg_kernel(const float* __restrict__ images, const float* __restrict__ masks,
                    const float* __restrict__ transforms, const int* __restrict__ transposed, float* __restrict__ out,
                    float* __restrict__ out_mask, int B, Params p) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   const int64_t total = (int64_t)B * p.H * p.W;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int x = (int)(i % p.W);
@@ -112,8 +114,10 @@ TDL_API int tdl_augment_seg(const float* images, const float* masks, const float
   int64_t blocks = (total + 255) / 256;
   const int64_t cap = (int64_t)tdl::num_sms() * 8;
   if (blocks > cap) blocks = cap;
-  tdl::augment::augment_seg_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(images, masks, transforms, transposed,
-                                                                                   out, out_mask, B, p);
+  {
+    cudaError_t _le = tdl::launch_pdl(tdl::augment::augment_seg_kernel, dim3((int)blocks), dim3(256), 0, (cudaStream_t)stream, images, masks, transforms, transposed, out, out_mask, B, p);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "tdl::augment::augment_seg_kernel");
+  }
   TDL_LAUNCH_OK("augment_seg_kernel");
   return 0;
 }

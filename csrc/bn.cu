@@ -45,6 +45,8 @@ __device__ __forceinline__ float bn_affine(float x, float scale, float shift) { 
 // ---- forward statistics: per-CTA partial (sum, sumsq) -> scratch[gx][2][C] ----
 __global__ void __launch_bounds__(kThreads)
 bn_partial_stats_kernel(const bf16* __restrict__ x, int64_t rows, int C, int tx, int ty, float* __restrict__ partial) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   extern __shared__ float sm[];  // [ty][tx][16]
   const int cx = threadIdx.x % tx;
   const int ry = threadIdx.x / tx;
@@ -140,6 +142,8 @@ bn_finalize_stats_kernel(const float* __restrict__ partial, int nparts, int C, d
                          float* __restrict__ running_mean, float* __restrict__ running_var, float decay, float eps,
                          float* __restrict__ mean_out, float* __restrict__ invstd_out, float* __restrict__ scale_out,
                          float* __restrict__ shift_out) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   const int c = blockIdx.x * kFinCh + (threadIdx.x % kFinCh);
   double s, q;
   reduce_partials(partial, nparts, C, c, &s, &q);
@@ -162,6 +166,8 @@ bn_finalize_stats_kernel(const float* __restrict__ partial, int nparts, int C, d
 __global__ void bn_infer_scale_shift_kernel(const float* __restrict__ gamma, const float* __restrict__ beta,
                                             const float* __restrict__ rm, const float* __restrict__ rv, float eps,
                                             float* __restrict__ scale, float* __restrict__ shift, int C) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   const float invstd = rsqrtf(rv[c] + eps);
@@ -178,6 +184,8 @@ __global__ void __launch_bounds__(kThreads)
 bn_apply_kernel(const bf16* __restrict__ x, const float* __restrict__ scale, const float* __restrict__ shift,
                 const bf16* __restrict__ residual, bf16* __restrict__ y, uint8_t* __restrict__ mask_out, int64_t rows,
                 int C, int tx, int ty, int relu) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   const int cx = threadIdx.x % tx;
   const int ry = threadIdx.x / tx;
   const int cv = blockIdx.y * tx + cx;
@@ -239,6 +247,8 @@ bn_bwd_partial_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ x, c
                       const float* __restrict__ scale, const float* __restrict__ shift,
                       const float* __restrict__ mean, const float* __restrict__ invstd, int64_t rows, int C, int tx,
                       int ty, int relu, int z_bits, float* __restrict__ partial) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   extern __shared__ float sm[];
   const int cx = threadIdx.x % tx;
   const int ry = threadIdx.x / tx;
@@ -337,6 +347,8 @@ bn_bwd_partial_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ x, c
 __global__ void __launch_bounds__(kFinThreads)
 bn_bwd_finalize_kernel(const float* __restrict__ partial, int nparts, int C, float* __restrict__ dbeta,
                        float* __restrict__ dgamma, float* __restrict__ acc_dbeta, float* __restrict__ acc_dgamma) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   const int c = blockIdx.x * kFinCh + (threadIdx.x % kFinCh);
   double s, q;
   reduce_partials(partial, nparts, C, c, &s, &q);
@@ -355,6 +367,8 @@ bn_bwd_apply_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ x, con
                     const float* __restrict__ invstd, const float* __restrict__ dbeta,
                     const float* __restrict__ dgamma, float inv_n, bf16* __restrict__ dx, bf16* __restrict__ dres,
                     int64_t rows, int C, int tx, int ty, int relu, int z_bits) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   const int cx = threadIdx.x % tx;
   const int ry = threadIdx.x / tx;
   const int cv = blockIdx.y * tx + cx;
@@ -486,13 +500,16 @@ TDL_API int tdl_bn_fwd_stats(const void* x, int64_t rows, int C, float* scratch,
   TDL_REQUIRE(scratch_floats >= (int64_t)s.gx * 2 * C, "scratch too small (see tdl_bn_scratch_floats)");
   cudaStream_t st = (cudaStream_t)stream;
   dim3 grid(s.gx, s.gy);
-  bn_partial_stats_kernel<<<grid, kThreads, kThreads * 16 * sizeof(float), st>>>((const bf16*)x, rows, C, s.tx, s.ty,
-                                                                                  scratch);
+  {
+    cudaError_t _le = tdl::launch_pdl(bn_partial_stats_kernel, dim3(grid), dim3(kThreads), kThreads * 16 * sizeof(float), st, (const bf16*)x, rows, C, s.tx, s.ty, scratch);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "bn_partial_stats_kernel");
+  }
   TDL_LAUNCH_OK("bn_partial_stats_kernel");
   const double unbias = rows > 1 ? (double)rows / (double)(rows - 1) : 1.0;
-  bn_finalize_stats_kernel<<<(C + kFinCh - 1) / kFinCh, kFinThreads, 0, st>>>(
-      scratch, s.gx, C, 1.0 / (double)rows, unbias, gamma, beta, running_mean, running_var, decay, eps, mean, invstd,
-      scale, shift);
+  {
+    cudaError_t _le = tdl::launch_pdl(bn_finalize_stats_kernel, dim3((C + kFinCh - 1) / kFinCh), dim3(kFinThreads), 0, st, scratch, s.gx, C, 1.0 / (double)rows, unbias, gamma, beta, running_mean, running_var, decay, eps, mean, invstd, scale, shift);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "bn_finalize_stats_kernel");
+  }
   TDL_LAUNCH_OK("bn_finalize_stats_kernel");
   return 0;
 }
@@ -504,9 +521,10 @@ TDL_API int tdl_bn_finalize_partials(const float* partial, int nparts, int64_t r
                                      float eps, float* mean, float* invstd, float* scale, float* shift, void* stream) {
   TDL_REQUIRE(C > 0 && nparts > 0 && rows > 0, "bad arguments");
   const double unbias = rows > 1 ? (double)rows / (double)(rows - 1) : 1.0;
-  bn_finalize_stats_kernel<<<(C + kFinCh - 1) / kFinCh, kFinThreads, 0, (cudaStream_t)stream>>>(
-      partial, nparts, C, 1.0 / (double)rows, unbias, gamma, beta, running_mean, running_var, decay, eps, mean, invstd,
-      scale, shift);
+  {
+    cudaError_t _le = tdl::launch_pdl(bn_finalize_stats_kernel, dim3((C + kFinCh - 1) / kFinCh), dim3(kFinThreads), 0, (cudaStream_t)stream, partial, nparts, C, 1.0 / (double)rows, unbias, gamma, beta, running_mean, running_var, decay, eps, mean, invstd, scale, shift);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "bn_finalize_stats_kernel");
+  }
   TDL_LAUNCH_OK("bn_finalize_stats_kernel");
   return 0;
 }
@@ -514,8 +532,10 @@ TDL_API int tdl_bn_finalize_partials(const float* partial, int nparts, int64_t r
 TDL_API int tdl_bn_infer_scale_shift(const float* gamma, const float* beta, const float* running_mean,
                                      const float* running_var, float eps, float* scale, float* shift, int C,
                                      void* stream) {
-  bn_infer_scale_shift_kernel<<<(C + 127) / 128, 128, 0, (cudaStream_t)stream>>>(gamma, beta, running_mean,
-                                                                                 running_var, eps, scale, shift, C);
+  {
+    cudaError_t _le = tdl::launch_pdl(bn_infer_scale_shift_kernel, dim3((C + 127) / 128), dim3(128), 0, (cudaStream_t)stream, gamma, beta, running_mean, running_var, eps, scale, shift, C);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "bn_infer_scale_shift_kernel");
+  }
   TDL_LAUNCH_OK("bn_infer_scale_shift_kernel");
   return 0;
 }
@@ -529,8 +549,10 @@ TDL_API int tdl_bn_apply(const void* x, const float* scale, const float* shift, 
   if (rows == 0) return 0;
   ReduceShape s = apply_shape(rows, C);
   dim3 grid(s.gx, s.gy);
-  bn_apply_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>((const bf16*)x, scale, shift, (const bf16*)residual,
-                                                               (bf16*)y, (uint8_t*)mask_out, rows, C, s.tx, s.ty, relu);
+  {
+    cudaError_t _le = tdl::launch_pdl(bn_apply_kernel, dim3(grid), dim3(kThreads), 0, (cudaStream_t)stream, (const bf16*)x, scale, shift, (const bf16*)residual, (bf16*)y, (uint8_t*)mask_out, rows, C, s.tx, s.ty, relu);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "bn_apply_kernel");
+  }
   TDL_LAUNCH_OK("bn_apply_kernel");
   return 0;
 }
@@ -546,12 +568,15 @@ TDL_API int tdl_bn_bwd_reduce(const void* dz, const void* x, const void* z, int 
   TDL_REQUIRE(scratch_floats >= (int64_t)s.gx * 2 * C, "scratch too small (see tdl_bn_scratch_floats)");
   cudaStream_t st = (cudaStream_t)stream;
   dim3 grid(s.gx, s.gy);
-  bn_bwd_partial_kernel<<<grid, kThreads, kThreads * 16 * sizeof(float), st>>>(
-      (const bf16*)dz, (const bf16*)x, (const bf16*)z, scale, shift, mean, invstd, rows, C, s.tx, s.ty, relu,
-      z_is_bitmask, scratch);
+  {
+    cudaError_t _le = tdl::launch_pdl(bn_bwd_partial_kernel, dim3(grid), dim3(kThreads), kThreads * 16 * sizeof(float), st, (const bf16*)dz, (const bf16*)x, (const bf16*)z, scale, shift, mean, invstd, rows, C, s.tx, s.ty, relu, z_is_bitmask, scratch);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "bn_bwd_partial_kernel");
+  }
   TDL_LAUNCH_OK("bn_bwd_partial_kernel");
-  bn_bwd_finalize_kernel<<<(C + kFinCh - 1) / kFinCh, kFinThreads, 0, st>>>(scratch, s.gx, C, dbeta, dgamma, acc_dbeta,
-                                                                            acc_dgamma);
+  {
+    cudaError_t _le = tdl::launch_pdl(bn_bwd_finalize_kernel, dim3((C + kFinCh - 1) / kFinCh), dim3(kFinThreads), 0, st, scratch, s.gx, C, dbeta, dgamma, acc_dbeta, acc_dgamma);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "bn_bwd_finalize_kernel");
+  }
   TDL_LAUNCH_OK("bn_bwd_finalize_kernel");
   return 0;
 }
@@ -561,8 +586,10 @@ TDL_API int tdl_bn_bwd_reduce(const void* dz, const void* x, const void* z, int 
 TDL_API int tdl_bn_bwd_finalize_partials(const float* partial, int nparts, int C, float* dgamma, float* dbeta,
                                          float* acc_dgamma, float* acc_dbeta, void* stream) {
   TDL_REQUIRE(C > 0 && nparts > 0, "bad shape");
-  bn_bwd_finalize_kernel<<<(C + kFinCh - 1) / kFinCh, kFinThreads, 0, (cudaStream_t)stream>>>(
-      partial, nparts, C, dbeta, dgamma, acc_dbeta, acc_dgamma);
+  {
+    cudaError_t _le = tdl::launch_pdl(bn_bwd_finalize_kernel, dim3((C + kFinCh - 1) / kFinCh), dim3(kFinThreads), 0, (cudaStream_t)stream, partial, nparts, C, dbeta, dgamma, acc_dbeta, acc_dgamma);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "bn_bwd_finalize_kernel");
+  }
   TDL_LAUNCH_OK("bn_bwd_finalize_kernel");
   return 0;
 }
@@ -574,9 +601,10 @@ TDL_API int tdl_bn_bwd_apply(const void* dz, const void* x, const void* z, int z
   if (rows == 0) return 0;
   ReduceShape s = apply_shape(rows, C);
   dim3 grid(s.gx, s.gy);
-  bn_bwd_apply_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(
-      (const bf16*)dz, (const bf16*)x, (const bf16*)z, scale, shift, mean, invstd, dbeta, dgamma, 1.f / (float)rows,
-      (bf16*)dx, (bf16*)dres, rows, C, s.tx, s.ty, relu, z_is_bitmask);
+  {
+    cudaError_t _le = tdl::launch_pdl(bn_bwd_apply_kernel, dim3(grid), dim3(kThreads), 0, (cudaStream_t)stream, (const bf16*)dz, (const bf16*)x, (const bf16*)z, scale, shift, mean, invstd, dbeta, dgamma, 1.f / (float)rows, (bf16*)dx, (bf16*)dres, rows, C, s.tx, s.ty, relu, z_is_bitmask);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "bn_bwd_apply_kernel");
+  }
   TDL_LAUNCH_OK("bn_bwd_apply_kernel");
   return 0;
 }
@@ -655,13 +683,16 @@ TDL_API int tdl_bn_fwd_stats_noalloc(const void* x, int64_t rows, int C, const f
   if (rc != 0) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   dim3 grid(s.gx, s.gy);
-  bn_partial_stats_kernel<<<grid, kThreads, kThreads * 16 * sizeof(float), st>>>((const bf16*)x, rows, C, s.tx, s.ty,
-                                                                                  scratch);
+  {
+    cudaError_t _le = tdl::launch_pdl(bn_partial_stats_kernel, dim3(grid), dim3(kThreads), kThreads * 16 * sizeof(float), st, (const bf16*)x, rows, C, s.tx, s.ty, scratch);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "bn_partial_stats_kernel");
+  }
   TDL_LAUNCH_OK("bn_partial_stats_kernel");
   const double unbias = rows > 1 ? (double)rows / (double)(rows - 1) : 1.0;
-  bn_finalize_stats_kernel<<<(C + kFinCh - 1) / kFinCh, kFinThreads, 0, st>>>(scratch, s.gx, C, 1.0 / (double)rows, unbias, gamma,
-                                                                  beta, running_mean, running_var, decay, eps, mean,
-                                                                  invstd, scale, shift);
+  {
+    cudaError_t _le = tdl::launch_pdl(bn_finalize_stats_kernel, dim3((C + kFinCh - 1) / kFinCh), dim3(kFinThreads), 0, st, scratch, s.gx, C, 1.0 / (double)rows, unbias, gamma, beta, running_mean, running_var, decay, eps, mean, invstd, scale, shift);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "bn_finalize_stats_kernel");
+  }
   TDL_LAUNCH_OK("bn_finalize_stats_kernel");
   return 0;
 }

@@ -198,6 +198,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
                   const __grid_constant__ CUtensorMap tm_id, const __grid_constant__ CUtensorMap tm_bx,
                   const Geometry g, const float* __restrict__ bias, const bf16* __restrict__ residual,
                   float* __restrict__ stats) {
+  ptx::pdl_trigger();
   using Cfg = FpropCfg<BLOCK_N, kBwdStats>;
   constexpr int kStages = Cfg::kStages;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -264,6 +265,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
     __syncwarp();
     ptx::tmem_alloc<Cfg::kTmemCols>(tmem_slot);
   }
+  ptx::pdl_wait();  // set-up above overlapped the previous kernel's tail; global memory is touched from here on
   if constexpr (kStats || kBwdStats) {  // this CTA's statistics slot starts at zero
     float* slot = stats + (size_t)blockIdx.x * 2 * g.K;
     for (int i = threadIdx.x; i < 2 * g.K; i += kFpropThreads) slot[i] = 0.f;
@@ -807,6 +809,7 @@ template <int MT, int BLOCK_N, int TP = 1>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_wgrad_kernel(const __grid_constant__ CUtensorMap tm_dy, const __grid_constant__ CUtensorMap tm_x,
                   const Geometry g, float* __restrict__ dw, int m_tiles_co, int n_tiles_ci) {
+  ptx::pdl_trigger();
   using Cfg = WgradCfg<MT, BLOCK_N, TP>;
   constexpr int kStages = Cfg::kStages;
   extern __shared__ uint8_t smem_raw[];
@@ -861,6 +864,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tm_dy, const __grid_consta
     __syncwarp();
     ptx::tmem_alloc<Cfg::kTmemCols>(tmem_slot);
   }
+  ptx::pdl_wait();  // set-up above overlapped the previous kernel's tail
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
@@ -984,6 +988,8 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tm_dy, const __grid_consta
 // ------------------------------------------------------------------------------------------
 __global__ void weight_prep_kernel(const float* __restrict__ w, bf16* __restrict__ w_fprop,
                                    bf16* __restrict__ w_dgrad, int K, int taps, int C) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   const size_t total = (size_t)K * taps * C;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     const int c = (int)(i % C);
@@ -1000,6 +1006,8 @@ __global__ void weight_prep_kernel(const float* __restrict__ w, bf16* __restrict
 // which made this 6 % of the reference network's step).  blockDim = (32, 8), grid = (c-tiles, k-tiles, taps).
 __global__ void weight_prep_tiled_kernel(const float* __restrict__ w, bf16* __restrict__ w_fprop,
                                          bf16* __restrict__ w_dgrad, int K, int taps, int C) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   __shared__ float tile[32][33];
   const int t = blockIdx.z;
   const int c0 = blockIdx.x * 32, k0 = blockIdx.y * 32;
@@ -1026,6 +1034,8 @@ __global__ void weight_prep_tiled_kernel(const float* __restrict__ w, bf16* __re
 // x[2*h2 + dy][2*w2 + dx][c]; lanes >= 4*C and pixels beyond an odd H/W are zero.
 __global__ void stem_pack_kernel(const bf16* __restrict__ x, bf16* __restrict__ planes, int N, int H, int W, int C,
                                  int H2, int W2) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   const int64_t total = (int64_t)N * H2 * 2 * W2;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int w2 = (int)(i % W2);
@@ -1056,6 +1066,8 @@ __global__ void stem_pack_kernel(const bf16* __restrict__ x, bf16* __restrict__ 
 // cp = (dy*2+dx)*C + c  <-  original tap r = 2*(r2 - pad2_h) + dy + pad_h (same for s), zero when outside the filter.
 __global__ void stem_weight_prep_kernel(const float* __restrict__ w, bf16* __restrict__ out, int K, int R, int S, int C,
                                         int Th, int Tw, int pad_h, int pad_w, int pad2_h, int pad2_w) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   const int total = K * Th * Tw * 16;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
     const int cp = i & 15;
@@ -1087,8 +1099,10 @@ static int launch_stem(const CUtensorMap& tx, const CUtensorMap& tw, const CUten
   const int total = g.tiles_n * g.tiles_h * g.tiles_w;
   const int grid = total < tdl::num_sms() ? total : tdl::num_sms();
   if (nparts) *nparts = grid;
-  conv_fprop_kernel<64, false, kStats, true><<<grid, kFpropThreads, Cfg::kSmemBytes, st>>>(tx, tw, ty, ty, ty, ty, g, nullptr,
-                                                                                           nullptr, stats);
+  {
+    cudaError_t _le = tdl::launch_pdl(conv_fprop_kernel<64, false, kStats, true>, dim3(grid), dim3(kFpropThreads), Cfg::kSmemBytes, st, tx, tw, ty, ty, ty, ty, g, nullptr, nullptr, stats);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "conv_fprop_kernel");
+  }
   TDL_LAUNCH_OK("conv_fprop_kernel(stem)");
   return 0;
 }
@@ -1116,6 +1130,7 @@ template <int NBLK>  // NBLK = 2 * row taps
 __global__ void __launch_bounds__(kThreads, 1)
 stem_wgrad_kernel(const __grid_constant__ CUtensorMap tm_dy, const __grid_constant__ CUtensorMap tm_x,
                   const StemWgradGeo g, float* __restrict__ dwp) {
+  ptx::pdl_trigger();
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + g.stages * g.stage_bytes);
@@ -1152,6 +1167,7 @@ stem_wgrad_kernel(const __grid_constant__ CUtensorMap tm_dy, const __grid_consta
     __syncwarp();
     ptx::tmem_alloc<256>(tmem_slot);
   }
+  ptx::pdl_wait();  // set-up above overlapped the previous kernel's tail
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
@@ -1262,6 +1278,8 @@ stem_wgrad_kernel(const __grid_constant__ CUtensorMap tm_dy, const __grid_consta
 __global__ void stem_wgrad_unpack_kernel(const float* __restrict__ dwp, float* __restrict__ dw, int K, int R, int S,
                                          int C, int Th, int Tw, int pad_h, int pad_w, int pad2_h, int pad2_w,
                                          int accumulate) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   const int total = K * R * S * C;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
     const int c = i % C;
@@ -1291,8 +1309,10 @@ const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& ty, const CUten
   const int total = g.tiles_n * g.tiles_h * g.tiles_w * g.n_tiles;
   const int grid = total < tdl::num_sms() ? total : tdl::num_sms();
   if (nparts) *nparts = grid;
-  conv_fprop_kernel<BLOCK_N, kFused, kStats, false, kResMma, kBwdStats><<<grid, kFpropThreads, Cfg::kSmemBytes, st>>>(
-      tx, tw, ty, tres, tid, tbx, g, bias, res, stats);
+  {
+    cudaError_t _le = tdl::launch_pdl(conv_fprop_kernel<BLOCK_N, kFused, kStats, false, kResMma, kBwdStats>, dim3(grid), dim3(kFpropThreads), Cfg::kSmemBytes, st, tx, tw, ty, tres, tid, tbx, g, bias, res, stats);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "conv_fprop_kernel");
+  }
   TDL_LAUNCH_OK("conv_fprop_kernel");
   return 0;
 }
@@ -1323,6 +1343,8 @@ static int launch_fprop(const CUtensorMap& tx, const CUtensorMap& tw, const CUte
 // 64x64 bf16 identity block in global memory (the B operand of the residual-on-the-tensor-core iterations)
 __device__ __align__(1024) bf16 g_identity64[64 * 64];
 __global__ void identity64_init_kernel() {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   for (int i = threadIdx.x; i < 64 * 64; i += blockDim.x) g_identity64[i] = __float2bfloat16((i >> 6) == (i & 63) ? 1.f : 0.f);
 }
 static int identity64_address(const void** out, cudaStream_t st) {
@@ -1334,7 +1356,10 @@ static int identity64_address(const void** out, cudaStream_t st) {
   if (addr[dev] == nullptr) {
     void* p = nullptr;
     TDL_CUDA_OK(cudaGetSymbolAddress(&p, g_identity64));
-    identity64_init_kernel<<<1, 256, 0, st>>>();  // ordered before the first consumer on the same stream
+    {
+      cudaError_t _le = tdl::launch_pdl(identity64_init_kernel, dim3(1), dim3(256), 0, st);
+      if (_le != cudaSuccess) return tdl::cuda_fail(_le, "identity64_init_kernel");
+    }  // ordered before the first consumer on the same stream
     TDL_LAUNCH_OK("identity64_init_kernel");
     addr[dev] = p;
   }
@@ -1383,7 +1408,10 @@ static int launch_wgrad(const CUtensorMap& tdy, const CUtensorMap& tx, const Geo
   }
   if (splits < 1) splits = 1;
   dim3 grid(splits, items);
-  conv_wgrad_kernel<MT, BLOCK_N, TP><<<grid, kThreads, Cfg::kSmemBytes, st>>>(tdy, tx, g, dw, m_tiles, n_tiles);
+  {
+    cudaError_t _le = tdl::launch_pdl(conv_wgrad_kernel<MT, BLOCK_N, TP>, dim3(grid), dim3(kThreads), Cfg::kSmemBytes, st, tdy, tx, g, dw, m_tiles, n_tiles);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "conv_wgrad_kernel");
+  }
   TDL_LAUNCH_OK("conv_wgrad_kernel");
   return 0;
 }
@@ -1676,13 +1704,19 @@ TDL_API int tdl_conv2d_weight_prep(const float* w, void* w_fprop, void* w_dgrad,
   if (total == 0) return 0;
   if (w_dgrad != nullptr && taps <= 65535 && cdiv(K, 32) <= 65535) {
     dim3 grid((unsigned)cdiv(C, 32), (unsigned)cdiv(K, 32), (unsigned)taps);
-    weight_prep_tiled_kernel<<<grid, dim3(32, 8), 0, (cudaStream_t)stream>>>(w, (bf16*)w_fprop, (bf16*)w_dgrad, K, taps, C);
+    {
+      cudaError_t _le = tdl::launch_pdl(weight_prep_tiled_kernel, dim3(grid), dim3(dim3(32, 8)), 0, (cudaStream_t)stream, w, (bf16*)w_fprop, (bf16*)w_dgrad, K, taps, C);
+      if (_le != cudaSuccess) return tdl::cuda_fail(_le, "weight_prep_tiled_kernel");
+    }
     TDL_LAUNCH_OK("weight_prep_tiled_kernel");
     return 0;
   }
   int blocks = (int)cdiv((int64_t)total, 256);
   if (blocks > 4 * num_sms()) blocks = 4 * num_sms();
-  weight_prep_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(w, (bf16*)w_fprop, (bf16*)w_dgrad, K, taps, C);
+  {
+    cudaError_t _le = tdl::launch_pdl(weight_prep_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, w, (bf16*)w_fprop, (bf16*)w_dgrad, K, taps, C);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "weight_prep_kernel");
+  }
   TDL_LAUNCH_OK("weight_prep_kernel");
   return 0;
 }
@@ -1702,7 +1736,10 @@ TDL_API int tdl_conv_stem_pack(const void* x, void* planes, int N, int H, int W,
   if (total == 0) return 0;
   int64_t blocks = cdiv(total, 256);
   if (blocks > (int64_t)num_sms() * 16) blocks = (int64_t)num_sms() * 16;
-  stem_pack_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>((const bf16*)x, (bf16*)planes, N, H, W, C, H2, W2);
+  {
+    cudaError_t _le = tdl::launch_pdl(stem_pack_kernel, dim3((int)blocks), dim3(256), 0, (cudaStream_t)stream, (const bf16*)x, (bf16*)planes, N, H, W, C, H2, W2);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "stem_pack_kernel");
+  }
   TDL_LAUNCH_OK("stem_pack_kernel");
   return 0;
 }
@@ -1722,8 +1759,10 @@ TDL_API int tdl_conv_stem_weight_prep(const float* w, void* w_packed, int K, int
   stem_taps(R, pad_h, &th, &p2h);
   stem_taps(S, pad_w, &tw, &p2w);
   const int total = K * th * tw * 16;
-  stem_weight_prep_kernel<<<(int)cdiv(total, 256), 256, 0, (cudaStream_t)stream>>>(w, (bf16*)w_packed, K, R, S, C, th,
-                                                                                tw, pad_h, pad_w, p2h, p2w);
+  {
+    cudaError_t _le = tdl::launch_pdl(stem_weight_prep_kernel, dim3((int)cdiv(total, 256)), dim3(256), 0, (cudaStream_t)stream, w, (bf16*)w_packed, K, R, S, C, th, tw, pad_h, pad_w, p2h, p2w);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "stem_weight_prep_kernel");
+  }
   TDL_LAUNCH_OK("stem_weight_prep_kernel");
   return 0;
 }
@@ -1846,11 +1885,16 @@ TDL_API int tdl_conv_stem_wgrad(const void* planes, const void* dy, float* dwp_s
   TDL_CUDA_OK(cudaMemsetAsync(dwp_scratch, 0, sizeof(float) * (size_t)K * th * tw * 16, st));
   const int total = N * P * g.tiles_w;
   const int grid = total < tdl::num_sms() ? total : tdl::num_sms();
-  kern<<<grid, kThreads, smem_bytes, st>>>(tdy, tx, g, dwp_scratch);
+  {
+    cudaError_t _le = tdl::launch_pdl(kern, dim3(grid), dim3(kThreads), smem_bytes, st, tdy, tx, g, dwp_scratch);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "kern");
+  }
   TDL_LAUNCH_OK("stem_wgrad_kernel");
   const int n_out = K * R * S * C;
-  stem_wgrad_unpack_kernel<<<(int)cdiv(n_out, 256), 256, 0, st>>>(dwp_scratch, dw, K, R, S, C, th, tw, pad_h, pad_w,
-                                                                 p2h, p2w, accumulate);
+  {
+    cudaError_t _le = tdl::launch_pdl(stem_wgrad_unpack_kernel, dim3((int)cdiv(n_out, 256)), dim3(256), 0, st, dwp_scratch, dw, K, R, S, C, th, tw, pad_h, pad_w, p2h, p2w, accumulate);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "stem_wgrad_unpack_kernel");
+  }
   TDL_LAUNCH_OK("stem_wgrad_unpack_kernel");
   return 0;
 }

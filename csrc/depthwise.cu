@@ -48,6 +48,8 @@ __global__ void __launch_bounds__(kThreads)
 depthwise3x3_kernel(const bf16* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
                     const bf16* __restrict__ mask, bf16* __restrict__ y, Shape s, int tx, int ty, int relu_in,
                     int relu_out) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   const int cx = threadIdx.x % tx, sy = threadIdx.x / tx;
   const int c4 = s.C / 4;
   const int cv = blockIdx.y * tx + cx;
@@ -135,6 +137,8 @@ template <bool kDense>
 __global__ void __launch_bounds__(kThreads)
 depthwise3x3_wgrad_kernel(const bf16* __restrict__ x, const bf16* __restrict__ dy, const bf16* __restrict__ ymask,
                           float* __restrict__ dw, float* __restrict__ dbias, Shape s, int tx, int ty, int relu_in) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   extern __shared__ float sm[];  // [ty][tx][4]
   const int cx = threadIdx.x % tx, sy = threadIdx.x / tx;
   const int c4 = s.C / 4;
@@ -256,6 +260,8 @@ template <int S>
 __global__ void __launch_bounds__(kThreads)
 depthwise3x3_dgrad_strided_kernel(const bf16* __restrict__ dy, const float* __restrict__ w, const bf16* __restrict__ xmask,
                                   bf16* __restrict__ dx, int H, int W, int C, int P, int Q, int pad_h, int pad_w) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   constexpr int kCells = (3 + S - 1) / S;
   const int c8 = C >> 3;
   const int n = blockIdx.y;
@@ -326,11 +332,15 @@ TDL_API int tdl_depthwise3x3_fwd(const void* x, const float* w, const float* bia
   dim3 grid(l.gx, l.gy);
   cudaStream_t st = (cudaStream_t)stream;
   if (stride == 1 && dil == 1)
-    depthwise3x3_kernel<true><<<grid, kThreads, 0, st>>>((const bf16*)x, w, bias, (const bf16*)mask, (bf16*)y, s, l.tx,
-                                                         l.ty, relu_in, relu_out);
+    {
+      cudaError_t _le = tdl::launch_pdl(depthwise3x3_kernel<true>, dim3(grid), dim3(kThreads), 0, st, (const bf16*)x, w, bias, (const bf16*)mask, (bf16*)y, s, l.tx, l.ty, relu_in, relu_out);
+      if (_le != cudaSuccess) return tdl::cuda_fail(_le, "depthwise3x3_kernel");
+    }
   else
-    depthwise3x3_kernel<false><<<grid, kThreads, 0, st>>>((const bf16*)x, w, bias, (const bf16*)mask, (bf16*)y, s, l.tx,
-                                                          l.ty, relu_in, relu_out);
+    {
+      cudaError_t _le = tdl::launch_pdl(depthwise3x3_kernel<false>, dim3(grid), dim3(kThreads), 0, st, (const bf16*)x, w, bias, (const bf16*)mask, (bf16*)y, s, l.tx, l.ty, relu_in, relu_out);
+      if (_le != cudaSuccess) return tdl::cuda_fail(_le, "depthwise3x3_kernel");
+    }
   TDL_LAUNCH_OK("depthwise3x3_kernel");
   return 0;
 }
@@ -343,8 +353,10 @@ TDL_API int tdl_depthwise3x3_dgrad_s2(const void* dy, const float* w, const void
   TDL_REQUIRE(N <= 65535 && (int64_t)H * W * C < (1ll << 31), "shape too large for the strided depthwise dgrad kernel");
   if ((int64_t)N * H * W == 0) return 0;
   dim3 grid((unsigned)cdiv((int64_t)H * W * (C / 8), kThreads), (unsigned)N);
-  depthwise3x3_dgrad_strided_kernel<2><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
-      (const bf16*)dy, w, (const bf16*)xmask, (bf16*)dx, H, W, C, P, Q, pad_h, pad_w);
+  {
+    cudaError_t _le = tdl::launch_pdl(depthwise3x3_dgrad_strided_kernel<2>, dim3(grid), dim3(kThreads), 0, (cudaStream_t)stream, (const bf16*)dy, w, (const bf16*)xmask, (bf16*)dx, H, W, C, P, Q, pad_h, pad_w);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "depthwise3x3_dgrad_strided_kernel");
+  }
   TDL_LAUNCH_OK("depthwise3x3_dgrad_strided_kernel");
   return 0;
 }
@@ -362,11 +374,15 @@ TDL_API int tdl_depthwise3x3_wgrad(const void* x, const void* dy, const void* ym
   cudaStream_t st = (cudaStream_t)stream;
   const size_t smem = (size_t)kThreads * 4 * sizeof(float);
   if (stride == 1 && dil == 1)
-    depthwise3x3_wgrad_kernel<true><<<grid, kThreads, smem, st>>>((const bf16*)x, (const bf16*)dy, (const bf16*)ymask,
-                                                                  dw, dbias, s, l.tx, l.ty, relu_in);
+    {
+      cudaError_t _le = tdl::launch_pdl(depthwise3x3_wgrad_kernel<true>, dim3(grid), dim3(kThreads), smem, st, (const bf16*)x, (const bf16*)dy, (const bf16*)ymask, dw, dbias, s, l.tx, l.ty, relu_in);
+      if (_le != cudaSuccess) return tdl::cuda_fail(_le, "depthwise3x3_wgrad_kernel");
+    }
   else
-    depthwise3x3_wgrad_kernel<false><<<grid, kThreads, smem, st>>>((const bf16*)x, (const bf16*)dy, (const bf16*)ymask,
-                                                                   dw, dbias, s, l.tx, l.ty, relu_in);
+    {
+      cudaError_t _le = tdl::launch_pdl(depthwise3x3_wgrad_kernel<false>, dim3(grid), dim3(kThreads), smem, st, (const bf16*)x, (const bf16*)dy, (const bf16*)ymask, dw, dbias, s, l.tx, l.ty, relu_in);
+      if (_le != cudaSuccess) return tdl::cuda_fail(_le, "depthwise3x3_wgrad_kernel");
+    }
   TDL_LAUNCH_OK("depthwise3x3_wgrad_kernel");
   return 0;
 }
@@ -484,6 +500,8 @@ depthwise3x3_tma_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
                         const float* __restrict__ w, const float* __restrict__ bias, int has_mask,
                         bf16* __restrict__ y, const TShape s, int stages, int relu_in, int relu_out,
                         float* __restrict__ stats) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int x_bytes = ((s.BH * s.BW * 128 + 1023) / 1024) * 1024;
@@ -650,6 +668,8 @@ __global__ void __launch_bounds__(kT)
 depthwise3x3_tma_wgrad_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_dy,
                               float* __restrict__ dw, float* __restrict__ dbias, const TShape s, int stages,
                               int relu_in) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int x_bytes = ((s.BH * s.BW * 128 + 1023) / 1024) * 1024;
@@ -826,7 +846,9 @@ TDL_API int tdl_depthwise3x3_tma_wgrad(const void* x, const void* dy, float* dw,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));                    \
       attr = true;                                                                                                   \
     }                                                                                                                \
-    depthwise3x3_tma_wgrad_kernel<S, D><<<grid, kT, smem, st>>>(tmx, tmg, dw, dbias, s, stages, relu_in);             \
+    cudaError_t _le = tdl::launch_pdl(depthwise3x3_tma_wgrad_kernel<S, D>, dim3(grid), dim3(kT), smem, st, tmx, tmg, dw,  \
+                                      dbias, s, stages, relu_in);                                                    \
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "depthwise3x3_tma_wgrad_kernel");                             \
   } while (0)
   if (stride == 1 && dil == 1) TDL_DWW_LAUNCH(1, 1);
   else if (stride == 1) TDL_DWW_LAUNCH(1, 2);
@@ -879,8 +901,9 @@ static int depthwise3x3_tma_fwd_impl(const void* x, const float* w, const float*
                                        200 * 1024));                                                                 \
       attr = true;                                                                                                   \
     }                                                                                                                \
-    depthwise3x3_tma_kernel<S, D><<<grid, kT, smem, st>>>(tm, tmm, w, bias, has_mask, (tdl::bf16*)y, s, stages,       \
-                                                          relu_in, relu_out, stats);                                 \
+    cudaError_t _le = tdl::launch_pdl(depthwise3x3_tma_kernel<S, D>, dim3(grid), dim3(kT), smem, st, tm, tmm, w, bias,     \
+                                      has_mask, (tdl::bf16*)y, s, stages, relu_in, relu_out, stats);                 \
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "depthwise3x3_tma_kernel");                                   \
   } while (0)
   if (stride == 1 && dil == 1) TDL_DW_LAUNCH(1, 1);
   else if (stride == 1) TDL_DW_LAUNCH(1, 2);

@@ -43,6 +43,8 @@ template <int IPT>
 __global__ void __launch_bounds__(kLovaszThreads)
 lovasz_hinge_kernel(const float* __restrict__ logits, const float* __restrict__ labels, int P, float grad_scale,
                     float* __restrict__ loss_out, float* __restrict__ dlogits) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   extern __shared__ uint8_t lv_smem[];
   constexpr int T = kLovaszThreads;
   unsigned long long* skey = reinterpret_cast<unsigned long long*>(lv_smem);  // [IPT][T]
@@ -191,7 +193,10 @@ static int launch_lovasz(const float* logits, const float* labels, int B, int P,
     TDL_CUDA_OK(cudaFuncSetAttribute(lovasz_hinge_kernel<IPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     attr_set = true;
   }
-  lovasz_hinge_kernel<IPT><<<B, kLovaszThreads, smem, st>>>(logits, labels, P, grad_scale, loss_out, dlogits);
+  {
+    cudaError_t _le = tdl::launch_pdl(lovasz_hinge_kernel<IPT>, dim3(B), dim3(kLovaszThreads), smem, st, logits, labels, P, grad_scale, loss_out, dlogits);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "lovasz_hinge_kernel");
+  }
   TDL_LAUNCH_OK("lovasz_hinge_kernel");
   return 0;
 }
@@ -202,6 +207,8 @@ static int launch_lovasz(const float* logits, const float* labels, int B, int P,
 __global__ void __launch_bounds__(256)
 seg_metrics_kernel(const float* __restrict__ logits, const float* __restrict__ labels, int P, float logit_thr,
                    int reference_compat, float* __restrict__ iou_out, float* __restrict__ acc_out) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   __shared__ int red[4][8];
   const int img = blockIdx.x;
   int tp = 0, fp = 0, fn = 0, ok = 0;
@@ -243,6 +250,8 @@ __global__ void __launch_bounds__(256)
 softmax_ce_kernel(const float* __restrict__ logits, const long long* __restrict__ labels, int rows, int classes,
                   float grad_scale, int topk, float* __restrict__ loss_rows, float* __restrict__ dlogits,
                   float* __restrict__ top1, float* __restrict__ topk_out) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (row >= rows) return;
@@ -302,8 +311,10 @@ TDL_API int tdl_lovasz_hinge(const float* logits, const float* labels, int B, in
 TDL_API int tdl_seg_metrics(const float* logits, const float* labels, int B, int P, float logit_threshold,
                             int reference_compat, float* iou_out, float* acc_out, void* stream) {
   if (B <= 0) return 0;
-  seg_metrics_kernel<<<B, 256, 0, (cudaStream_t)stream>>>(logits, labels, P, logit_threshold, reference_compat,
-                                                          iou_out, acc_out);
+  {
+    cudaError_t _le = tdl::launch_pdl(seg_metrics_kernel, dim3(B), dim3(256), 0, (cudaStream_t)stream, logits, labels, P, logit_threshold, reference_compat, iou_out, acc_out);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "seg_metrics_kernel");
+  }
   TDL_LAUNCH_OK("seg_metrics_kernel");
   return 0;
 }
@@ -312,8 +323,10 @@ TDL_API int tdl_softmax_ce(const float* logits, const void* labels_i64, int rows
                            int topk, float* loss_rows, float* dlogits, float* top1, float* topk_out, void* stream) {
   if (rows <= 0) return 0;
   const int warps = 8;
-  softmax_ce_kernel<<<(rows + warps - 1) / warps, warps * 32, 0, (cudaStream_t)stream>>>(
-      logits, (const long long*)labels_i64, rows, classes, grad_scale, topk, loss_rows, dlogits, top1, topk_out);
+  {
+    cudaError_t _le = tdl::launch_pdl(softmax_ce_kernel, dim3((rows + warps - 1) / warps), dim3(warps * 32), 0, (cudaStream_t)stream, logits, (const long long*)labels_i64, rows, classes, grad_scale, topk, loss_rows, dlogits, top1, topk_out);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "softmax_ce_kernel");
+  }
   TDL_LAUNCH_OK("softmax_ce_kernel");
   return 0;
 }

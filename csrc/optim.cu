@@ -17,6 +17,8 @@ constexpr int kThreads = 256;
 // lr_state[0] = scheduled lr, lr_state[1] = Adam lr_t (bias corrected), global_step += 1.
 __global__ void lr_schedule_kernel(long long* global_step, float base_lr, float decay_rate, float decay_steps,
                                    float beta1, float beta2, float* lr_state) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   const long long step = *global_step;  // value before this step's increment (tf.train.exponential_decay)
   float lr = base_lr;
   if (decay_steps > 0.f) lr = base_lr * powf(decay_rate, (float)step / decay_steps);
@@ -38,6 +40,8 @@ __global__ void __launch_bounds__(kThreads)
 sgd_momentum_kernel(float* __restrict__ p, G* __restrict__ g, float* __restrict__ mom, bf16* __restrict__ shadow,
                     int64_t n, const float* __restrict__ lr_state, float momentum, float weight_decay,
                     float grad_scale, int zero_grad) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   const float lr = lr_state[0];
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     float w = p[i];
@@ -56,6 +60,8 @@ __global__ void __launch_bounds__(kThreads)
 adam_kernel(float* __restrict__ p, G* __restrict__ g, float* __restrict__ m1, float* __restrict__ m2,
             bf16* __restrict__ shadow, int64_t n, const float* __restrict__ lr_state, float beta1, float beta2,
             float eps, float grad_scale, int zero_grad) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   const float lr_t = lr_state[1];
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     const float gr = load_grad<G>(g, i) * grad_scale;
@@ -71,6 +77,8 @@ adam_kernel(float* __restrict__ p, G* __restrict__ g, float* __restrict__ m1, fl
 }
 
 __global__ void cast_f32_to_bf16_kernel(const float* __restrict__ src, bf16* __restrict__ dst, int64_t n) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
     dst[i] = __float2bfloat16(src[i]);
 }
@@ -91,8 +99,10 @@ using namespace tdl::optim;
 
 TDL_API int tdl_lr_schedule_step(void* global_step_i64, float base_lr, float decay_rate, float decay_steps,
                                  float beta1, float beta2, float* lr_state, void* stream) {
-  lr_schedule_kernel<<<1, 1, 0, (cudaStream_t)stream>>>((long long*)global_step_i64, base_lr, decay_rate, decay_steps,
-                                                        beta1, beta2, lr_state);
+  {
+    cudaError_t _le = tdl::launch_pdl(lr_schedule_kernel, dim3(1), dim3(1), 0, (cudaStream_t)stream, (long long*)global_step_i64, base_lr, decay_rate, decay_steps, beta1, beta2, lr_state);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "lr_schedule_kernel");
+  }
   TDL_LAUNCH_OK("lr_schedule_kernel");
   return 0;
 }
@@ -103,13 +113,15 @@ TDL_API int tdl_sgd_momentum_flat(float* param, void* grad, float* mom, void* sh
   if (n <= 0) return 0;
   cudaStream_t st = (cudaStream_t)stream;
   if (grad_is_bf16)
-    sgd_momentum_kernel<bf16><<<blocks_for(n), kThreads, 0, st>>>(param, (bf16*)grad, mom, (bf16*)shadow_bf16, n,
-                                                                   lr_state, momentum, weight_decay, grad_scale,
-                                                                   zero_grad);
+    {
+      cudaError_t _le = tdl::launch_pdl(sgd_momentum_kernel<bf16>, dim3(blocks_for(n)), dim3(kThreads), 0, st, param, (bf16*)grad, mom, (bf16*)shadow_bf16, n, lr_state, momentum, weight_decay, grad_scale, zero_grad);
+      if (_le != cudaSuccess) return tdl::cuda_fail(_le, "sgd_momentum_kernel");
+    }
   else
-    sgd_momentum_kernel<float><<<blocks_for(n), kThreads, 0, st>>>(param, (float*)grad, mom, (bf16*)shadow_bf16, n,
-                                                                    lr_state, momentum, weight_decay, grad_scale,
-                                                                    zero_grad);
+    {
+      cudaError_t _le = tdl::launch_pdl(sgd_momentum_kernel<float>, dim3(blocks_for(n)), dim3(kThreads), 0, st, param, (float*)grad, mom, (bf16*)shadow_bf16, n, lr_state, momentum, weight_decay, grad_scale, zero_grad);
+      if (_le != cudaSuccess) return tdl::cuda_fail(_le, "sgd_momentum_kernel");
+    }
   TDL_LAUNCH_OK("sgd_momentum_kernel");
   return 0;
 }
@@ -120,18 +132,25 @@ TDL_API int tdl_adam_flat(float* param, void* grad, float* m1, float* m2, void* 
   if (n <= 0) return 0;
   cudaStream_t st = (cudaStream_t)stream;
   if (grad_is_bf16)
-    adam_kernel<bf16><<<blocks_for(n), kThreads, 0, st>>>(param, (bf16*)grad, m1, m2, (bf16*)shadow_bf16, n, lr_state,
-                                                           beta1, beta2, eps, grad_scale, zero_grad);
+    {
+      cudaError_t _le = tdl::launch_pdl(adam_kernel<bf16>, dim3(blocks_for(n)), dim3(kThreads), 0, st, param, (bf16*)grad, m1, m2, (bf16*)shadow_bf16, n, lr_state, beta1, beta2, eps, grad_scale, zero_grad);
+      if (_le != cudaSuccess) return tdl::cuda_fail(_le, "adam_kernel");
+    }
   else
-    adam_kernel<float><<<blocks_for(n), kThreads, 0, st>>>(param, (float*)grad, m1, m2, (bf16*)shadow_bf16, n,
-                                                            lr_state, beta1, beta2, eps, grad_scale, zero_grad);
+    {
+      cudaError_t _le = tdl::launch_pdl(adam_kernel<float>, dim3(blocks_for(n)), dim3(kThreads), 0, st, param, (float*)grad, m1, m2, (bf16*)shadow_bf16, n, lr_state, beta1, beta2, eps, grad_scale, zero_grad);
+      if (_le != cudaSuccess) return tdl::cuda_fail(_le, "adam_kernel");
+    }
   TDL_LAUNCH_OK("adam_kernel");
   return 0;
 }
 
 TDL_API int tdl_cast_f32_to_bf16(const float* src, void* dst, int64_t n, void* stream) {
   if (n <= 0) return 0;
-  cast_f32_to_bf16_kernel<<<blocks_for(n), kThreads, 0, (cudaStream_t)stream>>>(src, (bf16*)dst, n);
+  {
+    cudaError_t _le = tdl::launch_pdl(cast_f32_to_bf16_kernel, dim3(blocks_for(n)), dim3(kThreads), 0, (cudaStream_t)stream, src, (bf16*)dst, n);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "cast_f32_to_bf16_kernel");
+  }
   TDL_LAUNCH_OK("cast_f32_to_bf16_kernel");
   return 0;
 }

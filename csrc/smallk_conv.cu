@@ -30,6 +30,8 @@ __device__ __forceinline__ void load_weights_smem(const float* __restrict__ w, _
 __global__ void __launch_bounds__(kThreads)
 fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
            __nv_bfloat16* __restrict__ y, const Geo g) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __nv_bfloat16* sw = reinterpret_cast<__nv_bfloat16*>(smem_raw);
   const int taps = g.R * g.S;
@@ -78,6 +80,8 @@ fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w, con
 __global__ void __launch_bounds__(kThreads)
 bwd_data_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict__ w, __nv_bfloat16* __restrict__ dx,
                 const Geo g) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __nv_bfloat16* sw = reinterpret_cast<__nv_bfloat16*>(smem_raw);
   const int taps = g.R * g.S;
@@ -139,6 +143,8 @@ bwd_data_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict__ 
 __global__ void __launch_bounds__(kThreads)
 bwd_weight_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy, float* __restrict__ dw,
                   float* __restrict__ dbias, const Geo g) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   extern __shared__ __align__(16) unsigned char smem_raw[];
   float* sacc = reinterpret_cast<float*>(smem_raw);  // [taps][C]
   const int taps = g.R * g.S;
@@ -227,8 +233,10 @@ TDL_API int tdl_conv2d_smallk_fwd(const void* x, const float* w, const float* bi
   const size_t smem = (size_t)K * R * S * C * sizeof(__nv_bfloat16);
   TDL_REQUIRE(smem <= 200 * 1024, "weights do not fit in shared memory");
   TDL_CUDA_OK(cudaFuncSetAttribute(fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  fwd_kernel<<<grid_for((int64_t)N * P * Q, kThreads / 32), kThreads, smem, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)x, w, bias, (__nv_bfloat16*)y, g);
+  {
+    cudaError_t _le = tdl::launch_pdl(fwd_kernel, dim3(grid_for((int64_t)N * P * Q, kThreads / 32)), dim3(kThreads), smem, (cudaStream_t)stream, (const __nv_bfloat16*)x, w, bias, (__nv_bfloat16*)y, g);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "fwd_kernel");
+  }
   TDL_LAUNCH_OK("smallk conv fwd");
   return 0;
 }
@@ -240,8 +248,10 @@ TDL_API int tdl_conv2d_smallk_bwd_data(const void* dy, const float* w, void* dx,
   const size_t smem = (size_t)K * R * S * C * sizeof(__nv_bfloat16);
   TDL_REQUIRE(smem <= 200 * 1024, "weights do not fit in shared memory");
   TDL_CUDA_OK(cudaFuncSetAttribute(bwd_data_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  bwd_data_kernel<<<grid_for((int64_t)N * H * W, kThreads / 32), kThreads, smem, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)dy, w, (__nv_bfloat16*)dx, g);
+  {
+    cudaError_t _le = tdl::launch_pdl(bwd_data_kernel, dim3(grid_for((int64_t)N * H * W, kThreads / 32)), dim3(kThreads), smem, (cudaStream_t)stream, (const __nv_bfloat16*)dy, w, (__nv_bfloat16*)dx, g);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "bwd_data_kernel");
+  }
   TDL_LAUNCH_OK("smallk conv bwd data");
   return 0;
 }
@@ -258,8 +268,10 @@ TDL_API int tdl_conv2d_smallk_bwd_weight(const void* x, const void* dy, float* d
   const int groups = kThreads / (C / 8);
   int blocks = grid_for((int64_t)N * P * Q, groups * 16);
   if (blocks > num_sms() * 2) blocks = num_sms() * 2;
-  bwd_weight_kernel<<<blocks, kThreads, smem, (cudaStream_t)stream>>>((const __nv_bfloat16*)x,
-                                                                      (const __nv_bfloat16*)dy, dw, dbias, g);
+  {
+    cudaError_t _le = tdl::launch_pdl(bwd_weight_kernel, dim3(blocks), dim3(kThreads), smem, (cudaStream_t)stream, (const __nv_bfloat16*)x, (const __nv_bfloat16*)dy, dw, dbias, g);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "bwd_weight_kernel");
+  }
   TDL_LAUNCH_OK("smallk conv bwd weight");
   return 0;
 }

@@ -25,6 +25,8 @@ static int grid_for(int64_t work) {
 __global__ void __launch_bounds__(kThreads)
 maxpool_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, uint8_t* __restrict__ idx, int N, int H, int W,
                    int C, int P, int Q, int k, int stride, int pad_h, int pad_w) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   const int c8 = C / 8;
   const int64_t total = (int64_t)N * P * Q * c8;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -61,6 +63,8 @@ maxpool_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, uint8_t* __
 __global__ void __launch_bounds__(kThreads)
 maxpool_bwd_kernel(const bf16* __restrict__ dy, const uint8_t* __restrict__ idx, bf16* __restrict__ dx, int N, int H,
                    int W, int C, int P, int Q, int k, int stride, int pad_h, int pad_w) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   const int c8 = C / 8;
   const int64_t total = (int64_t)N * H * W * c8;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -105,6 +109,8 @@ template <int K, int S>
 __global__ void __launch_bounds__(kThreads)
 maxpool_fwd_rows_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, uint8_t* __restrict__ idx, int H, int W,
                         int C, int P, int Q, int pad_h, int pad_w) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   const int c8 = C >> 3;
   const int n = blockIdx.y;
   const bf16* xn = x + (int64_t)n * H * W * C;
@@ -156,6 +162,8 @@ template <int K, int S>
 __global__ void __launch_bounds__(kThreads)
 maxpool_bwd_block_kernel(const bf16* __restrict__ dy, const uint8_t* __restrict__ idx, bf16* __restrict__ dx, int H,
                          int W, int C, int P, int Q, int pad_h, int pad_w, int A, int B) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   constexpr int kCells = (K + S - 1) / S;
   const int c8 = C >> 3;
   const int n = blockIdx.y;
@@ -217,6 +225,8 @@ maxpool_bwd_block_kernel(const bf16* __restrict__ dy, const uint8_t* __restrict_
 // ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kThreads)
 gap_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, int HW, int C) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   __shared__ float sm[8][32][8];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int c8 = C / 8;
@@ -249,6 +259,8 @@ gap_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, int HW, int C) 
 
 __global__ void __launch_bounds__(kThreads)
 gap_bwd_kernel(const bf16* __restrict__ dy, bf16* __restrict__ dx, int64_t total_vec, int HW, int c8) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   const float inv = 1.f / (float)HW;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total_vec; i += (int64_t)gridDim.x * blockDim.x) {
     const int cv = (int)(i % c8);
@@ -268,6 +280,8 @@ __global__ void __launch_bounds__(kThreads)
 depthwise_fwd_kernel(const bf16* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
                      bf16* __restrict__ y, int N, int H, int W, int C, int P, int Q, int R, int S, int stride,
                      int dil, int pad_h, int pad_w, int relu) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   const int c8 = C / 8;
   const int64_t total = (int64_t)N * P * Q * c8;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -305,6 +319,8 @@ __global__ void __launch_bounds__(kThreads)
 depthwise_bwd_data_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ y, const float* __restrict__ w,
                           bf16* __restrict__ dx, int N, int H, int W, int C, int P, int Q, int R, int S, int stride,
                           int dil, int pad_h, int pad_w, int relu) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   const int c8 = C / 8;
   const int64_t total = (int64_t)N * H * W * c8;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -349,6 +365,8 @@ __global__ void __launch_bounds__(kThreads)
 depthwise_bwd_weight_kernel(const bf16* __restrict__ x, const bf16* __restrict__ dy, const bf16* __restrict__ y,
                             float* __restrict__ dw, float* __restrict__ dbias, int N, int H, int W, int C, int P,
                             int Q, int R, int S, int stride, int dil, int pad_h, int pad_w, int relu, int tx, int ty) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   extern __shared__ float sm[];  // [ty][tx][8]
   const int cx = threadIdx.x % tx;
   const int ry = threadIdx.x / tx;
@@ -452,6 +470,8 @@ __device__ __forceinline__ UpCoord up_coord(int o, int in, int out) {
 template <typename T>
 __global__ void __launch_bounds__(kThreads)
 upsample_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int N, int H, int W, int C, int OH, int OW) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   const int64_t total = (int64_t)N * OH * OW * C;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int c = (int)(i % C);
@@ -474,6 +494,8 @@ upsample_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int N, int H, in
 template <typename T>
 __global__ void __launch_bounds__(kThreads)
 upsample_bwd_kernel(const T* __restrict__ dy, float* __restrict__ dx, int N, int H, int W, int C, int OH, int OW) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   const int64_t total = (int64_t)N * OH * OW * C;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int c = (int)(i % C);
@@ -504,13 +526,15 @@ TDL_API int tdl_maxpool_fwd(const void* x, void* y, void* idx_u8, int N, int H, 
   const int64_t work = (int64_t)N * P * Q * (C / 8);
   if (work == 0) return 0;
   if (k == 3 && stride == 2 && N <= 65535 && (int64_t)P * Q * C < (1ll << 31))
-    maxpool_fwd_rows_kernel<3, 2><<<dim3((unsigned)cdiv((int64_t)P * Q * (C / 8), kThreads), N), kThreads, 0,
-                                    (cudaStream_t)stream>>>((const bf16*)x, (bf16*)y,
-                                                                               (uint8_t*)idx_u8, H, W, C, P, Q, pad_h,
-                                                                               pad_w);
+    {
+      cudaError_t _le = tdl::launch_pdl(maxpool_fwd_rows_kernel<3, 2>, dim3(dim3((unsigned)cdiv((int64_t)P * Q * (C / 8), kThreads), N)), dim3(kThreads), 0, (cudaStream_t)stream, (const bf16*)x, (bf16*)y, (uint8_t*)idx_u8, H, W, C, P, Q, pad_h, pad_w);
+      if (_le != cudaSuccess) return tdl::cuda_fail(_le, "maxpool_fwd_rows_kernel");
+    }
   else
-    maxpool_fwd_kernel<<<grid_for(work), kThreads, 0, (cudaStream_t)stream>>>((const bf16*)x, (bf16*)y, (uint8_t*)idx_u8,
-                                                                              N, H, W, C, P, Q, k, stride, pad_h, pad_w);
+    {
+      cudaError_t _le = tdl::launch_pdl(maxpool_fwd_kernel, dim3(grid_for(work)), dim3(kThreads), 0, (cudaStream_t)stream, (const bf16*)x, (bf16*)y, (uint8_t*)idx_u8, N, H, W, C, P, Q, k, stride, pad_h, pad_w);
+      if (_le != cudaSuccess) return tdl::cuda_fail(_le, "maxpool_fwd_kernel");
+    }
   TDL_LAUNCH_OK("maxpool_fwd_kernel");
   return 0;
 }
@@ -522,13 +546,15 @@ TDL_API int tdl_maxpool_bwd(const void* dy, const void* idx_u8, void* dx, int N,
   if (work == 0) return 0;
   if (k == 3 && stride == 2 && N <= 65535 && (int64_t)H * W * C < (1ll << 31)) {
     const int A = (H + pad_h + 1) / 2, B = (W + pad_w + 1) / 2;  // 2x2 pixel blocks on the window grid
-    maxpool_bwd_block_kernel<3, 2><<<dim3((unsigned)cdiv((int64_t)A * B * (C / 8), kThreads), N), kThreads, 0,
-                                     (cudaStream_t)stream>>>(
-        (const bf16*)dy, (const uint8_t*)idx_u8, (bf16*)dx, H, W, C, P, Q, pad_h, pad_w, A, B);
+    {
+      cudaError_t _le = tdl::launch_pdl(maxpool_bwd_block_kernel<3, 2>, dim3(dim3((unsigned)cdiv((int64_t)A * B * (C / 8), kThreads), N)), dim3(kThreads), 0, (cudaStream_t)stream, (const bf16*)dy, (const uint8_t*)idx_u8, (bf16*)dx, H, W, C, P, Q, pad_h, pad_w, A, B);
+      if (_le != cudaSuccess) return tdl::cuda_fail(_le, "maxpool_bwd_block_kernel");
+    }
   } else
-    maxpool_bwd_kernel<<<grid_for(work), kThreads, 0, (cudaStream_t)stream>>>((const bf16*)dy, (const uint8_t*)idx_u8,
-                                                                              (bf16*)dx, N, H, W, C, P, Q, k, stride,
-                                                                              pad_h, pad_w);
+    {
+      cudaError_t _le = tdl::launch_pdl(maxpool_bwd_kernel, dim3(grid_for(work)), dim3(kThreads), 0, (cudaStream_t)stream, (const bf16*)dy, (const uint8_t*)idx_u8, (bf16*)dx, N, H, W, C, P, Q, k, stride, pad_h, pad_w);
+      if (_le != cudaSuccess) return tdl::cuda_fail(_le, "maxpool_bwd_kernel");
+    }
   TDL_LAUNCH_OK("maxpool_bwd_kernel");
   return 0;
 }
@@ -537,7 +563,10 @@ TDL_API int tdl_gap_fwd(const void* x, void* y, int N, int HW, int C, void* stre
   TDL_REQUIRE(C % 8 == 0, "C must be a multiple of 8");
   if (N == 0) return 0;
   dim3 grid(N, (unsigned)cdiv(C / 8, 32));
-  gap_fwd_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>((const bf16*)x, (bf16*)y, HW, C);
+  {
+    cudaError_t _le = tdl::launch_pdl(gap_fwd_kernel, dim3(grid), dim3(kThreads), 0, (cudaStream_t)stream, (const bf16*)x, (bf16*)y, HW, C);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "gap_fwd_kernel");
+  }
   TDL_LAUNCH_OK("gap_fwd_kernel");
   return 0;
 }
@@ -546,7 +575,10 @@ TDL_API int tdl_gap_bwd(const void* dy, void* dx, int N, int HW, int C, void* st
   TDL_REQUIRE(C % 8 == 0, "C must be a multiple of 8");
   const int64_t total = (int64_t)N * HW * (C / 8);
   if (total == 0) return 0;
-  gap_bwd_kernel<<<grid_for(total), kThreads, 0, (cudaStream_t)stream>>>((const bf16*)dy, (bf16*)dx, total, HW, C / 8);
+  {
+    cudaError_t _le = tdl::launch_pdl(gap_bwd_kernel, dim3(grid_for(total)), dim3(kThreads), 0, (cudaStream_t)stream, (const bf16*)dy, (bf16*)dx, total, HW, C / 8);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "gap_bwd_kernel");
+  }
   TDL_LAUNCH_OK("gap_bwd_kernel");
   return 0;
 }
@@ -557,8 +589,10 @@ TDL_API int tdl_depthwise_fwd(const void* x, const float* w, const float* bias, 
   TDL_REQUIRE(C % 8 == 0, "C must be a multiple of 8");
   const int64_t work = (int64_t)N * P * Q * (C / 8);
   if (work == 0) return 0;
-  depthwise_fwd_kernel<<<grid_for(work), kThreads, 0, (cudaStream_t)stream>>>(
-      (const bf16*)x, w, bias, (bf16*)y, N, H, W, C, P, Q, R, S, stride, dil, pad_h, pad_w, relu);
+  {
+    cudaError_t _le = tdl::launch_pdl(depthwise_fwd_kernel, dim3(grid_for(work)), dim3(kThreads), 0, (cudaStream_t)stream, (const bf16*)x, w, bias, (bf16*)y, N, H, W, C, P, Q, R, S, stride, dil, pad_h, pad_w, relu);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "depthwise_fwd_kernel");
+  }
   TDL_LAUNCH_OK("depthwise_fwd_kernel");
   return 0;
 }
@@ -573,9 +607,10 @@ TDL_API int tdl_depthwise_bwd(const void* x, const float* w, const void* dy, con
   if (dx) {
     const int64_t work = (int64_t)N * H * W * (C / 8);
     if (work)
-      depthwise_bwd_data_kernel<<<grid_for(work), kThreads, 0, st>>>((const bf16*)dy, (const bf16*)y, w, (bf16*)dx, N,
-                                                                     H, W, C, P, Q, R, S, stride, dil, pad_h, pad_w,
-                                                                     relu);
+      {
+        cudaError_t _le = tdl::launch_pdl(depthwise_bwd_data_kernel, dim3(grid_for(work)), dim3(kThreads), 0, st, (const bf16*)dy, (const bf16*)y, w, (bf16*)dx, N, H, W, C, P, Q, R, S, stride, dil, pad_h, pad_w, relu);
+        if (_le != cudaSuccess) return tdl::cuda_fail(_le, "depthwise_bwd_data_kernel");
+      }
     TDL_LAUNCH_OK("depthwise_bwd_data_kernel");
   }
   if (dw) {
@@ -590,9 +625,10 @@ TDL_API int tdl_depthwise_bwd(const void* x, const float* w, const void* dy, con
     if (gx > cap) gx = cap;
     if (gx < 1) gx = 1;
     dim3 grid((unsigned)gx, gy);
-    depthwise_bwd_weight_kernel<<<grid, kThreads, kThreads * 8 * sizeof(float), st>>>(
-        (const bf16*)x, (const bf16*)dy, (const bf16*)y, dw, dbias, N, H, W, C, P, Q, R, S, stride, dil, pad_h, pad_w,
-        relu, tx, ty);
+    {
+      cudaError_t _le = tdl::launch_pdl(depthwise_bwd_weight_kernel, dim3(grid), dim3(kThreads), kThreads * 8 * sizeof(float), st, (const bf16*)x, (const bf16*)dy, (const bf16*)y, dw, dbias, N, H, W, C, P, Q, R, S, stride, dil, pad_h, pad_w, relu, tx, ty);
+      if (_le != cudaSuccess) return tdl::cuda_fail(_le, "depthwise_bwd_weight_kernel");
+    }
     TDL_LAUNCH_OK("depthwise_bwd_weight_kernel");
   }
   return 0;
@@ -603,11 +639,15 @@ TDL_API int tdl_upsample_fwd(const void* x, void* y, int N, int H, int W, int C,
   const int64_t total = (int64_t)N * OH * OW * C;
   if (total == 0) return 0;
   if (is_bf16)
-    upsample_fwd_kernel<bf16><<<grid_for(total), kThreads, 0, (cudaStream_t)stream>>>((const bf16*)x, (bf16*)y, N, H, W,
-                                                                                     C, OH, OW);
+    {
+      cudaError_t _le = tdl::launch_pdl(upsample_fwd_kernel<bf16>, dim3(grid_for(total)), dim3(kThreads), 0, (cudaStream_t)stream, (const bf16*)x, (bf16*)y, N, H, W, C, OH, OW);
+      if (_le != cudaSuccess) return tdl::cuda_fail(_le, "upsample_fwd_kernel");
+    }
   else
-    upsample_fwd_kernel<float><<<grid_for(total), kThreads, 0, (cudaStream_t)stream>>>((const float*)x, (float*)y, N,
-                                                                                      H, W, C, OH, OW);
+    {
+      cudaError_t _le = tdl::launch_pdl(upsample_fwd_kernel<float>, dim3(grid_for(total)), dim3(kThreads), 0, (cudaStream_t)stream, (const float*)x, (float*)y, N, H, W, C, OH, OW);
+      if (_le != cudaSuccess) return tdl::cuda_fail(_le, "upsample_fwd_kernel");
+    }
   TDL_LAUNCH_OK("upsample_fwd_kernel");
   return 0;
 }
@@ -618,11 +658,15 @@ TDL_API int tdl_upsample_bwd(const void* dy, float* dx, int N, int H, int W, int
   const int64_t total = (int64_t)N * OH * OW * C;
   if (total == 0) return 0;
   if (is_bf16)
-    upsample_bwd_kernel<bf16><<<grid_for(total), kThreads, 0, (cudaStream_t)stream>>>((const bf16*)dy, dx, N, H, W, C,
-                                                                                     OH, OW);
+    {
+      cudaError_t _le = tdl::launch_pdl(upsample_bwd_kernel<bf16>, dim3(grid_for(total)), dim3(kThreads), 0, (cudaStream_t)stream, (const bf16*)dy, dx, N, H, W, C, OH, OW);
+      if (_le != cudaSuccess) return tdl::cuda_fail(_le, "upsample_bwd_kernel");
+    }
   else
-    upsample_bwd_kernel<float><<<grid_for(total), kThreads, 0, (cudaStream_t)stream>>>((const float*)dy, dx, N, H, W,
-                                                                                      C, OH, OW);
+    {
+      cudaError_t _le = tdl::launch_pdl(upsample_bwd_kernel<float>, dim3(grid_for(total)), dim3(kThreads), 0, (cudaStream_t)stream, (const float*)dy, dx, N, H, W, C, OH, OW);
+      if (_le != cudaSuccess) return tdl::cuda_fail(_le, "upsample_bwd_kernel");
+    }
   TDL_LAUNCH_OK("upsample_bwd_kernel");
   return 0;
 }
@@ -635,6 +679,8 @@ namespace spatial {
 __global__ void __launch_bounds__(kThreads)
 u8_to_bf16_kernel(const uint8_t* __restrict__ x, bf16* __restrict__ y, int64_t pixels, int C, int Cpad,
                   const float* __restrict__ mean, const float* __restrict__ inv_std) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   const int64_t total = pixels * Cpad;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int c = (int)(i % Cpad);
@@ -652,8 +698,10 @@ TDL_API int tdl_u8_to_bf16_normalize(const void* x_u8, void* y_bf16, int64_t pix
   TDL_REQUIRE(Cpad >= C, "Cpad must be >= C");
   const int64_t total = pixels * Cpad;
   if (total == 0) return 0;
-  tdl::spatial::u8_to_bf16_kernel<<<tdl::spatial::grid_for(total), tdl::spatial::kThreads, 0, (cudaStream_t)stream>>>(
-      (const uint8_t*)x_u8, (tdl::bf16*)y_bf16, pixels, C, Cpad, mean, inv_std);
+  {
+    cudaError_t _le = tdl::launch_pdl(tdl::spatial::u8_to_bf16_kernel, dim3(tdl::spatial::grid_for(total)), dim3(tdl::spatial::kThreads), 0, (cudaStream_t)stream, (const uint8_t*)x_u8, (tdl::bf16*)y_bf16, pixels, C, Cpad, mean, inv_std);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "tdl::spatial::u8_to_bf16_kernel");
+  }
   TDL_LAUNCH_OK("u8_to_bf16_kernel");
   return 0;
 }
@@ -665,6 +713,8 @@ namespace tdl {
 namespace spatial {
 __global__ void __launch_bounds__(kThreads)
 colsum_kernel(const bf16* __restrict__ dy, float* __restrict__ out, int64_t rows, int C, int tx, int ty) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
   extern __shared__ float sm[];  // [ty][tx][8]
   const int c8 = C >> 3;
   const int cx = threadIdx.x % tx, ry = threadIdx.x / tx;
@@ -718,8 +768,10 @@ TDL_API int tdl_colsum_bf16(const void* dy, float* out, int64_t rows, int C, voi
   const int64_t cap = (int64_t)tdl::num_sms() * 4 / gy;
   if (gx > cap) gx = cap;
   if (gx < 1) gx = 1;
-  colsum_kernel<<<dim3((unsigned)gx, (unsigned)gy), kThreads, kThreads * 8 * sizeof(float), (cudaStream_t)stream>>>(
-      (const tdl::bf16*)dy, out, rows, C, tx, ty);
+  {
+    cudaError_t _le = tdl::launch_pdl(colsum_kernel, dim3(dim3((unsigned)gx, (unsigned)gy)), dim3(kThreads), kThreads * 8 * sizeof(float), (cudaStream_t)stream, (const tdl::bf16*)dy, out, rows, C, tx, ty);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "colsum_kernel");
+  }
   TDL_LAUNCH_OK("colsum_kernel");
   return 0;
 }

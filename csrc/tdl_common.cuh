@@ -111,6 +111,36 @@ inline int num_sms() {
 
 inline int64_t cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }
 
+// Programmatic dependent launch: the kernel may be scheduled while its predecessor in the stream is still draining
+// (every CTA of the predecessor has called pdl_trigger()); it runs its set-up and then blocks in pdl_wait() until the
+// predecessor grid has completed and flushed.  Removes the launch + drain gap between the ~500 small kernels of a
+// training step, also inside a captured CUDA graph.  Every kernel launched through here MUST call pdl_wait() before
+// its first global-memory access (transitivity of "my predecessor has finished" depends on it).  TDL_PDL=1 enables.
+inline bool pdl_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("TDL_PDL");
+    v = e ? atoi(e) : 0;  // opt-in until validated on hardware
+  }
+  return v != 0;
+}
+
+template <typename... KArgs, typename Stream, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, Stream st,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = (cudaStream_t)st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 }  // namespace tdl
 
 // ----------------------------------------------------------------------------------------
@@ -118,6 +148,11 @@ inline int64_t cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }
 // ----------------------------------------------------------------------------------------
 namespace tdl {
 namespace ptx {
+
+// Programmatic dependent launch (see tdl::launch_pdl): let the next kernel in the stream be scheduled / wait for the
+// previous one to have completed.  Both are no-ops for a kernel launched without the attribute.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
