@@ -115,7 +115,8 @@ TDL_API int tdl_augment_seg(const float* images, const float* masks, const float
   const int64_t cap = (int64_t)tdl::num_sms() * 8;
   if (blocks > cap) blocks = cap;
   {
-    cudaError_t _le = tdl::launch_pdl(tdl::augment::augment_seg_kernel, dim3((int)blocks), dim3(256), 0, (cudaStream_t)stream, images, masks, transforms, transposed, out, out_mask, B, p);
+    cudaError_t _le = tdl::launch_pdl(tdl::augment::augment_seg_kernel, dim3((int)blocks), dim3(256), 0,
+        (cudaStream_t)stream, images, masks, transforms, transposed, out, out_mask, B, p);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "tdl::augment::augment_seg_kernel");
   }
   TDL_LAUNCH_OK("augment_seg_kernel");

@@ -501,13 +501,16 @@ TDL_API int tdl_bn_fwd_stats(const void* x, int64_t rows, int C, float* scratch,
   cudaStream_t st = (cudaStream_t)stream;
   dim3 grid(s.gx, s.gy);
   {
-    cudaError_t _le = tdl::launch_pdl(bn_partial_stats_kernel, dim3(grid), dim3(kThreads), kThreads * 16 * sizeof(float), st, (const bf16*)x, rows, C, s.tx, s.ty, scratch);
+    cudaError_t _le = tdl::launch_pdl(bn_partial_stats_kernel, dim3(grid), dim3(kThreads),
+        kThreads * 16 * sizeof(float), st, (const bf16*)x, rows, C, s.tx, s.ty, scratch);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "bn_partial_stats_kernel");
   }
   TDL_LAUNCH_OK("bn_partial_stats_kernel");
   const double unbias = rows > 1 ? (double)rows / (double)(rows - 1) : 1.0;
   {
-    cudaError_t _le = tdl::launch_pdl(bn_finalize_stats_kernel, dim3((C + kFinCh - 1) / kFinCh), dim3(kFinThreads), 0, st, scratch, s.gx, C, 1.0 / (double)rows, unbias, gamma, beta, running_mean, running_var, decay, eps, mean, invstd, scale, shift);
+    cudaError_t _le = tdl::launch_pdl(bn_finalize_stats_kernel, dim3((C + kFinCh - 1) / kFinCh), dim3(kFinThreads), 0,
+        st, scratch, s.gx, C, 1.0 / (double)rows, unbias, gamma, beta, running_mean, running_var, decay, eps, mean,
+        invstd, scale, shift);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "bn_finalize_stats_kernel");
   }
   TDL_LAUNCH_OK("bn_finalize_stats_kernel");
@@ -522,7 +525,9 @@ TDL_API int tdl_bn_finalize_partials(const float* partial, int nparts, int64_t r
   TDL_REQUIRE(C > 0 && nparts > 0 && rows > 0, "bad arguments");
   const double unbias = rows > 1 ? (double)rows / (double)(rows - 1) : 1.0;
   {
-    cudaError_t _le = tdl::launch_pdl(bn_finalize_stats_kernel, dim3((C + kFinCh - 1) / kFinCh), dim3(kFinThreads), 0, (cudaStream_t)stream, partial, nparts, C, 1.0 / (double)rows, unbias, gamma, beta, running_mean, running_var, decay, eps, mean, invstd, scale, shift);
+    cudaError_t _le = tdl::launch_pdl(bn_finalize_stats_kernel, dim3((C + kFinCh - 1) / kFinCh), dim3(kFinThreads), 0,
+        (cudaStream_t)stream, partial, nparts, C, 1.0 / (double)rows, unbias, gamma, beta, running_mean, running_var,
+        decay, eps, mean, invstd, scale, shift);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "bn_finalize_stats_kernel");
   }
   TDL_LAUNCH_OK("bn_finalize_stats_kernel");
@@ -533,7 +538,8 @@ TDL_API int tdl_bn_infer_scale_shift(const float* gamma, const float* beta, cons
                                      const float* running_var, float eps, float* scale, float* shift, int C,
                                      void* stream) {
   {
-    cudaError_t _le = tdl::launch_pdl(bn_infer_scale_shift_kernel, dim3((C + 127) / 128), dim3(128), 0, (cudaStream_t)stream, gamma, beta, running_mean, running_var, eps, scale, shift, C);
+    cudaError_t _le = tdl::launch_pdl(bn_infer_scale_shift_kernel, dim3((C + 127) / 128), dim3(128), 0,
+        (cudaStream_t)stream, gamma, beta, running_mean, running_var, eps, scale, shift, C);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "bn_infer_scale_shift_kernel");
   }
   TDL_LAUNCH_OK("bn_infer_scale_shift_kernel");
@@ -550,7 +556,8 @@ TDL_API int tdl_bn_apply(const void* x, const float* scale, const float* shift, 
   ReduceShape s = apply_shape(rows, C);
   dim3 grid(s.gx, s.gy);
   {
-    cudaError_t _le = tdl::launch_pdl(bn_apply_kernel, dim3(grid), dim3(kThreads), 0, (cudaStream_t)stream, (const bf16*)x, scale, shift, (const bf16*)residual, (bf16*)y, (uint8_t*)mask_out, rows, C, s.tx, s.ty, relu);
+    cudaError_t _le = tdl::launch_pdl(bn_apply_kernel, dim3(grid), dim3(kThreads), 0, (cudaStream_t)stream,
+        (const bf16*)x, scale, shift, (const bf16*)residual, (bf16*)y, (uint8_t*)mask_out, rows, C, s.tx, s.ty, relu);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "bn_apply_kernel");
   }
   TDL_LAUNCH_OK("bn_apply_kernel");
@@ -569,12 +576,15 @@ TDL_API int tdl_bn_bwd_reduce(const void* dz, const void* x, const void* z, int 
   cudaStream_t st = (cudaStream_t)stream;
   dim3 grid(s.gx, s.gy);
   {
-    cudaError_t _le = tdl::launch_pdl(bn_bwd_partial_kernel, dim3(grid), dim3(kThreads), kThreads * 16 * sizeof(float), st, (const bf16*)dz, (const bf16*)x, (const bf16*)z, scale, shift, mean, invstd, rows, C, s.tx, s.ty, relu, z_is_bitmask, scratch);
+    cudaError_t _le = tdl::launch_pdl(bn_bwd_partial_kernel, dim3(grid), dim3(kThreads),
+        kThreads * 16 * sizeof(float), st, (const bf16*)dz, (const bf16*)x, (const bf16*)z, scale, shift, mean,
+        invstd, rows, C, s.tx, s.ty, relu, z_is_bitmask, scratch);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "bn_bwd_partial_kernel");
   }
   TDL_LAUNCH_OK("bn_bwd_partial_kernel");
   {
-    cudaError_t _le = tdl::launch_pdl(bn_bwd_finalize_kernel, dim3((C + kFinCh - 1) / kFinCh), dim3(kFinThreads), 0, st, scratch, s.gx, C, dbeta, dgamma, acc_dbeta, acc_dgamma);
+    cudaError_t _le = tdl::launch_pdl(bn_bwd_finalize_kernel, dim3((C + kFinCh - 1) / kFinCh), dim3(kFinThreads), 0,
+        st, scratch, s.gx, C, dbeta, dgamma, acc_dbeta, acc_dgamma);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "bn_bwd_finalize_kernel");
   }
   TDL_LAUNCH_OK("bn_bwd_finalize_kernel");
@@ -587,7 +597,8 @@ TDL_API int tdl_bn_bwd_finalize_partials(const float* partial, int nparts, int C
                                          float* acc_dgamma, float* acc_dbeta, void* stream) {
   TDL_REQUIRE(C > 0 && nparts > 0, "bad shape");
   {
-    cudaError_t _le = tdl::launch_pdl(bn_bwd_finalize_kernel, dim3((C + kFinCh - 1) / kFinCh), dim3(kFinThreads), 0, (cudaStream_t)stream, partial, nparts, C, dbeta, dgamma, acc_dbeta, acc_dgamma);
+    cudaError_t _le = tdl::launch_pdl(bn_bwd_finalize_kernel, dim3((C + kFinCh - 1) / kFinCh), dim3(kFinThreads), 0,
+        (cudaStream_t)stream, partial, nparts, C, dbeta, dgamma, acc_dbeta, acc_dgamma);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "bn_bwd_finalize_kernel");
   }
   TDL_LAUNCH_OK("bn_bwd_finalize_kernel");
@@ -602,7 +613,9 @@ TDL_API int tdl_bn_bwd_apply(const void* dz, const void* x, const void* z, int z
   ReduceShape s = apply_shape(rows, C);
   dim3 grid(s.gx, s.gy);
   {
-    cudaError_t _le = tdl::launch_pdl(bn_bwd_apply_kernel, dim3(grid), dim3(kThreads), 0, (cudaStream_t)stream, (const bf16*)dz, (const bf16*)x, (const bf16*)z, scale, shift, mean, invstd, dbeta, dgamma, 1.f / (float)rows, (bf16*)dx, (bf16*)dres, rows, C, s.tx, s.ty, relu, z_is_bitmask);
+    cudaError_t _le = tdl::launch_pdl(bn_bwd_apply_kernel, dim3(grid), dim3(kThreads), 0, (cudaStream_t)stream,
+        (const bf16*)dz, (const bf16*)x, (const bf16*)z, scale, shift, mean, invstd, dbeta, dgamma, 1.f / (float)rows,
+        (bf16*)dx, (bf16*)dres, rows, C, s.tx, s.ty, relu, z_is_bitmask);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "bn_bwd_apply_kernel");
   }
   TDL_LAUNCH_OK("bn_bwd_apply_kernel");
@@ -684,13 +697,16 @@ TDL_API int tdl_bn_fwd_stats_noalloc(const void* x, int64_t rows, int C, const f
   cudaStream_t st = (cudaStream_t)stream;
   dim3 grid(s.gx, s.gy);
   {
-    cudaError_t _le = tdl::launch_pdl(bn_partial_stats_kernel, dim3(grid), dim3(kThreads), kThreads * 16 * sizeof(float), st, (const bf16*)x, rows, C, s.tx, s.ty, scratch);
+    cudaError_t _le = tdl::launch_pdl(bn_partial_stats_kernel, dim3(grid), dim3(kThreads),
+        kThreads * 16 * sizeof(float), st, (const bf16*)x, rows, C, s.tx, s.ty, scratch);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "bn_partial_stats_kernel");
   }
   TDL_LAUNCH_OK("bn_partial_stats_kernel");
   const double unbias = rows > 1 ? (double)rows / (double)(rows - 1) : 1.0;
   {
-    cudaError_t _le = tdl::launch_pdl(bn_finalize_stats_kernel, dim3((C + kFinCh - 1) / kFinCh), dim3(kFinThreads), 0, st, scratch, s.gx, C, 1.0 / (double)rows, unbias, gamma, beta, running_mean, running_var, decay, eps, mean, invstd, scale, shift);
+    cudaError_t _le = tdl::launch_pdl(bn_finalize_stats_kernel, dim3((C + kFinCh - 1) / kFinCh), dim3(kFinThreads), 0,
+        st, scratch, s.gx, C, 1.0 / (double)rows, unbias, gamma, beta, running_mean, running_var, decay, eps, mean,
+        invstd, scale, shift);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "bn_finalize_stats_kernel");
   }
   TDL_LAUNCH_OK("bn_finalize_stats_kernel");

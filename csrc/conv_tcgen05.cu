@@ -1100,7 +1100,8 @@ static int launch_stem(const CUtensorMap& tx, const CUtensorMap& tw, const CUten
   const int grid = total < tdl::num_sms() ? total : tdl::num_sms();
   if (nparts) *nparts = grid;
   {
-    cudaError_t _le = tdl::launch_pdl(conv_fprop_kernel<64, false, kStats, true>, dim3(grid), dim3(kFpropThreads), Cfg::kSmemBytes, st, tx, tw, ty, ty, ty, ty, g, nullptr, nullptr, stats);
+    cudaError_t _le = tdl::launch_pdl(conv_fprop_kernel<64, false, kStats, true>, dim3(grid), dim3(kFpropThreads),
+        Cfg::kSmemBytes, st, tx, tw, ty, ty, ty, ty, g, nullptr, nullptr, stats);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "conv_fprop_kernel");
   }
   TDL_LAUNCH_OK("conv_fprop_kernel(stem)");
@@ -1310,7 +1311,8 @@ const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& ty, const CUten
   const int grid = total < tdl::num_sms() ? total : tdl::num_sms();
   if (nparts) *nparts = grid;
   {
-    cudaError_t _le = tdl::launch_pdl(conv_fprop_kernel<BLOCK_N, kFused, kStats, false, kResMma, kBwdStats>, dim3(grid), dim3(kFpropThreads), Cfg::kSmemBytes, st, tx, tw, ty, tres, tid, tbx, g, bias, res, stats);
+    cudaError_t _le = tdl::launch_pdl(conv_fprop_kernel<BLOCK_N, kFused, kStats, false, kResMma, kBwdStats>,
+        dim3(grid), dim3(kFpropThreads), Cfg::kSmemBytes, st, tx, tw, ty, tres, tid, tbx, g, bias, res, stats);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "conv_fprop_kernel");
   }
   TDL_LAUNCH_OK("conv_fprop_kernel");
@@ -1409,7 +1411,8 @@ static int launch_wgrad(const CUtensorMap& tdy, const CUtensorMap& tx, const Geo
   if (splits < 1) splits = 1;
   dim3 grid(splits, items);
   {
-    cudaError_t _le = tdl::launch_pdl(conv_wgrad_kernel<MT, BLOCK_N, TP>, dim3(grid), dim3(kThreads), Cfg::kSmemBytes, st, tdy, tx, g, dw, m_tiles, n_tiles);
+    cudaError_t _le = tdl::launch_pdl(conv_wgrad_kernel<MT, BLOCK_N, TP>, dim3(grid), dim3(kThreads), Cfg::kSmemBytes,
+        st, tdy, tx, g, dw, m_tiles, n_tiles);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "conv_wgrad_kernel");
   }
   TDL_LAUNCH_OK("conv_wgrad_kernel");
@@ -1705,7 +1708,8 @@ TDL_API int tdl_conv2d_weight_prep(const float* w, void* w_fprop, void* w_dgrad,
   if (w_dgrad != nullptr && taps <= 65535 && cdiv(K, 32) <= 65535) {
     dim3 grid((unsigned)cdiv(C, 32), (unsigned)cdiv(K, 32), (unsigned)taps);
     {
-      cudaError_t _le = tdl::launch_pdl(weight_prep_tiled_kernel, dim3(grid), dim3(dim3(32, 8)), 0, (cudaStream_t)stream, w, (bf16*)w_fprop, (bf16*)w_dgrad, K, taps, C);
+      cudaError_t _le = tdl::launch_pdl(weight_prep_tiled_kernel, dim3(grid), dim3(dim3(32, 8)), 0,
+          (cudaStream_t)stream, w, (bf16*)w_fprop, (bf16*)w_dgrad, K, taps, C);
       if (_le != cudaSuccess) return tdl::cuda_fail(_le, "weight_prep_tiled_kernel");
     }
     TDL_LAUNCH_OK("weight_prep_tiled_kernel");
@@ -1714,7 +1718,8 @@ TDL_API int tdl_conv2d_weight_prep(const float* w, void* w_fprop, void* w_dgrad,
   int blocks = (int)cdiv((int64_t)total, 256);
   if (blocks > 4 * num_sms()) blocks = 4 * num_sms();
   {
-    cudaError_t _le = tdl::launch_pdl(weight_prep_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, w, (bf16*)w_fprop, (bf16*)w_dgrad, K, taps, C);
+    cudaError_t _le = tdl::launch_pdl(weight_prep_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, w,
+        (bf16*)w_fprop, (bf16*)w_dgrad, K, taps, C);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "weight_prep_kernel");
   }
   TDL_LAUNCH_OK("weight_prep_kernel");
@@ -1737,7 +1742,8 @@ TDL_API int tdl_conv_stem_pack(const void* x, void* planes, int N, int H, int W,
   int64_t blocks = cdiv(total, 256);
   if (blocks > (int64_t)num_sms() * 16) blocks = (int64_t)num_sms() * 16;
   {
-    cudaError_t _le = tdl::launch_pdl(stem_pack_kernel, dim3((int)blocks), dim3(256), 0, (cudaStream_t)stream, (const bf16*)x, (bf16*)planes, N, H, W, C, H2, W2);
+    cudaError_t _le = tdl::launch_pdl(stem_pack_kernel, dim3((int)blocks), dim3(256), 0, (cudaStream_t)stream,
+        (const bf16*)x, (bf16*)planes, N, H, W, C, H2, W2);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "stem_pack_kernel");
   }
   TDL_LAUNCH_OK("stem_pack_kernel");
@@ -1760,7 +1766,8 @@ TDL_API int tdl_conv_stem_weight_prep(const float* w, void* w_packed, int K, int
   stem_taps(S, pad_w, &tw, &p2w);
   const int total = K * th * tw * 16;
   {
-    cudaError_t _le = tdl::launch_pdl(stem_weight_prep_kernel, dim3((int)cdiv(total, 256)), dim3(256), 0, (cudaStream_t)stream, w, (bf16*)w_packed, K, R, S, C, th, tw, pad_h, pad_w, p2h, p2w);
+    cudaError_t _le = tdl::launch_pdl(stem_weight_prep_kernel, dim3((int)cdiv(total, 256)), dim3(256), 0,
+        (cudaStream_t)stream, w, (bf16*)w_packed, K, R, S, C, th, tw, pad_h, pad_w, p2h, p2w);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "stem_weight_prep_kernel");
   }
   TDL_LAUNCH_OK("stem_weight_prep_kernel");
@@ -1892,7 +1899,8 @@ TDL_API int tdl_conv_stem_wgrad(const void* planes, const void* dy, float* dwp_s
   TDL_LAUNCH_OK("stem_wgrad_kernel");
   const int n_out = K * R * S * C;
   {
-    cudaError_t _le = tdl::launch_pdl(stem_wgrad_unpack_kernel, dim3((int)cdiv(n_out, 256)), dim3(256), 0, st, dwp_scratch, dw, K, R, S, C, th, tw, pad_h, pad_w, p2h, p2w, accumulate);
+    cudaError_t _le = tdl::launch_pdl(stem_wgrad_unpack_kernel, dim3((int)cdiv(n_out, 256)), dim3(256), 0, st,
+        dwp_scratch, dw, K, R, S, C, th, tw, pad_h, pad_w, p2h, p2w, accumulate);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "stem_wgrad_unpack_kernel");
   }
   TDL_LAUNCH_OK("stem_wgrad_unpack_kernel");

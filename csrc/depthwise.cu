@@ -333,12 +333,14 @@ TDL_API int tdl_depthwise3x3_fwd(const void* x, const float* w, const float* bia
   cudaStream_t st = (cudaStream_t)stream;
   if (stride == 1 && dil == 1)
     {
-      cudaError_t _le = tdl::launch_pdl(depthwise3x3_kernel<true>, dim3(grid), dim3(kThreads), 0, st, (const bf16*)x, w, bias, (const bf16*)mask, (bf16*)y, s, l.tx, l.ty, relu_in, relu_out);
+      cudaError_t _le = tdl::launch_pdl(depthwise3x3_kernel<true>, dim3(grid), dim3(kThreads), 0, st, (const bf16*)x,
+          w, bias, (const bf16*)mask, (bf16*)y, s, l.tx, l.ty, relu_in, relu_out);
       if (_le != cudaSuccess) return tdl::cuda_fail(_le, "depthwise3x3_kernel");
     }
   else
     {
-      cudaError_t _le = tdl::launch_pdl(depthwise3x3_kernel<false>, dim3(grid), dim3(kThreads), 0, st, (const bf16*)x, w, bias, (const bf16*)mask, (bf16*)y, s, l.tx, l.ty, relu_in, relu_out);
+      cudaError_t _le = tdl::launch_pdl(depthwise3x3_kernel<false>, dim3(grid), dim3(kThreads), 0, st, (const bf16*)x,
+          w, bias, (const bf16*)mask, (bf16*)y, s, l.tx, l.ty, relu_in, relu_out);
       if (_le != cudaSuccess) return tdl::cuda_fail(_le, "depthwise3x3_kernel");
     }
   TDL_LAUNCH_OK("depthwise3x3_kernel");
@@ -354,7 +356,8 @@ TDL_API int tdl_depthwise3x3_dgrad_s2(const void* dy, const float* w, const void
   if ((int64_t)N * H * W == 0) return 0;
   dim3 grid((unsigned)cdiv((int64_t)H * W * (C / 8), kThreads), (unsigned)N);
   {
-    cudaError_t _le = tdl::launch_pdl(depthwise3x3_dgrad_strided_kernel<2>, dim3(grid), dim3(kThreads), 0, (cudaStream_t)stream, (const bf16*)dy, w, (const bf16*)xmask, (bf16*)dx, H, W, C, P, Q, pad_h, pad_w);
+    cudaError_t _le = tdl::launch_pdl(depthwise3x3_dgrad_strided_kernel<2>, dim3(grid), dim3(kThreads), 0,
+        (cudaStream_t)stream, (const bf16*)dy, w, (const bf16*)xmask, (bf16*)dx, H, W, C, P, Q, pad_h, pad_w);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "depthwise3x3_dgrad_strided_kernel");
   }
   TDL_LAUNCH_OK("depthwise3x3_dgrad_strided_kernel");
@@ -375,12 +378,14 @@ TDL_API int tdl_depthwise3x3_wgrad(const void* x, const void* dy, const void* ym
   const size_t smem = (size_t)kThreads * 4 * sizeof(float);
   if (stride == 1 && dil == 1)
     {
-      cudaError_t _le = tdl::launch_pdl(depthwise3x3_wgrad_kernel<true>, dim3(grid), dim3(kThreads), smem, st, (const bf16*)x, (const bf16*)dy, (const bf16*)ymask, dw, dbias, s, l.tx, l.ty, relu_in);
+      cudaError_t _le = tdl::launch_pdl(depthwise3x3_wgrad_kernel<true>, dim3(grid), dim3(kThreads), smem, st,
+          (const bf16*)x, (const bf16*)dy, (const bf16*)ymask, dw, dbias, s, l.tx, l.ty, relu_in);
       if (_le != cudaSuccess) return tdl::cuda_fail(_le, "depthwise3x3_wgrad_kernel");
     }
   else
     {
-      cudaError_t _le = tdl::launch_pdl(depthwise3x3_wgrad_kernel<false>, dim3(grid), dim3(kThreads), smem, st, (const bf16*)x, (const bf16*)dy, (const bf16*)ymask, dw, dbias, s, l.tx, l.ty, relu_in);
+      cudaError_t _le = tdl::launch_pdl(depthwise3x3_wgrad_kernel<false>, dim3(grid), dim3(kThreads), smem, st,
+          (const bf16*)x, (const bf16*)dy, (const bf16*)ymask, dw, dbias, s, l.tx, l.ty, relu_in);
       if (_le != cudaSuccess) return tdl::cuda_fail(_le, "depthwise3x3_wgrad_kernel");
     }
   TDL_LAUNCH_OK("depthwise3x3_wgrad_kernel");

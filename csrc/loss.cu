@@ -194,7 +194,8 @@ static int launch_lovasz(const float* logits, const float* labels, int B, int P,
     attr_set = true;
   }
   {
-    cudaError_t _le = tdl::launch_pdl(lovasz_hinge_kernel<IPT>, dim3(B), dim3(kLovaszThreads), smem, st, logits, labels, P, grad_scale, loss_out, dlogits);
+    cudaError_t _le = tdl::launch_pdl(lovasz_hinge_kernel<IPT>, dim3(B), dim3(kLovaszThreads), smem, st, logits,
+        labels, P, grad_scale, loss_out, dlogits);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "lovasz_hinge_kernel");
   }
   TDL_LAUNCH_OK("lovasz_hinge_kernel");
@@ -312,7 +313,8 @@ TDL_API int tdl_seg_metrics(const float* logits, const float* labels, int B, int
                             int reference_compat, float* iou_out, float* acc_out, void* stream) {
   if (B <= 0) return 0;
   {
-    cudaError_t _le = tdl::launch_pdl(seg_metrics_kernel, dim3(B), dim3(256), 0, (cudaStream_t)stream, logits, labels, P, logit_threshold, reference_compat, iou_out, acc_out);
+    cudaError_t _le = tdl::launch_pdl(seg_metrics_kernel, dim3(B), dim3(256), 0, (cudaStream_t)stream, logits, labels,
+        P, logit_threshold, reference_compat, iou_out, acc_out);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "seg_metrics_kernel");
   }
   TDL_LAUNCH_OK("seg_metrics_kernel");
@@ -324,7 +326,9 @@ TDL_API int tdl_softmax_ce(const float* logits, const void* labels_i64, int rows
   if (rows <= 0) return 0;
   const int warps = 8;
   {
-    cudaError_t _le = tdl::launch_pdl(softmax_ce_kernel, dim3((rows + warps - 1) / warps), dim3(warps * 32), 0, (cudaStream_t)stream, logits, (const long long*)labels_i64, rows, classes, grad_scale, topk, loss_rows, dlogits, top1, topk_out);
+    cudaError_t _le = tdl::launch_pdl(softmax_ce_kernel, dim3((rows + warps - 1) / warps), dim3(warps * 32), 0,
+        (cudaStream_t)stream, logits, (const long long*)labels_i64, rows, classes, grad_scale, topk, loss_rows,
+        dlogits, top1, topk_out);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "softmax_ce_kernel");
   }
   TDL_LAUNCH_OK("softmax_ce_kernel");

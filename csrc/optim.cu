@@ -100,7 +100,8 @@ using namespace tdl::optim;
 TDL_API int tdl_lr_schedule_step(void* global_step_i64, float base_lr, float decay_rate, float decay_steps,
                                  float beta1, float beta2, float* lr_state, void* stream) {
   {
-    cudaError_t _le = tdl::launch_pdl(lr_schedule_kernel, dim3(1), dim3(1), 0, (cudaStream_t)stream, (long long*)global_step_i64, base_lr, decay_rate, decay_steps, beta1, beta2, lr_state);
+    cudaError_t _le = tdl::launch_pdl(lr_schedule_kernel, dim3(1), dim3(1), 0, (cudaStream_t)stream,
+        (long long*)global_step_i64, base_lr, decay_rate, decay_steps, beta1, beta2, lr_state);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "lr_schedule_kernel");
   }
   TDL_LAUNCH_OK("lr_schedule_kernel");
@@ -114,12 +115,14 @@ TDL_API int tdl_sgd_momentum_flat(float* param, void* grad, float* mom, void* sh
   cudaStream_t st = (cudaStream_t)stream;
   if (grad_is_bf16)
     {
-      cudaError_t _le = tdl::launch_pdl(sgd_momentum_kernel<bf16>, dim3(blocks_for(n)), dim3(kThreads), 0, st, param, (bf16*)grad, mom, (bf16*)shadow_bf16, n, lr_state, momentum, weight_decay, grad_scale, zero_grad);
+      cudaError_t _le = tdl::launch_pdl(sgd_momentum_kernel<bf16>, dim3(blocks_for(n)), dim3(kThreads), 0, st, param,
+          (bf16*)grad, mom, (bf16*)shadow_bf16, n, lr_state, momentum, weight_decay, grad_scale, zero_grad);
       if (_le != cudaSuccess) return tdl::cuda_fail(_le, "sgd_momentum_kernel");
     }
   else
     {
-      cudaError_t _le = tdl::launch_pdl(sgd_momentum_kernel<float>, dim3(blocks_for(n)), dim3(kThreads), 0, st, param, (float*)grad, mom, (bf16*)shadow_bf16, n, lr_state, momentum, weight_decay, grad_scale, zero_grad);
+      cudaError_t _le = tdl::launch_pdl(sgd_momentum_kernel<float>, dim3(blocks_for(n)), dim3(kThreads), 0, st, param,
+          (float*)grad, mom, (bf16*)shadow_bf16, n, lr_state, momentum, weight_decay, grad_scale, zero_grad);
       if (_le != cudaSuccess) return tdl::cuda_fail(_le, "sgd_momentum_kernel");
     }
   TDL_LAUNCH_OK("sgd_momentum_kernel");
@@ -133,12 +136,14 @@ TDL_API int tdl_adam_flat(float* param, void* grad, float* m1, float* m2, void* 
   cudaStream_t st = (cudaStream_t)stream;
   if (grad_is_bf16)
     {
-      cudaError_t _le = tdl::launch_pdl(adam_kernel<bf16>, dim3(blocks_for(n)), dim3(kThreads), 0, st, param, (bf16*)grad, m1, m2, (bf16*)shadow_bf16, n, lr_state, beta1, beta2, eps, grad_scale, zero_grad);
+      cudaError_t _le = tdl::launch_pdl(adam_kernel<bf16>, dim3(blocks_for(n)), dim3(kThreads), 0, st, param,
+          (bf16*)grad, m1, m2, (bf16*)shadow_bf16, n, lr_state, beta1, beta2, eps, grad_scale, zero_grad);
       if (_le != cudaSuccess) return tdl::cuda_fail(_le, "adam_kernel");
     }
   else
     {
-      cudaError_t _le = tdl::launch_pdl(adam_kernel<float>, dim3(blocks_for(n)), dim3(kThreads), 0, st, param, (float*)grad, m1, m2, (bf16*)shadow_bf16, n, lr_state, beta1, beta2, eps, grad_scale, zero_grad);
+      cudaError_t _le = tdl::launch_pdl(adam_kernel<float>, dim3(blocks_for(n)), dim3(kThreads), 0, st, param,
+          (float*)grad, m1, m2, (bf16*)shadow_bf16, n, lr_state, beta1, beta2, eps, grad_scale, zero_grad);
       if (_le != cudaSuccess) return tdl::cuda_fail(_le, "adam_kernel");
     }
   TDL_LAUNCH_OK("adam_kernel");
@@ -148,7 +153,8 @@ TDL_API int tdl_adam_flat(float* param, void* grad, float* m1, float* m2, void* 
 TDL_API int tdl_cast_f32_to_bf16(const float* src, void* dst, int64_t n, void* stream) {
   if (n <= 0) return 0;
   {
-    cudaError_t _le = tdl::launch_pdl(cast_f32_to_bf16_kernel, dim3(blocks_for(n)), dim3(kThreads), 0, (cudaStream_t)stream, src, (bf16*)dst, n);
+    cudaError_t _le = tdl::launch_pdl(cast_f32_to_bf16_kernel, dim3(blocks_for(n)), dim3(kThreads), 0,
+        (cudaStream_t)stream, src, (bf16*)dst, n);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "cast_f32_to_bf16_kernel");
   }
   TDL_LAUNCH_OK("cast_f32_to_bf16_kernel");

@@ -234,7 +234,8 @@ TDL_API int tdl_conv2d_smallk_fwd(const void* x, const float* w, const float* bi
   TDL_REQUIRE(smem <= 200 * 1024, "weights do not fit in shared memory");
   TDL_CUDA_OK(cudaFuncSetAttribute(fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   {
-    cudaError_t _le = tdl::launch_pdl(fwd_kernel, dim3(grid_for((int64_t)N * P * Q, kThreads / 32)), dim3(kThreads), smem, (cudaStream_t)stream, (const __nv_bfloat16*)x, w, bias, (__nv_bfloat16*)y, g);
+    cudaError_t _le = tdl::launch_pdl(fwd_kernel, dim3(grid_for((int64_t)N * P * Q, kThreads / 32)), dim3(kThreads),
+        smem, (cudaStream_t)stream, (const __nv_bfloat16*)x, w, bias, (__nv_bfloat16*)y, g);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "fwd_kernel");
   }
   TDL_LAUNCH_OK("smallk conv fwd");
@@ -249,7 +250,8 @@ TDL_API int tdl_conv2d_smallk_bwd_data(const void* dy, const float* w, void* dx,
   TDL_REQUIRE(smem <= 200 * 1024, "weights do not fit in shared memory");
   TDL_CUDA_OK(cudaFuncSetAttribute(bwd_data_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   {
-    cudaError_t _le = tdl::launch_pdl(bwd_data_kernel, dim3(grid_for((int64_t)N * H * W, kThreads / 32)), dim3(kThreads), smem, (cudaStream_t)stream, (const __nv_bfloat16*)dy, w, (__nv_bfloat16*)dx, g);
+    cudaError_t _le = tdl::launch_pdl(bwd_data_kernel, dim3(grid_for((int64_t)N * H * W, kThreads / 32)),
+        dim3(kThreads), smem, (cudaStream_t)stream, (const __nv_bfloat16*)dy, w, (__nv_bfloat16*)dx, g);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "bwd_data_kernel");
   }
   TDL_LAUNCH_OK("smallk conv bwd data");
@@ -269,7 +271,8 @@ TDL_API int tdl_conv2d_smallk_bwd_weight(const void* x, const void* dy, float* d
   int blocks = grid_for((int64_t)N * P * Q, groups * 16);
   if (blocks > num_sms() * 2) blocks = num_sms() * 2;
   {
-    cudaError_t _le = tdl::launch_pdl(bwd_weight_kernel, dim3(blocks), dim3(kThreads), smem, (cudaStream_t)stream, (const __nv_bfloat16*)x, (const __nv_bfloat16*)dy, dw, dbias, g);
+    cudaError_t _le = tdl::launch_pdl(bwd_weight_kernel, dim3(blocks), dim3(kThreads), smem, (cudaStream_t)stream,
+        (const __nv_bfloat16*)x, (const __nv_bfloat16*)dy, dw, dbias, g);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "bwd_weight_kernel");
   }
   TDL_LAUNCH_OK("smallk conv bwd weight");

@@ -527,12 +527,16 @@ TDL_API int tdl_maxpool_fwd(const void* x, void* y, void* idx_u8, int N, int H, 
   if (work == 0) return 0;
   if (k == 3 && stride == 2 && N <= 65535 && (int64_t)P * Q * C < (1ll << 31))
     {
-      cudaError_t _le = tdl::launch_pdl(maxpool_fwd_rows_kernel<3, 2>, dim3(dim3((unsigned)cdiv((int64_t)P * Q * (C / 8), kThreads), N)), dim3(kThreads), 0, (cudaStream_t)stream, (const bf16*)x, (bf16*)y, (uint8_t*)idx_u8, H, W, C, P, Q, pad_h, pad_w);
+      cudaError_t _le = tdl::launch_pdl(maxpool_fwd_rows_kernel<3, 2>,
+          dim3(dim3((unsigned)cdiv((int64_t)P * Q * (C / 8), kThreads), N)), dim3(kThreads), 0, (cudaStream_t)stream,
+          (const bf16*)x, (bf16*)y, (uint8_t*)idx_u8, H, W, C, P, Q, pad_h, pad_w);
       if (_le != cudaSuccess) return tdl::cuda_fail(_le, "maxpool_fwd_rows_kernel");
     }
   else
     {
-      cudaError_t _le = tdl::launch_pdl(maxpool_fwd_kernel, dim3(grid_for(work)), dim3(kThreads), 0, (cudaStream_t)stream, (const bf16*)x, (bf16*)y, (uint8_t*)idx_u8, N, H, W, C, P, Q, k, stride, pad_h, pad_w);
+      cudaError_t _le = tdl::launch_pdl(maxpool_fwd_kernel, dim3(grid_for(work)), dim3(kThreads), 0,
+          (cudaStream_t)stream, (const bf16*)x, (bf16*)y, (uint8_t*)idx_u8, N, H, W, C, P, Q, k, stride, pad_h,
+          pad_w);
       if (_le != cudaSuccess) return tdl::cuda_fail(_le, "maxpool_fwd_kernel");
     }
   TDL_LAUNCH_OK("maxpool_fwd_kernel");
@@ -547,12 +551,16 @@ TDL_API int tdl_maxpool_bwd(const void* dy, const void* idx_u8, void* dx, int N,
   if (k == 3 && stride == 2 && N <= 65535 && (int64_t)H * W * C < (1ll << 31)) {
     const int A = (H + pad_h + 1) / 2, B = (W + pad_w + 1) / 2;  // 2x2 pixel blocks on the window grid
     {
-      cudaError_t _le = tdl::launch_pdl(maxpool_bwd_block_kernel<3, 2>, dim3(dim3((unsigned)cdiv((int64_t)A * B * (C / 8), kThreads), N)), dim3(kThreads), 0, (cudaStream_t)stream, (const bf16*)dy, (const uint8_t*)idx_u8, (bf16*)dx, H, W, C, P, Q, pad_h, pad_w, A, B);
+      cudaError_t _le = tdl::launch_pdl(maxpool_bwd_block_kernel<3, 2>,
+          dim3(dim3((unsigned)cdiv((int64_t)A * B * (C / 8), kThreads), N)), dim3(kThreads), 0, (cudaStream_t)stream,
+          (const bf16*)dy, (const uint8_t*)idx_u8, (bf16*)dx, H, W, C, P, Q, pad_h, pad_w, A, B);
       if (_le != cudaSuccess) return tdl::cuda_fail(_le, "maxpool_bwd_block_kernel");
     }
   } else
     {
-      cudaError_t _le = tdl::launch_pdl(maxpool_bwd_kernel, dim3(grid_for(work)), dim3(kThreads), 0, (cudaStream_t)stream, (const bf16*)dy, (const uint8_t*)idx_u8, (bf16*)dx, N, H, W, C, P, Q, k, stride, pad_h, pad_w);
+      cudaError_t _le = tdl::launch_pdl(maxpool_bwd_kernel, dim3(grid_for(work)), dim3(kThreads), 0,
+          (cudaStream_t)stream, (const bf16*)dy, (const uint8_t*)idx_u8, (bf16*)dx, N, H, W, C, P, Q, k, stride,
+          pad_h, pad_w);
       if (_le != cudaSuccess) return tdl::cuda_fail(_le, "maxpool_bwd_kernel");
     }
   TDL_LAUNCH_OK("maxpool_bwd_kernel");
@@ -564,7 +572,8 @@ TDL_API int tdl_gap_fwd(const void* x, void* y, int N, int HW, int C, void* stre
   if (N == 0) return 0;
   dim3 grid(N, (unsigned)cdiv(C / 8, 32));
   {
-    cudaError_t _le = tdl::launch_pdl(gap_fwd_kernel, dim3(grid), dim3(kThreads), 0, (cudaStream_t)stream, (const bf16*)x, (bf16*)y, HW, C);
+    cudaError_t _le = tdl::launch_pdl(gap_fwd_kernel, dim3(grid), dim3(kThreads), 0, (cudaStream_t)stream,
+        (const bf16*)x, (bf16*)y, HW, C);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "gap_fwd_kernel");
   }
   TDL_LAUNCH_OK("gap_fwd_kernel");
@@ -576,7 +585,8 @@ TDL_API int tdl_gap_bwd(const void* dy, void* dx, int N, int HW, int C, void* st
   const int64_t total = (int64_t)N * HW * (C / 8);
   if (total == 0) return 0;
   {
-    cudaError_t _le = tdl::launch_pdl(gap_bwd_kernel, dim3(grid_for(total)), dim3(kThreads), 0, (cudaStream_t)stream, (const bf16*)dy, (bf16*)dx, total, HW, C / 8);
+    cudaError_t _le = tdl::launch_pdl(gap_bwd_kernel, dim3(grid_for(total)), dim3(kThreads), 0, (cudaStream_t)stream,
+        (const bf16*)dy, (bf16*)dx, total, HW, C / 8);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "gap_bwd_kernel");
   }
   TDL_LAUNCH_OK("gap_bwd_kernel");
@@ -590,7 +600,9 @@ TDL_API int tdl_depthwise_fwd(const void* x, const float* w, const float* bias, 
   const int64_t work = (int64_t)N * P * Q * (C / 8);
   if (work == 0) return 0;
   {
-    cudaError_t _le = tdl::launch_pdl(depthwise_fwd_kernel, dim3(grid_for(work)), dim3(kThreads), 0, (cudaStream_t)stream, (const bf16*)x, w, bias, (bf16*)y, N, H, W, C, P, Q, R, S, stride, dil, pad_h, pad_w, relu);
+    cudaError_t _le = tdl::launch_pdl(depthwise_fwd_kernel, dim3(grid_for(work)), dim3(kThreads), 0,
+        (cudaStream_t)stream, (const bf16*)x, w, bias, (bf16*)y, N, H, W, C, P, Q, R, S, stride, dil, pad_h, pad_w,
+        relu);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "depthwise_fwd_kernel");
   }
   TDL_LAUNCH_OK("depthwise_fwd_kernel");
@@ -608,7 +620,8 @@ TDL_API int tdl_depthwise_bwd(const void* x, const float* w, const void* dy, con
     const int64_t work = (int64_t)N * H * W * (C / 8);
     if (work)
       {
-        cudaError_t _le = tdl::launch_pdl(depthwise_bwd_data_kernel, dim3(grid_for(work)), dim3(kThreads), 0, st, (const bf16*)dy, (const bf16*)y, w, (bf16*)dx, N, H, W, C, P, Q, R, S, stride, dil, pad_h, pad_w, relu);
+        cudaError_t _le = tdl::launch_pdl(depthwise_bwd_data_kernel, dim3(grid_for(work)), dim3(kThreads), 0, st,
+            (const bf16*)dy, (const bf16*)y, w, (bf16*)dx, N, H, W, C, P, Q, R, S, stride, dil, pad_h, pad_w, relu);
         if (_le != cudaSuccess) return tdl::cuda_fail(_le, "depthwise_bwd_data_kernel");
       }
     TDL_LAUNCH_OK("depthwise_bwd_data_kernel");
@@ -626,7 +639,9 @@ TDL_API int tdl_depthwise_bwd(const void* x, const float* w, const void* dy, con
     if (gx < 1) gx = 1;
     dim3 grid((unsigned)gx, gy);
     {
-      cudaError_t _le = tdl::launch_pdl(depthwise_bwd_weight_kernel, dim3(grid), dim3(kThreads), kThreads * 8 * sizeof(float), st, (const bf16*)x, (const bf16*)dy, (const bf16*)y, dw, dbias, N, H, W, C, P, Q, R, S, stride, dil, pad_h, pad_w, relu, tx, ty);
+      cudaError_t _le = tdl::launch_pdl(depthwise_bwd_weight_kernel, dim3(grid), dim3(kThreads),
+          kThreads * 8 * sizeof(float), st, (const bf16*)x, (const bf16*)dy, (const bf16*)y, dw, dbias, N, H, W, C, P,
+          Q, R, S, stride, dil, pad_h, pad_w, relu, tx, ty);
       if (_le != cudaSuccess) return tdl::cuda_fail(_le, "depthwise_bwd_weight_kernel");
     }
     TDL_LAUNCH_OK("depthwise_bwd_weight_kernel");
@@ -640,12 +655,14 @@ TDL_API int tdl_upsample_fwd(const void* x, void* y, int N, int H, int W, int C,
   if (total == 0) return 0;
   if (is_bf16)
     {
-      cudaError_t _le = tdl::launch_pdl(upsample_fwd_kernel<bf16>, dim3(grid_for(total)), dim3(kThreads), 0, (cudaStream_t)stream, (const bf16*)x, (bf16*)y, N, H, W, C, OH, OW);
+      cudaError_t _le = tdl::launch_pdl(upsample_fwd_kernel<bf16>, dim3(grid_for(total)), dim3(kThreads), 0,
+          (cudaStream_t)stream, (const bf16*)x, (bf16*)y, N, H, W, C, OH, OW);
       if (_le != cudaSuccess) return tdl::cuda_fail(_le, "upsample_fwd_kernel");
     }
   else
     {
-      cudaError_t _le = tdl::launch_pdl(upsample_fwd_kernel<float>, dim3(grid_for(total)), dim3(kThreads), 0, (cudaStream_t)stream, (const float*)x, (float*)y, N, H, W, C, OH, OW);
+      cudaError_t _le = tdl::launch_pdl(upsample_fwd_kernel<float>, dim3(grid_for(total)), dim3(kThreads), 0,
+          (cudaStream_t)stream, (const float*)x, (float*)y, N, H, W, C, OH, OW);
       if (_le != cudaSuccess) return tdl::cuda_fail(_le, "upsample_fwd_kernel");
     }
   TDL_LAUNCH_OK("upsample_fwd_kernel");
@@ -659,12 +676,14 @@ TDL_API int tdl_upsample_bwd(const void* dy, float* dx, int N, int H, int W, int
   if (total == 0) return 0;
   if (is_bf16)
     {
-      cudaError_t _le = tdl::launch_pdl(upsample_bwd_kernel<bf16>, dim3(grid_for(total)), dim3(kThreads), 0, (cudaStream_t)stream, (const bf16*)dy, dx, N, H, W, C, OH, OW);
+      cudaError_t _le = tdl::launch_pdl(upsample_bwd_kernel<bf16>, dim3(grid_for(total)), dim3(kThreads), 0,
+          (cudaStream_t)stream, (const bf16*)dy, dx, N, H, W, C, OH, OW);
       if (_le != cudaSuccess) return tdl::cuda_fail(_le, "upsample_bwd_kernel");
     }
   else
     {
-      cudaError_t _le = tdl::launch_pdl(upsample_bwd_kernel<float>, dim3(grid_for(total)), dim3(kThreads), 0, (cudaStream_t)stream, (const float*)dy, dx, N, H, W, C, OH, OW);
+      cudaError_t _le = tdl::launch_pdl(upsample_bwd_kernel<float>, dim3(grid_for(total)), dim3(kThreads), 0,
+          (cudaStream_t)stream, (const float*)dy, dx, N, H, W, C, OH, OW);
       if (_le != cudaSuccess) return tdl::cuda_fail(_le, "upsample_bwd_kernel");
     }
   TDL_LAUNCH_OK("upsample_bwd_kernel");
@@ -699,7 +718,9 @@ TDL_API int tdl_u8_to_bf16_normalize(const void* x_u8, void* y_bf16, int64_t pix
   const int64_t total = pixels * Cpad;
   if (total == 0) return 0;
   {
-    cudaError_t _le = tdl::launch_pdl(tdl::spatial::u8_to_bf16_kernel, dim3(tdl::spatial::grid_for(total)), dim3(tdl::spatial::kThreads), 0, (cudaStream_t)stream, (const uint8_t*)x_u8, (tdl::bf16*)y_bf16, pixels, C, Cpad, mean, inv_std);
+    cudaError_t _le = tdl::launch_pdl(tdl::spatial::u8_to_bf16_kernel, dim3(tdl::spatial::grid_for(total)),
+        dim3(tdl::spatial::kThreads), 0, (cudaStream_t)stream, (const uint8_t*)x_u8, (tdl::bf16*)y_bf16, pixels, C,
+        Cpad, mean, inv_std);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "tdl::spatial::u8_to_bf16_kernel");
   }
   TDL_LAUNCH_OK("u8_to_bf16_kernel");
@@ -769,7 +790,8 @@ TDL_API int tdl_colsum_bf16(const void* dy, float* out, int64_t rows, int C, voi
   if (gx > cap) gx = cap;
   if (gx < 1) gx = 1;
   {
-    cudaError_t _le = tdl::launch_pdl(colsum_kernel, dim3(dim3((unsigned)gx, (unsigned)gy)), dim3(kThreads), kThreads * 8 * sizeof(float), (cudaStream_t)stream, (const tdl::bf16*)dy, out, rows, C, tx, ty);
+    cudaError_t _le = tdl::launch_pdl(colsum_kernel, dim3(dim3((unsigned)gx, (unsigned)gy)), dim3(kThreads),
+        kThreads * 8 * sizeof(float), (cudaStream_t)stream, (const tdl::bf16*)dy, out, rows, C, tx, ty);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "colsum_kernel");
   }
   TDL_LAUNCH_OK("colsum_kernel");

@@ -115,3 +115,39 @@ def test_xception_output_stride_16():
     with torch.no_grad():
         f = m(torch.randn(1, 129, 129, 3))
     assert f.shape[1:3] == (9, 9)
+
+
+def test_end_points_wanted_fuses_unit_tails_without_changing_values(seg):
+    """``wanted`` only changes WHICH tensors are materialised (the others fuse relu(shortcut + conv3) into conv3):
+    block outputs, the requested pre-activation end point and the network output stay the same."""
+    from tensorflowdistributedlearning_b200.models.resnet import EndPoints
+
+    seg.eval()
+    torch.manual_seed(1)
+    x = torch.randn(2, 101, 101, 2)
+    low = "model/resnet_v2/block1/unit_1/bottleneck_v2/conv3"
+    with torch.no_grad():
+        net_all, ep_all = seg.backbone(x, collect=True)
+        net_w, ep_w = seg.backbone(x, collect=True, wanted=(low,))
+        net_none, ep_none = seg.backbone(x, collect=False)
+    assert isinstance(ep_w, EndPoints) and ep_none is None
+    assert torch.allclose(net_all, net_w, atol=1e-5) and torch.allclose(net_all, net_none, atol=1e-5)
+    assert torch.allclose(ep_all[low], ep_w[low], atol=1e-5)
+    for k in ("model/resnet_v2/block1", "model/resnet_v2/block4", "model/resnet_v2/block2/unit_3/bottleneck_v2"):
+        assert torch.allclose(ep_all[k], ep_w[k], atol=1e-5), k
+    # pre-activation tensors nobody asked for are not kept alive
+    assert "model/resnet_v2/block2/unit_1/bottleneck_v2/conv3" in ep_all
+    assert "model/resnet_v2/block2/unit_1/bottleneck_v2/conv3" not in ep_w
+
+
+def test_conv2d_residual_relu_fallback_matches_composition():
+    from tensorflowdistributedlearning_b200.ops import functional as Fn
+
+    torch.manual_seed(2)
+    x = torch.randn(2, 9, 9, 16)
+    w = torch.randn(24, 1, 1, 16) / 4
+    b = torch.randn(24)
+    r = torch.randn(2, 9, 9, 24)
+    y = Fn.conv2d(x, w, b, residual=r, relu=True)
+    ref = torch.relu(Fn.conv2d(x, w, b) + r)
+    assert torch.allclose(y, ref, atol=1e-6)
