@@ -1329,6 +1329,8 @@ static int launch_fprop(const CUtensorMap& tx, const CUtensorMap& tw, const CUte
     return launch_fprop_t<BLOCK_N, false, false, false, true>(tx, tw, ty, tres, tid, tbx, g, bias, res, stats, nparts, st);
   }
   if (g.res_mma) {
+    if (stats)  // + BatchNorm statistics of the stored (bias / residual / ReLU applied) output
+      return launch_fprop_t<BLOCK_N, true, true, true>(tx, tw, ty, tres, tid, tbx, g, bias, res, stats, nparts, st);
     if (g.has_bias || g.relu)
       return launch_fprop_t<BLOCK_N, true, false, true>(tx, tw, ty, tres, tid, tbx, g, bias, res, stats, nparts, st);
     return launch_fprop_t<BLOCK_N, false, false, true>(tx, tw, ty, tres, tid, tbx, g, bias, res, stats, nparts, st);
@@ -1504,7 +1506,7 @@ static int fprop_impl(const void* x, const void* w, void* y, const float* bias, 
   g.relu = relu; g.has_bias = bias != nullptr; g.has_res = residual != nullptr;
   // "+ residual" without statistics / strided view: add it on the tensor core (an extra A operand x identity block);
   // the epilogue then never waits on a global load of the residual -- bias and ReLU, if any, stay in the epilogue
-  g.res_mma = (residual != nullptr && (stats == nullptr || bnb) && view == nullptr && (!bnb || (!bias && !relu))) ? 1 : 0;
+  g.res_mma = (residual != nullptr && view == nullptr && (!bnb || (!bias && !relu))) ? 1 : 0;
   if (g.res_mma) g.has_res = 0;
   if (bnb) {
     TDL_REQUIRE(stats && nparts && !view && bias == nullptr && !relu && stride == 1,
@@ -1637,6 +1639,18 @@ TDL_API int tdl_conv2d_fprop_stats_bf16(const void* x, const void* w, void* y, c
                                         int Q, float* stats_partial, int* nparts_host, void* stream) {
   TDL_REQUIRE(stats_partial != nullptr && nparts_host != nullptr, "stats buffers required");
   return fprop_impl(x, w, y, bias, nullptr, N, H, W, C, K, R, S, stride, dil, pad_h, pad_w, P, Q, 0, nullptr,
+                    stats_partial, nparts_host, stream);
+}
+
+// y = relu?(conv(x, w) + bias? + residual) with the residual added on the tensor core AND the per-CTA partial
+// (sum, sum of squares) of the stored output, for the BatchNorm that consumes y next (the reference unit's
+// relu(shortcut + conv3(.)) feeding the next unit's pre-activation BatchNorm, core/resnet.py:113,148-150).
+TDL_API int tdl_conv2d_fprop_res_stats_bf16(const void* x, const void* w, void* y, const float* bias,
+                                            const void* residual, int N, int H, int W, int C, int K, int R, int S,
+                                            int stride, int dil, int pad_h, int pad_w, int P, int Q, int relu,
+                                            float* stats_partial, int* nparts_host, void* stream) {
+  TDL_REQUIRE(residual != nullptr && stats_partial != nullptr && nparts_host != nullptr, "residual and stats required");
+  return fprop_impl(x, w, y, bias, residual, N, H, W, C, K, R, S, stride, dil, pad_h, pad_w, P, Q, relu, nullptr,
                     stats_partial, nparts_host, stream);
 }
 

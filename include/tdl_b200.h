@@ -141,6 +141,12 @@ int tdl_conv2d_dgrad_bnstats_bf16(const void* x, const void* w, void* y, const v
                                   const void* bn_x, const float* bn_mean, const float* bn_invstd, const float* bn_scale,
                                   const float* bn_shift, int N, int H, int W, int C, int K, int R, int S, int dil, int pad_h, int pad_w, int P, int Q,
                                   float* stats_partial, int* nparts_host, void* stream);
+/* relu?(conv + bias? + residual) with the residual on the tensor core and BatchNorm partial statistics of the
+ * stored output (stats_partial / nparts_host as in tdl_conv2d_fprop_stats_bf16). */
+int tdl_conv2d_fprop_res_stats_bf16(const void* x, const void* w, void* y, const float* bias, const void* residual,
+                                    int N, int H, int W, int C, int K, int R, int S, int stride, int dil, int pad_h,
+                                    int pad_w, int P, int Q, int relu, float* stats_partial, int* nparts_host,
+                                    void* stream);
 /* Convolution with 1..4 output channels (decoder 3x3 -> 1 logit).  CUDA-core dot products; weight is the
  * fp32 master [K,R,S,C]; stride 1; dw / dbias are accumulated into. */
 int tdl_conv2d_smallk_fwd(const void* x, const float* w, const float* bias, void* y, int N, int H, int W, int C, int K,

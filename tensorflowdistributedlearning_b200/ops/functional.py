@@ -182,7 +182,9 @@ class _ConvNative(torch.autograd.Function):
         partials = None
         if want_stats:
             y, partials, nparts = O.conv2d_fprop_stats(x, wf, R=Rk, S=Sk, stride=stride, dil=dil, pad_h=pt, pad_w=pl,
-                                                       out_hw=out_hw, bias=None if bias is None else bias.detach())
+                                                       out_hw=out_hw, bias=None if bias is None else bias.detach(),
+                                                       residual=(None if residual is None
+                                                                 else residual.detach().contiguous()), relu=relu_out)
             partials = partials[:nparts]
         else:
             # (+ residual) (+ ReLU) in the epilogue: the reference unit's relu(shortcut + conv3(...)), core/resnet.py:148
@@ -418,7 +420,7 @@ def conv2d(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] =
     """NHWC convolution, weight [K, R, S, C] (fp32 master).  TF 'SAME' geometry by default.
 
     ``residual`` / ``relu``: ``relu?(conv(x) + bias + residual)`` in the convolution's own epilogue (not combinable
-    with ``want_stats`` / ``want_tap``).
+    with ``want_tap``; with ``want_stats`` the statistics are those of the stored sum, and need the residual).
 
     ``want_stats=True`` returns ``(y, stats)`` where ``stats`` is either None (torch path) or the per-CTA partial
     BatchNorm statistics the tcgen05 kernel accumulated in its epilogue; pass it to :func:`batch_norm`.
@@ -439,7 +441,11 @@ def conv2d(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] =
             and not (want_stats or want_tap) and residual is None and not relu):
         return _ConvSmallK.apply(x.contiguous(), weight, bias, dil, (pt, pb, pl, pr), (P, Q))
     if _native_ok(x) and C % 8 == 0 and K % 8 == 0 and stride <= 2:
-        if want_stats or want_tap:
+        if want_stats and residual is not None and not want_tap:
+            # statistics of relu?(conv + bias + residual) as stored: for the BatchNorm that consumes the sum next
+            return _ConvNative.apply(x.contiguous(), weight, bias, stride, dil, (pt, pb, pl, pr), (P, Q), True, False,
+                                     residual, relu)
+        if (want_stats or want_tap) and residual is None and not relu:
             out = _ConvNative.apply(x.contiguous(), weight, bias, stride, dil, (pt, pb, pl, pr), (P, Q), want_stats,
                                     want_tap)
             if want_stats and want_tap:
@@ -447,10 +453,13 @@ def conv2d(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] =
             if want_tap:
                 return out[0], None, out[1]
             return out
+        assert not want_tap, "want_tap is not combinable with residual / relu"
         if residual is not None or relu:
-            return _ConvNative.apply(x.contiguous(), weight, bias, stride, dil, (pt, pb, pl, pr), (P, Q), False, False,
-                                     residual, relu)
-        return _ConvNative.apply(x.contiguous(), weight, bias, stride, dil, (pt, pb, pl, pr), (P, Q))
+            y = _ConvNative.apply(x.contiguous(), weight, bias, stride, dil, (pt, pb, pl, pr), (P, Q), False, False,
+                                  residual, relu)
+        else:
+            y = _ConvNative.apply(x.contiguous(), weight, bias, stride, dil, (pt, pb, pl, pr), (P, Q))
+        return (y, None) if want_stats else y
     # torch path (cuDNN on GPU through a channels-last view; plain CPU conv on CPU towers)
     wq = weight.to(x.dtype)
     bq = None if bias is None else bias.to(x.dtype)

@@ -128,6 +128,11 @@ class BatchNorm(TFModule):
 
     def forward(self, x: torch.Tensor, relu: bool = False, residual: Optional[torch.Tensor] = None,
                 stats: Optional[torch.Tensor] = None) -> torch.Tensor:
+        if stats is None and self.training:
+            # partial statistics the producing kernel left on the tensor (e.g. a unit tail relu(shortcut + conv3))
+            stats = getattr(x, "_tdl_stats", None)
+            if stats is not None and stats.shape[-1] != x.shape[-1]:
+                stats = None
         return TF.batch_norm(x, self.gamma, self.beta, self.moving_mean, self.moving_variance, decay=self.decay,
                              eps=self.eps, training=self.training, relu=relu, residual=residual, stats=stats)
 

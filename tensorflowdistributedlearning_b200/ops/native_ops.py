@@ -107,8 +107,10 @@ def conv2d_dgrad_bnstats(dy: torch.Tensor, w: torch.Tensor, *, R: int, S: int, d
 
 
 def conv2d_fprop_stats(x: torch.Tensor, w: torch.Tensor, *, R: int, S: int, stride: int = 1, dil: int = 1,
-                       pad_h: int = 0, pad_w: int = 0, out_hw=None, bias: Optional[torch.Tensor] = None):
+                       pad_h: int = 0, pad_w: int = 0, out_hw=None, bias: Optional[torch.Tensor] = None,
+                       residual: Optional[torch.Tensor] = None, relu: bool = False):
     """Convolution + per-CTA partial BatchNorm statistics of its (bf16) output in the same kernel.
+    With ``residual`` (and optionally ``relu``): statistics of ``relu?(conv + bias + residual)`` as stored.
     Returns (y, partials [sms, 2, K] fp32, nparts)."""
     _chk_bf16_nhwc(x, "x")
     _chk_bf16_nhwc(w, "w")
@@ -118,6 +120,16 @@ def conv2d_fprop_stats(x: torch.Tensor, w: torch.Tensor, *, R: int, S: int, stri
     y = torch.empty((n, p, q, k), dtype=torch.bfloat16, device=x.device)
     partials = torch.empty((int(N.lib().tdl_num_sms()), 2, k), dtype=torch.float32, device=x.device)
     nparts = ctypes.c_int(0)
+    if residual is not None:
+        _chk_bf16_nhwc(residual, "residual")
+        assert residual.shape == y.shape
+        rc = N.lib().tdl_conv2d_fprop_res_stats_bf16(N.ptr(x), N.ptr(w), N.ptr(y), N.ptr(bias), N.ptr(residual), _i(n),
+                                                     _i(h), _i(wd), _i(c), _i(k), _i(R), _i(S), _i(stride), _i(dil),
+                                                     _i(pad_h), _i(pad_w), _i(p), _i(q), _i(int(relu)),
+                                                     N.ptr(partials), ctypes.byref(nparts), N.stream_ptr())
+        N.check(rc, "tdl_conv2d_fprop_res_stats_bf16")
+        return y, partials, int(nparts.value)
+    assert not relu, "ReLU with statistics needs the residual form"
     rc = N.lib().tdl_conv2d_fprop_stats_bf16(N.ptr(x), N.ptr(w), N.ptr(y), N.ptr(bias), _i(n), _i(h), _i(wd), _i(c),
                                              _i(k), _i(R), _i(S), _i(stride), _i(dil), _i(pad_h), _i(pad_w), _i(p),
                                              _i(q), N.ptr(partials), ctypes.byref(nparts), N.stream_ptr())

@@ -234,6 +234,22 @@ def test_conv_fused_residual_relu_forward_and_gradients():
     assert rel_err(b.grad, bf.grad) < 2e-2
 
 
+def test_conv_fused_residual_relu_with_statistics(O):
+    """Unit tail relu(conv + bias + shortcut) that also leaves the BatchNorm partial statistics of the stored sum."""
+    torch.manual_seed(12)
+    N_, H, C, K = 3, 13, 264, 1032
+    x = torch.randn(N_, H, H, C, device="cuda").bfloat16()
+    w = (torch.randn(K, 1, C, device="cuda") / 16).bfloat16()
+    b = torch.randn(K, device="cuda")
+    r = torch.randn(N_, H, H, K, device="cuda").bfloat16()
+    y, partials, nparts = O.conv2d_fprop_stats(x, w, R=1, S=1, out_hw=(H, H), bias=b, residual=r, relu=True)
+    ref = _ref_conv(x, w, 1, 1, 1, 1, (0, 0, 0, 0), b, r, True)
+    assert rel_err(y, ref) < 1e-2
+    yf = y.float().reshape(-1, K)
+    assert rel_err(partials[:nparts, 0].sum(0), yf.sum(0)) < 1e-3
+    assert rel_err(partials[:nparts, 1].sum(0), (yf * yf).sum(0)) < 1e-3
+
+
 def test_residual_units_backward_with_premasked_gradients():
     """Three stacked v1.5 bottleneck units: the identity-shortcut gradient is added inside conv1's data gradient and
     the previous unit's ReLU backward is applied in the same epilogue; parameter and input gradients must match the
