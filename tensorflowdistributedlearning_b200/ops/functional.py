@@ -33,6 +33,47 @@ _FUSE_BN_BWD = os.environ.get("TDL_FUSE_BN_BWD", "0") == "1"  # measured slower 
 
 _FUSED_BN_HITS = 0
 
+# Batched weight preparation (trainer-owned steps only): the bf16 fprop / dgrad copies of every convolution weight
+# live in persistent buffers that ONE kernel refreshes at the start of a step (`begin_step`), instead of one small
+# launch per layer inside the forward pass.  Prepared copies are valid only within the step that made them: the
+# trainer calls `invalidate_prepared_weights()` after every step (eager or replayed), so an evaluation forward after
+# an optimizer update prepares its own.
+_WPREP_ON = False
+_WPREP = {}
+_WPREP_TABLE = None
+_WPREP_STEP = 0
+
+
+def enable_batched_weight_prep(flag: bool) -> None:
+    global _WPREP_ON, _WPREP_TABLE
+    _WPREP_ON = bool(flag)
+    _WPREP.clear()  # a fresh registry either way: entries belong to the trainer that enabled it
+    _WPREP_TABLE = None
+
+
+def invalidate_prepared_weights() -> None:
+    global _WPREP_STEP
+    _WPREP_STEP += 1
+
+
+def _prepare_all_weights() -> None:
+    from . import native_ops as O
+
+    global _WPREP_TABLE
+    if not _WPREP:
+        return
+    if _WPREP_TABLE is None:
+        if torch.cuda.is_current_stream_capturing():
+            return  # a layer first seen during capture: its own launch serves it, the table waits for an eager step
+        ents = list(_WPREP.values())
+        _WPREP_TABLE = (O.build_weight_prep_table([(e["w"].detach(), e["wf"], e["wd"], e["K"], e["taps"], e["C"])
+                                                   for e in ents]), ents)
+    (descs, starts, total), ents = _WPREP_TABLE
+    O.conv2d_weight_prep_batched(descs, starts, total)
+    _count(1)
+    for e in ents:
+        e["step"] = _WPREP_STEP
+
 
 def enable_fused_bn_backward(flag: bool) -> None:
     global _FUSE_BN_BWD
@@ -48,6 +89,9 @@ def begin_step() -> None:
     """Drop per-step bookkeeping (call at the start of every training step)."""
     _PREMASKED.clear()
     _BN_PARTIALS.clear()
+    if _WPREP_ON:
+        invalidate_prepared_weights()
+        _prepare_all_weights()
 
 
 _STEM_NATIVE = True       # first-layer tcgen05 kernel (off = cuDNN for the C<=4 stem, used for A/B timing)
@@ -174,10 +218,23 @@ class _ConvNative(torch.autograd.Function):
 
         K, Rk, Sk, C = weight.shape
         taps = Rk * Sk
-        wf = torch.empty((K, taps, C), dtype=torch.bfloat16, device=x.device)
         need_dgrad = ctx.needs_input_grad[0]
-        wd = torch.empty((C, taps, K), dtype=torch.bfloat16, device=x.device) if (need_dgrad and stride == 1) else None
-        O.conv2d_weight_prep(weight.detach(), wf, wd, K, taps, C)
+        need_wd = need_dgrad and stride == 1
+        ent = _WPREP.get(id(weight)) if _WPREP_ON else None
+        if (ent is not None and ent["w"] is weight and ent["step"] == _WPREP_STEP
+                and (ent["wd"] is not None or not need_wd)):
+            wf, wd = ent["wf"], (ent["wd"] if need_wd else None)  # refreshed by this step's one batched launch
+            prep_launches = 0
+        else:
+            wf = torch.empty((K, taps, C), dtype=torch.bfloat16, device=x.device)
+            wd = torch.empty((C, taps, K), dtype=torch.bfloat16, device=x.device) if need_wd else None
+            O.conv2d_weight_prep(weight.detach(), wf, wd, K, taps, C)
+            prep_launches = 1
+            if (_WPREP_ON and ent is None and isinstance(weight, torch.nn.Parameter) and weight.is_contiguous()
+                    and not torch.cuda.is_current_stream_capturing()):
+                global _WPREP_TABLE
+                _WPREP[id(weight)] = dict(w=weight, wf=wf, wd=wd, K=K, taps=taps, C=C, step=_WPREP_STEP)
+                _WPREP_TABLE = None
         pt, pb, pl, pr = pads
         partials = None
         if want_stats:
@@ -191,7 +248,7 @@ class _ConvNative(torch.autograd.Function):
             y = O.conv2d_fprop(x, wf, R=Rk, S=Sk, stride=stride, dil=dil, pad_h=pt, pad_w=pl, out_hw=out_hw,
                                bias=None if bias is None else bias.detach(),
                                residual=None if residual is None else residual.detach().contiguous(), relu=relu_out)
-        _count(2)
+        _count(1 + prep_launches)
         ctx.save_for_backward(x, wd if wd is not None else wf, y if relu_out else None)
         ctx.cfg = (K, Rk, Sk, C, stride, dil, pads, tuple(x.shape), bias is not None, wd is not None)
         outs = [y]

@@ -560,6 +560,34 @@ def conv2d_smallk_bwd_weight(x, dy, dw, dbias, dil, pad_h, pad_w):
     N.check(rc, "tdl_conv2d_smallk_bwd_weight")
 
 
+def build_weight_prep_table(entries):
+    """entries: list of (w fp32 [K,taps*C...], wf bf16, wd bf16 or None, K, taps, C).  Returns (descs, block_start,
+    total_blocks) device tensors for :func:`conv2d_weight_prep_batched` (48-byte records, see include/tdl_b200.h)."""
+    import numpy as np
+
+    rec = np.zeros(len(entries), dtype=np.dtype([("w", "<u8"), ("wf", "<u8"), ("wd", "<u8"), ("K", "<i4"),
+                                                 ("taps", "<i4"), ("C", "<i4"), ("ct", "<i4"), ("kt", "<i4"),
+                                                 ("pad", "<i4")]))
+    assert rec.dtype.itemsize == 48
+    starts, total = [], 0
+    dev = entries[0][0].device
+    for i, (w, wf, wd, K, taps, C) in enumerate(entries):
+        assert w.dtype == torch.float32 and w.is_contiguous() and wf.dtype == torch.bfloat16
+        ct, kt = (C + 31) // 32, (K + 31) // 32
+        rec[i] = (w.data_ptr(), wf.data_ptr(), 0 if wd is None else wd.data_ptr(), K, taps, C, ct, kt, 0)
+        starts.append(total)
+        total += ct * kt * taps
+    descs = torch.from_numpy(rec.view(np.uint8).copy()).to(dev)
+    block_start = torch.tensor(starts, dtype=torch.int32).to(dev)
+    return descs, block_start, total
+
+
+def conv2d_weight_prep_batched(descs: torch.Tensor, block_start: torch.Tensor, total_blocks: int) -> None:
+    rc = N.lib().tdl_conv2d_weight_prep_batched(N.ptr(descs), N.ptr(block_start), _i(block_start.numel()),
+                                                _i(total_blocks), N.stream_ptr())
+    N.check(rc, "tdl_conv2d_weight_prep_batched")
+
+
 def conv_stem_pack(x: torch.Tensor) -> torch.Tensor:
     """[N,H,W,C<=4] bf16 -> space-to-depth planes [N, ceil(H/2), 2, ceil(W/2), 8] bf16 for the first-layer kernel."""
     _chk_bf16_nhwc(x, "x")

@@ -55,6 +55,12 @@ class TowerTrainer:
         self.metrics = {}
         self.use_graph = bool(use_graph and dev.type == "cuda")
         self._nvtx = os.environ.get("TDL_NVTX", "0") == "1"
+        if dev.type == "cuda":
+            from ..ops import functional as TF
+
+            # one launch per step re-lays every convolution weight (instead of one per layer): the trainer owns the
+            # step boundaries this needs (TDL_BATCHED_WPREP=0 restores the per-layer launches)
+            TF.enable_batched_weight_prep(os.environ.get("TDL_BATCHED_WPREP", "1") != "0")
         self._graph: Optional[torch.cuda.CUDAGraph] = None
         self._copy_stream = torch.cuda.Stream() if dev.type == "cuda" else None
         self._copied = torch.cuda.Event() if dev.type == "cuda" else None
@@ -108,6 +114,8 @@ class TowerTrainer:
             if k not in self.metrics:
                 self.metrics[k] = torch.zeros_like(v)
             self.metrics[k].copy_(v)
+        if self.device.type == "cuda":
+            TF.invalidate_prepared_weights()  # the optimizer has moved the weights
 
     def warmup_and_capture(self, warmup: int = 3) -> None:
         """Eager warm-up steps (they train: they are real steps), then capture one step into a CUDA graph."""
@@ -137,6 +145,9 @@ class TowerTrainer:
         """One training step on whatever is in the device input buffers (no host traffic)."""
         if self._graph is not None:
             self._graph.replay()
+            from ..ops import functional as TF
+
+            TF.invalidate_prepared_weights()  # replays run no Python: say so for any eager forward that follows
         else:
             self._step_body()
 
@@ -181,5 +192,9 @@ class TowerTrainer:
         return float(self.loss.item())
 
     def close(self) -> None:
+        if self.device.type == "cuda":
+            from ..ops import functional as TF
+
+            TF.enable_batched_weight_prep(False)  # drops the persistent copies and the table
         self._graph = None
         self.opt.close()

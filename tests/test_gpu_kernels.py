@@ -650,6 +650,38 @@ def test_trainer_step_native_matches_torch_path_and_learns():
     assert abs(curves["native"][-1] - curves["torch"][-1]) < 0.5, curves
 
 
+def test_batched_weight_prep_matches_per_layer_launches(monkeypatch):
+    """One re-layout launch per step (persistent bf16 copies) trains bit-identically to one launch per layer, uses
+    fewer launches, and an eager forward after a replay sees the UPDATED weights (prepared copies are per step)."""
+    from tensorflowdistributedlearning_b200 import models
+    from tensorflowdistributedlearning_b200.parallel.tower import TowerGroup
+    from tensorflowdistributedlearning_b200.parallel.trainer import TowerTrainer, classification_loss
+
+    group = TowerGroup(device="cuda")
+    out = {}
+    for mode in ("1", "0"):
+        monkeypatch.setenv("TDL_BATCHED_WPREP", mode)
+        torch.manual_seed(4)
+        tr = TowerTrainer(models.resnet50(num_classes=8), group, batch=16, input_hwc=(64, 64, 3),
+                          loss_fn=classification_loss, use_graph=True, kind="sgdm", lr=0.05, momentum=0.9)
+        gen = torch.Generator().manual_seed(2)
+        tr.images.copy_(torch.randint(0, 256, tr.images.shape, dtype=torch.uint8, generator=gen))
+        tr.labels.copy_(torch.randint(0, 8, tr.labels.shape, generator=gen))
+        tr.warmup_and_capture(warmup=3)
+        losses = []
+        for _ in range(5):
+            tr.run_step()
+            losses.append(float(tr.loss.item()))
+        tr.model.eval()
+        with torch.no_grad():
+            y = tr.model(tr._prepare_input()).float().clone()
+        out[mode] = (losses, y, tr.launches_per_step)
+        tr.close()
+    assert out["1"][0] == out["0"][0], (out["1"][0], out["0"][0])
+    assert torch.equal(out["1"][1], out["0"][1])
+    assert out["1"][2] < out["0"][2] - 40, (out["1"][2], out["0"][2])
+
+
 def test_gpu_augmentation_matches_cpu_oracle(O):
     import numpy as np
 
