@@ -38,6 +38,7 @@ class _DepthwiseNative(torch.autograd.Function):
             y = O.depthwise_fwd(xin, wd, bd, stride, dil, pads[0], pads[2], out_hw, relu)
         TF._count(1)
         ctx.save_for_backward(x, weight, y if relu else None)
+        ctx.set_materialize_grads(False)  # no zero-fill for the (non-differentiable) statistics output
         ctx.cfg = (stride, dil, pads, relu, relu_in, bias is not None, fast)
         if want_stats:
             if partials is None:  # shape not served by the fused kernel: an empty marker the caller maps to "no stats"
@@ -51,6 +52,8 @@ class _DepthwiseNative(torch.autograd.Function):
         from . import native_ops as O
 
         x, weight, y = ctx.saved_tensors
+        if dy is None:
+            return (None,) * 10
         stride, dil, pads, relu, relu_in, has_bias, fast = ctx.cfg
         dy = dy.contiguous()
         kh, kw, C = weight.shape

@@ -212,6 +212,10 @@ class _ConvNative(torch.autograd.Function):
 
         ctx.weight_param, ctx.bias_param, ctx.want_tap = weight, bias, want_tap
         ctx.relu_out, ctx.has_residual = bool(relu_out), residual is not None
+        # the statistics output is not differentiable and the tap's gradient may be absent: do not let autograd
+        # launch a zero-fill for each of them every step
+        ctx.set_materialize_grads(False)
+        ctx.y_shape = (x.shape[0], out_hw[0], out_hw[1], weight.shape[0])
         # the 1-bit ReLU mask of the input tensor, when its producer left one (BatchNorm + residual + ReLU)
         ctx.in_mask = getattr(x, "_tdl_relu_mask", None) if want_tap else None
         ctx.bn_src = getattr(x, "_tdl_bn_src", None) if _FUSE_BN_BWD else None
@@ -271,6 +275,8 @@ class _ConvNative(torch.autograd.Function):
         K, Rk, Sk, C, stride, dil, pads, xshape, has_bias, has_wd = ctx.cfg
         pt, pb, pl, pr = pads
         n, h, w, _ = xshape
+        if dy is None:  # only the tap / statistics outputs were used downstream
+            dy = torch.zeros(ctx.y_shape, dtype=x.dtype, device=x.device)
         dy = dy.contiguous()
         if ctx.relu_out:  # backward of the fused output ReLU: everything below, and the residual branch, sees dy * (y > 0)
             dy = torch.ops.aten.threshold_backward(dy, y_relu, 0)
@@ -372,6 +378,7 @@ class _ConvStem(torch.autograd.Function):
         res = O.conv_stem_fprop(planes, wp, (x.shape[1], x.shape[2]), K, Rk, Sk, pt, pl, out_hw, want_stats)
         _count(3)
         ctx.save_for_backward(x, weight, planes)
+        ctx.set_materialize_grads(False)  # no zero-fill for the (non-differentiable) statistics output
         ctx.weight_param = weight
         ctx.cfg = (pads, want_stats)
         if want_stats:
@@ -384,6 +391,8 @@ class _ConvStem(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dy, *rest):
         x, weight, planes = ctx.saved_tensors
+        if dy is None:
+            return None, None, None, None, None
         (pt, pb, pl, pr), _ = ctx.cfg
         K, Rk, Sk, C = weight.shape
         need_dx, need_dw = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
