@@ -38,6 +38,7 @@ class _DepthwiseNative(torch.autograd.Function):
             y = O.depthwise_fwd(xin, wd, bd, stride, dil, pads[0], pads[2], out_hw, relu)
         TF._count(1)
         ctx.save_for_backward(x, weight, y if relu else None)
+        ctx.weight_param, ctx.bias_param = weight, bias
         ctx.set_materialize_grads(False)  # no zero-fill for the (non-differentiable) statistics output
         ctx.cfg = (stride, dil, pads, relu, relu_in, bias is not None, fast)
         if want_stats:
@@ -59,8 +60,32 @@ class _DepthwiseNative(torch.autograd.Function):
         kh, kw, C = weight.shape
         wd = weight.detach().float().contiguous()
         if fast:
-            dw, db = O.depthwise3x3_wgrad(x, dy, y if relu else None, stride, dil, pads[0], pads[2], relu_in, has_bias)
-            dw = dw.view(3, 3, C)
+            wp, bp = ctx.weight_param, ctx.bias_param
+            ymask = y if relu else None
+            if TF._direct_ok(wp) and (not has_bias or TF._direct_ok(bp)):
+                # straight into the flat gradient bucket, and -- nothing downstream in backward reads it -- on the
+                # weight-gradient side stream (see _ConvNative.backward)
+                def run():
+                    O.depthwise3x3_wgrad(x, dy, ymask, stride, dil, pads[0], pads[2], relu_in, has_bias,
+                                         dw_out=wp.grad, db_out=bp.grad if has_bias else None)
+                if TF._ASYNC_WGRAD:
+                    side = TF._side_stream()
+                    side.wait_stream(torch.cuda.current_stream())
+                    with torch.cuda.stream(side):
+                        run()
+                    for t in (x, dy, ymask):
+                        if t is not None:
+                            t.record_stream(side)
+                    TF._SIDE_DIRTY = True
+                else:
+                    run()
+                TF._notify(wp)
+                if has_bias:
+                    TF._notify(bp)
+                dw = db = None
+            else:
+                dw, db = O.depthwise3x3_wgrad(x, dy, ymask, stride, dil, pads[0], pads[2], relu_in, has_bias)
+                dw = dw.view(3, 3, C)
             TF._count(1)
             dx = None
             if ctx.needs_input_grad[0]:

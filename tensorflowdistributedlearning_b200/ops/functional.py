@@ -271,6 +271,7 @@ class _ConvNative(torch.autograd.Function):
     def backward(ctx, dy, *rest):
         from . import native_ops as O
 
+        global _SIDE_DIRTY
         x, wsaved, y_relu = ctx.saved_tensors
         K, Rk, Sk, C, stride, dil, pads, xshape, has_bias, has_wd = ctx.cfg
         pt, pb, pl, pr = pads
@@ -328,7 +329,6 @@ class _ConvNative(torch.autograd.Function):
             wp = ctx.weight_param
             if _direct_ok(wp):
                 if _ASYNC_WGRAD:
-                    global _SIDE_DIRTY
                     side = _side_stream()
                     side.wait_stream(torch.cuda.current_stream())  # dy (and x) are complete on the main stream
                     with torch.cuda.stream(side):
@@ -350,7 +350,15 @@ class _ConvNative(torch.autograd.Function):
             bp = ctx.bias_param
             if K % 8 == 0:  # one pass over dy (bf16 -> fp32 column sums) instead of a cast plus a generic reduction
                 if _direct_ok(bp):
-                    O.colsum_(dy.view(-1, K), bp.grad)
+                    if _ASYNC_WGRAD:  # like the weight gradient, nothing downstream in backward reads it
+                        side = _side_stream()
+                        side.wait_stream(torch.cuda.current_stream())
+                        with torch.cuda.stream(side):
+                            O.colsum_(dy.view(-1, K), bp.grad)
+                        dy.record_stream(side)
+                        _SIDE_DIRTY = True
+                    else:
+                        O.colsum_(dy.view(-1, K), bp.grad)
                     _notify(bp)
                 else:
                     db = O.colsum_(dy.view(-1, K), torch.zeros(K, dtype=torch.float32, device=dy.device))

@@ -505,11 +505,23 @@ def depthwise3x3_fwd(x, w9c, bias, mask, stride, dil, pad_h, pad_w, out_hw, relu
     return (y, None) if want_stats else y
 
 
-def depthwise3x3_wgrad(x, dy, ymask, stride, dil, pad_h, pad_w, relu_in, want_bias):
+def depthwise3x3_wgrad(x, dy, ymask, stride, dil, pad_h, pad_w, relu_in, want_bias, dw_out=None, db_out=None):
+    """dw [9, C] (and db [C]) of a 3x3 depthwise convolution.  ``dw_out`` / ``db_out`` (fp32, contiguous): the
+    gradients are ADDED into these buffers instead of freshly zeroed ones (direct accumulation into ``.grad``)."""
     n, h, w, c = x.shape
     _, p, q, _ = dy.shape
-    dw = torch.zeros((9, c), dtype=torch.float32, device=x.device)
-    db = torch.zeros((c,), dtype=torch.float32, device=x.device) if want_bias else None
+    if dw_out is not None:
+        assert dw_out.dtype == torch.float32 and dw_out.is_contiguous() and dw_out.numel() == 9 * c
+        dw = dw_out.view(9, c)
+    else:
+        dw = torch.zeros((9, c), dtype=torch.float32, device=x.device)
+    if not want_bias:
+        db = None
+    elif db_out is not None:
+        assert db_out.dtype == torch.float32 and db_out.is_contiguous() and db_out.numel() == c
+        db = db_out
+    else:
+        db = torch.zeros((c,), dtype=torch.float32, device=x.device)
     tma_ok = ymask is None and c % 8 == 0 and ((stride in (1, 2) and dil == 1) or (stride == 1 and dil == 2))
     if tma_ok:
         rc = N.lib().tdl_depthwise3x3_tma_wgrad(N.ptr(x), N.ptr(dy), N.ptr(dw), N.ptr(db), _i(n), _i(h), _i(w), _i(c),

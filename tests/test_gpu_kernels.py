@@ -650,6 +650,39 @@ def test_trainer_step_native_matches_torch_path_and_learns():
     assert abs(curves["native"][-1] - curves["torch"][-1]) < 0.5, curves
 
 
+def test_trainer_xception_direct_depthwise_gradients_match_torch_path():
+    """Xception-41 through the trainer: depthwise weight gradients accumulate straight into the flat bucket on the
+    side stream; the loss curve must follow the torch-op tower's."""
+    from tensorflowdistributedlearning_b200 import models
+    from tensorflowdistributedlearning_b200.ops import functional as TFn
+    from tensorflowdistributedlearning_b200.parallel.tower import TowerGroup
+    from tensorflowdistributedlearning_b200.parallel.trainer import TowerTrainer, classification_loss
+
+    group = TowerGroup(device="cuda")
+    curves = {}
+    for name, flag in (("native", False), ("torch", True)):
+        torch.manual_seed(5)
+        TFn.force_reference(flag)
+        try:
+            tr = TowerTrainer(models.build("xception41", num_classes=8), group, batch=8, input_hwc=(128, 128, 3),
+                              loss_fn=classification_loss, use_graph=(not flag), kind="sgdm", lr=0.02, momentum=0.9)
+            gen = torch.Generator().manual_seed(3)
+            tr.images.copy_(torch.randint(0, 256, tr.images.shape, dtype=torch.uint8, generator=gen))
+            tr.labels.copy_(torch.randint(0, 8, tr.labels.shape, generator=gen))
+            tr.warmup_and_capture(warmup=3)
+            losses = []
+            for _ in range(10):
+                tr.run_step()
+                losses.append(float(tr.loss.item()))
+            curves[name] = losses
+            tr.close()
+        finally:
+            TFn.force_reference(False)
+    assert curves["native"][-1] < curves["native"][0], curves
+    assert abs(curves["native"][0] - curves["torch"][0]) < 0.2, curves
+    assert abs(curves["native"][-1] - curves["torch"][-1]) < 0.6, curves
+
+
 def test_batched_weight_prep_matches_per_layer_launches(monkeypatch):
     """One re-layout launch per step (persistent bf16 copies) trains bit-identically to one launch per layer, uses
     fewer launches, and an eager forward after a replay sees the UPDATED weights (prepared copies are per step)."""
