@@ -472,7 +472,18 @@ class _ConvSmallK(torch.autograd.Function):
             gb = None
             if want_b:
                 gb = bp.grad if direct_b else torch.zeros(wd.shape[0], dtype=torch.float32, device=x.device)
-            O.conv2d_smallk_bwd_weight(x, dy, gw, gb, dil, pt, pl)
+            if _ASYNC_WGRAD and direct_w and (direct_b or not want_b):
+                # first node of backward: its weight gradient overlaps everything that follows on the main stream
+                global _SIDE_DIRTY
+                side = _side_stream()
+                side.wait_stream(torch.cuda.current_stream())
+                with torch.cuda.stream(side):
+                    O.conv2d_smallk_bwd_weight(x, dy, gw, gb, dil, pt, pl)
+                x.record_stream(side)
+                dy.record_stream(side)
+                _SIDE_DIRTY = True
+            else:
+                O.conv2d_smallk_bwd_weight(x, dy, gw, gb, dil, pt, pl)
             _count(1)
             if direct_w:
                 _notify(wp)
