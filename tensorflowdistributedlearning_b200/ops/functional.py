@@ -38,17 +38,34 @@ _FUSED_BN_HITS = 0
 # launch per layer inside the forward pass.  Prepared copies are valid only within the step that made them: the
 # trainer calls `invalidate_prepared_weights()` after every step (eager or replayed), so an evaluation forward after
 # an optimizer update prepares its own.
+class _WeightPrepRegistry:
+    """Persistent bf16 copies + the device table of one trainer.  The trainer holds a reference for as long as its
+    captured graph may replay: the graph's nodes point at these buffers, so they must outlive any registry switch
+    (a second trainer in the process) -- superseded tables are kept too (a few hundred bytes each)."""
+
+    def __init__(self):
+        self.entries = {}
+        self.table = None
+        self.retired = []
+
+    def drop_table(self):
+        if self.table is not None:
+            self.retired.append(self.table)
+        self.table = None
+
+
 _WPREP_ON = False
-_WPREP = {}
-_WPREP_TABLE = None
+_WPREP = _WeightPrepRegistry()
 _WPREP_STEP = 0
 
 
-def enable_batched_weight_prep(flag: bool) -> None:
-    global _WPREP_ON, _WPREP_TABLE
+def enable_batched_weight_prep(flag: bool):
+    """Starts a fresh registry (entries belong to the trainer that enables it) and returns it -- keep the reference
+    while a CUDA graph captured under it may still be replayed."""
+    global _WPREP_ON, _WPREP
     _WPREP_ON = bool(flag)
-    _WPREP.clear()  # a fresh registry either way: entries belong to the trainer that enabled it
-    _WPREP_TABLE = None
+    _WPREP = _WeightPrepRegistry()
+    return _WPREP
 
 
 def invalidate_prepared_weights() -> None:
@@ -59,16 +76,16 @@ def invalidate_prepared_weights() -> None:
 def _prepare_all_weights() -> None:
     from . import native_ops as O
 
-    global _WPREP_TABLE
-    if not _WPREP:
+    reg = _WPREP
+    if not reg.entries:
         return
-    if _WPREP_TABLE is None:
+    if reg.table is None:
         if torch.cuda.is_current_stream_capturing():
             return  # a layer first seen during capture: its own launch serves it, the table waits for an eager step
-        ents = list(_WPREP.values())
-        _WPREP_TABLE = (O.build_weight_prep_table([(e["w"].detach(), e["wf"], e["wd"], e["K"], e["taps"], e["C"])
-                                                   for e in ents]), ents)
-    (descs, starts, total), ents = _WPREP_TABLE
+        ents = list(reg.entries.values())
+        reg.table = (O.build_weight_prep_table([(e["w"].detach(), e["wf"], e["wd"], e["K"], e["taps"], e["C"])
+                                                for e in ents]), ents)
+    (descs, starts, total), ents = reg.table
     O.conv2d_weight_prep_batched(descs, starts, total)
     _count(1)
     for e in ents:
@@ -224,7 +241,7 @@ class _ConvNative(torch.autograd.Function):
         taps = Rk * Sk
         need_dgrad = ctx.needs_input_grad[0]
         need_wd = need_dgrad and stride == 1
-        ent = _WPREP.get(id(weight)) if _WPREP_ON else None
+        ent = _WPREP.entries.get(id(weight)) if _WPREP_ON else None
         if (ent is not None and ent["w"] is weight and ent["step"] == _WPREP_STEP
                 and (ent["wd"] is not None or not need_wd)):
             wf, wd = ent["wf"], (ent["wd"] if need_wd else None)  # refreshed by this step's one batched launch
@@ -234,11 +251,12 @@ class _ConvNative(torch.autograd.Function):
             wd = torch.empty((C, taps, K), dtype=torch.bfloat16, device=x.device) if need_wd else None
             O.conv2d_weight_prep(weight.detach(), wf, wd, K, taps, C)
             prep_launches = 1
-            if (_WPREP_ON and ent is None and isinstance(weight, torch.nn.Parameter) and weight.is_contiguous()
-                    and not torch.cuda.is_current_stream_capturing()):
-                global _WPREP_TABLE
-                _WPREP[id(weight)] = dict(w=weight, wf=wf, wd=wd, K=K, taps=taps, C=C, step=_WPREP_STEP)
-                _WPREP_TABLE = None
+            stale = ent is not None and (ent["w"] is not weight or (need_wd and ent["wd"] is None))
+            if (_WPREP_ON and (ent is None or stale) and isinstance(weight, torch.nn.Parameter)
+                    and weight.is_contiguous() and not torch.cuda.is_current_stream_capturing()):
+                # (a replaced entry's buffers stay alive through the retired table that still lists them)
+                _WPREP.entries[id(weight)] = dict(w=weight, wf=wf, wd=wd, K=K, taps=taps, C=C, step=_WPREP_STEP)
+                _WPREP.drop_table()
         pt, pb, pl, pr = pads
         partials = None
         if want_stats:

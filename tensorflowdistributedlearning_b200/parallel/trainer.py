@@ -60,7 +60,7 @@ class TowerTrainer:
 
             # one launch per step re-lays every convolution weight (instead of one per layer): the trainer owns the
             # step boundaries this needs (TDL_BATCHED_WPREP=0 restores the per-layer launches)
-            TF.enable_batched_weight_prep(os.environ.get("TDL_BATCHED_WPREP", "1") != "0")
+            self._wprep = TF.enable_batched_weight_prep(os.environ.get("TDL_BATCHED_WPREP", "1") != "0")
         self._graph: Optional[torch.cuda.CUDAGraph] = None
         self._copy_stream = torch.cuda.Stream() if dev.type == "cuda" else None
         self._copied = torch.cuda.Event() if dev.type == "cuda" else None
