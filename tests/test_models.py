@@ -151,3 +151,21 @@ def test_conv2d_residual_relu_fallback_matches_composition():
     y = Fn.conv2d(x, w, b, residual=r, relu=True)
     ref = torch.relu(Fn.conv2d(x, w, b) + r)
     assert torch.allclose(y, ref, atol=1e-6)
+
+
+def test_weight_prep_table_layout_matches_the_c_abi():
+    """The batched weight-prep table: 48-byte little-endian records and block prefix sums (include/tdl_b200.h)."""
+    import numpy as np
+
+    from tensorflowdistributedlearning_b200.ops import native_ops as O
+
+    w1, w2 = torch.zeros(40, 9, 72), torch.zeros(64, 1, 33)
+    f1, f2 = torch.zeros(40, 9, 72, dtype=torch.bfloat16), torch.zeros(64, 1, 33, dtype=torch.bfloat16)
+    d1 = torch.zeros(72, 9, 40, dtype=torch.bfloat16)
+    descs, starts, total = O.build_weight_prep_table([(w1, f1, d1, 40, 9, 72), (w2, f2, None, 64, 1, 33)])
+    assert descs.dtype == torch.uint8 and descs.numel() == 2 * 48
+    rec = np.frombuffer(descs.numpy().tobytes(), dtype=np.dtype("<u8,<u8,<u8,<i4,<i4,<i4,<i4,<i4,<i4"))
+    assert rec[0][0] == w1.data_ptr() and rec[0][1] == f1.data_ptr() and rec[0][2] == d1.data_ptr()
+    assert tuple(rec[0])[3:] == (40, 9, 72, 3, 2, 0)
+    assert rec[1][2] == 0 and tuple(rec[1])[3:] == (64, 1, 33, 2, 2, 0)
+    assert starts.tolist() == [0, 3 * 2 * 9] and total == 3 * 2 * 9 + 2 * 2 * 1
