@@ -1,3 +1,5 @@
-"""Reference-compatible ``core.layers`` (reference: core/layers.py): module-style equivalents of the slim helpers."""
-from tensorflowdistributedlearning_b200.ops.layers import (SplitSeparableConv2d as split_separable_conv2d,  # noqa: F401
-                                                           fixed_padding as _fixed_padding, upsample as _upsample)
+"""Reference-compatible ``core.layers`` (reference: core/layers.py:6-109): functional forms with the reference's
+arguments (variables are created on first use under ``scope``, see ``tensorflowdistributedlearning_b200.compat``);
+the module class is exported as ``SplitSeparableConv2d``."""
+from tensorflowdistributedlearning_b200.compat import _fixed_padding, _upsample, split_separable_conv2d  # noqa: F401
+from tensorflowdistributedlearning_b200.ops.layers import SplitSeparableConv2d  # noqa: F401

@@ -15,7 +15,18 @@ struct Params {
   int H, W, pad;
   float mean, inv_std;
   int laplace_2d;  // 0 = the reference's 1-D [1,-6,1] along W, 1 = the intended 2-D kernel
+  float brightness;  // per-sample additive delta on the normalised image (tf.image.random_brightness), set per pixel
 };
+
+// decoded pixel in [0, 1]: fp32 as is, uint8 / 255 with the correctly rounded division the CPU decode uses
+template <typename T>
+__device__ __forceinline__ float load_px(const T* __restrict__ img, int i);
+template <>
+__device__ __forceinline__ float load_px<float>(const float* __restrict__ img, int i) { return img[i]; }
+template <>
+__device__ __forceinline__ float load_px<uint8_t>(const uint8_t* __restrict__ img, int i) {
+  return __fdiv_rn((float)img[i], 255.f);
+}
 
 __device__ __forceinline__ int reflect(int i, int n) {
   if (i < 0) i = -i;
@@ -24,17 +35,19 @@ __device__ __forceinline__ int reflect(int i, int n) {
 }
 
 // value of the (optionally transposed) reflect-padded, normalised image at padded coordinates (px, py); 0 outside
-__device__ __forceinline__ float padded_at(const float* __restrict__ img, const Params& p, int transposed, int px,
+template <typename T>
+__device__ __forceinline__ float padded_at(const T* __restrict__ img, const Params& p, int transposed, int px,
                                            int py, bool normalise) {
   const int Hp = p.H + 2 * p.pad, Wp = p.W + 2 * p.pad;
   if (px < 0 || py < 0 || px >= Wp || py >= Hp) return 0.f;
   if (transposed) { const int t = px; px = py; py = t; }
   const int y = reflect(py - p.pad, p.H), x = reflect(px - p.pad, p.W);
-  const float v = img[y * p.W + x];
-  return normalise ? (v - p.mean) * p.inv_std : v;
+  const float v = load_px<T>(img, y * p.W + x);
+  return normalise ? (v - p.mean) * p.inv_std + p.brightness : v;
 }
 
-__device__ __forceinline__ float sample_bilinear(const float* __restrict__ img, const Params& p, const float* t,
+template <typename T>
+__device__ __forceinline__ float sample_bilinear(const T* __restrict__ img, const Params& p, const float* t,
                                                  int transposed, int xo, int yo) {
   const float X = (float)(xo + p.pad), Y = (float)(yo + p.pad);
   const float k = t[6] * X + t[7] * Y + 1.f;
@@ -51,7 +64,8 @@ __device__ __forceinline__ float sample_bilinear(const float* __restrict__ img, 
   return top * (1.f - fy) + bot * fy;
 }
 
-__device__ __forceinline__ float sample_nearest(const float* __restrict__ img, const Params& p, const float* t,
+template <typename T>
+__device__ __forceinline__ float sample_nearest(const T* __restrict__ img, const Params& p, const float* t,
                                                 int transposed, int xo, int yo) {
   const float X = (float)(xo + p.pad), Y = (float)(yo + p.pad);
   const float k = t[6] * X + t[7] * Y + 1.f;
@@ -60,10 +74,12 @@ __device__ __forceinline__ float sample_nearest(const float* __restrict__ img, c
   return padded_at(img, p, transposed, (int)rintf(sx), (int)rintf(sy), false);
 }
 
+template <typename T>
 __global__ void __launch_bounds__(256)
-augment_seg_kernel(const float* __restrict__ images, const float* __restrict__ masks,
-                   const float* __restrict__ transforms, const int* __restrict__ transposed, float* __restrict__ out,
-                   float* __restrict__ out_mask, int B, Params p) {
+augment_seg_kernel(const T* __restrict__ images, const T* __restrict__ masks,
+                   const float* __restrict__ transforms, const int* __restrict__ transposed,
+                   const float* __restrict__ brightness, float* __restrict__ out, float* __restrict__ out_mask, int B,
+                   Params p) {
   ptx::pdl_trigger();
   ptx::pdl_wait();
   const int64_t total = (int64_t)B * p.H * p.W;
@@ -71,7 +87,8 @@ augment_seg_kernel(const float* __restrict__ images, const float* __restrict__ m
     const int x = (int)(i % p.W);
     const int y = (int)((i / p.W) % p.H);
     const int b = (int)(i / ((int64_t)p.W * p.H));
-    const float* img = images + (int64_t)b * p.H * p.W;
+    const T* img = images + (int64_t)b * p.H * p.W;
+    p.brightness = brightness ? brightness[b] : 0.f;
     float t[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) t[j] = transforms[b * 8 + j];
@@ -100,25 +117,39 @@ augment_seg_kernel(const float* __restrict__ images, const float* __restrict__ m
 }  // namespace augment
 }  // namespace tdl
 
-// images/masks: [B, H, W] fp32 in [0,1] (decoded, un-normalised); transforms: [B, 8] output->input projective
-// transforms in the reflect-padded frame; transposed: [B] 0/1.  out: [B, H, W, 2] (normalised image, laplace),
-// out_mask: [B, H, W, 1].  masks/out_mask may be NULL.
-TDL_API int tdl_augment_seg(const float* images, const float* masks, const float* transforms, const int* transposed,
-                            float* out, float* out_mask, int B, int H, int W, int pad, float mean, float stddev,
-                            int laplace_2d, void* stream) {
+// images/masks: [B, H, W] decoded, un-normalised: fp32 in [0,1], or (input_is_u8) raw uint8 that the kernel divides
+// by 255; transforms: [B, 8] output->input projective transforms in the reflect-padded frame; transposed: [B] 0/1;
+// brightness: [B] additive delta on the normalised image (tf.image.random_brightness,
+// preprocessing/preprocessing.py:169-170) or NULL.  out: [B, H, W, 2] (normalised image, laplace), out_mask:
+// [B, H, W, 1].  masks/out_mask may be NULL.
+TDL_API int tdl_augment_seg_ex(const void* images, const void* masks, int input_is_u8, const float* transforms,
+                               const int* transposed, const float* brightness, float* out, float* out_mask, int B,
+                               int H, int W, int pad, float mean, float stddev, int laplace_2d, void* stream) {
   TDL_REQUIRE(H > pad && W > pad, "reflect padding must be smaller than the image");
   TDL_REQUIRE(stddev > 0.f, "stddev must be positive");
   if (B <= 0) return 0;
-  tdl::augment::Params p = {H, W, pad, mean, 1.f / stddev, laplace_2d};
+  tdl::augment::Params p = {H, W, pad, mean, 1.f / stddev, laplace_2d, 0.f};
   const int64_t total = (int64_t)B * H * W;
   int64_t blocks = (total + 255) / 256;
   const int64_t cap = (int64_t)tdl::num_sms() * 8;
   if (blocks > cap) blocks = cap;
-  {
-    cudaError_t _le = tdl::launch_pdl(tdl::augment::augment_seg_kernel, dim3((int)blocks), dim3(256), 0,
-        (cudaStream_t)stream, images, masks, transforms, transposed, out, out_mask, B, p);
-    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "tdl::augment::augment_seg_kernel");
-  }
+  cudaError_t le;
+  if (input_is_u8)
+    le = tdl::launch_pdl(tdl::augment::augment_seg_kernel<uint8_t>, dim3((int)blocks), dim3(256), 0,
+                         (cudaStream_t)stream, (const uint8_t*)images, (const uint8_t*)masks, transforms, transposed,
+                         brightness, out, out_mask, B, p);
+  else
+    le = tdl::launch_pdl(tdl::augment::augment_seg_kernel<float>, dim3((int)blocks), dim3(256), 0,
+                         (cudaStream_t)stream, (const float*)images, (const float*)masks, transforms, transposed,
+                         brightness, out, out_mask, B, p);
+  if (le != cudaSuccess) return tdl::cuda_fail(le, "tdl::augment::augment_seg_kernel");
   TDL_LAUNCH_OK("augment_seg_kernel");
   return 0;
+}
+
+TDL_API int tdl_augment_seg(const float* images, const float* masks, const float* transforms, const int* transposed,
+                            float* out, float* out_mask, int B, int H, int W, int pad, float mean, float stddev,
+                            int laplace_2d, void* stream) {
+  return tdl_augment_seg_ex(images, masks, 0, transforms, transposed, nullptr, out, out_mask, B, H, W, pad, mean,
+                            stddev, laplace_2d, stream);
 }

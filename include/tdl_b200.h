@@ -170,6 +170,11 @@ int tdl_u8_to_bf16_normalize(const void* x_u8, void* y_bf16, int64_t pixels, int
 int tdl_augment_seg(const float* images, const float* masks, const float* transforms, const int* transposed,
                     float* out, float* out_mask, int B, int H, int W, int pad, float mean, float stddev,
                     int laplace_2d, void* stream);
+/* same, with raw uint8 decoded inputs (input_is_u8: the kernel divides by 255) and an optional per-sample brightness
+ * delta (preprocessing/preprocessing.py:169-170); this is the entry point the input pipeline calls per batch */
+int tdl_augment_seg_ex(const void* images, const void* masks, int input_is_u8, const float* transforms,
+                       const int* transposed, const float* brightness, float* out, float* out_mask, int B, int H,
+                       int W, int pad, float mean, float stddev, int laplace_2d, void* stream);
 
 /* ---- losses / metrics (reference: core/losses.py:5-92 pinned to CPU at model.py:391; core/metric.py:6-71) ---- */
 int tdl_lovasz_hinge(const float* logits, const float* labels, int B, int P, float grad_scale, float* loss_out,

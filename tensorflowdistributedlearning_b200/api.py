@@ -61,6 +61,9 @@ class Model:
         self.optim_overrides = {k: kwargs[k] for k in ("comm", "overlap", "bucket_cap_mb") if k in kwargs}
         self.throttle_secs = kwargs.get("throttle_secs", 300)
         self.workers = kwargs.get("workers", 4)
+        # decode on CPU threads, one augmentation kernel launch per batch on the GPU (K20); CPU towers augment on host
+        self._device_augment = kwargs.get("device_augment")
+        self.sharded_eval = kwargs.get("sharded_eval", True)
 
         self.model_name = os.path.basename(os.path.normpath(model_dir))
         self.model_dir = model_dir
@@ -103,8 +106,11 @@ class Model:
             ds = SegmentationFolder(pairs, augment=augment, reference_compat=self.reference_compat, seed=self.seed,
                                     input_shape=self.input_shape)
             rank, world = (0, 1) if single_tower else (self.group.rank, self.group.world)
+            on_gpu = self.group.device.type == "cuda"
+            dev_aug = on_gpu if self._device_augment is None else bool(self._device_augment)
             return iter(BatchLoader(ds, batch_size, shuffle=shuffle, repeat=repeat, rank=rank, world=world,
-                                    workers=self.workers, seed=self.seed + fold, prefetch=2 * max(self.n_towers, 1)))
+                                    workers=self.workers, seed=self.seed + fold, prefetch=2 * max(self.n_towers, 1),
+                                    device_augment=dev_aug, device=self.group.device if on_gpu else None))
         return input_fn
 
     def _make_test_input(self, batch_size: int, test_directory: str, tti: str):
@@ -143,15 +149,37 @@ class Model:
                                                                        greater_is_better=True),
                                           exports_to_keep=self.save_best),)
             eval_batch = per_tower * 2
-            eval_spec = EvalSpec(self._make_input_fn("eval", i, eval_batch, repeat=True, single_tower=True),
+            sharded = bool(self.sharded_eval and self.group.distributed)
+            eval_spec = EvalSpec(self._make_input_fn("eval", i, eval_batch, repeat=True, single_tower=not sharded),
                                  steps=max(len(test_index) // eval_batch, 1), throttle_secs=self.throttle_secs,
-                                 start_delay_secs=0, exporters=exporters)
+                                 start_delay_secs=0, exporters=exporters, sharded=sharded)
             results[i] = est.train_and_evaluate(train_spec, eval_spec)
             self.n_params = est.n_params
             if est.trainer is not None:
                 est.trainer.close()
             if self.group.is_primary:
                 print(f"INFO:Finished fold {i}")
+        return results
+
+    # ---- evaluate (no training) ----
+    def evaluate(self, batch_size: int, steps: Optional[int] = None, checkpoint_path: Optional[str] = None,
+                 folds: Optional[Sequence[int]] = None) -> Dict[int, Dict[str, float]]:
+        """Evaluate every trained fold's newest checkpoint (or ``checkpoint_path`` for a single fold) on that fold's
+        held-out split, without training: what ``tf.estimator`` does for the reference's EvalSpec (model.py:207-223).
+        The ``eval`` symlink directories of the folds must exist (``train`` creates them)."""
+        results = {}
+        for fold in (range(self.n_folds) if folds is None else folds):
+            pairs = F.list_fold(self.model_dir, "eval", fold) if os.path.isdir(f"{self.model_dir}/fold{fold}") else []
+            if not pairs:
+                continue
+            est = self._estimator(fold)
+            sharded = bool(self.sharded_eval and self.group.distributed)
+            n = steps or max(len(pairs) // batch_size, 1)
+            results[fold] = est.evaluate(self._make_input_fn("eval", fold, batch_size, repeat=True,
+                                                             single_tower=not sharded),
+                                         steps=n, checkpoint_path=checkpoint_path, sharded=sharded)
+        if not results:
+            raise RuntimeError(f"no fold with evaluation data found under {self.model_dir}")
         return results
 
     # ---- predict ----

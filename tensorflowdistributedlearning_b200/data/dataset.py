@@ -4,6 +4,9 @@
   laplace channel per sample (``data/preprocessing.py``); pairing is by id.
 * ``SyntheticClassification`` / ``SyntheticSegmentation`` -- deterministic random data of a named shape, used by
   every BASELINE.json config (there is no network for datasets).
+* ``BatchLoader(device_augment=True)`` -- the worker threads only decode; one ``tdl_augment_seg_ex`` launch per
+  batch does reflect pad / transpose / warp / crop / normalise / laplace on the GPU (``data/gpu_augment.py``), with
+  the per-sample parameters drawn exactly as the CPU path draws them (same seed -> same augmentation).
 * ``BatchLoader``         -- shuffle buffer (10 x batch, crossing epoch boundaries like ``shuffle_and_repeat``),
   worker threads for decode/augment (the reference maps single-threaded, model.py:315), pinned batches,
   prefetch depth 2 x towers.  Every tower dequeues whole consecutive batches (A17): tower r of N takes
@@ -37,9 +40,25 @@ class SegmentationFolder:
         img_path, mask_path = self.pairs[i]
         image = PP.parse_image(img_path, self.input_shape)
         mask = PP.parse_image(mask_path, self.input_shape)
-        rng = np.random.RandomState((self.seed * 1_000_003 + epoch * 7919 + i) % (2 ** 31 - 1))
+        rng = self._rng(i, epoch)
         feats, mask = PP.read_and_preprocess(image, mask, self.augment, rng, self.reference_compat, **self.aug_kw)
         return feats["images"], mask
+
+    def _rng(self, i: int, epoch: int) -> np.random.RandomState:
+        return np.random.RandomState((self.seed * 1_000_003 + epoch * 7919 + i) % (2 ** 31 - 1))
+
+    def raw(self, i: int, epoch: int = 0, pad: int = 40):
+        """(image uint8 [H,W], mask uint8 [H,W], augmentation parameters) -- the decode-only half of ``__getitem__``;
+        the parameters are drawn from the same generator state, so the device path reproduces the CPU path."""
+        img_path, mask_path = self.pairs[i]
+        image = PP.parse_image_u8(img_path, self.input_shape)
+        mask = PP.parse_image_u8(mask_path, self.input_shape)
+        if self.augment:
+            h, w = self.input_shape
+            params = PP.sample_augmentation(self._rng(i, epoch), h + 2 * pad, w + 2 * pad, **self.aug_kw)
+        else:
+            params = PP.identity_augmentation()
+        return image, mask, params
 
 
 class SyntheticSegmentation:
@@ -95,8 +114,15 @@ class BatchLoader:
 
     def __init__(self, dataset, batch_size: int, shuffle: bool = False, repeat: bool = True, rank: int = 0,
                  world: int = 1, workers: int = 4, prefetch: Optional[int] = None, seed: int = 0,
-                 drop_last: bool = True, pin: Optional[bool] = None):
+                 drop_last: bool = True, pin: Optional[bool] = None, device_augment: bool = False,
+                 augment_fn: Optional[Callable] = None, device=None):
+        """``device_augment``: the dataset must offer ``raw(i, epoch) -> (image_u8, mask_u8, params)``; batches are
+        yielded as DEVICE tensors ([B,H,W,2] fp32, [B,H,W,1] fp32) produced by one augmentation kernel launch per
+        batch on the consumer's current stream (``augment_fn`` defaults to ``gpu_augment.augment_batch``)."""
         self.ds, self.batch, self.shuffle, self.repeat = dataset, batch_size, shuffle, repeat
+        self.device_augment, self.augment_fn, self.device = bool(device_augment), augment_fn, device
+        if self.device_augment and not hasattr(dataset, "raw"):
+            raise TypeError("device_augment=True needs a dataset with raw(i, epoch) -> (image_u8, mask_u8, params)")
         self.rank, self.world, self.workers, self.seed, self.drop_last = rank, world, max(workers, 1), seed, drop_last
         self.prefetch = prefetch or 2 * world
         self.pin = torch.cuda.is_available() if pin is None else pin
@@ -127,15 +153,32 @@ class BatchLoader:
             yield buf.pop()
 
     def _batches_for_this_tower(self) -> Iterator[List[Tuple[int, int]]]:
-        cur, b = [], 0
+        """Tower r's batch of every COMPLETE round of ``world`` batches.  A single-pass stream whose batch count is
+        not a multiple of ``world`` drops the ragged last round on every tower: otherwise the low ranks would run one
+        more synchronous step than the others and wait for peers that never launch it."""
+        cur, b, mine = [], 0, None
         for item in self._index_stream():
             cur.append(item)
             if len(cur) == self.batch:
                 if b % self.world == self.rank:
-                    yield cur
+                    mine = cur
                 cur, b = [], b + 1
-        if cur and not self.drop_last and b % self.world == self.rank:
+                if b % self.world == 0:
+                    yield mine
+                    mine = None
+        if cur and not self.drop_last and self.world == 1:
             yield cur
+
+    def _augment_on_device(self, xs: torch.Tensor, ys: torch.Tensor, params):
+        """uint8 batch -> device (async copy from pinned memory) -> one augmentation kernel on the current stream."""
+        fn = self.augment_fn
+        if fn is None:
+            from .gpu_augment import augment_batch as fn
+        dev = self.device
+        if dev is None:
+            dev = torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available() else torch.device("cpu")
+        compat = getattr(self.ds, "reference_compat", True)
+        return fn(xs.to(dev, non_blocking=True), ys.to(dev, non_blocking=True), params, reference_compat=compat)
 
     def __iter__(self):
         q: "queue.Queue" = queue.Queue(maxsize=self.prefetch)
@@ -149,13 +192,20 @@ class BatchLoader:
                     for idxs in self._batches_for_this_tower():
                         if stop.is_set():
                             return
-                        samples = list(pool.map(lambda ie: self.ds.__getitem__(ie[0], ie[1]), idxs))
-                        xs, ys = _collate(samples)
+                        if self.device_augment:  # decode only; the warp runs on the GPU, once per batch
+                            raws = list(pool.map(lambda ie: self.ds.raw(ie[0], ie[1]), idxs))
+                            xs = torch.from_numpy(np.stack([r[0] for r in raws]))
+                            ys = torch.from_numpy(np.stack([r[1] for r in raws]))
+                            params = [r[2] for r in raws]
+                        else:
+                            samples = list(pool.map(lambda ie: self.ds.__getitem__(ie[0], ie[1]), idxs))
+                            xs, ys = _collate(samples)
+                            params = None
                         if self.pin:
                             xs, ys = xs.pin_memory(), ys.pin_memory()
                         while not stop.is_set():
                             try:
-                                q.put((xs, ys), timeout=0.1)
+                                q.put((xs, ys, params), timeout=0.1)
                                 break
                             except queue.Full:
                                 continue
@@ -172,6 +222,10 @@ class BatchLoader:
                     return
                 if isinstance(item, Exception):
                     raise item
-                yield item
+                xs, ys, params = item
+                if params is not None:
+                    yield self._augment_on_device(xs, ys, params)
+                else:
+                    yield xs, ys
         finally:
             stop.set()

@@ -40,6 +40,17 @@ def parse_image(filename: str, size: Tuple[int, int] = (101, 101)) -> np.ndarray
     return arr[:, :, None]
 
 
+def parse_image_u8(filename: str, size: Tuple[int, int] = (101, 101)) -> np.ndarray:
+    """The decoded single-channel image as raw uint8 [H, W] (what the device-side augmentation ingests)."""
+    from PIL import Image
+
+    with Image.open(filename) as im:
+        arr = np.asarray(im.convert("L"), dtype=np.uint8)
+    if arr.shape != tuple(size):
+        raise ValueError(f"{filename}: expected {size}, got {arr.shape}")
+    return arr
+
+
 def normalise(image: np.ndarray) -> np.ndarray:
     return (image - MEAN) / STD
 
@@ -138,10 +149,14 @@ def central_crop(img: np.ndarray, fraction: float) -> np.ndarray:
 # ---------------------------------------------------------------------------------------------
 def sample_augmentation(rng: np.random.RandomState, height: int, width: int, horizontal_flip=True, vertical_flip=True,
                         rotate_range=10, crop_probability=0.0, crop_min_percent=0.9, crop_max_percent=1.1,
-                        height_shift_range=0.2, width_shift_range=0.2, constant_shift=None) -> Dict:
-    """Draw one sample's augmentation parameters and the composed output->input transform."""
+                        height_shift_range=0.2, width_shift_range=0.2, constant_shift=None,
+                        brightness_range=0.0) -> Dict:
+    """Draw one sample's augmentation parameters and the composed output->input transform.
+    ``brightness_range`` > 0 adds a delta ~ U(-range, range) to the normalised image before the warp
+    (tf.image.random_brightness, preprocessing/preprocessing.py:169-170; the reference's default 0 draws nothing)."""
     ts = []
     do_transpose = bool(rng.rand() < 0.5)
+    brightness = float(rng.uniform(-brightness_range, brightness_range)) if brightness_range > 0 else 0.0
     if horizontal_flip and rng.rand() < 0.5:
         ts.append(np.array([-1, 0, width, 0, 1, 0, 0, 0], dtype=np.float64))
     if vertical_flip and rng.rand() < 0.5:
@@ -163,7 +178,7 @@ def sample_augmentation(rng: np.random.RandomState, height: int, width: int, hor
         top = rng.uniform(0, height * (1 - pct))
         ts.append(np.array([pct, 0, left, 0, pct, top, 0, 0], dtype=np.float64))
     t = compose_transforms(*ts) if ts else np.array([1, 0, 0, 0, 1, 0, 0, 0], dtype=np.float64)
-    return {"transpose": do_transpose, "transform": t}
+    return {"transpose": do_transpose, "transform": t, "brightness": brightness}
 
 
 def apply_augmentation(image: np.ndarray, mask: np.ndarray, params: Dict, reference_compat: bool = True, pad: int = 40):
@@ -176,11 +191,18 @@ def apply_augmentation(image: np.ndarray, mask: np.ndarray, params: Dict, refere
     h = image.shape[0]
     if params["transpose"]:
         image, mask = image.transpose(1, 0, 2), mask.transpose(1, 0, 2)
+    if params.get("brightness", 0.0):
+        image = image + np.float32(params["brightness"])
     image = transform_image(image, params["transform"], "BILINEAR")
     mask = transform_image(mask, params["transform"], "NEAREST")
     image, mask = central_crop(image, h0 / h), central_crop(mask, h0 / h)
     image = np.concatenate([image, laplace(image, reference_compat)], axis=-1).astype(np.float32)
     return image, mask.astype(np.float32)
+
+
+def identity_augmentation() -> Dict:
+    """Parameters under which the augmentation kernels reduce to normalise + laplace (evaluation batches)."""
+    return {"transpose": False, "transform": np.array([1, 0, 0, 0, 1, 0, 0, 0], dtype=np.float64), "brightness": 0.0}
 
 
 def read_and_preprocess(image: np.ndarray, mask: np.ndarray, augment: bool = False,

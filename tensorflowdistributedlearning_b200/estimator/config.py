@@ -2,8 +2,9 @@
 module-level constants + **kwargs, model.py:13-24,29-38,63-121)."""
 from __future__ import annotations
 
-from dataclasses import asdict, dataclass, field
-from typing import Any, Callable, Dict, Optional, Tuple
+import ast
+from dataclasses import asdict, dataclass, field, fields
+from typing import Any, Callable, Dict, Iterable, Optional, Tuple
 
 
 @dataclass
@@ -20,6 +21,20 @@ class ModelConfig:
     block_type: str = "bottleneck"
     in_channels: int = 2
     num_classes: Optional[int] = None
+
+    def build(self, model_name: str = "model"):
+        """The network this configuration names: ``refseg`` = the reference's segmentation network under the variable
+        scope ``model_name`` (model.py:353-370); anything else goes through ``models.build``."""
+        from .. import models
+
+        if self.name.lower().replace("_", "") in ("refseg", "resnetmodel", "seg"):
+            return models.ResNetSegModel(
+                model_name=model_name, in_channels=self.in_channels, weight_decay=self.weight_decay,
+                batch_norm_decay=self.batch_norm_decay, batch_norm_epsilon=self.batch_norm_epsilon,
+                batch_norm_scale=self.batch_norm_scale, output_stride=self.output_stride, base_depth=self.base_depth,
+                input_shape=tuple(self.input_shape), n_blocks=tuple(self.n_blocks), block_type=self.block_type)
+        kw = {} if self.num_classes is None else {"num_classes": self.num_classes}
+        return models.build(self.name, **kw)
 
 
 @dataclass
@@ -67,3 +82,31 @@ class EvalSpec:
     start_delay_secs: int = 0
     exporters: Tuple = field(default_factory=tuple)
     name: str = "eval"
+    sharded: bool = False                # True: input_fn yields this tower's share, all towers evaluate (SUM on read)
+
+
+def apply_overrides(sections: Dict[str, Any], items: Iterable[str]) -> Dict[str, Any]:
+    """Command-line overrides of dataclass fields: every item is ``section.field=value`` (``model.base_depth=128``,
+    ``optim.lr=0.01``, ``run.save_checkpoints_steps=100``); values are Python literals, bare words stay strings.
+    Unknown sections / fields are errors ("a CLI that overrides dataclass fields")."""
+    for item in items or ():
+        if "=" not in item or "." not in item.split("=", 1)[0]:
+            raise ValueError(f"override '{item}': expected section.field=value")
+        key, raw = item.split("=", 1)
+        section, name = key.split(".", 1)
+        if section not in sections:
+            raise ValueError(f"override '{item}': unknown section '{section}' (have {sorted(sections)})")
+        cfg = sections[section]
+        if name not in {f.name for f in fields(cfg)}:
+            raise ValueError(f"override '{item}': {type(cfg).__name__} has no field '{name}'")
+        try:
+            value = ast.literal_eval(raw)
+        except (ValueError, SyntaxError):
+            value = raw
+        cur = getattr(cfg, name)
+        if isinstance(cur, tuple) and isinstance(value, list):
+            value = tuple(value)
+        if isinstance(cur, float) and isinstance(value, int) and not isinstance(value, bool):
+            value = float(value)
+        setattr(cfg, name, value)
+    return sections

@@ -6,8 +6,11 @@ Behavioural contract kept from the reference:
   * train metrics are streaming means since the start of training; eval metrics restart per evaluate call
   * ``train_and_evaluate``: train continuously; after a checkpoint, if >= ``throttle_secs`` since the last
     evaluation, evaluate that state and hand the result to the exporters; final evaluate + export at max_steps
-  * evaluation and prediction run on tower 0's device (``eval_distribute`` is None in the reference)
-  * summaries / checkpoints are written by tower 0; the logged loss is the tower mean
+  * prediction runs on tower 0's device; evaluation is sharded over the towers by default (every tower evaluates
+    batches r, r+N, ... of the same stream and the metric accumulators are SUM-reduced on read -- same numbers as the
+    reference's single-device evaluation, and no tower idles behind a timed barrier while tower 0 evaluates)
+  * summaries / checkpoints are written by tower 0; the logged loss is the tower mean (it rides, with the metric
+    sums, in the packed statistics reduction of the step)
 """
 from __future__ import annotations
 
@@ -37,6 +40,12 @@ class StreamingMean:
     def update(self, v: torch.Tensor) -> None:
         self.total += v.detach().double().sum()
         self.count += v.numel()
+
+    def update_global(self, total: torch.Tensor, count: float) -> None:
+        """Add an already cross-tower-reduced (sum, count): the accumulators then hold the global totals on every
+        tower and ``value()`` needs no collective."""
+        self.total += total.detach().double()
+        self.count += count
 
     def value(self, group: Optional[TowerGroup] = None) -> float:
         t = torch.stack([self.total, self.count])
@@ -100,6 +109,7 @@ class Estimator:
                 model, self.group, batch=images.shape[0], input_hwc=tuple(images.shape[1:]),
                 label_shape=tuple(labels.shape[1:]), label_dtype=labels.dtype, loss_fn=self.task["loss_fn"],
                 use_graph=self.config.use_cuda_graph, input_is_u8=self.input_is_u8, mean=self.mean, std=self.std,
+                keep_output_sample=self.task_name == "segmentation",
                 kind=o.kind, lr=o.lr, momentum=o.momentum, weight_decay=o.weight_decay, beta1=o.beta1, beta2=o.beta2,
                 eps=o.eps, decay_steps=o.decay_steps, decay_rate=o.decay_rate, comm=o.comm,
                 bucket_cap_mb=o.bucket_cap_mb, overlap=o.overlap)
@@ -183,14 +193,24 @@ class Estimator:
                 nxt = None
             loss = trainer.train_step(cur[0], cur[1], prefetch=nxt)
             step += 1
+            world = self.group.world
             for k, m in self._train_metrics.items():
-                if k in trainer.metrics:
+                if k in trainer.metric_sums:  # tower mean of the per-tower sums, reduced inside the step (X4)
+                    m.update_global(trainer.metric_sums[k] * world, trainer.metrics[k].numel() * world)
+                elif k in trainer.metrics:
                     m.update(trainer.metrics[k])
             values: Dict = {"loss": loss, self.task["loss_key"]: loss, "learning_rate": None}
             if self.config.save_summary_steps and step % self.config.save_summary_steps == 0:
                 for k, name in self.task["metric_keys"].items():
-                    values[name] = self._train_metrics[k].value(self.group)
+                    reduced = k in trainer.metric_sums
+                    values[name] = self._train_metrics[k].value(None if reduced else self.group)
                 values["learning_rate"] = trainer.opt.current_lr()
+                if self.group.is_primary and trainer.output_sample is not None:
+                    # the reference's four train-mode image summaries, first sample only (model.py:406-439,470-473)
+                    prob = torch.sigmoid(trainer.output_sample[:, :, 0])
+                    values["images"] = {
+                        "train_image": trainer.images[0, :, :, 0].float(), "train_label": trainer.labels[0, :, :, 0].float(),
+                        "train_prob": prob, "train_prediction": (prob > self.params.get("threshold", 0.5)).float()}
             values = {k: v for k, v in values.items() if v is not None}
             for h in hooks:
                 h.after_step(self, step, values)
@@ -204,8 +224,13 @@ class Estimator:
     # ---- evaluate ----
     @torch.no_grad()
     def evaluate(self, input_fn: Callable[[], Iterable], steps: Optional[int] = None, name: str = "eval",
-                 checkpoint_path: Optional[str] = None) -> Dict[str, float]:
+                 checkpoint_path: Optional[str] = None, sharded: bool = False) -> Dict[str, float]:
+        """``sharded=True`` (all towers must call): ``input_fn`` yields THIS tower's batches (r, r+N, ... of the global
+        stream), ``steps`` counts global batches, and the accumulators are SUM-reduced over towers when read."""
         model = self._ensure_model()
+        sharded = bool(sharded and self.group.distributed)
+        if sharded and steps is not None:
+            steps = len(range(self.group.rank, steps, self.group.world))
         if checkpoint_path is not None:
             ckpt.load_checkpoint(checkpoint_path, model, None)
         elif self.trainer is None:
@@ -233,8 +258,9 @@ class Estimator:
             last = (x, y, logits)
             n += 1
         step = self.global_step
-        result = {name_: metrics[k].value() for k, name_ in self.task["metric_keys"].items()}
-        result[self.task["loss_key"]] = loss_mean.value()
+        g = self.group if sharded else None
+        result = {name_: metrics[k].value(g) for k, name_ in self.task["metric_keys"].items()}
+        result[self.task["loss_key"]] = loss_mean.value(g)
         result["loss"] = result[self.task["loss_key"]]
         result["global_step"] = step
         if writer is not None:
@@ -289,9 +315,15 @@ class Estimator:
                  "evaluated_step": -1}
 
         def run_eval(step: int) -> None:
-            if self.group.is_primary:
+            if getattr(eval_spec, "sharded", False) and self.group.distributed:
+                # every tower evaluates its share; nobody waits behind a collective timeout for tower 0
+                res = self.evaluate(eval_spec.input_fn, eval_spec.steps, eval_spec.name, sharded=True)
+            elif self.group.is_primary:
                 res = self.evaluate(eval_spec.input_fn, eval_spec.steps, eval_spec.name)
-                state["result"] = res
+            else:
+                res = None
+            state["result"] = res
+            if self.group.is_primary:
                 for ex in eval_spec.exporters:
                     ex.export(self, res)
             state["evaluated_step"] = step

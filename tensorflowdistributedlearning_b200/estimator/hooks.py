@@ -4,7 +4,8 @@
   (reference: RunConfig(save_checkpoints_steps=500), model.py:118; log Test.ipynb:203,207)
 * ``StepCounterHook``     -- ``global_step/sec`` + loss every 100 steps (Test.ipynb:209-213), device-timed,
   max over towers
-* ``SummarySaverHook``    -- scalars (and up to one image per tag) every N steps into ``{dir}`` as TensorBoard
+* ``SummarySaverHook``    -- scalars (and up to one image per tag: ``{mode}_image/_label/_prob/_prediction``,
+  model.py:406-439, handed over in ``values["images"]``) every N steps into ``{dir}`` as TensorBoard
   events plus a JSONL mirror (reference: SummarySaverHook(save_steps=20 / 1), model.py:470-481)
 * ``NanLossHook``         -- abort on a non-finite loss (failure detection)
 Only tower 0 writes files (A27); every tower runs the hooks so collective calls stay aligned.
@@ -100,7 +101,10 @@ class SummaryWriter:
                 self._tb.add_scalar(k, float(v), step)
 
     def image(self, tag: str, img_hw: torch.Tensor, step: int) -> None:
-        """img_hw: [H, W] float tensor; written as an 8-bit PNG by the event writer (CPU encode, no graphics API)."""
+        """img_hw: [H, W] float tensor; written as an 8-bit PNG by the event writer (CPU encode, no graphics API).
+        The JSONL mirror records that the tag was written (tag, step, shape)."""
+        self._jsonl.write(json.dumps({"step": int(step), "image": tag, "shape": list(img_hw.shape)}) + "\n")
+        self._jsonl.flush()
         if self._tb is None:
             return
         x = img_hw.detach().float().cpu()

@@ -21,6 +21,7 @@ import torch
 import torch.nn as nn
 
 ALIGN = 8  # elements; keeps every tensor 32-byte (fp32) / 16-byte (bf16) aligned inside the flat buffers
+N_SCALARS = 8  # per-step scalars that ride behind the moving statistics: slot 0 = loss, 1.. = metric sums (X4/X5)
 
 
 @dataclass
@@ -93,7 +94,11 @@ class FlatParams:
                     self.stat_refs.append((m, name, soff, b.numel(), b.shape))
                     soff += _round_up(b.numel())
         self.stats_total = soff
-        self.stats_flat = alloc(max(self.stats_total, ALIGN), torch.float32, "stats")
+        # the logged loss (tower mean, X5) and the per-step metric sums (X4) travel in the same buffer, so one packed
+        # one-shot reduction per step covers moving statistics and scalars
+        self.scalar_offset = soff
+        self.stats_flat = alloc(self.stats_total + N_SCALARS, torch.float32, "stats")
+        self.scalars = self.stats_flat[self.scalar_offset:self.scalar_offset + N_SCALARS]
         for m, name, o, n, shape in self.stat_refs:
             view = self.stats_flat[o:o + n].view(shape)
             view.copy_(m._buffers[name])

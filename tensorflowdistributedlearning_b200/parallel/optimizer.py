@@ -190,14 +190,15 @@ class DistributedOptimizer:
             else:
                 for b in f.buckets:
                     self._launch_bucket(b)
-            if self.sync_bn_stats and f.stats_total > 0:
-                self._p2p_stats.all_reduce_mean_(self._stats_staging, 0, f.stats_total)
+            # one packed one-shot: moving statistics (X3) + loss / metric scalars (X4, X5)
+            lo = 0 if self.sync_bn_stats else f.scalar_offset
+            self._p2p_stats.all_reduce_mean_(self._stats_staging, lo, f.stats_flat.numel() - lo)
             return
         if self.comm in ("nccl", "gloo"):
             dist.all_reduce(f.grad_flat)
-            if self.sync_bn_stats and f.stats_total > 0:
-                dist.all_reduce(f.stats_flat)
-                f.stats_flat.div_(self.group.world)
+            packed = f.stats_flat if self.sync_bn_stats else f.scalars
+            dist.all_reduce(packed)
+            packed.div_(self.group.world)
         scale = 1.0 / self.group.world
         if self.on_gpu:
             from ..ops import native_ops as O

@@ -35,7 +35,7 @@ class TowerTrainer:
     def __init__(self, model: torch.nn.Module, group: TowerGroup, *, batch: int, input_hwc: Tuple[int, int, int],
                  label_shape: Tuple[int, ...] = (), label_dtype=torch.int64,
                  loss_fn: Callable = classification_loss, compute_dtype=torch.bfloat16, use_graph: bool = True,
-                 mean=None, std=None, input_is_u8: bool = True, **opt_kw):
+                 mean=None, std=None, input_is_u8: bool = True, keep_output_sample: bool = False, **opt_kw):
         self.group = group
         dev = group.device
         self.device = dev
@@ -51,8 +51,16 @@ class TowerTrainer:
         self.labels = torch.zeros((batch, *label_shape), dtype=label_dtype, device=dev)
         self.mean = torch.tensor(mean if mean is not None else [0.0] * c, dtype=torch.float32, device=dev)
         self.inv_std = 1.0 / torch.tensor(std if std is not None else [1.0] * c, dtype=torch.float32, device=dev)
+        # `loss` is what gets logged: the MEAN over towers (EstimatorSpec(loss=...) under MirroredStrategy, model.py:491-500,
+        # SURVEY X5); `local_loss` is this tower's own.  `metric_sums[k]` is the tower mean of the per-tower SUM of
+        # metric k over the batch -- times the world size it is the global sum `tf.metrics.mean` accumulates (X4).
+        # All of them ride behind the moving statistics in the packed one-shot reduction of the step.
         self.loss = torch.zeros((), dtype=torch.float32, device=dev)
+        self.local_loss = torch.zeros((), dtype=torch.float32, device=dev)
         self.metrics = {}
+        self.metric_sums = {}
+        self.keep_output_sample = keep_output_sample
+        self.output_sample: Optional[torch.Tensor] = None  # model output of sample 0 (image summaries, model.py:406-439)
         self.use_graph = bool(use_graph and dev.type == "cuda")
         self._nvtx = os.environ.get("TDL_NVTX", "0") == "1"
         if dev.type == "cuda":
@@ -106,14 +114,27 @@ class TowerTrainer:
         mark("tdl/backward+bucket_allreduce")
         loss.backward()
         done()
+        scalars = self.opt.flat.scalars
+        keys = sorted(metrics)[:scalars.numel() - 1]
+        self.local_loss.copy_(loss.detach())
+        scalars[:1 + len(keys)].copy_(torch.stack([loss.detach().float()] +
+                                                  [metrics[k].detach().float().sum() for k in keys]))
         mark("tdl/optimizer_tail")
-        self.opt.step()
+        self.opt.step()  # gradients + optimizer, then ONE packed mean over towers: moving statistics, loss, metric sums
         done()
-        self.loss.copy_(loss.detach())
+        self.loss.copy_(scalars[0])
+        for i, k in enumerate(keys):
+            if k not in self.metric_sums:
+                self.metric_sums[k] = torch.zeros((), dtype=torch.float32, device=self.device)
+            self.metric_sums[k].copy_(scalars[1 + i])
         for k, v in metrics.items():
             if k not in self.metrics:
                 self.metrics[k] = torch.zeros_like(v)
             self.metrics[k].copy_(v)
+        if self.keep_output_sample:
+            if self.output_sample is None:
+                self.output_sample = torch.zeros_like(out[0], dtype=torch.float32)
+            self.output_sample.copy_(out[0].detach())
         if self.device.type == "cuda":
             TF.invalidate_prepared_weights()  # the optimizer has moved the weights
 
@@ -162,6 +183,15 @@ class TowerTrainer:
         if self._stage_images is None:
             self._stage_images = torch.empty_like(self.images)
             self._stage_labels = torch.empty_like(self.labels)
+        if images_host.is_cuda:
+            # a batch the input pipeline already produced on the device (GPU augmentation): it was written on the
+            # current stream, so the move into the staging buffers simply follows it there
+            cur = torch.cuda.current_stream()
+            self._stage_images.copy_(images_host, non_blocking=True)
+            self._stage_labels.copy_(labels_host, non_blocking=True)
+            self._copied.record(cur)
+            self._staged = True
+            return
         self._copy_stream.wait_event(self._stage_free)  # the previous staging contents have been consumed
         with torch.cuda.stream(self._copy_stream):
             self._stage_images.copy_(images_host, non_blocking=True)

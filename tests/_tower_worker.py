@@ -15,6 +15,8 @@ from tensorflowdistributedlearning_b200.parallel.tower import TowerGroup  # noqa
 def main():
     out_dir, mode = sys.argv[1], sys.argv[2]
     group = TowerGroup(device="cpu")
+    if mode == "trainer_scalars":
+        return trainer_scalars(out_dir, group)
     torch.manual_seed(100 + group.rank)  # different init per tower: the X2 broadcast must make them equal
     model = models.SmallResNet(num_classes=10)
     if mode == "frozen_bn":
@@ -38,6 +40,28 @@ def main():
         hashes.append(opt.flat.param_flat.clone())
     torch.save({"params": opt.flat.param_flat.clone(), "stats": opt.flat.stats_flat.clone(), "per_step": hashes,
                 "step": int(opt.global_step.item()), "loss": float(loss)}, os.path.join(out_dir, f"{mode}_w{group.world}_r{group.rank}.pt"))
+    group.barrier()
+    group.shutdown()
+
+
+def trainer_scalars(out_dir, group):
+    """X4/X5: the logged loss is the tower mean and the metric sums are global, both out of the step's packed
+    reduction (no extra collective)."""
+    from tensorflowdistributedlearning_b200.parallel.trainer import TowerTrainer, classification_loss
+
+    torch.manual_seed(5)
+    model = models.SmallResNet(num_classes=10)
+    tr = TowerTrainer(model, group, batch=8, input_hwc=(32, 32, 3), loss_fn=classification_loss, input_is_u8=False,
+                      use_graph=False, kind="sgdm", lr=0.05)
+    g = torch.Generator().manual_seed(11 + group.rank)  # every tower sees different data
+    rec = []
+    for _ in range(2):
+        x = torch.randn(8, 32, 32, 3, generator=g)
+        y = torch.randint(0, 10, (8,), generator=g)
+        logged = tr.train_step(x, y)
+        rec.append(dict(logged=logged, local=float(tr.local_loss), top1_mean_of_sums=float(tr.metric_sums["top1"]),
+                        top1_local_sum=float(tr.metrics["top1"].float().sum())))
+    torch.save(rec, os.path.join(out_dir, f"trainer_scalars_w{group.world}_r{group.rank}.pt"))
     group.barrier()
     group.shutdown()
 

@@ -72,6 +72,15 @@ def test_train_results_and_files(trained):
         assert os.path.exists(os.path.join(fold, "train", "summaries.jsonl"))
         assert os.path.exists(os.path.join(fold, "eval", "summaries.jsonl"))
         assert os.path.isdir(os.path.join(fold, "export", "best_exporter"))
+        # the reference's four image summaries per mode (model.py:406-439): train every save_summary_steps, eval per run
+        for mode in ("train", "eval"):
+            with open(os.path.join(fold, mode, "summaries.jsonl")) as f:
+                recs = [json.loads(line) for line in f]
+            tags = {r_["image"] for r_ in recs if "image" in r_}
+            assert tags == {f"{mode}_image", f"{mode}_label", f"{mode}_prob", f"{mode}_prediction"}, (mode, tags)
+        with open(os.path.join(fold, "train", "summaries.jsonl")) as f:
+            steps = sorted({r_["step"] for r_ in map(json.loads, f) if r_.get("image") == "train_prob"})
+        assert steps == [2, 4, 6]
 
 
 def test_checkpoint_has_tf_variable_names_and_layout(trained):
@@ -223,3 +232,48 @@ def test_tf_tensor_bundle_roundtrip_and_checkpoint_interop(tmp_path):
     assert ckpt.load_checkpoint(pfx, m2) == 7
     for (n1, p1), (_, p2) in zip(m1.state_dict().items(), m2.state_dict().items()):
         assert torch.equal(p1, p2), n1
+
+
+def test_cli_eval_command_and_config_overrides(tmp_path, capsys):
+    """`eval` evaluates a checkpoint without training (model.py:207-223) and `--set section.field=value` reaches the
+    ModelConfig / OptimConfig / RunConfig dataclasses."""
+    from tensorflowdistributedlearning_b200.__main__ import main
+    from tensorflowdistributedlearning_b200.estimator.config import (ModelConfig, OptimConfig, RunConfig,
+                                                                     apply_overrides)
+
+    cfg = {"model": ModelConfig(), "optim": OptimConfig(), "run": RunConfig()}
+    apply_overrides(cfg, ["model.base_depth=16", "model.n_blocks=[1,1,1]", "optim.lr=3e-4", "optim.comm=nccl",
+                          "run.save_checkpoints_steps=2", "model.input_shape=(37,37)"])
+    assert cfg["model"].base_depth == 16 and cfg["model"].n_blocks == (1, 1, 1) and cfg["optim"].lr == 3e-4
+    assert cfg["optim"].comm == "nccl" and cfg["run"].save_checkpoints_steps == 2 and cfg["model"].input_shape == (37, 37)
+    with pytest.raises(ValueError):
+        apply_overrides(cfg, ["model.no_such_field=1"])
+    with pytest.raises(ValueError):
+        apply_overrides(cfg, ["nosection.lr=1"])
+
+    small = ["--set", "model.base_depth=16", "--set", "model.n_blocks=[1,1,1]", "--set", "model.input_shape=(37,37)",
+             "--set", "run.use_cuda_graph=False"]
+    d = str(tmp_path / "clirun")
+    assert main(["train", "--model", "refseg", "--data", "synthetic", "--model-dir", d, "--steps", "2", "--batch", "2",
+                 "--set", "run.save_checkpoints_steps=1", *small]) == 0
+    assert ckpt.list_checkpoints(d) == [0, 1, 2]
+    capsys.readouterr()
+    assert main(["eval", "--model", "refseg", "--data", "synthetic", "--model-dir", d, "--steps", "2", "--batch", "2",
+                 *small]) == 0
+    out = json.loads(capsys.readouterr().out.strip().splitlines()[-1])
+    assert out["global_step"] == 2 and "metrics/mean_iou" in out and "loss/lovasz_loss" in out
+    assert main(["eval", "--model", "refseg", "--data", "synthetic", "--model-dir", d, "--steps", "1", "--batch", "2",
+                 "--checkpoint", os.path.join(d, "model.ckpt-1"), *small]) == 0
+    out1 = json.loads(capsys.readouterr().out.strip().splitlines()[-1])
+    assert set(out1) == set(out)
+    assert ckpt.list_checkpoints(d) == [0, 1, 2]            # evaluation wrote no checkpoint, trained nothing
+
+
+def test_model_evaluate_without_training(trained):
+    m, model_dir, *_ = trained
+    before = {i: ckpt.list_checkpoints(os.path.join(model_dir, f"fold{i}")) for i in (0, 1)}
+    res = m.evaluate(batch_size=4)
+    assert set(res) == {0, 1}
+    for i in (0, 1):
+        assert res[i]["global_step"] == 6 and 0.0 <= res[i]["metrics/mean_iou"] <= 1.0
+        assert ckpt.list_checkpoints(os.path.join(model_dir, f"fold{i}")) == before[i]

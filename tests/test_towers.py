@@ -54,6 +54,18 @@ def test_moving_statistics_are_the_tower_mean(runs):
     assert not torch.equal(a["stats"], frozen)           # ... and actually updated by training-mode BN
 
 
+def test_logged_loss_is_tower_mean_and_metric_sums_are_global(tmp_path):
+    """X5 / X4 (model.py:491-500, core/metric.py:42): every tower logs the MEAN of the towers' losses, and the metric
+    sums that feed the streaming means are the tower mean of the per-tower sums (x world = the global sum)."""
+    a, b = _run(tmp_path, "trainer_scalars", 2)
+    for ra, rb in zip(a, b):
+        assert ra["local"] != rb["local"]                                   # different data per tower ...
+        assert ra["logged"] == rb["logged"]                                 # ... one logged value everywhere
+        assert abs(ra["logged"] - 0.5 * (ra["local"] + rb["local"])) < 1e-6
+        want = 0.5 * (ra["top1_local_sum"] + rb["top1_local_sum"])
+        assert abs(ra["top1_mean_of_sums"] - want) < 1e-6 and ra["top1_mean_of_sums"] == rb["top1_mean_of_sums"]
+
+
 def test_a_dead_tower_is_detected_not_waited_for(tmp_path):
     """Fault injection: tower 1 exits abruptly before step 1; tower 0 must fail with an error from the
     collective (peer closed / timeout) instead of hanging, and the launcher must report a non-zero exit."""
