@@ -20,11 +20,14 @@ __global__ void lr_schedule_kernel(long long* global_step, float base_lr, float 
   ptx::pdl_trigger();
   ptx::pdl_wait();
   const long long step = *global_step;  // value before this step's increment (tf.train.exponential_decay)
-  float lr = base_lr;
-  if (decay_steps > 0.f) lr = base_lr * powf(decay_rate, (float)step / decay_steps);
-  const float t = (float)(step + 1);
-  lr_state[0] = lr;
-  lr_state[1] = lr * sqrtf(1.f - powf(beta2, t)) / (1.f - powf(beta1, t));
+  // One thread, once per step: do it in double.  (The translation unit is built with --use_fast_math, under which
+  // powf / sqrtf / division turn into approximate intrinsics: 1 - __powf(0.999f, t) loses ~1e-4 relative at small t,
+  // and a float cast of the step stops counting at 2^24.  Double-precision pow is not affected by that flag.)
+  double lr = (double)base_lr;
+  if (decay_steps > 0.f) lr *= pow((double)decay_rate, (double)step / (double)decay_steps);
+  const double t = (double)(step + 1);
+  lr_state[0] = (float)lr;
+  lr_state[1] = (float)(lr * sqrt(1.0 - pow((double)beta2, t)) / (1.0 - pow((double)beta1, t)));
   *global_step = step + 1;
 }
 

@@ -15,8 +15,11 @@
 //
 // Signals are per-(CTA, source-rank) epoch counters written with st.release.sys and polled with
 // ld.acquire.sys; epochs only ever grow, so there is no reset and no ABA, and they live in device
-// memory so a captured CUDA graph replays correctly.  A spin that exceeds ~2 s traps with the
-// rank / CTA / peer it was waiting for (failure detection instead of a silent hang).
+// memory so a captured CUDA graph replays correctly.  A spin that exceeds the communicator's time
+// limit (wall-clock nanoseconds from %globaltimer, default = the host-side collective timeout
+// TDL_COLLECTIVE_TIMEOUT_S, so a slow input pipeline on one tower does not kill the job after a
+// couple of seconds) writes {rank, CTA, peer, epoch} into a host-mapped status word and traps, so
+// the Python side can say which tower went missing (failure detection instead of a silent hang).
 #include "tdl_common.cuh"
 
 namespace tdl {
@@ -35,6 +38,8 @@ struct Comm {
   int emulate;                 // 1: all "peers" live on this GPU and ranks are launched one after another
   float* mc_grad;              // NVLS multicast address of the gradient buckets (nullptr when not available)
   float* mc_param;             // NVLS multicast address of the parameter buckets
+  unsigned long long timeout_ns;  // how long a CTA waits for a peer before it reports and traps
+  int* status;                 // host-mapped: [0] = 1 when a wait timed out, [1..4] = rank, CTA, peer, epoch
 };
 
 enum OptKind { kNone = 0, kSgdMomentum = 1, kAdam = 2 };
@@ -61,6 +66,12 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
   return v;
 }
 
+__device__ __forceinline__ unsigned long long ptx_globaltimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
 // CTA-level barrier across ranks: CTA b of every rank meets CTA b of every other rank.
 __device__ __forceinline__ void cross_rank_barrier(const Comm& cm, uint32_t epoch) {
   __syncthreads();
@@ -68,9 +79,19 @@ __device__ __forceinline__ void cross_rank_barrier(const Comm& cm, uint32_t epoc
     const int peer = threadIdx.x;
     st_release_sys(cm.flags[peer] + (size_t)blockIdx.x * kMaxWorld + cm.rank, epoch);
     const uint32_t* mine = cm.flags[cm.rank] + (size_t)blockIdx.x * kMaxWorld + peer;
-    long long t0 = clock64();
+    unsigned long long t0 = 0;
+    uint32_t spins = 0;
     while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0) {
-      if (clock64() - t0 > 4000000000LL) {
+      if ((++spins & 1023u) != 0) continue;  // look at the wall clock every 1024 polls
+      const unsigned long long now = ptx_globaltimer();
+      if (t0 == 0) t0 = now;
+      if (now - t0 > cm.timeout_ns) {
+        if (cm.status) {
+          cm.status[1] = cm.rank; cm.status[2] = (int)blockIdx.x; cm.status[3] = peer; cm.status[4] = (int)epoch;
+          __threadfence_system();
+          cm.status[0] = 1;
+          __threadfence_system();
+        }
         printf("tdl_b200 p2p: rank %d CTA %d timed out waiting for rank %d (epoch %u)\n", cm.rank, (int)blockIdx.x,
                peer, epoch);
         __trap();
@@ -391,6 +412,12 @@ broadcast_kernel(const Comm cm, int src, int64_t offset, int64_t n) {
 using namespace tdl;
 using namespace tdl::p2p;
 
+#include <map>
+static std::map<Comm*, int*>& g_status_host() {  // host addresses of the communicators' status words
+  static std::map<Comm*, int*> m;
+  return m;
+}
+
 // ---- symmetric heap: plain cudaMalloc allocations that can be exported through cudaIpc ----
 TDL_API int tdl_symm_alloc(int64_t bytes, void** out) {
   TDL_REQUIRE(bytes > 0, "bytes must be positive");
@@ -438,7 +465,32 @@ TDL_API int tdl_p2p_comm_create(int world, int rank, void** grad_ptrs, void** pa
     c->flags[r] = flag_ptrs ? (uint32_t*)flag_ptrs[r] : nullptr;
   }
   c->epoch = (uint32_t*)epoch_local;
+  c->timeout_ns = 600ull * 1000000000ull;
+  // status word in pinned, device-mapped host memory: it survives the sticky error a trap leaves behind
+  int* host_status = nullptr;
+  if (cudaHostAlloc((void**)&host_status, 8 * sizeof(int), cudaHostAllocMapped) == cudaSuccess) {
+    memset(host_status, 0, 8 * sizeof(int));
+    int* dev_status = nullptr;
+    if (cudaHostGetDevicePointer((void**)&dev_status, host_status, 0) == cudaSuccess) c->status = dev_status;
+    g_status_host()[c] = host_status;
+  } else {
+    (void)cudaGetLastError();
+  }
   *out_comm = c;
+  return 0;
+}
+// How long a CTA waits for a peer's signal before it gives up (seconds; <= 0 keeps the current limit).
+TDL_API int tdl_p2p_comm_set_timeout(void* comm, double seconds) {
+  Comm* c = (Comm*)comm;
+  TDL_REQUIRE(c != nullptr, "null communicator");
+  if (seconds > 0) c->timeout_ns = (unsigned long long)(seconds * 1e9);
+  return 0;
+}
+// Reads the status word: out5 = {timed_out, rank, cta, peer, epoch}.  Plain host memory: safe to call after a CUDA
+// error has poisoned the context.
+TDL_API int tdl_p2p_comm_status(void* comm, int* out5) {
+  auto it = g_status_host().find((Comm*)comm);
+  for (int i = 0; i < 5; ++i) out5[i] = it == g_status_host().end() ? 0 : ((volatile int*)it->second)[i];
   return 0;
 }
 // Attach NVLS multicast addresses (from a CUDA multicast object bound to the same buffers) to a communicator.
@@ -450,6 +502,11 @@ TDL_API int tdl_p2p_comm_set_multicast(void* comm, void* mc_grad, void* mc_param
   return 0;
 }
 TDL_API int tdl_p2p_comm_destroy(void* comm) {
+  auto it = g_status_host().find((Comm*)comm);
+  if (it != g_status_host().end()) {
+    (void)cudaFreeHost(it->second);
+    g_status_host().erase(it);
+  }
   delete (Comm*)comm;
   return 0;
 }

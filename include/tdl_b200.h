@@ -205,6 +205,11 @@ int tdl_ipc_close(void* p);
 int tdl_p2p_flag_bytes(void);
 int tdl_p2p_comm_create(int world, int rank, void** grad_ptrs, void** param_ptrs, void** flag_ptrs, void* epoch_local,
                         int emulate, void** out_comm);
+/* failure detection: how long a kernel waits for a peer's signal (seconds) before it records {rank, CTA, peer, epoch}
+ * in a host-mapped status word and traps; tdl_p2p_comm_status reads the word back (out5 = timed_out, rank, cta, peer,
+ * epoch) and works after the trap has poisoned the CUDA context */
+int tdl_p2p_comm_set_timeout(void* comm, double seconds);
+int tdl_p2p_comm_status(void* comm, int* out5);
 int tdl_p2p_comm_set_multicast(void* comm, void* mc_grad, void* mc_param); /* NVLS multicast addresses, mode 3 */
 int tdl_p2p_comm_destroy(void* comm);
 int tdl_p2p_broadcast(void* comm, int src, int64_t offset, int64_t n, int max_blocks, void* stream); /* param mirror */

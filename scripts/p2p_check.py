@@ -1,7 +1,9 @@
 """Multi-GPU checks and the all-reduce+optimizer sweep (BASELINE config 5).  Run under torchrun, one rank per GPU:
 
     python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 --master-port 29511 \
-        scripts/p2p_check.py [correctness] [stress] [sweep] [train]
+        scripts/p2p_check.py [correctness] [stress] [sweep] [train] [resume] [nvls] [dead_nccl]
+
+`tests/test_gpu_multi.py` runs correctness / stress / train / resume / dead_nccl under pytest on boxes with >= 2 GPUs.
 
 Every timing is CUDA-event device time, max over ranks.  Rank 0 appends JSON lines to gpurun_out/p2p_check.jsonl.
 """
@@ -285,10 +287,150 @@ def train():
         emit(test="train_vs_nccl", variant=list(k), rel_err=rel_err(v, base), ok=rel_err(v, base) < 5e-2)
 
 
+def resume():
+    """Checkpoint / resume with the optimizer state sharded over the towers (two-shot buckets update m1 / m2 on the
+    owned slice only): train, checkpoint at step 3, resume in a fresh process-state, and compare with the uninterrupted
+    run.  Part 1 drives the optimizer with seeded gradients (every kernel on that path is deterministic), so the
+    comparison is bit-exact; part 2 is the full trainer, whose weight-gradient kernels accumulate with fp32 atomics and
+    are only reproducible to rounding."""
+    import shutil
+    import tempfile
+
+    from tensorflowdistributedlearning_b200 import models
+    from tensorflowdistributedlearning_b200.estimator import checkpoint as ckpt
+    from tensorflowdistributedlearning_b200.parallel.optimizer import DistributedOptimizer
+    from tensorflowdistributedlearning_b200.parallel.trainer import TowerTrainer, classification_loss
+
+    box = [tempfile.mkdtemp(prefix="tdl_resume_") if R == 0 else None]
+    dist.broadcast_object_list(box, 0)
+    tmp = box[0]
+
+    def seeded_grad(opt, step):
+        g = torch.Generator(device="cuda").manual_seed(1000 * step + R)
+        opt.flat.grad_flat.copy_(torch.randn(opt.flat.total, device="cuda", generator=g) * 0.01)
+
+    for kind in ("sgdm", "adam"):
+        def make(seed):
+            torch.manual_seed(seed)
+            model = models.resnet50(num_classes=32).cuda()
+            return model, DistributedOptimizer(model, group, kind=kind, lr=0.05 if kind == "sgdm" else 1e-3,
+                                               momentum=0.9, decay_steps=100.0, decay_rate=0.5, comm="p2p",
+                                               overlap=False, bucket_cap_mb=8.0)
+
+        model, opt = make(3)
+        big = sum(1 for b in opt.flat.buckets if b.numel * 4 > opt.TWO_SHOT_MIN_BYTES)
+        for step in range(6):
+            seeded_grad(opt, step)
+            opt.begin_step()
+            opt.step()
+        torch.cuda.synchronize()
+        want = opt.flat.param_flat.clone()
+        opt.close()
+        dist.barrier()
+
+        model, opt = make(3)
+        for step in range(3):
+            seeded_grad(opt, step)
+            opt.begin_step()
+            opt.step()
+        torch.cuda.synchronize()
+        opt.consolidate_state()                       # every tower; then tower 0 writes (X7)
+        d = os.path.join(tmp, f"opt_{kind}")
+        if R == 0:
+            ckpt.save_checkpoint(d, model, opt, step=3)
+        dist.barrier()
+        opt.close()
+        model, opt = make(99)                         # different initial weights: everything must come from the file
+        got_step = ckpt.load_checkpoint(ckpt.latest_checkpoint(d), model, opt)
+        for step in range(3, 6):
+            seeded_grad(opt, step)
+            opt.begin_step()
+            opt.step()
+        torch.cuda.synchronize()
+        got = opt.flat.param_flat
+        same = torch.tensor([float(torch.equal(got, want))], device="cuda")
+        dist.all_reduce(same, op=dist.ReduceOp.MIN)
+        emit(test="resume_optimizer", kind=kind, two_shot_buckets=big, restored_step=got_step,
+             bit_equal=bool(same.item()), max_abs_diff=float((got - want).abs().max()),
+             ok=bool(same.item()) and big > 0 and got_step == 3)
+        opt.close()
+        dist.barrier()
+
+    # part 2: the whole trainer (graph replay, overlap, wgrad atomics)
+    def batch(tr, step):
+        gen = torch.Generator().manual_seed(7000 + 10 * step + R)
+        tr.images.copy_(torch.randint(0, 256, tr.images.shape, dtype=torch.uint8, generator=gen))
+        tr.labels.copy_(torch.randint(0, 32, tr.labels.shape, generator=gen))
+
+    def make_tr(seed):
+        torch.manual_seed(seed)
+        return TowerTrainer(models.resnet50(num_classes=32), group, batch=16, input_hwc=(64, 64, 3),
+                            loss_fn=classification_loss, use_graph=False, kind="adam", lr=1e-3, comm="p2p",
+                            overlap=True, bucket_cap_mb=8.0)
+
+    tr = make_tr(3)
+    for step in range(6):
+        batch(tr, step)
+        tr.run_step()
+    torch.cuda.synchronize()
+    want = tr.opt.flat.param_flat.clone()
+    tr.close()
+    dist.barrier()
+    tr = make_tr(3)
+    for step in range(3):
+        batch(tr, step)
+        tr.run_step()
+    torch.cuda.synchronize()
+    tr.opt.consolidate_state()
+    d = os.path.join(tmp, "trainer")
+    if R == 0:
+        ckpt.save_checkpoint(d, tr.model, tr.opt, step=3)
+    dist.barrier()
+    m2_owned = [float(tr.opt.m2[lo:hi].abs().sum()) for lo, hi in tr.opt.owned_ranges()]
+    tr.close()
+    tr = make_tr(99)
+    ckpt.load_checkpoint(ckpt.latest_checkpoint(d), tr.model, tr.opt)
+    # the restored Adam slots are complete on every tower, not just this tower's slice
+    total = float(tr.opt.m2.abs().sum())
+    for step in range(3, 6):
+        batch(tr, step)
+        tr.run_step()
+    torch.cuda.synchronize()
+    err = rel_err(tr.opt.flat.param_flat, want)
+    worst = torch.tensor([err], device="cuda")
+    dist.all_reduce(worst, op=dist.ReduceOp.MAX)
+    emit(test="resume_trainer", rel_err=float(worst.item()), m2_total=total, m2_owned_share=sum(m2_owned) / max(total, 1e-30),
+         ok=float(worst.item()) < 2e-3 and sum(m2_owned) < 0.9 * total)
+    tr.close()
+    dist.barrier()
+    if R == 0:
+        shutil.rmtree(tmp, ignore_errors=True)
+
+
+def dead_nccl():
+    """Fault injection on the NCCL baseline path (host-side collective timeout): tower 1 exits before
+    step 1; the surviving towers must come back with an error instead of waiting forever.  No device-side trap is
+    provoked: the gradient path here is `comm="nccl"`."""
+    from tensorflowdistributedlearning_b200 import models
+    from tensorflowdistributedlearning_b200.parallel.trainer import TowerTrainer, classification_loss
+
+    torch.manual_seed(3)
+    tr = TowerTrainer(models.SmallResNet(num_classes=10), group, batch=8, input_hwc=(32, 32, 3),
+                      loss_fn=classification_loss, use_graph=False, kind="sgdm", lr=0.05, comm="nccl")
+    for step in range(3):
+        if R == 1 and step == 1:
+            os._exit(17)
+        tr.run_step()
+        torch.cuda.synchronize()
+        print(f"rank {R} finished step {step}", flush=True)
+    emit(test="dead_nccl", ok=False, note="every step completed although tower 1 died")
+
+
 if __name__ == "__main__":
     which = sys.argv[1:] or ["correctness", "stress", "train", "sweep"]
     t0 = time.time()
     for w in which:
-        {"correctness": correctness, "stress": stress, "sweep": sweep, "train": train, "nvls": nvls}[w]()
+        {"correctness": correctness, "stress": stress, "sweep": sweep, "train": train, "nvls": nvls, "resume": resume,
+         "dead_nccl": dead_nccl}[w]()
         emit(test=w, event="done", secs=round(time.time() - t0, 1))
     group.shutdown()

@@ -78,8 +78,10 @@ def save_checkpoint(model_dir: str, model: torch.nn.Module, optimizer=None, step
                 tensors[f"{name}/{slot2}"] = to_tf_layout(_unpad(sd["m2"][o:o + p.numel()].view(p.shape), shape),
                                                           kind).float().cpu().contiguous()
         if sd["kind"] == "adam":
-            tensors["beta1_power"] = torch.tensor(optimizer.beta1 ** step, dtype=torch.float32)
-            tensors["beta2_power"] = torch.tensor(optimizer.beta2 ** step, dtype=torch.float32)
+            # TF initialises beta*_power to beta and multiplies once per apply: after `step` updates it holds
+            # beta ** (step + 1) (so the step-0 checkpoint stores beta, never 1.0 -- 1 - beta1_power must be > 0)
+            tensors["beta1_power"] = torch.tensor(optimizer.beta1 ** (step + 1), dtype=torch.float32)
+            tensors["beta2_power"] = torch.tensor(optimizer.beta2 ** (step + 1), dtype=torch.float32)
     step = int(step or 0)
     tensors["global_step"] = torch.tensor(step, dtype=torch.int64)
     prefix = _ckpt_prefix(model_dir, step)

@@ -156,6 +156,12 @@ class Estimator:
         with open(latest + ".json") as f:
             return int(json.load(f)["global_step"])
 
+    def prepare_save(self) -> None:
+        """Collective part of a checkpoint: all towers call it before tower 0 writes (optimizer slots are sharded over
+        the towers on the P2P two-shot path)."""
+        if self.trainer is not None:
+            self.trainer.opt.consolidate_state()
+
     def save_checkpoint(self, step: int, keep: int = 5) -> str:
         return ckpt.save_checkpoint(self.model_dir, self.model, self.trainer.opt if self.trainer else None, step, keep,
                                     extra={"params": {k: str(v) for k, v in self.params.items()}})

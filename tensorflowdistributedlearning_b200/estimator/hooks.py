@@ -37,6 +37,7 @@ class CheckpointSaverHook(Hook):
         if self._last == step:
             return
         self._last = step
+        estimator.prepare_save()  # every tower: gathers the sharded optimizer slots so tower 0's copy is complete
         if estimator.group.is_primary:
             path = estimator.save_checkpoint(step, keep=self.keep)
         else:

@@ -321,7 +321,9 @@ class _ConvNative(torch.autograd.Function):
                 if partials is None:
                     dx = O.conv2d_fprop(dy, wsaved, stride=1, residual=res, out_mask=mask, **geo)
                 if mask is not None:  # this IS the total gradient of x (tap), with x's ReLU backward already applied
-                    _PREMASKED[dx.data_ptr()] = mask.data_ptr()
+                    # (version-guarded: autograd summing another consumer's gradient into dx in place keeps the
+                    # address but bumps the version, and the sum is NOT masked as a whole any more)
+                    _PREMASKED[dx.data_ptr()] = (dx._version, mask.data_ptr())
                 d_tap = None
                 _count(1)
             else:
@@ -635,7 +637,9 @@ class _BNNative(torch.autograd.Function):
         dz2 = dz.contiguous().view(-1, C)
         g, b = ctx.gamma_param, ctx.beta_param
         direct = _direct_ok(g) and _direct_ok(b)
-        premasked = (z2 is not None and has_res and _PREMASKED.pop(dz2.data_ptr(), None) == z2.data_ptr())
+        pm = _PREMASKED.pop(dz2.data_ptr(), None)
+        premasked = (z2 is not None and has_res and pm is not None and pm[0] == dz2._version
+                     and pm[1] == z2.data_ptr())  # otherwise mask here: masking twice is harmless (idempotent)
         partials = None
         ent = _BN_PARTIALS.pop(dz2.data_ptr(), None)
         if ent is not None and ent[0] == dz2._version and ent[1] == x2.data_ptr() and ent[3] == premasked:

@@ -223,8 +223,60 @@ class DistributedOptimizer:
                 f.grad_flat.zero_()
 
     # ---- checkpoint state ----
+    TWO_SHOT_MIN_BYTES = 1 << 19  # buckets above this take the reduce-scatter path (csrc/p2p_allreduce.cu, mode 0)
+
+    def owned_ranges(self):
+        """Element ranges of the flat buffers whose optimizer slots THIS tower keeps up to date.
+
+        One-shot buckets (and every non-P2P path) update the full state on every tower.  Two-shot / NVLS buckets run
+        the optimizer on the owned slice only -- rank r's share of the bucket's 4-element vectors, the same split
+        ``two_shot_kernel`` computes -- so the other (W-1)/W of ``m1`` / ``m2`` on a tower is stale."""
+        if self.comm != "p2p" or not self.group.distributed:
+            return [(0, self.flat.total)]
+        w, r = self.group.world, self.group.rank
+        out = []
+        for b in self.flat.buckets:
+            if b.numel * 4 <= self.TWO_SHOT_MIN_BYTES:
+                out.append((b.offset, b.offset + b.numel))
+                continue
+            n4 = b.numel // 4
+            per = (n4 + w - 1) // w
+            lo, hi = min(per * r, n4), min(per * r + per, n4)
+            if hi > lo:
+                out.append((b.offset + lo * 4, b.offset + hi * 4))
+            if r == w - 1 and b.numel % 4:
+                out.append((b.offset + n4 * 4, b.offset + b.numel))
+        return out
+
+    def consolidate_state(self) -> None:
+        """Make ``m1`` / ``m2`` complete on every tower (collective: every tower calls it).  Needed before tower 0
+        writes a checkpoint (X7: the reference's Saver reads the primary copy, which there holds the full Adam slots,
+        model.py:117-121): with the sharded two-shot update each tower only owns a slice of every large bucket."""
+        if self.comm != "p2p" or not self.group.distributed:
+            return
+        one_shot = {(b.offset, b.offset + b.numel) for b in self.flat.buckets
+                    if b.numel * 4 <= self.TWO_SHOT_MIN_BYTES}
+        for slot in (self.m1, self.m2):
+            if slot is None:
+                continue
+            full = torch.zeros_like(slot)
+            for lo, hi in self.owned_ranges():
+                if (lo, hi) in one_shot and self.group.rank != 0:
+                    continue  # replicated state: tower 0's copy stands for all
+                full[lo:hi] = slot[lo:hi]
+            self.group.all_reduce_sum_(full)  # disjoint supports: the sum is the concatenation of the owned slices
+            slot.copy_(full)
+
     def state_dict(self):
         return {"global_step": int(self.global_step.item()), "m1": self.m1, "m2": self.m2, "kind": self.kind}
+
+    def peer_timeout(self):
+        """Who a P2P kernel gave up waiting for (None if nobody): see ``P2PComm.timed_out``."""
+        for c in (self._p2p, self._p2p_stats):
+            who = c.timed_out() if c is not None else None
+            if who is not None:
+                return who
+        return None
 
     def current_lr(self) -> float:
         return float(self.lr_state[0].item())

