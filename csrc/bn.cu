@@ -623,6 +623,551 @@ TDL_API int tdl_bn_bwd_apply(const void* dz, const void* x, const void* z, int z
 }
 
 // ------------------------------------------------------------------------------------------------------------
+// Finalize folded into the apply kernels (thread-block clusters + distributed shared memory).
+//
+// A BatchNorm layer used to cost a statistics pass (or the producing convolution's epilogue), a tiny "finalize" launch
+// that folds the per-CTA partial rows into per-channel constants, and the apply pass -- and the same again in
+// backward.  The ~106 finalize launches of a ResNet-50 step are pure latency (about half a millisecond per step).
+// Here the apply kernels do the fold themselves: the grid is launched as clusters of up to 8 CTAs along the row
+// dimension, the first CTA of every cluster reduces the partial rows of its channel group in fp64 (fixed order, so
+// the result is the same in every cluster and from run to run), leaves the per-channel constants in its shared
+// memory, and the other CTAs of the cluster read them through DSMEM after one cluster barrier.  The redundancy is
+// grid/8 instead of grid, which keeps the extra L2 reads far below the tensor traffic.  The first cluster also writes
+// the per-channel outputs (mean / invstd / scale / shift, moving averages; dgamma / dbeta) exactly once.
+// ------------------------------------------------------------------------------------------------------------
+namespace tdl {
+namespace bn {
+
+constexpr int kMaxCluster = 8;
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// 4 consecutive floats from the shared memory of CTA `rank` of this cluster (the address is this CTA's own address of
+// the same variable)
+__device__ __forceinline__ float4 ld_dsmem_f32x4(const float* local_ptr, uint32_t rank) {
+  uint32_t ra;
+  float4 v;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(ptx::smem_u32(local_ptr)), "r"(rank));
+  asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "r"(ra)
+               : "memory");
+  return v;
+}
+
+// fp64 column sums of partial[nparts][2][C] over all rows for channels [c_lo, c_lo + nch); nch divides kThreads.
+// Result valid in threads < nch (thread c owns channel c_lo + c).
+__device__ __forceinline__ void fold_partial_rows(const float* __restrict__ partial, int nparts, int C, int c_lo,
+                                                  int nch, double* red, double* s_out, double* q_out) {
+  const int tid = threadIdx.x;
+  const int slices = kThreads / nch;
+  const int c = tid % nch, sl = tid / nch;
+  const int ch = c_lo + c;
+  double s = 0.0, q = 0.0;
+  if (ch < C) {
+    int p = sl;
+    for (; p + 3 * slices < nparts; p += 4 * slices) {  // four independent row pairs in flight
+      float a[4], b[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        a[u] = partial[((size_t)(p + u * slices) * 2) * C + ch];
+        b[u] = partial[((size_t)(p + u * slices) * 2 + 1) * C + ch];
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) { s += (double)a[u]; q += (double)b[u]; }
+    }
+    for (; p < nparts; p += slices) {
+      s += (double)partial[((size_t)p * 2) * C + ch];
+      q += (double)partial[((size_t)p * 2 + 1) * C + ch];
+    }
+  }
+  red[tid] = s;
+  red[kThreads + tid] = q;
+  __syncthreads();
+  if (sl == 0) {
+    for (int t = 1; t < slices; ++t) {
+      s += red[t * nch + c];
+      q += red[kThreads + t * nch + c];
+    }
+  }
+  *s_out = s;
+  *q_out = q;
+}
+
+// ---- forward: finalize + y = relu?(x*scale + shift (+ residual)) ----
+template <bool kRes, bool kRelu, bool kMask>
+__global__ void __launch_bounds__(kThreads)
+bn_apply_fin_kernel(const bf16* __restrict__ x, const float* __restrict__ partial, int nparts, double inv_n,
+                    double unbias, const float* __restrict__ gamma, const float* __restrict__ beta,
+                    float* __restrict__ running_mean, float* __restrict__ running_var, float decay, float eps,
+                    float* __restrict__ mean_out, float* __restrict__ invstd_out, float* __restrict__ scale_out,
+                    float* __restrict__ shift_out, const bf16* __restrict__ residual, bf16* __restrict__ y,
+                    uint8_t* __restrict__ mask_out, int64_t rows, int C, int tx, int ty) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
+  __shared__ double red[2 * kThreads];
+  __shared__ __align__(16) float s_sc[kThreads], s_sh[kThreads];
+  const int nch = tx * 8;
+  const int c_lo = blockIdx.y * nch;
+  if (cluster_ctarank() == 0) {
+    double s, q;
+    fold_partial_rows(partial, nparts, C, c_lo, nch, red, &s, &q);
+    if (threadIdx.x < nch) {
+      const int ch = c_lo + threadIdx.x;
+      float scale = 0.f, shift = 0.f;
+      if (ch < C) {
+        const double m = s * inv_n;
+        double var = q * inv_n - m * m;
+        if (var < 0.0) var = 0.0;
+        const float invstd = (float)(1.0 / sqrt(var + (double)eps));
+        const float g = gamma ? gamma[ch] : 1.f;
+        const float b = beta ? beta[ch] : 0.f;
+        scale = g * invstd;
+        shift = b - (float)m * scale;
+        if (blockIdx.x == 0) {  // the per-channel outputs are written once, by the first cluster
+          mean_out[ch] = (float)m;
+          invstd_out[ch] = invstd;
+          scale_out[ch] = scale;
+          shift_out[ch] = shift;
+          if (running_mean) running_mean[ch] = decay * running_mean[ch] + (1.f - decay) * (float)m;
+          if (running_var) running_var[ch] = decay * running_var[ch] + (1.f - decay) * (float)(var * unbias);
+        }
+      }
+      s_sc[threadIdx.x] = scale;
+      s_sh[threadIdx.x] = shift;
+    }
+  }
+  cluster_sync_all();
+  const int cx = threadIdx.x % tx;
+  const int ry = threadIdx.x / tx;
+  const int cv = blockIdx.y * tx + cx;
+  float sc[8], sh[8];
+  {
+    const float4 a0 = ld_dsmem_f32x4(s_sc + cx * 8, 0), a1 = ld_dsmem_f32x4(s_sc + cx * 8 + 4, 0);
+    const float4 b0 = ld_dsmem_f32x4(s_sh + cx * 8, 0), b1 = ld_dsmem_f32x4(s_sh + cx * 8 + 4, 0);
+    sc[0] = a0.x; sc[1] = a0.y; sc[2] = a0.z; sc[3] = a0.w; sc[4] = a1.x; sc[5] = a1.y; sc[6] = a1.z; sc[7] = a1.w;
+    sh[0] = b0.x; sh[1] = b0.y; sh[2] = b0.z; sh[3] = b0.w; sh[4] = b1.x; sh[5] = b1.y; sh[6] = b1.z; sh[7] = b1.w;
+  }
+  cluster_sync_all();  // the first CTA's shared memory must outlive every read of it
+  if (cv >= C / 8) return;
+  const int64_t step = (int64_t)gridDim.x * ty;
+  const int64_t col = (int64_t)cv * 8;
+  const int c8 = C >> 3;
+  auto one = [&](int64_t r, const bf16x8& xv, const bf16x8& rv) {
+    float f[8];
+    unpack8(xv, f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) f[j] = bn_affine(f[j], sc[j], sh[j]);
+    if constexpr (kRes) {
+      float rr[8];
+      unpack8(rv, rr);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] += rr[j];
+    }
+    if constexpr (kRelu) {
+      if constexpr (kMask) {
+        uint32_t m = 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) m |= (f[j] > 0.f ? 1u : 0u) << j;
+        mask_out[r * c8 + cv] = (uint8_t)m;
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
+    }
+    st8(y + r * C + col, pack8(f));
+  };
+  constexpr int U = kRes ? 2 : 4;  // rows in flight per thread (16-byte loads: U, or 2U with a residual)
+  int64_t r = (int64_t)blockIdx.x * ty + ry;
+  for (; r + (U - 1) * step < rows; r += U * step) {
+    bf16x8 xv[U], rv[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      xv[u] = ld8(x + (r + u * step) * C + col);
+      if constexpr (kRes) rv[u] = ld8(residual + (r + u * step) * C + col);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) one(r + u * step, xv[u], rv[u]);
+  }
+  for (; r < rows; r += step) {
+    bf16x8 xv = ld8(x + r * C + col), rv;
+    if constexpr (kRes) rv = ld8(residual + r * C + col);
+    one(r, xv, rv);
+  }
+}
+
+// ReLU mask source of the backward kernels
+enum MaskMode { kNoRelu = 0, kRecompute = 1, kBits = 2, kFromZ = 3 };
+
+template <int MODE>
+__device__ __forceinline__ void apply_mask(float* g, const float* f, const float* sc, const float* sh, int mb,
+                                           const bf16x8& zv) {
+  if constexpr (MODE == kBits) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) g[j] = ((mb >> j) & 1) ? g[j] : 0.f;
+  } else if constexpr (MODE == kFromZ) {
+    float zz[8];
+    unpack8(zv, zz);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) g[j] = zz[j] > 0.f ? g[j] : 0.f;
+  } else if constexpr (MODE == kRecompute) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) g[j] = bn_affine(f[j], sc[j], sh[j]) > 0.f ? g[j] : 0.f;
+  }
+}
+
+// ---- backward reduce, specialised per mask source, four rows in flight ----
+template <int MODE>
+__global__ void __launch_bounds__(kThreads)
+bn_bwd_partial_t_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ x, const void* __restrict__ zraw,
+                        const float* __restrict__ scale, const float* __restrict__ shift,
+                        const float* __restrict__ mean, const float* __restrict__ invstd, int64_t rows, int C, int tx,
+                        int ty, float* __restrict__ partial) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
+  extern __shared__ float sm[];
+  const int cx = threadIdx.x % tx;
+  const int ry = threadIdx.x / tx;
+  const int c8 = C / 8;
+  const int cv = blockIdx.y * tx + cx;
+  float s[8], q[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) s[j] = q[j] = 0.f;
+  if (cv < c8) {
+    float sc[8], sh[8], mu[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      mu[j] = mean[cv * 8 + j];
+      if constexpr (MODE == kRecompute) {
+        sc[j] = scale[cv * 8 + j];
+        sh[j] = shift[cv * 8 + j];
+      }
+    }
+    const int64_t step = (int64_t)gridDim.x * ty;
+    const int64_t col = (int64_t)cv * 8;
+    const uint8_t* zb = reinterpret_cast<const uint8_t*>(zraw);
+    const bf16* zt = reinterpret_cast<const bf16*>(zraw);
+    auto one = [&](const bf16x8& gv, const bf16x8& xv, int mb, const bf16x8& zv) {
+      float g[8], f[8];
+      unpack8(gv, g);
+      unpack8(xv, f);
+      apply_mask<MODE>(g, f, sc, sh, mb, zv);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        s[j] += g[j];
+        q[j] = fmaf(g[j], f[j] - mu[j], q[j]);
+      }
+    };
+    constexpr int U = MODE == kFromZ ? 2 : 4;
+    int64_t r = (int64_t)blockIdx.x * ty + ry;
+    for (; r + (U - 1) * step < rows; r += U * step) {
+      bf16x8 gv[U], xv[U], zv[U];
+      int mb[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        gv[u] = ld8(dz + (r + u * step) * C + col);
+        xv[u] = ld8(x + (r + u * step) * C + col);
+        if constexpr (MODE == kBits) mb[u] = zb[(r + u * step) * c8 + cv];
+        if constexpr (MODE == kFromZ) zv[u] = ld8(zt + (r + u * step) * C + col);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) one(gv[u], xv[u], mb[u], zv[u]);
+    }
+    for (; r < rows; r += step) {
+      bf16x8 gv = ld8(dz + r * C + col), xv = ld8(x + r * C + col), zv;
+      int mb = 0;
+      if constexpr (MODE == kBits) mb = zb[r * c8 + cv];
+      if constexpr (MODE == kFromZ) zv = ld8(zt + r * C + col);
+      one(gv, xv, mb, zv);
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) q[j] *= invstd[cv * 8 + j];
+  }
+  float* mine = sm + (size_t)(ry * tx + cx) * 16;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    mine[j] = s[j];
+    mine[8 + j] = q[j];
+  }
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < tx * 16; idx += kThreads) {
+    const int col = idx >> 4;
+    const int val = idx & 15;
+    const int cvv = blockIdx.y * tx + col;
+    if (cvv >= c8) continue;
+    float acc = 0.f;
+    for (int t = 0; t < ty; ++t) acc += sm[(size_t)(t * tx + col) * 16 + val];
+    const int which = val >> 3;
+    const int ch = cvv * 8 + (val & 7);
+    partial[((size_t)blockIdx.x * 2 + which) * C + ch] = acc;
+  }
+}
+
+// ---- backward: finalize (dbeta, dgamma) + dx = A*dy + B*x + D; dres = dy ----
+template <int MODE, bool kDres>
+__global__ void __launch_bounds__(kThreads)
+bn_bwd_apply_fin_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ x, const void* __restrict__ zraw,
+                        const float* __restrict__ scale, const float* __restrict__ shift,
+                        const float* __restrict__ mean, const float* __restrict__ invstd,
+                        const float* __restrict__ partial, int nparts, float inv_n, float* __restrict__ dgamma_out,
+                        float* __restrict__ dbeta_out, float* __restrict__ acc_dgamma, float* __restrict__ acc_dbeta,
+                        bf16* __restrict__ dx, bf16* __restrict__ dres, int64_t rows, int C, int tx, int ty) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
+  __shared__ double red[2 * kThreads];
+  __shared__ __align__(16) float s_A[kThreads], s_B[kThreads], s_D[kThreads], s_S[kThreads];
+  const int nch = tx * 8;
+  const int c_lo = blockIdx.y * nch;
+  if (cluster_ctarank() == 0) {
+    double s, q;
+    fold_partial_rows(partial, nparts, C, c_lo, nch, red, &s, &q);
+    if (threadIdx.x < nch) {
+      const int ch = c_lo + threadIdx.x;
+      float A = 0.f, B = 0.f, D = 0.f, S = 0.f;
+      if (ch < C) {
+        const float dbeta = (float)s, dgamma = (float)q;
+        A = scale[ch];  // == gamma * invstd
+        S = shift[ch];
+        const float k = A * invstd[ch] * dgamma * inv_n;
+        B = -k;
+        D = k * mean[ch] - A * dbeta * inv_n;
+        if (blockIdx.x == 0) {
+          dbeta_out[ch] = dbeta;
+          dgamma_out[ch] = dgamma;
+          if (acc_dbeta) acc_dbeta[ch] += dbeta;
+          if (acc_dgamma) acc_dgamma[ch] += dgamma;
+        }
+      }
+      s_A[threadIdx.x] = A;
+      s_B[threadIdx.x] = B;
+      s_D[threadIdx.x] = D;
+      s_S[threadIdx.x] = S;
+    }
+  }
+  cluster_sync_all();
+  const int cx = threadIdx.x % tx;
+  const int ry = threadIdx.x / tx;
+  const int cv = blockIdx.y * tx + cx;
+  float sc[8], sh[8], B[8], D[8];
+  {
+    const float4 a0 = ld_dsmem_f32x4(s_A + cx * 8, 0), a1 = ld_dsmem_f32x4(s_A + cx * 8 + 4, 0);
+    const float4 b0 = ld_dsmem_f32x4(s_B + cx * 8, 0), b1 = ld_dsmem_f32x4(s_B + cx * 8 + 4, 0);
+    const float4 d0 = ld_dsmem_f32x4(s_D + cx * 8, 0), d1 = ld_dsmem_f32x4(s_D + cx * 8 + 4, 0);
+    sc[0] = a0.x; sc[1] = a0.y; sc[2] = a0.z; sc[3] = a0.w; sc[4] = a1.x; sc[5] = a1.y; sc[6] = a1.z; sc[7] = a1.w;
+    B[0] = b0.x; B[1] = b0.y; B[2] = b0.z; B[3] = b0.w; B[4] = b1.x; B[5] = b1.y; B[6] = b1.z; B[7] = b1.w;
+    D[0] = d0.x; D[1] = d0.y; D[2] = d0.z; D[3] = d0.w; D[4] = d1.x; D[5] = d1.y; D[6] = d1.z; D[7] = d1.w;
+    if constexpr (MODE == kRecompute) {
+      const float4 s0 = ld_dsmem_f32x4(s_S + cx * 8, 0), s1 = ld_dsmem_f32x4(s_S + cx * 8 + 4, 0);
+      sh[0] = s0.x; sh[1] = s0.y; sh[2] = s0.z; sh[3] = s0.w; sh[4] = s1.x; sh[5] = s1.y; sh[6] = s1.z; sh[7] = s1.w;
+    }
+  }
+  cluster_sync_all();
+  if (cv >= C / 8) return;
+  const int64_t step = (int64_t)gridDim.x * ty;
+  const int64_t col = (int64_t)cv * 8;
+  const int c8 = C >> 3;
+  const uint8_t* zb = reinterpret_cast<const uint8_t*>(zraw);
+  const bf16* zt = reinterpret_cast<const bf16*>(zraw);
+  auto one = [&](int64_t r, const bf16x8& gv, const bf16x8& xv, int mb, const bf16x8& zv) {
+    float g[8], f[8], o[8];
+    unpack8(gv, g);
+    unpack8(xv, f);
+    apply_mask<MODE>(g, f, sc, sh, mb, zv);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = fmaf(sc[j], g[j], fmaf(B[j], f[j], D[j]));
+    st8(dx + r * C + col, pack8(o));
+    if constexpr (kDres) st8(dres + r * C + col, pack8(g));
+  };
+  constexpr int U = MODE == kFromZ ? 2 : 3;
+  int64_t r = (int64_t)blockIdx.x * ty + ry;
+  for (; r + (U - 1) * step < rows; r += U * step) {
+    bf16x8 gv[U], xv[U], zv[U];
+    int mb[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      gv[u] = ld8(dz + (r + u * step) * C + col);
+      xv[u] = ld8(x + (r + u * step) * C + col);
+      if constexpr (MODE == kBits) mb[u] = zb[(r + u * step) * c8 + cv];
+      if constexpr (MODE == kFromZ) zv[u] = ld8(zt + (r + u * step) * C + col);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) one(r + u * step, gv[u], xv[u], mb[u], zv[u]);
+  }
+  for (; r < rows; r += step) {
+    bf16x8 gv = ld8(dz + r * C + col), xv = ld8(x + r * C + col), zv;
+    int mb = 0;
+    if constexpr (MODE == kBits) mb = zb[r * c8 + cv];
+    if constexpr (MODE == kFromZ) zv = ld8(zt + r * C + col);
+    one(r, gv, xv, mb, zv);
+  }
+}
+
+// Launch as clusters of `cl` CTAs along x (cl divides grid.x), with the programmatic-launch attribute when enabled.
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_clustered(void (*kernel)(KArgs...), dim3 grid, int cl, size_t smem, cudaStream_t st,
+                                    Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = (unsigned)cl;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = tdl::pdl_enabled() ? 2 : 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
+// grid of the fused apply kernels: the plain apply shape with gx rounded down to whole clusters
+static ReduceShape fused_shape(int64_t rows, int C, int* cluster) {
+  ReduceShape s = apply_shape(rows, C);
+  static int max_cl = 0;  // TDL_BN_CLUSTER: cluster size of the fused apply kernels (1, 2, 4 or 8; default 8)
+  if (max_cl == 0) {
+    const char* e = getenv("TDL_BN_CLUSTER");
+    max_cl = e ? atoi(e) : kMaxCluster;
+    if (max_cl < 1 || max_cl > kMaxCluster || (max_cl & (max_cl - 1))) max_cl = kMaxCluster;
+  }
+  int cl = max_cl;
+  while (cl > s.gx) cl >>= 1;
+  if (cl < 1) cl = 1;
+  s.gx = s.gx / cl * cl;
+  *cluster = cl;
+  return s;
+}
+
+static int mask_mode(int relu, const void* z, int z_is_bitmask) {
+  if (!relu) return kNoRelu;
+  if (!z) return kRecompute;
+  return z_is_bitmask ? kBits : kFromZ;
+}
+
+static int g_bwd_partial_t_ctas[4] = {0, 0, 0, 0};
+
+}  // namespace bn
+}  // namespace tdl
+
+// y = relu?(BN(x) (+ residual)) straight from the partial (sum, sum of squares) rows: statistics finalize, moving
+// averages and the normalise pass in ONE launch.  partial: [nparts][2][C] fp32 covering `stat_rows` pixels (from
+// tdl_conv2d_fprop_stats_bf16 / tdl_bn_partial_stats).  mean / invstd / scale / shift ([C] each) are outputs (the
+// backward pass needs them).  mask_out as in tdl_bn_apply.
+TDL_API int tdl_bn_apply_fused(const void* x, const float* partial, int nparts, int64_t stat_rows, const float* gamma,
+                               const float* beta, float* running_mean, float* running_var, float decay, float eps,
+                               float* mean, float* invstd, float* scale, float* shift, const void* residual, void* y,
+                               void* mask_out, int64_t rows, int C, int relu, void* stream) {
+  TDL_REQUIRE(C > 0 && C % 8 == 0, "C must be a positive multiple of 8");
+  TDL_REQUIRE(nparts > 0 && stat_rows > 0 && rows > 0, "bad arguments");
+  TDL_REQUIRE(mean && invstd && scale && shift, "per-channel outputs required");
+  int cl = 1;
+  ReduceShape s = fused_shape(rows, C, &cl);
+  dim3 grid(s.gx, s.gy);
+  const double inv_n = 1.0 / (double)stat_rows;
+  const double unbias = stat_rows > 1 ? (double)stat_rows / (double)(stat_rows - 1) : 1.0;
+  cudaStream_t st = (cudaStream_t)stream;
+  const bool res = residual != nullptr, mk = mask_out != nullptr && relu;
+  cudaError_t e;
+#define TDL_BN_FWD(R_, L_, M_)                                                                                     \
+  e = launch_clustered(bn_apply_fin_kernel<R_, L_, M_>, grid, cl, 0, st, (const bf16*)x, partial, nparts, inv_n,   \
+                       unbias, gamma, beta, running_mean, running_var, decay, eps, mean, invstd, scale, shift,     \
+                       (const bf16*)residual, (bf16*)y, (uint8_t*)mask_out, rows, C, s.tx, s.ty)
+  if (res && relu && mk) TDL_BN_FWD(true, true, true);
+  else if (res && relu) TDL_BN_FWD(true, true, false);
+  else if (res) TDL_BN_FWD(true, false, false);
+  else if (relu && mk) TDL_BN_FWD(false, true, true);
+  else if (relu) TDL_BN_FWD(false, true, false);
+  else TDL_BN_FWD(false, false, false);
+#undef TDL_BN_FWD
+  if (e != cudaSuccess) return tdl::cuda_fail(e, "bn_apply_fin_kernel");
+  TDL_LAUNCH_OK("bn_apply_fin_kernel");
+  return 0;
+}
+
+// Partial (sum, sum of squares) rows of x[rows, C] into scratch ([*nparts][2][C]); the first half of tdl_bn_fwd_stats.
+TDL_API int tdl_bn_partial_stats(const void* x, int64_t rows, int C, float* scratch, int64_t scratch_floats,
+                                 int* nparts, void* stream) {
+  TDL_REQUIRE(C > 0 && C % 8 == 0, "C must be a positive multiple of 8");
+  TDL_REQUIRE(rows > 0 && nparts, "bad arguments");
+  ReduceShape s = reduce_shape(rows, C, resident_ctas(bn_partial_stats_kernel, &g_fwd_stats_ctas));
+  TDL_REQUIRE(scratch_floats >= (int64_t)s.gx * 2 * C, "scratch too small (see tdl_bn_scratch_floats)");
+  cudaError_t e = tdl::launch_pdl(bn_partial_stats_kernel, dim3(s.gx, s.gy), dim3(kThreads),
+                                  kThreads * 16 * sizeof(float), (cudaStream_t)stream, (const bf16*)x, rows, C, s.tx,
+                                  s.ty, scratch);
+  if (e != cudaSuccess) return tdl::cuda_fail(e, "bn_partial_stats_kernel");
+  TDL_LAUNCH_OK("bn_partial_stats_kernel");
+  *nparts = s.gx;
+  return 0;
+}
+
+// Partial rows of (sum dy, sum dy * xhat), dy = dz with the ReLU mask applied: the reduction half of
+// tdl_bn_bwd_reduce, specialised per mask source.  Feed scratch / *nparts to tdl_bn_bwd_apply_fused.
+TDL_API int tdl_bn_bwd_partial(const void* dz, const void* x, const void* z, int z_is_bitmask, const float* scale,
+                               const float* shift, const float* mean, const float* invstd, int64_t rows, int C,
+                               int relu, float* scratch, int64_t scratch_floats, int* nparts, void* stream) {
+  TDL_REQUIRE(C > 0 && C % 8 == 0, "C must be a positive multiple of 8");
+  TDL_REQUIRE(rows > 0 && nparts, "bad arguments");
+  const int mode = mask_mode(relu, z, z_is_bitmask);
+  void (*kern)(const bf16*, const bf16*, const void*, const float*, const float*, const float*, const float*, int64_t,
+               int, int, int, float*) =
+      mode == kNoRelu ? bn_bwd_partial_t_kernel<kNoRelu>
+      : mode == kRecompute ? bn_bwd_partial_t_kernel<kRecompute>
+      : mode == kBits ? bn_bwd_partial_t_kernel<kBits> : bn_bwd_partial_t_kernel<kFromZ>;
+  ReduceShape s = reduce_shape(rows, C, resident_ctas(kern, &g_bwd_partial_t_ctas[mode]));
+  TDL_REQUIRE(scratch_floats >= (int64_t)s.gx * 2 * C, "scratch too small (see tdl_bn_scratch_floats)");
+  cudaError_t e = tdl::launch_pdl(kern, dim3(s.gx, s.gy), dim3(kThreads), kThreads * 16 * sizeof(float),
+                                  (cudaStream_t)stream, (const bf16*)dz, (const bf16*)x, z, scale, shift, mean, invstd,
+                                  rows, C, s.tx, s.ty, scratch);
+  if (e != cudaSuccess) return tdl::cuda_fail(e, "bn_bwd_partial_t_kernel");
+  TDL_LAUNCH_OK("bn_bwd_partial_t_kernel");
+  *nparts = s.gx;
+  return 0;
+}
+
+// dgamma / dbeta from the partial rows AND dx (and dres) in one launch (replaces tdl_bn_bwd_finalize_partials +
+// tdl_bn_bwd_apply).  dgamma / dbeta ([C]) are written; acc_* (may be NULL) are added to.
+TDL_API int tdl_bn_bwd_apply_fused(const void* dz, const void* x, const void* z, int z_is_bitmask, const float* scale,
+                                   const float* shift, const float* mean, const float* invstd, const float* partial,
+                                   int nparts, float* dgamma, float* dbeta, float* acc_dgamma, float* acc_dbeta,
+                                   void* dx, void* dres, int64_t rows, int C, int relu, void* stream) {
+  TDL_REQUIRE(C > 0 && C % 8 == 0, "C must be a positive multiple of 8");
+  TDL_REQUIRE(nparts > 0 && rows > 0 && dgamma && dbeta, "bad arguments");
+  int cl = 1;
+  ReduceShape s = fused_shape(rows, C, &cl);
+  dim3 grid(s.gx, s.gy);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int mode = mask_mode(relu, z, z_is_bitmask);
+  const float inv_n = 1.f / (float)rows;
+  cudaError_t e;
+#define TDL_BN_BWD(M_, D_)                                                                                          \
+  e = launch_clustered(bn_bwd_apply_fin_kernel<M_, D_>, grid, cl, 0, st, (const bf16*)dz, (const bf16*)x, z, scale, \
+                       shift, mean, invstd, partial, nparts, inv_n, dgamma, dbeta, acc_dgamma, acc_dbeta,           \
+                       (bf16*)dx, (bf16*)dres, rows, C, s.tx, s.ty)
+  if (dres) {
+    if (mode == kNoRelu) TDL_BN_BWD(kNoRelu, true);
+    else if (mode == kRecompute) TDL_BN_BWD(kRecompute, true);
+    else if (mode == kBits) TDL_BN_BWD(kBits, true);
+    else TDL_BN_BWD(kFromZ, true);
+  } else {
+    if (mode == kNoRelu) TDL_BN_BWD(kNoRelu, false);
+    else if (mode == kRecompute) TDL_BN_BWD(kRecompute, false);
+    else if (mode == kBits) TDL_BN_BWD(kBits, false);
+    else TDL_BN_BWD(kFromZ, false);
+  }
+#undef TDL_BN_BWD
+  if (e != cudaSuccess) return tdl::cuda_fail(e, "bn_bwd_apply_fin_kernel");
+  TDL_LAUNCH_OK("bn_bwd_apply_fin_kernel");
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------------------
 // Allocation-free variant of tdl_bn_fwd_stats.
 //
 // Some users of this library cannot hand us scratch memory because they cannot obtain any: processes whose

@@ -107,6 +107,10 @@ struct Geometry {
   // shift instead of re-fetching a shifted copy per tap (the tap-shifted form is bound by L2->smem bandwidth there)
   int halo, halo_pw, halo_pbytes, halo_ptx, halo_nb, halo_bo;
   int has_mask; // res_mma only: zero outputs whose bit in a [pixels][K/8] byte mask is clear (fused ReLU backward)
+  // which tap of the weight tensor filter position (r, s) reads: tap_base + r * tap_sr + s * tap_ss (default 0, S, 1).
+  // A parity class of a strided data gradient walks a strided subset of the full flipped filter this way, so it needs
+  // no re-laid-out copy of its taps.
+  int tap_base, tap_sr, tap_ss;
 };
 
 // Pick the (TN, TH, TW) pixel patch with the best row utilisation for `rows` GEMM rows.
@@ -336,7 +340,7 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
           }
           continue;
         }
-        int tap = 0, kb = 0, r = 0, s = 0;  // advanced incrementally: no divisions on the TMA-issue path
+        int tap = g.tap_base, kb = 0, r = 0, s = 0;  // advanced incrementally: no divisions on the TMA-issue path
         for (int it = 0; it < k_iters; ++it) {
           ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
           if (leader) {
@@ -352,10 +356,11 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
           }
           if (++kb == g.num_kb) {
             kb = 0;
-            ++tap;
+            tap += g.tap_ss;
             if (++s == g.S) {
               s = 0;
               ++r;
+              tap = g.tap_base + r * g.tap_sr;
             }
           }
         }
@@ -1491,12 +1496,18 @@ struct BnBwd {
   const float* shift;
 };
 
+// A strided subset of the taps of a larger filter: `w` holds w_taps taps per output channel and filter position
+// (r, s) of this launch reads tap base + r * sr + s * ss of it.
+struct TapSel {
+  int w_taps, base, sr, ss;
+};
+
 static int g_halo_mode = -1;  // -1 = read TDL_HALO on first use, 0 = off (default), 1 = on, 2 = on with base offsets
 
 static int fprop_impl(const void* x, const void* w, void* y, const float* bias, const void* residual, int N, int H,
                       int W, int C, int K, int R, int S, int stride, int dil, int pad_h, int pad_w, int P, int Q,
                       int relu, const OutView* view, float* stats, int* nparts, void* stream,
-                      const void* out_mask = nullptr, const BnBwd* bnb = nullptr) {
+                      const void* out_mask = nullptr, const BnBwd* bnb = nullptr, const TapSel* taps = nullptr) {
   TDL_REQUIRE(C % 8 == 0 && K % 8 == 0, "channel counts must be multiples of 8 (16-byte TMA strides)");
   TDL_REQUIRE(stride >= 1 && stride <= 8 && dil >= 1, "bad stride/dilation");
   TDL_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(w) & 15) == 0 &&
@@ -1512,6 +1523,12 @@ static int fprop_impl(const void* x, const void* w, void* y, const float* bias, 
     g.N = N; g.H = H; g.W = W; g.P = P; g.Q = Q;
   }
   g.C = C; g.K = K; g.R = R; g.S = S; g.stride = stride; g.dil = dil; g.pad_h = pad_h; g.pad_w = pad_w;
+  g.tap_base = taps ? taps->base : 0; g.tap_sr = taps ? taps->sr : S; g.tap_ss = taps ? taps->ss : 1;
+  if (taps) {
+    const int last = taps->base + (R - 1) * taps->sr + (S - 1) * taps->ss;
+    TDL_REQUIRE(taps->base >= 0 && last >= 0 && taps->base < taps->w_taps && last < taps->w_taps,
+                "tap selection walks outside the weight tensor");
+  }
   choose_patch(g.N, g.P, g.Q, kBlockM, stride, &g.TN, &g.TH, &g.TW);
   g.tiles_n = (int)cdiv(g.N, g.TN);
   g.tiles_h = (int)cdiv(g.P, g.TH);
@@ -1532,7 +1549,7 @@ static int fprop_impl(const void* x, const void* w, void* y, const float* bias, 
       g_halo_mode = (e != nullptr) ? atoi(e) : 0;
     }
     const int enabled = g_halo_mode != 0, use_bo = g_halo_mode == 2;
-    if (enabled && !flat && !view && residual == nullptr && bnb == nullptr && R * S > 1 && stride == 1 && dil <= 2 && P >= 12 &&
+    if (enabled && !taps && !flat && !view && residual == nullptr && bnb == nullptr && R * S > 1 && stride == 1 && dil <= 2 && P >= 12 &&
         Q >= 12) {
       const int th_tiles = (int)cdiv(P, 16);
       const int th = (int)cdiv(P, th_tiles);
@@ -1589,7 +1606,7 @@ static int fprop_impl(const void* x, const void* w, void* y, const float* bias, 
     if (rc) return rc;
   }
   {
-    uint64_t dims[3] = {(uint64_t)C, (uint64_t)(R * S), (uint64_t)K};
+    uint64_t dims[3] = {(uint64_t)C, (uint64_t)(taps ? taps->w_taps : R * S), (uint64_t)K};
     uint32_t box[3] = {64, 1, (uint32_t)block_n};
     uint32_t es[3] = {1, 1, 1};
     int rc = encode_bf16(&tw, w, 3, dims, box, es);
@@ -1714,6 +1731,21 @@ TDL_API int tdl_conv2d_fprop_strided_out_bf16(const void* x, const void* w, void
   TDL_REQUIRE((P - 1) * y_step + y_off_h < y_full_h && (Q - 1) * y_step + y_off_w < y_full_w, "view exceeds tensor");
   return fprop_impl(x, w, y, nullptr, nullptr, N, H, W, C, K, R, S, 1, dil, pad_h, pad_w, P, Q, 0, &v, nullptr, nullptr,
                     stream);
+}
+
+// Same, reading its R x S taps out of a LARGER filter: `w` is [K, w_taps, C] and filter position (r, s) uses tap
+// tap_base + r * tap_sr + s * tap_ss.  With w = the flipped / transposed data-gradient copy of a strided convolution's
+// weights (tdl_conv2d_weight_prep) one call per input-parity class needs no per-class weight copy.
+TDL_API int tdl_conv2d_fprop_strided_out_taps_bf16(const void* x, const void* w, void* y, int N, int H, int W, int C,
+                                                   int K, int R, int S, int w_taps, int tap_base, int tap_sr, int tap_ss,
+                                                   int dil, int pad_h, int pad_w, int P, int Q, int y_full_h,
+                                                   int y_full_w, int y_step, int y_off_h, int y_off_w, void* stream) {
+  OutView v = {y_full_h, y_full_w, y_step, y_off_h, y_off_w};
+  TapSel t = {w_taps, tap_base, tap_sr, tap_ss};
+  TDL_REQUIRE(y_step >= 1 && y_off_h >= 0 && y_off_w >= 0, "bad output view");
+  TDL_REQUIRE((P - 1) * y_step + y_off_h < y_full_h && (Q - 1) * y_step + y_off_w < y_full_w, "view exceeds tensor");
+  return fprop_impl(x, w, y, nullptr, nullptr, N, H, W, C, K, R, S, 1, dil, pad_h, pad_w, P, Q, 0, &v, nullptr, nullptr,
+                    stream, nullptr, nullptr, &t);
 }
 
 // dw[K,R*S,C] (fp32) += sum over pixels of dy[N,P,Q,K]^T * shifted x[N,H,W,C].  Caller zeroes dw.

@@ -46,6 +46,12 @@ int tdl_conv2d_fprop_stats_bf16(const void* x, const void* w, void* y, const flo
 int tdl_conv2d_fprop_strided_out_bf16(const void* x, const void* w, void* y, int N, int H, int W, int C, int K, int R,
                                       int S, int dil, int pad_h, int pad_w, int P, int Q, int y_full_h, int y_full_w,
                                       int y_step, int y_off_h, int y_off_w, void* stream);
+/* same, with the R x S taps read out of a larger filter w [K, w_taps, C]: position (r,s) uses tap
+ * tap_base + r*tap_sr + s*tap_ss (a parity class of a strided data gradient on the full flipped weight copy) */
+int tdl_conv2d_fprop_strided_out_taps_bf16(const void* x, const void* w, void* y, int N, int H, int W, int C, int K,
+                                           int R, int S, int w_taps, int tap_base, int tap_sr, int tap_ss, int dil,
+                                           int pad_h, int pad_w, int P, int Q, int y_full_h, int y_full_w, int y_step,
+                                           int y_off_h, int y_off_w, void* stream);
 /* dw [K, R*S, C] fp32 is ACCUMULATED into (zero it first): dw += dy^T (*) x */
 int tdl_conv2d_wgrad_bf16(const void* x, const void* dy, float* dw, int N, int H, int W, int C, int K, int R, int S,
                           int stride, int dil, int pad_h, int pad_w, int P, int Q, void* stream);

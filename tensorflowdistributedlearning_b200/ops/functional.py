@@ -32,6 +32,17 @@ _FUSE_BN_BWD = os.environ.get("TDL_FUSE_BN_BWD", "0") == "1"  # measured slower 
 
 
 _FUSED_BN_HITS = 0
+# BatchNorm with the statistics finalize folded into the apply kernels (cluster + DSMEM, csrc/bn.cu): one launch less
+# per BatchNorm in forward and one less in backward -- numerically identical, but MEASURED SLOWER on B200 (the fold is
+# a serial latency chain in front of the streaming loop and cluster launches stream slower: ResNet-50 19.3 -> 32.1
+# ms/step, profiles/bn_fold_experiment.txt), so it is off unless TDL_BN_FOLD=1 asks for it.
+_BN_FOLD = os.environ.get("TDL_BN_FOLD", "0") == "1"
+
+
+def enable_bn_fold(flag: bool) -> None:
+    global _BN_FOLD
+    _BN_FOLD = bool(flag)
+
 
 # Batched weight preparation (trainer-owned steps only): the bf16 fprop / dgrad copies of every convolution weight
 # live in persistent buffers that ONE kernel refreshes at the start of a step (`begin_step`), instead of one small
@@ -47,6 +58,7 @@ class _WeightPrepRegistry:
         self.entries = {}
         self.table = None
         self.retired = []
+        self.zero_dx = {}  # pre-zeroed data-gradient buffers of strided convolutions with tap-less parity classes
 
     def drop_table(self):
         if self.table is not None:
@@ -240,7 +252,7 @@ class _ConvNative(torch.autograd.Function):
         K, Rk, Sk, C = weight.shape
         taps = Rk * Sk
         need_dgrad = ctx.needs_input_grad[0]
-        need_wd = need_dgrad and stride == 1
+        need_wd = need_dgrad  # stride 1: the whole flipped copy; stride 2: each parity class walks a subset of it
         ent = _WPREP.entries.get(id(weight)) if _WPREP_ON else None
         if (ent is not None and ent["w"] is weight and ent["step"] == _WPREP_STEP
                 and (ent["wd"] is not None or not need_wd)):
@@ -302,7 +314,7 @@ class _ConvNative(torch.autograd.Function):
         d_tap = rest[-1] if (ctx.want_tap and rest and rest[-1] is not None) else None
         dx = dw = db = None
         if ctx.needs_input_grad[0]:
-            if has_wd:
+            if has_wd and stride == 1:
                 mask = ctx.in_mask if (d_tap is not None and C % 32 == 0) else None
                 src = ctx.bn_src
                 geo = dict(R=Rk, S=Sk, dil=dil, pad_h=(Rk - 1) * dil - pt, pad_w=(Sk - 1) * dil - pl, out_hw=(h, w))
@@ -328,14 +340,19 @@ class _ConvNative(torch.autograd.Function):
                 _count(1)
             else:
                 # strided data gradient: one tcgen05 launch per input-parity class, strided TMA stores
-                dx = O.conv2d_dgrad_strided(dy, wsaved, (n, h, w, C), R=Rk, S=Sk, stride=stride, pad_h=pt, pad_w=pl)
+                dx = O.conv2d_dgrad_strided(dy, wsaved, (n, h, w, C), R=Rk, S=Sk, stride=stride, pad_h=pt, pad_w=pl,
+                                            zero_buffers=_WPREP.zero_dx if _WPREP_ON else None,
+                                            zero_key=(id(ctx.weight_param)
+                                                      if isinstance(ctx.weight_param, torch.nn.Parameter) else None))
                 _count(stride * stride)
         if d_tap is not None and dx is not None:
             dx = dx + d_tap
         if ctx.needs_input_grad[1] and C <= 16:
             # tiny Cin (channel-padded RGB stem): a 128x64 tensor-core tile would be >90% padding, cuDNN's
             # small-channel wgrad is the better tool for this one layer
-            w4 = wsaved.view(K, Rk, Sk, C).permute(0, 3, 1, 2)
+            w4 = ctx.weight_param.detach().to(x.dtype).permute(0, 3, 1, 2)  # only its shape matters here
+            if w4.shape[1] != C:
+                w4 = F.pad(w4, (0, 0, 0, 0, 0, C - w4.shape[1]))
             xin = x.permute(0, 3, 1, 2)
             if pt != pb or pl != pr:
                 xin = F.pad(xin, (pl, pr, pt, pb))
@@ -597,6 +614,24 @@ class _BNNative(torch.autograd.Function):
         C = shape[-1]
         x2 = x.reshape(-1, C)
         r2 = None if residual is None else residual.reshape(-1, C)
+        need_z = training and relu and residual is not None
+        if training and _BN_FOLD:
+            if partials is None:
+                partials, nparts = O.bn_partial_stats(x2)
+                _count(1)
+            else:
+                nparts = partials.shape[0]
+            z, zmask, mean, invstd, scale, shift = O.bn_apply_fused(x2, partials, nparts, x2.shape[0], gamma, beta,
+                                                                    running_mean, running_var, decay, eps, r2, relu,
+                                                                    want_mask=need_z)
+            _count(1)
+            ctx.save_for_backward(x2, zmask, scale, shift, mean, invstd)
+            ctx.cfg = (relu, residual is not None, training, shape)
+            global _LAST_RELU_MASK, _LAST_BN_SRC
+            _LAST_RELU_MASK = zmask
+            _LAST_BN_SRC = dict(x=x2, mean=mean, invstd=invstd, scale=scale, shift=shift, relu=bool(relu),
+                                has_res=residual is not None)
+            return z.view(shape)
         if training and partials is not None:
             mean, invstd, scale, shift = O.bn_finalize_partials(partials, partials.shape[0], x2.shape[0], gamma, beta,
                                                                 running_mean, running_var, decay, eps)
@@ -608,7 +643,6 @@ class _BNNative(torch.autograd.Function):
             scale, shift = O.bn_infer_scale_shift(gamma, beta, running_mean, running_var, eps)
             mean = invstd = None
             _count(1)
-        need_z = training and relu and residual is not None
         if need_z:
             # with a residual the ReLU mask cannot be recomputed from x alone: keep it as 1 bit per element (written by
             # the same kernel) instead of making both backward kernels re-read the whole activation
@@ -619,7 +653,6 @@ class _BNNative(torch.autograd.Function):
         if training:
             ctx.save_for_backward(x2, zmask, scale, shift, mean, invstd)
         ctx.cfg = (relu, residual is not None, training, shape)
-        global _LAST_RELU_MASK, _LAST_BN_SRC
         _LAST_RELU_MASK = zmask
         _LAST_BN_SRC = (dict(x=x2, mean=mean, invstd=invstd, scale=scale, shift=shift, relu=bool(relu),
                              has_res=residual is not None) if training else None)
@@ -646,24 +679,25 @@ class _BNNative(torch.autograd.Function):
             partials = ent[2]  # the kernel that produced dz already reduced (sum dz, sum dz * xhat)
             global _FUSED_BN_HITS
             _FUSED_BN_HITS += 1
+        bwd = O.bn_bwd_fused if _BN_FOLD else O.bn_bwd
         if premasked:
             # the consumer's data-gradient kernel already applied this layer's ReLU mask: no masking here, and the
             # residual branch's gradient is the incoming gradient itself (nothing to write)
-            dx, _, dgamma, dbeta = O.bn_bwd(dz2, x2, None, scale, shift, mean, invstd, False, False,
+            dx, _, dgamma, dbeta = bwd(dz2, x2, None, scale, shift, mean, invstd, False, False,
                                             acc_dgamma=g.grad if direct else None,
                                             acc_dbeta=b.grad if direct else None, partials=partials)
             dres = dz2
         elif has_res and not relu:
             # no activation after the sum: the residual branch's gradient is the incoming gradient, nothing to write
-            dx, _, dgamma, dbeta = O.bn_bwd(dz2, x2, None, scale, shift, mean, invstd, False, False,
-                                            acc_dgamma=g.grad if direct else None,
-                                            acc_dbeta=b.grad if direct else None, partials=partials)
+            dx, _, dgamma, dbeta = bwd(dz2, x2, None, scale, shift, mean, invstd, False, False,
+                                       acc_dgamma=g.grad if direct else None,
+                                       acc_dbeta=b.grad if direct else None, partials=partials)
             dres = dz2
         else:
-            dx, dres, dgamma, dbeta = O.bn_bwd(dz2, x2, z2, scale, shift, mean, invstd, relu, has_res,
-                                               acc_dgamma=g.grad if direct else None,
-                                               acc_dbeta=b.grad if direct else None, partials=partials)
-        _count(3 if partials is not None else 4)
+            dx, dres, dgamma, dbeta = bwd(dz2, x2, z2, scale, shift, mean, invstd, relu, has_res,
+                                          acc_dgamma=g.grad if direct else None,
+                                          acc_dbeta=b.grad if direct else None, partials=partials)
+        _count((3 if partials is not None else 4) - (1 if _BN_FOLD else 0))
         if direct:
             _notify(g)
             _notify(b)

@@ -148,18 +148,24 @@ def bn_finalize_partials(partials: torch.Tensor, nparts: int, rows: int, gamma, 
     return out[0], out[1], out[2], out[3]
 
 
-def conv2d_dgrad_strided(dy: torch.Tensor, wf: torch.Tensor, in_shape, *, R: int, S: int, stride: int, pad_h: int,
-                         pad_w: int) -> torch.Tensor:
+def conv2d_dgrad_strided(dy: torch.Tensor, wd: torch.Tensor, in_shape, *, R: int, S: int, stride: int, pad_h: int,
+                         pad_w: int, zero_buffers: Optional[dict] = None, zero_key=None) -> torch.Tensor:
     """Data gradient of a stride-`stride` convolution (dilation 1) on the tcgen05 kernel.
 
-    dx is split into stride*stride input-parity classes; class (a, b) is a stride-1 convolution of dy with the
-    taps r = r0 + stride*i, s = s0 + stride*j (flipped, channel-transposed), written through a strided TMA store.
-    wf: bf16 [K, R*S, C] forward weights.
-    """
+    dx is split into stride*stride input-parity classes; class (a, b) is a stride-1 convolution of dy with the taps
+    r = r0 + stride*i, s = s0 + stride*j, written through a strided TMA store.  ``wd``: the flipped / transposed
+    data-gradient copy [C, R*S (flipped), K] of the weights (``conv2d_weight_prep``); every class reads its taps out of
+    it through a (base, row stride, column stride) walk, so no per-class weight copy is made.
+
+    Classes without a tap (1x1 stride 2: three of four) must read as zero.  ``zero_buffers`` (a dict owned by the
+    caller, e.g. the trainer's weight-prep registry) keeps one pre-zeroed dx per (``zero_key`` = the layer, shape): the
+    kernels only ever write the non-empty classes, so the zeros survive from step to step and the per-step fill of the
+    whole tensor goes away.  The returned tensor is then SHARED between steps: consume it before the layer's next
+    backward.  Without a dict / key the tensor is zero-filled on every call."""
     _chk_bf16_nhwc(dy, "dy")
     n, h, w, c = in_shape
     _, p, q, k = dy.shape
-    w4 = wf.view(k, R, S, c)
+    assert wd.dtype == torch.bfloat16 and wd.is_contiguous() and wd.numel() == c * R * S * k
     empty_class = False
     classes = []
     for a in range(stride):
@@ -175,16 +181,26 @@ def conv2d_dgrad_strided(dy: torch.Tensor, wf: torch.Tensor, in_shape, *, R: int
                 empty_class = True
                 continue
             classes.append((a, b, r0, s0, nr, ns, ha, wb))
-    dx = (torch.zeros if empty_class else torch.empty)(in_shape, dtype=torch.bfloat16, device=dy.device)
+    if not empty_class:
+        dx = torch.empty(in_shape, dtype=torch.bfloat16, device=dy.device)
+    else:
+        key = (zero_key, tuple(in_shape))
+        dx = zero_buffers.get(key) if (zero_buffers is not None and zero_key is not None) else None
+        if dx is None:
+            dx = torch.zeros(in_shape, dtype=torch.bfloat16, device=dy.device)
+            if zero_buffers is not None and zero_key is not None and not torch.cuda.is_current_stream_capturing():
+                zero_buffers[key] = dx
     for (a, b, r0, s0, nr, ns, ha, wb) in classes:
-        # Wd[c, r', s', k] = W[k, r0 + stride*(nr-1-r'), s0 + stride*(ns-1-s'), c]
-        wsub = w4[:, r0::stride, s0::stride, :].flip(1, 2).permute(3, 1, 2, 0).contiguous()
+        # class taps, flipped: position (r', s') reads W[k, r0 + stride*(nr-1-r'), s0 + stride*(ns-1-s'), c], which in
+        # the fully flipped copy sits at tap ((R-1-r0-stride*(nr-1)) + stride*r') * S + (S-1-s0-stride*(ns-1)) + stride*s'
+        base = (R - 1 - r0 - stride * (nr - 1)) * S + (S - 1 - s0 - stride * (ns - 1))
         oh = (a + pad_h - r0) // stride
         ow = (b + pad_w - s0) // stride
-        rc = N.lib().tdl_conv2d_fprop_strided_out_bf16(
-            N.ptr(dy), N.ptr(wsub), N.ptr(dx), _i(n), _i(p), _i(q), _i(k), _i(c), _i(nr), _i(ns), _i(1),
-            _i(nr - 1 - oh), _i(ns - 1 - ow), _i(ha), _i(wb), _i(h), _i(w), _i(stride), _i(a), _i(b), N.stream_ptr())
-        N.check(rc, "tdl_conv2d_fprop_strided_out_bf16")
+        rc = N.lib().tdl_conv2d_fprop_strided_out_taps_bf16(
+            N.ptr(dy), N.ptr(wd), N.ptr(dx), _i(n), _i(p), _i(q), _i(k), _i(c), _i(nr), _i(ns), _i(R * S), _i(base),
+            _i(stride * S), _i(stride), _i(1), _i(nr - 1 - oh), _i(ns - 1 - ow), _i(ha), _i(wb), _i(h), _i(w),
+            _i(stride), _i(a), _i(b), N.stream_ptr())
+        N.check(rc, "tdl_conv2d_fprop_strided_out_taps_bf16")
     return dx
 
 
@@ -262,6 +278,64 @@ def bn_apply(x2d, scale, shift, residual2d, relu: bool, want_mask: bool = False)
     return (y, mask) if want_mask else y
 
 
+def bn_partial_stats(x2d: torch.Tensor):
+    """Partial (sum, sum of squares) rows of x2d [rows, C] -> (scratch [nparts, 2, C] view, nparts): the statistics
+    pass alone, for ``bn_apply_fused`` when no producing kernel left partials."""
+    rows, C = x2d.shape
+    scratch = _bn_scratch(rows, C, x2d.device)
+    nparts = ctypes.c_int(0)
+    rc = N.lib().tdl_bn_partial_stats(N.ptr(x2d), _i64(rows), _i(C), N.ptr(scratch), _i64(scratch.numel()),
+                                      ctypes.byref(nparts), N.stream_ptr())
+    N.check(rc, "tdl_bn_partial_stats")
+    return scratch, int(nparts.value)
+
+
+def bn_apply_fused(x2d, partials, nparts: int, stat_rows: int, gamma, beta, running_mean, running_var, decay: float,
+                   eps: float, residual2d, relu: bool, want_mask: bool = False):
+    """Statistics finalize + moving averages + y = relu?(x*scale + shift (+ residual)) in ONE launch (thread-block
+    clusters: the first CTA of every cluster folds the partial rows, the others read the constants through DSMEM).
+    Returns (y, mask_or_None, mean, invstd, scale, shift)."""
+    rows, C = x2d.shape
+    y = torch.empty_like(x2d)
+    mask = torch.empty((rows, C // 8), dtype=torch.uint8, device=x2d.device) if (want_mask and relu) else None
+    out = torch.empty((4, C), dtype=torch.float32, device=x2d.device)
+    rc = N.lib().tdl_bn_apply_fused(N.ptr(x2d), N.ptr(partials), _i(nparts), _i64(stat_rows), N.ptr(gamma),
+                                    N.ptr(beta), N.ptr(running_mean), N.ptr(running_var), _f(decay), _f(eps),
+                                    N.ptr(out[0]), N.ptr(out[1]), N.ptr(out[2]), N.ptr(out[3]), N.ptr(residual2d),
+                                    N.ptr(y), N.ptr(mask), _i64(rows), _i(C), _i(int(relu)), N.stream_ptr())
+    N.check(rc, "tdl_bn_apply_fused")
+    return y, mask, out[0], out[1], out[2], out[3]
+
+
+def bn_bwd_fused(dz2d, x2d, z2d, scale, shift, mean, invstd, relu: bool, want_dres: bool,
+                 acc_dgamma=None, acc_dbeta=None, partials=None):
+    """Same contract as ``bn_bwd`` in two launches instead of three: the (mask-specialised) reduction pass, then ONE
+    kernel that folds the partial rows into dgamma / dbeta and writes dx (and dres)."""
+    rows, C = x2d.shape
+    dev = x2d.device
+    dgb = torch.empty((2, C), dtype=torch.float32, device=dev)
+    zbits = int(z2d is not None and z2d.dtype == torch.uint8)
+    if partials is None:
+        scratch = _bn_scratch(rows, C, dev)
+        nparts = ctypes.c_int(0)
+        rc = N.lib().tdl_bn_bwd_partial(N.ptr(dz2d), N.ptr(x2d), N.ptr(z2d), _i(zbits), N.ptr(scale), N.ptr(shift),
+                                        N.ptr(mean), N.ptr(invstd), _i64(rows), _i(C), _i(int(relu)), N.ptr(scratch),
+                                        _i64(scratch.numel()), ctypes.byref(nparts), N.stream_ptr())
+        N.check(rc, "tdl_bn_bwd_partial")
+        partials, np_ = scratch, int(nparts.value)
+    else:
+        assert partials.dtype == torch.float32 and partials.shape[1:] == (2, C) and partials.is_contiguous()
+        np_ = partials.shape[0]
+    dx = torch.empty_like(x2d)
+    dres = torch.empty_like(x2d) if want_dres else None
+    rc = N.lib().tdl_bn_bwd_apply_fused(N.ptr(dz2d), N.ptr(x2d), N.ptr(z2d), _i(zbits), N.ptr(scale), N.ptr(shift),
+                                        N.ptr(mean), N.ptr(invstd), N.ptr(partials), _i(np_), N.ptr(dgb[0]),
+                                        N.ptr(dgb[1]), N.ptr(acc_dgamma), N.ptr(acc_dbeta), N.ptr(dx), N.ptr(dres),
+                                        _i64(rows), _i(C), _i(int(relu)), N.stream_ptr())
+    N.check(rc, "tdl_bn_bwd_apply_fused")
+    return dx, dres, dgb[0], dgb[1]
+
+
 def bn_bwd(dz2d, x2d, z2d, scale, shift, mean, invstd, relu: bool, want_dres: bool,
            acc_dgamma=None, acc_dbeta=None, partials=None):
     """Returns (dx, dres_or_None, dgamma, dbeta).  ``partials`` ([nparts, 2, C], from ``conv2d_dgrad_bnstats``):
@@ -289,6 +363,19 @@ def bn_bwd(dz2d, x2d, z2d, scale, shift, mean, invstd, relu: bool, want_dres: bo
 
 def _bn_bwd_reduce(dz2d, x2d, z2d, zbits, scale, shift, mean, invstd, rows, C, relu, dgb, acc_dgamma, acc_dbeta):
     scratch = _bn_scratch(rows, C, x2d.device)
+    if C >= 256:
+        # wide tensors: the mask-specialised reduction with four rows in flight (fewer registers, more loads
+        # outstanding) -- 185 -> 161 us on [802816, 256], 64 -> 56 us on [50176, 1024]; narrow tensors measured equal
+        # or a little slower with it (profiles/bn_fold_experiment.txt), they keep the generic kernel
+        nparts = ctypes.c_int(0)
+        rc = N.lib().tdl_bn_bwd_partial(N.ptr(dz2d), N.ptr(x2d), N.ptr(z2d), _i(zbits), N.ptr(scale), N.ptr(shift),
+                                        N.ptr(mean), N.ptr(invstd), _i64(rows), _i(C), _i(int(relu)), N.ptr(scratch),
+                                        _i64(scratch.numel()), ctypes.byref(nparts), N.stream_ptr())
+        N.check(rc, "tdl_bn_bwd_partial")
+        rc = N.lib().tdl_bn_bwd_finalize_partials(N.ptr(scratch), _i(int(nparts.value)), _i(C), N.ptr(dgb[0]),
+                                                  N.ptr(dgb[1]), N.ptr(acc_dgamma), N.ptr(acc_dbeta), N.stream_ptr())
+        N.check(rc, "tdl_bn_bwd_finalize_partials")
+        return rc
     rc = N.lib().tdl_bn_bwd_reduce(N.ptr(dz2d), N.ptr(x2d), N.ptr(z2d), _i(zbits), N.ptr(scale), N.ptr(shift),
                                    N.ptr(mean), N.ptr(invstd), _i64(rows), _i(C), _i(int(relu)), N.ptr(scratch),
                                    _i64(scratch.numel()), N.ptr(dgb[0]), N.ptr(dgb[1]), N.ptr(acc_dgamma),

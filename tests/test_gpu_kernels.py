@@ -152,7 +152,18 @@ def test_conv_dgrad_strided_parity_classes(O, case):
     pb = (P - 1) * 2 + R - H - pt
     wf = (torch.randn(K, R * R, C, device="cuda") / math.sqrt(R * R * C)).bfloat16()
     dy = torch.randn(N, P, P, K, device="cuda").bfloat16()
-    dx = O.conv2d_dgrad_strided(dy, wf, (N, H, H, C), R=R, S=R, stride=2, pad_h=pt, pad_w=pt)
+    # the flipped / transposed data-gradient copy [C, taps (flipped), K]: every parity class walks a subset of its taps
+    wd = wf.float().view(K, R * R, C).flip(1).permute(2, 1, 0).contiguous().bfloat16()
+    cache = {}
+    dx = O.conv2d_dgrad_strided(dy, wd, (N, H, H, C), R=R, S=R, stride=2, pad_h=pt, pad_w=pt, zero_buffers=cache,
+                                zero_key="layer")
+    if R == 1:  # three tap-less classes: the pre-zeroed buffer is kept and handed out again, zeros intact
+        assert len(cache) == 1
+        dx2 = O.conv2d_dgrad_strided(dy, wd, (N, H, H, C), R=R, S=R, stride=2, pad_h=pt, pad_w=pt,
+                                     zero_buffers=cache, zero_key="layer")
+        assert dx2.data_ptr() == dx.data_ptr() and float(dx2[:, 1::2].abs().max()) == 0.0
+    else:
+        assert not cache
     xr = torch.zeros(N, C, H + pt + max(pb, 0), H + pt + max(pb, 0), device="cuda", requires_grad=True)
     w4 = wf.float().view(K, R, R, C).permute(0, 3, 1, 2)
     yr = F.conv2d(xr, w4, None, stride=2)[:, :, :P, :P]
@@ -446,6 +457,59 @@ def test_batch_norm_fwd_bwd(O, rows, C, relu, res):
         dx2, dres2, dg2, db2 = O.bn_bwd(dz, x, zmask, scale, shift, mean, invstd, relu, res)
         assert torch.equal(dx2, dx) and torch.equal(dres2, dres)
         assert rel_err(dg2, dg) < 1e-6 and rel_err(db2, db) < 1e-6
+
+
+@pytest.mark.parametrize("rows,C,relu,res", [(4096, 64, True, False), (5000, 256, True, True), (777, 2048, False, False),
+                                             (802816, 64, True, False), (50176, 1024, True, True), (12, 8, True, False),
+                                             (3001, 72, False, True)])
+def test_batch_norm_with_the_finalize_folded_into_the_apply_kernels(O, rows, C, relu, res):
+    """Cluster / DSMEM variant (one launch less per BatchNorm in each direction) against the three-launch path it
+    replaces -- same partial rows in, so the per-channel constants must agree to fp32 rounding and the tensors bit for
+    bit wherever the constants do -- and against the fp32 reference."""
+    torch.manual_seed(3)
+    x = (torch.randn(rows, C, device="cuda") * 2 + 0.5).bfloat16()
+    gamma = torch.rand(C, device="cuda") + 0.5
+    beta = torch.randn(C, device="cuda") * 0.1
+    r = torch.randn(rows, C, device="cuda").bfloat16() if res else None
+    rm0, rv0 = torch.zeros(C, device="cuda"), torch.ones(C, device="cuda")
+    mean0, invstd0, scale0, shift0 = O.bn_fwd_stats(x, gamma, beta, rm0, rv0, 0.99, 1e-3)
+    z0 = O.bn_apply(x, scale0, shift0, r, relu)
+    rm, rv = torch.zeros(C, device="cuda"), torch.ones(C, device="cuda")
+    partials, nparts = O.bn_partial_stats(x)
+    z, zmask, mean, invstd, scale, shift = O.bn_apply_fused(x, partials, nparts, rows, gamma, beta, rm, rv, 0.99, 1e-3,
+                                                            r, relu, want_mask=res and relu)
+    for a, b in ((mean, mean0), (invstd, invstd0), (scale, scale0), (shift, shift0), (rm, rm0), (rv, rv0)):
+        assert torch.equal(a, b)                       # same fp64 fold of the same rows, same order
+    assert torch.equal(z, z0)
+    xf = x.float()
+    zr = (xf - xf.mean(0)) / torch.sqrt(xf.var(0, unbiased=False) + 1e-3) * gamma + beta
+    if res:
+        zr = zr + r.float()
+    if relu:
+        zr = zr.relu()
+    assert rel_err(z, zr) < 1e-2
+    dz = torch.randn(rows, C, device="cuda").bfloat16()
+    for zarg in ([zmask] if zmask is not None else []) + [z if res else None]:
+        dx0, dres0, dg0, db0 = O.bn_bwd(dz, x, zarg, scale, shift, mean, invstd, relu, res)
+        acc_g, acc_b = torch.ones(C, device="cuda"), torch.full((C,), 2.0, device="cuda")
+        dx, dres, dg, db = O.bn_bwd_fused(dz, x, zarg, scale, shift, mean, invstd, relu, res, acc_dgamma=acc_g,
+                                          acc_dbeta=acc_b)
+        # the reduction kernels differ (four rows in flight instead of two): sums agree to fp32 rounding
+        assert rel_err(dg, dg0) < 1e-5 and rel_err(db, db0) < 1e-5
+        assert rel_err(acc_g - 1.0, dg) < 1e-5 and rel_err(acc_b - 2.0, db) < 1e-5
+        assert rel_err(dx, dx0) < 4e-3
+        if res:
+            assert torch.equal(dres, dres0)
+    xr = xf.clone().requires_grad_(True)
+    g_, b_ = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+    out = (xr - xr.mean(0)) / torch.sqrt(xr.var(0, unbiased=False) + 1e-3) * g_ + b_
+    if res:
+        out = out + r.float()
+    if relu:
+        out = out * (z.float() > 0).float()
+    out.backward(dz.float())
+    assert rel_err(dx, xr.grad) < 1e-2
+    assert rel_err(dg, g_.grad) < 2e-3 and rel_err(db, b_.grad) < 2e-3
 
 
 def test_fused_optimizers_and_device_schedule(O):
