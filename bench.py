@@ -279,7 +279,7 @@ def measure(model_name, args, group, warmup):
         "dtype": "bf16", "data": "synthetic", "impl": "ours",
         "config": {"model": model_name, "global_batch": global_batch, "per_tower_batch": batch,
                    "image": f"{h}x{w}x{c}", "seq_len": None, "parallelism": f"dp{n_gpus}",
-                   "optimizer": cfg["opt"], "grad_comm": trainer.opt.comm, "nvls": bool(getattr(trainer.opt, "nvls", False)), "cuda_graph": trainer._graph is not None,
+                   "optimizer": cfg["opt"], "grad_comm": trainer.opt.comm, "grad_wire": trainer.opt.grad_wire, "nvls": bool(getattr(trainer.opt, "nvls", False)), "cuda_graph": trainer._graph is not None,
                    "overlap": trainer.opt.overlap,
                    "l2": "no flush needed: each step streams far more than the 126 MB L2 (activations >> L2)",
                    "weights": "random init", "loss_after_timed_steps": round(loss_dev, 4)},

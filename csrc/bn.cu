@@ -183,7 +183,7 @@ __global__ void bn_infer_scale_shift_kernel(const float* __restrict__ gamma, con
 __global__ void __launch_bounds__(kThreads)
 bn_apply_kernel(const bf16* __restrict__ x, const float* __restrict__ scale, const float* __restrict__ shift,
                 const bf16* __restrict__ residual, bf16* __restrict__ y, uint8_t* __restrict__ mask_out, int64_t rows,
-                int C, int tx, int ty, int relu) {
+                int C, int tx, int ty, int relu, int64_t ldy) {  // ldy: row pitch of y in elements (C, or a concat buffer's)
   ptx::pdl_trigger();
   ptx::pdl_wait();
   const int cx = threadIdx.x % tx;
@@ -216,7 +216,7 @@ bn_apply_kernel(const bf16* __restrict__ x, const float* __restrict__ scale, con
 #pragma unroll
       for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
     }
-    st8(y + r * C + col, pack8(f));
+    st8(y + r * ldy + col, pack8(f));
   };
   int64_t r = (int64_t)blockIdx.x * ty + ry;
   for (; r + step < rows; r += 2 * step) {
@@ -246,7 +246,7 @@ __global__ void __launch_bounds__(kThreads)
 bn_bwd_partial_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ x, const bf16* __restrict__ z,
                       const float* __restrict__ scale, const float* __restrict__ shift,
                       const float* __restrict__ mean, const float* __restrict__ invstd, int64_t rows, int C, int tx,
-                      int ty, int relu, int z_bits, float* __restrict__ partial) {
+                      int ty, int relu, int z_bits, float* __restrict__ partial, int64_t ld_dz) {
   ptx::pdl_trigger();
   ptx::pdl_wait();
   extern __shared__ float sm[];
@@ -294,7 +294,7 @@ bn_bwd_partial_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ x, c
     };
     int64_t r = (int64_t)blockIdx.x * ty + ry;
     for (; r + step < rows; r += 2 * step) {
-      const bf16x8 g0 = ld8(dz + r * C + col), g1 = ld8(dz + (r + step) * C + col);
+      const bf16x8 g0 = ld8(dz + r * ld_dz + col), g1 = ld8(dz + (r + step) * ld_dz + col);
       const bf16x8 x0 = ld8(x + r * C + col), x1 = ld8(x + (r + step) * C + col);
       if (relu && z && z_bits) {
         const uint8_t* zb = reinterpret_cast<const uint8_t*>(z);
@@ -311,7 +311,7 @@ bn_bwd_partial_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ x, c
       }
     }
     for (; r < rows; r += step) {
-      const bf16x8 g0 = ld8(dz + r * C + col), x0 = ld8(x + r * C + col);
+      const bf16x8 g0 = ld8(dz + r * ld_dz + col), x0 = ld8(x + r * C + col);
       if (relu && z && z_bits) {
         one(g0, x0, nullptr, (int)reinterpret_cast<const uint8_t*>(z)[r * c8 + cv]);
       } else if (relu && z) {
@@ -366,7 +366,12 @@ bn_bwd_apply_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ x, con
                     const float* __restrict__ scale, const float* __restrict__ shift, const float* __restrict__ mean,
                     const float* __restrict__ invstd, const float* __restrict__ dbeta,
                     const float* __restrict__ dgamma, float inv_n, bf16* __restrict__ dx, bf16* __restrict__ dres,
-                    int64_t rows, int C, int tx, int ty, int relu, int z_bits) {
+                    int64_t rows, int C, int tx, int ty, int relu, int z_bits, int64_t ld_dz,
+                    const bf16* __restrict__ addend, int mask_by_x) {
+  // addend (may be null): a second gradient of the SAME tensor x (the identity shortcut of a residual unit takes an alias
+  // of the BatchNorm's input), added here instead of by a separate elementwise kernel.  mask_by_x: x is itself the
+  // output of a ReLU (x >= 0); its backward -- zero where x == 0 -- is applied to the total, so the producer of x does
+  // not need a pass of its own for it.
   ptx::pdl_trigger();
   ptx::pdl_wait();
   const int cx = threadIdx.x % tx;
@@ -405,12 +410,22 @@ bn_bwd_apply_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ x, con
     }
 #pragma unroll
     for (int j = 0; j < 8; ++j) o[j] = fmaf(sc[j], g[j], fmaf(B[j], f[j], D[j]));
+    if (addend) {
+      float a[8];
+      unpack8(ld8(addend + r * C + col), a);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] += a[j];
+    }
+    if (mask_by_x) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = f[j] > 0.f ? o[j] : 0.f;
+    }
     st8(dx + r * C + col, pack8(o));
     if (dres) st8(dres + r * C + col, pack8(g));
   };
   int64_t r = (int64_t)blockIdx.x * ty + ry;
   for (; r + step < rows; r += 2 * step) {
-    const bf16x8 g0 = ld8(dz + r * C + col), g1 = ld8(dz + (r + step) * C + col);
+    const bf16x8 g0 = ld8(dz + r * ld_dz + col), g1 = ld8(dz + (r + step) * ld_dz + col);
     const bf16x8 x0 = ld8(x + r * C + col), x1 = ld8(x + (r + step) * C + col);
     if (relu && z && z_bits) {
       const uint8_t* zb = reinterpret_cast<const uint8_t*>(z);
@@ -427,7 +442,7 @@ bn_bwd_apply_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ x, con
     }
   }
   for (; r < rows; r += step) {
-    const bf16x8 g0 = ld8(dz + r * C + col), x0 = ld8(x + r * C + col);
+    const bf16x8 g0 = ld8(dz + r * ld_dz + col), x0 = ld8(x + r * C + col);
     if (relu && z && z_bits) {
       one(r, g0, x0, nullptr, (int)reinterpret_cast<const uint8_t*>(z)[r * (C >> 3) + cv]);
     } else if (relu && z) {
@@ -549,28 +564,38 @@ TDL_API int tdl_bn_infer_scale_shift(const float* gamma, const float* beta, cons
 // y = relu?(x*scale + shift (+ residual))
 // mask_out (may be NULL; only meaningful with relu): [rows][C/8] bytes, bit j of byte (r, c/8) = (pre-ReLU value of
 // channel 8*(c/8)+j was > 0).  Pass it as `z` with z_is_bitmask = 1 to the backward entry points.
-TDL_API int tdl_bn_apply(const void* x, const float* scale, const float* shift, const void* residual, void* y,
-                         void* mask_out, int64_t rows, int C, int relu, void* stream) {
+// ldy = elements between consecutive rows of y (>= C, multiple of 8): y may be a channel slice of a wider buffer, which
+// is how concatenations disappear (every ASPP branch normalises straight into its slice).
+TDL_API int tdl_bn_apply_ld(const void* x, const float* scale, const float* shift, const void* residual, void* y,
+                            void* mask_out, int64_t rows, int C, int relu, int64_t ldy, void* stream) {
   TDL_REQUIRE(C > 0 && C % 8 == 0, "C must be a positive multiple of 8");
+  TDL_REQUIRE(ldy >= C && ldy % 8 == 0, "ldy must be a multiple of 8, at least C");
   if (rows == 0) return 0;
   ReduceShape s = apply_shape(rows, C);
   dim3 grid(s.gx, s.gy);
   {
     cudaError_t _le = tdl::launch_pdl(bn_apply_kernel, dim3(grid), dim3(kThreads), 0, (cudaStream_t)stream,
-        (const bf16*)x, scale, shift, (const bf16*)residual, (bf16*)y, (uint8_t*)mask_out, rows, C, s.tx, s.ty, relu);
+        (const bf16*)x, scale, shift, (const bf16*)residual, (bf16*)y, (uint8_t*)mask_out, rows, C, s.tx, s.ty, relu,
+        ldy);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "bn_apply_kernel");
   }
   TDL_LAUNCH_OK("bn_apply_kernel");
   return 0;
 }
+TDL_API int tdl_bn_apply(const void* x, const float* scale, const float* shift, const void* residual, void* y,
+                         void* mask_out, int64_t rows, int C, int relu, void* stream) {
+  return tdl_bn_apply_ld(x, scale, shift, residual, y, mask_out, rows, C, relu, C, stream);
+}
 
 // dbeta/dgamma for this layer (written), optionally also accumulated into acc_* (the flat gradient slots).
-TDL_API int tdl_bn_bwd_reduce(const void* dz, const void* x, const void* z, int z_is_bitmask, const float* scale,
-                              const float* shift, const float* mean, const float* invstd, int64_t rows, int C, int relu,
-                              float* scratch,
-                              int64_t scratch_floats, float* dgamma, float* dbeta, float* acc_dgamma,
-                              float* acc_dbeta, void* stream) {
+// ld_dz = elements between consecutive rows of dz (>= C, multiple of 8): dz may be a channel slice of the gradient of a
+// concat buffer.
+TDL_API int tdl_bn_bwd_reduce_ld(const void* dz, const void* x, const void* z, int z_is_bitmask, const float* scale,
+                                 const float* shift, const float* mean, const float* invstd, int64_t rows, int C,
+                                 int relu, int64_t ld_dz, float* scratch, int64_t scratch_floats, float* dgamma,
+                                 float* dbeta, float* acc_dgamma, float* acc_dbeta, void* stream) {
   TDL_REQUIRE(C > 0 && C % 8 == 0, "C must be a positive multiple of 8");
+  TDL_REQUIRE(ld_dz >= C && ld_dz % 8 == 0, "ld_dz must be a multiple of 8, at least C");
   ReduceShape s = reduce_shape(rows, C, resident_ctas(bn_bwd_partial_kernel, &g_bwd_partial_ctas));
   TDL_REQUIRE(scratch_floats >= (int64_t)s.gx * 2 * C, "scratch too small (see tdl_bn_scratch_floats)");
   cudaStream_t st = (cudaStream_t)stream;
@@ -578,7 +603,7 @@ TDL_API int tdl_bn_bwd_reduce(const void* dz, const void* x, const void* z, int 
   {
     cudaError_t _le = tdl::launch_pdl(bn_bwd_partial_kernel, dim3(grid), dim3(kThreads),
         kThreads * 16 * sizeof(float), st, (const bf16*)dz, (const bf16*)x, (const bf16*)z, scale, shift, mean,
-        invstd, rows, C, s.tx, s.ty, relu, z_is_bitmask, scratch);
+        invstd, rows, C, s.tx, s.ty, relu, z_is_bitmask, scratch, ld_dz);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "bn_bwd_partial_kernel");
   }
   TDL_LAUNCH_OK("bn_bwd_partial_kernel");
@@ -589,6 +614,15 @@ TDL_API int tdl_bn_bwd_reduce(const void* dz, const void* x, const void* z, int 
   }
   TDL_LAUNCH_OK("bn_bwd_finalize_kernel");
   return 0;
+}
+
+TDL_API int tdl_bn_bwd_reduce(const void* dz, const void* x, const void* z, int z_is_bitmask, const float* scale,
+                              const float* shift, const float* mean, const float* invstd, int64_t rows, int C, int relu,
+                              float* scratch,
+                              int64_t scratch_floats, float* dgamma, float* dbeta, float* acc_dgamma,
+                              float* acc_dbeta, void* stream) {
+  return tdl_bn_bwd_reduce_ld(dz, x, z, z_is_bitmask, scale, shift, mean, invstd, rows, C, relu, C, scratch,
+                              scratch_floats, dgamma, dbeta, acc_dgamma, acc_dbeta, stream);
 }
 
 // BatchNorm-backward sums that were already reduced per CTA elsewhere (the data-gradient kernel's epilogue,
@@ -605,21 +639,38 @@ TDL_API int tdl_bn_bwd_finalize_partials(const float* partial, int nparts, int C
   return 0;
 }
 
-TDL_API int tdl_bn_bwd_apply(const void* dz, const void* x, const void* z, int z_is_bitmask, const float* scale,
-                             const float* shift, const float* mean, const float* invstd, const float* dgamma, const float* dbeta,
-                             void* dx, void* dres, int64_t rows, int C, int relu, void* stream) {
+// addend ([rows, C] bf16, may be NULL): added to dx (a second gradient of the BatchNorm's input, e.g. a residual unit's
+// identity shortcut).  mask_by_x != 0: the input x is a ReLU output; dx is zeroed where x == 0 (that ReLU's backward).
+TDL_API int tdl_bn_bwd_apply_ex(const void* dz, const void* x, const void* z, int z_is_bitmask, const float* scale,
+                                const float* shift, const float* mean, const float* invstd, const float* dgamma,
+                                const float* dbeta, void* dx, void* dres, int64_t rows, int C, int relu, int64_t ld_dz,
+                                const void* addend, int mask_by_x, void* stream) {
   TDL_REQUIRE(C > 0 && C % 8 == 0, "C must be a positive multiple of 8");
+  TDL_REQUIRE(ld_dz >= C && ld_dz % 8 == 0, "ld_dz must be a multiple of 8, at least C");
   if (rows == 0) return 0;
   ReduceShape s = apply_shape(rows, C);
   dim3 grid(s.gx, s.gy);
   {
     cudaError_t _le = tdl::launch_pdl(bn_bwd_apply_kernel, dim3(grid), dim3(kThreads), 0, (cudaStream_t)stream,
         (const bf16*)dz, (const bf16*)x, (const bf16*)z, scale, shift, mean, invstd, dbeta, dgamma, 1.f / (float)rows,
-        (bf16*)dx, (bf16*)dres, rows, C, s.tx, s.ty, relu, z_is_bitmask);
+        (bf16*)dx, (bf16*)dres, rows, C, s.tx, s.ty, relu, z_is_bitmask, ld_dz, (const bf16*)addend, mask_by_x);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "bn_bwd_apply_kernel");
   }
   TDL_LAUNCH_OK("bn_bwd_apply_kernel");
   return 0;
+}
+TDL_API int tdl_bn_bwd_apply_ld(const void* dz, const void* x, const void* z, int z_is_bitmask, const float* scale,
+                                const float* shift, const float* mean, const float* invstd, const float* dgamma,
+                                const float* dbeta, void* dx, void* dres, int64_t rows, int C, int relu, int64_t ld_dz,
+                                void* stream) {
+  return tdl_bn_bwd_apply_ex(dz, x, z, z_is_bitmask, scale, shift, mean, invstd, dgamma, dbeta, dx, dres, rows, C, relu,
+                             ld_dz, nullptr, 0, stream);
+}
+TDL_API int tdl_bn_bwd_apply(const void* dz, const void* x, const void* z, int z_is_bitmask, const float* scale,
+                             const float* shift, const float* mean, const float* invstd, const float* dgamma, const float* dbeta,
+                             void* dx, void* dres, int64_t rows, int C, int relu, void* stream) {
+  return tdl_bn_bwd_apply_ld(dz, x, z, z_is_bitmask, scale, shift, mean, invstd, dgamma, dbeta, dx, dres, rows, C, relu,
+                             C, stream);
 }
 
 // ------------------------------------------------------------------------------------------------------------

@@ -38,6 +38,7 @@ struct Comm {
   int emulate;                 // 1: all "peers" live on this GPU and ranks are launched one after another
   float* mc_grad;              // NVLS multicast address of the gradient buckets (nullptr when not available)
   float* mc_param;             // NVLS multicast address of the parameter buckets
+  bf16* wire[kMaxWorld];       // peer-mapped bf16 "wire" copies of the gradient buckets (same element offsets), or null
   unsigned long long timeout_ns;  // how long a CTA waits for a peer before it reports and traps
   int* status;                 // host-mapped: [0] = 1 when a wait timed out, [1..4] = rank, CTA, peer, epoch
 };
@@ -313,6 +314,210 @@ two_shot_kernel(const Comm cm, const StepArgs a) {
   if (threadIdx.x == 0) cm.epoch[blockIdx.x] = epoch;
 }
 
+// ---- bf16 wire format (the fused cast of the north star) ----
+// Gradients are accumulated in fp32 (weight-gradient kernels red.add into the bucket) but cross NVLink as bf16:
+//   phase 0 (local): every rank packs its whole fp32 bucket into its bf16 wire buffer and, in the same pass, clears the
+//                    fp32 bucket for the next step -- peers only ever read the wire copy, so the clear no longer has
+//                    to wait behind the second barrier;
+//   barrier;
+//   phase 1: rank r reduces slice r from every rank's wire copy (16-byte loads = 8 gradients, half the reduce-scatter
+//            bytes of the fp32 path), accumulates in fp32 in rank order, applies 1/N and the optimizer to the fp32 master
+//            slice and stores the updated fp32 weights into every peer's parameter buffer; barrier.
+// Work is split in 8-element vectors; vector v of slice s belongs to global thread (v - s_lo) mod nthr in BOTH phases,
+// so the per-CTA cross-rank barrier covers exactly the data a CTA's peers-with-the-same-index are about to read.
+__device__ __forceinline__ void unpack_bf16x8(const uint4& raw, float* f) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 t = __bfloat1622float2(h[i]);
+    f[2 * i] = t.x;
+    f[2 * i + 1] = t.y;
+  }
+}
+
+__device__ __forceinline__ void wire_slice(const Comm& cm, int64_t n8, int sl, int64_t* lo, int64_t* hi) {
+  const int64_t per = (n8 + cm.world - 1) / cm.world;
+  const int64_t a = per * sl < n8 ? per * sl : n8;
+  *lo = a;
+  *hi = a + per < n8 ? a + per : n8;
+}
+
+template <int U>
+__global__ void __launch_bounds__(kThreads)
+two_shot_wire_kernel(const Comm cm, const StepArgs a, int phases) {
+  uint32_t epoch = cm.epoch[blockIdx.x];
+  const int64_t n8 = a.n / 8;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t nthr = (int64_t)gridDim.x * blockDim.x;
+  if (phases & 1) {
+    float* g = cm.grad[cm.rank] + a.offset;
+    bf16* wr = cm.wire[cm.rank] + a.offset;
+    for (int sl = 0; sl < cm.world; ++sl) {
+      int64_t lo, hi;
+      wire_slice(cm, n8, sl, &lo, &hi);
+      for (int64_t v = lo + tid; v < hi; v += nthr) {
+        const float4 g0 = *reinterpret_cast<const float4*>(g + v * 8);
+        const float4 g1 = *reinterpret_cast<const float4*>(g + v * 8 + 4);
+        __nv_bfloat162 h[4] = {__floats2bfloat162_rn(g0.x, g0.y), __floats2bfloat162_rn(g0.z, g0.w),
+                               __floats2bfloat162_rn(g1.x, g1.y), __floats2bfloat162_rn(g1.z, g1.w)};
+        *reinterpret_cast<uint4*>(wr + v * 8) = *reinterpret_cast<const uint4*>(h);
+        if (a.zero_grad) {
+          *reinterpret_cast<float4*>(g + v * 8) = make_float4(0.f, 0.f, 0.f, 0.f);
+          *reinterpret_cast<float4*>(g + v * 8 + 4) = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+      }
+    }
+    // ragged tail (< 8 elements): read by the last rank's global threads 0..6
+    if (n8 * 8 + tid < a.n) {
+      wr[n8 * 8 + tid] = __float2bfloat16(g[n8 * 8 + tid]);
+      if (a.zero_grad) g[n8 * 8 + tid] = 0.f;
+    }
+    __threadfence_system();
+  }
+  if (!(phases & 2)) return;
+  cross_rank_barrier(cm, ++epoch);  // every rank's wire copy of this bucket is complete
+  const float lr = a.lr_state[0];
+  const float lr_t = a.lr_state[1];
+  const float scale = a.grad_scale / (float)cm.world;
+  int64_t v_lo, v_hi;
+  wire_slice(cm, n8, cm.rank, &v_lo, &v_hi);
+  for (int64_t v0 = v_lo + tid; v0 < v_hi; v0 += nthr * U) {
+    int64_t idx[U];
+    int nvalid = 0;
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      idx[u] = a.offset + (v0 + (int64_t)u * nthr) * 8;
+      if (v0 + (int64_t)u * nthr < v_hi) nvalid = u + 1;
+    }
+    float acc[U][8];
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[u][j] = 0.f;
+#pragma unroll
+    for (int r = 0; r < kMaxWorld; ++r) {
+      if (r < cm.world) {
+        uint4 raw[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u)  // all loads of this peer are issued before the first add
+          raw[u] = u < nvalid ? *reinterpret_cast<const uint4*>(cm.wire[r] + idx[u]) : make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          float f[8];
+          unpack_bf16x8(raw[u], f);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[u][j] += f[j];
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (u >= nvalid) break;
+      const int64_t i = idx[u];
+      float4 w0 = *reinterpret_cast<const float4*>(cm.param[cm.rank] + i);
+      float4 w1 = *reinterpret_cast<const float4*>(cm.param[cm.rank] + i + 4);
+      w0.x = opt_update(a, w0.x, acc[u][0] * scale, i, lr, lr_t);
+      w0.y = opt_update(a, w0.y, acc[u][1] * scale, i + 1, lr, lr_t);
+      w0.z = opt_update(a, w0.z, acc[u][2] * scale, i + 2, lr, lr_t);
+      w0.w = opt_update(a, w0.w, acc[u][3] * scale, i + 3, lr, lr_t);
+      w1.x = opt_update(a, w1.x, acc[u][4] * scale, i + 4, lr, lr_t);
+      w1.y = opt_update(a, w1.y, acc[u][5] * scale, i + 5, lr, lr_t);
+      w1.z = opt_update(a, w1.z, acc[u][6] * scale, i + 6, lr, lr_t);
+      w1.w = opt_update(a, w1.w, acc[u][7] * scale, i + 7, lr, lr_t);
+#pragma unroll
+      for (int r = 0; r < kMaxWorld; ++r) {
+        if (r < cm.world) {
+          *reinterpret_cast<float4*>(cm.param[r] + i) = w0;
+          *reinterpret_cast<float4*>(cm.param[r] + i + 4) = w1;
+        }
+      }
+    }
+  }
+  if (cm.rank == cm.world - 1) {  // ragged tail: owned by the last rank
+    for (int64_t i = a.offset + n8 * 8 + tid; i < a.offset + a.n; i += nthr) {
+      float s = 0.f;
+      for (int r = 0; r < cm.world; ++r) s += __bfloat162float(cm.wire[r][i]);
+      const float w = opt_update(a, cm.param[cm.rank][i], s * scale, i, lr, lr_t);
+      for (int r = 0; r < cm.world; ++r) cm.param[r][i] = w;
+    }
+  }
+  __threadfence_system();
+  cross_rank_barrier(cm, ++epoch);  // every slice has landed everywhere; every wire copy has been read
+  __syncthreads();
+  if (threadIdx.x == 0) cm.epoch[blockIdx.x] = epoch;
+}
+
+// Small buckets with the bf16 wire format: every rank reduces everything (one signal round trip, no second hop).
+__global__ void __launch_bounds__(kThreads)
+one_shot_wire_kernel(const Comm cm, const StepArgs a, int phases) {
+  uint32_t epoch = cm.epoch[blockIdx.x];
+  const int64_t n8 = a.n / 8;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t nthr = (int64_t)gridDim.x * blockDim.x;
+  if (phases & 1) {
+    float* g = cm.grad[cm.rank] + a.offset;
+    bf16* wr = cm.wire[cm.rank] + a.offset;
+    for (int64_t v = tid; v < n8; v += nthr) {
+      const float4 g0 = *reinterpret_cast<const float4*>(g + v * 8);
+      const float4 g1 = *reinterpret_cast<const float4*>(g + v * 8 + 4);
+      __nv_bfloat162 h[4] = {__floats2bfloat162_rn(g0.x, g0.y), __floats2bfloat162_rn(g0.z, g0.w),
+                             __floats2bfloat162_rn(g1.x, g1.y), __floats2bfloat162_rn(g1.z, g1.w)};
+      *reinterpret_cast<uint4*>(wr + v * 8) = *reinterpret_cast<const uint4*>(h);
+      if (a.zero_grad) {
+        *reinterpret_cast<float4*>(g + v * 8) = make_float4(0.f, 0.f, 0.f, 0.f);
+        *reinterpret_cast<float4*>(g + v * 8 + 4) = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    }
+    if (n8 * 8 + tid < a.n) {
+      wr[n8 * 8 + tid] = __float2bfloat16(g[n8 * 8 + tid]);
+      if (a.zero_grad) g[n8 * 8 + tid] = 0.f;
+    }
+    __threadfence_system();
+  }
+  if (!(phases & 2)) return;
+  cross_rank_barrier(cm, ++epoch);
+  const float lr = a.lr_state[0];
+  const float lr_t = a.lr_state[1];
+  const float scale = a.grad_scale / (float)cm.world;
+  float* out = cm.param[cm.rank];
+  for (int64_t v = tid; v < n8; v += nthr) {
+    const int64_t i = a.offset + v * 8;
+    uint4 raw[kMaxWorld];
+#pragma unroll
+    for (int r = 0; r < kMaxWorld; ++r)
+      raw[r] = r < cm.world ? *reinterpret_cast<const uint4*>(cm.wire[r] + i) : make_uint4(0u, 0u, 0u, 0u);
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int r = 0; r < kMaxWorld; ++r) {
+      if (r < cm.world) {
+        float f[8];
+        unpack_bf16x8(raw[r], f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += f[j];
+      }
+    }
+    float4 w0 = *reinterpret_cast<const float4*>(out + i), w1 = *reinterpret_cast<const float4*>(out + i + 4);
+    w0.x = opt_update(a, w0.x, acc[0] * scale, i, lr, lr_t);
+    w0.y = opt_update(a, w0.y, acc[1] * scale, i + 1, lr, lr_t);
+    w0.z = opt_update(a, w0.z, acc[2] * scale, i + 2, lr, lr_t);
+    w0.w = opt_update(a, w0.w, acc[3] * scale, i + 3, lr, lr_t);
+    w1.x = opt_update(a, w1.x, acc[4] * scale, i + 4, lr, lr_t);
+    w1.y = opt_update(a, w1.y, acc[5] * scale, i + 5, lr, lr_t);
+    w1.z = opt_update(a, w1.z, acc[6] * scale, i + 6, lr, lr_t);
+    w1.w = opt_update(a, w1.w, acc[7] * scale, i + 7, lr, lr_t);
+    *reinterpret_cast<float4*>(out + i) = w0;
+    *reinterpret_cast<float4*>(out + i + 4) = w1;
+  }
+  for (int64_t i = a.offset + n8 * 8 + tid; i < a.offset + a.n; i += nthr) {
+    float s = 0.f;
+    for (int r = 0; r < cm.world; ++r) s += __bfloat162float(cm.wire[r][i]);
+    out[i] = opt_update(a, out[i], s * scale, i, lr, lr_t);
+  }
+  cross_rank_barrier(cm, ++epoch);  // all peers have finished reading my wire copy
+  __syncthreads();
+  if (threadIdx.x == 0) cm.epoch[blockIdx.x] = epoch;
+}
+
 // ---- NVLS: the reduction happens inside NVSwitch, the all-gather is one multicast store ----
 // multimem.ld_reduce on the multicast address returns the sum over every GPU's copy of the addressed gradient
 // (reduced in the switch, fp32), multimem.st writes the updated weights into every GPU's parameter bucket at once.
@@ -501,6 +706,13 @@ TDL_API int tdl_p2p_comm_set_multicast(void* comm, void* mc_grad, void* mc_param
   c->mc_param = (float*)mc_param;
   return 0;
 }
+// Attach the peer-mapped bf16 wire buffers (index = rank; same element offsets as the gradient buckets).
+TDL_API int tdl_p2p_comm_set_wire(void* comm, void** wire_ptrs) {
+  Comm* c = (Comm*)comm;
+  TDL_REQUIRE(c != nullptr && wire_ptrs != nullptr, "null communicator / table");
+  for (int r = 0; r < c->world; ++r) c->wire[r] = (bf16*)wire_ptrs[r];
+  return 0;
+}
 TDL_API int tdl_p2p_comm_destroy(void* comm) {
   auto it = g_status_host().find((Comm*)comm);
   if (it != g_status_host().end()) {
@@ -546,6 +758,39 @@ TDL_API int tdl_p2p_fused_step(void* comm, int64_t offset, int64_t n, int mode, 
   else if (mode == 4) nvls_kernel<8><<<blocks, kThreads, 0, st>>>(*cm, s);
   else two_shot_kernel<<<blocks, kThreads, 0, st>>>(*cm, s);
   TDL_LAUNCH_OK("p2p fused step");
+  return 0;
+}
+
+// Same fused step with the gradients crossing NVLink as bf16 (fp32 buckets are packed into the wire buffers and cleared
+// by the kernel's first phase).  mode: 0 = by size, 1 = one-shot, 2 = two-shot.  kind: 1 = SGD-momentum, 2 = Adam.
+// phases: 3 = pack + reduce (normal use); 1 / 2 run one phase only (single-GPU emulation launches every rank's phase 1
+// before any phase 2, because its "ranks" cannot wait for each other).
+TDL_API int tdl_p2p_fused_step_wire(void* comm, int64_t offset, int64_t n, int mode, int kind, int zero_grad,
+                                    float* m1, float* m2, const float* lr_state, float a, float b, float c,
+                                    float grad_scale, int max_blocks, int phases, void* stream) {
+  Comm* cm = (Comm*)comm;
+  TDL_REQUIRE(cm != nullptr, "null communicator");
+  TDL_REQUIRE(cm->wire[cm->rank] != nullptr, "no wire buffers attached (tdl_p2p_comm_set_wire)");
+  TDL_REQUIRE(offset % 8 == 0, "bucket offsets must be multiples of 8 elements");
+  TDL_REQUIRE(kind == kSgdMomentum || kind == kAdam, "wire format: SGD-momentum or Adam");
+  TDL_REQUIRE(phases >= 1 && phases <= 3, "phases is 1, 2 or 3");
+  if (n <= 0) return 0;
+  StepArgs s;
+  s.offset = offset; s.n = n; s.kind = kind; s.grad_is_bf16 = 0; s.zero_grad = zero_grad;
+  s.m1 = m1; s.m2 = m2; s.lr_state = lr_state; s.a = a; s.b = b; s.c = c; s.grad_scale = grad_scale;
+  if (mode == 0) mode = (n * 4 <= (1 << 19)) ? 1 : 2;
+  // the grid must not depend on `phases`: both phases use the same (CTA, thread) -> vector assignment
+  int64_t work = mode == 1 ? n / 8 : n / 8 / cm->world;
+  int blocks = (int)cdiv(work, (int64_t)kThreads * 2);
+  if (max_blocks <= 0) max_blocks = 128;
+  if (max_blocks > kMaxBlocks) max_blocks = kMaxBlocks;
+  if (max_blocks > num_sms()) max_blocks = num_sms();
+  if (blocks > max_blocks) blocks = max_blocks;
+  if (blocks < 1) blocks = 1;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (mode == 1) one_shot_wire_kernel<<<blocks, kThreads, 0, st>>>(*cm, s, phases);
+  else two_shot_wire_kernel<2><<<blocks, kThreads, 0, st>>>(*cm, s, phases);
+  TDL_LAUNCH_OK("p2p fused step (bf16 wire)");
   return 0;
 }
 

@@ -105,10 +105,14 @@ maxpool_bwd_kernel(const bf16* __restrict__ dy, const uint8_t* __restrict__ idx,
 // Compile-time window/stride variants, one thread per (pixel, 8 channels) with blockIdx.y = image: no 64-bit index
 // arithmetic or runtime-stride divisions (the generic kernels above spend most of their issue slots on those), all window loads in flight
 // at once.  Used for the 3x3 stride-2 pool of the ResNet root (core/resnet.py:241).
-template <int K, int S>
+// kStats: the kernel also leaves per-CTA partial (sum, sum of squares) of the pooled values per channel in
+// stats[cta][2][C] -- the batch statistics of the `postnorm` BatchNorm that follows the root pool in the reference
+// network (core/resnet.py:241-242), so that BatchNorm needs no statistics pass of its own.  Requires
+// kThreads % (C/8) == 0 (every thread of a CTA then keeps the same channel group for the whole CTA).
+template <int K, int S, bool kStats = false>
 __global__ void __launch_bounds__(kThreads)
 maxpool_fwd_rows_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, uint8_t* __restrict__ idx, int H, int W,
-                        int C, int P, int Q, int pad_h, int pad_w) {
+                        int C, int P, int Q, int pad_h, int pad_w, float* __restrict__ stats = nullptr) {
   ptx::pdl_trigger();
   ptx::pdl_wait();
   const int c8 = C >> 3;
@@ -116,6 +120,11 @@ maxpool_fwd_rows_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, uint8_
   const bf16* xn = x + (int64_t)n * H * W * C;
   const int64_t orow = (int64_t)n * P * Q * C;
   const int i = blockIdx.x * kThreads + threadIdx.x;  // (p, q, cv) inside image n, 32-bit arithmetic only
+  float st_s[8], st_q[8];
+  if constexpr (kStats) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) st_s[j] = st_q[j] = 0.f;
+  }
   if (i < P * Q * c8) {
     const int pq = i / c8;
     const int cv = i - pq * c8;
@@ -151,6 +160,26 @@ maxpool_fwd_rows_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, uint8_
     packed.x = (uint32_t)arg[0] | ((uint32_t)arg[1] << 8) | ((uint32_t)arg[2] << 16) | ((uint32_t)arg[3] << 24);
     packed.y = (uint32_t)arg[4] | ((uint32_t)arg[5] << 8) | ((uint32_t)arg[6] << 16) | ((uint32_t)arg[7] << 24);
     *reinterpret_cast<uint2*>(idx + orow + (int64_t)i * 8) = packed;
+    if constexpr (kStats) {  // the maximum of bf16 values is a bf16 value: these ARE the stored numbers
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { st_s[j] = best[j]; st_q[j] = best[j] * best[j]; }
+    }
+  }
+  if constexpr (kStats) {
+    // thread t owns channel group t % c8 (kThreads % c8 == 0): fold the kThreads / c8 pixel slots per group
+    __shared__ float sm[kThreads * 16];
+    float* mine = sm + threadIdx.x * 16;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { mine[j] = st_s[j]; mine[8 + j] = st_q[j]; }
+    __syncthreads();
+    const int slots = kThreads / c8;
+    float* row = stats + ((size_t)blockIdx.y * gridDim.x + blockIdx.x) * 2 * C;
+    for (int e = threadIdx.x; e < c8 * 16; e += kThreads) {
+      const int cv = e >> 4, val = e & 15;
+      float acc = 0.f;
+      for (int t = 0; t < slots; ++t) acc += sm[(t * c8 + cv) * 16 + val];
+      row[(size_t)(val >> 3) * C + cv * 8 + (val & 7)] = acc;
+    }
   }
 }
 
@@ -469,7 +498,8 @@ __device__ __forceinline__ UpCoord up_coord(int o, int in, int out) {
 
 template <typename T>
 __global__ void __launch_bounds__(kThreads)
-upsample_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int N, int H, int W, int C, int OH, int OW) {
+upsample_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int N, int H, int W, int C, int OH, int OW,
+                    int64_t ldy) {  // ldy: elements between consecutive output pixels (C, or a wider concat buffer's)
   ptx::pdl_trigger();
   ptx::pdl_wait();
   const int64_t total = (int64_t)N * OH * OW * C;
@@ -487,13 +517,14 @@ upsample_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int N, int H, in
     const float br = to_f<T>(base[((int64_t)cy.hi * W + cx.hi) * C]);
     const float top = tl + (tr - tl) * cx.w;
     const float bot = bl + (br - bl) * cx.w;
-    y[i] = from_f<T>(top + (bot - top) * cy.w);
+    y[(i / C) * ldy + c] = from_f<T>(top + (bot - top) * cy.w);
   }
 }
 
 template <typename T>
 __global__ void __launch_bounds__(kThreads)
-upsample_bwd_kernel(const T* __restrict__ dy, float* __restrict__ dx, int N, int H, int W, int C, int OH, int OW) {
+upsample_bwd_kernel(const T* __restrict__ dy, float* __restrict__ dx, int N, int H, int W, int C, int OH, int OW,
+                    int64_t ld_dy) {
   ptx::pdl_trigger();
   ptx::pdl_wait();
   const int64_t total = (int64_t)N * OH * OW * C;
@@ -504,7 +535,7 @@ upsample_bwd_kernel(const T* __restrict__ dy, float* __restrict__ dx, int N, int
     const int oy = (int)(t % OH);
     const int n = (int)(t / OH);
     const UpCoord cy = up_coord(oy, H, OH), cx = up_coord(ox, W, OW);
-    const float g = to_f<T>(dy[i]);
+    const float g = to_f<T>(dy[(i / C) * ld_dy + c]);
     float* base = dx + (int64_t)n * H * W * C + c;
     atomicAdd(base + ((int64_t)cy.lo * W + cx.lo) * C, g * (1.f - cy.w) * (1.f - cx.w));
     atomicAdd(base + ((int64_t)cy.lo * W + cx.hi) * C, g * (1.f - cy.w) * cx.w);
@@ -527,9 +558,9 @@ TDL_API int tdl_maxpool_fwd(const void* x, void* y, void* idx_u8, int N, int H, 
   if (work == 0) return 0;
   if (k == 3 && stride == 2 && N <= 65535 && (int64_t)P * Q * C < (1ll << 31))
     {
-      cudaError_t _le = tdl::launch_pdl(maxpool_fwd_rows_kernel<3, 2>,
+      cudaError_t _le = tdl::launch_pdl(maxpool_fwd_rows_kernel<3, 2, false>,
           dim3(dim3((unsigned)cdiv((int64_t)P * Q * (C / 8), kThreads), N)), dim3(kThreads), 0, (cudaStream_t)stream,
-          (const bf16*)x, (bf16*)y, (uint8_t*)idx_u8, H, W, C, P, Q, pad_h, pad_w);
+          (const bf16*)x, (bf16*)y, (uint8_t*)idx_u8, H, W, C, P, Q, pad_h, pad_w, (float*)nullptr);
       if (_le != cudaSuccess) return tdl::cuda_fail(_le, "maxpool_fwd_rows_kernel");
     }
   else
@@ -540,6 +571,27 @@ TDL_API int tdl_maxpool_fwd(const void* x, void* y, void* idx_u8, int N, int H, 
       if (_le != cudaSuccess) return tdl::cuda_fail(_le, "maxpool_fwd_kernel");
     }
   TDL_LAUNCH_OK("maxpool_fwd_kernel");
+  return 0;
+}
+
+// 3x3 stride-2 max-pool that also leaves the partial BatchNorm statistics of its output: stats_partial is
+// [*nparts][2][C] fp32 with *nparts = N * ceil(P*Q*(C/8) / 256) rows (tdl_maxpool_stats_rows); feed both to
+// tdl_bn_finalize_partials.  Needs 256 % (C/8) == 0.
+TDL_API int tdl_maxpool_stats_rows(int N, int C, int P, int Q) {
+  return N * (int)cdiv((int64_t)P * Q * (C / 8), kThreads);
+}
+TDL_API int tdl_maxpool_fwd_stats(const void* x, void* y, void* idx_u8, int N, int H, int W, int C, int P, int Q,
+                                  int pad_h, int pad_w, float* stats_partial, int* nparts, void* stream) {
+  TDL_REQUIRE(C % 8 == 0 && kThreads % (C / 8) == 0, "C/8 must divide 256");
+  TDL_REQUIRE(N >= 1 && N <= 65535 && (int64_t)P * Q * C < (1ll << 31), "shape out of range for the fused pool");
+  TDL_REQUIRE(stats_partial != nullptr && nparts != nullptr, "statistics buffers required");
+  const unsigned gx = (unsigned)cdiv((int64_t)P * Q * (C / 8), kThreads);
+  cudaError_t e = tdl::launch_pdl(maxpool_fwd_rows_kernel<3, 2, true>, dim3(gx, N), dim3(kThreads), 0,
+                                  (cudaStream_t)stream, (const bf16*)x, (bf16*)y, (uint8_t*)idx_u8, H, W, C, P, Q,
+                                  pad_h, pad_w, stats_partial);
+  if (e != cudaSuccess) return tdl::cuda_fail(e, "maxpool_fwd_rows_kernel<stats>");
+  TDL_LAUNCH_OK("maxpool_fwd_rows_kernel<stats>");
+  *nparts = (int)gx * N;
   return 0;
 }
 
@@ -649,45 +701,58 @@ TDL_API int tdl_depthwise_bwd(const void* x, const float* w, const void* dy, con
   return 0;
 }
 
-TDL_API int tdl_upsample_fwd(const void* x, void* y, int N, int H, int W, int C, int OH, int OW, int is_bf16,
-                             void* stream) {
+// ldy: elements between consecutive output pixels of y (>= C): y may be a channel slice of a wider buffer, so the
+// result lands where a concat would have copied it.
+TDL_API int tdl_upsample_fwd_ld(const void* x, void* y, int N, int H, int W, int C, int OH, int OW, int64_t ldy,
+                                int is_bf16, void* stream) {
+  TDL_REQUIRE(ldy >= C, "ldy must be at least C");
   const int64_t total = (int64_t)N * OH * OW * C;
   if (total == 0) return 0;
   if (is_bf16)
     {
       cudaError_t _le = tdl::launch_pdl(upsample_fwd_kernel<bf16>, dim3(grid_for(total)), dim3(kThreads), 0,
-          (cudaStream_t)stream, (const bf16*)x, (bf16*)y, N, H, W, C, OH, OW);
+          (cudaStream_t)stream, (const bf16*)x, (bf16*)y, N, H, W, C, OH, OW, ldy);
       if (_le != cudaSuccess) return tdl::cuda_fail(_le, "upsample_fwd_kernel");
     }
   else
     {
       cudaError_t _le = tdl::launch_pdl(upsample_fwd_kernel<float>, dim3(grid_for(total)), dim3(kThreads), 0,
-          (cudaStream_t)stream, (const float*)x, (float*)y, N, H, W, C, OH, OW);
+          (cudaStream_t)stream, (const float*)x, (float*)y, N, H, W, C, OH, OW, ldy);
       if (_le != cudaSuccess) return tdl::cuda_fail(_le, "upsample_fwd_kernel");
     }
   TDL_LAUNCH_OK("upsample_fwd_kernel");
   return 0;
 }
 
-// dx (fp32, caller-zeroed) += scatter of dy through the same interpolation weights
-TDL_API int tdl_upsample_bwd(const void* dy, float* dx, int N, int H, int W, int C, int OH, int OW, int is_bf16,
+TDL_API int tdl_upsample_fwd(const void* x, void* y, int N, int H, int W, int C, int OH, int OW, int is_bf16,
                              void* stream) {
+  return tdl_upsample_fwd_ld(x, y, N, H, W, C, OH, OW, C, is_bf16, stream);
+}
+
+// dx (fp32, caller-zeroed) += scatter of dy through the same interpolation weights; ld_dy as ldy above
+TDL_API int tdl_upsample_bwd_ld(const void* dy, float* dx, int N, int H, int W, int C, int OH, int OW, int64_t ld_dy,
+                                int is_bf16, void* stream) {
+  TDL_REQUIRE(ld_dy >= C, "ld_dy must be at least C");
   const int64_t total = (int64_t)N * OH * OW * C;
   if (total == 0) return 0;
   if (is_bf16)
     {
       cudaError_t _le = tdl::launch_pdl(upsample_bwd_kernel<bf16>, dim3(grid_for(total)), dim3(kThreads), 0,
-          (cudaStream_t)stream, (const bf16*)dy, dx, N, H, W, C, OH, OW);
+          (cudaStream_t)stream, (const bf16*)dy, dx, N, H, W, C, OH, OW, ld_dy);
       if (_le != cudaSuccess) return tdl::cuda_fail(_le, "upsample_bwd_kernel");
     }
   else
     {
       cudaError_t _le = tdl::launch_pdl(upsample_bwd_kernel<float>, dim3(grid_for(total)), dim3(kThreads), 0,
-          (cudaStream_t)stream, (const float*)dy, dx, N, H, W, C, OH, OW);
+          (cudaStream_t)stream, (const float*)dy, dx, N, H, W, C, OH, OW, ld_dy);
       if (_le != cudaSuccess) return tdl::cuda_fail(_le, "upsample_bwd_kernel");
     }
   TDL_LAUNCH_OK("upsample_bwd_kernel");
   return 0;
+}
+TDL_API int tdl_upsample_bwd(const void* dy, float* dx, int N, int H, int W, int C, int OH, int OW, int is_bf16,
+                             void* stream) {
+  return tdl_upsample_bwd_ld(dy, dx, N, H, W, C, OH, OW, C, is_bf16, stream);
 }
 
 // ------------------------------------------------------------------------------------------

@@ -87,11 +87,53 @@ int tdl_bn_bwd_reduce(const void* dz, const void* x, const void* z, int z_is_bit
                       float* acc_dbeta, void* stream);
 int tdl_bn_bwd_finalize_partials(const float* partial, int nparts, int C, float* dgamma, float* dbeta,
                                  float* acc_dgamma, float* acc_dbeta, void* stream);
+/* leading-dimension / fused forms: y, dz may be channel slices of wider buffers (row pitch ld >= C);
+ * tdl_bn_bwd_apply_ex also adds `addend` (a second gradient of the BatchNorm's input: the identity shortcut of a residual
+ * unit) and, with mask_by_x, applies the ReLU backward of the input tensor itself (core/resnet.py:71-87,126-148) */
+int tdl_bn_apply_ld(const void* x, const float* scale, const float* shift, const void* residual, void* y,
+                    void* mask_out, int64_t rows, int C, int relu, int64_t ldy, void* stream);
+int tdl_bn_bwd_reduce_ld(const void* dz, const void* x, const void* z, int z_is_bitmask, const float* scale,
+                         const float* shift, const float* mean, const float* invstd, int64_t rows, int C, int relu,
+                         int64_t ld_dz, float* scratch, int64_t scratch_floats, float* dgamma, float* dbeta,
+                         float* acc_dgamma, float* acc_dbeta, void* stream);
+int tdl_bn_bwd_apply_ld(const void* dz, const void* x, const void* z, int z_is_bitmask, const float* scale,
+                        const float* shift, const float* mean, const float* invstd, const float* dgamma,
+                        const float* dbeta, void* dx, void* dres, int64_t rows, int C, int relu, int64_t ld_dz,
+                        void* stream);
+int tdl_bn_bwd_apply_ex(const void* dz, const void* x, const void* z, int z_is_bitmask, const float* scale,
+                        const float* shift, const float* mean, const float* invstd, const float* dgamma,
+                        const float* dbeta, void* dx, void* dres, int64_t rows, int C, int relu, int64_t ld_dz,
+                        const void* addend, int mask_by_x, void* stream);
+/* one-launch forms with the statistics finalize folded in (thread-block clusters + DSMEM; measured slower, opt-in) and
+ * the halves of the two-launch forms */
+int tdl_bn_apply_fused(const void* x, const float* partial, int nparts, int64_t stat_rows, const float* gamma,
+                       const float* beta, float* running_mean, float* running_var, float decay, float eps, float* mean,
+                       float* invstd, float* scale, float* shift, const void* residual, void* y, void* mask_out,
+                       int64_t rows, int C, int relu, void* stream);
+int tdl_bn_partial_stats(const void* x, int64_t rows, int C, float* scratch, int64_t scratch_floats, int* nparts,
+                         void* stream);
+int tdl_bn_bwd_partial(const void* dz, const void* x, const void* z, int z_is_bitmask, const float* scale,
+                       const float* shift, const float* mean, const float* invstd, int64_t rows, int C, int relu,
+                       float* scratch, int64_t scratch_floats, int* nparts, void* stream);
+int tdl_bn_bwd_apply_fused(const void* dz, const void* x, const void* z, int z_is_bitmask, const float* scale,
+                           const float* shift, const float* mean, const float* invstd, const float* partial, int nparts,
+                           float* dgamma, float* dbeta, float* acc_dgamma, float* acc_dbeta, void* dx, void* dres,
+                           int64_t rows, int C, int relu, void* stream);
+/* upsample into / out of a channel slice (row pitch ld >= C) */
+int tdl_upsample_fwd_ld(const void* x, void* y, int N, int H, int W, int C, int OH, int OW, int64_t ldy, int is_bf16,
+                        void* stream);
+int tdl_upsample_bwd_ld(const void* dy, float* dx, int N, int H, int W, int C, int OH, int OW, int64_t ld_dy,
+                        int is_bf16, void* stream);
 int tdl_bn_bwd_apply(const void* dz, const void* x, const void* z, int z_is_bitmask, const float* scale,
                      const float* shift, const float* mean, const float* invstd, const float* dgamma,
                      const float* dbeta, void* dx, void* dres, int64_t rows, int C, int relu, void* stream);
 
 /* ---- spatial ops (reference: core/resnet.py:241,246-248,464-465; core/layers.py:34-42,82-109) ---- */
+/* 3x3 / stride-2 max-pool fused with the partial BatchNorm statistics of its output (the reference's pool1 ->
+ * postnorm, core/resnet.py:241-242): stats_partial [*nparts][2][C], rows = tdl_maxpool_stats_rows(); 256 % (C/8) == 0 */
+int tdl_maxpool_stats_rows(int N, int C, int P, int Q);
+int tdl_maxpool_fwd_stats(const void* x, void* y, void* idx_u8, int N, int H, int W, int C, int P, int Q, int pad_h,
+                          int pad_w, float* stats_partial, int* nparts, void* stream);
 int tdl_maxpool_fwd(const void* x, void* y, void* idx_u8, int N, int H, int W, int C, int P, int Q, int k, int stride,
                     int pad_h, int pad_w, void* stream);
 int tdl_maxpool_bwd(const void* dy, const void* idx_u8, void* dx, int N, int H, int W, int C, int P, int Q, int k,
@@ -216,6 +258,13 @@ int tdl_p2p_comm_create(int world, int rank, void** grad_ptrs, void** param_ptrs
  * epoch) and works after the trap has poisoned the CUDA context */
 int tdl_p2p_comm_set_timeout(void* comm, double seconds);
 int tdl_p2p_comm_status(void* comm, int* out5);
+/* bf16 wire format: gradients accumulate in fp32 buckets but cross NVLink as bf16 (the cast is fused into the bucket
+ * kernel: phase 1 packs + clears the fp32 bucket, phase 2 reduces the peers' bf16 copies in fp32 and runs the optimizer).
+ * wire_ptrs[rank] = peer-mapped bf16 buffers with the gradient buckets' element offsets. */
+int tdl_p2p_comm_set_wire(void* comm, void** wire_ptrs);
+int tdl_p2p_fused_step_wire(void* comm, int64_t offset, int64_t n, int mode, int kind, int zero_grad, float* m1,
+                            float* m2, const float* lr_state, float a, float b, float c, float grad_scale,
+                            int max_blocks, int phases, void* stream);
 int tdl_p2p_comm_set_multicast(void* comm, void* mc_grad, void* mc_param); /* NVLS multicast addresses, mode 3 */
 int tdl_p2p_comm_destroy(void* comm);
 int tdl_p2p_broadcast(void* comm, int src, int64_t offset, int64_t n, int max_blocks, void* stream); /* param mirror */

@@ -252,17 +252,187 @@ def sweep():
     comm.close(); gbuf.close(); pbuf.close()
 
 
+def graph_timed(fn, reps, replays=5):
+    """Device time of ONE call of `fn`, measured on `reps` back-to-back calls captured in a CUDA graph and replayed:
+    the ranks are kept in step by the kernels' own cross-rank barriers, so neither the host's launch cost nor the
+    launch skew between the rank processes is in the number (an eager loop measures mostly those below ~1 MiB).
+    Median over `replays` replays of (graph time / reps), max over ranks.  Falls back to an eager back-to-back loop if
+    `fn` cannot be captured."""
+    torch.cuda.synchronize()
+    dist.barrier()
+    g = None
+    side = torch.cuda.Stream()
+    try:
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(2):
+                fn()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        dist.barrier()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            for _ in range(reps):
+                fn()
+    except Exception:  # noqa: BLE001
+        g = None
+    torch.cuda.synchronize()
+    dist.barrier()
+
+    def run():
+        if g is not None:
+            g.replay()
+        else:
+            for _ in range(reps):
+                fn()
+
+    for _ in range(2):
+        run()
+    ts = []
+    for _ in range(replays):
+        torch.cuda.synchronize()
+        dist.barrier()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        run()
+        e.record()
+        torch.cuda.synchronize()
+        ts.append(group.max_over_ranks(s.elapsed_time(e)) / reps)
+    ts.sort()
+    return ts[len(ts) // 2], g is not None
+
+
+def sweep2():
+    """BASELINE config 5, graph-timed: fused all-reduce + optimizer, 1 KiB .. 1 GiB, {fp32, bf16 wire} x {SGD-momentum,
+    Adam} x {one-shot, two-shot} (+ NVLS fp32 where the fabric exposes multicast) next to ncclAllReduce alone and
+    ncclAllReduce + a separate fused optimizer kernel.  Sizes are bytes of fp32 GRADIENT (S); the NVLink roofline of the
+    two-shot path is 2 (W-1)/W S / link bandwidth (fp32 wire) or (W-1)/W 1.5 S (bf16 wire: half the reduce-scatter
+    bytes, fp32 weights back)."""
+    sizes = [1 << k for k in range(10, 31, 2)] + [(32 << 20), 51_114_064 * 2, 167_256_100]
+    sizes = sorted(set(int(x) // 32 * 32 for x in sizes if x >= 1024))
+    maxn = max(sizes) // 4
+    use_mc = os.environ.get("TDL_SWEEP_NVLS", "1") == "1"
+    try:
+        gbuf = SymmetricBuffer(maxn * 4, multicast=use_mc)
+        pbuf = SymmetricBuffer(maxn * 4, multicast=use_mc)
+    except Exception:  # noqa: BLE001
+        gbuf, pbuf = SymmetricBuffer(maxn * 4), SymmetricBuffer(maxn * 4)
+    wbuf = SymmetricBuffer(maxn * 2)
+    comm = P2PComm(gbuf, pbuf)
+    comm.set_wire(wbuf)
+    m1, m2 = torch.zeros(maxn, device="cuda"), torch.zeros(maxn, device="cuda")
+    lr_state = torch.tensor([1e-3, 1e-3], device="cuda")
+    gt = gbuf.tensor()
+    gt.normal_()
+    emit(test="sweep2_setup", nvls=bool(comm.has_multicast), sizes=len(sizes))
+    for nbytes in sizes:
+        n = nbytes // 4
+        reps = 20 if nbytes <= (16 << 20) else (8 if nbytes <= (256 << 20) else 4)
+        res = {"bytes": nbytes, "reps": reps}
+        blocks_for = (lambda mode: 32 if mode == 1 else 128)
+        for kind, kname in ((1, "sgdm"), (2, "adam")):
+            kw = dict(kind=kind, m1=m1, m2=m2 if kind == 2 else None, lr_state=lr_state, a=0.9,
+                      b=(0.0 if kind == 1 else 0.999), c=(0.0 if kind == 1 else 1e-8))
+            for mode in (1, 2):
+                if mode == 1 and nbytes > (16 << 20):
+                    continue
+                if mode == 2 and nbytes < (64 << 10):
+                    continue
+                t, graphed = graph_timed(lambda: comm.fused_step(0, n, grad_is_bf16=False, zero_grad=False, mode=mode,
+                                                                 max_blocks=blocks_for(mode), **kw), reps)
+                res[f"fp32_{kname}_mode{mode}_us"] = t * 1e3
+                t, _ = graph_timed(lambda: comm.fused_step_wire(0, n, zero_grad=False, mode=mode,
+                                                                max_blocks=blocks_for(mode), **kw), reps)
+                res[f"bf16_{kname}_mode{mode}_us"] = t * 1e3
+                res["graphed"] = graphed
+            if comm.has_multicast and nbytes >= (1 << 20) and n % 4 == 0:
+                # few CTAs with 4 switch-reduced loads in flight each: more CTAs only queue up inside the switch
+                # (profiles/runs/p2p_nvls_sweep_8gpu.jsonl: 32 CTAs 2.26 ms, 128 CTAs 3.3 ms at 1 GiB)
+                for nb in (32, 64):
+                    t, _ = graph_timed(lambda: comm.fused_step(0, n, grad_is_bf16=False, zero_grad=False, mode=3,
+                                                               max_blocks=nb, **kw), reps)
+                    res[f"nvls_b{nb}_{kname}_us"] = t * 1e3
+                res[f"nvls_{kname}_us"] = min(res[f"nvls_b32_{kname}_us"], res[f"nvls_b64_{kname}_us"])
+        g2, p2, mm = gt[:n], torch.zeros(n, device="cuda"), torch.zeros(n, device="cuda")
+
+        def nccl_path():
+            dist.all_reduce(g2)
+            O.sgd_momentum_flat(p2, g2, mm, None, lr_state, 0.9, 0.0, 1.0 / W, False)
+
+        res["nccl_plus_sgdm_us"] = graph_timed(nccl_path, reps)[0] * 1e3
+        t, nccl_graphed = graph_timed(lambda: dist.all_reduce(g2), reps)
+        res["nccl_allreduce_us"], res["nccl_graphed"] = t * 1e3, nccl_graphed
+        best_fp32 = min(v for k, v in res.items() if k.startswith("fp32_sgdm"))
+        best_bf16 = min(v for k, v in res.items() if k.startswith("bf16_sgdm"))
+        best_any = min(v for k, v in res.items() if k.endswith("_us") and not k.startswith("nccl"))
+        wire_fp32 = 2.0 * (W - 1) / W * nbytes
+        wire_bf16 = 1.5 * (W - 1) / W * nbytes
+        res.update(best_fp32_sgdm_us=best_fp32, best_bf16_sgdm_us=best_bf16, best_us=best_any,
+                   frac_of_900_fp32=wire_fp32 / best_fp32 / 1e3 / 900.0, frac_of_900_bf16=wire_bf16 / best_bf16 / 1e3 / 900.0,
+                   busbw_equiv_gbs=wire_fp32 / best_any / 1e3, frac_of_900_busbw_equiv=wire_fp32 / best_any / 1e3 / 900.0,
+                   nccl_busbw_gbs=wire_fp32 / res["nccl_allreduce_us"] / 1e3,
+                   speedup_vs_nccl_allreduce_alone=res["nccl_allreduce_us"] / best_any,
+                   speedup_vs_nccl_plus_opt=res["nccl_plus_sgdm_us"] / best_any)
+        emit(test="sweep2", **res)
+        del g2, p2, mm
+    comm.close(); gbuf.close(); pbuf.close(); wbuf.close()
+
+
+def wire():
+    """bf16 wire format on real peers: fused step vs the ordered fp32 sum of the bf16-rounded gradients."""
+    for n in (256, 1000 + 3, 65536 + 5, 1 << 20, (1 << 24) + 7):
+        for mode in (1, 2):
+            for kind in (1, 2):
+                npad = (n + 15) // 8 * 8
+                gbuf, pbuf, wbuf = SymmetricBuffer(npad * 4), SymmetricBuffer(npad * 4), SymmetricBuffer(npad * 2)
+                comm = P2PComm(gbuf, pbuf)
+                comm.set_wire(wbuf)
+                torch.manual_seed(1000 + R)
+                g = torch.randn(n, device="cuda")
+                torch.manual_seed(5)
+                p0 = torch.randn(n, device="cuda")
+                gbuf.tensor()[:n].copy_(g)
+                pbuf.tensor()[:n].copy_(p0)
+                m1, m2 = torch.zeros(npad, device="cuda"), torch.zeros(npad, device="cuda")
+                lr_state = torch.tensor([0.1, 0.05], device="cuda")
+                torch.cuda.synchronize()
+                dist.barrier()
+                comm.fused_step_wire(0, n, kind=kind, zero_grad=True, m1=m1, m2=m2, lr_state=lr_state, a=0.9,
+                                     b=(1e-4 if kind == 1 else 0.999), c=1e-8, mode=mode)
+                torch.cuda.synchronize()
+                allg = [torch.empty_like(g) for _ in range(W)]
+                dist.all_gather(allg, g)
+                gm = torch.zeros_like(g)
+                for t in allg:
+                    gm = gm + t.bfloat16().float()
+                gm = gm * (1.0 / W)
+                ref = (p0 - 0.1 * (gm + 1e-4 * p0)) if kind == 1 else (p0 - 0.05 * (0.1 * gm) / ((0.001 * gm * gm).sqrt() + 1e-8))
+                got = pbuf.tensor()[:n]
+                err = rel_err(got, ref)
+                chk = got.clone()
+                dist.broadcast(chk, 0)
+                same = torch.tensor([float(torch.equal(chk, got))], device="cuda")
+                dist.all_reduce(same, op=dist.ReduceOp.MIN)
+                zeroed = float(gbuf.tensor()[:n].abs().max()) == 0.0
+                emit(test="wire", n=n, mode=mode, kind=kind, rel_err=err, mirrors_identical=bool(same.item()),
+                     grad_zeroed=zeroed, ok=err < 1e-5 and bool(same.item()) and zeroed)
+                dist.barrier()
+                comm.close(); gbuf.close(); pbuf.close(); wbuf.close()
+
+
 def train():
     """ResNet-50 (small images) for a few steps: p2p vs nccl gradient paths give the same weights; mirrors identical."""
     from tensorflowdistributedlearning_b200 import models
     from tensorflowdistributedlearning_b200.parallel.trainer import TowerTrainer, classification_loss
 
     finals = {}
-    for comm_kind, graph, overlap in (("nccl", False, False), ("p2p", False, False), ("p2p", True, False), ("p2p", True, True)):
+    for comm_kind, graph, overlap, wire_fmt in (("nccl", False, False, "fp32"), ("p2p", False, False, "fp32"),
+                                                 ("p2p", True, False, "fp32"), ("p2p", True, True, "fp32"),
+                                                 ("p2p", False, False, "bf16"), ("p2p", True, True, "bf16")):
         torch.manual_seed(3)
         tr = TowerTrainer(models.resnet50(num_classes=32), group, batch=16, input_hwc=(64, 64, 3),
                           loss_fn=classification_loss, use_graph=graph, kind="sgdm", lr=0.05, momentum=0.9,
-                          comm=comm_kind, overlap=overlap, bucket_cap_mb=8.0)
+                          comm=comm_kind, overlap=overlap, bucket_cap_mb=8.0, grad_wire=wire_fmt)
         gen = torch.Generator().manual_seed(50 + R)
         tr.images.copy_(torch.randint(0, 256, tr.images.shape, dtype=torch.uint8, generator=gen))
         tr.labels.copy_(torch.randint(0, 32, tr.labels.shape, generator=gen))
@@ -276,13 +446,14 @@ def train():
         same = torch.tensor([float(torch.equal(chk, p))], device="cuda")
         dist.all_reduce(same, op=dist.ReduceOp.MIN)
         s = tr.opt.flat.stats_flat.clone(); s0 = s.clone(); dist.broadcast(s0, 0)
-        finals[(comm_kind, graph, overlap)] = p
-        emit(test="train", comm=comm_kind, graph=graph, overlap=overlap, loss=float(tr.loss.item()),
+        finals[(comm_kind, graph, overlap, wire_fmt)] = p
+        emit(test="train", comm=comm_kind, graph=graph, overlap=overlap, grad_wire=tr.opt.grad_wire,
+             loss=float(tr.loss.item()),
              mirrors_identical=bool(same.item()), stats_identical=bool(torch.equal(s, s0)),
              buckets=len(tr.opt.flat.buckets), ok=bool(same.item()))
         tr.close()
         dist.barrier()
-    base = finals[("nccl", False, False)]
+    base = finals[("nccl", False, False, "fp32")]
     for k, v in finals.items():
         emit(test="train_vs_nccl", variant=list(k), rel_err=rel_err(v, base), ok=rel_err(v, base) < 5e-2)
 
@@ -434,6 +605,6 @@ if __name__ == "__main__":
     t0 = time.time()
     for w in which:
         {"correctness": correctness, "stress": stress, "sweep": sweep, "train": train, "nvls": nvls, "resume": resume,
-         "dead_nccl": dead_nccl}[w]()
+         "dead_nccl": dead_nccl, "wire": wire, "sweep2": sweep2}[w]()
         emit(test=w, event="done", secs=round(time.time() - t0, 1))
     group.shutdown()

@@ -67,8 +67,13 @@ class Bottleneck(TFModule):
                             weight_decay=bn.weight_decay, pad_in=True)
 
     def forward(self, x, end_points: Optional[dict] = None, prefix: str = ""):
-        pre = self.preact(x, relu=True)
-        sc = L.subsample(x, self.stride) if self.shortcut is None else self.shortcut(pre)
+        if self.shortcut is None and self.stride == 1:
+            # identity shortcut at full resolution: it takes an alias of the pre-activation BatchNorm's input, so its
+            # gradient is added (and the input's own ReLU backward applied) inside that BatchNorm's backward kernel
+            pre, sc = self.preact(x, relu=True, want_tap=True)
+        else:
+            pre = self.preact(x, relu=True)
+            sc = L.subsample(x, self.stride) if self.shortcut is None else self.shortcut(pre)
         r = self.conv1(pre)
         r = self.conv2(r)
         want_r = end_points is not None and f"{prefix}{self.scope}/conv3" in getattr(end_points, "wanted", ())
@@ -271,10 +276,15 @@ class ResNetV2Beta(TFModule):
         if self.symmetric_padding:
             from ..ops import pooling as P
             net = P.max_pool(net, 3, 2, (1, 1, 1, 1))
+            pool_stats = None
+        elif self.postnorm is not None and self.training:
+            # pool1 -> postnorm (core/resnet.py:241-242): the pooling kernel leaves the BatchNorm statistics of its
+            # output, the BatchNorm runs no statistics pass of its own
+            net, pool_stats = L.max_pool_same(net, 3, 2, want_stats=True)
         else:
-            net = L.max_pool_same(net, 3, 2)
+            net, pool_stats = L.max_pool_same(net, 3, 2), None
         if self.postnorm is not None:
-            net = self.postnorm(net, relu=True)
+            net = self.postnorm(net, relu=True, stats=pool_stats)
         for mods, bscope in zip(self.blocks, self.block_scopes):
             for m in mods:
                 net = m(net, end_points, self.prefix)
@@ -407,17 +417,38 @@ class ResNetSegModel(TFModule):
         self.dec_3x3 = Conv2d(2 * base_depth, 1, 3, use_bias=True, scope=f"{P}decoder/conv_3x3",
                               weight_decay=weight_decay)
 
+    @staticmethod
+    def _branch(m: ConvBNAct, x, upsample: bool = False):
+        """conv of a ConvBNAct, with its BatchNorm left for the concat kernel to apply (straight into a channel slice)."""
+        if m.training:
+            y, stats = m.conv(x, want_stats=True)
+        else:
+            y, stats = m.conv(x), None
+        return {"x": y, "bn": m.bn, "relu": m.relu, "stats": stats, "upsample": upsample}
+
     def forward(self, x):
+        from ..ops import functional as TF
+
         _, ep = self.backbone(x, collect=True, wanted=(self.low_key,))
         feat = ep[self.block4_key]
         size = feat.shape[1:3]
-        branches = [self.aspp_1x1(feat)] + [m(feat) for m in self.aspp_sep]
-        pooled = self.aspp_pool(L.global_avg_pool(feat, keepdims=True))
-        branches.append(L.upsample(pooled, size))
-        aspp = self.aspp_out(torch.cat(branches, dim=-1))
         low = ep[self.low_key]
-        aspp_up = L.upsample(aspp, low.shape[1:3])
-        dec = torch.cat([self.dec_1x1(low), aspp_up], dim=-1)
+        pooled_in = L.global_avg_pool(feat, keepdims=True)
+        if TF._native_ok(feat) and all(m.bn.c_p % 8 == 0 for m in (self.aspp_1x1, self.aspp_pool, self.dec_1x1)):
+            # K12: no concatenation -- every branch's BatchNorm (the pooled branch: BatchNorm + `_upsample`) writes
+            # its channel slice of ONE buffer (core/resnet.py:470); same for the decoder's pair (core/resnet.py:485)
+            aspp_in = TF.batch_norm_concat(
+                [self._branch(self.aspp_1x1, feat)] +
+                [self._branch(m.pointwise, m.depthwise(feat)) for m in self.aspp_sep] +
+                [self._branch(self.aspp_pool, pooled_in, upsample=True)], size)
+            aspp = self.aspp_out(aspp_in)
+            dec = TF.batch_norm_concat([self._branch(self.dec_1x1, low), {"x": aspp, "bn": None, "upsample": True}],
+                                       low.shape[1:3])
+        else:
+            branches = [self.aspp_1x1(feat)] + [m(feat) for m in self.aspp_sep]
+            branches.append(L.upsample(self.aspp_pool(pooled_in), size))
+            aspp = self.aspp_out(torch.cat(branches, dim=-1))
+            dec = torch.cat([self.dec_1x1(low), L.upsample(aspp, low.shape[1:3])], dim=-1)
         dec = self.dec_3x3(dec)
         return L.upsample(dec.float(), self.input_shape)
 

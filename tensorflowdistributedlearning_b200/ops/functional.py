@@ -20,6 +20,11 @@ from . import reference as R
 # data_ptr of the gradient -> data_ptr of the 1-bit mask that was applied.  Consumed by that tensor's BatchNorm backward,
 # which then skips its own masking and returns the gradient itself for the residual input.
 _PREMASKED = {}
+# A gradient whose tensor is the output of a convolution with a fused output ReLU and that ALREADY carries that ReLU's
+# backward: data_ptr of the gradient -> (version, data_ptr of the activation).  Left by the BatchNorm that consumed the
+# activation (its backward kernel zeroes the gradient where the activation is 0); the convolution then skips its own
+# masking pass.
+_RELU_DONE = {}
 _LAST_RELU_MASK = None
 # BatchNorm -> consumer convolution hand-off for the fused backward reductions: the BatchNorm's output tensor carries
 # ``_tdl_bn_src`` (its input, batch statistics, affine, mask); the consumer's data-gradient kernel reduces
@@ -117,6 +122,7 @@ def fused_bn_backward_hits() -> int:
 def begin_step() -> None:
     """Drop per-step bookkeeping (call at the start of every training step)."""
     _PREMASKED.clear()
+    _RELU_DONE.clear()
     _BN_PARTIALS.clear()
     if _WPREP_ON:
         invalidate_prepared_weights()
@@ -310,7 +316,10 @@ class _ConvNative(torch.autograd.Function):
             dy = torch.zeros(ctx.y_shape, dtype=x.dtype, device=x.device)
         dy = dy.contiguous()
         if ctx.relu_out:  # backward of the fused output ReLU: everything below, and the residual branch, sees dy * (y > 0)
-            dy = torch.ops.aten.threshold_backward(dy, y_relu, 0)
+            done = _RELU_DONE.pop(dy.data_ptr(), None)
+            if done is None or done != (dy._version, y_relu.data_ptr()):
+                dy = torch.ops.aten.threshold_backward(dy, y_relu, 0)
+            # else: the only consumer of y was a BatchNorm whose backward kernel already zeroed dy where y == 0
         d_tap = rest[-1] if (ctx.want_tap and rest and rest[-1] is not None) else None
         dx = dw = db = None
         if ctx.needs_input_grad[0]:
@@ -579,6 +588,8 @@ def conv2d(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] =
         if residual is not None or relu:
             y = _ConvNative.apply(x.contiguous(), weight, bias, stride, dil, (pt, pb, pl, pr), (P, Q), False, False,
                                   residual, relu)
+            if relu:
+                y._tdl_relu_out = True  # y >= 0, and the producing node owns the backward of that ReLU
         else:
             y = _ConvNative.apply(x.contiguous(), weight, bias, stride, dil, (pt, pb, pl, pr), (P, Q))
         return (y, None) if want_stats else y
@@ -605,10 +616,14 @@ def conv2d(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] =
 # ---------------------------------------------------------------------------------------------
 class _BNNative(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, gamma, beta, running_mean, running_var, residual, decay, eps, relu, training, partials=None):
+    def forward(ctx, x, gamma, beta, running_mean, running_var, residual, decay, eps, relu, training, partials=None,
+                want_tap=False):
         from . import native_ops as O
 
         ctx.gamma_param, ctx.beta_param = gamma, beta
+        ctx.want_tap = bool(want_tap)
+        ctx.x_is_relu_out = bool(getattr(x, "_tdl_relu_out", False))
+        ctx.set_materialize_grads(False)
 
         shape = x.shape
         C = shape[-1]
@@ -631,7 +646,7 @@ class _BNNative(torch.autograd.Function):
             _LAST_RELU_MASK = zmask
             _LAST_BN_SRC = dict(x=x2, mean=mean, invstd=invstd, scale=scale, shift=shift, relu=bool(relu),
                                 has_res=residual is not None)
-            return z.view(shape)
+            return (z.view(shape), x.view_as(x)) if want_tap else z.view(shape)
         if training and partials is not None:
             mean, invstd, scale, shift = O.bn_finalize_partials(partials, partials.shape[0], x2.shape[0], gamma, beta,
                                                                 running_mean, running_var, decay, eps)
@@ -656,10 +671,12 @@ class _BNNative(torch.autograd.Function):
         _LAST_RELU_MASK = zmask
         _LAST_BN_SRC = (dict(x=x2, mean=mean, invstd=invstd, scale=scale, shift=shift, relu=bool(relu),
                              has_res=residual is not None) if training else None)
-        return z.view(shape)
+        # want_tap: an alias of the input for an identity shortcut -- its gradient comes back to THIS node and is added
+        # inside the backward apply kernel (no separate elementwise add; core/resnet.py:71-87,126-148)
+        return (z.view(shape), x.view_as(x)) if want_tap else z.view(shape)
 
     @staticmethod
-    def backward(ctx, dz):
+    def backward(ctx, dz, d_tap=None):
         from . import native_ops as O
 
         relu, has_res, training, shape = ctx.cfg
@@ -667,7 +684,13 @@ class _BNNative(torch.autograd.Function):
             raise RuntimeError("backward through inference-mode BatchNorm is not supported")
         x2, z2, scale, shift, mean, invstd = ctx.saved_tensors
         C = shape[-1]
+        if dz is None:  # only the alias was used downstream
+            dz = torch.zeros(shape, dtype=x2.dtype, device=x2.device)
         dz2 = dz.contiguous().view(-1, C)
+        addend = None if d_tap is None else d_tap.contiguous().view(-1, C)
+        # the tap makes this node's dx the gradient of the input from ALL of this unit's uses of it; when the input is
+        # itself a ReLU output, that ReLU's backward is applied here as well (the producer is told through _RELU_DONE)
+        mask_by_x = ctx.want_tap and ctx.x_is_relu_out and not _BN_FOLD
         g, b = ctx.gamma_param, ctx.beta_param
         direct = _direct_ok(g) and _direct_ok(b)
         pm = _PREMASKED.pop(dz2.data_ptr(), None)
@@ -680,23 +703,28 @@ class _BNNative(torch.autograd.Function):
             global _FUSED_BN_HITS
             _FUSED_BN_HITS += 1
         bwd = O.bn_bwd_fused if _BN_FOLD else O.bn_bwd
+        extra = {} if _BN_FOLD else dict(addend=addend, mask_by_x=mask_by_x)
         if premasked:
             # the consumer's data-gradient kernel already applied this layer's ReLU mask: no masking here, and the
             # residual branch's gradient is the incoming gradient itself (nothing to write)
             dx, _, dgamma, dbeta = bwd(dz2, x2, None, scale, shift, mean, invstd, False, False,
-                                            acc_dgamma=g.grad if direct else None,
-                                            acc_dbeta=b.grad if direct else None, partials=partials)
+                                       acc_dgamma=g.grad if direct else None,
+                                       acc_dbeta=b.grad if direct else None, partials=partials, **extra)
             dres = dz2
         elif has_res and not relu:
             # no activation after the sum: the residual branch's gradient is the incoming gradient, nothing to write
             dx, _, dgamma, dbeta = bwd(dz2, x2, None, scale, shift, mean, invstd, False, False,
                                        acc_dgamma=g.grad if direct else None,
-                                       acc_dbeta=b.grad if direct else None, partials=partials)
+                                       acc_dbeta=b.grad if direct else None, partials=partials, **extra)
             dres = dz2
         else:
             dx, dres, dgamma, dbeta = bwd(dz2, x2, z2, scale, shift, mean, invstd, relu, has_res,
                                           acc_dgamma=g.grad if direct else None,
-                                          acc_dbeta=b.grad if direct else None, partials=partials)
+                                          acc_dbeta=b.grad if direct else None, partials=partials, **extra)
+        if _BN_FOLD and addend is not None:
+            dx = dx + addend
+        if mask_by_x:
+            _RELU_DONE[dx.data_ptr()] = (dx._version, x2.data_ptr())
         _count((3 if partials is not None else 4) - (1 if _BN_FOLD else 0))
         if direct:
             _notify(g)
@@ -704,21 +732,31 @@ class _BNNative(torch.autograd.Function):
             dgamma = dbeta = None
         return (dx.view(shape), dgamma if ctx.needs_input_grad[1] else None,
                 dbeta if ctx.needs_input_grad[2] else None, None, None,
-                dres.view(shape) if has_res else None, None, None, None, None, None)
+                dres.view(shape) if has_res else None, None, None, None, None, None, None)
 
 
 def batch_norm(x: torch.Tensor, gamma, beta, running_mean, running_var, *, decay: float, eps: float,
                training: bool, relu: bool = False, residual: Optional[torch.Tensor] = None,
-               stats: Optional[torch.Tensor] = None) -> torch.Tensor:
+               stats: Optional[torch.Tensor] = None, want_tap: bool = False):
     """y = relu?(BN(x) + residual?) over the last (channel) axis with TF fused-BN semantics.
-    ``stats``: partial statistics of ``x`` from ``conv2d(..., want_stats=True)`` (skips the statistics pass)."""
+    ``stats``: partial statistics of ``x`` from ``conv2d(..., want_stats=True)`` (skips the statistics pass).
+    ``want_tap=True`` -> (y, x_alias): feed ``x_alias`` to an identity shortcut and its gradient is added inside this
+    BatchNorm's backward kernel instead of by a separate elementwise add."""
     C = x.shape[-1]
     if _native_ok(x) and C % 8 == 0 and gamma is not None and beta is not None:
         res = None if residual is None else residual.contiguous()
         global _LAST_RELU_MASK, _LAST_BN_SRC
         _LAST_RELU_MASK = _LAST_BN_SRC = None
-        out = _BNNative.apply(x.contiguous(), gamma, beta, running_mean, running_var, res, decay, eps, relu,
-                              training, stats if training else None)
+        tap = None
+        xin = x.contiguous()
+        if xin is not x and getattr(x, "_tdl_relu_out", False):
+            xin._tdl_relu_out = True
+        if want_tap and training and torch.is_grad_enabled():
+            out, tap = _BNNative.apply(xin, gamma, beta, running_mean, running_var, res, decay, eps, relu, training,
+                                       stats, True)
+        else:
+            out = _BNNative.apply(xin, gamma, beta, running_mean, running_var, res, decay, eps, relu,
+                                  training, stats if training else None)
         if _LAST_RELU_MASK is not None:
             # lets the next convolution's data-gradient kernel apply this ReLU's backward (see _ConvNative)
             out._tdl_relu_mask = _LAST_RELU_MASK
@@ -727,6 +765,10 @@ def batch_norm(x: torch.Tensor, gamma, beta, running_mean, running_var, *, decay
             # lets the consumer convolution's data-gradient kernel reduce this BatchNorm's backward sums (_ConvNative)
             out._tdl_bn_src = _LAST_BN_SRC
             _LAST_BN_SRC = None
+        if relu:
+            out._tdl_relu_out = True
+        if want_tap:
+            return out, (tap if tap is not None else x)
         return out
     if training:
         y = R.batch_norm_train(x, gamma, beta, running_mean, running_var, decay, eps)
@@ -734,7 +776,132 @@ def batch_norm(x: torch.Tensor, gamma, beta, running_mean, running_var, *, decay
         y = R.batch_norm_infer(x, gamma, beta, running_mean, running_var, eps)
     if residual is not None:
         y = y + residual
-    return F.relu(y) if relu else y
+    y = F.relu(y) if relu else y
+    return (y, x) if want_tap else y
+
+
+class _BNConcat(torch.autograd.Function):
+    """Several branches that end in BatchNorm (+ReLU) (+ the reference's `_upsample`), concatenated along channels
+    WITHOUT a concatenation: every branch normalises (or upsamples) straight into its channel slice of one buffer, and
+    in backward every branch reads its slice of the buffer's gradient in place (core/resnet.py:470,485).
+
+    ``meta``: per branch a dict {kind: "bn" | "bn_up" | "up", C, relu, decay, eps, training}; ``tensors``: per branch
+    the flattened (x, stats, gamma, beta, moving_mean, moving_variance) for the BatchNorm kinds, (x,) for "up"."""
+
+    @staticmethod
+    def forward(ctx, meta, out_hw, *tensors):
+        from . import native_ops as O
+
+        ctx.set_materialize_grads(False)
+        it = iter(tensors)
+        branches = []
+        for m in meta:
+            if m["kind"] == "up":
+                branches.append((m, next(it)))
+            else:
+                branches.append((m, next(it), next(it), next(it), next(it), next(it), next(it)))
+        n = branches[0][1].shape[0]
+        oh, ow = out_hw
+        ctot = sum(m["C"] for m in meta)
+        buf = torch.empty((n, oh, ow, ctot), dtype=torch.bfloat16, device=branches[0][1].device)
+        buf2 = buf.view(-1, ctot)
+        saved, lo = [], 0
+        ctx.params = []
+        for b in branches:
+            m = b[0]
+            C = m["C"]
+            sl4, sl2 = buf[..., lo:lo + C], buf2[:, lo:lo + C]
+            if m["kind"] == "up":
+                O.upsample_fwd(b[1].contiguous(), out_hw, out=sl4)
+                _count(1)
+                saved.append(None)
+                ctx.params.append(None)
+            else:
+                _, x, stats, gamma, beta, rm, rv = b
+                x2 = x.reshape(-1, C)
+                if m["training"] and stats is not None:
+                    mean, invstd, scale, shift = O.bn_finalize_partials(stats, stats.shape[0], x2.shape[0], gamma, beta,
+                                                                        rm, rv, m["decay"], m["eps"])
+                    _count(1)
+                elif m["training"]:
+                    mean, invstd, scale, shift = O.bn_fwd_stats(x2, gamma, beta, rm, rv, m["decay"], m["eps"])
+                    _count(2)
+                else:
+                    scale, shift = O.bn_infer_scale_shift(gamma, beta, rm, rv, m["eps"])
+                    mean = invstd = None
+                    _count(1)
+                if m["kind"] == "bn":
+                    O.bn_apply(x2, scale, shift, None, m["relu"], out=sl2)
+                    _count(1)
+                else:  # normalise the small map, then upsample it into the slice
+                    z = O.bn_apply(x2, scale, shift, None, m["relu"]).view(x.shape)
+                    O.upsample_fwd(z, out_hw, out=sl4)
+                    _count(2)
+                saved.append((x2, scale, shift, mean, invstd))
+                ctx.params.append((gamma, beta))
+            lo += C
+        ctx.meta, ctx.saved, ctx.out_hw = meta, saved, out_hw
+        ctx.in_shapes = [b[1].shape for b in branches]
+        return buf
+
+    @staticmethod
+    def backward(ctx, dbuf):
+        from . import native_ops as O
+
+        dbuf = dbuf.contiguous()
+        ctot = dbuf.shape[-1]
+        d2 = dbuf.view(-1, ctot)
+        grads, lo = [], 0
+        for m, sv, pr, shape in zip(ctx.meta, ctx.saved, ctx.params, ctx.in_shapes):
+            C = m["C"]
+            if m["kind"] == "up":
+                grads.append(O.upsample_bwd(dbuf[..., lo:lo + C], tuple(shape), ctx.out_hw))
+                _count(1)
+            else:
+                if not m["training"]:
+                    raise RuntimeError("backward through inference-mode BatchNorm is not supported")
+                x2, scale, shift, mean, invstd = sv
+                gamma, beta = pr
+                direct = _direct_ok(gamma) and _direct_ok(beta)
+                if m["kind"] == "bn_up":
+                    dz2 = O.upsample_bwd(dbuf[..., lo:lo + C], tuple(shape), ctx.out_hw).reshape(-1, C)
+                    _count(1)
+                else:
+                    dz2 = d2[:, lo:lo + C]  # read in place, row pitch = the whole buffer's channel count
+                dx, _, dgamma, dbeta = O.bn_bwd(dz2, x2, None, scale, shift, mean, invstd, m["relu"], False,
+                                                acc_dgamma=gamma.grad if direct else None,
+                                                acc_dbeta=beta.grad if direct else None)
+                _count(4)
+                if direct:
+                    _notify(gamma)
+                    _notify(beta)
+                    dgamma = dbeta = None
+                grads += [dx.view(shape), None, dgamma if gamma is not None else None,
+                          dbeta if beta is not None else None, None, None]
+            lo += C
+        return (None, None, *grads)
+
+
+def batch_norm_concat(branches, out_hw):
+    """``branches``: list of dicts, each either
+         {"x": tensor [N,h,w,C], "bn": BatchNorm module, "relu": bool, "stats": partials or None, "upsample": bool}
+       or {"x": tensor [N,h,w,C], "bn": None, "upsample": True}   (an already activated tensor, only resized)
+    -> [N, out_h, out_w, sum C]: the channel concatenation of relu?(BN(x)) (resized with the reference's `_upsample` when
+    ``upsample``), written slice by slice with no concatenation pass.  CUDA bf16 only; callers keep the plain
+    ``torch.cat`` formulation for the torch path."""
+    meta, tensors = [], []
+    for b in branches:
+        x, bn = b["x"], b.get("bn")
+        C = x.shape[-1]
+        if bn is None:
+            meta.append(dict(kind="up", C=C))
+            tensors.append(x)
+            continue
+        meta.append(dict(kind="bn_up" if b.get("upsample") else "bn", C=C, relu=bool(b.get("relu", True)),
+                         decay=bn.decay, eps=bn.eps, training=bn.training))
+        tensors += [x.contiguous(), b.get("stats") if bn.training else None, bn.gamma, bn.beta, bn.moving_mean,
+                    bn.moving_variance]
+    return _BNConcat.apply(meta, tuple(out_hw), *tensors)
 
 
 # ---------------------------------------------------------------------------------------------

@@ -127,14 +127,15 @@ class BatchNorm(TFModule):
         self.register_buffer("moving_variance", torch.ones(cp))
 
     def forward(self, x: torch.Tensor, relu: bool = False, residual: Optional[torch.Tensor] = None,
-                stats: Optional[torch.Tensor] = None) -> torch.Tensor:
+                stats: Optional[torch.Tensor] = None, want_tap: bool = False):
         if stats is None and self.training:
             # partial statistics the producing kernel left on the tensor (e.g. a unit tail relu(shortcut + conv3))
             stats = getattr(x, "_tdl_stats", None)
             if stats is not None and stats.shape[-1] != x.shape[-1]:
                 stats = None
         return TF.batch_norm(x, self.gamma, self.beta, self.moving_mean, self.moving_variance, decay=self.decay,
-                             eps=self.eps, training=self.training, relu=relu, residual=residual, stats=stats)
+                             eps=self.eps, training=self.training, relu=relu, residual=residual, stats=stats,
+                             want_tap=want_tap)
 
     def tf_variables(self):
         d = {f"{self.scope}/beta": (self.beta, "plain", (self.c,)),
@@ -216,10 +217,10 @@ class SplitSeparableConv2d(TFModule):
         return self.pointwise(self.depthwise(x))
 
 
-def max_pool_same(x: torch.Tensor, k: int = 3, stride: int = 2) -> torch.Tensor:
+def max_pool_same(x: torch.Tensor, k: int = 3, stride: int = 2, want_stats: bool = False):
     from . import pooling as P
 
-    return P.max_pool_same(x, k, stride)
+    return P.max_pool_same(x, k, stride, want_stats)
 
 
 def global_avg_pool(x: torch.Tensor, keepdims: bool = True) -> torch.Tensor:

@@ -266,15 +266,25 @@ def bn_infer_scale_shift(gamma, beta, running_mean, running_var, eps: float):
     return out[0], out[1]
 
 
-def bn_apply(x2d, scale, shift, residual2d, relu: bool, want_mask: bool = False):
+def _row_pitch(t2d: torch.Tensor, C: int) -> int:
+    """Elements between consecutive rows of a [rows, C] tensor that may be a channel slice of a wider buffer."""
+    assert t2d.dim() == 2 and t2d.shape[1] == C and t2d.stride(1) == 1, (t2d.shape, t2d.stride())
+    ld = t2d.stride(0) if t2d.shape[0] > 1 else max(t2d.stride(0), C)
+    assert ld >= C and ld % 8 == 0 and t2d.data_ptr() % 16 == 0, (ld, C)
+    return int(ld)
+
+
+def bn_apply(x2d, scale, shift, residual2d, relu: bool, want_mask: bool = False, out: Optional[torch.Tensor] = None):
     """y = relu(x*scale + shift (+ residual)).  ``want_mask`` additionally returns the 1-bit-per-element ReLU mask
-    ([rows, C/8] uint8) that the backward kernels accept in place of the activation."""
+    ([rows, C/8] uint8) that the backward kernels accept in place of the activation.  ``out``: write into this
+    [rows, C] tensor instead of a new one -- it may be a channel slice of a wider buffer (row pitch > C), which is how a
+    concatenation of normalised branches costs no copy."""
     rows, C = x2d.shape
-    y = torch.empty_like(x2d)
+    y = torch.empty_like(x2d) if out is None else out
     mask = torch.empty((rows, C // 8), dtype=torch.uint8, device=x2d.device) if (want_mask and relu) else None
-    rc = N.lib().tdl_bn_apply(N.ptr(x2d), N.ptr(scale), N.ptr(shift), N.ptr(residual2d), N.ptr(y), N.ptr(mask),
-                              _i64(rows), _i(C), _i(int(relu)), N.stream_ptr())
-    N.check(rc, "tdl_bn_apply")
+    rc = N.lib().tdl_bn_apply_ld(N.ptr(x2d), N.ptr(scale), N.ptr(shift), N.ptr(residual2d), N.ptr(y), N.ptr(mask),
+                                 _i64(rows), _i(C), _i(int(relu)), _i64(_row_pitch(y, C)), N.stream_ptr())
+    N.check(rc, "tdl_bn_apply_ld")
     return (y, mask) if want_mask else y
 
 
@@ -337,13 +347,15 @@ def bn_bwd_fused(dz2d, x2d, z2d, scale, shift, mean, invstd, relu: bool, want_dr
 
 
 def bn_bwd(dz2d, x2d, z2d, scale, shift, mean, invstd, relu: bool, want_dres: bool,
-           acc_dgamma=None, acc_dbeta=None, partials=None):
+           acc_dgamma=None, acc_dbeta=None, partials=None, addend=None, mask_by_x: bool = False):
     """Returns (dx, dres_or_None, dgamma, dbeta).  ``partials`` ([nparts, 2, C], from ``conv2d_dgrad_bnstats``):
-    the reduction over (dz, x) has already been done by the kernel that produced dz."""
+    the reduction over (dz, x) has already been done by the kernel that produced dz.  ``addend`` ([rows, C] bf16): a
+    second gradient of x, added inside the apply kernel; ``mask_by_x``: x is a ReLU output, dx is zeroed where x == 0."""
     rows, C = x2d.shape
     dev = x2d.device
     dgb = torch.empty((2, C), dtype=torch.float32, device=dev)
     zbits = int(z2d is not None and z2d.dtype == torch.uint8)  # the 1-bit ReLU mask written by bn_apply
+    ld = _row_pitch(dz2d, C)  # dz may be a channel slice of a concat buffer's gradient (row pitch > C)
     if partials is not None:
         assert partials.dtype == torch.float32 and partials.shape[1:] == (2, C) and partials.is_contiguous()
         rc = N.lib().tdl_bn_bwd_finalize_partials(N.ptr(partials), _i(partials.shape[0]), _i(C), N.ptr(dgb[0]),
@@ -351,19 +363,24 @@ def bn_bwd(dz2d, x2d, z2d, scale, shift, mean, invstd, relu: bool, want_dres: bo
         N.check(rc, "tdl_bn_bwd_finalize_partials")
     else:
         rc = _bn_bwd_reduce(dz2d, x2d, z2d, zbits, scale, shift, mean, invstd, rows, C, relu, dgb, acc_dgamma,
-                            acc_dbeta)
+                            acc_dbeta, ld)
     dx = torch.empty_like(x2d)
     dres = torch.empty_like(x2d) if want_dres else None
-    rc = N.lib().tdl_bn_bwd_apply(N.ptr(dz2d), N.ptr(x2d), N.ptr(z2d), _i(zbits), N.ptr(scale), N.ptr(shift),
-                                  N.ptr(mean), N.ptr(invstd), N.ptr(dgb[0]), N.ptr(dgb[1]), N.ptr(dx), N.ptr(dres), _i64(rows),
-                                  _i(C), _i(int(relu)), N.stream_ptr())
-    N.check(rc, "tdl_bn_bwd_apply")
+    if addend is not None:
+        assert addend.dtype == torch.bfloat16 and addend.is_contiguous() and addend.numel() == rows * C
+    rc = N.lib().tdl_bn_bwd_apply_ex(N.ptr(dz2d), N.ptr(x2d), N.ptr(z2d), _i(zbits), N.ptr(scale), N.ptr(shift),
+                                     N.ptr(mean), N.ptr(invstd), N.ptr(dgb[0]), N.ptr(dgb[1]), N.ptr(dx), N.ptr(dres),
+                                     _i64(rows), _i(C), _i(int(relu)), _i64(ld), N.ptr(addend), _i(int(mask_by_x)),
+                                     N.stream_ptr())
+    N.check(rc, "tdl_bn_bwd_apply_ex")
     return dx, dres, dgb[0], dgb[1]
 
 
-def _bn_bwd_reduce(dz2d, x2d, z2d, zbits, scale, shift, mean, invstd, rows, C, relu, dgb, acc_dgamma, acc_dbeta):
+def _bn_bwd_reduce(dz2d, x2d, z2d, zbits, scale, shift, mean, invstd, rows, C, relu, dgb, acc_dgamma, acc_dbeta,
+                   ld=None):
     scratch = _bn_scratch(rows, C, x2d.device)
-    if C >= 256:
+    ld = C if ld is None else ld
+    if C >= 256 and ld == C:
         # wide tensors: the mask-specialised reduction with four rows in flight (fewer registers, more loads
         # outstanding) -- 185 -> 161 us on [802816, 256], 64 -> 56 us on [50176, 1024]; narrow tensors measured equal
         # or a little slower with it (profiles/bn_fold_experiment.txt), they keep the generic kernel
@@ -376,10 +393,10 @@ def _bn_bwd_reduce(dz2d, x2d, z2d, zbits, scale, shift, mean, invstd, rows, C, r
                                                   N.ptr(dgb[1]), N.ptr(acc_dgamma), N.ptr(acc_dbeta), N.stream_ptr())
         N.check(rc, "tdl_bn_bwd_finalize_partials")
         return rc
-    rc = N.lib().tdl_bn_bwd_reduce(N.ptr(dz2d), N.ptr(x2d), N.ptr(z2d), _i(zbits), N.ptr(scale), N.ptr(shift),
-                                   N.ptr(mean), N.ptr(invstd), _i64(rows), _i(C), _i(int(relu)), N.ptr(scratch),
-                                   _i64(scratch.numel()), N.ptr(dgb[0]), N.ptr(dgb[1]), N.ptr(acc_dgamma),
-                                   N.ptr(acc_dbeta), N.stream_ptr())
+    rc = N.lib().tdl_bn_bwd_reduce_ld(N.ptr(dz2d), N.ptr(x2d), N.ptr(z2d), _i(zbits), N.ptr(scale), N.ptr(shift),
+                                      N.ptr(mean), N.ptr(invstd), _i64(rows), _i(C), _i(int(relu)), _i64(ld),
+                                      N.ptr(scratch), _i64(scratch.numel()), N.ptr(dgb[0]), N.ptr(dgb[1]),
+                                      N.ptr(acc_dgamma), N.ptr(acc_dbeta), N.stream_ptr())
     N.check(rc, "tdl_bn_bwd_reduce")
     return rc
 
@@ -477,6 +494,23 @@ def maxpool_fwd(x, k, stride, pad_h, pad_w, out_hw):
     return y, idx
 
 
+def maxpool_fwd_stats(x, pad_h, pad_w, out_hw):
+    """3x3 / stride-2 max-pool + per-CTA partial (sum, sum of squares) of the pooled tensor in the same kernel.
+    Returns (y, idx, partials [nparts, 2, C])."""
+    _chk_bf16_nhwc(x, "x")
+    n, h, w, c = x.shape
+    p, q = out_hw
+    y = torch.empty((n, p, q, c), dtype=torch.bfloat16, device=x.device)
+    idx = torch.empty((n, p, q, c), dtype=torch.uint8, device=x.device)
+    rows = int(N.lib().tdl_maxpool_stats_rows(_i(n), _i(c), _i(p), _i(q)))
+    partials = torch.empty((rows, 2, c), dtype=torch.float32, device=x.device)
+    nparts = ctypes.c_int(0)
+    rc = N.lib().tdl_maxpool_fwd_stats(N.ptr(x), N.ptr(y), N.ptr(idx), _i(n), _i(h), _i(w), _i(c), _i(p), _i(q),
+                                       _i(pad_h), _i(pad_w), N.ptr(partials), ctypes.byref(nparts), N.stream_ptr())
+    N.check(rc, "tdl_maxpool_fwd_stats")
+    return y, idx, partials[:int(nparts.value)]
+
+
 def maxpool_bwd(dy, idx, in_shape, k, stride, pad_h, pad_w):
     n, h, w, c = in_shape
     _, p, q, _ = dy.shape
@@ -534,23 +568,31 @@ def depthwise_bwd(x, w_rsc, dy, y, stride, dil, pad_h, pad_w, relu):
     return dx, dw, db
 
 
-def upsample_fwd(x, out_hw):
+def upsample_fwd(x, out_hw, out: Optional[torch.Tensor] = None):
+    """``out``: an [N, OH, OW, C] tensor to write into; it may be a channel slice of a wider buffer."""
     n, h, w, c = x.shape
     oh, ow = out_hw
-    y = torch.empty((n, oh, ow, c), dtype=x.dtype, device=x.device)
-    rc = N.lib().tdl_upsample_fwd(N.ptr(x), N.ptr(y), _i(n), _i(h), _i(w), _i(c), _i(oh), _i(ow),
-                                  _i(int(x.dtype == torch.bfloat16)), N.stream_ptr())
-    N.check(rc, "tdl_upsample_fwd")
+    y = torch.empty((n, oh, ow, c), dtype=x.dtype, device=x.device) if out is None else out
+    assert y.dtype == x.dtype and tuple(y.shape) == (n, oh, ow, c) and y.stride(3) == 1
+    ld = y.stride(2)
+    assert y.stride(1) == ow * ld and (n == 1 or y.stride(0) == oh * ow * ld), "out must be a channel slice"
+    rc = N.lib().tdl_upsample_fwd_ld(N.ptr(x), N.ptr(y), _i(n), _i(h), _i(w), _i(c), _i(oh), _i(ow), _i64(ld),
+                                     _i(int(x.dtype == torch.bfloat16)), N.stream_ptr())
+    N.check(rc, "tdl_upsample_fwd_ld")
     return y
 
 
 def upsample_bwd(dy, in_shape, out_hw):
+    """``dy`` [N, OH, OW, C] may be a channel slice of a wider gradient buffer."""
     n, h, w, c = in_shape
     oh, ow = out_hw
+    assert dy.stride(3) == 1
+    ld = dy.stride(2)
+    assert dy.stride(1) == ow * ld and (n == 1 or dy.stride(0) == oh * ow * ld), "dy must be a channel slice"
     dx = torch.zeros(in_shape, dtype=torch.float32, device=dy.device)
-    rc = N.lib().tdl_upsample_bwd(N.ptr(dy), N.ptr(dx), _i(n), _i(h), _i(w), _i(c), _i(oh), _i(ow),
-                                  _i(int(dy.dtype == torch.bfloat16)), N.stream_ptr())
-    N.check(rc, "tdl_upsample_bwd")
+    rc = N.lib().tdl_upsample_bwd_ld(N.ptr(dy), N.ptr(dx), _i(n), _i(h), _i(w), _i(c), _i(oh), _i(ow), _i64(ld),
+                                     _i(int(dy.dtype == torch.bfloat16)), N.stream_ptr())
+    N.check(rc, "tdl_upsample_bwd_ld")
     return dx.to(dy.dtype)
 
 

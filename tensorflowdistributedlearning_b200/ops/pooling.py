@@ -12,32 +12,47 @@ from . import reference as R
 
 class _MaxPoolNative(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, k, stride, pads, out_hw):
+    def forward(ctx, x, k, stride, pads, out_hw, want_stats=False):
         from . import native_ops as O
 
-        y, idx = O.maxpool_fwd(x, k, stride, pads[0], pads[2], out_hw)
-        TF._count(1)
-        ctx.save_for_backward(idx)
+        ctx.set_materialize_grads(False)
         ctx.cfg = (k, stride, pads, tuple(x.shape))
+        TF._count(1)
+        if want_stats:  # + the batch statistics of the pooled tensor for the BatchNorm that follows
+            y, idx, partials = O.maxpool_fwd_stats(x, pads[0], pads[2], out_hw)
+            ctx.save_for_backward(idx)
+            ctx.mark_non_differentiable(partials)
+            return y, partials
+        y, idx = O.maxpool_fwd(x, k, stride, pads[0], pads[2], out_hw)
+        ctx.save_for_backward(idx)
         return y
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy, *_unused):
         from . import native_ops as O
 
         (idx,) = ctx.saved_tensors
         k, stride, pads, in_shape = ctx.cfg
         dx = O.maxpool_bwd(dy.contiguous(), idx, in_shape, k, stride, pads[0], pads[2])
         TF._count(1)
-        return dx, None, None, None, None
+        return dx, None, None, None, None, None
 
 
-def max_pool_same(x: torch.Tensor, k: int = 3, stride: int = 2) -> torch.Tensor:
+def max_pool_same(x: torch.Tensor, k: int = 3, stride: int = 2, want_stats: bool = False):
+    """TF 'SAME' max-pool.  ``want_stats=True`` -> (y, stats): ``stats`` is None (torch path / unsupported shape) or the
+    partial BatchNorm statistics of ``y`` accumulated by the pooling kernel itself; pass it to the BatchNorm that
+    consumes ``y`` (the reference's pool1 -> postnorm, core/resnet.py:241-242)."""
     n, h, w, c = x.shape
     P, Q, pt, pb, pl, pr = TF.conv_pads(h, w, k, k, stride, 1, "SAME")
     if TF._native_ok(x) and c % 8 == 0:
-        return _MaxPoolNative.apply(x.contiguous(), k, stride, (pt, pb, pl, pr), (P, Q))
-    return R.max_pool_same_nhwc(x, k, stride)
+        fused = (want_stats and k == 3 and stride == 2 and 256 % (c // 8) == 0 and n <= 65535
+                 and P * Q * c < (1 << 31))
+        if fused:
+            return _MaxPoolNative.apply(x.contiguous(), k, stride, (pt, pb, pl, pr), (P, Q), True)
+        y = _MaxPoolNative.apply(x.contiguous(), k, stride, (pt, pb, pl, pr), (P, Q))
+        return (y, None) if want_stats else y
+    y = R.max_pool_same_nhwc(x, k, stride)
+    return (y, None) if want_stats else y
 
 
 class _GapNative(torch.autograd.Function):

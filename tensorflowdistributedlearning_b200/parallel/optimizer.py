@@ -33,7 +33,7 @@ class DistributedOptimizer:
                  momentum: float = 0.9, weight_decay: float = 0.0, beta1: float = 0.9, beta2: float = 0.999,
                  eps: float = 1e-8, decay_steps: float = 0.0, decay_rate: float = 1.0, comm: Optional[str] = None,
                  bucket_cap_mb: float = 32.0, overlap: bool = True, sync_bn_stats: bool = True,
-                 comm_max_blocks: int = 64, async_wgrad: bool = True):
+                 comm_max_blocks: int = 64, async_wgrad: bool = True, grad_wire: Optional[str] = None):
         if kind not in ("adam", "sgdm"):
             raise ValueError("kind must be 'adam' or 'sgdm'")
         self.group, self.kind = group, kind
@@ -50,6 +50,11 @@ class DistributedOptimizer:
         if not group.distributed:
             comm = "local"
         self.comm = comm
+        # how gradients cross NVLink on the P2P path: "bf16" (default: the fp32 buckets are packed to bf16 inside the
+        # bucket kernel and reduced with fp32 accumulation -- half the reduce-scatter bytes) or "fp32"
+        self.grad_wire = grad_wire or os.environ.get("TDL_GRAD_WIRE", "bf16")
+        if self.grad_wire not in ("bf16", "fp32"):
+            raise ValueError("grad_wire must be 'bf16' or 'fp32'")
         self._p2p = None
         self._p2p_stats = None
         alloc = None
@@ -88,11 +93,19 @@ class DistributedOptimizer:
 
             self._p2p = P2PComm(self._symm["grad"], self._symm["param"])
             self.nvls = self.nvls and self._p2p.has_multicast
+            if self.grad_wire == "bf16" and not self.nvls:
+                from .p2p import SymmetricBuffer
+
+                self._symm["wire"] = SymmetricBuffer(self.flat.total * 2)
+                self._p2p.set_wire(self._symm["wire"])
+            else:
+                self.grad_wire = "fp32"
             self._p2p_stats = P2PComm(self._symm["stats"], None)
             self._stats_staging = torch.zeros_like(self.flat.stats_flat)
             self._p2p.broadcast_params_(self.flat.total)
             torch.cuda.synchronize()
         else:
+            self.grad_wire = "fp32"  # only the P2P kernels have a wire format of their own
             group.broadcast_(self.flat.param_flat)
         group.broadcast_(self.flat.stats_flat)
         # overlap machinery
@@ -143,10 +156,16 @@ class DistributedOptimizer:
     def _launch_bucket(self, b) -> None:
         a, bb, c = ((self.momentum, self.weight_decay, 0.0) if self.kind == "sgdm"
                     else (self.beta1, self.beta2, self.eps))
+        if self.grad_wire == "bf16":
+            self._p2p.fused_step_wire(b.offset, b.numel, kind=1 if self.kind == "sgdm" else 2, zero_grad=True,
+                                      m1=self.m1, m2=self.m2, lr_state=self.lr_state, a=a, b=bb, c=c, mode=0,
+                                      max_blocks=self.comm_max_blocks)
+            return
         self._p2p.fused_step(b.offset, b.numel, kind=1 if self.kind == "sgdm" else 2, grad_is_bf16=False,
                              zero_grad=True, m1=self.m1, m2=self.m2, lr_state=self.lr_state, a=a, b=bb, c=c,
                              mode=3 if (self.nvls and b.numel * 4 > (1 << 19)) else 0,
-                             max_blocks=self.comm_max_blocks)
+                             # NVLS: 32 CTAs are the optimum at every size (more only queue up inside the switch)
+                             max_blocks=min(self.comm_max_blocks, 32) if self.nvls else self.comm_max_blocks)
 
     def _on_grad_ready(self, p) -> None:
         i = self.flat.bucket_of[id(p)]
@@ -234,18 +253,19 @@ class DistributedOptimizer:
         if self.comm != "p2p" or not self.group.distributed:
             return [(0, self.flat.total)]
         w, r = self.group.world, self.group.rank
+        vec = 8 if self.grad_wire == "bf16" else 4  # elements per work unit of the bucket kernels
         out = []
         for b in self.flat.buckets:
             if b.numel * 4 <= self.TWO_SHOT_MIN_BYTES:
                 out.append((b.offset, b.offset + b.numel))
                 continue
-            n4 = b.numel // 4
-            per = (n4 + w - 1) // w
-            lo, hi = min(per * r, n4), min(per * r + per, n4)
+            nv = b.numel // vec
+            per = (nv + w - 1) // w
+            lo, hi = min(per * r, nv), min(per * r + per, nv)
             if hi > lo:
-                out.append((b.offset + lo * 4, b.offset + hi * 4))
-            if r == w - 1 and b.numel % 4:
-                out.append((b.offset + n4 * 4, b.offset + b.numel))
+                out.append((b.offset + lo * vec, b.offset + hi * vec))
+            if r == w - 1 and b.numel % vec:
+                out.append((b.offset + nv * vec, b.offset + b.numel))
         return out
 
     def consolidate_state(self) -> None:

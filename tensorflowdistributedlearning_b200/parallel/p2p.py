@@ -130,6 +130,7 @@ class P2PComm:
                                         N.ptr(self.epoch), ctypes.c_int(int(self.emulated)), ctypes.byref(out)),
                 "tdl_p2p_comm_create")
         self.handle = out
+        self.wire = None
         # the device-side wait limit follows the host-side collective timeout (a hard-coded 2 s limit killed
         # every tower when one of them stalled in its input pipeline); TDL_P2P_TIMEOUT_S overrides it on its own
         import os
@@ -143,6 +144,22 @@ class P2PComm:
         if not self.emulated and dist.is_initialized() and self.world > 1:
             torch.cuda.synchronize()
             dist.barrier(group=group)
+
+    def set_wire(self, wire: SymmetricBuffer) -> None:
+        """Attach the bf16 wire buffers (one per rank, gradient-bucket element offsets): enables ``fused_step_wire``."""
+        self.wire = wire
+        N.check(N.lib().tdl_p2p_comm_set_wire(self.handle, wire.ptr_table()), "tdl_p2p_comm_set_wire")
+
+    def fused_step_wire(self, offset: int, n: int, *, kind: int, zero_grad: bool, m1, m2, lr_state, a: float, b: float,
+                        c: float, grad_scale: float = 1.0, mode: int = 0, max_blocks: int = 64, phases: int = 3):
+        """The fused step with gradients crossing NVLink as bf16: phase 1 packs (and clears) this rank's fp32 bucket into
+        its wire buffer, phase 2 reduces every rank's wire copy in fp32 and runs the optimizer (``phases=3`` = both)."""
+        rc = N.lib().tdl_p2p_fused_step_wire(self.handle, ctypes.c_int64(offset), ctypes.c_int64(n), ctypes.c_int(mode),
+                                             ctypes.c_int(kind), ctypes.c_int(int(zero_grad)), N.ptr(m1), N.ptr(m2),
+                                             N.ptr(lr_state), ctypes.c_float(a), ctypes.c_float(b), ctypes.c_float(c),
+                                             ctypes.c_float(grad_scale), ctypes.c_int(max_blocks), ctypes.c_int(phases),
+                                             N.stream_ptr())
+        N.check(rc, "tdl_p2p_fused_step_wire")
 
     def fused_step(self, offset: int, n: int, *, kind: int, grad_is_bf16: bool, zero_grad: bool, m1, m2, lr_state,
                    a: float, b: float, c: float, grad_scale: float = 1.0, mode: int = 0, max_blocks: int = 64):

@@ -10,6 +10,15 @@ if ROOT not in sys.path:
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+    # The oracles of the GPU tests are "plain PyTorch fp32": keep them fp32.  With TF32 left on, cuDNN / cuBLAS round
+    # the reference's inputs to 10 mantissa bits -- barely more than the bf16 kernels under test carry.
+    try:
+        import torch
+
+        torch.backends.cudnn.allow_tf32 = False
+        torch.backends.cuda.matmul.allow_tf32 = False
+    except Exception:  # noqa: BLE001
+        pass
 
 
 def pytest_collection_modifyitems(config, items):

@@ -55,6 +55,75 @@ CONV_CASES = [
 ]
 
 
+def test_conv_at_the_benchmark_shape(O):
+    """ResNet-50's first 3x3 at the benchmark batch (N = 256, 56 x 56 x 64 -> 64): fprop, data gradient and weight
+    gradient against fp32 convolutions of the same bf16-rounded operands (the tiny-shape cases above cannot see
+    scheduling / wave-quantisation / 32-bit-offset errors that only appear with ~10^5 tiles)."""
+    torch.manual_seed(21)
+    N, H, C, K, R = 256, 56, 64, 64, 3
+    x = torch.randn(N, H, H, C, device="cuda").bfloat16()
+    w = (torch.randn(K, R * R, C, device="cuda") / math.sqrt(R * R * C)).bfloat16()
+    y = O.conv2d_fprop(x, w, R=R, S=R, pad_h=1, pad_w=1, out_hw=(H, H))
+    ref = _ref_conv(x, w, R, R, 1, 1, (1, 1, 1, 1))
+    assert rel_err(y, ref) < 1e-2
+    del ref
+    dy = torch.randn(N, H, H, K, device="cuda").bfloat16()
+    wd = w.float().view(K, R * R, C).flip(1).permute(2, 1, 0).contiguous().bfloat16()
+    dx = O.conv2d_fprop(dy, wd, R=R, S=R, pad_h=1, pad_w=1, out_hw=(H, H))
+    w4 = w.float().view(K, R, R, C).permute(0, 3, 1, 2).contiguous()
+    dxr = torch.nn.grad.conv2d_input((N, C, H, H), w4, dy.float().permute(0, 3, 1, 2), padding=1).permute(0, 2, 3, 1)
+    assert rel_err(dx, dxr) < 1e-2
+    del dxr
+    dw = torch.zeros(K, R * R, C, device="cuda")
+    O.conv2d_wgrad(x, dy, dw, R=R, S=R, pad_h=1, pad_w=1)
+    dwr = torch.nn.grad.conv2d_weight(x.float().permute(0, 3, 1, 2), (K, C, R, R), dy.float().permute(0, 3, 1, 2),
+                                      padding=1).permute(0, 2, 3, 1).reshape(K, R * R, C)
+    assert rel_err(dw, dwr) < 1e-2    # 802,816-term fp32 sums of bf16 products on both sides
+
+
+def test_tensors_past_two_gib(O):
+    """A 1x1 convolution whose OUTPUT is 3.3 GB (256 x 112 x 112 x 512 bf16) and BatchNorm over it: byte offsets
+    cross 2^31 and 2^32 inside one tensor.  Checked on slices from the start, the middle and the very end."""
+    torch.manual_seed(22)
+    N, H, C, K = 256, 112, 64, 512
+    x = torch.randn(N, H, H, C, device="cuda").bfloat16()
+    w = (torch.randn(K, 1, C, device="cuda") / 8).bfloat16()
+    y, partials, nparts = O.conv2d_fprop_stats(x, w, R=1, S=1, out_hw=(H, H))
+    assert y.numel() * 2 > (1 << 31) * 1.5
+    wf = w.float().view(K, C)
+    for n0 in (0, 127, 255):
+        ref = x[n0].float().reshape(-1, C) @ wf.t()
+        assert rel_err(y[n0].reshape(-1, K), ref) < 1e-2, n0
+    rows = N * H * H
+    gamma, beta = torch.rand(K, device="cuda") + 0.5, torch.randn(K, device="cuda") * 0.1
+    mean, invstd, scale, shift = O.bn_finalize_partials(partials[:nparts], nparts, rows, gamma, beta, None, None, 0.99,
+                                                        1e-3)
+    # statistics over all 3.2 M rows: compare with a chunked fp64 reduction of the stored tensor
+    s = torch.zeros(K, dtype=torch.float64, device="cuda")
+    q = torch.zeros(K, dtype=torch.float64, device="cuda")
+    for n0 in range(0, N, 16):
+        c = y[n0:n0 + 16].reshape(-1, K).double()
+        s += c.sum(0)
+        q += (c * c).sum(0)
+    m_ref = s / rows
+    v_ref = q / rows - m_ref * m_ref
+    assert rel_err(mean, m_ref.float()) < 1e-3 and rel_err(1 / invstd ** 2 - 1e-3, v_ref.float()) < 1e-3
+    z = O.bn_apply(y.view(rows, K), scale, shift, None, True)
+    for n0 in (0, 200, 255):
+        sl = slice(n0 * H * H, (n0 + 1) * H * H)
+        zr = (y.view(rows, K)[sl].float() * scale + shift).relu()
+        assert rel_err(z[sl], zr) < 1e-2, n0
+    del z
+    dz = torch.randn(rows, K, device="cuda", dtype=torch.bfloat16)
+    dx, _, dg, db = O.bn_bwd(dz, y.view(rows, K), None, scale, shift, mean, invstd, True, False)
+    sl = slice(rows - 4096, rows)   # the last rows of the tensor, > 3 GB into it
+    yl, dzl = y.view(rows, K)[sl].float(), dz[sl].float()
+    dyl = dzl * ((yl * scale + shift) > 0).float()
+    xhat = (yl - mean) * invstd
+    dxr = gamma * invstd * (dyl - db / rows - xhat * dg / rows)
+    assert rel_err(dx[sl], dxr) < 2e-2
+
+
 @pytest.fixture(params=[0, 1], ids=["tap_shifted", "halo_reuse"])
 def halo_mode(request):
     """Run the convolution cases with both main loops (the halo-reuse one is off by default: correct but slower)."""
@@ -276,25 +345,30 @@ def test_residual_units_backward_with_premasked_gradients():
     x0 = torch.randn(4, 16, 16, 64, device="cuda").bfloat16()
     g0 = torch.randn(4, 16, 16, 256, device="cuda").bfloat16()
     grads = {}
-    for name, flag in (("native", False), ("torch", True)):
+    for name, flag, dt in (("native", False, torch.bfloat16), ("torch_bf16", True, torch.bfloat16),
+                           ("torch_fp32", True, torch.float32)):
         Fn.force_reference(flag)
         try:
             Fn.begin_step()
             for p in units.parameters():
                 p.grad = None
-            x = x0.clone().requires_grad_(True)
+            x = x0.detach().clone().to(dt).requires_grad_(True)
             h = x
             for u in units:
                 h = u(h)
-            h.backward(g0)
+            h.backward(g0.to(dt))
             grads[name] = [x.grad.float().clone()] + [p.grad.float().clone() for p in units.parameters()]
         finally:
             Fn.force_reference(False)
-    if not grads["native"]:
-        pytest.fail("no gradients")
-    for a, b in zip(grads["native"], grads["torch"]):
-        cos = torch.nn.functional.cosine_similarity(a.flatten(), b.flatten(), dim=0)
-        assert float(cos) > 0.98, (a.shape, float(cos))
+
+    def l2(a, b):
+        return float((a - b).norm() / (b.norm() + 1e-12))
+
+    # bf16-justified bound instead of a direction check: against the fp32 run of the same graph, the native kernels may
+    # be at most twice as far off as the plain torch bf16 path is (same number format, different rounding points), with
+    # a floor of 2 % for tensors the bf16 path happens to hit almost exactly
+    for i, (a, b, f) in enumerate(zip(grads["native"], grads["torch_bf16"], grads["torch_fp32"])):
+        assert l2(a, f) <= max(2.0 * l2(b, f), 2e-2), (i, tuple(a.shape), l2(a, f), l2(b, f))
 
 
 def test_bn_backward_sums_taken_from_the_producing_dgrad_kernel():
@@ -677,6 +751,53 @@ def test_p2p_fused_step_emulated_ranks(O, world):
     pbuf.close()
 
 
+@pytest.mark.parametrize("world", [2, 8])
+def test_p2p_fused_step_bf16_wire_emulated_ranks(O, world):
+    """bf16 wire format on one GPU (all ranks' buffers local, barriers off): every rank's pack phase first, then every
+    rank's reduce phase.  The mean is the fp32 sum of the bf16-ROUNDED gradients in rank order -- exactly what the
+    reference below computes -- so the comparison stays tight; mirrors bit-identical; fp32 buckets cleared."""
+    from tensorflowdistributedlearning_b200.parallel.p2p import P2PComm, SymmetricBuffer
+
+    torch.manual_seed(9)
+    lr_state = torch.tensor([0.1, 0.05], device="cuda")
+    for n in (300_003, 4_099):      # two-shot with a ragged tail, and a one-shot sized bucket
+        npad = (n + 15) // 8 * 8
+        gbuf = SymmetricBuffer(npad * 4, emulate_world=world)
+        pbuf = SymmetricBuffer(npad * 4, emulate_world=world)
+        wbuf = SymmetricBuffer(npad * 2, emulate_world=world)
+        grads = [torch.randn(n, device="cuda") for _ in range(world)]
+        p0 = torch.randn(n, device="cuda")
+        for kind in (1, 2):
+            for mode in (1, 2):
+                for r in range(world):
+                    gbuf.tensor(torch.float32, r)[:n].copy_(grads[r])
+                    pbuf.tensor(torch.float32, r)[:n].copy_(p0)
+                comms = [P2PComm(gbuf, pbuf, emulate_rank=r) for r in range(world)]
+                for c in comms:
+                    c.set_wire(wbuf)
+                states = [(torch.zeros(npad, device="cuda"), torch.zeros(npad, device="cuda")) for _ in range(world)]
+                for phase in (1, 2):
+                    for r in range(world):
+                        comms[r].fused_step_wire(0, n, kind=kind, zero_grad=True, m1=states[r][0], m2=states[r][1],
+                                                 lr_state=lr_state, a=0.9, b=(1e-4 if kind == 1 else 0.999), c=1e-8,
+                                                 mode=mode, phases=phase)
+                torch.cuda.synchronize()
+                g = torch.zeros(n, device="cuda")
+                for t in grads:
+                    g = g + t.bfloat16().float()
+                g = g * (1.0 / world)
+                ref = ((p0 - 0.1 * (g + 1e-4 * p0)) if kind == 1
+                       else (p0 - 0.05 * (0.1 * g) / ((0.001 * g * g).sqrt() + 1e-8)))
+                for r in range(world):
+                    got = pbuf.tensor(torch.float32, r)[:n]
+                    assert rel_err(got, ref) < 1e-5, (n, kind, mode, r)
+                    assert torch.equal(got, pbuf.tensor(torch.float32, 0)[:n])
+                    assert float(gbuf.tensor(torch.float32, r)[:n].abs().max()) == 0.0
+                for c in comms:
+                    c.close()
+        gbuf.close(); pbuf.close(); wbuf.close()
+
+
 def test_trainer_step_native_matches_torch_path_and_learns():
     """Same weights, same batches: the native-kernel tower and the torch-op tower follow the same loss curve."""
     from tensorflowdistributedlearning_b200 import _native as N
@@ -779,7 +900,7 @@ def test_batched_weight_prep_matches_per_layer_launches(monkeypatch):
         out[mode] = (losses, y, tr.launches_per_step)
         tr.close()
     for a, b in zip(out["1"][0], out["0"][0]):
-        assert abs(a - b) <= 5e-3 * max(abs(a), abs(b)) + 1e-6, (out["1"][0], out["0"][0])
+        assert abs(a - b) <= 3e-2 * max(abs(a), abs(b)) + 1e-4, (out["1"][0], out["0"][0])
     assert rel_err(out["1"][1], out["0"][1]) < 2e-2
     assert out["1"][2] < out["0"][2] - 40, (out["1"][2], out["0"][2])
 

@@ -5,6 +5,7 @@ Each case launches ``scripts/p2p_check.py <mode>`` under torchrun and requires e
 say ``ok``:
   correctness -- one-shot / two-shot fused all-reduce + SGD-momentum / Adam vs the ordered fp32 reference, ragged tails,
                  mirrors bit-identical, gradients cleared; packed in-place mean (BN statistics / scalars)
+  wire        -- the same with gradients crossing NVLink as bf16 (packed and cleared inside the bucket kernel)
   stress      -- 3000 back-to-back small one-/two-shots with changing payloads (signal-pad races)
   train       -- ResNet-50 steps: p2p (eager, graph, overlap) vs the NCCL baseline path, mirrors identical
   resume      -- checkpoint at step 3 with the optimizer slots sharded over the towers, resume, compare with the
@@ -55,7 +56,7 @@ def _records(stdout):
 
 @needs2
 @pytest.mark.parametrize("world", WORLDS)
-@pytest.mark.parametrize("mode", ["correctness", "stress", "train", "resume"])
+@pytest.mark.parametrize("mode", ["correctness", "wire", "stress", "train", "resume"])
 def test_p2p(world, mode):
     r = _launch(world, [mode])
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
