@@ -786,6 +786,417 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
 }
 
 // ------------------------------------------------------------------------------------------
+// fprop on CTA pairs (cta_group::2)
+// ------------------------------------------------------------------------------------------
+// The single-CTA kernel above moves (128 + BLOCK_N) x 64 operand elements from L2 into shared memory for every
+// 128 x BLOCK_N x 64 MMA block.  With BLOCK_N = 256 that is 48 KB per 512 tensor-core cycles = 96 B/clk per SM, and all
+// 148 SMs together can pull only ~43 B/clk each out of L2: layers with enough arithmetic to be tensor-bound run at
+// ~45 % of the tensor peak because of operand traffic, not because of the MMA rate (this is also where a big cuBLAS
+// GEMM saturates on this chip).  Here two CTAs of a cluster (one TPC) share ONE M = 256 MMA: each CTA owns its own
+// 128-pixel tile (A operand, accumulator rows, epilogue) and loads only HALF of the weight tile; the tensor core reads
+// the two halves out of both CTAs' shared memory.  Operand bytes per CTA and stage drop from 48 KB to 32 KB
+// (BLOCK_N = 256) or 32 KB to 24 KB (BLOCK_N = 128), and the freed shared memory deepens the pipeline.
+//   * the even CTA of the pair issues every MMA (tcgen05.mma.cta_group::2) and owns the "full" barriers: both CTAs'
+//     TMA loads count their bytes on the leader's barrier (cp.async.bulk.tensor ... .cta_group::2);
+//   * tcgen05.commit ... .multicast::cluster frees a pipeline stage / publishes an accumulator in BOTH CTAs;
+//   * the epilogue warps of both CTAs hand their accumulator back by arriving on the leader's barrier.
+// Epilogue variants (bias / residual / ReLU, BatchNorm statistics, residual on the tensor core + mask) are the
+// single-CTA kernel's, per CTA.  Not here: the first-layer mode, halo mode, fused BatchNorm-backward sums.
+template <int BLOCK_N>
+struct Fprop2Cfg {
+  static constexpr int kBHalfBytes = (BLOCK_N / 2) * kBlockK * 2;
+  static constexpr int kStageBytes = kABytes + kBHalfBytes;
+  static constexpr int kAccBufs = BLOCK_N <= 128 ? 4 : 2;
+  static constexpr int kTmemCols = kAccBufs * BLOCK_N;
+  static constexpr int kOutBytes = 2 * kBlockM * 128;
+  static constexpr int kBarBytes = 256;
+  static constexpr int kAlignSlack = 384;
+  static constexpr int kStagesRaw = (227 * 1024 - kOutBytes - kAlignSlack - kBarBytes) / kStageBytes;
+  static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kOutBytes + kAlignSlack + kBarBytes;
+  static_assert((2 * kStages + 2 * kAccBufs) * 8 + 4 <= kBarBytes, "barrier region too small");
+};
+
+template <int BLOCK_N, bool kFused, bool kStats, bool kResMma>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kFpropThreads, 1)
+conv_fprop2_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_w,
+                   const __grid_constant__ CUtensorMap tm_y, const __grid_constant__ CUtensorMap tm_res,
+                   const __grid_constant__ CUtensorMap tm_id, const Geometry g, const float* __restrict__ bias,
+                   const bf16* __restrict__ residual, float* __restrict__ stats) {
+  ptx::pdl_trigger();
+  using Cfg = Fprop2Cfg<BLOCK_N>;
+  constexpr int kStages = Cfg::kStages;
+  constexpr int kAcc = Cfg::kAccBufs;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  if (smem - smem_raw > Cfg::kAlignSlack) {
+    if (threadIdx.x == 0) printf("tdl_b200: dynamic shared memory base is misaligned by %d bytes\n", (int)(smem - smem_raw));
+    __trap();
+  }
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + kStages * kABytes;
+  uint8_t* smem_out = smem + kStages * Cfg::kStageBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_out + Cfg::kOutBytes);
+  uint64_t* full_bar = bars;                 // used in the leader only: bytes of BOTH CTAs land on it
+  uint64_t* empty_bar = bars + kStages;      // per CTA: the leader's commit frees the stage in both
+  uint64_t* tmem_full = bars + 2 * kStages;  // per CTA
+  uint64_t* tmem_empty = tmem_full + kAcc;   // used in the leader only: 2 CTAs x 4 epilogue warps arrive
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + kAcc);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = ptx::cluster_ctarank();  // 0 = leader
+  const int pair = (int)blockIdx.x >> 1;
+  const int num_pairs = (int)gridDim.x >> 1;
+
+  const int m_tiles = g.tiles_n * g.tiles_h * g.tiles_w;
+  const int pair_tiles = ((m_tiles + 1) >> 1) * g.n_tiles;  // an odd last M tile pairs with an all-padding one
+  const int k_iters = g.R * g.S * g.num_kb;
+  const uint32_t a_tx = (uint32_t)(g.TN * g.TH * g.TW) * 128u;
+  const uint32_t stage_tx = 2u * (a_tx + (uint32_t)Cfg::kBHalfBytes);  // both CTAs' loads of one stage
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tm_x);
+    ptx::prefetch_tmap(&tm_w);
+    ptx::prefetch_tmap(&tm_y);
+    if constexpr (kResMma) {
+      ptx::prefetch_tmap(&tm_res);
+      ptx::prefetch_tmap(&tm_id);
+    }
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int i = 0; i < kStages; ++i) {
+        ptx::mbar_init(&full_bar[i], 1);
+        ptx::mbar_init(&empty_bar[i], 1);
+      }
+      for (int i = 0; i < kAcc; ++i) {
+        ptx::mbar_init(&tmem_full[i], 1);
+        ptx::mbar_init(&tmem_empty[i], 8);  // one arrival per epilogue warp of the draining group, from both CTAs
+      }
+      ptx::fence_mbar_init();
+    }
+    __syncwarp();
+    ptx::tmem_alloc_pair<Cfg::kTmemCols>(tmem_slot);
+  }
+  ptx::pdl_wait();
+  if constexpr (kStats) {
+    float* slot = stats + (size_t)blockIdx.x * 2 * g.K;
+    for (int i = threadIdx.x; i < 2 * g.K; i += kFpropThreads) slot[i] = 0.f;
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::cluster_sync_all();  // both CTAs' barriers are initialised and both TMEM allocations are done
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer (both CTAs: own A tile, own half of the weight tile) =====================
+    const bool leader_lane = ptx::elect_one();
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int pt = pair; pt < pair_tiles; pt += num_pairs) {
+      const int n_tile = pt % g.n_tiles;
+      const int m_tile = 2 * (pt / g.n_tiles) + (int)rank;  // may be == m_tiles: every coordinate out of range = zeros
+      const int tw_i = m_tile % g.tiles_w;
+      const int th_i = (m_tile / g.tiles_w) % g.tiles_h;
+      const int tn_i = m_tile / (g.tiles_w * g.tiles_h);
+      const int w_in = tw_i * g.TW * g.stride - g.pad_w;
+      const int h_in = th_i * g.TH * g.stride - g.pad_h;
+      const int n_in = tn_i * g.TN;
+      const int co_half = n_tile * BLOCK_N + (int)rank * (BLOCK_N / 2);
+      int tap = g.tap_base, kb = 0, r = 0, s = 0;
+      for (int it = 0; it < k_iters; ++it) {
+        ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+        if (leader_lane) {
+          if (rank == 0) ptx::mbar_expect_tx(&full_bar[stage], stage_tx);
+          ptx::tma_load_4d_pair(smem_a + stage * kABytes, &tm_x, &full_bar[stage], kb * kBlockK, w_in + s * g.dil,
+                                h_in + r * g.dil, n_in);
+          ptx::tma_load_3d_pair(smem_b + stage * Cfg::kBHalfBytes, &tm_w, &full_bar[stage], kb * kBlockK, tap, co_half);
+        }
+        if (++stage == kStages) {
+          stage = 0;
+          phase ^= 1;
+        }
+        if (++kb == g.num_kb) {
+          kb = 0;
+          tap += g.tap_ss;
+          if (++s == g.S) {
+            s = 0;
+            ++r;
+            tap = g.tap_base + r * g.tap_sr;
+          }
+        }
+      }
+      if constexpr (kResMma) {
+        const int res_chunks = min(BLOCK_N / 64, (g.K - n_tile * BLOCK_N + 63) / 64);
+        for (int j = 0; j < res_chunks; ++j) {
+          ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+          if (leader_lane) {
+            if (rank == 0) ptx::mbar_expect_tx(&full_bar[stage], 2u * (a_tx + 4096u));
+            ptx::tma_load_4d_pair(smem_a + stage * kABytes, &tm_res, &full_bar[stage], n_tile * BLOCK_N + j * 64,
+                                  tw_i * g.TW, th_i * g.TH, tn_i * g.TN);
+            // this CTA's 32 rows of the 64 x 64 identity block
+            ptx::tma_load_2d_pair(smem_b + stage * Cfg::kBHalfBytes, &tm_id, &full_bar[stage], 0, (int)rank * 32);
+          }
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer: the leader CTA only =====================
+    if (rank == 0) {
+      const bool leader_lane = ptx::elect_one();
+      constexpr uint32_t idesc = ptx::umma_idesc_bf16(2 * kBlockM, BLOCK_N, 0, 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int pt = pair; pt < pair_tiles; pt += num_pairs) {
+        ptx::mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+        ptx::tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BLOCK_N);
+        for (int it = 0; it < k_iters; ++it) {
+          ptx::mbar_wait(&full_bar[stage], phase);
+          ptx::tc_fence_after();
+          const uint64_t a_desc = ptx::umma_smem_desc_sw128(ptx::smem_u32(smem_a + stage * kABytes), 16, 1024);
+          const uint64_t b_desc = ptx::umma_smem_desc_sw128(ptx::smem_u32(smem_b + stage * Cfg::kBHalfBytes), 16, 1024);
+          if (leader_lane) {
+#pragma unroll
+            for (int k = 0; k < kBlockK / 16; ++k)
+              ptx::umma_bf16_pair(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc,
+                                  (it > 0 || k > 0) ? 1u : 0u);
+            ptx::umma_commit_pair(&empty_bar[stage]);  // frees the stage in both CTAs
+          }
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        if constexpr (kResMma) {
+          constexpr uint32_t idesc64 = ptx::umma_idesc_bf16(2 * kBlockM, 64, 0, 0);
+          const int n_tile = pt % g.n_tiles;
+          const int res_chunks = min(BLOCK_N / 64, (g.K - n_tile * BLOCK_N + 63) / 64);
+          for (int j = 0; j < res_chunks; ++j) {
+            ptx::mbar_wait(&full_bar[stage], phase);
+            ptx::tc_fence_after();
+            const uint64_t a_desc = ptx::umma_smem_desc_sw128(ptx::smem_u32(smem_a + stage * kABytes), 16, 1024);
+            const uint64_t b_desc =
+                ptx::umma_smem_desc_sw128(ptx::smem_u32(smem_b + stage * Cfg::kBHalfBytes), 16, 1024);
+            if (leader_lane) {
+#pragma unroll
+              for (int k = 0; k < kBlockK / 16; ++k)
+                ptx::umma_bf16_pair(d_tmem + (uint32_t)(j * 64), a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k),
+                                    idesc64, 1u);
+              ptx::umma_commit_pair(&empty_bar[stage]);
+            }
+            if (++stage == kStages) {
+              stage = 0;
+              phase ^= 1;
+            }
+          }
+        }
+        if (leader_lane) ptx::umma_commit_pair(&tmem_full[acc]);  // accumulator complete in both CTAs
+        if (++acc == kAcc) {
+          acc = 0;
+          acc_phase ^= 1;
+        }
+      }
+    }
+  } else {
+    // ===================== epilogue warps (per CTA, as in the single-CTA kernel) =====================
+    const int ewarp = warp - kEpiWarp0;
+    const int group = ewarp >> 2;
+    const int quarter = warp & 3;
+    const int row = quarter * 32 + lane;
+    const int patch = g.TH * g.TW;
+    const int dn = row / patch;
+    const int rem = row - dn * patch;
+    const int dh = rem / g.TW;
+    const int dw = rem - dh * g.TW;
+    const bool row_in_patch = row < g.TN * patch;
+    const bool issuer = ((ewarp & 3) == 0 && lane == 0);
+    const int bar_id = 1 + group;
+    const uint32_t row_off = (uint32_t)row * 128u;
+    const uint32_t sw = (uint32_t)(row & 7);
+    const uint32_t tmem_lane = tmem_base + ((uint32_t)(quarter * 32) << 16);
+    uint8_t* out_tile = smem_out + group * (kBlockM * 128);
+    constexpr int kChunks = BLOCK_N / 64;
+    float sacc[kChunks][4];
+#pragma unroll
+    for (int c = 0; c < kChunks; ++c) sacc[c][0] = sacc[c][1] = sacc[c][2] = sacc[c][3] = 0.f;
+    int stat_n_tile = -1;
+    auto flush_stats = [&](int nt) {
+      if (issuer) ptx::tma_store_wait_read<0>();
+      ptx::named_bar_sync(bar_id, 128);
+      float* st = reinterpret_cast<float*>(out_tile);
+#pragma unroll
+      for (int c = 0; c < kChunks; ++c)
+#pragma unroll
+        for (int v = 0; v < 4; ++v) {
+          st[((quarter * kChunks + c) * 4 + v) * 32 + lane] = sacc[c][v];
+          sacc[c][v] = 0.f;
+        }
+      ptx::named_bar_sync(bar_id, 128);
+      float* slot = stats + (size_t)blockIdx.x * 2 * g.K;
+      for (int idx = quarter * 32 + lane; idx < kChunks * 128; idx += 128) {
+        const int c = idx >> 7, v = (idx >> 5) & 3, ln = idx & 31;
+        float tot = 0.f;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) tot += st[((e * kChunks + c) * 4 + v) * 32 + ln];
+        const int ch = nt * BLOCK_N + c * 64 + 2 * ln + (v >> 1);
+        if (ch < g.K) atomicAdd(&slot[(size_t)(v & 1) * g.K + ch], tot);
+      }
+      ptx::named_bar_sync(bar_id, 128);
+    };
+    uint32_t tile_count = (uint32_t)group;
+    for (int pt = pair + group * num_pairs; pt < pair_tiles; pt += 2 * num_pairs, tile_count += 2) {
+      const int acc = (int)(tile_count % kAcc);
+      const uint32_t acc_phase = (tile_count / kAcc) & 1u;
+      const int n_tile = pt % g.n_tiles;
+      const int m_tile = 2 * (pt / g.n_tiles) + (int)rank;
+      const bool real_tile = m_tile < m_tiles;
+      const int tw_i = m_tile % g.tiles_w;
+      const int th_i = (m_tile / g.tiles_w) % g.tiles_h;
+      const int tn_i = m_tile / (g.tiles_w * g.tiles_h);
+      bool valid = true;
+      size_t pix = 0;
+      if constexpr (kFused || kStats || kResMma) {
+        const int n = tn_i * g.TN + dn;
+        const int p = th_i * g.TH + dh;
+        const int q = tw_i * g.TW + dw;
+        valid = real_tile && row_in_patch && n < g.N && p < g.P && q < g.Q;
+        pix = ((size_t)n * g.P + p) * g.Q + q;
+      }
+      const int chunks = min(BLOCK_N / 64, (g.K - n_tile * BLOCK_N + 63) / 64);
+      uint32_t vm = 0xffffffffu;
+      if constexpr (kStats) {
+        if (n_tile != stat_n_tile) {
+          if (stat_n_tile >= 0) flush_stats(stat_n_tile);
+          stat_n_tile = n_tile;
+        }
+        vm = __ballot_sync(0xffffffffu, valid);
+      }
+      ptx::mbar_wait(&tmem_full[acc], acc_phase);
+      ptx::tc_fence_after();
+#pragma unroll
+      for (int cc = 0; cc < kChunks; ++cc) {
+        if (cc >= chunks) break;
+        const int co_chunk = n_tile * BLOCK_N + cc * 64;
+        if (issuer) ptx::tma_store_wait_read<0>();
+        ptx::named_bar_sync(bar_id, 128);
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          uint32_t v[32];
+          ptx::tmem_ld_32x32(tmem_lane + (uint32_t)(acc * BLOCK_N + cc * 64 + half * 32), v);
+          ptx::tmem_ld_wait();
+          if (half == 1 && cc == chunks - 1) {
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive_leader(&tmem_empty[acc]);  // the MMA warp lives in the leader CTA
+          }
+          const int co0 = co_chunk + half * 32;
+          float f[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+          if constexpr (kFused) {
+#pragma unroll
+            for (int j8 = 0; j8 < 4; ++j8) {
+              const int co = co0 + j8 * 8;
+              if (co < g.K) {
+                if (g.has_bias) {
+                  const float4 b0 = *reinterpret_cast<const float4*>(bias + co);
+                  const float4 b1 = *reinterpret_cast<const float4*>(bias + co + 4);
+                  f[j8 * 8 + 0] += b0.x; f[j8 * 8 + 1] += b0.y; f[j8 * 8 + 2] += b0.z; f[j8 * 8 + 3] += b0.w;
+                  f[j8 * 8 + 4] += b1.x; f[j8 * 8 + 5] += b1.y; f[j8 * 8 + 6] += b1.z; f[j8 * 8 + 7] += b1.w;
+                }
+                if (g.has_res && valid) {
+                  float rr[8];
+                  unpack8(ld8(residual + pix * g.K + co), rr);
+#pragma unroll
+                  for (int j = 0; j < 8; ++j) f[j8 * 8 + j] += rr[j];
+                }
+                if (g.relu) {
+#pragma unroll
+                  for (int j = 0; j < 8; ++j) f[j8 * 8 + j] = fmaxf(f[j8 * 8 + j], 0.f);
+                }
+              }
+            }
+          }
+          if constexpr (kResMma) {
+            if (g.has_mask && valid && co0 < g.K) {
+              const uint8_t* mrow = reinterpret_cast<const uint8_t*>(residual) + pix * (size_t)(g.K >> 3) + (co0 >> 3);
+              const uint32_t mbits = *reinterpret_cast<const uint32_t*>(mrow);
+#pragma unroll
+              for (int j = 0; j < 32; ++j) f[j] = ((mbits >> j) & 1u) ? f[j] : 0.f;
+            }
+          }
+          uint32_t packed[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const __nv_bfloat162 h2 = __floats2bfloat162_rn(f[2 * j], f[2 * j + 1]);
+            packed[j] = *reinterpret_cast<const uint32_t*>(&h2);
+          }
+#pragma unroll
+          for (int j8 = 0; j8 < 4; ++j8) {
+            const uint32_t chunk16 = (uint32_t)(half * 4 + j8);
+            *reinterpret_cast<uint4*>(out_tile + row_off + ((chunk16 ^ sw) << 4)) =
+                make_uint4(packed[j8 * 4], packed[j8 * 4 + 1], packed[j8 * 4 + 2], packed[j8 * 4 + 3]);
+          }
+        }
+        ptx::fence_proxy_async_smem();
+        ptx::named_bar_sync(bar_id, 128);
+        if (issuer && real_tile) {
+          ptx::tma_store_4d(&tm_y, out_tile, co_chunk, tw_i * g.TW, th_i * g.TH, tn_i * g.TN);
+          ptx::tma_store_commit();
+        }
+        if constexpr (kStats) {
+          const uint8_t* rows = out_tile + (uint32_t)(quarter * 32) * 128u + ((uint32_t)(lane & 3) << 2);
+          const uint32_t c16 = (uint32_t)(lane >> 2);
+          float s0 = 0.f, q0 = 0.f, s1 = 0.f, q1 = 0.f;
+#pragma unroll
+          for (int i0 = 0; i0 < 32; i0 += 16) {
+            uint32_t wv[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i)
+              wv[i] = *reinterpret_cast<const uint32_t*>(rows + (i0 + i) * 128 + ((c16 ^ (uint32_t)(i & 7)) << 4));
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              const bool ok = (vm >> (i0 + i)) & 1u;
+              const float f0 = ok ? __uint_as_float(wv[i] << 16) : 0.f;
+              const float f1 = ok ? __uint_as_float(wv[i] & 0xffff0000u) : 0.f;
+              s0 += f0;
+              q0 = fmaf(f0, f0, q0);
+              s1 += f1;
+              q1 = fmaf(f1, f1, q1);
+            }
+          }
+          sacc[cc][0] += s0;
+          sacc[cc][1] += q0;
+          sacc[cc][2] += s1;
+          sacc[cc][3] += q1;
+        }
+      }
+    }
+    if constexpr (kStats) {
+      if (stat_n_tile >= 0) flush_stats(stat_n_tile);
+    }
+    if (issuer) ptx::tma_store_wait_all<0>();
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::cluster_sync_all();  // neither CTA may release TMEM / shared memory while its partner can still touch it
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc_pair<Cfg::kTmemCols>(tmem_base);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
 // wgrad kernel:  dW[co, tap, ci] += sum_pixels dY[pixel, co] * X[pixel shifted by tap, ci]
 // GEMM M = Cout (128), N = Cin (BLOCK_N), K = pixels (64 per stage).  Both operands are stored
 // with the GEMM-K (pixel) index as the *row* of a 128B-swizzled tile, i.e. MN-major.
@@ -1398,6 +1809,53 @@ static int launch_fprop(const CUtensorMap& tx, const CUtensorMap& tw, const CUte
   return launch_fprop_t<BLOCK_N, false, false>(tx, tw, ty, tres, tid, tbx, g, bias, res, stats, nparts, st);
 }
 
+template <int BLOCK_N, bool kFused, bool kStats, bool kResMma>
+static int launch_fprop2_t(const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& ty, const CUtensorMap& tres,
+                           const CUtensorMap& tid, const Geometry& g, const float* bias, const bf16* res, float* stats,
+                           int* nparts, cudaStream_t st) {
+  using Cfg = Fprop2Cfg<BLOCK_N>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    TDL_CUDA_OK(cudaFuncSetAttribute(conv_fprop2_kernel<BLOCK_N, kFused, kStats, kResMma>,
+                                     cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    attr_set = true;
+  }
+  const int m_tiles = g.tiles_n * g.tiles_h * g.tiles_w;
+  const int pair_tiles = ((m_tiles + 1) / 2) * g.n_tiles;
+  const int max_pairs = tdl::num_sms() / 2;
+  const int pairs = pair_tiles < max_pairs ? pair_tiles : max_pairs;
+  const int grid = 2 * pairs;  // clusters of two CTAs (compile-time __cluster_dims__)
+  if (nparts) *nparts = grid;
+  {
+    cudaError_t _le = tdl::launch_pdl(conv_fprop2_kernel<BLOCK_N, kFused, kStats, kResMma>, dim3(grid),
+                                      dim3(kFpropThreads), Cfg::kSmemBytes, st, tx, tw, ty, tres, tid, g, bias, res,
+                                      stats);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "conv_fprop2_kernel");
+  }
+  TDL_LAUNCH_OK("conv_fprop2_kernel");
+  return 0;
+}
+
+// CTA-pair variants (see conv_fprop2_kernel); same dispatch as launch_fprop without the BatchNorm-backward form
+template <int BLOCK_N>
+static int launch_fprop2(const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& ty, const CUtensorMap& tres,
+                         const CUtensorMap& tid, const Geometry& g, const float* bias, const bf16* res, float* stats,
+                         int* nparts, cudaStream_t st) {
+  if (g.res_mma) {
+    if (stats) return launch_fprop2_t<BLOCK_N, true, true, true>(tx, tw, ty, tres, tid, g, bias, res, stats, nparts, st);
+    if (g.has_bias || g.relu)
+      return launch_fprop2_t<BLOCK_N, true, false, true>(tx, tw, ty, tres, tid, g, bias, res, stats, nparts, st);
+    return launch_fprop2_t<BLOCK_N, false, false, true>(tx, tw, ty, tres, tid, g, bias, res, stats, nparts, st);
+  }
+  const bool fused = g.has_bias || g.has_res || g.relu;
+  if (stats) {
+    if (fused) return launch_fprop2_t<BLOCK_N, true, true, false>(tx, tw, ty, tres, tid, g, bias, res, stats, nparts, st);
+    return launch_fprop2_t<BLOCK_N, false, true, false>(tx, tw, ty, tres, tid, g, bias, res, stats, nparts, st);
+  }
+  if (fused) return launch_fprop2_t<BLOCK_N, true, false, false>(tx, tw, ty, tres, tid, g, bias, res, stats, nparts, st);
+  return launch_fprop2_t<BLOCK_N, false, false, false>(tx, tw, ty, tres, tid, g, bias, res, stats, nparts, st);
+}
+
 // 64x64 bf16 identity block in global memory (the B operand of the residual-on-the-tensor-core iterations)
 __device__ __align__(1024) bf16 g_identity64[64 * 64];
 __global__ void identity64_init_kernel() {
@@ -1502,6 +1960,9 @@ struct TapSel {
   int w_taps, base, sr, ss;
 };
 
+// CTA-pair (cta_group::2) kernel for Cout tiles of 128 / 256: -1 = read TDL_CONV_2CTA on first use, 0 = off, 1 = on
+static int g_pair_mode = -1;
+
 static int g_halo_mode = -1;  // -1 = read TDL_HALO on first use, 0 = off (default), 1 = on, 2 = on with base offsets
 
 static int fprop_impl(const void* x, const void* w, void* y, const float* bias, const void* residual, int N, int H,
@@ -1591,6 +2052,16 @@ static int fprop_impl(const void* x, const void* w, void* y, const float* bias, 
   }
   const int block_n = K > 128 ? 256 : (K > 64 ? 128 : 64);
   g.n_tiles = (int)cdiv(K, block_n);
+  if (g_pair_mode < 0) {
+    const char* e = getenv("TDL_CONV_2CTA");
+    g_pair_mode = e ? atoi(e) : 1;
+  }
+  // CTA pairs: M = 256 MMAs, each CTA loads half of the weight tile (conv_fprop2_kernel).  Needs at least two M tiles,
+  // and a K loop of at least four stages: with fewer (e.g. 1x1 128 -> 512) the per-tile hand-over between two CTAs
+  // costs more than the halved weight traffic saves (measured 0.93x there, 1.05-1.12x on the deep layers,
+  // profiles/conv_pair_timing.txt).
+  const bool pair = g_pair_mode != 0 && !g.halo && !bnb && block_n >= 128 &&
+                    g.tiles_n * g.tiles_h * g.tiles_w >= 2 && R * S * g.num_kb >= 4;
 
   CUtensorMap tx, tw;
   {
@@ -1607,7 +2078,7 @@ static int fprop_impl(const void* x, const void* w, void* y, const float* bias, 
   }
   {
     uint64_t dims[3] = {(uint64_t)C, (uint64_t)(taps ? taps->w_taps : R * S), (uint64_t)K};
-    uint32_t box[3] = {64, 1, (uint32_t)block_n};
+    uint32_t box[3] = {64, 1, (uint32_t)(pair ? block_n / 2 : block_n)};
     uint32_t es[3] = {1, 1, 1};
     int rc = encode_bf16(&tw, w, 3, dims, box, es);
     if (rc) return rc;
@@ -1641,7 +2112,7 @@ static int fprop_impl(const void* x, const void* w, void* y, const float* bias, 
     rc = identity64_address(&ident, st);
     if (rc) return rc;
     uint64_t idims[2] = {64, 64};
-    uint32_t ibox[2] = {64, 64};
+    uint32_t ibox[2] = {64, (uint32_t)(pair ? 32 : 64)};
     rc = encode_bf16(&tid, ident, 2, idims, ibox, es);
     if (rc) return rc;
   }
@@ -1655,6 +2126,10 @@ static int fprop_impl(const void* x, const void* w, void* y, const float* bias, 
     uint32_t es[4] = {1, 1, 1, 1};
     int rc = encode_bf16(&tbx, bnb->x, 4, dims, box, es);
     if (rc) return rc;
+  }
+  if (pair) {
+    if (block_n == 256) return launch_fprop2<256>(tx, tw, ty, tres, tid, g, bias, aux, stats, nparts, st);
+    return launch_fprop2<128>(tx, tw, ty, tres, tid, g, bias, aux, stats, nparts, st);
   }
   if (block_n == 256) return launch_fprop<256>(tx, tw, ty, tres, tid, tbx, g, bias, aux, stats, nparts, st);
   if (block_n == 128) return launch_fprop<128>(tx, tw, ty, tres, tid, tbx, g, bias, aux, stats, nparts, st);
@@ -2015,6 +2490,14 @@ TDL_API int tdl_conv_stem_wgrad(const void* planes, const void* dy, float* dwp_s
   TDL_LAUNCH_OK("stem_wgrad_unpack_kernel");
   return 0;
 }
+
+// 0 = single-CTA MMAs, 1 = CTA pairs (cta_group::2, M = 256) for convolutions with Cout tiles of 128 / 256
+TDL_API int tdl_conv2d_set_pair_mode(int mode) {
+  TDL_REQUIRE(mode == 0 || mode == 1, "pair mode must be 0 or 1");
+  g_pair_mode = mode;
+  return 0;
+}
+TDL_API int tdl_conv2d_get_pair_mode() { return g_pair_mode < 0 ? 0 : g_pair_mode; }
 
 // Experimental: 0 = tap-shifted loads (default), 1 = halo reuse for stride-1 RxS filters on maps >= 12x12 (one patch load
 // per 64-channel block, taps read it at a row shift), 2 = the same with "matrix base offset" set (known wrong on B200).

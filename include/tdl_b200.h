@@ -37,6 +37,8 @@ int tdl_conv2d_fprop_bf16(const void* x, const void* w, void* y, const float* bi
 int tdl_conv2d_fprop_res_mask_bf16(const void* x, const void* w, void* y, const void* residual, const void* out_mask,
                                    int N, int H, int W, int C, int K, int R, int S, int stride, int dil, int pad_h,
                                    int pad_w, int P, int Q, void* stream);
+int tdl_conv2d_set_pair_mode(int mode); /* 1 = CTA pairs (tcgen05 cta_group::2, M = 256 MMAs, half a weight tile per CTA) for Cout tiles of 128/256; also TDL_CONV_2CTA */
+int tdl_conv2d_get_pair_mode(void);
 int tdl_conv2d_set_halo_mode(int mode); /* experimental halo-reuse main loop for stride-1 RxS filters: 0 off (default), 1 on */
 int tdl_conv2d_fprop_stats_bf16(const void* x, const void* w, void* y, const float* bias, int N, int H, int W, int C,
                                 int K, int R, int S, int stride, int dil, int pad_h, int pad_w, int P, int Q,

@@ -55,6 +55,55 @@ CONV_CASES = [
 ]
 
 
+def test_conv_cta_pairs_match_single_cta(O):
+    """cta_group::2 kernel (two CTAs share one M = 256 MMA, each loads half of the weight tile): same accumulation order
+    per output element as the single-CTA kernel, so the results must be bit-identical -- plain, fused epilogue,
+    BatchNorm statistics, residual on the tensor core with the 1-bit mask, odd M-tile counts, ragged channels."""
+    import ctypes
+
+    from tensorflowdistributedlearning_b200 import _native as N
+
+    lib = N.lib()
+    was = int(lib.tdl_conv2d_get_pair_mode())
+    cases = [(4, 14, 128, 512, 1, 1, 1, True, True, True), (3, 13, 72, 136, 3, 1, 1, False, False, False),
+             (8, 7, 512, 512, 3, 1, 1, False, False, False), (2, 13, 128, 128, 3, 1, 8, False, False, False),
+             (2, 56, 256, 512, 1, 2, 1, False, False, False), (5, 5, 256, 1032, 1, 1, 1, True, True, True),
+             (1, 9, 256, 256, 1, 1, 1, False, False, False)]
+    try:
+        for (n, h, c, k, r, stride, dil, use_b, use_r, relu) in cases:
+            torch.manual_seed(1)
+            x = torch.randn(n, h, h, c, device="cuda").bfloat16()
+            w = (torch.randn(k, r * r, c, device="cuda") / math.sqrt(r * r * c)).bfloat16()
+            b = torch.randn(k, device="cuda") if use_b else None
+            P, pt, pb = O.same_pad(h, r, stride, dil)
+            res = torch.randn(n, P, P, k, device="cuda").bfloat16() if use_r else None
+            outs, sts = {}, {}
+            for mode in (0, 1):
+                lib.tdl_conv2d_set_pair_mode(ctypes.c_int(mode))
+                outs[mode] = O.conv2d_fprop(x, w, R=r, S=r, stride=stride, dil=dil, pad_h=pt, pad_w=pt, out_hw=(P, P),
+                                            bias=b, residual=res, relu=relu)
+                if not use_r and not relu:
+                    y, partials, nparts = O.conv2d_fprop_stats(x, w, R=r, S=r, stride=stride, dil=dil, pad_h=pt,
+                                                               pad_w=pt, out_hw=(P, P), bias=b)
+                    sts[mode] = (y, partials[:nparts].double().sum(0))
+            assert torch.equal(outs[0], outs[1]), (n, h, c, k, r)
+            assert rel_err(outs[1], _ref_conv(x, w, r, r, stride, dil, (pt, pb, pt, pb), b, res, relu)) < 1e-2
+            if sts:
+                assert torch.equal(sts[0][0], sts[1][0]) and rel_err(sts[1][1], sts[0][1]) < 1e-6
+        for (n, h, c, k) in ((4, 14, 64, 256), (3, 13, 128, 1024)):
+            dy = torch.randn(n, h, h, c, device="cuda").bfloat16()
+            wd = (torch.randn(k, 1, c, device="cuda") / math.sqrt(c)).bfloat16()
+            res = torch.randn(n, h, h, k, device="cuda").bfloat16()
+            mask = torch.randint(0, 256, (n * h * h, k // 8), dtype=torch.uint8, device="cuda")
+            outs = {}
+            for mode in (0, 1):
+                lib.tdl_conv2d_set_pair_mode(ctypes.c_int(mode))
+                outs[mode] = O.conv2d_fprop(dy, wd, R=1, S=1, out_hw=(h, h), residual=res, out_mask=mask)
+            assert torch.equal(outs[0], outs[1])
+    finally:
+        lib.tdl_conv2d_set_pair_mode(ctypes.c_int(was))
+
+
 def test_conv_at_the_benchmark_shape(O):
     """ResNet-50's first 3x3 at the benchmark batch (N = 256, 56 x 56 x 64 -> 64): fprop, data gradient and weight
     gradient against fp32 convolutions of the same bf16-rounded operands (the tiny-shape cases above cannot see
