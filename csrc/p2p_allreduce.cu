@@ -41,6 +41,7 @@ struct Comm {
   bf16* wire[kMaxWorld];       // peer-mapped bf16 "wire" copies of the gradient buckets (same element offsets), or null
   unsigned long long timeout_ns;  // how long a CTA waits for a peer before it reports and traps
   int* status;                 // host-mapped: [0] = 1 when a wait timed out, [1..4] = rank, CTA, peer, epoch
+  uint32_t* debug_seen;        // debug builds of the protocol (TDL_P2P_DEBUG=1): [kMaxBlocks][kMaxWorld] last value seen
 };
 
 enum OptKind { kNone = 0, kSgdMomentum = 1, kAdam = 2 };
@@ -82,6 +83,35 @@ __device__ __forceinline__ void cross_rank_barrier(const Comm& cm, uint32_t epoc
     const uint32_t* mine = cm.flags[cm.rank] + (size_t)blockIdx.x * kMaxWorld + peer;
     unsigned long long t0 = 0;
     uint32_t spins = 0;
+    if (cm.debug_seen) {
+      // protocol assertions (race detection for the signal pads): what peer `peer` wrote for this CTA must
+      // never go backwards, and a peer can be at most ONE barrier ahead of us (it cannot pass barrier e+1 before we
+      // arrive at it).  A violation means a lost / reordered / foreign write into the pad: report it and stop.
+      uint32_t* seen = cm.debug_seen + (size_t)blockIdx.x * kMaxWorld + peer;
+      for (;;) {
+        const uint32_t v = ld_acquire_sys(mine);
+        const bool backwards = (int32_t)(v - *seen) < 0;
+        const bool too_far = (int32_t)(v - epoch) > 1;
+        if (backwards || too_far) {
+          if (cm.status) {
+            cm.status[1] = cm.rank; cm.status[2] = (int)blockIdx.x; cm.status[3] = peer; cm.status[4] = (int)v;
+            __threadfence_system();
+            cm.status[0] = backwards ? 2 : 3;
+            __threadfence_system();
+          }
+          printf("tdl_b200 p2p DEBUG: rank %d CTA %d peer %d: signal %u after %u while waiting for epoch %u (%s)\n",
+                 cm.rank, (int)blockIdx.x, peer, v, *seen, epoch, backwards ? "went backwards" : "too far ahead");
+          __trap();
+        }
+        *seen = v;
+        if ((int32_t)(v - epoch) >= 0) break;
+        if ((++spins & 1023u) == 0) {
+          const unsigned long long now = ptx_globaltimer();
+          if (t0 == 0) t0 = now;
+          if (now - t0 > cm.timeout_ns) break;  // fall through to the timeout report below
+        }
+      }
+    }
     while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0) {
       if ((++spins & 1023u) != 0) continue;  // look at the wall clock every 1024 polls
       const unsigned long long now = ptx_globaltimer();
@@ -689,6 +719,14 @@ TDL_API int tdl_p2p_comm_set_timeout(void* comm, double seconds) {
   Comm* c = (Comm*)comm;
   TDL_REQUIRE(c != nullptr, "null communicator");
   if (seconds > 0) c->timeout_ns = (unsigned long long)(seconds * 1e9);
+  return 0;
+}
+// Turns the signal-pad protocol assertions on: `seen` is a zeroed device array of kMaxBlocks * kMaxWorld u32 owned by
+// the caller (NULL turns them off).  Status codes 2 / 3 (tdl_p2p_comm_status) = "signal went backwards" / "too far ahead".
+TDL_API int tdl_p2p_comm_set_debug(void* comm, void* seen) {
+  Comm* c = (Comm*)comm;
+  TDL_REQUIRE(c != nullptr, "null communicator");
+  c->debug_seen = (uint32_t*)seen;
   return 0;
 }
 // Reads the status word: out5 = {timed_out, rank, cta, peer, epoch}.  Plain host memory: safe to call after a CUDA

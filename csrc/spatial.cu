@@ -303,6 +303,90 @@ gap_bwd_kernel(const bf16* __restrict__ dy, bf16* __restrict__ dx, int64_t total
 }
 
 // ------------------------------------------------------------------------------------------
+// global average pool folded into the 1x1 convolution that follows it (the "image pooling" branch of the
+// reference's ASPP: reduce_mean -> 1x1 conv, core/resnet.py:464-466).  out[n, k] = sum_c mean_hw(x[n, :, :, c]) * w[k, c].
+// The pooled vector never goes to memory as an activation (only as the small fp32 [N, C] tensor the weight gradient
+// needs), and the M = N "GEMM" with a handful of rows does not occupy a 128-row tensor-core tile that is ~75 % padding.
+// ------------------------------------------------------------------------------------------
+constexpr int kGapKT = 64;  // output channels per CTA
+
+__global__ void __launch_bounds__(kThreads)
+gap_conv1x1_fwd_kernel(const bf16* __restrict__ x, const float* __restrict__ w, bf16* __restrict__ y,
+                       float* __restrict__ gap_out, int HW, int C, int K) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
+  extern __shared__ float gap[];  // [C]
+  const int n = blockIdx.x;
+  const int c8 = C >> 3;
+  const float inv = 1.f / (float)HW;
+  // phase 1: mean over the HW pixels of image n, 8 channels per thread-visit
+  for (int cv = threadIdx.x; cv < c8; cv += kThreads) {
+    float s[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s[j] = 0.f;
+    for (int r = 0; r < HW; ++r) {
+      float f[8];
+      unpack8(ld8(x + ((int64_t)n * HW + r) * C + cv * 8), f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s[j] += f[j];
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      gap[cv * 8 + j] = s[j] * inv;
+      if (blockIdx.y == 0) gap_out[(int64_t)n * C + cv * 8 + j] = s[j] * inv;
+    }
+  }
+  __syncthreads();
+  // phase 2: one warp per output channel, kGapKT channels per CTA
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int kk = warp; kk < kGapKT; kk += kThreads / 32) {
+    const int k = blockIdx.y * kGapKT + kk;
+    if (k >= K) break;
+    const float* wr = w + (int64_t)k * C;
+    float acc = 0.f;
+    for (int c = lane; c < C; c += 32) acc = fmaf(gap[c], wr[c], acc);
+    acc = warp_sum(acc);
+    if (lane == 0) y[(int64_t)n * K + k] = __float2bfloat16(acc);
+  }
+}
+
+// dx[n, r, c] = (sum_k dy[n, k] * w[k, c]) / HW
+__global__ void __launch_bounds__(kThreads)
+gap_conv1x1_bwd_data_kernel(const bf16* __restrict__ dy, const float* __restrict__ w, bf16* __restrict__ dx, int HW,
+                            int C, int K) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
+  __shared__ __align__(16) bf16 dg[kThreads];
+  const int n = blockIdx.x;
+  const int c = blockIdx.y * kThreads + threadIdx.x;
+  float acc = 0.f;
+  if (c < C)
+    for (int k = 0; k < K; ++k) acc = fmaf(__bfloat162float(dy[(int64_t)n * K + k]), w[(int64_t)k * C + c], acc);
+  dg[threadIdx.x] = __float2bfloat16(acc / (float)HW);
+  __syncthreads();
+  const int c0 = blockIdx.y * kThreads;
+  const int nvec = min(kThreads, C - c0) >> 3;  // 16-byte vectors of this CTA's channel chunk
+  for (int i = threadIdx.x; i < HW * nvec; i += kThreads) {
+    const int r = i / nvec, v = i - r * nvec;
+    st8(dx + ((int64_t)n * HW + r) * C + c0 + v * 8, ld8(dg + v * 8));
+  }
+}
+
+// dw[k, c] += sum_n dy[n, k] * gap[n, c]
+__global__ void __launch_bounds__(kThreads)
+gap_conv1x1_bwd_weight_kernel(const bf16* __restrict__ dy, const float* __restrict__ gap, float* __restrict__ dw, int N,
+                              int C, int K) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
+  const int k = blockIdx.x;
+  const int c = blockIdx.y * kThreads + threadIdx.x;
+  if (c >= C) return;
+  float acc = 0.f;
+  for (int n = 0; n < N; ++n) acc = fmaf(__bfloat162float(dy[(int64_t)n * K + k]), gap[(int64_t)n * C + c], acc);
+  dw[(int64_t)k * C + c] += acc;
+}
+
+// ------------------------------------------------------------------------------------------
 // depthwise convolution, weights [R*S, C] fp32
 // ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kThreads)
@@ -642,6 +726,42 @@ TDL_API int tdl_gap_bwd(const void* dy, void* dx, int N, int HW, int C, void* st
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "gap_bwd_kernel");
   }
   TDL_LAUNCH_OK("gap_bwd_kernel");
+  return 0;
+}
+
+// y[N, K] (bf16) = mean_hw(x[N, HW, C]) . w[K, C]^T (fp32 master weights); gap_out [N, C] fp32 keeps the pooled vectors
+// for the weight gradient.  C % 8 == 0, C <= 12288 (the pooled vector lives in shared memory).
+TDL_API int tdl_gap_conv1x1_fwd(const void* x, const float* w, void* y, float* gap_out, int N, int HW, int C, int K,
+                                void* stream) {
+  TDL_REQUIRE(C % 8 == 0 && C > 0 && C <= 12288, "C must be a multiple of 8, at most 12288");
+  TDL_REQUIRE(N >= 1 && K >= 1 && HW >= 1 && gap_out != nullptr, "bad shape");
+  dim3 grid(N, (unsigned)cdiv(K, kGapKT));
+  cudaError_t e = tdl::launch_pdl(gap_conv1x1_fwd_kernel, grid, dim3(kThreads), (size_t)C * sizeof(float),
+                                  (cudaStream_t)stream, (const bf16*)x, w, (bf16*)y, gap_out, HW, C, K);
+  if (e != cudaSuccess) return tdl::cuda_fail(e, "gap_conv1x1_fwd_kernel");
+  TDL_LAUNCH_OK("gap_conv1x1_fwd_kernel");
+  return 0;
+}
+// dx [N, HW, C] bf16 (written) and dw [K, C] fp32 (ACCUMULATED into) of the fused pool + 1x1; either may be NULL.
+TDL_API int tdl_gap_conv1x1_bwd(const void* dy, const float* w, const float* gap, void* dx, float* dw, int N, int HW,
+                                int C, int K, void* stream) {
+  TDL_REQUIRE(C % 8 == 0 && C > 0, "C must be a multiple of 8");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dx) {
+    dim3 grid(N, (unsigned)cdiv(C, kThreads));
+    cudaError_t e = tdl::launch_pdl(gap_conv1x1_bwd_data_kernel, grid, dim3(kThreads), 0, st, (const bf16*)dy, w,
+                                    (bf16*)dx, HW, C, K);
+    if (e != cudaSuccess) return tdl::cuda_fail(e, "gap_conv1x1_bwd_data_kernel");
+    TDL_LAUNCH_OK("gap_conv1x1_bwd_data_kernel");
+  }
+  if (dw) {
+    TDL_REQUIRE(gap != nullptr, "the pooled vectors are needed for the weight gradient");
+    dim3 grid(K, (unsigned)cdiv(C, kThreads));
+    cudaError_t e = tdl::launch_pdl(gap_conv1x1_bwd_weight_kernel, grid, dim3(kThreads), 0, st, (const bf16*)dy, gap,
+                                    dw, N, C, K);
+    if (e != cudaSuccess) return tdl::cuda_fail(e, "gap_conv1x1_bwd_weight_kernel");
+    TDL_LAUNCH_OK("gap_conv1x1_bwd_weight_kernel");
+  }
   return 0;
 }
 

@@ -131,6 +131,12 @@ int tdl_bn_bwd_apply(const void* dz, const void* x, const void* z, int z_is_bitm
                      const float* dbeta, void* dx, void* dres, int64_t rows, int C, int relu, void* stream);
 
 /* ---- spatial ops (reference: core/resnet.py:241,246-248,464-465; core/layers.py:34-42,82-109) ---- */
+/* global average pool folded into the 1x1 convolution that follows (the ASPP image-pooling branch, core/resnet.py:464-466):
+ * y [N,K] bf16 = mean_hw(x [N,HW,C]) . w [K,C]^T, w = fp32 master weights; gap_out [N,C] fp32 is kept for the backward.
+ * bwd: dx [N,HW,C] bf16 written, dw [K,C] fp32 accumulated into (either may be NULL) */
+int tdl_gap_conv1x1_fwd(const void* x, const float* w, void* y, float* gap_out, int N, int HW, int C, int K, void* stream);
+int tdl_gap_conv1x1_bwd(const void* dy, const float* w, const float* gap, void* dx, float* dw, int N, int HW, int C, int K,
+                        void* stream);
 /* 3x3 / stride-2 max-pool fused with the partial BatchNorm statistics of its output (the reference's pool1 ->
  * postnorm, core/resnet.py:241-242): stats_partial [*nparts][2][C], rows = tdl_maxpool_stats_rows(); 256 % (C/8) == 0 */
 int tdl_maxpool_stats_rows(int N, int C, int P, int Q);
@@ -260,6 +266,9 @@ int tdl_p2p_comm_create(int world, int rank, void** grad_ptrs, void** param_ptrs
  * epoch) and works after the trap has poisoned the CUDA context */
 int tdl_p2p_comm_set_timeout(void* comm, double seconds);
 int tdl_p2p_comm_status(void* comm, int* out5);
+/* protocol assertions for the signal pads (debug: TDL_P2P_DEBUG=1): every poll checks that a peer's epoch never goes
+ * backwards and is at most one barrier ahead; `seen` = zeroed device array of 256 * 8 u32 (NULL = off) */
+int tdl_p2p_comm_set_debug(void* comm, void* seen);
 /* bf16 wire format: gradients accumulate in fp32 buckets but cross NVLink as bf16 (the cast is fused into the bucket
  * kernel: phase 1 packs + clears the fp32 bucket, phase 2 reduces the peers' bf16 copies in fp32 and runs the optimizer).
  * wire_ptrs[rank] = peer-mapped bf16 buffers with the gradient buckets' element offsets. */

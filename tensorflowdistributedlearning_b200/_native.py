@@ -116,7 +116,7 @@ def lib() -> ctypes.CDLL:
 
 
 # kernels launched per C-ABI entry point (default 1); used for the bench's "gpu_launches" count
-_KERNELS_PER_CALL = {"tdl_bn_fwd_stats": 2, "tdl_bn_bwd_reduce": 2, "tdl_depthwise_bwd": 2}
+_KERNELS_PER_CALL = {"tdl_bn_fwd_stats": 2, "tdl_bn_bwd_reduce": 2, "tdl_depthwise_bwd": 2, "tdl_gap_conv1x1_bwd": 2}
 kernel_launches = 0
 
 

@@ -433,18 +433,23 @@ class ResNetSegModel(TFModule):
         feat = ep[self.block4_key]
         size = feat.shape[1:3]
         low = ep[self.low_key]
-        pooled_in = L.global_avg_pool(feat, keepdims=True)
         if TF._native_ok(feat) and all(m.bn.c_p % 8 == 0 for m in (self.aspp_1x1, self.aspp_pool, self.dec_1x1)):
+            from ..ops import pooling as PL
+
+            # K10: image pooling = global mean folded into its 1x1 convolution (core/resnet.py:464-466), one kernel
+            pooled_y = PL.gap_conv1x1(feat, self.aspp_pool.conv.weight)
             # K12: no concatenation -- every branch's BatchNorm (the pooled branch: BatchNorm + `_upsample`) writes
             # its channel slice of ONE buffer (core/resnet.py:470); same for the decoder's pair (core/resnet.py:485)
             aspp_in = TF.batch_norm_concat(
                 [self._branch(self.aspp_1x1, feat)] +
                 [self._branch(m.pointwise, m.depthwise(feat)) for m in self.aspp_sep] +
-                [self._branch(self.aspp_pool, pooled_in, upsample=True)], size)
+                [{"x": pooled_y, "bn": self.aspp_pool.bn, "relu": self.aspp_pool.relu, "stats": None,
+                  "upsample": True}], size)
             aspp = self.aspp_out(aspp_in)
             dec = TF.batch_norm_concat([self._branch(self.dec_1x1, low), {"x": aspp, "bn": None, "upsample": True}],
                                        low.shape[1:3])
         else:
+            pooled_in = L.global_avg_pool(feat, keepdims=True)
             branches = [self.aspp_1x1(feat)] + [m(feat) for m in self.aspp_sep]
             branches.append(L.upsample(self.aspp_pool(pooled_in), size))
             aspp = self.aspp_out(torch.cat(branches, dim=-1))

@@ -521,6 +521,31 @@ def maxpool_bwd(dy, idx, in_shape, k, stride, pad_h, pad_w):
     return dx
 
 
+def gap_conv1x1_fwd(x, w_master):
+    """y [N, 1, 1, K] = mean_hw(x [N, H, W, C]) . w [K, C]^T in one kernel; also returns the pooled vectors [N, C] fp32."""
+    _chk_bf16_nhwc(x, "x")
+    n, h, wd, c = x.shape
+    k = w_master.shape[0]
+    assert w_master.dtype == torch.float32 and w_master.is_contiguous() and w_master.numel() == k * c
+    y = torch.empty((n, 1, 1, k), dtype=torch.bfloat16, device=x.device)
+    gap = torch.empty((n, c), dtype=torch.float32, device=x.device)
+    rc = N.lib().tdl_gap_conv1x1_fwd(N.ptr(x), N.ptr(w_master), N.ptr(y), N.ptr(gap), _i(n), _i(h * wd), _i(c), _i(k),
+                                     N.stream_ptr())
+    N.check(rc, "tdl_gap_conv1x1_fwd")
+    return y, gap
+
+
+def gap_conv1x1_bwd(dy, w_master, gap, in_shape, want_dx: bool, dw: Optional[torch.Tensor]):
+    """dx [N,H,W,C] bf16 (if ``want_dx``) and ``dw`` [K, C] fp32 += (if given) of the fused pool + 1x1."""
+    n, h, wd, c = in_shape
+    k = w_master.shape[0]
+    dx = torch.empty(in_shape, dtype=torch.bfloat16, device=dy.device) if want_dx else None
+    rc = N.lib().tdl_gap_conv1x1_bwd(N.ptr(dy), N.ptr(w_master), N.ptr(gap), N.ptr(dx), N.ptr(dw), _i(n), _i(h * wd),
+                                     _i(c), _i(k), N.stream_ptr())
+    N.check(rc, "tdl_gap_conv1x1_bwd")
+    return dx
+
+
 def gap_fwd(x):
     _chk_bf16_nhwc(x, "x")
     n, h, w, c = x.shape

@@ -72,6 +72,52 @@ class _GapNative(torch.autograd.Function):
         return O.gap_bwd(dy.contiguous(), ctx.shape)
 
 
+class _GapConv1x1(torch.autograd.Function):
+    """Global average pool folded into the 1x1 convolution that follows it (core/resnet.py:464-466)."""
+
+    @staticmethod
+    def forward(ctx, x, weight):
+        from . import native_ops as O
+
+        K = weight.shape[0]
+        w2 = weight.detach().view(K, -1)
+        y, gap = O.gap_conv1x1_fwd(x, w2)
+        TF._count(1)
+        ctx.save_for_backward(gap)
+        ctx.weight_param, ctx.in_shape = weight, tuple(x.shape)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        from . import native_ops as O
+
+        (gap,) = ctx.saved_tensors
+        wp = ctx.weight_param
+        K = wp.shape[0]
+        dy2 = dy.contiguous().view(-1, K)
+        direct = TF._direct_ok(wp)
+        dw = None
+        if ctx.needs_input_grad[1]:
+            dw = wp.grad.view(K, -1) if direct else torch.zeros((K, gap.shape[1]), dtype=torch.float32, device=dy.device)
+        dx = O.gap_conv1x1_bwd(dy2, wp.detach().view(K, -1), gap, ctx.in_shape, ctx.needs_input_grad[0], dw)
+        TF._count(2)
+        if direct and dw is not None:
+            TF._notify(wp)
+            dw = None
+        return dx, (None if dw is None else dw.view(wp.shape))
+
+
+def gap_conv1x1(x: torch.Tensor, weight: torch.Tensor) -> torch.Tensor:
+    """[N,H,W,C] -> [N,1,1,K]: conv1x1(global_avg_pool(x)) with ``weight`` [K,1,1,C] (fp32 master, no bias), one kernel
+    on the GPU when the shape suits the fused kernel (few images x few output channels: the seg-net's pooling branch)."""
+    n, h, w, c = x.shape
+    K = weight.shape[0]
+    if (TF._native_ok(x) and c % 8 == 0 and c <= 12288 and tuple(weight.shape[1:3]) == (1, 1) and weight.shape[3] == c
+            and weight.is_contiguous() and n * ((K + 63) // 64) <= 4096 and n <= 256):
+        return _GapConv1x1.apply(x.contiguous(), weight)
+    return TF.conv2d(global_avg_pool(x, keepdims=True), weight)
+
+
 def global_avg_pool(x: torch.Tensor, keepdims: bool = True) -> torch.Tensor:
     """mean over H, W of NHWC -> [N,1,1,C] (keepdims) or [N,C]."""
     n, h, w, c = x.shape

@@ -11,6 +11,7 @@ TensorFlow for the reference (model.py:115-119).
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import List, Optional
 
 import torch
@@ -133,10 +134,13 @@ class P2PComm:
         self.wire = None
         # the device-side wait limit follows the host-side collective timeout (a hard-coded 2 s limit killed
         # every tower when one of them stalled in its input pipeline); TDL_P2P_TIMEOUT_S overrides it on its own
-        import os
-
         limit = float(os.environ.get("TDL_P2P_TIMEOUT_S", os.environ.get("TDL_COLLECTIVE_TIMEOUT_S", "600")))
         N.check(lib.tdl_p2p_comm_set_timeout(self.handle, ctypes.c_double(limit)), "tdl_p2p_comm_set_timeout")
+        self._debug_seen = None
+        if os.environ.get("TDL_P2P_DEBUG", "0") == "1":
+            # protocol assertions on every signal-pad poll (epochs monotone per (CTA, peer), at most one barrier ahead)
+            self._debug_seen = torch.zeros(256 * 8, dtype=torch.int32, device="cuda")
+            N.check(lib.tdl_p2p_comm_set_debug(self.handle, N.ptr(self._debug_seen)), "tdl_p2p_comm_set_debug")
         self.has_multicast = bool(grad.mc_ptr and param is not None and param.mc_ptr)
         if self.has_multicast:
             N.check(lib.tdl_p2p_comm_set_multicast(self.handle, ctypes.c_void_p(grad.mc_ptr),
@@ -191,7 +195,8 @@ class P2PComm:
         N.lib().tdl_p2p_comm_status(self.handle, out)
         if not out[0]:
             return None
-        return {"rank": out[1], "cta": out[2], "peer": out[3], "epoch": out[4]}
+        why = {1: "timeout", 2: "signal went backwards", 3: "signal too far ahead"}.get(out[0], str(out[0]))
+        return {"rank": out[1], "cta": out[2], "peer": out[3], "epoch": out[4], "why": why}
 
     def close(self):
         if self.handle is not None:

@@ -55,6 +55,86 @@ CONV_CASES = [
 ]
 
 
+def test_gap_folded_into_the_following_1x1_conv(O):
+    """conv1x1(global_avg_pool(x)) in one kernel (the ASPP image-pooling branch), forward and both gradients
+    against fp32 torch ops on the same bf16-rounded activations."""
+    from tensorflowdistributedlearning_b200.ops import pooling as PL
+
+    torch.manual_seed(31)
+    for (n, h, c, k) in ((32, 13, 1024, 256), (5, 7, 72, 40)):
+        x = torch.randn(n, h, h, c, device="cuda").bfloat16().requires_grad_(True)
+        w = (torch.randn(k, 1, 1, c, device="cuda") / math.sqrt(c)).requires_grad_(True)
+        y = PL.gap_conv1x1(x, w)
+        assert type(y.grad_fn).__name__.startswith("_GapConv1x1") and y.shape == (n, 1, 1, k)
+        g = torch.randn_like(y)
+        y.backward(g)
+        xr = x.detach().float().requires_grad_(True)
+        wr = w.detach().clone().requires_grad_(True)
+        yr = xr.mean((1, 2)) @ wr.view(k, c).t()
+        yr.backward(g.float().view(n, k))
+        assert rel_err(y.view(n, k), yr) < 1e-2
+        assert rel_err(x.grad, xr.grad) < 1e-2
+        assert rel_err(w.grad.view(k, c), wr.grad.view(k, c)) < 1e-2
+
+
+def test_max_pool_fused_postnorm_statistics(O):
+    """the 3x3 / stride-2 pool leaves the partial BatchNorm statistics of its output (pool1 -> postnorm)."""
+    from tensorflowdistributedlearning_b200.ops import pooling as PL
+
+    torch.manual_seed(32)
+    for (n, h, c) in ((32, 51, 128), (3, 17, 64)):
+        x = torch.randn(n, h, h, c, device="cuda").bfloat16()
+        y0 = PL.max_pool_same(x, 3, 2)
+        y, stats = PL.max_pool_same(x, 3, 2, want_stats=True)
+        assert stats is not None and torch.equal(y, y0)
+        yf = y.float().reshape(-1, c)
+        tot = stats.double().sum(0)
+        assert rel_err(tot[0], yf.double().sum(0)) < 1e-5 and rel_err(tot[1], (yf.double() ** 2).sum(0)) < 1e-5
+
+
+def test_batch_norm_branches_written_into_channel_slices(O):
+    """BatchNorm(+ReLU) branches (one of them resized by the reference's `_upsample`, one plain resize)
+    normalised straight into channel slices of one buffer == torch.cat of the separately computed branches, and the
+    gradients read the slices of the buffer's gradient in place."""
+    from tensorflowdistributedlearning_b200.ops import functional as Fn
+    from tensorflowdistributedlearning_b200.ops import layers as L
+
+    torch.manual_seed(33)
+    n, h = 4, 13
+    bns = [L.BatchNorm(c, 0.99, 1e-3).cuda().train() for c in (64, 72, 32)]
+    for bn in bns:
+        torch.nn.init.uniform_(bn.gamma, 0.5, 1.5)
+        torch.nn.init.normal_(bn.beta, std=0.1)
+    xs = [torch.randn(n, h, h, 64, device="cuda").bfloat16(), torch.randn(n, h, h, 72, device="cuda").bfloat16(),
+          torch.randn(n, 1, 1, 32, device="cuda").bfloat16(), torch.randn(n, 7, 7, 40, device="cuda").bfloat16()]
+    outs = {}
+    for name in ("sliced", "cat"):
+        for bn in bns:
+            bn.zero_grad(set_to_none=True)
+            bn.moving_mean.zero_()
+            bn.moving_variance.fill_(1.0)
+        leaves = [t.clone().requires_grad_(True) for t in xs]
+        if name == "sliced":
+            y = Fn.batch_norm_concat([{"x": leaves[0], "bn": bns[0], "relu": True}, {"x": leaves[1], "bn": bns[1], "relu": False},
+                                      {"x": leaves[2], "bn": bns[2], "relu": True, "upsample": True},
+                                      {"x": leaves[3], "bn": None, "upsample": True}], (h, h))
+        else:
+            y = torch.cat([bns[0](leaves[0], relu=True), bns[1](leaves[1], relu=False),
+                           L.upsample(bns[2](leaves[2], relu=True), (h, h)), L.upsample(leaves[3], (h, h))], dim=-1)
+        g = torch.randn(n, h, h, 64 + 72 + 32 + 40, device="cuda", generator=torch.Generator("cuda").manual_seed(5)).bfloat16()
+        y.backward(g)
+        outs[name] = (y.detach().clone(), [t.grad.clone() for t in leaves],
+                      [bn.gamma.grad.clone() for bn in bns] + [bn.beta.grad.clone() for bn in bns],
+                      [bn.moving_mean.clone() for bn in bns])
+    assert torch.equal(outs["sliced"][0], outs["cat"][0])
+    for a, b in zip(outs["sliced"][1], outs["cat"][1]):
+        assert rel_err(a, b) < 1e-2
+    for a, b in zip(outs["sliced"][2], outs["cat"][2]):
+        assert rel_err(a, b) < 1e-3
+    for a, b in zip(outs["sliced"][3], outs["cat"][3]):
+        assert torch.equal(a, b)
+
+
 def test_conv_cta_pairs_match_single_cta(O):
     """cta_group::2 kernel (two CTAs share one M = 256 MMA, each loads half of the weight tile): same accumulation order
     per output element as the single-CTA kernel, so the results must be bit-identical -- plain, fused epilogue,
