@@ -639,40 +639,6 @@ TDL_API int tdl_bn_bwd_finalize_partials(const float* partial, int nparts, int C
   return 0;
 }
 
-// addend ([rows, C] bf16, may be NULL): added to dx (a second gradient of the BatchNorm's input, e.g. a residual unit's
-// identity shortcut).  mask_by_x != 0: the input x is a ReLU output; dx is zeroed where x == 0 (that ReLU's backward).
-TDL_API int tdl_bn_bwd_apply_ex(const void* dz, const void* x, const void* z, int z_is_bitmask, const float* scale,
-                                const float* shift, const float* mean, const float* invstd, const float* dgamma,
-                                const float* dbeta, void* dx, void* dres, int64_t rows, int C, int relu, int64_t ld_dz,
-                                const void* addend, int mask_by_x, void* stream) {
-  TDL_REQUIRE(C > 0 && C % 8 == 0, "C must be a positive multiple of 8");
-  TDL_REQUIRE(ld_dz >= C && ld_dz % 8 == 0, "ld_dz must be a multiple of 8, at least C");
-  if (rows == 0) return 0;
-  ReduceShape s = apply_shape(rows, C);
-  dim3 grid(s.gx, s.gy);
-  {
-    cudaError_t _le = tdl::launch_pdl(bn_bwd_apply_kernel, dim3(grid), dim3(kThreads), 0, (cudaStream_t)stream,
-        (const bf16*)dz, (const bf16*)x, (const bf16*)z, scale, shift, mean, invstd, dbeta, dgamma, 1.f / (float)rows,
-        (bf16*)dx, (bf16*)dres, rows, C, s.tx, s.ty, relu, z_is_bitmask, ld_dz, (const bf16*)addend, mask_by_x);
-    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "bn_bwd_apply_kernel");
-  }
-  TDL_LAUNCH_OK("bn_bwd_apply_kernel");
-  return 0;
-}
-TDL_API int tdl_bn_bwd_apply_ld(const void* dz, const void* x, const void* z, int z_is_bitmask, const float* scale,
-                                const float* shift, const float* mean, const float* invstd, const float* dgamma,
-                                const float* dbeta, void* dx, void* dres, int64_t rows, int C, int relu, int64_t ld_dz,
-                                void* stream) {
-  return tdl_bn_bwd_apply_ex(dz, x, z, z_is_bitmask, scale, shift, mean, invstd, dgamma, dbeta, dx, dres, rows, C, relu,
-                             ld_dz, nullptr, 0, stream);
-}
-TDL_API int tdl_bn_bwd_apply(const void* dz, const void* x, const void* z, int z_is_bitmask, const float* scale,
-                             const float* shift, const float* mean, const float* invstd, const float* dgamma, const float* dbeta,
-                             void* dx, void* dres, int64_t rows, int C, int relu, void* stream) {
-  return tdl_bn_bwd_apply_ld(dz, x, z, z_is_bitmask, scale, shift, mean, invstd, dgamma, dbeta, dx, dres, rows, C, relu,
-                             C, stream);
-}
-
 // ------------------------------------------------------------------------------------------------------------
 // Finalize folded into the apply kernels (thread-block clusters + distributed shared memory).
 //
@@ -873,12 +839,14 @@ __device__ __forceinline__ void apply_mask(float* g, const float* f, const float
 }
 
 // ---- backward reduce, specialised per mask source, four rows in flight ----
+// (four resident CTAs per SM for the bit-mask variant: it fits 64 registers without spilling and gains ~5 % from the
+//  extra loads in flight; the recompute variant spills at 64 and measured slower, profiles/bn_fold_experiment.txt)
 template <int MODE>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, MODE == 2 ? 4 : 1)
 bn_bwd_partial_t_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ x, const void* __restrict__ zraw,
                         const float* __restrict__ scale, const float* __restrict__ shift,
                         const float* __restrict__ mean, const float* __restrict__ invstd, int64_t rows, int C, int tx,
-                        int ty, float* __restrict__ partial) {
+                        int ty, float* __restrict__ partial, int64_t ld_dz) {
   ptx::pdl_trigger();
   ptx::pdl_wait();
   extern __shared__ float sm[];
@@ -921,7 +889,7 @@ bn_bwd_partial_t_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ x,
       int mb[U];
 #pragma unroll
       for (int u = 0; u < U; ++u) {
-        gv[u] = ld8(dz + (r + u * step) * C + col);
+        gv[u] = ld8(dz + (r + u * step) * ld_dz + col);
         xv[u] = ld8(x + (r + u * step) * C + col);
         if constexpr (MODE == kBits) mb[u] = zb[(r + u * step) * c8 + cv];
         if constexpr (MODE == kFromZ) zv[u] = ld8(zt + (r + u * step) * C + col);
@@ -930,7 +898,7 @@ bn_bwd_partial_t_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ x,
       for (int u = 0; u < U; ++u) one(gv[u], xv[u], mb[u], zv[u]);
     }
     for (; r < rows; r += step) {
-      bf16x8 gv = ld8(dz + r * C + col), xv = ld8(x + r * C + col), zv;
+      bf16x8 gv = ld8(dz + r * ld_dz + col), xv = ld8(x + r * C + col), zv;
       int mb = 0;
       if constexpr (MODE == kBits) mb = zb[r * c8 + cv];
       if constexpr (MODE == kFromZ) zv = ld8(zt + r * C + col);
@@ -1058,6 +1026,89 @@ bn_bwd_apply_fin_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ x,
   }
 }
 
+// ---- backward apply, specialised per mask source (the generic kernel above carries every variant's registers) ----
+// dx = A*dy + B*x + D (+ addend) (masked by x > 0); dres = dy.  kExtra compiles the addend / mask_by_x handling in.
+template <int MODE, bool kDres, bool kExtra>
+__global__ void __launch_bounds__(kThreads)
+bn_bwd_apply_t_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ x, const void* __restrict__ zraw,
+                      const float* __restrict__ scale, const float* __restrict__ shift,
+                      const float* __restrict__ mean, const float* __restrict__ invstd,
+                      const float* __restrict__ dbeta, const float* __restrict__ dgamma, float inv_n,
+                      bf16* __restrict__ dx, bf16* __restrict__ dres, int64_t rows, int C, int tx, int ty,
+                      int64_t ld_dz, const bf16* __restrict__ addend, int mask_by_x) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
+  const int cx = threadIdx.x % tx;
+  const int ry = threadIdx.x / tx;
+  const int cv = blockIdx.y * tx + cx;
+  if (cv >= C / 8) return;
+  float sc[8], sh[8], B[8], D[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int c = cv * 8 + j;
+    sc[j] = scale[c];
+    if constexpr (MODE == kRecompute) sh[j] = shift[c];
+    const float k = sc[j] * invstd[c] * dgamma[c] * inv_n;
+    B[j] = -k;
+    D[j] = k * mean[c] - sc[j] * dbeta[c] * inv_n;
+  }
+  const int64_t step = (int64_t)gridDim.x * ty;
+  const int64_t col = (int64_t)cv * 8;
+  const int c8 = C >> 3;
+  const uint8_t* zb = reinterpret_cast<const uint8_t*>(zraw);
+  const bf16* zt = reinterpret_cast<const bf16*>(zraw);
+  auto one = [&](int64_t r, const bf16x8& gv, const bf16x8& xv, int mb, const bf16x8& zv, const bf16x8& av) {
+    float g[8], f[8], o[8];
+    unpack8(gv, g);
+    unpack8(xv, f);
+    apply_mask<MODE>(g, f, sc, sh, mb, zv);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = fmaf(sc[j], g[j], fmaf(B[j], f[j], D[j]));
+    if constexpr (kExtra) {
+      if (addend) {
+        float a[8];
+        unpack8(av, a);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] += a[j];
+      }
+      if (mask_by_x) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = f[j] > 0.f ? o[j] : 0.f;
+      }
+    }
+    st8(dx + r * C + col, pack8(o));
+    if constexpr (kDres) st8(dres + r * C + col, pack8(g));
+  };
+  constexpr int U = 2;
+  int64_t r = (int64_t)blockIdx.x * ty + ry;
+  for (; r + (U - 1) * step < rows; r += U * step) {
+    bf16x8 gv[U], xv[U], zv[U], av[U];
+    int mb[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      gv[u] = ld8(dz + (r + u * step) * ld_dz + col);
+      xv[u] = ld8(x + (r + u * step) * C + col);
+      if constexpr (MODE == kBits) mb[u] = zb[(r + u * step) * c8 + cv];
+      if constexpr (MODE == kFromZ) zv[u] = ld8(zt + (r + u * step) * C + col);
+      if constexpr (kExtra) {
+        if (addend) av[u] = ld8(addend + (r + u * step) * C + col);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) one(r + u * step, gv[u], xv[u], mb[u], zv[u], av[u]);
+  }
+  for (; r < rows; r += step) {
+    bf16x8 gv = ld8(dz + r * ld_dz + col), xv = ld8(x + r * C + col), zv, av;
+    int mb = 0;
+    if constexpr (MODE == kBits) mb = zb[r * c8 + cv];
+    if constexpr (MODE == kFromZ) zv = ld8(zt + r * C + col);
+    if constexpr (kExtra) {
+      if (addend) av = ld8(addend + r * C + col);
+    }
+    one(r, gv, xv, mb, zv, av);
+  }
+}
+
 // Launch as clusters of `cl` CTAs along x (cl divides grid.x), with the programmatic-launch attribute when enabled.
 template <typename... KArgs, typename... Args>
 static cudaError_t launch_clustered(void (*kernel)(KArgs...), dim3 grid, int cl, size_t smem, cudaStream_t st,
@@ -1160,14 +1211,16 @@ TDL_API int tdl_bn_partial_stats(const void* x, int64_t rows, int C, float* scra
 
 // Partial rows of (sum dy, sum dy * xhat), dy = dz with the ReLU mask applied: the reduction half of
 // tdl_bn_bwd_reduce, specialised per mask source.  Feed scratch / *nparts to tdl_bn_bwd_apply_fused.
-TDL_API int tdl_bn_bwd_partial(const void* dz, const void* x, const void* z, int z_is_bitmask, const float* scale,
-                               const float* shift, const float* mean, const float* invstd, int64_t rows, int C,
-                               int relu, float* scratch, int64_t scratch_floats, int* nparts, void* stream) {
+TDL_API int tdl_bn_bwd_partial_ld(const void* dz, const void* x, const void* z, int z_is_bitmask, const float* scale,
+                                  const float* shift, const float* mean, const float* invstd, int64_t rows, int C,
+                                  int relu, int64_t ld_dz, float* scratch, int64_t scratch_floats, int* nparts,
+                                  void* stream) {
   TDL_REQUIRE(C > 0 && C % 8 == 0, "C must be a positive multiple of 8");
   TDL_REQUIRE(rows > 0 && nparts, "bad arguments");
+  TDL_REQUIRE(ld_dz >= C && ld_dz % 8 == 0, "ld_dz must be a multiple of 8, at least C");
   const int mode = mask_mode(relu, z, z_is_bitmask);
   void (*kern)(const bf16*, const bf16*, const void*, const float*, const float*, const float*, const float*, int64_t,
-               int, int, int, float*) =
+               int, int, int, float*, int64_t) =
       mode == kNoRelu ? bn_bwd_partial_t_kernel<kNoRelu>
       : mode == kRecompute ? bn_bwd_partial_t_kernel<kRecompute>
       : mode == kBits ? bn_bwd_partial_t_kernel<kBits> : bn_bwd_partial_t_kernel<kFromZ>;
@@ -1175,11 +1228,17 @@ TDL_API int tdl_bn_bwd_partial(const void* dz, const void* x, const void* z, int
   TDL_REQUIRE(scratch_floats >= (int64_t)s.gx * 2 * C, "scratch too small (see tdl_bn_scratch_floats)");
   cudaError_t e = tdl::launch_pdl(kern, dim3(s.gx, s.gy), dim3(kThreads), kThreads * 16 * sizeof(float),
                                   (cudaStream_t)stream, (const bf16*)dz, (const bf16*)x, z, scale, shift, mean, invstd,
-                                  rows, C, s.tx, s.ty, scratch);
+                                  rows, C, s.tx, s.ty, scratch, ld_dz);
   if (e != cudaSuccess) return tdl::cuda_fail(e, "bn_bwd_partial_t_kernel");
   TDL_LAUNCH_OK("bn_bwd_partial_t_kernel");
   *nparts = s.gx;
   return 0;
+}
+TDL_API int tdl_bn_bwd_partial(const void* dz, const void* x, const void* z, int z_is_bitmask, const float* scale,
+                               const float* shift, const float* mean, const float* invstd, int64_t rows, int C,
+                               int relu, float* scratch, int64_t scratch_floats, int* nparts, void* stream) {
+  return tdl_bn_bwd_partial_ld(dz, x, z, z_is_bitmask, scale, shift, mean, invstd, rows, C, relu, C, scratch,
+                               scratch_floats, nparts, stream);
 }
 
 // dgamma / dbeta from the partial rows AND dx (and dres) in one launch (replaces tdl_bn_bwd_finalize_partials +
@@ -1216,6 +1275,59 @@ TDL_API int tdl_bn_bwd_apply_fused(const void* dz, const void* x, const void* z,
   if (e != cudaSuccess) return tdl::cuda_fail(e, "bn_bwd_apply_fin_kernel");
   TDL_LAUNCH_OK("bn_bwd_apply_fin_kernel");
   return 0;
+}
+
+// addend ([rows, C] bf16, may be NULL): added to dx (a second gradient of the BatchNorm's input, e.g. a residual unit's
+// identity shortcut).  mask_by_x != 0: the input x is a ReLU output; dx is zeroed where x == 0 (that ReLU's backward).
+TDL_API int tdl_bn_bwd_apply_ex(const void* dz, const void* x, const void* z, int z_is_bitmask, const float* scale,
+                                const float* shift, const float* mean, const float* invstd, const float* dgamma,
+                                const float* dbeta, void* dx, void* dres, int64_t rows, int C, int relu, int64_t ld_dz,
+                                const void* addend, int mask_by_x, void* stream) {
+  TDL_REQUIRE(C > 0 && C % 8 == 0, "C must be a positive multiple of 8");
+  TDL_REQUIRE(ld_dz >= C && ld_dz % 8 == 0, "ld_dz must be a multiple of 8, at least C");
+  if (rows == 0) return 0;
+  ReduceShape s = apply_shape(rows, C);
+  dim3 grid(s.gx, s.gy);
+  const int mode = mask_mode(relu, z, z_is_bitmask);
+  const bool extra = addend != nullptr || mask_by_x != 0;
+  const float inv_n = 1.f / (float)rows;
+  cudaError_t e;
+#define TDL_BN_BWD_T(M_, D_, X_)                                                                                     \
+  e = tdl::launch_pdl(bn_bwd_apply_t_kernel<M_, D_, X_>, dim3(grid), dim3(kThreads), 0, (cudaStream_t)stream,        \
+                      (const bf16*)dz, (const bf16*)x, z, scale, shift, mean, invstd, dbeta, dgamma, inv_n, (bf16*)dx, \
+                      (bf16*)dres, rows, C, s.tx, s.ty, ld_dz, (const bf16*)addend, mask_by_x)
+#define TDL_BN_BWD_M(M_)                                  \
+  do {                                                    \
+    if (dres) {                                           \
+      if (extra) TDL_BN_BWD_T(M_, true, true);            \
+      else TDL_BN_BWD_T(M_, true, false);                 \
+    } else {                                              \
+      if (extra) TDL_BN_BWD_T(M_, false, true);           \
+      else TDL_BN_BWD_T(M_, false, false);                \
+    }                                                     \
+  } while (0)
+  if (mode == kNoRelu) TDL_BN_BWD_M(kNoRelu);
+  else if (mode == kRecompute) TDL_BN_BWD_M(kRecompute);
+  else if (mode == kBits) TDL_BN_BWD_M(kBits);
+  else TDL_BN_BWD_M(kFromZ);
+#undef TDL_BN_BWD_M
+#undef TDL_BN_BWD_T
+  if (e != cudaSuccess) return tdl::cuda_fail(e, "bn_bwd_apply_t_kernel");
+  TDL_LAUNCH_OK("bn_bwd_apply_t_kernel");
+  return 0;
+}
+TDL_API int tdl_bn_bwd_apply_ld(const void* dz, const void* x, const void* z, int z_is_bitmask, const float* scale,
+                                const float* shift, const float* mean, const float* invstd, const float* dgamma,
+                                const float* dbeta, void* dx, void* dres, int64_t rows, int C, int relu, int64_t ld_dz,
+                                void* stream) {
+  return tdl_bn_bwd_apply_ex(dz, x, z, z_is_bitmask, scale, shift, mean, invstd, dgamma, dbeta, dx, dres, rows, C, relu,
+                             ld_dz, nullptr, 0, stream);
+}
+TDL_API int tdl_bn_bwd_apply(const void* dz, const void* x, const void* z, int z_is_bitmask, const float* scale,
+                             const float* shift, const float* mean, const float* invstd, const float* dgamma, const float* dbeta,
+                             void* dx, void* dres, int64_t rows, int C, int relu, void* stream) {
+  return tdl_bn_bwd_apply_ld(dz, x, z, z_is_bitmask, scale, shift, mean, invstd, dgamma, dbeta, dx, dres, rows, C, relu,
+                             C, stream);
 }
 
 // ------------------------------------------------------------------------------------------------------------

@@ -61,31 +61,43 @@ namespace tdl {
 
 typedef __nv_bfloat16 bf16;
 
+// One 16-byte word.  The payload is a uint4 on purpose: a struct of four __nv_bfloat162 (the first version) is copied
+// member by member -- ptxas emitted FOUR 32-bit LDG / STG per 16 bytes in every kernel that used ld8 / st8 (all
+// BatchNorm, pooling and depthwise kernels), i.e. 4x the load/store instructions and 4x the L1 wavefronts of a
+// 128-bit access, and those "memory-bound" kernels were in fact bound by the L1 / LSU pipe (ncu: l1tex sectors 4x
+// the L2 sectors, profiles/ncu_bn_bwd_partial_802816x64.txt).
 struct __align__(16) bf16x8 {
-  __nv_bfloat162 v[4];
+  uint4 raw;
 };
 
 __device__ __forceinline__ void unpack8(const bf16x8& in, float* out) {
+  const uint32_t w[4] = {in.raw.x, in.raw.y, in.raw.z, in.raw.w};
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    float2 f = __bfloat1622float2(in.v[i]);
-    out[2 * i] = f.x;
-    out[2 * i + 1] = f.y;
+  for (int i = 0; i < 4; ++i) {  // a bf16 is the upper half of an fp32
+    out[2 * i] = __uint_as_float(w[i] << 16);
+    out[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
   }
 }
 
 __device__ __forceinline__ bf16x8 pack8(const float* in) {
-  bf16x8 o;
+  uint32_t w[4];
 #pragma unroll
-  for (int i = 0; i < 4; ++i) o.v[i] = __floats2bfloat162_rn(in[2 * i], in[2 * i + 1]);
+  for (int i = 0; i < 4; ++i) {
+    const __nv_bfloat162 h = __floats2bfloat162_rn(in[2 * i], in[2 * i + 1]);
+    w[i] = *reinterpret_cast<const uint32_t*>(&h);
+  }
+  bf16x8 o;
+  o.raw = make_uint4(w[0], w[1], w[2], w[3]);
   return o;
 }
 
 __device__ __forceinline__ bf16x8 ld8(const bf16* p) {
-  return *reinterpret_cast<const bf16x8*>(p);
+  bf16x8 r;
+  r.raw = *reinterpret_cast<const uint4*>(p);  // LDG.E.128
+  return r;
 }
 __device__ __forceinline__ void st8(bf16* p, const bf16x8& v) {
-  *reinterpret_cast<bf16x8*>(p) = v;
+  *reinterpret_cast<uint4*>(p) = v.raw;        // STG.E.128
 }
 
 __device__ __forceinline__ float warp_sum(float v) {

@@ -117,6 +117,9 @@ int tdl_bn_partial_stats(const void* x, int64_t rows, int C, float* scratch, int
 int tdl_bn_bwd_partial(const void* dz, const void* x, const void* z, int z_is_bitmask, const float* scale,
                        const float* shift, const float* mean, const float* invstd, int64_t rows, int C, int relu,
                        float* scratch, int64_t scratch_floats, int* nparts, void* stream);
+int tdl_bn_bwd_partial_ld(const void* dz, const void* x, const void* z, int z_is_bitmask, const float* scale,
+                          const float* shift, const float* mean, const float* invstd, int64_t rows, int C, int relu,
+                          int64_t ld_dz, float* scratch, int64_t scratch_floats, int* nparts, void* stream);
 int tdl_bn_bwd_apply_fused(const void* dz, const void* x, const void* z, int z_is_bitmask, const float* scale,
                            const float* shift, const float* mean, const float* invstd, const float* partial, int nparts,
                            float* dgamma, float* dbeta, float* acc_dgamma, float* acc_dbeta, void* dx, void* dres,

@@ -380,24 +380,16 @@ def _bn_bwd_reduce(dz2d, x2d, z2d, zbits, scale, shift, mean, invstd, rows, C, r
                    ld=None):
     scratch = _bn_scratch(rows, C, x2d.device)
     ld = C if ld is None else ld
-    if C >= 256 and ld == C:
-        # wide tensors: the mask-specialised reduction with four rows in flight (fewer registers, more loads
-        # outstanding) -- 185 -> 161 us on [802816, 256], 64 -> 56 us on [50176, 1024]; narrow tensors measured equal
-        # or a little slower with it (profiles/bn_fold_experiment.txt), they keep the generic kernel
-        nparts = ctypes.c_int(0)
-        rc = N.lib().tdl_bn_bwd_partial(N.ptr(dz2d), N.ptr(x2d), N.ptr(z2d), _i(zbits), N.ptr(scale), N.ptr(shift),
-                                        N.ptr(mean), N.ptr(invstd), _i64(rows), _i(C), _i(int(relu)), N.ptr(scratch),
-                                        _i64(scratch.numel()), ctypes.byref(nparts), N.stream_ptr())
-        N.check(rc, "tdl_bn_bwd_partial")
-        rc = N.lib().tdl_bn_bwd_finalize_partials(N.ptr(scratch), _i(int(nparts.value)), _i(C), N.ptr(dgb[0]),
-                                                  N.ptr(dgb[1]), N.ptr(acc_dgamma), N.ptr(acc_dbeta), N.stream_ptr())
-        N.check(rc, "tdl_bn_bwd_finalize_partials")
-        return rc
-    rc = N.lib().tdl_bn_bwd_reduce_ld(N.ptr(dz2d), N.ptr(x2d), N.ptr(z2d), _i(zbits), N.ptr(scale), N.ptr(shift),
-                                      N.ptr(mean), N.ptr(invstd), _i64(rows), _i(C), _i(int(relu)), _i64(ld),
-                                      N.ptr(scratch), _i64(scratch.numel()), N.ptr(dgb[0]), N.ptr(dgb[1]),
-                                      N.ptr(acc_dgamma), N.ptr(acc_dbeta), N.stream_ptr())
-    N.check(rc, "tdl_bn_bwd_reduce")
+    # the mask-specialised reduction with four rows in flight (128-bit loads, fewer registers than the generic kernel:
+    # [802816, 64] 56 -> 48 us, [802816, 256] 185 -> 148 us, profiles/bn_fold_experiment.txt), then the fp64 fold
+    nparts = ctypes.c_int(0)
+    rc = N.lib().tdl_bn_bwd_partial_ld(N.ptr(dz2d), N.ptr(x2d), N.ptr(z2d), _i(zbits), N.ptr(scale), N.ptr(shift),
+                                       N.ptr(mean), N.ptr(invstd), _i64(rows), _i(C), _i(int(relu)), _i64(ld),
+                                       N.ptr(scratch), _i64(scratch.numel()), ctypes.byref(nparts), N.stream_ptr())
+    N.check(rc, "tdl_bn_bwd_partial_ld")
+    rc = N.lib().tdl_bn_bwd_finalize_partials(N.ptr(scratch), _i(int(nparts.value)), _i(C), N.ptr(dgb[0]),
+                                              N.ptr(dgb[1]), N.ptr(acc_dgamma), N.ptr(acc_dbeta), N.stream_ptr())
+    N.check(rc, "tdl_bn_bwd_finalize_partials")
     return rc
 
 
