@@ -106,11 +106,19 @@ struct Geometry {
   // halo mode (stride-1 RxS > 1x1): the haloed input patch of a K block is loaded ONCE and every tap reads it at a row
   // shift instead of re-fetching a shifted copy per tap (the tap-shifted form is bound by L2->smem bandwidth there)
   int halo, halo_pw, halo_pbytes, halo_ptx, halo_nb, halo_bo;
+  // halo_res: the whole weight tensor of the (single) Cout tile stays in shared memory behind the two patch buffers,
+  // so a tile costs one patch load per K block and its taps issue back to back with no barrier in between
+  int halo_res;
   int has_mask; // res_mma only: zero outputs whose bit in a [pixels][K/8] byte mask is clear (fused ReLU backward)
   // which tap of the weight tensor filter position (r, s) reads: tap_base + r * tap_sr + s * tap_ss (default 0, S, 1).
   // A parity class of a strided data gradient walks a strided subset of the full flipped filter this way, so it needs
   // no re-laid-out copy of its taps.
   int tap_base, tap_sr, tap_ss;
+  // wgrad, three taps per CTA ("row mode", 1x3 / 3x3 stride-1 filters on maps up to 62 wide): a stage is TH whole image
+  // rows at a pitch of Q + 2 positions for BOTH operands (dY's two extra columns are out of range = zero), so the
+  // three taps of a filter row read ONE haloed X tile at row shifts 0 / 1 / 2 instead of three shifted copies.
+  // 1 = one N = 192 MMA whose 64-column blocks sit one pixel row (128 B) apart, 2 = three N = 64 MMAs.
+  int wrow;
 };
 
 // Pick the (TN, TH, TW) pixel patch with the best row utilisation for `rows` GEMM rows.
@@ -227,7 +235,8 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
   uint64_t* patch_empty = patch_full + 2;
   uint64_t* x_bar = patch_empty + 2;    // kBwdStats: the group's BatchNorm-input tile has landed
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(x_bar + 2);
-  uint8_t* smem_bh = smem + 2 * g.halo_pbytes;  // halo mode: weight-tile ring behind the two patch buffers
+  // halo mode: weight-tile ring behind the two patch buffers; resident form: all weights behind halo_nb patch buffers
+  uint8_t* smem_bh = smem + (g.halo_res ? g.halo_nb : 2) * g.halo_pbytes;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -297,6 +306,13 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
         for (int a = 0; a * 8192 < g.sp_wbytes; ++a)
           if (leader) ptx::tma_load_2d(smem_b + a * 8192, &tm_w, w_bar, a * 64, 0);
       }
+      if (!kStem && !kResMma && g.halo_res) {  // resident weights: [K block][tap] tiles, one barrier for all of them
+        const int taps = g.R * g.S;
+        if (leader) ptx::mbar_expect_tx(w_bar, (uint32_t)(taps * g.num_kb * Cfg::kBBytes));
+        for (int kb2 = 0; kb2 < g.num_kb; ++kb2)
+          for (int t = 0; t < taps; ++t)
+            if (leader) ptx::tma_load_3d(smem_bh + (kb2 * taps + t) * Cfg::kBBytes, &tm_w, w_bar, kb2 * kBlockK, t, 0);
+      }
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const int n_tile = tile % g.n_tiles;
         const int m_tile = tile / g.n_tiles;
@@ -322,6 +338,18 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
         const int n_in = tn_i * g.TN;
         if (!kStem && !kResMma && g.halo) {
           const int taps = g.R * g.S;
+          if (g.halo_res) {  // patches ride the stage barriers: halo_nb buffers, nothing else to load
+            for (int kb2 = 0; kb2 < g.num_kb; ++kb2) {
+              ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+              if (leader) ptx::mbar_expect_tx(&full_bar[stage], (uint32_t)g.halo_ptx);
+              if (leader) ptx::tma_load_4d(smem + stage * g.halo_pbytes, &tm_x, &full_bar[stage], kb2 * kBlockK, w_in, h_in, n_in);
+              if (++stage == g.halo_nb) {
+                stage = 0;
+                phase ^= 1;
+              }
+            }
+            continue;
+          }
           for (int kb2 = 0; kb2 < g.num_kb; ++kb2) {
             ptx::mbar_wait(&patch_empty[pb], pphase ^ 1);
             if (leader) ptx::mbar_expect_tx(&patch_full[pb], (uint32_t)g.halo_ptx);
@@ -399,6 +427,9 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
         stem_b0 = ptx::umma_smem_desc_sw128(ptx::smem_u32(smem_b), 16, 1024);
         if (blockIdx.x < total_tiles) ptx::mbar_wait(w_bar, 0);
       }
+      if (!kStem && !kResMma && g.halo_res) {
+        if (blockIdx.x < total_tiles) ptx::mbar_wait(w_bar, 0);
+      }
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         ptx::mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
         ptx::tc_fence_after();
@@ -406,6 +437,39 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constan
         if (!kStem && !kResMma && g.halo) {
           const uint32_t sbo = (uint32_t)g.halo_pw * 128u;  // one tile row (8 pixels) per 8-row group of the M tile
           bool first = true;
+          if (g.halo_res) {  // weights resident: the taps of a K block issue back to back, one barrier per patch
+            uint32_t b_tile = ptx::smem_u32(smem_bh);
+            for (int kb2 = 0; kb2 < g.num_kb; ++kb2) {
+              ptx::mbar_wait(&full_bar[stage], phase);
+              ptx::tc_fence_after();
+              const uint32_t a_patch = ptx::smem_u32(smem + stage * g.halo_pbytes);
+              uint32_t row_off = 0;  // r * dil * patch width, in pixels
+              for (int r = 0; r < g.R; ++r, row_off += (uint32_t)(g.dil * g.halo_pw)) {
+                for (int sx = 0; sx < g.S; ++sx, b_tile += (uint32_t)Cfg::kBBytes) {
+                  const uint32_t shift = (uint32_t)(sx * g.dil);
+                  const uint64_t a_desc = ptx::umma_smem_desc_sw128_bo(a_patch + (row_off + shift) * 128u, 16, sbo, 0u);
+                  const uint64_t b_desc = ptx::umma_smem_desc_sw128(b_tile, 16, 1024);
+#pragma unroll
+                  for (int k = 0; k < kBlockK / 16; ++k) {
+                    if (leader) ptx::umma_bf16(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc,
+                                   (first && k == 0) ? 0u : 1u);
+                  }
+                  first = false;
+                }
+              }
+              if (leader) ptx::umma_commit(&empty_bar[stage]);  // the patch may be overwritten once these MMAs retire
+              if (++stage == g.halo_nb) {
+                stage = 0;
+                phase ^= 1;
+              }
+            }
+            if (leader) ptx::umma_commit(&tmem_full[acc]);
+            if (++acc == kAcc) {
+              acc = 0;
+              acc_phase ^= 1;
+            }
+            continue;
+          }
           for (int kb2 = 0; kb2 < g.num_kb; ++kb2) {
             ptx::mbar_wait(&patch_full[hpb], hpphase);
             ptx::tc_fence_after();
@@ -1224,7 +1288,7 @@ struct WgradCfg {
 template <int MT, int BLOCK_N, int TP = 1>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_wgrad_kernel(const __grid_constant__ CUtensorMap tm_dy, const __grid_constant__ CUtensorMap tm_x,
-                  const Geometry g, float* __restrict__ dw, int m_tiles_co, int n_tiles_ci) {
+                  const Geometry g, float* __restrict__ dw, int m_tiles_co, int n_tiles_ci, int bulk_epi) {
   ptx::pdl_trigger();
   using Cfg = WgradCfg<MT, BLOCK_N, TP>;
   constexpr int kStages = Cfg::kStages;
@@ -1256,7 +1320,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tm_dy, const __grid_consta
   if (my_iters <= 0) return;  // uniform across the CTA
 
   // Pixel rows a TMA box does not cover must read as zero in BOTH operands for every stage.
-  if (g.TN * g.TH * g.TW < 64) {
+  if (g.TN * g.TH * g.TW < 64 || g.wrow) {
     uint4 z = make_uint4(0, 0, 0, 0);
     uint4* p4 = reinterpret_cast<uint4*>(smem);
     const int n16 = kStages * Cfg::kStageBytes / 16;
@@ -1287,7 +1351,11 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tm_dy, const __grid_consta
   const uint32_t tmem_base = *tmem_slot;
 
   const uint32_t px_bytes = (uint32_t)(g.TN * g.TH * g.TW) * 128u;  // one 64-channel box
-  const uint32_t stage_tx = px_bytes * (uint32_t)(2 * MT + ntaps * (BLOCK_N / 64));
+  const bool wrow = TP == 3 && g.wrow != 0;
+  // row mode loads only the 64-channel dY blocks that exist (the rest of the A tile stays at its initial zero)
+  const int a_blocks = wrow ? min(2 * MT, (g.K - co_tile * (128 * MT) + 63) / 64) : 2 * MT;
+  const uint32_t stage_tx = wrow ? px_bytes * (uint32_t)(a_blocks + 1)
+                                 : px_bytes * (uint32_t)(2 * MT + ntaps * (BLOCK_N / 64));
 
   if (warp == 0) {
     if (lane == 0) {  // (the elected-lane form of conv_fprop_kernel measured slower here: few, long stages)
@@ -1302,6 +1370,17 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tm_dy, const __grid_consta
         ptx::mbar_expect_tx(&full_bar[stage], stage_tx);
         uint8_t* a = smem_a + stage * Cfg::kABytes;
         uint8_t* b = smem_b + stage * Cfg::kBBytes;
+        if (wrow) {
+          for (int h = 0; h < a_blocks; ++h)
+            ptx::tma_load_4d(a + h * 8192, &tm_dy, &full_bar[stage], co_tile * (128 * MT) + h * 64, 0, th_i * g.TH, tn_i);
+          ptx::tma_load_4d(b, &tm_x, &full_bar[stage], ci_tile * BLOCK_N, -g.pad_w, th_i * g.TH + r * g.dil - g.pad_h,
+                           tn_i);
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+          continue;
+        }
 #pragma unroll
         for (int h = 0; h < 2 * MT; ++h)
           ptx::tma_load_4d(a + h * 8192, &tm_dy, &full_bar[stage], co_tile * (128 * MT) + h * 64, tw_i * g.TW,
@@ -1340,6 +1419,34 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tm_dy, const __grid_consta
       for (int i = 0; i < my_iters; ++i) {
         ptx::mbar_wait(&full_bar[stage], phase);
         ptx::tc_fence_after();
+        if (TP == 3 && g.wrow) {
+          // one haloed X tile; tap s is the same tile one pixel row (128 B) further on
+          const uint32_t b_addr = ptx::smem_u32(smem_b + stage * Cfg::kBBytes);
+          const uint64_t a_desc = ptx::umma_smem_desc_sw128(ptx::smem_u32(smem_a + stage * Cfg::kABytes), 8192, 1024);
+          if (g.wrow == 1) {
+            const uint64_t b_desc = ptx::umma_smem_desc_sw128(b_addr, 128, 1024);
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              ptx::umma_bf16(tmem_base, a_desc + (uint64_t)(128 * k), b_desc + (uint64_t)(128 * k), idesc,
+                             (i > 0 || k > 0) ? 1u : 0u);
+          } else {
+            constexpr uint32_t idesc64 = ptx::umma_idesc_bf16(128, 64, 1, 1);
+#pragma unroll
+            for (int t = 0; t < 3; ++t) {
+              const uint64_t b_desc = ptx::umma_smem_desc_sw128(b_addr + (uint32_t)t * 128u, 8192, 1024);
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                ptx::umma_bf16(tmem_base + (uint32_t)(t * 64), a_desc + (uint64_t)(128 * k),
+                               b_desc + (uint64_t)(128 * k), idesc64, (i > 0 || k > 0) ? 1u : 0u);
+            }
+          }
+          ptx::umma_commit(&empty_bar[stage]);
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+          continue;
+        }
         // MN-major SW128: 64-element MN blocks 8192 B apart (LBO), 8-pixel-row groups 1024 B apart (SBO)
         const uint64_t b_desc = ptx::umma_smem_desc_sw128(ptx::smem_u32(smem_b + stage * Cfg::kBBytes), 8192, 1024);
 #pragma unroll
@@ -1366,6 +1473,38 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tm_dy, const __grid_consta
     ptx::mbar_wait(tmem_full, 0);
     ptx::tc_fence_after();
     const int taps = g.R * g.S;
+    if (bulk_epi) {
+      // Every MMA has retired, so the pipeline buffers are free: each thread stages ITS accumulator row in shared
+      // memory (row pitch 260 floats: conflict-free 16-byte stores) and hands whole (row, tap) segments -- contiguous
+      // in dW -- to the copy engine as bulk reductions.  A per-thread red.global.add.v4 touches 32 different rows per
+      // warp instruction, half a sector each; the bulk form adds full lines.
+      constexpr int kPitch = 260;
+      float* stg = reinterpret_cast<float*>(smem) + (size_t)(quarter * 32 + lane) * kPitch;
+#pragma unroll 1
+      for (int mt = 0; mt < MT; ++mt) {
+        const int co = co_tile * (128 * MT) + mt * 128 + quarter * 32 + lane;
+        if (mt > 0) ptx::tma_store_wait_read<0>();  // this thread's previous segments have left its staging row
+#pragma unroll 1
+        for (int c = 0; c < ntaps * (BLOCK_N / 32); ++c) {
+          uint32_t v[32];
+          ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(mt * BLOCK_N * TP + c * 32), v);
+          ptx::tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; j += 4)
+            *reinterpret_cast<uint4*>(stg + c * 32 + j) = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+        }
+        ptx::fence_proxy_async_smem();
+        const int ci0 = ci_tile * BLOCK_N;
+        const int ncols = min(BLOCK_N, g.C - ci0);
+        if (co < g.K && ncols > 0) {
+          for (int t = 0; t < ntaps; ++t)
+            ptx::bulk_reduce_add_f32(dw + ((size_t)co * taps + tap + t) * g.C + ci0, stg + t * BLOCK_N,
+                                     (uint32_t)ncols * 4u);
+        }
+        ptx::tma_store_commit();
+      }
+      ptx::tma_store_wait_all<0>();
+    } else
 #pragma unroll 1
     for (int mt = 0; mt < MT; ++mt) {
       const int co = co_tile * (128 * MT) + mt * 128 + quarter * 32 + lane;
@@ -1883,6 +2022,11 @@ static int identity64_address(const void** out, cudaStream_t st) {
   return 0;
 }
 
+// wgrad epilogue: 1 = bulk reductions from a shared-memory staging tile, 0 = per-thread red.global.add.v4.f32
+static int g_wgrad_bulk = -1;
+static int g_wgrad_snap = -1;         // whole-wave grids (see launch_wgrad)
+static float g_wgrad_model_k = -1.f;  // constant of the split-count cost model (see launch_wgrad)
+
 template <int MT, int BLOCK_N, int TP = 1>
 static int launch_wgrad(const CUtensorMap& tdy, const CUtensorMap& tx, const Geometry& g, float* dw, cudaStream_t st) {
   using Cfg = WgradCfg<MT, BLOCK_N, TP>;
@@ -1891,6 +2035,10 @@ static int launch_wgrad(const CUtensorMap& tdy, const CUtensorMap& tx, const Geo
     TDL_CUDA_OK(cudaFuncSetAttribute(conv_wgrad_kernel<MT, BLOCK_N, TP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      Cfg::kSmemBytes));
     attr_set = true;
+  }
+  if (g_wgrad_bulk < 0) {
+    const char* e = getenv("TDL_WGRAD_BULK");
+    g_wgrad_bulk = e ? atoi(e) : 1;
   }
   const int m_tiles = (int)tdl::cdiv(g.K, 128 * MT);
   const int n_tiles = (int)tdl::cdiv(g.C, BLOCK_N);
@@ -1911,7 +2059,7 @@ static int launch_wgrad(const CUtensorMap& tdy, const CUtensorMap& tx, const Geo
     // optimum depends only on patches / items: splits* = sqrt(1.1 * patches / items).  More splits than that just
     // moves time from the tensor core into atomics (13x13 / 7x7 layers: 9 -> 2-4 splits, -10 % step time on the
     // reference network); fewer, longer CTAs also leave SMs to the main stream the wgrad overlaps with.
-    static float model_k = -1.f;  // TDL_WGRAD_SPLIT_MODEL: the constant of the model (0 = off)
+    float& model_k = g_wgrad_model_k;  // TDL_WGRAD_SPLIT_MODEL: the constant of the model (0 = off)
     if (model_k < 0.f) {
       const char* e = getenv("TDL_WGRAD_SPLIT_MODEL");
       model_k = e ? (float)atof(e) : 1.1f;
@@ -1923,10 +2071,25 @@ static int launch_wgrad(const CUtensorMap& tdy, const CUtensorMap& tx, const Geo
     }
   }
   if (splits < 1) splits = 1;
+  {
+    // One CTA per SM (the pipeline takes the whole shared memory): a grid of 1.5 waves costs two.  Snap a grid that
+    // ends in a partial wave down to whole waves (3x3 64 -> 64 @56x56: 219 CTAs = 1.48 waves -> 147).
+    int& snap = g_wgrad_snap;  // TDL_WGRAD_WAVE_SNAP=0 turns it off
+    if (snap < 0) {
+      const char* e = getenv("TDL_WGRAD_WAVE_SNAP");
+      snap = e ? atoi(e) : 1;
+    }
+    const int ctas = splits * items;
+    if (snap && ctas > sms && ctas % sms != 0) {
+      const int whole = (ctas / sms) * sms / items;
+      if (whole >= 1) splits = whole;
+    }
+  }
   dim3 grid(splits, items);
   {
     cudaError_t _le = tdl::launch_pdl(conv_wgrad_kernel<MT, BLOCK_N, TP>, dim3(grid), dim3(kThreads), Cfg::kSmemBytes,
-        st, tdy, tx, g, dw, m_tiles, n_tiles);
+        st, tdy, tx, g, dw, m_tiles, n_tiles,
+        (g_wgrad_bulk != 0 && (reinterpret_cast<uintptr_t>(dw) & 15) == 0) ? 1 : 0);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "conv_wgrad_kernel");
   }
   TDL_LAUNCH_OK("conv_wgrad_kernel");
@@ -1964,6 +2127,8 @@ struct TapSel {
 static int g_pair_mode = -1;
 
 static int g_halo_mode = -1;  // -1 = read TDL_HALO on first use, 0 = off (default), 1 = on, 2 = on with base offsets
+static int g_halo_res_mode = -1;  // halo form with resident weights where they fit: -1 = read TDL_HALO_RES, default 1
+static int g_wrow_mode = -1;      // wgrad row mode for 64-channel 3-wide filters: -1 = read TDL_WGRAD_ROW, default 1
 
 static int fprop_impl(const void* x, const void* w, void* y, const float* bias, const void* residual, int N, int H,
                       int W, int C, int K, int R, int S, int stride, int dil, int pad_h, int pad_w, int P, int Q,
@@ -2009,8 +2174,12 @@ static int fprop_impl(const void* x, const void* w, void* y, const float* bias, 
       const char* e = getenv("TDL_HALO");
       g_halo_mode = (e != nullptr) ? atoi(e) : 0;
     }
+    if (g_halo_res_mode < 0) {
+      const char* e = getenv("TDL_HALO_RES");
+      g_halo_res_mode = (e != nullptr) ? atoi(e) : 1;
+    }
     const int enabled = g_halo_mode != 0, use_bo = g_halo_mode == 2;
-    if (enabled && !taps && !flat && !view && residual == nullptr && bnb == nullptr && R * S > 1 && stride == 1 && dil <= 2 && P >= 12 &&
+    if (!taps && !flat && !view && residual == nullptr && bnb == nullptr && R * S > 1 && stride == 1 && dil <= 2 && P >= 12 &&
         Q >= 12) {
       const int th_tiles = (int)cdiv(P, 16);
       const int th = (int)cdiv(P, th_tiles);
@@ -2022,7 +2191,24 @@ static int fprop_impl(const void* x, const void* w, void* y, const float* bias, 
       int nb = ring / bbytes;
       const int max_nb = block_n_pre == 256 ? 4 : (block_n_pre == 128 ? 6 : 8);
       if (nb > max_nb) nb = max_nb;
-      if (nb >= 2) {
+      // Resident weights (halo_res): with ONE Cout tile and the whole [K blocks][taps] weight tensor fitting behind the
+      // patch buffers (3x3 64 -> 64: 72 KB), the per-tap weight loads and their barrier round trips -- what made the
+      // plain halo form lose -- disappear: a tile is one patch load and R*S*4 MMAs issued back to back.
+      // The resident form needs no 8-pixel rounding of the patch width (the swizzle follows absolute addresses, so any
+      // 128-byte row pitch works) and spends the rest of the ring on patch buffers: a patch takes ~2 us to arrive and
+      // a tile's MMAs ~0.6 us, so two buffers would leave the tensor core waiting.
+      const int pw_r = 8 + (S - 1) * dil;
+      const int pbytes_r = (int)cdiv((int64_t)pw_r * ph * 128, 1024) * 1024;
+      const int wbytes_r = R * S * g.num_kb * bbytes;
+      int nb_r = (192 * 1024 - wbytes_r) / pbytes_r;
+      if (nb_r > (block_n_pre == 64 ? 8 : 6)) nb_r = block_n_pre == 64 ? 8 : 6;  // the stage barriers there are
+      const bool res = g_halo_res_mode != 0 && K <= block_n_pre && wbytes_r < 192 * 1024 && nb_r >= 3;
+      if (res) {
+        g.halo = 1; g.halo_pw = pw_r; g.halo_pbytes = pbytes_r; g.halo_ptx = pw_r * ph * 128; g.halo_nb = nb_r;
+        g.halo_bo = 0; g.halo_res = 1;
+        g.TN = 1; g.TH = th; g.TW = 8;
+        g.tiles_n = g.N; g.tiles_h = (int)cdiv(g.P, g.TH); g.tiles_w = (int)cdiv(g.Q, 8);
+      } else if (enabled && nb >= 2) {
         g.halo = 1; g.halo_pw = pw; g.halo_pbytes = pbytes; g.halo_ptx = pw * ph * 128; g.halo_nb = nb;
         g.halo_bo = use_bo;
         g.TN = 1; g.TH = th; g.TW = 8;
@@ -2242,6 +2428,18 @@ TDL_API int tdl_conv2d_wgrad_bf16(const void* x, const void* dy, float* dw, int 
   g.tiles_w = (int)cdiv(g.Q, g.TW);
   const int block_n = C >= 256 ? 256 : (C > 64 ? 128 : 64);
   const int mt = K >= 256 ? 2 : 1;
+  if (g_wrow_mode < 0) {
+    const char* e = getenv("TDL_WGRAD_ROW");
+    g_wrow_mode = e ? atoi(e) : 1;
+  }
+  // row mode (see Geometry::wrow): the three taps of a filter row share one haloed X tile
+  if (g_wrow_mode != 0 && !flat && mt == 1 && block_n == 64 && S == 3 && stride == 1 && dil == 1 && pad_w == 1 &&
+      Q == W && Q + 2 <= 64) {
+    g.wrow = g_wrow_mode;
+    g.TN = 1; g.TW = Q + 2; g.TH = 64 / (Q + 2);
+    if (g.TH > P) g.TH = P;
+    g.tiles_n = N; g.tiles_h = (int)cdiv(P, g.TH); g.tiles_w = 1;
+  }
   CUtensorMap tdy, tx;
   {
     uint64_t dims[4] = {(uint64_t)K, (uint64_t)g.Q, (uint64_t)g.P, (uint64_t)g.N};
@@ -2504,5 +2702,34 @@ TDL_API int tdl_conv2d_get_pair_mode() { return g_pair_mode < 0 ? 0 : g_pair_mod
 TDL_API int tdl_conv2d_set_halo_mode(int mode) {
   TDL_REQUIRE(mode >= 0 && mode <= 2, "halo mode must be 0, 1 or 2");
   g_halo_mode = mode;
+  return 0;
+}
+
+// Halo form with the weights resident in shared memory, picked on its own for stride-1 RxS layers with one Cout tile
+// whose weights fit beside two patch buffers (3x3 64 -> 64): 1 = on (default), 0 = off.
+// wgrad grid tuning (measurement hooks): whole-wave snapping on / off, constant of the split-count model (< 0 = default)
+TDL_API int tdl_conv2d_set_wgrad_tuning(int wave_snap, float model_k) {
+  tdl::conv::g_wgrad_snap = wave_snap ? 1 : 0;
+  tdl::conv::g_wgrad_model_k = model_k < 0.f ? 1.1f : model_k;
+  return 0;
+}
+
+// wgrad epilogue: 0 = per-thread red.global.add, 1 = bulk reductions through shared memory (default)
+TDL_API int tdl_conv2d_set_wgrad_bulk_mode(int mode) {
+  TDL_REQUIRE(mode == 0 || mode == 1, "wgrad epilogue mode must be 0 or 1");
+  tdl::conv::g_wgrad_bulk = mode;
+  return 0;
+}
+
+// wgrad row mode (Geometry::wrow): 0 = off, 1 = one N = 192 MMA over row-shifted blocks (default), 2 = three N = 64 MMAs
+TDL_API int tdl_conv2d_set_wgrad_row_mode(int mode) {
+  TDL_REQUIRE(mode >= 0 && mode <= 2, "wgrad row mode must be 0, 1 or 2");
+  g_wrow_mode = mode;
+  return 0;
+}
+
+TDL_API int tdl_conv2d_set_halo_res_mode(int mode) {
+  TDL_REQUIRE(mode == 0 || mode == 1, "resident-weight halo mode must be 0 or 1");
+  g_halo_res_mode = mode;
   return 0;
 }

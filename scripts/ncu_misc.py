@@ -1,5 +1,5 @@
 """Driver for ncu captures of single kernels: python scripts/ncu_misc.py <kind>, kind in bn | bn64 | bnwide | lovasz |
-optim | adam | stem | stemwgrad | stats1x1 | resmma | conv3x3[_halo] | pair | depthwise | depthwise_bwd | smallk | maxpool |
+optim | adam | stem | stemwgrad | stats1x1 | resmma | conv3x3[_halo] | wgrad64 | pair | depthwise | depthwise_bwd | smallk | maxpool |
 upsample | softmaxce | segmetrics | augment | p2p | p2p_wire  (scripts/ncu_all.sh captures one kernel of each)"""
 import os
 import sys
@@ -82,6 +82,13 @@ elif kind in ("conv3x3", "conv3x3_halo"):
     w = (torch.randn(64, 9, 64, device="cuda") / 24).bfloat16()
     for _ in range(3):
         O.conv2d_fprop(x, w, R=3, S=3, pad_h=1, pad_w=1, out_hw=(56, 56))
+elif kind == "wgrad64":
+    # weight gradient of ResNet-50's stage-1 3x3 (64 -> 64 @56x56): row mode, the taps of a filter row share one tile
+    x = torch.randn(256, 56, 56, 64, device="cuda").bfloat16()
+    dy = torch.randn(256, 56, 56, 64, device="cuda").bfloat16()
+    dw = torch.zeros(64, 9, 64, device="cuda")
+    for _ in range(3):
+        O.conv2d_wgrad(x, dy, dw, R=3, S=3, pad_h=1, pad_w=1)
 elif kind == "depthwise":
     x = torch.randn(64, 38, 38, 728, device="cuda").bfloat16()
     w = torch.randn(9, 728, device="cuda")

@@ -253,14 +253,44 @@ def test_tensors_past_two_gib(O):
     assert rel_err(dx[sl], dxr) < 2e-2
 
 
-@pytest.fixture(params=[0, 1], ids=["tap_shifted", "halo_reuse"])
+@pytest.fixture(params=[0, 1, 2], ids=["tap_shifted", "halo_reuse", "default"])
 def halo_mode(request):
-    """Run the convolution cases with both main loops (the halo-reuse one is off by default: correct but slower)."""
+    """Run the convolution cases with every main loop: tap-shifted loads, halo reuse with streamed weights (off by
+    default: correct but slower), and the default (halo reuse with resident weights where they fit, else tap-shifted)."""
     from tensorflowdistributedlearning_b200 import _native
 
-    assert _native.lib().tdl_conv2d_set_halo_mode(request.param) == 0
+    lib = _native.lib()
+    assert lib.tdl_conv2d_set_halo_mode(1 if request.param == 1 else 0) == 0
+    assert lib.tdl_conv2d_set_halo_res_mode(1 if request.param == 2 else 0) == 0
     yield request.param
-    _native.lib().tdl_conv2d_set_halo_mode(0)
+    lib.tdl_conv2d_set_halo_mode(0)
+    lib.tdl_conv2d_set_halo_res_mode(1)
+
+
+def test_conv3x3_resident_weight_halo_loop_is_bit_equal_to_tap_shifted(O):
+    """3x3 64 -> 64 (one K block): the resident-weight halo loop accumulates the taps in the same order as the
+    tap-shifted loop, so outputs and fused BatchNorm partial sums' totals must agree -- the former bit for bit."""
+    from tensorflowdistributedlearning_b200 import _native
+
+    lib = _native.lib()
+    torch.manual_seed(77)
+    try:
+        for (n, h, c, k) in ((4, 56, 64, 64), (3, 51, 64, 48), (2, 13, 32, 64)):
+            x = torch.randn(n, h, h, c, device="cuda").bfloat16()
+            w = (torch.randn(k, 9, c, device="cuda") / math.sqrt(9 * c)).bfloat16()
+            outs = []
+            for mode in (0, 1):
+                assert lib.tdl_conv2d_set_halo_res_mode(mode) == 0
+                y = O.conv2d_fprop(x, w, R=3, S=3, stride=1, dil=1, pad_h=1, pad_w=1, out_hw=(h, h))
+                ys, partials, nparts = O.conv2d_fprop_stats(x, w, R=3, S=3, stride=1, pad_h=1, pad_w=1, out_hw=(h, h))
+                outs.append((y, ys, partials[:nparts].double().sum(0)))
+            assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+            assert torch.equal(outs[0][0], outs[0][1])
+            assert rel_err(outs[1][2], outs[0][2]) < 1e-5
+            ref = _ref_conv(x, w, 3, 3, 1, 1, (1, 1, 1, 1))
+            assert rel_err(outs[1][0], ref) < 2e-2
+    finally:
+        lib.tdl_conv2d_set_halo_res_mode(1)
 
 
 @pytest.mark.parametrize("case", CONV_CASES)
@@ -283,8 +313,25 @@ def test_conv_fprop_tcgen05(O, case, halo_mode):
                                   (2, 28, 128, 256, 1, 2, 1),
                                   # narrow filters with taps: three / two taps per CTA in one wide MMA
                                   (3, 28, 64, 64, 3, 1, 1), (2, 19, 40, 72, 3, 1, 2), (2, 29, 128, 128, 3, 2, 1),
-                                  (2, 14, 104, 128, 3, 1, 1), (2, 16, 64, 64, 2, 1, 1)])
-def test_conv_wgrad_tcgen05(O, case):
+                                  (2, 14, 104, 128, 3, 1, 1), (2, 16, 64, 64, 2, 1, 1),
+                                  # row mode: the taps of a filter row read one haloed input tile at row shifts
+                                  (2, 56, 64, 64, 3, 1, 1), (2, 51, 64, 128, 3, 1, 1), (3, 13, 32, 48, 3, 1, 1),
+                                  (2, 62, 64, 64, 3, 1, 1)])
+@pytest.mark.parametrize("row_mode", [0, 1, 2], ids=["shifted_copies", "row_shared_wide", "row_shared_narrow"])
+def test_conv_wgrad_tcgen05(O, case, row_mode):
+    from tensorflowdistributedlearning_b200 import _native
+
+    N, H, C, K, R, stride, dil = case
+    if row_mode and not (R == 3 and stride == 1 and dil == 1 and C <= 64 and K < 256 and H <= 62):
+        pytest.skip("row mode does not apply to this shape")
+    assert _native.lib().tdl_conv2d_set_wgrad_row_mode(row_mode) == 0
+    try:
+        _wgrad_case(O, case)
+    finally:
+        _native.lib().tdl_conv2d_set_wgrad_row_mode(1)
+
+
+def _wgrad_case(O, case):
     N, H, C, K, R, stride, dil = case
     torch.manual_seed(1)
     x = torch.randn(N, H, H, C, device="cuda").bfloat16()
