@@ -1538,6 +1538,200 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tm_dy, const __grid_consta
 }
 
 // ------------------------------------------------------------------------------------------
+// wgrad on a CTA pair (cta_group::2): one 256 (Cout) x BLOCK_N (Cin) tile of one tap per PAIR.  Each CTA loads its own
+// 128 output channels of dY and HALF of the X tile; the leader issues M = 256 MMAs that read both CTAs' shared memory.
+// A single-CTA MMA is fed from shared memory at about (M + N) / 2 cycles per K = 16 step (measured: N = 64 -> 93 clk
+// against a 32 clk floor, N = 256 -> ~190 against 128), so the 128 x 256 tiles of conv_wgrad_kernel<2, 256> cannot pass
+// ~2/3 of the tensor rate; as a pair each SM fetches 128 + 128 rows per step, which is the floor.  It also halves the
+// L2 -> shared-memory bytes of the X operand.  The tensor maps cover this GPU's memory only; nothing is multicast.
+// ------------------------------------------------------------------------------------------
+template <int BLOCK_N>
+struct Wgrad2Cfg {
+  static_assert(BLOCK_N == 128 || BLOCK_N == 256, "pair tiles are 256 x 128 or 256 x 256");
+  static constexpr int kABytes = 128 * 64 * 2;              // this CTA's 2 blocks of [64 px][64 co]
+  static constexpr int kBBytes = (BLOCK_N / 2) * 64 * 2;    // this CTA's BLOCK_N/128 blocks of [64 px][64 ci]
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kStagesRaw = (192 * 1024) / kStageBytes;
+  static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
+  static constexpr int kTmemCols = BLOCK_N;                 // 128 lanes x BLOCK_N fp32 columns per CTA
+  static constexpr int kDataBytes = kStages * kStageBytes < 136 * 1024 ? 136 * 1024 : kStages * kStageBytes;
+  static constexpr int kSmemBytes = kDataBytes + 1024 + 256;  // (the bulk epilogue stages 128 rows x 1040 B)
+};
+
+template <int BLOCK_N>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+conv_wgrad2_kernel(const __grid_constant__ CUtensorMap tm_dy, const __grid_constant__ CUtensorMap tm_x,
+                   const Geometry g, float* __restrict__ dw, int m_tiles_co, int n_tiles_ci, int bulk_epi) {
+  ptx::pdl_trigger();
+  using Cfg = Wgrad2Cfg<BLOCK_N>;
+  constexpr int kStages = Cfg::kStages;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + kStages * Cfg::kABytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::kDataBytes);
+  uint64_t* full_bar = bars;             // used in the leader only: bytes of BOTH CTAs land on it
+  uint64_t* empty_bar = bars + kStages;  // per CTA: the leader's commit frees the stage in both
+  uint64_t* tmem_full = bars + 2 * kStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = ptx::cluster_ctarank();  // 0 = leader
+  const int split = (int)blockIdx.x >> 1;
+  const int nsplits = (int)gridDim.x >> 1;
+
+  int wi = blockIdx.y;
+  const int ci_tile = wi % n_tiles_ci;
+  wi /= n_tiles_ci;
+  const int co_tile = wi % m_tiles_co;
+  const int tap = wi / m_tiles_co;
+  const int r = tap / g.S;
+  const int s = tap - r * g.S;
+
+  const int patches = g.tiles_n * g.tiles_h * g.tiles_w;
+  const int my_iters = (patches - split + nsplits - 1) / nsplits;  // the same in both CTAs of the pair (>= 1: host)
+
+  if (g.TN * g.TH * g.TW < 64) {  // pixel rows a TMA box does not cover must read as zero in both operands
+    uint4 z = make_uint4(0, 0, 0, 0);
+    uint4* p4 = reinterpret_cast<uint4*>(smem);
+    const int n16 = kStages * Cfg::kStageBytes / 16;
+    for (int i = threadIdx.x; i < n16; i += kThreads) p4[i] = z;
+    ptx::fence_proxy_async_smem();
+  }
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tm_dy);
+    ptx::prefetch_tmap(&tm_x);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int i = 0; i < kStages; ++i) {
+        ptx::mbar_init(&full_bar[i], 1);
+        ptx::mbar_init(&empty_bar[i], 1);
+      }
+      ptx::mbar_init(tmem_full, 1);
+      ptx::fence_mbar_init();
+    }
+    __syncwarp();
+    ptx::tmem_alloc_pair<Cfg::kTmemCols>(tmem_slot);
+  }
+  ptx::pdl_wait();
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::cluster_sync_all();  // both CTAs' barriers are initialised, both TMEM allocations are done, smem is zeroed
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const uint32_t px_bytes = (uint32_t)(g.TN * g.TH * g.TW) * 128u;  // one 64-channel box
+  const uint32_t stage_tx = 2u * px_bytes * (uint32_t)(2 + BLOCK_N / 128);
+  const int co_base = co_tile * 256 + (int)rank * 128;
+  const int ci_base = ci_tile * BLOCK_N + (int)rank * (BLOCK_N / 2);
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int i = 0; i < my_iters; ++i) {
+        const int patch = split + i * nsplits;
+        const int tw_i = patch % g.tiles_w;
+        const int th_i = (patch / g.tiles_w) % g.tiles_h;
+        const int tn_i = patch / (g.tiles_w * g.tiles_h);
+        ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+        if (rank == 0) ptx::mbar_expect_tx(&full_bar[stage], stage_tx);
+        uint8_t* a = smem_a + stage * Cfg::kABytes;
+        uint8_t* b = smem_b + stage * Cfg::kBBytes;
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+          ptx::tma_load_4d_pair(a + h * 8192, &tm_dy, &full_bar[stage], co_base + h * 64, tw_i * g.TW, th_i * g.TH,
+                                tn_i * g.TN);
+#pragma unroll
+        for (int h = 0; h < BLOCK_N / 128; ++h)
+          ptx::tma_load_4d_pair(b + h * 8192, &tm_x, &full_bar[stage], ci_base + h * 64,
+                                tw_i * g.TW * g.stride + s * g.dil - g.pad_w,
+                                th_i * g.TH * g.stride + r * g.dil - g.pad_h, tn_i * g.TN);
+        if (++stage == kStages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (rank == 0 && lane == 0) {
+      constexpr uint32_t idesc = ptx::umma_idesc_bf16(256, BLOCK_N, 1, 1);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int i = 0; i < my_iters; ++i) {
+        ptx::mbar_wait(&full_bar[stage], phase);
+        ptx::tc_fence_after();
+        const uint64_t a_desc = ptx::umma_smem_desc_sw128(ptx::smem_u32(smem_a + stage * Cfg::kABytes), 8192, 1024);
+        const uint64_t b_desc = ptx::umma_smem_desc_sw128(ptx::smem_u32(smem_b + stage * Cfg::kBBytes), 8192, 1024);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          ptx::umma_bf16_pair(tmem_base, a_desc + (uint64_t)(128 * k), b_desc + (uint64_t)(128 * k), idesc,
+                              (i > 0 || k > 0) ? 1u : 0u);
+        ptx::umma_commit_pair(&empty_bar[stage]);  // frees the stage in both CTAs
+        if (++stage == kStages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      ptx::umma_commit_pair(tmem_full);  // accumulators complete in both CTAs
+    }
+  } else {
+    const int quarter = warp & 3;
+    ptx::mbar_wait(tmem_full, 0);
+    ptx::tc_fence_after();
+    const int taps = g.R * g.S;
+    const int co = co_base + quarter * 32 + lane;
+    const int ci0 = ci_tile * BLOCK_N;
+    const int ncols = min(BLOCK_N, g.C - ci0);
+    if (bulk_epi) {  // as in conv_wgrad_kernel: stage this thread's row, hand it to the copy engine as one reduction
+      constexpr int kPitch = 260;
+      float* stg = reinterpret_cast<float*>(smem) + (size_t)(quarter * 32 + lane) * kPitch;
+#pragma unroll 1
+      for (int c = 0; c < BLOCK_N / 32; ++c) {
+        uint32_t v[32];
+        ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(c * 32), v);
+        ptx::tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; j += 4)
+          *reinterpret_cast<uint4*>(stg + c * 32 + j) = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+      }
+      ptx::fence_proxy_async_smem();
+      if (co < g.K && ncols > 0)
+        ptx::bulk_reduce_add_f32(dw + ((size_t)co * taps + tap) * g.C + ci0, stg, (uint32_t)ncols * 4u);
+      ptx::tma_store_commit();
+      ptx::tma_store_wait_all<0>();
+    } else {
+#pragma unroll 1
+      for (int c = 0; c < BLOCK_N / 32; ++c) {
+        uint32_t v[32];
+        ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(c * 32), v);
+        ptx::tmem_ld_wait();
+        if (co < g.K) {
+          float* dst = dw + ((size_t)co * taps + tap) * g.C + ci0 + c * 32;
+#pragma unroll
+          for (int j = 0; j < 32; j += 4)
+            if (ci0 + c * 32 + j < g.C)
+              asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + j), "f"(__uint_as_float(v[j])),
+                           "f"(__uint_as_float(v[j + 1])), "f"(__uint_as_float(v[j + 2])),
+                           "f"(__uint_as_float(v[j + 3]))
+                           : "memory");
+        }
+      }
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::cluster_sync_all();  // neither CTA may release TMEM / shared memory while its partner's MMAs can still touch it
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc_pair<Cfg::kTmemCols>(tmem_base);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
 // weight re-layout:  fp32 master [K, R*S, C]  ->  bf16 fprop copy [K, R*S, C]
 //                                              and bf16 dgrad copy [C, R*S (flipped), K]
 // ------------------------------------------------------------------------------------------
@@ -2096,6 +2290,56 @@ static int launch_wgrad(const CUtensorMap& tdy, const CUtensorMap& tx, const Geo
   return 0;
 }
 
+// CTA-pair weight gradient (conv_wgrad2_kernel): -1 = read TDL_WGRAD_2CTA on first use, 0 = off, 1 = on
+static int g_wgrad_pair = -1;
+
+template <int BLOCK_N>
+static int launch_wgrad2(const CUtensorMap& tdy, const CUtensorMap& tx, const Geometry& g, float* dw, cudaStream_t st) {
+  using Cfg = Wgrad2Cfg<BLOCK_N>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    TDL_CUDA_OK(cudaFuncSetAttribute(conv_wgrad2_kernel<BLOCK_N>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     Cfg::kSmemBytes));
+    attr_set = true;
+  }
+  if (g_wgrad_bulk < 0) {
+    const char* e = getenv("TDL_WGRAD_BULK");
+    g_wgrad_bulk = e ? atoi(e) : 1;
+  }
+  if (g_wgrad_model_k < 0.f) {
+    const char* e = getenv("TDL_WGRAD_SPLIT_MODEL");
+    g_wgrad_model_k = e ? (float)atof(e) : 1.1f;
+  }
+  const int m_tiles = (int)tdl::cdiv(g.K, 256);
+  const int n_tiles = (int)tdl::cdiv(g.C, BLOCK_N);
+  const int items = m_tiles * n_tiles * g.R * g.S;
+  const int patches = g.tiles_n * g.tiles_h * g.tiles_w;
+  const int pairs = tdl::num_sms() / 2;  // one CTA per SM, two SMs per tile
+  int splits = pairs / items;
+  if (splits < 1) splits = 1;
+  if ((2 * pairs) / items > splits && patches / ((2 * pairs) / items) >= 32) splits = (2 * pairs) / items;
+  if (g_wgrad_model_k > 0.f) {  // same two-term model as launch_wgrad (main loop vs the tile's reduction into dW)
+    int s_model = (int)(sqrtf(g_wgrad_model_k * (float)patches / (float)items) + 0.5f);
+    if (s_model < 1) s_model = 1;
+    if (splits > s_model) splits = s_model;
+  }
+  if (splits > patches) splits = patches;
+  if (splits * items > pairs && (splits * items) % pairs != 0) {  // whole waves of pairs
+    const int whole = ((splits * items) / pairs) * pairs / items;
+    if (whole >= 1) splits = whole;
+  }
+  if (splits < 1) splits = 1;
+  dim3 grid(2 * splits, items);  // clusters of two CTAs along x (compile-time __cluster_dims__)
+  {
+    cudaError_t _le = tdl::launch_pdl(conv_wgrad2_kernel<BLOCK_N>, dim3(grid), dim3(kThreads), Cfg::kSmemBytes, st,
+                                      tdy, tx, g, dw, m_tiles, n_tiles,
+                                      (g_wgrad_bulk != 0 && (reinterpret_cast<uintptr_t>(dw) & 15) == 0) ? 1 : 0);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "conv_wgrad2_kernel");
+  }
+  TDL_LAUNCH_OK("conv_wgrad2_kernel");
+  return 0;
+}
+
 }  // namespace conv
 }  // namespace tdl
 
@@ -2456,6 +2700,19 @@ TDL_API int tdl_conv2d_wgrad_bf16(const void* x, const void* dy, float* dw, int 
     if (rc) return rc;
   }
   cudaStream_t st = (cudaStream_t)stream;
+  // CTA pairs for 256-wide Cout tiles (conv_wgrad2_kernel).  Alone the pair kernel is 1.3-1.5x faster on the deep 1x1
+  // layers (1024 -> 256 @14x14: 57 -> 39 us, 2048 -> 512 @7x7: 51 -> 35 us; profiles/wgrad_epilogue_and_grid.txt), but
+  // inside the training step the weight gradients run on a side stream next to the data-gradient chain, are not on
+  // the critical path, and two-CTA clusters wait for a free SM pair: ResNet-50 unchanged in cycles, Xception-41 /
+  // the reference network 0.6 % / 2 % slower.  Hence opt-in: TDL_WGRAD_2CTA=1 / tdl_conv2d_set_wgrad_pair_mode(1).
+  if (g_wgrad_pair < 0) {
+    const char* e = getenv("TDL_WGRAD_2CTA");
+    g_wgrad_pair = e ? atoi(e) : 0;
+  }
+  if (mt == 2 && g_wgrad_pair != 0 && block_n >= 128) {
+    if (block_n == 256) return launch_wgrad2<256>(tdy, tx, g, dw, st);
+    return launch_wgrad2<128>(tdy, tx, g, dw, st);
+  }
   if (mt == 2) {
     if (block_n == 256) return launch_wgrad<2, 256>(tdy, tx, g, dw, st);
     if (block_n == 128) return launch_wgrad<2, 128>(tdy, tx, g, dw, st);
@@ -2707,6 +2964,13 @@ TDL_API int tdl_conv2d_set_halo_mode(int mode) {
 
 // Halo form with the weights resident in shared memory, picked on its own for stride-1 RxS layers with one Cout tile
 // whose weights fit beside two patch buffers (3x3 64 -> 64): 1 = on (default), 0 = off.
+// CTA-pair weight gradient for Cout >= 256, Cin > 64: 1 = on, 0 = single-CTA kernel (default, see tdl_conv2d_wgrad_bf16)
+TDL_API int tdl_conv2d_set_wgrad_pair_mode(int mode) {
+  TDL_REQUIRE(mode == 0 || mode == 1, "wgrad pair mode must be 0 or 1");
+  tdl::conv::g_wgrad_pair = mode;
+  return 0;
+}
+
 // wgrad grid tuning (measurement hooks): whole-wave snapping on / off, constant of the split-count model (< 0 = default)
 TDL_API int tdl_conv2d_set_wgrad_tuning(int wave_snap, float model_k) {
   tdl::conv::g_wgrad_snap = wave_snap ? 1 : 0;

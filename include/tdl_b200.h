@@ -40,6 +40,7 @@ int tdl_conv2d_fprop_res_mask_bf16(const void* x, const void* w, void* y, const 
 int tdl_conv2d_set_pair_mode(int mode); /* 1 = CTA pairs (tcgen05 cta_group::2, M = 256 MMAs, half a weight tile per CTA) for Cout tiles of 128/256; also TDL_CONV_2CTA */
 int tdl_conv2d_get_pair_mode(void);
 int tdl_conv2d_set_halo_mode(int mode); /* experimental halo-reuse main loop for stride-1 RxS filters: 0 off (default), 1 on */
+int tdl_conv2d_set_wgrad_pair_mode(int mode); /* weight gradient on CTA pairs (tcgen05 cta_group::2, 256 x 256 tile per pair) for Cout >= 256: 1 on, 0 off (default: faster alone, not inside the overlapped training step) */
 int tdl_conv2d_set_wgrad_tuning(int wave_snap, float model_k); /* measurement hooks: whole-wave grids on/off, split-count model constant (< 0 = default 1.1) */
 int tdl_conv2d_set_wgrad_bulk_mode(int mode); /* weight-gradient epilogue: 1 = bulk reductions (cp.reduce.async.bulk) from shared memory (default), 0 = per-thread red.global.add */
 int tdl_conv2d_set_wgrad_row_mode(int mode); /* weight gradient of 64-channel 3-wide stride-1 filters: the taps of a filter row share one haloed input tile; 0 off, 1 on (default), 2 on with three narrow MMAs */

@@ -331,6 +331,41 @@ def test_conv_wgrad_tcgen05(O, case, row_mode):
         _native.lib().tdl_conv2d_set_wgrad_row_mode(1)
 
 
+@pytest.mark.parametrize("case", [(4, 14, 256, 256, 3, 1, 1), (2, 28, 128, 256, 1, 2, 1), (2, 14, 200, 320, 3, 1, 1),
+                                  (8, 7, 1024, 512, 1, 1, 1), (3, 13, 264, 520, 3, 1, 2), (1, 5, 256, 256, 3, 1, 1)])
+@pytest.mark.parametrize("bulk", [0, 1], ids=["red_add", "bulk_reduce"])
+def test_conv_wgrad_cta_pair_kernel(O, case, bulk):
+    """Cout >= 256: the weight gradient runs on CTA pairs (M = 256 MMAs, half an input tile per CTA).  Checked against
+    the fp32 reference and against the single-CTA kernel, with both epilogues (ragged channel counts, tiny maps whose
+    tiles have fewer than 64 pixels, strides and dilation included)."""
+    from tensorflowdistributedlearning_b200 import _native
+
+    lib = _native.lib()
+    N, H, C, K, R, stride, dil = case
+    torch.manual_seed(5)
+    x = torch.randn(N, H, H, C, device="cuda").bfloat16()
+    P, pt, pb = O.same_pad(H, R, stride, dil)
+    dy = torch.randn(N, P, P, K, device="cuda").bfloat16()
+    outs = []
+    try:
+        assert lib.tdl_conv2d_set_wgrad_bulk_mode(bulk) == 0
+        for pair in (0, 1):
+            assert lib.tdl_conv2d_set_wgrad_pair_mode(pair) == 0
+            dw = torch.zeros(K, R * R, C, device="cuda")
+            O.conv2d_wgrad(x, dy, dw, R=R, S=R, stride=stride, dil=dil, pad_h=pt, pad_w=pt)
+            outs.append(dw)
+    finally:
+        lib.tdl_conv2d_set_wgrad_pair_mode(0)
+        lib.tdl_conv2d_set_wgrad_bulk_mode(1)
+    xin = F.pad(x.float().permute(0, 3, 1, 2), (pt, pb, pt, pb))
+    wr = torch.zeros(K, C, R, R, device="cuda", requires_grad=True)
+    (gw,) = torch.autograd.grad(F.conv2d(xin, wr, None, stride=stride, dilation=dil), wr,
+                                dy.float().permute(0, 3, 1, 2))
+    ref = gw.permute(0, 2, 3, 1).reshape(K, R * R, C)
+    assert rel_err(outs[1], ref) < 2e-2
+    assert rel_err(outs[1], outs[0]) < 1e-4  # same bf16 products, fp32 sums in a different order
+
+
 def _wgrad_case(O, case):
     N, H, C, K, R, stride, dil = case
     torch.manual_seed(1)
