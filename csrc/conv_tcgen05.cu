@@ -64,6 +64,13 @@ static int encode_map(CUtensorMap* m, CUtensorMapDataType dtype, int elem_bytes,
   }
   CUresult r = fn(m, dtype, (cuuint32_t)rank, const_cast<void*>(base), gdim, gstr, b, e, CU_TENSOR_MAP_INTERLEAVE_NONE,
                   swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r == CUDA_ERROR_INVALID_CONTEXT) {
+    // A thread that has made no runtime call yet (autograd's backward thread whose first kernel is ours) has no
+    // current context for the driver entry point: bind the primary context and encode again.
+    cudaFree(nullptr);
+    r = fn(m, dtype, (cuuint32_t)rank, const_cast<void*>(base), gdim, gstr, b, e, CU_TENSOR_MAP_INTERLEAVE_NONE,
+           swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  }
   if (r != CUDA_SUCCESS) {
     snprintf(tdl::err_buf(), 512,
              "cuTensorMapEncodeTiled failed (%d): rank %d dims [%llu,%llu,%llu,%llu] box [%u,%u,%u,%u]", (int)r, rank,
@@ -1860,6 +1867,34 @@ __global__ void stem_pack_kernel(const bf16* __restrict__ x, bf16* __restrict__ 
   }
 }
 
+// RGB images (C = 3, even H and W): one thread builds BOTH planes of a 2x2 pixel block from two 12-byte reads (three
+// aligned 32-bit words per image row) and writes two 16-byte vectors.  The generic kernel above does eight scalar loads
+// with a division each per vector: 110 us for 256 x 224 x 224 against ~30 us of traffic.
+__global__ void __launch_bounds__(256)
+stem_pack_c3_kernel(const bf16* __restrict__ x, bf16* __restrict__ planes, int N, int H, int W, int H2, int W2) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
+  const int64_t total = (int64_t)N * H2 * W2;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int w2 = (int)(i % W2);
+    const int64_t nh = i / W2;  // n * H2 + h2
+    const int h2 = (int)(nh % H2);
+    const int n = (int)(nh / H2);
+    // pixels (2h2, 2w2), (2h2, 2w2+1) = 6 bf16 = words a0..a2; the row below = b0..b2
+    const uint32_t* r0 = reinterpret_cast<const uint32_t*>(x + (((int64_t)n * H + 2 * h2) * W + 2 * w2) * 3);
+    const uint32_t* r1 = reinterpret_cast<const uint32_t*>(x + (((int64_t)n * H + 2 * h2 + 1) * W + 2 * w2) * 3);
+    const uint32_t a0 = __ldg(r0), a1 = __ldg(r0 + 1), a2 = __ldg(r0 + 2);
+    const uint32_t b0 = __ldg(r1), b1 = __ldg(r1 + 1), b2 = __ldg(r1 + 2);
+    // packed channel cp = block * 3 + c, block = dy * 2 + dx: plane 0 = cp 0..7, plane 1 = cp 8..11 then zeros
+    bf16x8 p0, p1;
+    p0.raw = make_uint4(a0, a1, a2, b0);
+    p1.raw = make_uint4(b1, b2, 0u, 0u);
+    bf16* o = planes + (nh * 2 * W2 + w2) * 8;
+    st8(o, p0);
+    st8(o + (int64_t)W2 * 8, p1);
+  }
+}
+
 // fp32 master [K, R, S, C]  ->  bf16 [K][Th*Tw][16] for the space-to-depth problem: packed tap (r2, s2), channel
 // cp = (dy*2+dx)*C + c  <-  original tap r = 2*(r2 - pad2_h) + dy + pad_h (same for s), zero when outside the filter.
 __global__ void stem_weight_prep_kernel(const float* __restrict__ w, bf16* __restrict__ out, int K, int R, int S, int C,
@@ -2780,6 +2815,15 @@ TDL_API int tdl_conv_stem_pack(const void* x, void* planes, int N, int H, int W,
   if (total == 0) return 0;
   int64_t blocks = cdiv(total, 256);
   if (blocks > (int64_t)num_sms() * 16) blocks = (int64_t)num_sms() * 16;
+  if (C == 3 && H % 2 == 0 && W % 2 == 0 && (reinterpret_cast<uintptr_t>(x) & 3) == 0) {
+    int64_t b3 = cdiv(total / 2, 256);
+    if (b3 > (int64_t)num_sms() * 16) b3 = (int64_t)num_sms() * 16;
+    cudaError_t _le = tdl::launch_pdl(stem_pack_c3_kernel, dim3((int)b3), dim3(256), 0, (cudaStream_t)stream,
+                                      (const bf16*)x, (bf16*)planes, N, H, W, H2, W2);
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "stem_pack_c3_kernel");
+    TDL_LAUNCH_OK("stem_pack_c3_kernel");
+    return 0;
+  }
   {
     cudaError_t _le = tdl::launch_pdl(stem_pack_kernel, dim3((int)blocks), dim3(256), 0, (cudaStream_t)stream,
         (const bf16*)x, (bf16*)planes, N, H, W, C, H2, W2);

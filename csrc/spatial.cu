@@ -894,6 +894,42 @@ u8_to_bf16_kernel(const uint8_t* __restrict__ x, bf16* __restrict__ y, int64_t p
     y[i] = __float2bfloat16(v);
   }
 }
+// Unpadded images (Cpad == C <= 4, element count a multiple of 16): 16 bytes in, two 16-byte vectors out per thread;
+// the channel of element j is (first + j) % C with the per-channel constants in registers.
+template <int C>
+__global__ void __launch_bounds__(kThreads)
+u8_to_bf16_vec_kernel(const uint8_t* __restrict__ x, bf16* __restrict__ y, int64_t groups,
+                      const float* __restrict__ mean, const float* __restrict__ inv_std) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
+  float m[C], s[C];
+#pragma unroll
+  for (int c = 0; c < C; ++c) {
+    m[c] = mean[c];
+    s[c] = inv_std[c];
+  }
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < groups; i += (int64_t)gridDim.x * blockDim.x) {
+    const uint4 in = __ldg(reinterpret_cast<const uint4*>(x) + i);
+    const uint32_t wds[4] = {in.x, in.y, in.z, in.w};
+    int c = (int)((i * 16) % C);
+    float v[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      const float u = (float)((wds[j >> 2] >> (8 * (j & 3))) & 0xffu);
+      float mc = m[0], sc = s[0];
+#pragma unroll
+      for (int k = 1; k < C; ++k)
+        if (c == k) {
+          mc = m[k];
+          sc = s[k];
+        }
+      v[j] = (u * (1.f / 255.f) - mc) * sc;  // the same expression as the scalar kernel: identical rounding
+      if (++c == C) c = 0;
+    }
+    st8(y + i * 16, pack8(v));
+    st8(y + i * 16 + 8, pack8(v + 8));
+  }
+}
 }  // namespace spatial
 }  // namespace tdl
 
@@ -902,6 +938,22 @@ TDL_API int tdl_u8_to_bf16_normalize(const void* x_u8, void* y_bf16, int64_t pix
   TDL_REQUIRE(Cpad >= C, "Cpad must be >= C");
   const int64_t total = pixels * Cpad;
   if (total == 0) return 0;
+  if (Cpad == C && C >= 1 && C <= 4 && total % 16 == 0 && (reinterpret_cast<uintptr_t>(x_u8) & 15) == 0 &&
+      (reinterpret_cast<uintptr_t>(y_bf16) & 15) == 0) {
+    const int64_t groups = total / 16;
+    const dim3 grid(tdl::spatial::grid_for(groups)), block(tdl::spatial::kThreads);
+    cudaStream_t st = (cudaStream_t)stream;
+    cudaError_t _le;
+    switch (C) {
+      case 1: _le = tdl::launch_pdl(tdl::spatial::u8_to_bf16_vec_kernel<1>, grid, block, 0, st, (const uint8_t*)x_u8, (tdl::bf16*)y_bf16, groups, mean, inv_std); break;
+      case 2: _le = tdl::launch_pdl(tdl::spatial::u8_to_bf16_vec_kernel<2>, grid, block, 0, st, (const uint8_t*)x_u8, (tdl::bf16*)y_bf16, groups, mean, inv_std); break;
+      case 3: _le = tdl::launch_pdl(tdl::spatial::u8_to_bf16_vec_kernel<3>, grid, block, 0, st, (const uint8_t*)x_u8, (tdl::bf16*)y_bf16, groups, mean, inv_std); break;
+      default: _le = tdl::launch_pdl(tdl::spatial::u8_to_bf16_vec_kernel<4>, grid, block, 0, st, (const uint8_t*)x_u8, (tdl::bf16*)y_bf16, groups, mean, inv_std); break;
+    }
+    if (_le != cudaSuccess) return tdl::cuda_fail(_le, "tdl::spatial::u8_to_bf16_vec_kernel");
+    TDL_LAUNCH_OK("u8_to_bf16_vec_kernel");
+    return 0;
+  }
   {
     cudaError_t _le = tdl::launch_pdl(tdl::spatial::u8_to_bf16_kernel, dim3(tdl::spatial::grid_for(total)),
         dim3(tdl::spatial::kThreads), 0, (cudaStream_t)stream, (const uint8_t*)x_u8, (tdl::bf16*)y_bf16, pixels, C,

@@ -17,10 +17,13 @@ from tensorflowdistributedlearning_b200.parallel.trainer import TowerTrainer, cl
 
 ap = argparse.ArgumentParser()
 ap.add_argument("--model", default="resnet50")
-ap.add_argument("--batch", type=int, default=256)
-ap.add_argument("--size", type=int, default=224)
+ap.add_argument("--batch", type=int, default=0, help="default: the benchmark batch of the model")
+ap.add_argument("--size", type=int, default=0, help="default: the benchmark image size of the model")
 ap.add_argument("--out", default="gpurun_out/profile_step.txt")
 args = ap.parse_args()
+_defaults = {"xception41": (64, 299), "refseg": (32, 101)}  # everything else: 256 x 224x224 (bench.py's configs)
+args.batch = args.batch or _defaults.get(args.model, (256, 224))[0]
+args.size = args.size or _defaults.get(args.model, (256, 224))[1]
 
 group = TowerGroup(device="cuda")
 if args.model == "refseg":  # the reference's own network: 101x101x2 input, Lovasz hinge, Adam
@@ -35,8 +38,9 @@ if args.model == "refseg":  # the reference's own network: 101x101x2 input, Lova
 else:
     model = models.build(args.model, num_classes=1000)
     tr = TowerTrainer(model, group, batch=args.batch, input_hwc=(args.size, args.size, 3),
-                      loss_fn=classification_loss, use_graph=False, kind="sgdm", lr=0.1, momentum=0.9,
-                      weight_decay=1e-4)
+                      loss_fn=classification_loss, use_graph=False,
+                      **(dict(kind="adam", lr=1e-3) if args.model == "xception41" else
+                         dict(kind="sgdm", lr=0.1, momentum=0.9, weight_decay=1e-4)))
     tr.images.copy_(torch.randint(0, 256, tr.images.shape, dtype=torch.uint8))
     tr.labels.copy_(torch.randint(0, 1000, tr.labels.shape))
 for _ in range(3):

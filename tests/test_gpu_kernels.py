@@ -645,6 +645,38 @@ def test_conv_stem_space_to_depth_tcgen05(O, case):
     assert rel_err(w.grad, wr.grad.permute(0, 2, 3, 1)) < 2e-2
 
 
+@pytest.mark.parametrize("shape", [(3, 224, 224, 3), (2, 100, 52, 3), (2, 99, 51, 3), (2, 64, 64, 4), (2, 34, 30, 2)])
+def test_stem_pack_layout(O, shape):
+    """Space-to-depth packing [N,H,W,C] -> [N,H/2,2,W/2,8]: packed channel (dy*2+dx)*C + c, zero beyond 4*C and beyond
+    the image.  Even RGB images take the vectorised kernel, everything else the generic one; both against torch."""
+    n, h, w, c = shape
+    torch.manual_seed(8)
+    x = torch.randn(n, h, w, c, device="cuda").bfloat16()
+    planes = O.conv_stem_pack(x)
+    h2, w2 = (h + 1) // 2, (w + 1) // 2
+    xp = F.pad(x, (0, 0, 0, 2 * w2 - w, 0, 2 * h2 - h))
+    blocks = xp.view(n, h2, 2, w2, 2, c).permute(0, 1, 3, 2, 4, 5).reshape(n, h2, w2, 4 * c)  # [.., (dy,dx,c)]
+    ref = F.pad(blocks, (0, 16 - 4 * c)).view(n, h2, w2, 2, 8).permute(0, 1, 3, 2, 4)
+    assert planes.shape == (n, h2, 2, w2, 8) and torch.equal(planes, ref.contiguous())
+
+
+@pytest.mark.parametrize("shape", [(4, 224, 224, 3), (3, 101, 101, 2), (2, 64, 64, 4), (5, 33, 31, 3), (2, 16, 16, 1)])
+def test_u8_normalise_vectorised_equals_formula(O, shape):
+    """uint8 -> bf16 ((x/255 - mean) * inv_std): the 16-bytes-per-thread kernel (element counts divisible by 16) and the
+    scalar one give the bf16 rounding of the fp32 formula; with channel padding the extra lanes are zero."""
+    n, h, w, c = shape
+    torch.manual_seed(9)
+    x = torch.randint(0, 256, shape, dtype=torch.uint8, device="cuda")
+    mean = torch.rand(c, device="cuda")
+    inv_std = 1.0 / (0.2 + torch.rand(c, device="cuda"))
+    y = O.u8_to_bf16_normalize(x, mean, inv_std)
+    ref = ((x.float() * (1.0 / 255.0) - mean) * inv_std).bfloat16()
+    assert y.shape == x.shape and (y.float() - ref.float()).abs().max() <= 2 ** -7 * ref.float().abs().max()
+    assert (y != ref).float().mean() < 1e-3  # identical up to fma contraction on a handful of round-to-even ties
+    yp = O.u8_to_bf16_normalize(x, mean, inv_std, c_pad=8)
+    assert torch.equal(yp[..., :c], y) and not yp[..., c:].any()
+
+
 @pytest.mark.parametrize("variant", [0, 1])
 def test_conv_stem_wgrad_variants_and_accumulate(O, variant):
     """tdl_conv_stem_wgrad with M = 128 / M = 64 accumulators, overwrite and accumulate forms, odd image size."""
