@@ -67,14 +67,21 @@ class Bottleneck(TFModule):
                             weight_decay=bn.weight_decay, pad_in=True)
 
     def forward(self, x, end_points: Optional[dict] = None, prefix: str = ""):
-        if self.shortcut is None and self.stride == 1:
-            # identity shortcut at full resolution: it takes an alias of the pre-activation BatchNorm's input, so its
-            # gradient is added (and the input's own ReLU backward applied) inside that BatchNorm's backward kernel
-            pre, sc = self.preact(x, relu=True, want_tap=True)
+        # The pre-activation BatchNorm hands out an alias ("tap") of its input: whatever else reads the unit input
+        # (identity shortcut, subsampled shortcut) reads the alias, so that gradient comes back to the BatchNorm node
+        # and is added -- and the input's own ReLU backward applied -- inside its backward kernel.  A projection
+        # shortcut reads the pre-activation instead, through an alias handed out by conv1: its gradient is added on the
+        # tensor core inside conv1's data-gradient kernel.  No aten::add_ / threshold_backward per unit either way.
+        pre, xa = self.preact(x, relu=True, want_tap=True)
+        if self.shortcut is None:
+            sc = xa if self.stride == 1 else L.subsample(xa, self.stride)
+            r = self.conv1(pre)
+        elif self.training and torch.is_grad_enabled():
+            r, pa = self.conv1(pre, want_tap=True)
+            sc = self.shortcut(pa)
         else:
-            pre = self.preact(x, relu=True)
-            sc = L.subsample(x, self.stride) if self.shortcut is None else self.shortcut(pre)
-        r = self.conv1(pre)
+            r = self.conv1(pre)
+            sc = self.shortcut(pre)
         r = self.conv2(r)
         want_r = end_points is not None and f"{prefix}{self.scope}/conv3" in getattr(end_points, "wanted", ())
         if end_points is None or (hasattr(end_points, "wanted") and not want_r):
