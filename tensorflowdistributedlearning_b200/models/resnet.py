@@ -344,10 +344,9 @@ class ResNetClassifier(TFModule):
                                        stride_first=True) for i, n in enumerate(layers)]
         self.net = ResNetV2Beta(in_channels, blocks, num_classes=num_classes, global_pool=True, output_stride=None,
                                 root="7x7", scope=scope, bn=bn, postnorm=False, symmetric_padding=True)
-        # 3-channel images are zero-padded to 8 channels on the device (16-byte TMA rows) so that the 7x7 stem also
-        # runs on the tcgen05 kernel; the trainer reads this attribute
-        # (measured: with only 16 valid bytes per 128-byte TMA row the 7x7/s2 stem is TMA-row-bound on the generic
-        #  kernel -- 5.3 ms vs cuDNN's 1.5 ms -- so the stem stays on the cuDNN path until it has its own kernel)
+        # The 3-channel image goes to the first layer unpadded: the stem kernel packs it space-to-depth itself
+        # (csrc/conv_tcgen05.cu, kStem).  The trainer reads this attribute; a value would make it zero-pad the
+        # channels on the device (the generic kernel on a padded image measured 5.3 ms against the stem kernel's 0.18).
         self.input_channel_pad = None
         for m in self.modules():  # zero-init the last BN gamma of every unit (standard large-batch recipe)
             if isinstance(m, BottleneckV1) and m.conv3.bn.gamma is not None:
