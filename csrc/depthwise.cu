@@ -466,6 +466,7 @@ struct TShape {
   int N, H, W, C, P, Q, stride, dil, pad_h, pad_w;
   int TH, TW, BH, BW;          // output tile, input box
   int tiles_h, tiles_w;
+  int flip;                    // forward kernel: read the taps in reverse order (data gradient of a stride-1 layer)
 };
 
 constexpr int kT = 512;  // 16 warps: 16 channel-quads x 32 strip groups
@@ -534,7 +535,7 @@ depthwise3x3_tma_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
 #pragma unroll
   for (int t = 0; t < 9; ++t)
 #pragma unroll
-    for (int c = 0; c < 4; ++c) wt[t][c] = ch_ok ? w[(size_t)t * s.C + ch + c] : 0.f;
+    for (int c = 0; c < 4; ++c) wt[t][c] = ch_ok ? w[(size_t)(s.flip ? 8 - t : t) * s.C + ch + c] : 0.f;
 #pragma unroll
   for (int c = 0; c < 4; ++c) b8[c] = (bias && ch_ok) ? bias[ch + c] : 0.f;
   // optional fused BatchNorm statistics of the (bf16-rounded) output: a thread's four channels never change, so the
@@ -576,7 +577,19 @@ depthwise3x3_tma_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
   const uint32_t smem_base = ptx::smem_u32(smem);
   int it = 0, stage = 0;
   uint32_t parity = 0;
+  // tile coordinates advance by the grid stride without a division per tile
+  const int per_img = s.tiles_w * s.tiles_h;
+  const int step_n = (int)gridDim.x / per_img, step_r = (int)gridDim.x % per_img;
+  const int step_h = step_r / s.tiles_w, step_w = step_r % s.tiles_w;
+  int cur_n = (int)blockIdx.x / per_img, cur_h = ((int)blockIdx.x % per_img) / s.tiles_w,
+      cur_w = ((int)blockIdx.x % per_img) % s.tiles_w;
   for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
+    const int tw_i = cur_w, th_i = cur_h, n = cur_n;
+    cur_w += step_w;
+    if (cur_w >= s.tiles_w) { cur_w -= s.tiles_w; ++cur_h; }
+    cur_h += step_h;
+    if (cur_h >= s.tiles_h) { cur_h -= s.tiles_h; ++cur_n; }
+    cur_n += step_n;
     const int ahead = tile + (stages - 1) * gridDim.x;
     if (tid == 0 && ahead < tiles) issue(ahead, stage == 0 ? stages - 1 : stage - 1);  // consumed in iteration it-1
     ptx::mbar_wait(&full[stage], parity);
@@ -588,27 +601,48 @@ depthwise3x3_tma_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
       parity ^= 1;
     }
     if (active) {
-      const int tw_i = tile % s.tiles_w;
-      const int th_i = (tile / s.tiles_w) % s.tiles_h;
-      const int n = tile / (s.tiles_w * s.tiles_h);
       float acc[4][4];
 #pragma unroll
       for (int j = 0; j < 4; ++j)
 #pragma unroll
         for (int c = 0; c < 4; ++c) acc[j][c] = b8[c];
+      if (STRIDE == 1 && DIL == 1) {
+        // dense case on packed fp32 FMAs (fma.rn.f32x2, two channels per instruction): the inner product is 144 scalar
+        // FMAs per thread and tile, the largest single share of this issue-bound kernel's instructions
+        float2 a2[4][2];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          a2[j][0] = make_float2(b8[0], b8[1]);
+          a2[j][1] = make_float2(b8[2], b8[3]);
+        }
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+          float2 v2[6][2];
+#pragma unroll
+          for (int c = 0; c < 6; ++c) {
+            float v[4];
+            lds4_at(in_a + xoff[r][c], v, relu_in);
+            v2[c][0] = make_float2(v[0], v[1]);
+            v2[c][1] = make_float2(v[2], v[3]);
+          }
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int t = 0; t < 3; ++t) {
+              a2[j][0] = __ffma2_rn(v2[j + t][0], make_float2(wt[r * 3 + t][0], wt[r * 3 + t][1]), a2[j][0]);
+              a2[j][1] = __ffma2_rn(v2[j + t][1], make_float2(wt[r * 3 + t][2], wt[r * 3 + t][3]), a2[j][1]);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          acc[j][0] = a2[j][0].x; acc[j][1] = a2[j][0].y; acc[j][2] = a2[j][1].x; acc[j][3] = a2[j][1].y;
+        }
+      }
 #pragma unroll
       for (int r = 0; r < 3; ++r) {
         const int lrow0 = (ph * STRIDE + r * DIL) * s.BW + pw0 * STRIDE;
         if (STRIDE == 1 && DIL == 1) {
-          float v[6][4];
-#pragma unroll
-          for (int c = 0; c < 6; ++c) lds4_at(in_a + xoff[r][c], v[c], relu_in);
-#pragma unroll
-          for (int j = 0; j < 4; ++j)
-#pragma unroll
-            for (int t = 0; t < 3; ++t)
-#pragma unroll
-              for (int c = 0; c < 4; ++c) acc[j][c] = fmaf(v[j + t][c], wt[r * 3 + t][c], acc[j][c]);
+          // (done above)
         } else {
 #pragma unroll
           for (int j = 0; j < 4; ++j)
@@ -762,15 +796,34 @@ depthwise3x3_tma_wgrad_kernel(const __grid_constant__ CUtensorMap tm_x, const __
       for (int r = 0; r < 3; ++r) {
         const int lrow0 = (ph * STRIDE + r * DIL) * s.BW + pw0 * STRIDE;
         if (STRIDE == 1 && DIL == 1) {
-          float v[6][4];
+          // packed fp32 FMAs (two channels per instruction), as in the forward kernel
+          float2 v2[6][2], a2[3][2];
 #pragma unroll
-          for (int c = 0; c < 6; ++c) lds4_at(in_a + xoff[r][c], v[c], relu_in);
+          for (int c = 0; c < 6; ++c) {
+            float v[4];
+            lds4_at(in_a + xoff[r][c], v, relu_in);
+            v2[c][0] = make_float2(v[0], v[1]);
+            v2[c][1] = make_float2(v[2], v[3]);
+          }
 #pragma unroll
-          for (int j = 0; j < 4; ++j)
+          for (int t = 0; t < 3; ++t) {
+            a2[t][0] = make_float2(acc[r * 3 + t][0], acc[r * 3 + t][1]);
+            a2[t][1] = make_float2(acc[r * 3 + t][2], acc[r * 3 + t][3]);
+          }
 #pragma unroll
-            for (int t = 0; t < 3; ++t)
+          for (int j = 0; j < 4; ++j) {
+            const float2 g0 = make_float2(g[j][0], g[j][1]), g1 = make_float2(g[j][2], g[j][3]);
 #pragma unroll
-              for (int c = 0; c < 4; ++c) acc[r * 3 + t][c] = fmaf(g[j][c], v[j + t][c], acc[r * 3 + t][c]);
+            for (int t = 0; t < 3; ++t) {
+              a2[t][0] = __ffma2_rn(g0, v2[j + t][0], a2[t][0]);
+              a2[t][1] = __ffma2_rn(g1, v2[j + t][1], a2[t][1]);
+            }
+          }
+#pragma unroll
+          for (int t = 0; t < 3; ++t) {
+            acc[r * 3 + t][0] = a2[t][0].x; acc[r * 3 + t][1] = a2[t][0].y;
+            acc[r * 3 + t][2] = a2[t][1].x; acc[r * 3 + t][3] = a2[t][1].y;
+          }
         } else {
 #pragma unroll
           for (int j = 0; j < 4; ++j)
@@ -825,6 +878,7 @@ TDL_API int tdl_depthwise3x3_tma_wgrad(const void* x, const void* dy, float* dw,
   if ((int64_t)N * P * Q == 0) return 0;
   TShape s;
   s.N = N; s.H = H; s.W = W; s.C = C; s.P = P; s.Q = Q; s.stride = stride; s.dil = dil; s.pad_h = pad_h; s.pad_w = pad_w;
+  s.flip = 0;
   choose_tile(P, Q, stride, &s.TH, &s.TW);
   s.BW = (s.TW - 1) * stride + 2 * dil + 1;
   s.BH = (s.TH - 1) * stride + 2 * dil + 1;
@@ -871,7 +925,8 @@ TDL_API int tdl_depthwise3x3_tma_wgrad(const void* x, const void* dy, float* dw,
 
 static int depthwise3x3_tma_fwd_impl(const void* x, const float* w, const float* bias, const void* mask, void* y,
                                      int N, int H, int W, int C, int P, int Q, int stride, int dil, int pad_h,
-                                     int pad_w, int relu_in, int relu_out, float* stats, int* nparts, void* stream) {
+                                     int pad_w, int relu_in, int relu_out, float* stats, int* nparts, void* stream,
+                                     int flip_taps = 0) {
   using namespace tdl::dwt;
   TDL_REQUIRE(C % 8 == 0, "C must be a multiple of 8");
   TDL_REQUIRE((stride == 1 || stride == 2) && (dil == 1 || dil == 2) && !(stride == 2 && dil == 2),
@@ -879,6 +934,7 @@ static int depthwise3x3_tma_fwd_impl(const void* x, const float* w, const float*
   if ((int64_t)N * P * Q == 0) return 0;
   TShape s;
   s.N = N; s.H = H; s.W = W; s.C = C; s.P = P; s.Q = Q; s.stride = stride; s.dil = dil; s.pad_h = pad_h; s.pad_w = pad_w;
+  s.flip = flip_taps ? 1 : 0;
   choose_tile(P, Q, stride, &s.TH, &s.TW);
   s.BW = (s.TW - 1) * stride + 2 * dil + 1;
   s.BH = (s.TH - 1) * stride + 2 * dil + 1;
@@ -930,6 +986,14 @@ TDL_API int tdl_depthwise3x3_tma_fwd(const void* x, const float* w, const float*
                                      int pad_w, int relu_in, int relu_out, void* stream) {
   return depthwise3x3_tma_fwd_impl(x, w, bias, mask, y, N, H, W, C, P, Q, stride, dil, pad_h, pad_w, relu_in, relu_out,
                                    nullptr, nullptr, stream);
+}
+
+// Data gradient of a stride-1 depthwise layer = the forward kernel on dy with the taps read in reverse order
+// (`w` is the layer's own [9][C] weight tensor: no flipped copy), optionally masked by the input's ReLU.
+TDL_API int tdl_depthwise3x3_tma_dgrad(const void* dy, const float* w, const void* mask, void* dx, int N, int H, int W,
+                                       int C, int dil, int pad_h, int pad_w, void* stream) {
+  return depthwise3x3_tma_fwd_impl(dy, w, nullptr, mask, dx, N, H, W, C, H, W, 1, dil, pad_h, pad_w, 0, 0, nullptr,
+                                   nullptr, stream, 1);
 }
 
 // Forward + per-CTA partial BatchNorm statistics of the bf16 output (for the BatchNorm that follows the depthwise conv in

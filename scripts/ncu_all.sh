@@ -8,7 +8,7 @@ declare -A K=(
   [augment]="augment:augment_seg_kernel" [adam]="adam:adam_kernel" [maxpool_fwd]="maxpool:maxpool_fwd_rows_kernel"
   [maxpool_bwd]="maxpool:maxpool_bwd_block_kernel" [upsample_fwd]="upsample:upsample_fwd_kernel"
   [upsample_bwd]="upsample:upsample_bwd_kernel" [smallk_fwd]="smallk:fwd_kernel" [smallk_bwd_weight]="smallk:bwd_weight_kernel"
-  [depthwise_dgrad]="depthwise_bwd:depthwise3x3_tma_kernel" [depthwise_wgrad]="depthwise_bwd:depthwise3x3_tma_wgrad_kernel"
+  [depthwise_fwd]="depthwise:depthwise3x3_tma_kernel" [depthwise_dgrad]="depthwise_bwd:depthwise3x3_tma_kernel" [depthwise_wgrad]="depthwise_bwd:depthwise3x3_tma_wgrad_kernel"
   [p2p_two_shot]="p2p:two_shot_kernel" [p2p_one_shot]="p2p:one_shot_kernel" [p2p_two_shot_bf16_wire]="p2p_wire:two_shot_wire_kernel"
   [conv_pair_3x3_256_14x14]="pair:conv_fprop2_kernel" [bn_bwd_partial_802816x64]="bn64:bn_bwd_partial_kernel"
   [fprop_3x3_64_56x56_resident]="conv3x3:conv_fprop_kernel" [wgrad_3x3_64_56x56_row]="wgrad64:conv_wgrad_kernel"

@@ -97,8 +97,8 @@ class _DepthwiseNative(torch.autograd.Function):
                     TF._count(1)
                 if stride == 1 and not relu:
                     n, h, w, _ = x.shape
-                    dx = O.depthwise3x3_fwd(dy, wd.flip(0, 1).contiguous().view(9, C), None, x if relu_in else None, 1,
-                                            dil, 2 * dil - pads[0], 2 * dil - pads[2], (h, w), False, False)
+                    dx = O.depthwise3x3_dgrad_s1(dy, wd.contiguous().view(9, C), x if relu_in else None, dil,
+                                                 2 * dil - pads[0], 2 * dil - pads[2])
                 elif stride == 2 and dil == 1 and not relu:
                     dx = O.depthwise3x3_dgrad_s2(dy, wd.view(9, C), x if relu_in else None, tuple(x.shape), pads[0],
                                                  pads[2])
