@@ -186,6 +186,18 @@ def proxy_arm(args):
     return 0
 
 
+def _heap_kind(trainer):
+    """Which heap the gradient buffer lives in: 'vmm' (csrc/vmm_heap.cu, cuMemCreate + cuMulticast), 'torch-symm',
+    'cudaipc' (default P2P heap) or 'local'."""
+    p2p = getattr(trainer.opt, "_p2p", None)
+    g = getattr(p2p, "grad", None)
+    if g is None:
+        return "local"
+    if getattr(g, "_vmm_own", None) is not None:
+        return "vmm"
+    return "torch-symm" if getattr(g, "_torch_tensor", None) is not None else "cudaipc"
+
+
 def measure(model_name, args, group, warmup):
     """One configuration, two numbers (see the module docstring): K graph-replayed steps on device-resident inputs,
     then K steps through TowerTrainer.train_step with the per-step host->device copy and loss read-back."""
@@ -279,7 +291,7 @@ def measure(model_name, args, group, warmup):
         "dtype": "bf16", "data": "synthetic", "impl": "ours",
         "config": {"model": model_name, "global_batch": global_batch, "per_tower_batch": batch,
                    "image": f"{h}x{w}x{c}", "seq_len": None, "parallelism": f"dp{n_gpus}",
-                   "optimizer": cfg["opt"], "grad_comm": trainer.opt.comm, "grad_wire": trainer.opt.grad_wire, "nvls": bool(getattr(trainer.opt, "nvls", False)), "cuda_graph": trainer._graph is not None,
+                   "optimizer": cfg["opt"], "grad_comm": trainer.opt.comm, "grad_wire": trainer.opt.grad_wire, "nvls": bool(getattr(trainer.opt, "nvls", False)), "symm_heap": _heap_kind(trainer), "cuda_graph": trainer._graph is not None,
                    "overlap": trainer.opt.overlap,
                    "l2": "no flush needed: each step streams far more than the 126 MB L2 (activations >> L2)",
                    "weights": "random init", "loss_after_timed_steps": round(loss_dev, 4)},

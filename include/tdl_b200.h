@@ -263,6 +263,22 @@ int tdl_adam_flat(float* param, void* grad, float* m1, float* m2, void* shadow_b
                   void* stream);
 int tdl_cast_f32_to_bf16(const float* src, void* dst, int64_t n, void* stream);
 
+/* ---- symmetric heap on the CUDA VMM API with an NVLS multicast mapping (csrc/vmm_heap.cu) ----
+ * One process per GPU.  Every tower: tdl_vmm_query -> pad the size to *granularity -> tdl_vmm_alloc (maps its own
+ * physical allocation, returns a POSIX descriptor) -> pass the descriptor to every peer (UNIX socket, SCM_RIGHTS) ->
+ * tdl_vmm_import each peer's.  Multicast: tower 0 tdl_vmm_mc_create, descriptor to all, others tdl_vmm_mc_import; all
+ * tdl_vmm_mc_add_device; barrier; all tdl_vmm_mc_bind_map -> the address multimem.ld_reduce / multimem.st take.
+ * Imported descriptors become the library's (closed by the matching free). */
+int tdl_vmm_query(int world, int* vmm_ok, int* mc_ok, int64_t* granularity);
+int tdl_vmm_alloc(int64_t padded_bytes, void** alloc_out, void** ptr_out, int* fd_out);
+int tdl_vmm_import(int fd, int64_t padded_bytes, void** alloc_out, void** ptr_out);
+int tdl_vmm_free(void* alloc);
+int tdl_vmm_mc_create(int world, int64_t padded_bytes, void** mc_out, int* fd_out);
+int tdl_vmm_mc_import(int fd, int64_t padded_bytes, void** mc_out);
+int tdl_vmm_mc_add_device(void* mc);
+int tdl_vmm_mc_bind_map(void* mc, void* alloc, void** mc_ptr_out);
+int tdl_vmm_mc_free(void* mc);
+
 /* ---- symmetric heap + P2P fused all-reduce/optimizer over NVLink (reference: MirroredStrategy NCCL all-reduce,
  *      model.py:115-119, Test.ipynb:200) ---- */
 int tdl_symm_alloc(int64_t bytes, void** out);

@@ -1,7 +1,7 @@
 """Multi-GPU checks and the all-reduce+optimizer sweep (BASELINE config 5).  Run under torchrun, one rank per GPU:
 
     python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 --master-port 29511 \
-        scripts/p2p_check.py [correctness] [stress] [sweep] [train] [resume] [nvls] [dead_nccl]
+        scripts/p2p_check.py [correctness] [stress] [sweep] [train] [resume] [nvls] [nvls_small] [dead_nccl]
 
 `tests/test_gpu_multi.py` runs correctness / stress / train / resume / dead_nccl under pytest on boxes with >= 2 GPUs.
 
@@ -123,9 +123,15 @@ def correctness():
     comm.close(); sbuf.close()
 
 
-def nvls():
+def nvls_small():
+    """NVLS correctness only, on small buffers (the pytest case): allocation through the library's own VMM heap unless
+    TDL_SYMM_BACKEND=torch, multicast mapping, mode-3 fused step vs the ordered fp32 reference."""
+    nvls(sweep=False)
+
+
+def nvls(sweep=True):
     """NVLS multimem path: correctness vs the ordered fp32 reference and a timing sweep next to two-shot / NCCL."""
-    sizes = [1 << 22, 1 << 24, 51_114_064 // 16 * 16, 1 << 26, 167_256_100 // 16 * 16, 1 << 28, 1 << 30]
+    sizes = [1 << 22, 1 << 24, 51_114_064 // 16 * 16, 1 << 26, 167_256_100 // 16 * 16, 1 << 28, 1 << 30] if sweep else [1 << 23]
     maxn = max(sizes) // 4
     try:
         gbuf = SymmetricBuffer(maxn * 4, multicast=True)
@@ -134,7 +140,8 @@ def nvls():
         emit(test="nvls", available=False, error=f"{type(e).__name__}: {e}"[:300], ok=True)
         return
     comm = P2PComm(gbuf, pbuf)
-    emit(test="nvls", available=bool(comm.has_multicast), mc_grad=hex(gbuf.mc_ptr), ok=True)
+    emit(test="nvls", available=bool(comm.has_multicast), mc_grad=hex(gbuf.mc_ptr),
+         backend="vmm (csrc/vmm_heap.cu)" if gbuf._vmm_own is not None else "torch symmetric memory", ok=True)
     if not comm.has_multicast:
         return
     lr_state = torch.tensor([0.1, 0.05], device="cuda")
@@ -158,6 +165,23 @@ def nvls():
     emit(test="nvls_correctness", rel_err=rel_err(got, ref), mirrors_identical=bool(same.item()),
          grad_zeroed=float(gbuf.tensor()[:n].abs().max()) == 0.0, ok=rel_err(got, ref) < 1e-5 and bool(same.item()))
     dist.barrier()
+    # the same buffers through the UNICAST peer mappings of the heap: a two-shot step (peer loads + peer stores)
+    gbuf.tensor()[:n].copy_(g)
+    pbuf.tensor()[:n].copy_(p0)
+    m1.zero_()
+    torch.cuda.synchronize(); dist.barrier()
+    comm.fused_step(0, n, kind=1, grad_is_bf16=False, zero_grad=True, m1=m1, m2=None, lr_state=lr_state, a=0.9, b=1e-4,
+                    c=0.0, mode=2)
+    torch.cuda.synchronize()
+    got = pbuf.tensor()[:n]
+    chk = got.clone(); dist.broadcast(chk, 0)
+    same = torch.tensor([float(torch.equal(chk, got))], device="cuda"); dist.all_reduce(same, op=dist.ReduceOp.MIN)
+    emit(test="nvls_heap_peer_maps", rel_err=rel_err(got, ref), mirrors_identical=bool(same.item()),
+         ok=rel_err(got, ref) < 1e-5 and bool(same.item()))
+    dist.barrier()
+    if not sweep:
+        comm.close(); gbuf.close(); pbuf.close()
+        return
     gbuf.tensor().normal_()
     for nbytes in sizes:
         nn = nbytes // 4
@@ -604,7 +628,7 @@ if __name__ == "__main__":
     which = sys.argv[1:] or ["correctness", "stress", "train", "sweep"]
     t0 = time.time()
     for w in which:
-        {"correctness": correctness, "stress": stress, "sweep": sweep, "train": train, "nvls": nvls, "resume": resume,
+        {"correctness": correctness, "stress": stress, "sweep": sweep, "train": train, "nvls": nvls, "nvls_small": nvls_small, "resume": resume,
          "dead_nccl": dead_nccl, "wire": wire, "sweep2": sweep2}[w]()
         emit(test=w, event="done", secs=round(time.time() - t0, 1))
     group.shutdown()

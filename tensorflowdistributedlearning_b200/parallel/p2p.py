@@ -20,6 +20,53 @@ import torch.distributed as dist
 from .. import _native as N
 
 
+_FD_ROUND = [0]  # descriptor exchanges so far (identical on every tower: socket names must pair up)
+
+
+def exchange_fds(fd: Optional[int], rank: int, world: int, group=None, root: Optional[int] = None) -> List[Optional[int]]:
+    """Pass file descriptors between the towers of one node over abstract UNIX sockets (SCM_RIGHTS).
+
+    ``root=None``: all-gather -- every tower sends ``fd`` to every other tower; returns the list indexed by rank (own
+    entry = ``fd``).  ``root=r``: broadcast -- only tower ``r`` sends; every other tower's list has just entry ``r``.
+    Received descriptors are new descriptors of this process (the caller owns them).  Collective: all towers call it
+    in the same order."""
+    import socket
+    import struct
+
+    _FD_ROUND[0] += 1
+    base = f"\0tdl_fd_{os.environ.get('MASTER_PORT', '0')}_{os.getuid()}_{_FD_ROUND[0]}"
+    out: List[Optional[int]] = [None] * world
+    if root is None or root == rank:
+        out[rank] = fd
+    senders = [r for r in range(world) if r != rank and (root is None or r == root)]
+    srv = None
+    if senders:
+        srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+        srv.bind(f"{base}_{rank}")
+        srv.listen(world)
+    dist.barrier(group=group)  # every listener is up
+    try:
+        if root is None or root == rank:
+            for r in range(world):
+                if r == rank:
+                    continue
+                with socket.socket(socket.AF_UNIX, socket.SOCK_STREAM) as c:
+                    c.connect(f"{base}_{r}")
+                    socket.send_fds(c, [struct.pack("i", rank)], [int(fd)])
+        for _ in senders:
+            conn, _addr = srv.accept()
+            with conn:
+                msg, fds, _flags, _a = socket.recv_fds(conn, 4, 1)
+                if len(msg) != 4 or len(fds) != 1:
+                    raise RuntimeError("descriptor exchange: short message from a peer tower")
+                out[struct.unpack("i", msg)[0]] = fds[0]
+    finally:
+        if srv is not None:
+            srv.close()
+    dist.barrier(group=group)
+    return out
+
+
 class _RawCuda:
     """Zero-copy view of a raw device pointer for torch.as_tensor."""
 
@@ -31,9 +78,11 @@ class SymmetricBuffer:
     """One allocation per rank, same size everywhere, mapped into every peer."""
 
     def __init__(self, nbytes: int, group=None, emulate_world: int = 0, multicast: bool = False):
-        """``multicast=True`` allocates through torch's CUDA-VMM symmetric memory so that the buffer also gets an
-        NVLS multicast mapping (``self.mc_ptr``; 0 when the driver / fabric does not expose one).  The default path
-        is this library's own cudaIpc heap."""
+        """``multicast=True`` allocates from this library's CUDA-VMM heap (``csrc/vmm_heap.cu``: cuMemCreate + POSIX
+        descriptors passed between the towers + one cuMulticast object) so that the buffer also gets an NVLS multicast
+        mapping (``self.mc_ptr``; 0 when the driver / fabric does not expose one).  ``TDL_SYMM_BACKEND=torch`` uses
+        torch's symmetric-memory module for it instead (the earlier path; also the fallback when the driver has no
+        VMM descriptors).  Without ``multicast`` the buffer comes from the plain cudaIpc heap."""
         lib = N.lib()
         self.nbytes = int(nbytes)
         self.group = group
@@ -41,6 +90,12 @@ class SymmetricBuffer:
         self.mc_ptr = 0
         self._torch_tensor = None
         self._torch_handle = None
+        self._vmm_own = self._vmm_mc = None
+        self._vmm_peers: List[ctypes.c_void_p] = []
+        backend = os.environ.get("TDL_SYMM_BACKEND", "vmm")  # "torch": torch's symmetric memory (the round-1 path)
+        if (multicast and backend != "torch" and not self.emulated and dist.is_initialized()
+                and dist.get_world_size(group) > 1 and self._init_vmm(group)):
+            return
         if multicast and not self.emulated and dist.is_initialized() and dist.get_world_size(group) > 1:
             import torch.distributed._symmetric_memory as symm
 
@@ -89,6 +144,58 @@ class SymmetricBuffer:
                     self.ptrs.append(q.value)
         self._holders = [_RawCuda(p, self.nbytes) for p in self.ptrs]
 
+    def _init_vmm(self, group) -> bool:
+        """This library's own heap for multicast buffers (csrc/vmm_heap.cu): cuMemCreate allocations shared between the
+        towers as POSIX descriptors, every peer mapped, and one NVLS multicast object over all of them.  Returns False
+        (nothing allocated) when the driver lacks VMM descriptors -- the caller falls back."""
+        lib = N.lib()
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        vmm_ok, mc_ok, gran = ctypes.c_int(0), ctypes.c_int(0), ctypes.c_int64(0)
+        N.check(lib.tdl_vmm_query(ctypes.c_int(self.world), ctypes.byref(vmm_ok), ctypes.byref(mc_ok),
+                                  ctypes.byref(gran)), "tdl_vmm_query")
+        # every tower must take the same branch: agree on the minimum
+        caps = torch.tensor([vmm_ok.value, mc_ok.value, -gran.value], dtype=torch.int64, device="cuda")
+        dist.all_reduce(caps, op=dist.ReduceOp.MIN, group=group)
+        vmm_all, mc_all, gran_all = int(caps[0]), int(caps[1]), int(-caps[2])
+        if not vmm_all:
+            return False
+        padded = (self.nbytes + gran_all - 1) // gran_all * gran_all
+        own, ptr, fd = ctypes.c_void_p(), ctypes.c_void_p(), ctypes.c_int(-1)
+        N.check(lib.tdl_vmm_alloc(ctypes.c_int64(padded), ctypes.byref(own), ctypes.byref(ptr), ctypes.byref(fd)),
+                "tdl_vmm_alloc")
+        self._vmm_own, self._vmm_padded = own, padded
+        fds = exchange_fds(fd.value, self.rank, self.world, group)
+        self.ptrs = []
+        for r in range(self.world):
+            if r == self.rank:
+                self.ptrs.append(ptr.value)
+                continue
+            a, q = ctypes.c_void_p(), ctypes.c_void_p()
+            N.check(lib.tdl_vmm_import(ctypes.c_int(fds[r]), ctypes.c_int64(padded), ctypes.byref(a), ctypes.byref(q)),
+                    "tdl_vmm_import")
+            self._vmm_peers.append(a)
+            self.ptrs.append(q.value)
+        if mc_all:
+            mc, mfd = ctypes.c_void_p(), ctypes.c_int(-1)
+            if self.rank == 0:
+                N.check(lib.tdl_vmm_mc_create(ctypes.c_int(self.world), ctypes.c_int64(padded), ctypes.byref(mc),
+                                              ctypes.byref(mfd)), "tdl_vmm_mc_create")
+            got = exchange_fds(mfd.value if self.rank == 0 else None, self.rank, self.world, group, root=0)
+            if self.rank != 0:
+                N.check(lib.tdl_vmm_mc_import(ctypes.c_int(got[0]), ctypes.c_int64(padded), ctypes.byref(mc)),
+                        "tdl_vmm_mc_import")
+            N.check(lib.tdl_vmm_mc_add_device(mc), "tdl_vmm_mc_add_device")
+            dist.barrier(group=group)  # every device is registered before anyone binds memory
+            mptr = ctypes.c_void_p()
+            N.check(lib.tdl_vmm_mc_bind_map(mc, own, ctypes.byref(mptr)), "tdl_vmm_mc_bind_map")
+            self._vmm_mc, self.mc_ptr = mc, int(mptr.value)
+        self._own, self._opened = [], []
+        self._holders = [_RawCuda(p, self.nbytes) for p in self.ptrs]
+        self.tensor(torch.uint8).zero_()
+        torch.cuda.synchronize()
+        dist.barrier(group=group)
+        return True
+
     def tensor(self, dtype=torch.float32, rank: Optional[int] = None) -> torch.Tensor:
         """This rank's buffer (or, in emulation, the buffer of ``rank``) as a flat tensor of ``dtype``."""
         r = self.rank if rank is None else rank
@@ -105,6 +212,15 @@ class SymmetricBuffer:
 
     def close(self):
         lib = N.lib()
+        if self._vmm_mc is not None:
+            lib.tdl_vmm_mc_free(self._vmm_mc)
+            self._vmm_mc = None
+        for a in self._vmm_peers:
+            lib.tdl_vmm_free(a)
+        self._vmm_peers = []
+        if self._vmm_own is not None:
+            lib.tdl_vmm_free(self._vmm_own)
+            self._vmm_own = None
         for q in self._opened:
             lib.tdl_ipc_close(ctypes.c_void_p(q))
         for p in self._own:

@@ -17,6 +17,8 @@ def main():
     group = TowerGroup(device="cpu")
     if mode == "trainer_scalars":
         return trainer_scalars(out_dir, group)
+    if mode == "fd_exchange":
+        return fd_exchange(out_dir, group)
     torch.manual_seed(100 + group.rank)  # different init per tower: the X2 broadcast must make them equal
     model = models.SmallResNet(num_classes=10)
     if mode == "frozen_bn":
@@ -40,6 +42,35 @@ def main():
         hashes.append(opt.flat.param_flat.clone())
     torch.save({"params": opt.flat.param_flat.clone(), "stats": opt.flat.stats_flat.clone(), "per_step": hashes,
                 "step": int(opt.global_step.item()), "loss": float(loss)}, os.path.join(out_dir, f"{mode}_w{group.world}_r{group.rank}.pt"))
+    group.barrier()
+    group.shutdown()
+
+
+def fd_exchange(out_dir, group):
+    """The descriptor hand-over of the VMM symmetric heap (parallel/p2p.exchange_fds) with ordinary files standing in
+    for cuMem allocations: all-gather, then a broadcast from tower 0."""
+    from tensorflowdistributedlearning_b200.parallel.p2p import exchange_fds
+
+    path = os.path.join(out_dir, f"fdx_{group.rank}.txt")
+    with open(path, "w") as f:
+        f.write(f"tower {group.rank}")
+    fd = os.open(path, os.O_RDONLY)
+    got = exchange_fds(fd, group.rank, group.world, None)
+    texts = []
+    for r in range(group.world):
+        os.lseek(got[r], 0, os.SEEK_SET)
+        texts.append(os.read(got[r], 64).decode())
+        if r != group.rank:
+            os.close(got[r])
+    one = exchange_fds(fd if group.rank == 0 else None, group.rank, group.world, None, root=0)
+    os.lseek(one[0], 0, os.SEEK_SET)
+    root_text = os.read(one[0], 64).decode()
+    others_empty = all(one[r] is None for r in range(1, group.world))
+    if group.rank != 0:
+        os.close(one[0])
+    os.close(fd)
+    torch.save({"texts": texts, "root_text": root_text, "others_empty": others_empty},
+               os.path.join(out_dir, f"fd_exchange_w{group.world}_r{group.rank}.pt"))
     group.barrier()
     group.shutdown()
 

@@ -10,6 +10,8 @@ say ``ok``:
   train       -- ResNet-50 steps: p2p (eager, graph, overlap) vs the NCCL baseline path, mirrors identical
   resume      -- checkpoint at step 3 with the optimizer slots sharded over the towers, resume, compare with the
                  uninterrupted run (bit-equal on the deterministic optimizer path; rounding-level through the trainer)
+  nvls_small  -- buffers from the library's own VMM heap (cuMemCreate + descriptors over UNIX sockets + cuMulticast):
+                 peer mappings readable, NVLS fused step vs the fp32 reference (reports "unavailable" without multicast)
   dead_nccl   -- a tower exits mid-run on the NCCL path: the job ends with an error, nobody waits forever
 """
 import json
@@ -56,7 +58,7 @@ def _records(stdout):
 
 @needs2
 @pytest.mark.parametrize("world", WORLDS)
-@pytest.mark.parametrize("mode", ["correctness", "wire", "stress", "train", "resume"])
+@pytest.mark.parametrize("mode", ["correctness", "wire", "stress", "train", "resume", "nvls_small"])
 def test_p2p(world, mode):
     r = _launch(world, [mode])
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]

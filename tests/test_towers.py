@@ -76,3 +76,12 @@ def test_a_dead_tower_is_detected_not_waited_for(tmp_path):
     r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=300)
     assert r.returncode != 0
     assert not os.path.exists(os.path.join(tmp_path, "rank1_dies_w2_r0.pt"))  # tower 0 never reported success
+
+
+def test_descriptor_exchange_between_towers(tmp_path):
+    """The VMM symmetric heap shares its allocations as POSIX descriptors over UNIX sockets (parallel/p2p.py): the
+    all-gather form delivers every tower's descriptor to every tower, the broadcast form only tower 0's."""
+    for rec in _run(tmp_path, "fd_exchange", 3):
+        assert rec["texts"] == ["tower 0", "tower 1", "tower 2"]
+        assert rec["root_text"] == "tower 0" and rec["others_empty"]
+
