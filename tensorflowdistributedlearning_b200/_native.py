@@ -57,10 +57,15 @@ def needs_build() -> bool:
 
 def build(force: bool = False, verbose: bool = False) -> Path:
     """Compile every ``csrc/*.cu`` for sm_100a and link ``libtdl_b200.so`` (parallel nvcc -c)."""
-    with _lock:
-        if not force and not needs_build():
+    import fcntl
+
+    LIB_DIR.mkdir(parents=True, exist_ok=True)
+    # one builder at a time across PROCESSES too: the towers of a torchrun job import the package at the same moment,
+    # and a stale library would otherwise be rebuilt by all of them into the same object files
+    with _lock, open(LIB_DIR / ".build.lock", "w") as lock_file:
+        fcntl.flock(lock_file, fcntl.LOCK_EX)
+        if not force and not needs_build():  # (a tower that waited for the lock finds the library fresh)
             return LIB_PATH
-        LIB_DIR.mkdir(parents=True, exist_ok=True)
         obj_dir = LIB_DIR / "obj"
         obj_dir.mkdir(exist_ok=True)
         nvcc = _nvcc()
