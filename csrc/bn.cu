@@ -141,7 +141,7 @@ bn_finalize_stats_kernel(const float* __restrict__ partial, int nparts, int C, d
                          const float* __restrict__ gamma, const float* __restrict__ beta,
                          float* __restrict__ running_mean, float* __restrict__ running_var, float decay, float eps,
                          float* __restrict__ mean_out, float* __restrict__ invstd_out, float* __restrict__ scale_out,
-                         float* __restrict__ shift_out) {
+                         float* __restrict__ shift_out, const float* __restrict__ mean_offset) {
   ptx::pdl_trigger();
   ptx::pdl_wait();
   const int c = blockIdx.x * kFinCh + (threadIdx.x % kFinCh);
@@ -159,7 +159,10 @@ bn_finalize_stats_kernel(const float* __restrict__ partial, int nparts, int C, d
   invstd_out[c] = invstd;
   scale_out[c] = scale;
   shift_out[c] = b - (float)m * scale;
-  if (running_mean) running_mean[c] = decay * running_mean[c] + (1.f - decay) * (float)m;
+  // mean_offset: a per-channel constant the producer left OUT of the tensor because this normalisation removes it
+  // anyway (a folded convolution bias); the moving mean still has to see it
+  const float m_true = (float)m + (mean_offset ? mean_offset[c] : 0.f);
+  if (running_mean) running_mean[c] = decay * running_mean[c] + (1.f - decay) * m_true;
   if (running_var) running_var[c] = decay * running_var[c] + (1.f - decay) * (float)(var * unbias);
 }
 
@@ -525,7 +528,7 @@ TDL_API int tdl_bn_fwd_stats(const void* x, int64_t rows, int C, float* scratch,
   {
     cudaError_t _le = tdl::launch_pdl(bn_finalize_stats_kernel, dim3((C + kFinCh - 1) / kFinCh), dim3(kFinThreads), 0,
         st, scratch, s.gx, C, 1.0 / (double)rows, unbias, gamma, beta, running_mean, running_var, decay, eps, mean,
-        invstd, scale, shift);
+        invstd, scale, shift, (const float*)nullptr);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "bn_finalize_stats_kernel");
   }
   TDL_LAUNCH_OK("bn_finalize_stats_kernel");
@@ -534,19 +537,26 @@ TDL_API int tdl_bn_fwd_stats(const void* x, int64_t rows, int C, float* scratch,
 
 // Finish BatchNorm statistics from partial (sum, sumsq) rows produced elsewhere (tdl_conv2d_fprop_stats_bf16):
 // partial is [nparts][2][C] fp32 and `rows` is the number of pixels the sums cover.
-TDL_API int tdl_bn_finalize_partials(const float* partial, int nparts, int64_t rows, int C, const float* gamma,
-                                     const float* beta, float* running_mean, float* running_var, float decay,
-                                     float eps, float* mean, float* invstd, float* scale, float* shift, void* stream) {
+TDL_API int tdl_bn_finalize_partials_off(const float* partial, int nparts, int64_t rows, int C, const float* gamma,
+                                         const float* beta, float* running_mean, float* running_var, float decay,
+                                         float eps, float* mean, float* invstd, float* scale, float* shift,
+                                         const float* mean_offset, void* stream) {
   TDL_REQUIRE(C > 0 && nparts > 0 && rows > 0, "bad arguments");
   const double unbias = rows > 1 ? (double)rows / (double)(rows - 1) : 1.0;
   {
     cudaError_t _le = tdl::launch_pdl(bn_finalize_stats_kernel, dim3((C + kFinCh - 1) / kFinCh), dim3(kFinThreads), 0,
         (cudaStream_t)stream, partial, nparts, C, 1.0 / (double)rows, unbias, gamma, beta, running_mean, running_var,
-        decay, eps, mean, invstd, scale, shift);
+        decay, eps, mean, invstd, scale, shift, mean_offset);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "bn_finalize_stats_kernel");
   }
   TDL_LAUNCH_OK("bn_finalize_stats_kernel");
   return 0;
+}
+TDL_API int tdl_bn_finalize_partials(const float* partial, int nparts, int64_t rows, int C, const float* gamma,
+                                     const float* beta, float* running_mean, float* running_var, float decay,
+                                     float eps, float* mean, float* invstd, float* scale, float* shift, void* stream) {
+  return tdl_bn_finalize_partials_off(partial, nparts, rows, C, gamma, beta, running_mean, running_var, decay, eps,
+                                      mean, invstd, scale, shift, nullptr, stream);
 }
 
 TDL_API int tdl_bn_infer_scale_shift(const float* gamma, const float* beta, const float* running_mean,
@@ -1331,6 +1341,80 @@ TDL_API int tdl_bn_bwd_apply(const void* dz, const void* x, const void* z, int z
 }
 
 // ------------------------------------------------------------------------------------------------------------
+// BatchNorm WITHOUT activation in front of a 1x1 convolution, folded into that convolution (Xception's
+// depthwise -> BatchNorm -> pointwise, core/xception.py:184-210): conv(scale * y + shift) = conv'(y) + b' with
+// W'[k][c] = W[k][c] * scale[c] and b'[k] = b[k] + sum_c W[k][c] * shift[c].  The normalise pass over the activation
+// (one read + one write of the whole tensor) is replaced by a pass over the K x C weight matrix.
+// In backward the data gradient uses the ORIGINAL weights (it is the gradient w.r.t. the BatchNorm output, which the
+// BatchNorm backward kernels take as usual), and the weight gradient computed on the raw input y is corrected:
+// dW[k][c] = scale[c] * sum_px dz[px][k] y[px][c] + shift[c] * sum_px dz[px][k].
+// ------------------------------------------------------------------------------------------------------------
+namespace tdl {
+namespace bn {
+__global__ void __launch_bounds__(128)
+fold_affine_kernel(const float* __restrict__ w, const float* __restrict__ scale, const float* __restrict__ shift,
+                   const float* __restrict__ bias_in, bf16* __restrict__ wf, float* __restrict__ bias_out, int C) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
+  const int k = blockIdx.x;
+  const float* wr = w + (size_t)k * C;
+  bf16* out = wf + (size_t)k * C;
+  float acc = 0.f;
+  for (int c = threadIdx.x; c < C; c += 128) {
+    const float v = wr[c];
+    out[c] = __float2bfloat16(v * scale[c]);
+    acc = fmaf(v, shift[c], acc);
+  }
+  __shared__ float red[4];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) bias_out[k] = (bias_in ? bias_in[k] : 0.f) + red[0] + red[1] + red[2] + red[3];
+}
+
+__global__ void __launch_bounds__(256)
+fold_wgrad_fixup_kernel(float* __restrict__ dw, const float* __restrict__ scale, const float* __restrict__ shift,
+                        const float* __restrict__ dzsum, int K, int C) {
+  ptx::pdl_trigger();
+  ptx::pdl_wait();
+  const int64_t total = (int64_t)K * C;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    const int k = (int)(i / C);
+    dw[i] = dzsum ? fmaf(scale[c], dw[i], shift[c] * dzsum[k]) : scale[c] * dw[i];
+  }
+}
+}  // namespace bn
+}  // namespace tdl
+
+// w [K][C] fp32 master weights of a 1x1 convolution; wf [K][C] bf16 and bias_out [K] fp32 are written.
+TDL_API int tdl_conv1x1_fold_affine(const float* w, const float* scale, const float* shift, const float* bias_in,
+                                    void* wf, float* bias_out, int K, int C, void* stream) {
+  TDL_REQUIRE(K > 0 && C > 0, "empty weight matrix");
+  cudaError_t e = tdl::launch_pdl(tdl::bn::fold_affine_kernel, dim3(K), dim3(128), 0, (cudaStream_t)stream, w, scale,
+                                  shift, bias_in, (tdl::bf16*)wf, bias_out, C);
+  if (e != cudaSuccess) return tdl::cuda_fail(e, "fold_affine_kernel");
+  TDL_LAUNCH_OK("fold_affine_kernel");
+  return 0;
+}
+
+// In place on dw [K][C] (this step's raw weight gradient, nothing else accumulated into it yet); dzsum [K] = column
+// sums of the output gradient, or NULL when they are known to be zero (the convolution feeds a training-mode
+// BatchNorm: that BatchNorm's input gradient has zero mean per channel).
+TDL_API int tdl_conv1x1_fold_wgrad_fixup(float* dw, const float* scale, const float* shift, const float* dzsum, int K,
+                                         int C, void* stream) {
+  TDL_REQUIRE(K > 0 && C > 0, "empty weight matrix");
+  int64_t blocks = tdl::cdiv((int64_t)K * C, 256);
+  if (blocks > (int64_t)tdl::num_sms() * 8) blocks = (int64_t)tdl::num_sms() * 8;
+  cudaError_t e = tdl::launch_pdl(tdl::bn::fold_wgrad_fixup_kernel, dim3((unsigned)blocks), dim3(256), 0,
+                                  (cudaStream_t)stream, dw, scale, shift, dzsum, K, C);
+  if (e != cudaSuccess) return tdl::cuda_fail(e, "fold_wgrad_fixup_kernel");
+  TDL_LAUNCH_OK("fold_wgrad_fixup_kernel");
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------------------
 // Allocation-free variant of tdl_bn_fwd_stats.
 //
 // Some users of this library cannot hand us scratch memory because they cannot obtain any: processes whose
@@ -1414,7 +1498,7 @@ TDL_API int tdl_bn_fwd_stats_noalloc(const void* x, int64_t rows, int C, const f
   {
     cudaError_t _le = tdl::launch_pdl(bn_finalize_stats_kernel, dim3((C + kFinCh - 1) / kFinCh), dim3(kFinThreads), 0,
         st, scratch, s.gx, C, 1.0 / (double)rows, unbias, gamma, beta, running_mean, running_var, decay, eps, mean,
-        invstd, scale, shift);
+        invstd, scale, shift, (const float*)nullptr);
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "bn_finalize_stats_kernel");
   }
   TDL_LAUNCH_OK("bn_finalize_stats_kernel");

@@ -81,6 +81,12 @@ int tdl_bn_fwd_stats_noalloc(const void* x, int64_t rows, int C, const float* ga
 int tdl_bn_finalize_partials(const float* partial, int nparts, int64_t rows, int C, const float* gamma,
                              const float* beta, float* running_mean, float* running_var, float decay, float eps,
                              float* mean, float* invstd, float* scale, float* shift, void* stream);
+/* the same with mean_offset [C] (or NULL): a per-channel constant the producer left out of the tensor because this
+ * normalisation removes it (a folded convolution bias); only the moving mean sees it */
+int tdl_bn_finalize_partials_off(const float* partial, int nparts, int64_t rows, int C, const float* gamma,
+                                 const float* beta, float* running_mean, float* running_var, float decay, float eps,
+                                 float* mean, float* invstd, float* scale, float* shift, const float* mean_offset,
+                                 void* stream);
 int tdl_bn_infer_scale_shift(const float* gamma, const float* beta, const float* running_mean,
                              const float* running_var, float eps, float* scale, float* shift, int C, void* stream);
 /* mask_out (may be NULL): [rows][C/8] bytes, one bit per element = "pre-ReLU value > 0".  The backward entry points
@@ -262,6 +268,15 @@ int tdl_adam_flat(float* param, void* grad, float* m1, float* m2, void* shadow_b
                   float beta1, float beta2, float eps, float grad_scale, int grad_is_bf16, int zero_grad,
                   void* stream);
 int tdl_cast_f32_to_bf16(const float* src, void* dst, int64_t n, void* stream);
+
+/* BatchNorm (no activation) in front of a 1x1 convolution folded into the convolution: W' = W * scale (bf16),
+ * b' = b + W shift; and the matching correction of the weight gradient computed on the un-normalised input
+ * (dw = scale * dw + shift x dzsum, in place). */
+int tdl_conv1x1_fold_affine(const float* w /* [K][C] */, const float* scale, const float* shift,
+                            const float* bias_in /* or NULL */, void* wf_bf16, float* bias_out, int K, int C,
+                            void* stream);
+int tdl_conv1x1_fold_wgrad_fixup(float* dw /* [K][C] */, const float* scale, const float* shift,
+                                 const float* dzsum /* [K], or NULL = all zero */, int K, int C, void* stream);
 
 /* ---- symmetric heap on the CUDA VMM API with an NVLS multicast mapping (csrc/vmm_heap.cu) ----
  * One process per GPU.  Every tower: tdl_vmm_query -> pad the size to *granularity -> tdl_vmm_alloc (maps its own

@@ -56,7 +56,11 @@ class SeparableConv2dSame(TFModule):
         """``residual`` (the module's skip branch) is added inside the pointwise BatchNorm kernel."""
         if self.training:  # the depthwise kernel accumulates the statistics of its own output for dw_bn
             y, stats = self.depthwise(x, want_stats=True)
-            return self.pointwise(self.dw_bn(y, relu=self.relu, stats=stats), residual=residual)
+            # no activation between this BatchNorm and the pointwise conv: the normalise pass is folded into the
+            # pointwise weights instead of being run over the activation (ops/functional.batch_norm(defer_apply));
+            # 2 = the pointwise conv itself feeds a training-mode BatchNorm (its output gradient has zero column sums)
+            return self.pointwise(self.dw_bn(y, relu=self.relu, stats=stats, defer_apply=0 if self.relu else 2),
+                                  residual=residual)
         return self.pointwise(self.dw_bn(self.depthwise(x), relu=self.relu), residual=residual)
 
 

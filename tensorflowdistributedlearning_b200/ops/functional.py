@@ -25,6 +25,11 @@ _PREMASKED = {}
 # activation (its backward kernel zeroes the gradient where the activation is 0); the convolution then skips its own
 # masking pass.
 _RELU_DONE = {}
+_LAST_AFFINE = None
+_LAST_MEAN_OFFSET = None
+# BatchNorm without activation in front of a 1x1 convolution is folded into that convolution's weights (TDL_DEFER_BN=0
+# restores the separate normalise pass)
+_DEFER_BN = os.environ.get("TDL_DEFER_BN", "1") != "0"
 _LAST_RELU_MASK = None
 # BatchNorm -> consumer convolution hand-off for the fused backward reductions: the BatchNorm's output tensor carries
 # ``_tdl_bn_src`` (its input, batch statistics, affine, mask); the consumer's data-gradient kernel reduces
@@ -42,6 +47,12 @@ _FUSED_BN_HITS = 0
 # a serial latency chain in front of the streaming loop and cluster launches stream slower: ResNet-50 19.3 -> 32.1
 # ms/step, profiles/bn_fold_experiment.txt), so it is off unless TDL_BN_FOLD=1 asks for it.
 _BN_FOLD = os.environ.get("TDL_BN_FOLD", "0") == "1"
+
+
+def enable_defer_bn(flag: bool) -> None:
+    """BatchNorm without activation in front of a 1x1 convolution folded into the convolution (default on)."""
+    global _DEFER_BN
+    _DEFER_BN = bool(flag)
 
 
 def enable_bn_fold(flag: bool) -> None:
@@ -237,6 +248,24 @@ def conv_pads(h: int, w: int, kh: int, kw: int, stride: int, dil: int, padding) 
     return P, Q, pt, pb, pl, pr
 
 
+def _fold_wgrad_fixup(affine, dw_kc, dy, K):
+    """Weight gradient of a convolution whose input BatchNorm was folded into it (see _ConvNative.forward): the kernel
+    ran on the un-normalised input, dW = scale * dW_raw + shift x colsum(dy).  Same stream as the wgrad before it."""
+    if affine is None:
+        return
+    from . import native_ops as O
+
+    if affine[2]:
+        # the convolution feeds a training-mode BatchNorm: dy is that BatchNorm's input gradient, whose column sums are
+        # zero by construction -- the shift term vanishes and no pass over dy is needed
+        O.conv1x1_fold_wgrad_fixup_(dw_kc, affine[0], affine[1], None)
+        _count(1)
+        return
+    dzsum = O.colsum_(dy.view(-1, K), torch.zeros(K, dtype=torch.float32, device=dy.device))
+    O.conv1x1_fold_wgrad_fixup_(dw_kc, affine[0], affine[1], dzsum)
+    _count(2)
+
+
 class _ConvNative(torch.autograd.Function):
     """tcgen05 implicit-GEMM forward; dgrad = same kernel on flipped/transposed weights; wgrad = MN-major kernel."""
 
@@ -277,16 +306,32 @@ class _ConvNative(torch.autograd.Function):
                 _WPREP.drop_table()
         pt, pb, pl, pr = pads
         partials = None
+        # input = a BatchNorm output that was never written (batch_norm(defer_apply=True)): fold its scale / shift
+        # into this 1x1 convolution's weights; backward corrects the weight gradient (csrc/bn.cu, fold_* kernels)
+        ctx.affine = getattr(x, "_tdl_affine", None)
+        bias_eff = None if bias is None else bias.detach()
+        if ctx.affine is not None:
+            if not (taps == 1 and stride == 1 and pads == (0, 0, 0, 0) and residual is None and not want_tap):
+                raise RuntimeError("a deferred BatchNorm output may only feed a plain 1x1 stride-1 convolution")
+            wf, bias_eff = O.conv1x1_fold_affine(weight.detach().view(K, C), ctx.affine[0], ctx.affine[1], bias_eff)
+            prep_launches += 1
+            if ctx.affine[2]:
+                # the output goes into a training-mode BatchNorm, which removes any per-channel constant: leave the
+                # folded bias out of the tensor (the bias epilogue costs 45 % on these layers) and hand it to that
+                # BatchNorm's moving-mean update instead (conv2d() tags the output)
+                global _LAST_MEAN_OFFSET
+                _LAST_MEAN_OFFSET = bias_eff
+                bias_eff = None
         if want_stats:
             y, partials, nparts = O.conv2d_fprop_stats(x, wf, R=Rk, S=Sk, stride=stride, dil=dil, pad_h=pt, pad_w=pl,
-                                                       out_hw=out_hw, bias=None if bias is None else bias.detach(),
+                                                       out_hw=out_hw, bias=bias_eff,
                                                        residual=(None if residual is None
                                                                  else residual.detach().contiguous()), relu=relu_out)
             partials = partials[:nparts]
         else:
             # (+ residual) (+ ReLU) in the epilogue: the reference unit's relu(shortcut + conv3(...)), core/resnet.py:148
             y = O.conv2d_fprop(x, wf, R=Rk, S=Sk, stride=stride, dil=dil, pad_h=pt, pad_w=pl, out_hw=out_hw,
-                               bias=None if bias is None else bias.detach(),
+                               bias=bias_eff,
                                residual=None if residual is None else residual.detach().contiguous(), relu=relu_out)
         _count(1 + prep_launches)
         ctx.save_for_backward(x, wd if wd is not None else wf, y if relu_out else None)
@@ -380,16 +425,19 @@ class _ConvNative(torch.autograd.Function):
                     with torch.cuda.stream(side):
                         O.conv2d_wgrad(x, dy, wp.grad.view(K, Rk * Sk, C), R=Rk, S=Sk, stride=stride, dil=dil,
                                        pad_h=pt, pad_w=pl)
+                        _fold_wgrad_fixup(ctx.affine, wp.grad.view(K, C) if ctx.affine is not None else None, dy, K)
                     x.record_stream(side)   # keep the operands alive until the side stream is done with them
                     dy.record_stream(side)
                     _SIDE_DIRTY = True
                 else:
                     O.conv2d_wgrad(x, dy, wp.grad.view(K, Rk * Sk, C), R=Rk, S=Sk, stride=stride, dil=dil, pad_h=pt,
                                    pad_w=pl)
+                    _fold_wgrad_fixup(ctx.affine, wp.grad.view(K, C) if ctx.affine is not None else None, dy, K)
                 _notify(wp)
             else:
                 dw = torch.zeros((K, Rk * Sk, C), dtype=torch.float32, device=x.device)
                 O.conv2d_wgrad(x, dy, dw, R=Rk, S=Sk, stride=stride, dil=dil, pad_h=pt, pad_w=pl)
+                _fold_wgrad_fixup(ctx.affine, dw.view(K, C) if ctx.affine is not None else None, dy, K)
                 dw = dw.view(K, Rk, Sk, C)
             _count(1)
         if has_bias and ctx.needs_input_grad[2]:
@@ -564,6 +612,8 @@ def conv2d(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] =
         C = c
     assert c == C, f"channel mismatch: input {c} vs weight {C}"
     P, Q, pt, pb, pl, pr = conv_pads(h, w, Rk, Sk, stride, dil, padding)
+    if getattr(x, "_tdl_affine", None) is not None and not (_native_ok(x) and C % 8 == 0 and K % 8 == 0 and K > 4):
+        raise RuntimeError("a deferred BatchNorm output reached a convolution that cannot fold it")
     if (_native_ok(x) and c <= 4 and stride == 2 and dil == 1 and bias is None and K % 8 == 0 and K <= 64
             and max(Rk, Sk) <= 7 and not want_tap and _STEM_NATIVE and residual is None and not relu):
         out = _ConvStem.apply(x.contiguous(), weight, (pt, pb, pl, pr), (P, Q), want_stats)
@@ -577,8 +627,15 @@ def conv2d(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] =
             return _ConvNative.apply(x.contiguous(), weight, bias, stride, dil, (pt, pb, pl, pr), (P, Q), True, False,
                                      residual, relu)
         if (want_stats or want_tap) and residual is None and not relu:
+            global _LAST_MEAN_OFFSET
+            _LAST_MEAN_OFFSET = None
             out = _ConvNative.apply(x.contiguous(), weight, bias, stride, dil, (pt, pb, pl, pr), (P, Q), want_stats,
                                     want_tap)
+            if _LAST_MEAN_OFFSET is not None:
+                if not (want_stats and not want_tap):
+                    raise RuntimeError("a folded bias left out of the output needs the statistics-producing form")
+                out[0]._tdl_mean_offset = _LAST_MEAN_OFFSET
+                _LAST_MEAN_OFFSET = None
             if want_stats and want_tap:
                 return out
             if want_tap:
@@ -617,7 +674,7 @@ def conv2d(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] =
 class _BNNative(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, gamma, beta, running_mean, running_var, residual, decay, eps, relu, training, partials=None,
-                want_tap=False):
+                want_tap=False, defer=False):
         from . import native_ops as O
 
         ctx.gamma_param, ctx.beta_param = gamma, beta
@@ -647,9 +704,13 @@ class _BNNative(torch.autograd.Function):
             _LAST_BN_SRC = dict(x=x2, mean=mean, invstd=invstd, scale=scale, shift=shift, relu=bool(relu),
                                 has_res=residual is not None)
             return (z.view(shape), x.view_as(x)) if want_tap else z.view(shape)
+        mean_offset = getattr(x, "_tdl_mean_offset", None)
+        if mean_offset is not None and not (training and partials is not None and not _BN_FOLD):
+            raise RuntimeError("the producer left a folded bias out of this tensor: training-mode BatchNorm with the "
+                               "producer's partial statistics is the only valid consumer")
         if training and partials is not None:
             mean, invstd, scale, shift = O.bn_finalize_partials(partials, partials.shape[0], x2.shape[0], gamma, beta,
-                                                                running_mean, running_var, decay, eps)
+                                                                running_mean, running_var, decay, eps, mean_offset)
             _count(1)
         elif training:
             mean, invstd, scale, shift = O.bn_fwd_stats(x2, gamma, beta, running_mean, running_var, decay, eps)
@@ -658,13 +719,19 @@ class _BNNative(torch.autograd.Function):
             scale, shift = O.bn_infer_scale_shift(gamma, beta, running_mean, running_var, eps)
             mean = invstd = None
             _count(1)
-        if need_z:
+        if defer:
+            # The only consumer is a 1x1 convolution that folds scale / shift into its weights (_ConvNative): the
+            # normalised tensor is never written.  The output is an alias of the input; batch_norm() tags it.
+            assert training and not relu and residual is None and not want_tap
+            z, zmask = x2, None
+        elif need_z:
             # with a residual the ReLU mask cannot be recomputed from x alone: keep it as 1 bit per element (written by
             # the same kernel) instead of making both backward kernels re-read the whole activation
             z, zmask = O.bn_apply(x2, scale, shift, r2, relu, want_mask=True)
+            _count(1)
         else:
             z, zmask = O.bn_apply(x2, scale, shift, r2, relu), None
-        _count(1)
+            _count(1)
         if training:
             ctx.save_for_backward(x2, zmask, scale, shift, mean, invstd)
         ctx.cfg = (relu, residual is not None, training, shape)
@@ -673,6 +740,10 @@ class _BNNative(torch.autograd.Function):
                              has_res=residual is not None) if training else None)
         # want_tap: an alias of the input for an identity shortcut -- its gradient comes back to THIS node and is added
         # inside the backward apply kernel (no separate elementwise add; core/resnet.py:71-87,126-148)
+        if defer:
+            global _LAST_AFFINE
+            _LAST_AFFINE = (scale, shift, defer == 2)
+            return x.view_as(x)
         return (z.view(shape), x.view_as(x)) if want_tap else z.view(shape)
 
     @staticmethod
@@ -732,13 +803,18 @@ class _BNNative(torch.autograd.Function):
             dgamma = dbeta = None
         return (dx.view(shape), dgamma if ctx.needs_input_grad[1] else None,
                 dbeta if ctx.needs_input_grad[2] else None, None, None,
-                dres.view(shape) if has_res else None, None, None, None, None, None, None)
+                dres.view(shape) if has_res else None, None, None, None, None, None, None, None)
 
 
 def batch_norm(x: torch.Tensor, gamma, beta, running_mean, running_var, *, decay: float, eps: float,
                training: bool, relu: bool = False, residual: Optional[torch.Tensor] = None,
-               stats: Optional[torch.Tensor] = None, want_tap: bool = False):
+               stats: Optional[torch.Tensor] = None, want_tap: bool = False, defer_apply: bool = False):
     """y = relu?(BN(x) + residual?) over the last (channel) axis with TF fused-BN semantics.
+    ``defer_apply=True`` (training, no activation, no residual; the ONLY consumer must be a 1x1 stride-1 convolution
+    through :func:`conv2d`): the normalise pass is skipped, the result is an alias of ``x`` tagged with (scale, shift)
+    and the convolution folds them into its weights (Xception depthwise -> BN -> pointwise).  ``defer_apply=2``
+    additionally promises that the convolution's OUTPUT feeds a training-mode BatchNorm (so its output gradient has
+    zero column sums and the weight-gradient correction needs no pass over it).
     ``stats``: partial statistics of ``x`` from ``conv2d(..., want_stats=True)`` (skips the statistics pass).
     ``want_tap=True`` -> (y, x_alias): feed ``x_alias`` to an identity shortcut and its gradient is added inside this
     BatchNorm's backward kernel instead of by a separate elementwise add."""
@@ -751,6 +827,16 @@ def batch_norm(x: torch.Tensor, gamma, beta, running_mean, running_var, *, decay
         xin = x.contiguous()
         if xin is not x and getattr(x, "_tdl_relu_out", False):
             xin._tdl_relu_out = True
+        global _LAST_AFFINE
+        _LAST_AFFINE = None
+        defer = (defer_apply and training and torch.is_grad_enabled() and not relu and res is None and not want_tap
+                 and not _BN_FOLD and _DEFER_BN)
+        if defer:
+            out = _BNNative.apply(xin, gamma, beta, running_mean, running_var, None, decay, eps, False, True, stats,
+                                  False, 2 if defer_apply == 2 else 1)
+            out._tdl_affine = _LAST_AFFINE
+            _LAST_AFFINE = _LAST_BN_SRC = _LAST_RELU_MASK = None
+            return out
         if want_tap and training and torch.is_grad_enabled():
             out, tap = _BNNative.apply(xin, gamma, beta, running_mean, running_var, res, decay, eps, relu, training,
                                        stats, True)

@@ -127,7 +127,7 @@ class BatchNorm(TFModule):
         self.register_buffer("moving_variance", torch.ones(cp))
 
     def forward(self, x: torch.Tensor, relu: bool = False, residual: Optional[torch.Tensor] = None,
-                stats: Optional[torch.Tensor] = None, want_tap: bool = False):
+                stats: Optional[torch.Tensor] = None, want_tap: bool = False, defer_apply: bool = False):
         if stats is None and self.training:
             # partial statistics the producing kernel left on the tensor (e.g. a unit tail relu(shortcut + conv3))
             stats = getattr(x, "_tdl_stats", None)
@@ -135,7 +135,7 @@ class BatchNorm(TFModule):
                 stats = None
         return TF.batch_norm(x, self.gamma, self.beta, self.moving_mean, self.moving_variance, decay=self.decay,
                              eps=self.eps, training=self.training, relu=relu, residual=residual, stats=stats,
-                             want_tap=want_tap)
+                             want_tap=want_tap, defer_apply=defer_apply)
 
     def tf_variables(self):
         d = {f"{self.scope}/beta": (self.beta, "plain", (self.c,)),

@@ -138,12 +138,15 @@ def conv2d_fprop_stats(x: torch.Tensor, w: torch.Tensor, *, R: int, S: int, stri
 
 
 def bn_finalize_partials(partials: torch.Tensor, nparts: int, rows: int, gamma, beta, running_mean, running_var,
-                         decay: float, eps: float):
+                         decay: float, eps: float, mean_offset: Optional[torch.Tensor] = None):
+    """``mean_offset`` [C]: a constant per channel that is missing from the tensor the partial sums describe (a folded
+    convolution bias); it is added to the batch mean for the moving-mean update only."""
     C = partials.shape[-1]
     out = torch.empty((4, C), dtype=torch.float32, device=partials.device)
-    rc = N.lib().tdl_bn_finalize_partials(N.ptr(partials), _i(nparts), _i64(rows), _i(C), N.ptr(gamma), N.ptr(beta),
-                                          N.ptr(running_mean), N.ptr(running_var), _f(decay), _f(eps), N.ptr(out[0]),
-                                          N.ptr(out[1]), N.ptr(out[2]), N.ptr(out[3]), N.stream_ptr())
+    rc = N.lib().tdl_bn_finalize_partials_off(N.ptr(partials), _i(nparts), _i64(rows), _i(C), N.ptr(gamma),
+                                              N.ptr(beta), N.ptr(running_mean), N.ptr(running_var), _f(decay), _f(eps),
+                                              N.ptr(out[0]), N.ptr(out[1]), N.ptr(out[2]), N.ptr(out[3]),
+                                              N.ptr(mean_offset), N.stream_ptr())
     N.check(rc, "tdl_bn_finalize_partials")
     return out[0], out[1], out[2], out[3]
 
@@ -832,6 +835,31 @@ def depthwise3x3_dgrad_s2(dy, w9c, xmask, in_shape, pad_h, pad_w):
                                            _i(p), _i(q), _i(pad_h), _i(pad_w), N.stream_ptr())
     N.check(rc, "tdl_depthwise3x3_dgrad_s2")
     return dx
+
+
+def conv1x1_fold_affine(w_kc: torch.Tensor, scale: torch.Tensor, shift: torch.Tensor,
+                        bias: Optional[torch.Tensor] = None):
+    """BatchNorm (no activation) folded into the 1x1 convolution that follows: returns (W * scale as bf16 [K, 1, C],
+    bias + W @ shift as fp32 [K]).  ``w_kc``: fp32 master weights [K, C]."""
+    K, C = w_kc.shape
+    assert w_kc.dtype == torch.float32 and w_kc.is_contiguous()
+    wf = torch.empty((K, 1, C), dtype=torch.bfloat16, device=w_kc.device)
+    b = torch.empty((K,), dtype=torch.float32, device=w_kc.device)
+    rc = N.lib().tdl_conv1x1_fold_affine(N.ptr(w_kc), N.ptr(scale), N.ptr(shift), N.ptr(bias), N.ptr(wf), N.ptr(b),
+                                         _i(K), _i(C), N.stream_ptr())
+    N.check(rc, "tdl_conv1x1_fold_affine")
+    return wf, b
+
+
+def conv1x1_fold_wgrad_fixup_(dw_kc: torch.Tensor, scale: torch.Tensor, shift: torch.Tensor, dzsum: torch.Tensor):
+    """In place: dw[k][c] = scale[c] * dw[k][c] + shift[c] * dzsum[k] (weight gradient of the folded convolution);
+    ``dzsum=None``: the column sums are known to be zero."""
+    K, C = dw_kc.shape
+    assert dw_kc.dtype == torch.float32 and dw_kc.is_contiguous()
+    rc = N.lib().tdl_conv1x1_fold_wgrad_fixup(N.ptr(dw_kc), N.ptr(scale), N.ptr(shift), N.ptr(dzsum), _i(K), _i(C),
+                                              N.stream_ptr())
+    N.check(rc, "tdl_conv1x1_fold_wgrad_fixup")
+    return dw_kc
 
 
 def colsum_(dy2d: torch.Tensor, out: torch.Tensor) -> torch.Tensor:

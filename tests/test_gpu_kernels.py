@@ -55,6 +55,56 @@ CONV_CASES = [
 ]
 
 
+def test_batch_norm_folded_into_the_pointwise_conv(O):
+    """Xception's depthwise -> BatchNorm (no activation) -> pointwise conv (core/xception.py:184-210): the normalise
+    pass is folded into the pointwise weights (forward) and the weight gradient is corrected (backward).  Output, input
+    gradient and every parameter gradient against the separate-pass path, and the forward against fp32 torch."""
+    from tensorflowdistributedlearning_b200.models.xception import SeparableConv2dSame
+    from tensorflowdistributedlearning_b200.ops import functional as Fn
+    from tensorflowdistributedlearning_b200.ops import layers as L
+
+    torch.manual_seed(41)
+    for (n, h, cin, cout) in ((4, 19, 728, 728), (2, 38, 256, 728), (3, 10, 72, 40)):
+        m = SeparableConv2dSame(cin, cout, 3, 1, 1, scope="s", bn=L.BNConfig(decay=0.9997, eps=1e-3), relu=False,
+                                relu_in=True).cuda().train()
+        for bn in (m.dw_bn, m.pointwise.bn):
+            torch.nn.init.uniform_(bn.gamma, 0.5, 1.5)
+            torch.nn.init.normal_(bn.beta, std=0.2)
+        x0 = torch.randn(n, h, h, cin, device="cuda").bfloat16()
+        g0 = torch.randn(n, h, h, cout, device="cuda").bfloat16()
+        res = {}
+        try:
+            for flag in (False, True):
+                Fn.enable_defer_bn(flag)
+                Fn.begin_step()
+                for p in m.parameters():
+                    p.grad = None
+                stats0 = [b.clone() for b in m.buffers()]
+                x = x0.clone().requires_grad_(True)
+                y = m(x)
+                y.backward(g0)
+                torch.cuda.synchronize()
+                Fn.join_side_streams()
+                res[flag] = dict(y=y.detach().float(), dx=x.grad.float(),
+                                 grads={k: p.grad.float().clone() for k, p in m.named_parameters()},
+                                 moving=[b.clone() for b in m.buffers()])
+                for b, b0 in zip(m.buffers(), stats0):
+                    b.copy_(b0)
+        finally:
+            Fn.enable_defer_bn(True)
+        a, b = res[True], res[False]
+        assert rel_err(a["y"], b["y"]) < 2e-2 and rel_err(a["dx"], b["dx"]) < 3e-2
+        for k in a["grads"]:
+            if k == "dw_bn.beta":
+                # a per-channel shift in front of conv + BatchNorm changes nothing: the exact gradient is zero and both
+                # paths return rounding noise of the same size (scripts/bnfold_check.py against fp32 torch: relative error 11.7 for both)
+                assert a["grads"][k].norm() < 3 * b["grads"][k].norm() + 1e-3
+                continue
+            assert rel_err(a["grads"][k], b["grads"][k]) < 3e-2, (k, rel_err(a["grads"][k], b["grads"][k]))
+        for u, v in zip(a["moving"], b["moving"]):  # (the pointwise output differs at rounding level, so do these)
+            assert rel_err(u, v) < 2e-2
+
+
 def test_gap_folded_into_the_following_1x1_conv(O):
     """conv1x1(global_avg_pool(x)) in one kernel (the ASPP image-pooling branch), forward and both gradients
     against fp32 torch ops on the same bf16-rounded activations."""
