@@ -17,6 +17,8 @@ except Exception as e:
     print("bench FAILED", e)
 PY
 if [ "$N" = "8" ]; then
+  $TR --master-port 29525 scripts/p2p_check.py nvls_small > $OUT/nvls_small.log 2>&1; grep "^{" $OUT/nvls_small.log | cut -c1-200
+  $TR --master-port 29526 bench.py --gpus $N --steps 20 --warmup 5 --comm nvls --no-secondary > $OUT/bench_nvls.json 2> $OUT/bench_nvls.err; cut -c1-230 $OUT/bench_nvls.json
   $TR --master-port 29524 bench.py --model resnet152 --gpus $N --steps 10 --warmup 3 > $OUT/bench_resnet152.json 2> $OUT/bench_resnet152.err; cut -c1-220 $OUT/bench_resnet152.json
   rm -f gpurun_out/p2p_check.jsonl
   $TR --master-port 29521 scripts/p2p_check.py sweep2 > $OUT/sweep2.log 2>&1
