@@ -511,7 +511,7 @@ __global__ void __launch_bounds__(kT)
 depthwise3x3_tma_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_mask,
                         const float* __restrict__ w, const float* __restrict__ bias, int has_mask,
                         bf16* __restrict__ y, const TShape s, int stages, int relu_in, int relu_out,
-                        float* __restrict__ stats) {
+                        float* __restrict__ stats, const bf16* __restrict__ addend) {
   ptx::pdl_trigger();
   ptx::pdl_wait();
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -601,6 +601,19 @@ depthwise3x3_tma_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
       parity ^= 1;
     }
     if (active) {
+      const int p = th_i * s.TH + ph;
+      const int q0 = tw_i * s.TW + pw0;
+      const int64_t oidx = ((((int64_t)n * s.P + p) * s.Q + q0) * s.C) + ch;
+      // data-gradient use: the other consumer's gradient of this strip, requested NOW so that the loads are in flight
+      // while the taps are computed (issued next to their use they cost a memory round trip per output pixel)
+      uint2 ad[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) ad[j] = make_uint2(0u, 0u);
+      if (addend != nullptr && p < s.P) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (q0 + j < s.Q) ad[j] = __ldg(reinterpret_cast<const uint2*>(addend + oidx + (int64_t)j * s.C));
+      }
       float acc[4][4];
 #pragma unroll
       for (int j = 0; j < 4; ++j)
@@ -655,10 +668,8 @@ depthwise3x3_tma_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
             }
         }
       }
-      const int p = th_i * s.TH + ph;
       if (p < s.P) {
-        const int q0 = tw_i * s.TW + pw0;
-        bf16* orow = y + ((((int64_t)n * s.P + p) * s.Q + q0) * s.C) + ch;
+        bf16* orow = y + oidx;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           if (q0 + j >= s.Q) break;
@@ -672,6 +683,12 @@ depthwise3x3_tma_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_c
             else lds4(min_, ph * s.TW + pw0 + j, cvec, m, false);
 #pragma unroll
             for (int c = 0; c < 4; ++c) acc[j][c] = m[c] > 0.f ? acc[j][c] : 0.f;
+          }
+          if (addend) {  // added unmasked, after the input-ReLU mask
+            acc[j][0] += __uint_as_float(ad[j].x << 16);
+            acc[j][1] += __uint_as_float(ad[j].x & 0xffff0000u);
+            acc[j][2] += __uint_as_float(ad[j].y << 16);
+            acc[j][3] += __uint_as_float(ad[j].y & 0xffff0000u);
           }
           tdl::dw::st4(orow + (int64_t)j * s.C, acc[j]);
           if (stats) {
@@ -926,7 +943,7 @@ TDL_API int tdl_depthwise3x3_tma_wgrad(const void* x, const void* dy, float* dw,
 static int depthwise3x3_tma_fwd_impl(const void* x, const float* w, const float* bias, const void* mask, void* y,
                                      int N, int H, int W, int C, int P, int Q, int stride, int dil, int pad_h,
                                      int pad_w, int relu_in, int relu_out, float* stats, int* nparts, void* stream,
-                                     int flip_taps = 0) {
+                                     int flip_taps = 0, const void* addend = nullptr) {
   using namespace tdl::dwt;
   TDL_REQUIRE(C % 8 == 0, "C must be a multiple of 8");
   TDL_REQUIRE((stride == 1 || stride == 2) && (dil == 1 || dil == 2) && !(stride == 2 && dil == 2),
@@ -969,7 +986,8 @@ static int depthwise3x3_tma_fwd_impl(const void* x, const float* w, const float*
       attr = true;                                                                                                   \
     }                                                                                                                \
     cudaError_t _le = tdl::launch_pdl(depthwise3x3_tma_kernel<S, D>, dim3(grid), dim3(kT), smem, st, tm, tmm, w, bias,     \
-                                      has_mask, (tdl::bf16*)y, s, stages, relu_in, relu_out, stats);                 \
+                                      has_mask, (tdl::bf16*)y, s, stages, relu_in, relu_out, stats,                  \
+                                      (const tdl::bf16*)addend);                                                     \
     if (_le != cudaSuccess) return tdl::cuda_fail(_le, "depthwise3x3_tma_kernel");                                   \
   } while (0)
   if (stride == 1 && dil == 1) TDL_DW_LAUNCH(1, 1);
@@ -990,10 +1008,13 @@ TDL_API int tdl_depthwise3x3_tma_fwd(const void* x, const float* w, const float*
 
 // Data gradient of a stride-1 depthwise layer = the forward kernel on dy with the taps read in reverse order
 // (`w` is the layer's own [9][C] weight tensor: no flipped copy), optionally masked by the input's ReLU.
-TDL_API int tdl_depthwise3x3_tma_dgrad(const void* dy, const float* w, const void* mask, void* dx, int N, int H, int W,
-                                       int C, int dil, int pad_h, int pad_w, void* stream) {
+// `addend` (optional, same shape as dx): added AFTER the mask -- the gradient that reaches the layer's input through
+// another consumer (an Xception module's skip connection), so no separate elementwise add runs.
+TDL_API int tdl_depthwise3x3_tma_dgrad(const void* dy, const float* w, const void* mask, const void* addend, void* dx,
+                                       int N, int H, int W, int C, int dil, int pad_h, int pad_w, void* stream) {
+  TDL_REQUIRE(addend == nullptr || (reinterpret_cast<uintptr_t>(addend) & 7) == 0, "addend must be 8-byte aligned");
   return depthwise3x3_tma_fwd_impl(dy, w, nullptr, mask, dx, N, H, W, C, H, W, 1, dil, pad_h, pad_w, 0, 0, nullptr,
-                                   nullptr, stream, 1);
+                                   nullptr, stream, 1, addend);
 }
 
 // Forward + per-CTA partial BatchNorm statistics of the bf16 output (for the BatchNorm that follows the depthwise conv in

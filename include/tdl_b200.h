@@ -178,9 +178,10 @@ int tdl_depthwise3x3_tma_fwd(const void* x, const float* w, const float* bias, c
                              int H, int W, int C, int P, int Q, int stride, int dil, int pad_h, int pad_w,
                              int relu_in, int relu_out, void* stream);
 /* data gradient of a stride-1 3x3 depthwise layer (same map size in and out): the forward kernel on dy with the taps of
- * the layer's own [9][C] weights read in reverse order; mask (optional): zero dx where mask <= 0 (input ReLU) */
-int tdl_depthwise3x3_tma_dgrad(const void* dy, const float* w, const void* mask, void* dx, int N, int H, int W, int C,
-                               int dil, int pad_h, int pad_w, void* stream);
+ * the layer's own [9][C] weights read in reverse order; mask (optional): zero dx where mask <= 0 (input ReLU);
+ * addend (optional, dx-shaped): added after the mask (the gradient arriving through another consumer of the input) */
+int tdl_depthwise3x3_tma_dgrad(const void* dy, const float* w, const void* mask, const void* addend, void* dx, int N,
+                               int H, int W, int C, int dil, int pad_h, int pad_w, void* stream);
 int tdl_depthwise3x3_tma_fwd_stats(const void* x, const float* w, const float* bias, void* y, int N, int H, int W, int C,
                                    int P, int Q, int stride, int dil, int pad_h, int pad_w, int relu_in, int relu_out,
                                    float* stats_partial /* [2*tdl_num_sms()][2][C] */, int* nparts_host, void* stream);

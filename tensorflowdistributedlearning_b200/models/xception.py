@@ -19,6 +19,8 @@ from __future__ import annotations
 
 from typing import List, Optional, Sequence
 
+import os
+
 import torch
 import torch.nn as nn
 import torch.nn.functional as F
@@ -52,8 +54,14 @@ class SeparableConv2dSame(TFModule):
         self.pointwise = ConvBNAct(cin, cout, 1, scope=f"{scope}_pointwise", bn=bn, relu=relu, init_std=0.06)
         self.relu = relu
 
-    def forward(self, x, residual=None):
-        """``residual`` (the module's skip branch) is added inside the pointwise BatchNorm kernel."""
+    def forward(self, x, residual=None, want_tap: bool = False):
+        """``residual`` (the module's skip branch) is added inside the pointwise BatchNorm kernel.
+        ``want_tap=True`` (training): returns (out, x_alias) -- the module's skip connection reads ``x_alias`` so that
+        its gradient is added inside the depthwise data-gradient kernel."""
+        if want_tap:
+            y, stats, tap = self.depthwise(x, want_stats=True, want_tap=True)
+            return self.pointwise(self.dw_bn(y, relu=self.relu, stats=stats, defer_apply=0 if self.relu else 2),
+                                  residual=residual), tap
         if self.training:  # the depthwise kernel accumulates the statistics of its own output for dw_bn
             y, stats = self.depthwise(x, want_stats=True)
             # no activation between this BatchNorm and the pointwise conv: the normalise pass is folded into the
@@ -90,6 +98,14 @@ class XceptionModule(TFModule):
     def forward(self, x):
         # the skip connection (core/xception.py:211-222) rides into the last pointwise conv's BatchNorm kernel as its
         # residual input instead of a separate elementwise add (that conv has no activation when there is a skip...
+        if (self.skip != "none" and not self.act_in_sep and self.training and torch.is_grad_enabled()
+                and os.environ.get("TDL_DW_TAP", "1") != "0"):
+            # the skip branch reads an alias of x handed out by the first depthwise conv, so that branch's gradient is
+            # added inside the depthwise data-gradient kernel (no aten::add per module in backward)
+            r, xa = self.convs[0](x, want_tap=True)
+            skip = self.shortcut(xa) if self.skip == "conv" else xa
+            r = self.convs[1](r)
+            return self.convs[2](r, residual=skip)
         skip = self.shortcut(x) if self.skip == "conv" else (x if self.skip == "sum" else None)
         if skip is not None and self.act_in_sep:
             # ...unless the unit applies ReLU inside its separable convs: then the sum must stay outside the activation

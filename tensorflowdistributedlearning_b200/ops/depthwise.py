@@ -20,8 +20,10 @@ from . import reference as R
 
 class _DepthwiseNative(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, stride, dil, pads, out_hw, relu, relu_in, want_stats=False):
+    def forward(ctx, x, weight, bias, stride, dil, pads, out_hw, relu, relu_in, want_stats=False, want_tap=False):
         from . import native_ops as O
+
+        ctx.want_tap = bool(want_tap)
 
         kh, kw, C = weight.shape
         fast = kh == 3 and kw == 3
@@ -41,20 +43,26 @@ class _DepthwiseNative(torch.autograd.Function):
         ctx.weight_param, ctx.bias_param = weight, bias
         ctx.set_materialize_grads(False)  # no zero-fill for the (non-differentiable) statistics output
         ctx.cfg = (stride, dil, pads, relu, relu_in, bias is not None, fast)
+        outs = [y]
         if want_stats:
             if partials is None:  # shape not served by the fused kernel: an empty marker the caller maps to "no stats"
                 partials = torch.empty(0, device=x.device)
             ctx.mark_non_differentiable(partials)
-            return y, partials
-        return y
+            outs.append(partials)
+        if want_tap:
+            # an alias of the input for the enclosing module's skip connection: its gradient comes back to THIS node
+            # and is added inside the data-gradient kernel (after the input-ReLU mask) instead of by aten::add
+            outs.append(x.view_as(x))
+        return outs[0] if len(outs) == 1 else tuple(outs)
 
     @staticmethod
-    def backward(ctx, dy, *_):
+    def backward(ctx, dy, *rest):
         from . import native_ops as O
 
         x, weight, y = ctx.saved_tensors
+        d_tap = rest[-1] if (ctx.want_tap and rest and rest[-1] is not None) else None
         if dy is None:
-            return (None,) * 10
+            return (d_tap,) + (None,) * 10
         stride, dil, pads, relu, relu_in, has_bias, fast = ctx.cfg
         dy = dy.contiguous()
         kh, kw, C = weight.shape
@@ -98,7 +106,9 @@ class _DepthwiseNative(torch.autograd.Function):
                 if stride == 1 and not relu:
                     n, h, w, _ = x.shape
                     dx = O.depthwise3x3_dgrad_s1(dy, wd.contiguous().view(9, C), x if relu_in else None, dil,
-                                                 2 * dil - pads[0], 2 * dil - pads[2])
+                                                 2 * dil - pads[0], 2 * dil - pads[2],
+                                                 addend=None if d_tap is None else d_tap.contiguous())
+                    d_tap = None
                 elif stride == 2 and dil == 1 and not relu:
                     dx = O.depthwise3x3_dgrad_s2(dy, wd.view(9, C), x if relu_in else None, tuple(x.shape), pads[0],
                                                  pads[2])
@@ -113,11 +123,14 @@ class _DepthwiseNative(torch.autograd.Function):
             if relu_in:
                 dx = dx * (x > 0)
             TF._count(2)
-        return dx, dw, (db if has_bias else None), None, None, None, None, None, None, None
+        if d_tap is not None:
+            dx = d_tap if dx is None else dx + d_tap
+        return dx, dw, (db if has_bias else None), None, None, None, None, None, None, None, None
 
 
 def depthwise_conv2d(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None, stride: int = 1,
-                     dil: int = 1, padding="SAME", relu: bool = False, relu_in: bool = False, want_stats: bool = False):
+                     dil: int = 1, padding="SAME", relu: bool = False, relu_in: bool = False, want_stats: bool = False,
+                     want_tap: bool = False):
     """x [N,H,W,C], weight [kh,kw,C] -> [N,P,Q,C]; optional ReLU on the input, fused bias + ReLU on the output.
 
     ``want_stats=True`` returns ``(y, stats)``: ``stats`` are the partial BatchNorm statistics of ``y`` accumulated by the
@@ -125,6 +138,15 @@ def depthwise_conv2d(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch
     kh, kw, C = weight.shape
     n, h, w, c = x.shape
     P, Q, pt, pb, pl, pr = TF.conv_pads(h, w, kh, kw, stride, dil, padding)
+    if want_tap:
+        # (y, stats_or_None, x_alias): feed x_alias to whatever else reads x (a skip connection) and that gradient is
+        # added inside this layer's data-gradient kernel
+        if TF._native_ok(x) and C % 8 == 0 and torch.is_grad_enabled():
+            y, st, tap = _DepthwiseNative.apply(x.contiguous(), weight, bias, stride, dil, (pt, pb, pl, pr), (P, Q),
+                                                relu, relu_in, True, True)
+            return y, (st if st.numel() else None), tap
+        out = depthwise_conv2d(x, weight, bias, stride, dil, padding, relu, relu_in, True)
+        return out[0], out[1], x
     if TF._native_ok(x) and C % 8 == 0:
         if want_stats:
             y, st = _DepthwiseNative.apply(x.contiguous(), weight, bias, stride, dil, (pt, pb, pl, pr), (P, Q), relu,

@@ -189,11 +189,12 @@ class DepthwiseConv2d(TFModule):
         R.truncated_normal_(self.weight.data, init_std)
         self.bias = nn.Parameter(torch.zeros(c)) if use_bias else None
 
-    def forward(self, x, want_stats: bool = False):
+    def forward(self, x, want_stats: bool = False, want_tap: bool = False):
+        """``want_tap=True`` -> (y, stats_or_None, x_alias), see :func:`ops.depthwise.depthwise_conv2d`."""
         from . import depthwise as DW
 
         return DW.depthwise_conv2d(x, self.weight, self.bias, self.stride, self.rate, self.padding, self.relu,
-                                   self.relu_in, want_stats)
+                                   self.relu_in, want_stats, want_tap)
 
     def tf_variables(self):
         d = {f"{self.scope}/depthwise_weights": (self.weight, "depthwise")}

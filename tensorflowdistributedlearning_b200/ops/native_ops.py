@@ -654,18 +654,23 @@ def depthwise3x3_fwd(x, w9c, bias, mask, stride, dil, pad_h, pad_w, out_hw, relu
     return (y, None) if want_stats else y
 
 
-def depthwise3x3_dgrad_s1(dy, w9c, mask, dil, pad_h, pad_w):
+def depthwise3x3_dgrad_s1(dy, w9c, mask, dil, pad_h, pad_w, addend=None):
     """Data gradient of a stride-1 3x3 depthwise layer: ``w9c`` are the layer's own [9, C] fp32 weights (the kernel
     reads the taps in reverse order); ``pad_h/pad_w`` are the gradient problem's pads (2*dil - forward pad);
-    ``mask``: zero where mask <= 0.  Falls back to the generic kernel on a flipped copy for other dilations."""
+    ``mask``: zero where mask <= 0; ``addend`` (dx-shaped bf16): added after the mask inside the kernel.  Falls back
+    to the generic kernel on a flipped copy for other dilations."""
     _chk_bf16_nhwc(dy, "dy")
     n, h, w, c = dy.shape
     if not (c % 8 == 0 and dil in (1, 2)):
-        return depthwise3x3_fwd(dy, w9c.view(3, 3, c).flip(0, 1).contiguous().view(9, c), None, mask, 1, dil, pad_h,
-                                pad_w, (h, w), False, False)
+        dx = depthwise3x3_fwd(dy, w9c.view(3, 3, c).flip(0, 1).contiguous().view(9, c), None, mask, 1, dil, pad_h,
+                              pad_w, (h, w), False, False)
+        return dx if addend is None else dx + addend
     dx = torch.empty_like(dy)
-    rc = N.lib().tdl_depthwise3x3_tma_dgrad(N.ptr(dy), N.ptr(w9c), N.ptr(mask), N.ptr(dx), _i(n), _i(h), _i(w), _i(c),
-                                            _i(dil), _i(pad_h), _i(pad_w), N.stream_ptr())
+    if addend is not None:
+        _chk_bf16_nhwc(addend, "addend")
+        assert addend.shape == dy.shape
+    rc = N.lib().tdl_depthwise3x3_tma_dgrad(N.ptr(dy), N.ptr(w9c), N.ptr(mask), N.ptr(addend), N.ptr(dx), _i(n), _i(h),
+                                            _i(w), _i(c), _i(dil), _i(pad_h), _i(pad_w), N.stream_ptr())
     N.check(rc, "tdl_depthwise3x3_tma_dgrad")
     return dx
 
