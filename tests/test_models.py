@@ -169,3 +169,33 @@ def test_weight_prep_table_layout_matches_the_c_abi():
     assert tuple(rec[0])[3:] == (40, 9, 72, 3, 2, 0)
     assert rec[1][2] == 0 and tuple(rec[1])[3:] == (64, 1, 33, 2, 2, 0)
     assert starts.tolist() == [0, 3 * 2 * 9] and total == 3 * 2 * 9 + 2 * 2 * 1
+
+
+def test_xception_module_skip_tap_is_only_plumbing(monkeypatch):
+    """The skip branch of an Xception module may read an alias handed out by the first depthwise conv (so that its
+    gradient is added inside that layer's data-gradient kernel on the GPU).  On the torch path the alias is the input
+    itself: outputs and all gradients are identical with the tap on and off, for both skip types."""
+    import torch
+
+    from tensorflowdistributedlearning_b200.models.xception import XceptionModule
+    from tensorflowdistributedlearning_b200.ops.layers import BNConfig
+
+    for skip, stride, cin in (("sum", 1, 16), ("conv", 2, 8)):
+        torch.manual_seed(3)
+        m = XceptionModule(cin, [16, 16, 16], skip, stride, [1, 1, 1], 1, False, "u", BNConfig()).train()
+        x0 = torch.randn(2, 9, 9, cin)
+        res = []
+        for tap in ("1", "0"):
+            monkeypatch.setenv("TDL_DW_TAP", tap)
+            stats = [b.clone() for b in m.buffers()]
+            for p in m.parameters():
+                p.grad = None
+            x = x0.clone().requires_grad_(True)
+            y = m(x)
+            y.square().sum().backward()
+            res.append((y.detach(), x.grad.clone(), [p.grad.clone() for p in m.parameters()]))
+            for b, b0 in zip(m.buffers(), stats):
+                b.copy_(b0)
+        assert torch.equal(res[0][0], res[1][0]) and torch.allclose(res[0][1], res[1][1], atol=1e-6)
+        for a, b in zip(res[0][2], res[1][2]):
+            assert torch.allclose(a, b, atol=1e-5)
