@@ -471,10 +471,12 @@ bn_bwd_apply_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ x, con
 }
 
 // grid for the "thread owns a channel column" elementwise kernels
-static ReduceShape apply_shape(int64_t rows, int C) {
+// per_sm = CTAs of the kernel that fit on one SM: the grid is capped at ONE wave of them (threads loop over rows), a
+// grid of 8 per SM for a 4-per-SM kernel ran a second, partly filled wave of tiny CTAs on the small layers
+static ReduceShape apply_shape(int64_t rows, int C, int per_sm = 4) {
   ReduceShape s = reduce_shape(rows, C);
   int64_t want = cdiv(rows, (int64_t)s.ty * 4);
-  int64_t cap = (int64_t)num_sms() * 8 / s.gy;
+  int64_t cap = (int64_t)num_sms() * per_sm / s.gy;
   if (cap < 1) cap = 1;
   if (want > cap) want = cap;
   if (want < 1) want = 1;
@@ -1309,10 +1311,10 @@ TDL_API int tdl_bn_bwd_apply_ex(const void* dz, const void* x, const void* z, in
   TDL_REQUIRE(C > 0 && C % 8 == 0, "C must be a positive multiple of 8");
   TDL_REQUIRE(ld_dz >= C && ld_dz % 8 == 0, "ld_dz must be a multiple of 8, at least C");
   if (rows == 0) return 0;
-  ReduceShape s = apply_shape(rows, C);
+  const bool extra = addend != nullptr || mask_by_x != 0;
+  ReduceShape s = apply_shape(rows, C, extra ? 2 : 4);  // the addend / mask variants need 68-94 registers
   dim3 grid(s.gx, s.gy);
   const int mode = mask_mode(relu, z, z_is_bitmask);
-  const bool extra = addend != nullptr || mask_by_x != 0;
   const float inv_n = 1.f / (float)rows;
   cudaError_t e;
 #define TDL_BN_BWD_T(M_, D_, X_)                                                                                     \
