@@ -1798,7 +1798,11 @@ __global__ void __launch_bounds__(256)
 weight_prep_batched_kernel(const WPrepDesc* __restrict__ descs, const int* __restrict__ block_start, int nlayers) {
   ptx::pdl_trigger();
   ptx::pdl_wait();
-  __shared__ float tile[32][33];
+  // One 64 (Cout) x 64 (Cin) tile of one tap per block, two elements per access on both sides: 8-byte loads of the
+  // fp32 master, 4-byte bf16x2 stores of the forward copy, and after the transpose through shared memory 4-byte stores
+  // of the data-gradient copy (128 contiguous bytes per warp instruction everywhere).  The 32 x 32 scalar version
+  // moved 2-byte elements: 92 us for ResNet-50's 100 MB of weights against ~30 us of traffic.
+  __shared__ __nv_bfloat16 tile[64][66];
   int lo = 0, hi = nlayers - 1;
   const int b = blockIdx.x;
   while (lo < hi) {  // last layer whose first block is <= b
@@ -1813,22 +1817,27 @@ weight_prep_batched_kernel(const WPrepDesc* __restrict__ descs, const int* __res
   const int kt = local % d.ktiles;
   const int t = local / d.ktiles;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const int c0 = ct * 32, k0 = kt * 32;
-  for (int j = ty; j < 32; j += 8) {
-    const int k = k0 + j, c = c0 + tx;
-    if (k < d.K && c < d.C) {
+  const int c0 = ct * 64, k0 = kt * 64;
+  for (int j = ty; j < 64; j += 8) {
+    const int k = k0 + j, c = c0 + 2 * tx;
+    if (k < d.K && c < d.C) {  // C and K are even: a pair is all-in or all-out
       const size_t i = ((size_t)k * d.taps + t) * d.C + c;
-      const float v = d.w[i];
-      tile[j][tx] = v;
-      d.wf[i] = __float2bfloat16(v);
+      const float2 v = *reinterpret_cast<const float2*>(d.w + i);
+      const __nv_bfloat162 h = __floats2bfloat162_rn(v.x, v.y);
+      *reinterpret_cast<__nv_bfloat162*>(&tile[j][2 * tx]) = h;
+      *reinterpret_cast<__nv_bfloat162*>(d.wf + i) = h;
     }
   }
   if (d.wd == nullptr) return;  // uniform across the block
   __syncthreads();
-  for (int j = ty; j < 32; j += 8) {
-    const int c = c0 + j, k = k0 + tx;
-    if (k < d.K && c < d.C)
-      d.wd[((size_t)c * d.taps + (d.taps - 1 - t)) * d.K + k] = __float2bfloat16(tile[tx][j]);
+  for (int j = ty; j < 64; j += 8) {
+    const int c = c0 + j, k = k0 + 2 * tx;
+    if (k < d.K && c < d.C) {
+      __nv_bfloat162 h;
+      h.x = tile[2 * tx][j];
+      h.y = tile[2 * tx + 1][j];
+      *reinterpret_cast<__nv_bfloat162*>(d.wd + ((size_t)c * d.taps + (d.taps - 1 - t)) * d.K + k) = h;
+    }
   }
 }
 
@@ -2787,7 +2796,7 @@ TDL_API int tdl_conv2d_weight_prep(const float* w, void* w_fprop, void* w_dgrad,
 }
 
 // Batched form: `descs` is a device array of nlayers 48-byte records {const float* w; bf16* wf; bf16* wd (may be
-// null); int K, taps, C, ctiles = ceil(C/32), ktiles = ceil(K/32), 0}; block_start[l] = sum over earlier layers of
+// null); int K, taps, C, ctiles = ceil(C/64), ktiles = ceil(K/64), 0}; block_start[l] = sum over earlier layers of
 // ctiles * ktiles * taps (device, nlayers ints); total_blocks = the full sum.
 TDL_API int tdl_conv2d_weight_prep_batched(const void* descs, const int* block_start, int nlayers, int total_blocks,
                                            void* stream) {

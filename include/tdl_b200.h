@@ -197,8 +197,8 @@ int tdl_depthwise3x3_wgrad(const void* x, const void* dy, const void* ymask, flo
  * (tdl_conv_stem_weight_elems gives the element count).  K <= 64.  Optional fused BatchNorm partial statistics as in
  * tdl_conv2d_fprop_stats_bf16 (pass both stats pointers or neither). */
 /* Every layer's weight re-layout in one launch.  descs: device array of nlayers 48-byte records
- * {const float* w; bf16* wf; bf16* wd (NULL = no data-gradient copy); int K, taps, C, ceil(C/32), ceil(K/32), 0};
- * block_start: device int[nlayers], prefix sums of ceil(C/32) * ceil(K/32) * taps; total_blocks: the full sum. */
+ * {const float* w; bf16* wf; bf16* wd (NULL = no data-gradient copy); int K, taps, C, ceil(C/64), ceil(K/64), 0} (C, K even; w 8-byte aligned);
+ * block_start: device int[nlayers], prefix sums of ceil(C/64) * ceil(K/64) * taps; total_blocks: the full sum. */
 int tdl_conv2d_weight_prep_batched(const void* descs, const int* block_start, int nlayers, int total_blocks,
                                    void* stream);
 int tdl_conv_stem_pack(const void* x, void* planes, int N, int H, int W, int C, void* stream);

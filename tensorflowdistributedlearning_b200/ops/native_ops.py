@@ -755,7 +755,8 @@ def build_weight_prep_table(entries):
     dev = entries[0][0].device
     for i, (w, wf, wd, K, taps, C) in enumerate(entries):
         assert w.dtype == torch.float32 and w.is_contiguous() and wf.dtype == torch.bfloat16
-        ct, kt = (C + 31) // 32, (K + 31) // 32
+        assert C % 2 == 0 and K % 2 == 0 and w.data_ptr() % 8 == 0 and wf.data_ptr() % 4 == 0
+        ct, kt = (C + 63) // 64, (K + 63) // 64  # 64 x 64 tiles (csrc/conv_tcgen05.cu, weight_prep_batched_kernel)
         rec[i] = (w.data_ptr(), wf.data_ptr(), 0 if wd is None else wd.data_ptr(), K, taps, C, ct, kt, 0)
         starts.append(total)
         total += ct * kt * taps
