@@ -58,13 +58,12 @@ def fd_exchange(out_dir, group):
     got = exchange_fds(fd, group.rank, group.world, None)
     texts = []
     for r in range(group.world):
-        os.lseek(got[r], 0, os.SEEK_SET)
-        texts.append(os.read(got[r], 64).decode())
+        # pread: a descriptor received through SCM_RIGHTS shares its file offset with the sender's and the other towers'
+        texts.append(os.pread(got[r], 64, 0).decode())
         if r != group.rank:
             os.close(got[r])
     one = exchange_fds(fd if group.rank == 0 else None, group.rank, group.world, None, root=0)
-    os.lseek(one[0], 0, os.SEEK_SET)
-    root_text = os.read(one[0], 64).decode()
+    root_text = os.pread(one[0], 64, 0).decode()
     others_empty = all(one[r] is None for r in range(1, group.world))
     if group.rank != 0:
         os.close(one[0])

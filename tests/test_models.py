@@ -159,16 +159,16 @@ def test_weight_prep_table_layout_matches_the_c_abi():
 
     from tensorflowdistributedlearning_b200.ops import native_ops as O
 
-    w1, w2 = torch.zeros(40, 9, 72), torch.zeros(64, 1, 33)
-    f1, f2 = torch.zeros(40, 9, 72, dtype=torch.bfloat16), torch.zeros(64, 1, 33, dtype=torch.bfloat16)
+    w1, w2 = torch.zeros(40, 9, 72), torch.zeros(130, 1, 34)
+    f1, f2 = torch.zeros(40, 9, 72, dtype=torch.bfloat16), torch.zeros(130, 1, 34, dtype=torch.bfloat16)
     d1 = torch.zeros(72, 9, 40, dtype=torch.bfloat16)
-    descs, starts, total = O.build_weight_prep_table([(w1, f1, d1, 40, 9, 72), (w2, f2, None, 64, 1, 33)])
+    descs, starts, total = O.build_weight_prep_table([(w1, f1, d1, 40, 9, 72), (w2, f2, None, 130, 1, 34)])
     assert descs.dtype == torch.uint8 and descs.numel() == 2 * 48
     rec = np.frombuffer(descs.numpy().tobytes(), dtype=np.dtype("<u8,<u8,<u8,<i4,<i4,<i4,<i4,<i4,<i4"))
     assert rec[0][0] == w1.data_ptr() and rec[0][1] == f1.data_ptr() and rec[0][2] == d1.data_ptr()
-    assert tuple(rec[0])[3:] == (40, 9, 72, 3, 2, 0)
-    assert rec[1][2] == 0 and tuple(rec[1])[3:] == (64, 1, 33, 2, 2, 0)
-    assert starts.tolist() == [0, 3 * 2 * 9] and total == 3 * 2 * 9 + 2 * 2 * 1
+    assert tuple(rec[0])[3:] == (40, 9, 72, 2, 1, 0)          # 64 x 64 tiles: ceil(72 / 64), ceil(40 / 64)
+    assert rec[1][2] == 0 and tuple(rec[1])[3:] == (130, 1, 34, 1, 3, 0)
+    assert starts.tolist() == [0, 2 * 1 * 9] and total == 2 * 1 * 9 + 1 * 3 * 1
 
 
 def test_xception_module_skip_tap_is_only_plumbing(monkeypatch):
