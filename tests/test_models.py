@@ -199,3 +199,26 @@ def test_xception_module_skip_tap_is_only_plumbing(monkeypatch):
         assert torch.equal(res[0][0], res[1][0]) and torch.allclose(res[0][1], res[1][1], atol=1e-6)
         for a, b in zip(res[0][2], res[1][2]):
             assert torch.allclose(a, b, atol=1e-5)
+
+
+def test_batch_norm_fold_algebra():
+    """The identities behind folding a BatchNorm (no activation) into the 1x1 convolution that follows it
+    (csrc/bn.cu fold_* kernels): forward conv(scale*y + shift) = conv'(y) + W shift with W' = W * scale; weight
+    gradient dW = scale * (dz^T y) + shift x colsum(dz); data gradient w.r.t. the BatchNorm output = dz W (original W)."""
+    torch.manual_seed(9)
+    y = torch.randn(50, 12, dtype=torch.float64)
+    W = torch.randn(7, 12, dtype=torch.float64, requires_grad=True)
+    scale = torch.rand(12, dtype=torch.float64) + 0.5
+    shift = torch.randn(12, dtype=torch.float64)
+    bn_out = (y * scale + shift).requires_grad_(True)
+    z = bn_out @ W.t()
+    dz = torch.randn_like(z)
+    z.backward(dz)
+    z_fold = y @ (W.detach() * scale).t() + W.detach() @ shift
+    assert torch.allclose(z_fold, z.detach(), atol=1e-10)
+    dW_fold = scale * (dz.t() @ y) + shift[None, :] * dz.sum(0)[:, None]
+    assert torch.allclose(dW_fold, W.grad, atol=1e-10)
+    assert torch.allclose(dz @ W.detach(), bn_out.grad, atol=1e-10)
+    # a training-mode BatchNorm behind the convolution makes colsum(dz) vanish and removes W shift from the output
+    zc = z.detach() - z.detach().mean(0)
+    assert torch.allclose((y @ (W.detach() * scale).t()) - (y @ (W.detach() * scale).t()).mean(0), zc, atol=1e-10)
